@@ -1,0 +1,124 @@
+"""ctypes binding of the CPU oracle (TEST INFRASTRUCTURE ONLY).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
+may import this module.  The product package never does.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+REPO = os.path.dirname(_HERE)
+sys.path.insert(0, os.path.join(REPO, "tools"))
+from model_layout import (  # noqa: E402
+    DEFAULT_MODEL_PATH, DEFINES, MODEL_DTYPE, PARAMS_DTYPE, load_model, oracle_dtypes,
+)
+
+LIB_PATH = os.path.join(_HERE, "_build", "libhmj_oracle.so")
+_structs, ORC_DEFINES = oracle_dtypes()
+DATA_DTYPE = _structs["orc_data_t"]
+
+
+def build(force: bool = False) -> str:
+    if force or not os.path.exists(LIB_PATH):
+        subprocess.check_call(["make", "-C", _HERE, "_build/libhmj_oracle.so"], stdout=subprocess.DEVNULL)
+    return LIB_PATH
+
+
+def _ptr(a: np.ndarray):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class Oracle:
+    """Single-environment oracle: owns a model blob, a params struct and an orc_data_t."""
+
+    def __init__(self, model_path: str = DEFAULT_MODEL_PATH):
+        self.lib = C.CDLL(build())
+        self.model = load_model(model_path).copy()
+        assert self.lib.orc_sizeof_model() == MODEL_DTYPE.itemsize
+        assert self.lib.orc_sizeof_params() == PARAMS_DTYPE.itemsize
+        assert self.lib.orc_sizeof_data() == DATA_DTYPE.itemsize, (self.lib.orc_sizeof_data(), DATA_DTYPE.itemsize)
+        self.params = np.zeros(1, dtype=PARAMS_DTYPE)
+        self.data = np.zeros(1, dtype=DATA_DTYPE)
+        self.lib.orc_default_params(_ptr(self.model), _ptr(self.params))
+        self.lib.orc_reset_data(_ptr(self.model), _ptr(self.data))
+        self.lib.orc_norm.restype = C.c_double
+        self.lib.orc_cost_value.restype = C.c_double
+
+    # ---- convenience accessors
+    @property
+    def d(self):
+        return self.data[0]
+
+    @property
+    def p(self):
+        return self.params[0]
+
+    def reset(self):
+        self.lib.orc_reset_data(_ptr(self.model), _ptr(self.data))
+
+    def set_state(self, qpos, qvel, ctrl=None, warmstart=None, time=None):
+        self.data["qpos"][0] = qpos
+        self.data["qvel"][0] = qvel
+        if ctrl is not None:
+            self.data["ctrl"][0] = ctrl
+        if warmstart is not None:
+            self.data["qacc_warmstart"][0] = warmstart
+        if time is not None:
+            self.data["time"][0] = time
+
+    def call(self, name: str):
+        getattr(self.lib, name)(_ptr(self.model), _ptr(self.params), _ptr(self.data))
+
+    def forward(self):
+        self.call("orc_forward")
+
+    def step(self, n: int = 1):
+        return self.lib.orc_step_n(_ptr(self.model), _ptr(self.params), _ptr(self.data), int(n))
+
+    def contacts(self):
+        n = int(self.d["ncon"])
+        return self.d["contact"][:n]
+
+    # ---- mjpc pieces
+    def spline_sample(self, times, values, interpolation, t):
+        times = np.ascontiguousarray(times, dtype=np.float64)
+        values = np.ascontiguousarray(values, dtype=np.float64)
+        n = times.shape[0]
+        dim = values.shape[1] if n else 1
+        out = np.zeros(dim)
+        self.lib.orc_spline_sample(_ptr(times), _ptr(values), n, dim, int(interpolation), C.c_double(t), _ptr(out))
+        return out
+
+    def norm(self, x, params, ntype):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        prm = np.zeros(3)
+        prm[: len(params)] = params
+        return float(self.lib.orc_norm(_ptr(x), _ptr(prm), x.size, int(ntype)))
+
+    def cost_value(self, residual):
+        r = np.ascontiguousarray(residual, dtype=np.float64)
+        return float(self.lib.orc_cost_value(_ptr(self.model), _ptr(r)))
+
+    def rollout(self, state, time, spline_times, spline_values, horizon, interpolation=2):
+        ns, nu, nr = DEFINES["HMJ_NSTATE"], DEFINES["HMJ_NU"], DEFINES["HMJ_NRESIDUAL"]
+        state = np.ascontiguousarray(state, dtype=np.float64)
+        st = np.ascontiguousarray(spline_times, dtype=np.float64)
+        sv = np.ascontiguousarray(spline_values, dtype=np.float64)
+        out = {
+            "states": np.zeros((horizon, ns)), "actions": np.zeros((horizon, nu)), "times": np.zeros(horizon),
+            "residual": np.zeros((horizon, nr)), "costs": np.zeros(horizon), "trace": np.zeros((horizon, 3)),
+        }
+        tot = C.c_double(0)
+        fail = self.lib.orc_rollout(
+            _ptr(self.model), _ptr(self.params), _ptr(state), C.c_double(time), _ptr(st), _ptr(sv), st.shape[0],
+            int(interpolation), int(horizon), _ptr(out["states"]), _ptr(out["actions"]), _ptr(out["times"]),
+            _ptr(out["residual"]), _ptr(out["costs"]), _ptr(out["trace"]), C.byref(tot))
+        out["total_return"] = tot.value
+        out["failure"] = bool(fail)
+        return out
