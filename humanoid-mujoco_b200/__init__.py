@@ -1,0 +1,22 @@
+"""humanoid-mujoco_b200 — B200-native batched humanoid physics-and-rollout engine.
+
+Host-side mirror of the two reference seams:
+  * `BatchedHumanoidEnv` — the CPUEnv reset/step/observation contract (simulation/cpu_env.py) over N
+    lock-step environments;
+  * `SamplingPlanner` — mjpc's predictive-sampling planner (mjpc/planners/sampling/planner.cc) with
+    `Rollouts` running as a CUDA grid over samples.
+Both call the same C ABI (include/hmj_b200.h) through ctypes.  There is no CPU fallback: importing the
+package is cheap, creating a batch without the CUDA library or a GPU raises.
+
+The directory name has a hyphen (it is the name the build contract asks for); import it as
+`humanoid_mujoco_b200` (see humanoid_mujoco_b200.py at the repo root).
+"""
+from ._lib import HmjError, lib_path, load_library  # noqa: F401
+from .batch import HumanoidBatch, default_params, load_model  # noqa: F401
+from .env import BatchedHumanoidEnv  # noqa: F401
+from .planner import SamplingPlanner, SamplingPolicy, TimeSpline  # noqa: F401
+
+__all__ = [
+    "HmjError", "load_library", "lib_path", "HumanoidBatch", "default_params", "load_model",
+    "BatchedHumanoidEnv", "SamplingPlanner", "SamplingPolicy", "TimeSpline",
+]

@@ -1,0 +1,232 @@
+"""HumanoidBatch — thin object wrapper over the hmj_batch_* C ABI (include/hmj_b200.h).
+
+Plays the role of (MjModel, MjData) x N in the reference (simulation/cpu_env.py:86,397): state in,
+`step`/`forward`, state and derived quantities out.  numpy in / numpy out; device pointers are
+exposed for zero-copy torch interop.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import re
+
+import numpy as np
+
+from ._lib import check, load_library
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_HEADER = os.path.join(os.path.dirname(_HERE), "include", "hmj_model.h")
+MODEL_PATH = os.path.join(_HERE, "assets", "humanoid_model.bin")
+
+_CTYPES = {"int32_t": np.int32, "double": np.float64, "float": np.float32}
+
+
+def _parse_header(path):
+    """numpy dtypes of the POD structs in include/hmj_model.h (C alignment)."""
+    src = re.sub(r"/\*.*?\*/", "", open(path).read(), flags=re.S)
+    defines, types, structs = {}, dict(_CTYPES), {}
+    for m in re.finditer(r"#define\s+(HMJ_\w+)\s+(.+)", src):
+        try:
+            defines[m.group(1)] = int(eval(m.group(2).strip(), {}, dict(defines)))  # noqa: S307 (own header)
+        except Exception:
+            pass
+    for sm in re.finditer(r"typedef struct \w+ \{(.*?)\} (\w+);", src, re.S):
+        fields = []
+        for stmt in sm.group(1).split(";"):
+            stmt = stmt.strip()
+            if not stmt:
+                continue
+            m = re.match(r"(\w+)\s+(.*)", stmt, re.S)
+            for d in m.group(2).split(","):
+                dm = re.match(r"(\w+)((?:\[[^\]]+\])*)$", d.strip())
+                dims = tuple(int(eval(x, {}, dict(defines))) for x in re.findall(r"\[([^\]]+)\]", dm.group(2)))  # noqa: S307
+                fields.append((dm.group(1), types[m.group(1)], dims) if dims else (dm.group(1), types[m.group(1)]))
+        structs[sm.group(2)] = types[sm.group(2)] = np.dtype(fields, align=True)
+    return structs, defines
+
+
+_STRUCTS, DEFINES = _parse_header(_HEADER)
+MODEL_DTYPE = _STRUCTS["hmj_model_t"]
+PARAMS_DTYPE = _STRUCTS["hmj_params_t"]
+CONTACT_DTYPE = _STRUCTS["hmj_contact_t"]
+
+NQ, NV, NU = DEFINES["HMJ_NQ"], DEFINES["HMJ_NV"], DEFINES["HMJ_NU"]
+MAXCON = DEFINES["HMJ_MAXCON"]
+
+_ARRAY_SHAPES = {
+    "qpos": (NQ,), "qvel": (NV,), "time": (), "warmstart": (NV,), "ctrl": (NU,), "xfrc": (6,),
+    "geom_xpos": (DEFINES["HMJ_NGEOM"], 3), "geom_xmat": (DEFINES["HMJ_NGEOM"], 9), "cdof": (NV, 6), "com": (3,),
+    "qM": (DEFINES["HMJ_NM"],), "qfrc_smooth": (NV,), "qacc_smooth": (NV,), "qacc": (NV,), "qfrc_constraint": (NV,),
+    "sens": (16,), "residual": (DEFINES["HMJ_NRESIDUAL"],), "cost_sum": (), "cost_last": (), "trace": (3,), "returns": (),
+}
+_INT_ARRAYS = {"ncon", "nefc", "niter", "status", "xfrc_body"}
+
+
+def load_model(path: str = MODEL_PATH) -> np.ndarray:
+    raw = np.fromfile(path, dtype=np.uint8)
+    if raw.size != MODEL_DTYPE.itemsize:
+        raise ValueError(f"model blob is {raw.size} bytes, expected sizeof(hmj_model_t) = {MODEL_DTYPE.itemsize}")
+    m = raw.view(MODEL_DTYPE)
+    if int(m["magic"][0]) != DEFINES["HMJ_MAGIC"] or int(m["version"][0]) != DEFINES["HMJ_VERSION"]:
+        raise ValueError("model blob magic/version mismatch: re-run tools/compile_model.py")
+    return m.copy()
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def default_params(model: np.ndarray, n: int = 1) -> np.ndarray:
+    """hmj_params_t x n initialised from the model (the un-randomised MjModel fields)."""
+    lib = load_library()
+    p = np.zeros(1, dtype=PARAMS_DTYPE)
+    check(lib.hmj_default_params(_p(model), _p(p)))
+    return np.repeat(p, n)
+
+
+class HumanoidBatch:
+    """N lock-step humanoid simulations on one GPU."""
+
+    def __init__(self, n_envs: int, device: int = 0, model: np.ndarray | None = None):
+        self.lib = load_library()
+        self.model = load_model() if model is None else model
+        self.n = int(n_envs)
+        self.device = int(device)
+        h = C.c_void_p()
+        check(self.lib.hmj_batch_create(_p(self.model), self.n, self.device, C.byref(h)))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.lib.hmj_batch_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- parameters / state
+    def default_params(self) -> np.ndarray:
+        return default_params(self.model, self.n)
+
+    def set_params(self, params: np.ndarray, first: int = 0):
+        params = np.ascontiguousarray(params, dtype=PARAMS_DTYPE)
+        check(self.lib.hmj_batch_set_params(self._h, _p(params), first, params.shape[0]))
+
+    def get_params(self) -> np.ndarray:
+        out = np.zeros(self.n, dtype=PARAMS_DTYPE)
+        check(self.lib.hmj_batch_get_params(self._h, _p(out), 0, self.n))
+        return out
+
+    def _f64(self, a, shape):
+        if a is None:
+            return None
+        a = np.ascontiguousarray(a, dtype=np.float64)
+        if a.shape != (self.n,) + shape:
+            a = np.ascontiguousarray(np.broadcast_to(a, (self.n,) + shape))
+        return a
+
+    def set_state(self, qpos=None, qvel=None, time=None, warmstart=None):
+        a = [self._f64(qpos, (NQ,)), self._f64(qvel, (NV,)), self._f64(time, ()), self._f64(warmstart, (NV,))]
+        check(self.lib.hmj_batch_set_state(self._h, *[_p(x) for x in a]))
+
+    def get_state(self):
+        qpos, qvel = np.zeros((self.n, NQ)), np.zeros((self.n, NV))
+        time, ws = np.zeros(self.n), np.zeros((self.n, NV))
+        check(self.lib.hmj_batch_get_state(self._h, _p(qpos), _p(qvel), _p(time), _p(ws)))
+        return qpos, qvel, time, ws
+
+    def set_ctrl(self, ctrl):
+        check(self.lib.hmj_batch_set_ctrl(self._h, _p(self._f64(ctrl, (NU,)))))
+
+    def set_xfrc(self, body, wrench):
+        body = np.ascontiguousarray(np.broadcast_to(np.asarray(body, dtype=np.int32), (self.n,)))
+        check(self.lib.hmj_batch_set_xfrc(self._h, _p(body), _p(self._f64(wrench, (6,)))))
+
+    # ---- stepping
+    def step(self, ctrl=None, nsteps: int = 1):
+        check(self.lib.hmj_batch_step(self._h, _p(self._f64(ctrl, (NU,))), int(nsteps)))
+
+    def step_dev(self, ctrl_ptr: int | None = None, nsteps: int = 1):
+        check(self.lib.hmj_batch_step_dev(self._h, C.c_void_p(ctrl_ptr) if ctrl_ptr else None, int(nsteps)))
+
+    def forward(self):
+        check(self.lib.hmj_batch_forward(self._h))
+
+    def run_stage(self, stage: int):
+        check(self.lib.hmj_batch_run_stage(self._h, int(stage)))
+
+    def sync(self):
+        check(self.lib.hmj_batch_sync(self._h))
+
+    # ---- results
+    def get(self, name: str) -> np.ndarray:
+        if name in _INT_ARRAYS:
+            out = np.zeros(self.n, dtype=np.int32)
+        else:
+            out = np.zeros((self.n,) + _ARRAY_SHAPES[name])
+        check(self.lib.hmj_batch_get_array(self._h, name.encode(), _p(out), out.nbytes))
+        return out
+
+    def set(self, name: str, value):
+        if name in _INT_ARRAYS:
+            a = np.ascontiguousarray(np.broadcast_to(np.asarray(value, dtype=np.int32), (self.n,)))
+        else:
+            a = self._f64(value, _ARRAY_SHAPES[name])
+        check(self.lib.hmj_batch_set_array(self._h, name.encode(), _p(a), a.nbytes))
+
+    def contacts(self):
+        ncon = np.zeros(self.n, dtype=np.int32)
+        con = np.zeros((self.n, MAXCON), dtype=CONTACT_DTYPE)
+        check(self.lib.hmj_batch_get_contacts(self._h, _p(ncon), _p(con)))
+        return ncon, con
+
+    def device_ptr(self, name: str) -> int:
+        p = self.lib.hmj_batch_device_ptr(self._h, name.encode())
+        if not p:
+            raise KeyError(name)
+        return int(p)
+
+    @property
+    def stream(self) -> int:
+        return int(self.lib.hmj_batch_stream(self._h) or 0)
+
+    @property
+    def kernel_launches(self) -> int:
+        return int(self.lib.hmj_batch_kernel_launches(self._h))
+
+    # ---- env epilogue
+    def obs_reward(self, prev_action, latest_action, noise=None, max_sim_time=np.inf):
+        obs, rew = np.zeros((self.n, 30)), np.zeros(self.n)
+        term, trunc, selfc = (np.zeros(self.n, dtype=np.int32) for _ in range(3))
+        check(self.lib.hmj_env_obs_reward(
+            self._h, _p(self._f64(prev_action, (NU,))), _p(self._f64(latest_action, (NU,))), _p(self._f64(noise, (31,))),
+            float(max_sim_time), _p(obs), _p(rew), _p(term), _p(trunc), _p(selfc)))
+        return obs, rew, term.astype(bool), trunc.astype(bool), selfc.astype(bool)
+
+    # ---- planner rollouts
+    def plan_rollouts(self, state, time, spline_times, spline_values, horizon, interpolation=2, record=False):
+        state = np.ascontiguousarray(state, dtype=np.float64)
+        st = np.ascontiguousarray(spline_times, dtype=np.float64)
+        sv = np.ascontiguousarray(spline_values, dtype=np.float64)
+        assert sv.shape == (self.n, st.shape[0], NU), sv.shape
+        ret = np.zeros(self.n)
+        fail = np.zeros(self.n, dtype=np.int32)
+        check(self.lib.hmj_plan_rollouts(self._h, _p(state), float(time), _p(st), _p(sv), st.shape[0], int(interpolation),
+                                         int(horizon), int(bool(record)), _p(ret), _p(fail)))
+        return ret, fail.astype(bool)
+
+    def plan_argmin(self):
+        cost, idx = C.c_double(0), C.c_int32(0)
+        check(self.lib.hmj_plan_argmin(self._h, C.byref(cost), C.byref(idx)))
+        return cost.value, idx.value
+
+    def plan_fetch(self, sample: int, horizon: int):
+        ns, nr = DEFINES["HMJ_NSTATE"], DEFINES["HMJ_NRESIDUAL"]
+        out = {"states": np.zeros((horizon, ns)), "actions": np.zeros((horizon, NU)), "times": np.zeros(horizon),
+               "residual": np.zeros((horizon, nr)), "costs": np.zeros(horizon), "trace": np.zeros((horizon, 3))}
+        check(self.lib.hmj_plan_fetch(self._h, int(sample), int(horizon), _p(out["states"]), _p(out["actions"]), _p(out["times"]),
+                                      _p(out["residual"]), _p(out["costs"]), _p(out["trace"])))
+        return out

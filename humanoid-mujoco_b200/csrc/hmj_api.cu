@@ -1,0 +1,611 @@
+// hmj_api.cu — host side of the C ABI declared in include/hmj_b200.h.
+// Owns device buffers, derived lookup tables and one CUDA stream per batch; every entry point
+// returns an int status and never throws.  The product path: there is no CPU fallback — if CUDA
+// is unavailable every call fails with HMJ_ERR_CUDA.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/hmj_b200.h"
+#include "hmj_dev.cuh"
+
+static thread_local char g_err[512] = "";
+
+static int fail(int code, const char* fmt, const char* detail = "") {
+  snprintf(g_err, sizeof(g_err), fmt, detail);
+  return code;
+}
+
+#define CK(call)                                                                    \
+  do {                                                                              \
+    cudaError_t e_ = (call);                                                        \
+    if (e_ != cudaSuccess) return fail(HMJ_ERR_CUDA, "CUDA error: %s", cudaGetErrorString(e_)); \
+  } while (0)
+
+struct ArrayInfo { void* ptr; size_t bytes; };
+
+struct hmj_batch_ {
+  int n = 0;
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  hmj_tables_t* tab_dev = nullptr;
+  hmj_task_t* task_dev = nullptr;
+  hmj_tables_t* tab_host = nullptr;
+  hmj_buffers_t buf{};
+  std::vector<void*> allocs;
+  std::map<std::string, ArrayInfo> arrays;
+  // planner scratch
+  double* state_dev = nullptr;       // [37]
+  double* spline_times_dev = nullptr;// [64]
+  double* spline_values_dev = nullptr; size_t spline_values_cap = 0;
+  double* returns_dev = nullptr;     // [N]
+  int32_t* failure_dev = nullptr;    // [N]
+  double* argmin_dev = nullptr;      // [2]
+  hmj_record_t rec{};
+  int rec_cap = 0;
+  // env scratch
+  double* env_stage = nullptr; size_t env_stage_cap = 0;
+  int launches = 0;
+};
+
+extern "C" const char* hmj_last_error(void) { return g_err; }
+extern "C" int hmj_version(void) { return HMJ_VERSION; }
+extern "C" int hmj_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+  return n;
+}
+
+extern "C" int hmj_default_params(const hmj_model_t* m, hmj_params_t* p) {
+  if (!m || !p) return fail(HMJ_ERR_ARG, "null argument%s");
+  memset(p, 0, sizeof(*p));
+  p->timestep = m->timestep;
+  memcpy(p->body_mass, m->body_mass, sizeof(p->body_mass));
+  memcpy(p->dof_armature, m->dof_armature, sizeof(p->dof_armature));
+  memcpy(p->jnt_range, m->jnt_range, sizeof(p->jnt_range));
+  memcpy(p->jnt_margin, m->jnt_margin, sizeof(p->jnt_margin));
+  memcpy(p->jnt_stiffness, m->jnt_stiffness, sizeof(p->jnt_stiffness));
+  memcpy(p->act_gainprm0, m->act_gainprm0, sizeof(p->act_gainprm0));
+  memcpy(p->act_forcerange, m->act_forcerange, sizeof(p->act_forcerange));
+  memcpy(p->floor_friction, m->geom_friction[0], sizeof(p->floor_friction));
+  memcpy(p->hfield_data, m->hfield_data, sizeof(p->hfield_data));
+  return HMJ_OK;
+}
+
+static void build_tables(const hmj_model_t* m, hmj_tables_t* t) {
+  memset(t, 0, sizeof(*t));
+  t->m = *m;
+  // levels
+  int maxd = 0;
+  for (int b = 0; b < HMJ_NBODY; b++) maxd = m->body_depth[b] > maxd ? m->body_depth[b] : maxd;
+  t->nlevel = maxd + 1;
+  for (int b = 0; b < HMJ_NBODY; b++) {
+    int L = m->body_depth[b];
+    t->level_body[L][t->level_n[L]++] = b;
+  }
+  // subtree ranges (DFS numbering: descendants are contiguous)
+  for (int b = 0; b < HMJ_NBODY; b++) {
+    int e = b + 1;
+    while (e < HMJ_NBODY) {
+      int a = e;
+      while (a > b) a = m->body_parentid[a];
+      if (a != b) break;
+      e++;
+    }
+    t->subtree_end[b] = e;
+  }
+  for (int i = 0; i < HMJ_NV; i++) {
+    int adr = m->dof_Madr[i];
+    for (int j = i; j >= 0; j = m->dof_parentid[j]) { t->M_row[adr] = i; t->M_col[adr] = j; adr++; }
+    int jid = m->dof_jntid[i];
+    t->dof_hinge_jnt[i] = (m->jnt_type[jid] == HMJ_JNT_HINGE) ? jid : -1;
+  }
+  for (int b = 1; b < HMJ_NBODY; b++) {
+    int bb = b;
+    while (bb && !m->body_dofnum[bb]) bb = m->body_parentid[bb];
+    uint32_t mask = 0;
+    if (bb) {
+      int da = m->body_dofadr[bb] + m->body_dofnum[bb] - 1;
+      while (da >= 0) { mask |= 1u << da; da = m->dof_parentid[da]; }
+    }
+    t->body_dofmask[b] = mask;
+  }
+  int slot = 0;
+  for (int k = 0; k < m->npair; k++) {
+    t->pair_slot[k] = slot;
+    int n = (m->pair_geom1[k] == 0) ? HMJ_MAXCONPAIR : 1;
+    for (int s = 0; s < n; s++) t->slot_pair[slot + s] = k;
+    slot += n;
+  }
+  t->pair_slot[m->npair] = slot;
+  int adr = 0;
+  for (int k = 0; k < HMJ_NMESH; k++) {
+    int nv = m->mesh_vertnum[k], va = m->mesh_vertadr[k];
+    int npad = (nv + HMJ_MESH_PAD - 1) / HMJ_MESH_PAD * HMJ_MESH_PAD;
+    t->mesh_adr[k] = adr;
+    t->mesh_npad[k] = npad;
+    for (int i = 0; i < npad; i++) {
+      int src = i < nv ? i : 0;
+      t->vx[adr + i] = m->mesh_vert[va + src][0];
+      t->vy[adr + i] = m->mesh_vert[va + src][1];
+      t->vz[adr + i] = m->mesh_vert[va + src][2];
+    }
+    adr += npad;
+  }
+  int e = 0;
+  for (int i = 0; i < HMJ_NV; i++)
+    for (int j = 0; j <= i; j++) { t->tri_i[e] = i; t->tri_j[e] = j; e++; }
+}
+
+template <typename Tp>
+static int alloc_array(hmj_batch_* b, const char* name, Tp** out, size_t count) {
+  void* p = nullptr;
+  CK(cudaMalloc(&p, count * sizeof(Tp)));
+  CK(cudaMemsetAsync(p, 0, count * sizeof(Tp), b->stream));
+  b->allocs.push_back(p);
+  if (name) b->arrays[name] = ArrayInfo{p, count * sizeof(Tp)};
+  *out = (Tp*)p;
+  return HMJ_OK;
+}
+
+#define ALLOC(name, field, count)                                   \
+  do {                                                              \
+    int rc_ = alloc_array(b, name, &b->buf.field, (size_t)(count)); \
+    if (rc_) { hmj_batch_destroy(b); return rc_; }                  \
+  } while (0)
+
+extern "C" void hmj_batch_destroy(hmj_batch_t* b) {
+  if (!b) return;
+  cudaSetDevice(b->device);
+  if (b->stream) cudaStreamSynchronize(b->stream);
+  for (void* p : b->allocs) cudaFree(p);
+  if (b->tab_dev) cudaFree(b->tab_dev);
+  if (b->task_dev) cudaFree(b->task_dev);
+  if (b->stream) cudaStreamDestroy(b->stream);
+  delete b->tab_host;
+  delete b;
+}
+
+extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device, hmj_batch_t** out) {
+  if (!model || !out || n_envs <= 0) return fail(HMJ_ERR_ARG, "bad argument to hmj_batch_create%s");
+  if (model->magic != HMJ_MAGIC || model->version != HMJ_VERSION || model->sizeof_model != (int)sizeof(hmj_model_t))
+    return fail(HMJ_ERR_MODEL, "model blob magic/version/size mismatch%s");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+    return fail(HMJ_ERR_CUDA, "no CUDA device: the hmj_b200 engine has no CPU fallback%s");
+  if (device < 0 || device >= ndev) return fail(HMJ_ERR_ARG, "bad device index%s");
+  CK(cudaSetDevice(device));
+  hmj_batch_* b = new hmj_batch_();
+  b->n = n_envs;
+  b->device = device;
+  b->buf.n = n_envs;
+  CK(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
+  b->tab_host = new hmj_tables_t;
+  build_tables(model, b->tab_host);
+  CK(cudaMalloc((void**)&b->tab_dev, sizeof(hmj_tables_t)));
+  CK(cudaMemcpyAsync(b->tab_dev, b->tab_host, sizeof(hmj_tables_t), cudaMemcpyHostToDevice, b->stream));
+  hmj_task_t task;
+  memset(&task, 0, sizeof(task));
+  task.nterm = model->task_nterm;
+  for (int k = 0; k < model->task_nterm; k++) {
+    task.dim[k] = model->task_dim[k]; task.norm[k] = model->task_norm[k]; task.weight[k] = model->task_weight[k];
+    for (int q = 0; q < HMJ_MAXNORMPRM; q++) task.normprm[k][q] = model->task_normprm[k][q];
+  }
+  task.risk = model->task_risk;
+  task.height_goal = model->task_height_goal;
+  CK(cudaMalloc((void**)&b->task_dev, sizeof(hmj_task_t)));
+  CK(cudaMemcpyAsync(b->task_dev, &task, sizeof(task), cudaMemcpyHostToDevice, b->stream));
+
+  const size_t N = (size_t)n_envs;
+  ALLOC("qpos", qpos, N * HMJ_NQ);
+  ALLOC("qvel", qvel, N * HMJ_NV);
+  ALLOC("time", time, N);
+  ALLOC("warmstart", warmstart, N * HMJ_NV);
+  ALLOC("ctrl", ctrl, N * HMJ_NU);
+  ALLOC("xfrc", xfrc, N * 6);
+  ALLOC("xfrc_body", xfrc_body, N);
+  ALLOC("params", params, N);
+  ALLOC("geom_xpos", geom_xpos, N * HMJ_NGEOM * 3);
+  ALLOC("geom_xmat", geom_xmat, N * HMJ_NGEOM * 9);
+  ALLOC("cdof", cdof, N * HMJ_NV * 6);
+  ALLOC("com", com, N * 3);
+  ALLOC("qM", qM, N * HMJ_NM);
+  ALLOC("qfrc_smooth", qfrc_smooth, N * HMJ_NV);
+  ALLOC("sens", sens, N * SENS_NUM);
+  ALLOC("slots", slots, N * HMJ_NSLOT * HMJ_SLOT_DOUBLES);
+  ALLOC("qacc", qacc, N * HMJ_NV);
+  ALLOC("qacc_smooth", qacc_smooth, N * HMJ_NV);
+  ALLOC("qfrc_constraint", qfrc_constraint, N * HMJ_NV);
+  ALLOC("contact", contact, N * HMJ_MAXCON);
+  ALLOC("ncon", ncon, N);
+  ALLOC("nefc", nefc, N);
+  ALLOC("niter", niter, N);
+  ALLOC("status", status, N);
+  ALLOC("residual", residual, N * HMJ_NRESIDUAL);
+  ALLOC("cost_sum", cost_sum, N);
+  ALLOC("cost_last", cost_last, N);
+  ALLOC("trace", trace, N * 3);
+  {
+    int rc;
+    if ((rc = alloc_array(b, nullptr, &b->state_dev, HMJ_NSTATE)) || (rc = alloc_array(b, nullptr, &b->spline_times_dev, 64)) ||
+        (rc = alloc_array(b, "returns", &b->returns_dev, N)) || (rc = alloc_array(b, nullptr, &b->failure_dev, N)) ||
+        (rc = alloc_array(b, "argmin", &b->argmin_dev, 2))) {
+      hmj_batch_destroy(b);
+      return rc;
+    }
+  }
+  // default params and state (qpos0) for every env
+  {
+    std::vector<hmj_params_t> hp(N);
+    hmj_default_params(model, &hp[0]);
+    for (size_t i = 1; i < N; i++) hp[i] = hp[0];
+    CK(cudaMemcpyAsync(b->buf.params, hp.data(), N * sizeof(hmj_params_t), cudaMemcpyHostToDevice, b->stream));
+    std::vector<double> q(N * HMJ_NQ);
+    for (size_t i = 0; i < N; i++) memcpy(&q[i * HMJ_NQ], model->qpos0, sizeof(model->qpos0));
+    CK(cudaMemcpyAsync(b->buf.qpos, q.data(), q.size() * sizeof(double), cudaMemcpyHostToDevice, b->stream));
+    CK(cudaStreamSynchronize(b->stream));
+  }
+  *out = b;
+  return HMJ_OK;
+}
+
+extern "C" int hmj_batch_size(const hmj_batch_t* b) { return b ? b->n : 0; }
+extern "C" int hmj_batch_kernel_launches(const hmj_batch_t* b) { return b ? b->launches : 0; }
+extern "C" void* hmj_batch_stream(hmj_batch_t* b) { return b ? (void*)b->stream : nullptr; }
+
+extern "C" int hmj_batch_sync(hmj_batch_t* b) {
+  if (!b) return fail(HMJ_ERR_ARG, "null batch%s");
+  CK(cudaSetDevice(b->device));
+  CK(cudaStreamSynchronize(b->stream));
+  CK(cudaGetLastError());
+  return HMJ_OK;
+}
+
+static int h2d(hmj_batch_t* b, void* dst, const void* src, size_t bytes) {
+  if (!src) return HMJ_OK;
+  CK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, b->stream));
+  return HMJ_OK;
+}
+static int d2h(hmj_batch_t* b, void* dst, const void* src, size_t bytes) {
+  if (!dst) return HMJ_OK;
+  CK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, b->stream));
+  return HMJ_OK;
+}
+
+extern "C" int hmj_batch_set_params(hmj_batch_t* b, const hmj_params_t* params, int first, int count) {
+  if (!b || !params || first < 0 || count < 0 || first + count > b->n) return fail(HMJ_ERR_ARG, "bad argument to set_params%s");
+  CK(cudaSetDevice(b->device));
+  int rc = h2d(b, b->buf.params + first, params, (size_t)count * sizeof(hmj_params_t));
+  if (rc) return rc;
+  CK(cudaStreamSynchronize(b->stream));
+  return HMJ_OK;
+}
+
+extern "C" int hmj_batch_get_params(hmj_batch_t* b, hmj_params_t* params, int first, int count) {
+  if (!b || !params || first < 0 || count < 0 || first + count > b->n) return fail(HMJ_ERR_ARG, "bad argument to get_params%s");
+  CK(cudaSetDevice(b->device));
+  int rc = d2h(b, params, b->buf.params + first, (size_t)count * sizeof(hmj_params_t));
+  if (rc) return rc;
+  CK(cudaStreamSynchronize(b->stream));
+  return HMJ_OK;
+}
+
+extern "C" int hmj_batch_set_state(hmj_batch_t* b, const double* qpos, const double* qvel, const double* time, const double* ws) {
+  if (!b) return fail(HMJ_ERR_ARG, "null batch%s");
+  CK(cudaSetDevice(b->device));
+  const size_t N = b->n;
+  int rc;
+  if ((rc = h2d(b, b->buf.qpos, qpos, N * HMJ_NQ * 8)) || (rc = h2d(b, b->buf.qvel, qvel, N * HMJ_NV * 8)) ||
+      (rc = h2d(b, b->buf.time, time, N * 8)) || (rc = h2d(b, b->buf.warmstart, ws, N * HMJ_NV * 8)))
+    return rc;
+  CK(cudaStreamSynchronize(b->stream));
+  return HMJ_OK;
+}
+
+extern "C" int hmj_batch_get_state(hmj_batch_t* b, double* qpos, double* qvel, double* time, double* ws) {
+  if (!b) return fail(HMJ_ERR_ARG, "null batch%s");
+  CK(cudaSetDevice(b->device));
+  const size_t N = b->n;
+  int rc;
+  if ((rc = d2h(b, qpos, b->buf.qpos, N * HMJ_NQ * 8)) || (rc = d2h(b, qvel, b->buf.qvel, N * HMJ_NV * 8)) ||
+      (rc = d2h(b, time, b->buf.time, N * 8)) || (rc = d2h(b, ws, b->buf.warmstart, N * HMJ_NV * 8)))
+    return rc;
+  CK(cudaStreamSynchronize(b->stream));
+  return HMJ_OK;
+}
+
+extern "C" int hmj_batch_set_ctrl(hmj_batch_t* b, const double* ctrl) {
+  if (!b || !ctrl) return fail(HMJ_ERR_ARG, "bad argument to set_ctrl%s");
+  CK(cudaSetDevice(b->device));
+  int rc = h2d(b, b->buf.ctrl, ctrl, (size_t)b->n * HMJ_NU * 8);
+  if (rc) return rc;
+  CK(cudaStreamSynchronize(b->stream));
+  return HMJ_OK;
+}
+
+extern "C" int hmj_batch_set_xfrc(hmj_batch_t* b, const int32_t* body, const double* wrench) {
+  if (!b || !body || !wrench) return fail(HMJ_ERR_ARG, "bad argument to set_xfrc%s");
+  CK(cudaSetDevice(b->device));
+  int rc;
+  if ((rc = h2d(b, b->buf.xfrc_body, body, (size_t)b->n * 4)) || (rc = h2d(b, b->buf.xfrc, wrench, (size_t)b->n * 6 * 8))) return rc;
+  CK(cudaStreamSynchronize(b->stream));
+  return HMJ_OK;
+}
+
+static void enqueue_step(hmj_batch_t* b, int integrate) {
+  hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, b->stream);
+  hmj_launch_collide(b->tab_dev, b->buf, b->stream);
+  hmj_launch_solve(b->tab_dev, b->buf, integrate, b->stream);
+  b->launches += 3;
+}
+
+extern "C" int hmj_batch_step_dev(hmj_batch_t* b, const double* ctrl_dev, int nsteps) {
+  if (!b || nsteps < 0) return fail(HMJ_ERR_ARG, "bad argument to step%s");
+  CK(cudaSetDevice(b->device));
+  if (ctrl_dev && ctrl_dev != b->buf.ctrl)
+    CK(cudaMemcpyAsync(b->buf.ctrl, ctrl_dev, (size_t)b->n * HMJ_NU * 8, cudaMemcpyDeviceToDevice, b->stream));
+  for (int s = 0; s < nsteps; s++) enqueue_step(b, 1);
+  CK(cudaGetLastError());
+  return HMJ_OK;
+}
+
+extern "C" int hmj_batch_step(hmj_batch_t* b, const double* ctrl, int nsteps) {
+  if (!b || nsteps < 0) return fail(HMJ_ERR_ARG, "bad argument to step%s");
+  CK(cudaSetDevice(b->device));
+  int rc = h2d(b, b->buf.ctrl, ctrl, (size_t)b->n * HMJ_NU * 8);
+  if (rc) return rc;
+  for (int s = 0; s < nsteps; s++) enqueue_step(b, 1);
+  CK(cudaStreamSynchronize(b->stream));
+  CK(cudaGetLastError());
+  return HMJ_OK;
+}
+
+extern "C" int hmj_batch_forward(hmj_batch_t* b) {
+  if (!b) return fail(HMJ_ERR_ARG, "null batch%s");
+  CK(cudaSetDevice(b->device));
+  enqueue_step(b, 0);
+  CK(cudaStreamSynchronize(b->stream));
+  CK(cudaGetLastError());
+  return HMJ_OK;
+}
+
+extern "C" int hmj_batch_run_stage(hmj_batch_t* b, int stage) {
+  if (!b) return fail(HMJ_ERR_ARG, "null batch%s");
+  CK(cudaSetDevice(b->device));
+  switch (stage) {
+    case HMJ_STAGE_SMOOTH: hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, b->stream); break;
+    case HMJ_STAGE_COLLIDE: hmj_launch_collide(b->tab_dev, b->buf, b->stream); break;
+    case HMJ_STAGE_SOLVE: hmj_launch_solve(b->tab_dev, b->buf, 0, b->stream); break;
+    case HMJ_STAGE_SOLVE_INTEGRATE: hmj_launch_solve(b->tab_dev, b->buf, 1, b->stream); break;
+    default: return fail(HMJ_ERR_ARG, "unknown stage%s");
+  }
+  b->launches += 1;
+  CK(cudaStreamSynchronize(b->stream));
+  CK(cudaGetLastError());
+  return HMJ_OK;
+}
+
+extern "C" int hmj_batch_get_contacts(hmj_batch_t* b, int32_t* ncon, hmj_contact_t* contacts) {
+  if (!b) return fail(HMJ_ERR_ARG, "null batch%s");
+  CK(cudaSetDevice(b->device));
+  int rc;
+  if ((rc = d2h(b, ncon, b->buf.ncon, (size_t)b->n * 4)) ||
+      (rc = d2h(b, contacts, b->buf.contact, (size_t)b->n * HMJ_MAXCON * sizeof(hmj_contact_t))))
+    return rc;
+  CK(cudaStreamSynchronize(b->stream));
+  return HMJ_OK;
+}
+
+extern "C" void* hmj_batch_device_ptr(hmj_batch_t* b, const char* name) {
+  if (!b || !name) return nullptr;
+  auto it = b->arrays.find(name);
+  return it == b->arrays.end() ? nullptr : it->second.ptr;
+}
+
+extern "C" int hmj_batch_get_array(hmj_batch_t* b, const char* name, void* out, size_t bytes) {
+  if (!b || !name || !out) return fail(HMJ_ERR_ARG, "bad argument to get_array%s");
+  auto it = b->arrays.find(name);
+  if (it == b->arrays.end()) return fail(HMJ_ERR_ARG, "unknown array '%s'", name);
+  if (bytes != it->second.bytes) return fail(HMJ_ERR_ARG, "size mismatch for array '%s'", name);
+  CK(cudaSetDevice(b->device));
+  CK(cudaMemcpyAsync(out, it->second.ptr, bytes, cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  return HMJ_OK;
+}
+
+extern "C" int hmj_batch_set_array(hmj_batch_t* b, const char* name, const void* in, size_t bytes) {
+  if (!b || !name || !in) return fail(HMJ_ERR_ARG, "bad argument to set_array%s");
+  auto it = b->arrays.find(name);
+  if (it == b->arrays.end()) return fail(HMJ_ERR_ARG, "unknown array '%s'", name);
+  if (bytes != it->second.bytes) return fail(HMJ_ERR_ARG, "size mismatch for array '%s'", name);
+  CK(cudaSetDevice(b->device));
+  CK(cudaMemcpyAsync(it->second.ptr, in, bytes, cudaMemcpyHostToDevice, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  return HMJ_OK;
+}
+
+// ------------------------------------------------------------------ CPUEnv epilogue
+extern "C" int hmj_env_obs_reward_dev(hmj_batch_t* b, const double* prev_action_dev, const double* latest_action_dev,
+                                      const double* noise_dev, double max_sim_time, double* obs_dev, double* reward_dev,
+                                      int32_t* terminated_dev, int32_t* truncated_dev, int32_t* self_collision_dev) {
+  if (!b || !prev_action_dev || !latest_action_dev || !obs_dev || !reward_dev || !terminated_dev || !truncated_dev)
+    return fail(HMJ_ERR_ARG, "bad argument to env_obs_reward_dev%s");
+  CK(cudaSetDevice(b->device));
+  hmj_launch_env_obs_reward(b->tab_dev, b->buf, prev_action_dev, latest_action_dev, noise_dev, max_sim_time, obs_dev, reward_dev,
+                            terminated_dev, truncated_dev, self_collision_dev, b->stream);
+  b->launches += 1;
+  CK(cudaGetLastError());
+  return HMJ_OK;
+}
+
+extern "C" int hmj_env_obs_reward(hmj_batch_t* b, const double* prev_action, const double* latest_action, const double* noise,
+                                  double max_sim_time, double* obs, double* reward, int32_t* terminated, int32_t* truncated,
+                                  int32_t* self_collision) {
+  if (!b || !prev_action || !latest_action || !obs || !reward || !terminated || !truncated)
+    return fail(HMJ_ERR_ARG, "bad argument to env_obs_reward%s");
+  CK(cudaSetDevice(b->device));
+  const size_t N = b->n;
+  // staging layout (doubles): prev 12N | latest 12N | noise 31N | obs 30N | reward N | then int32: term N, trunc N, selfc N
+  const size_t nd = N * (12 + 12 + 31 + 30 + 1);
+  const size_t bytes = nd * 8 + 3 * N * 4;
+  if (b->env_stage_cap < bytes) {
+    void* p = nullptr;
+    CK(cudaMalloc(&p, bytes));
+    b->allocs.push_back(p);
+    b->env_stage = (double*)p;
+    b->env_stage_cap = bytes;
+  }
+  double* d_prev = b->env_stage;
+  double* d_lat = d_prev + 12 * N;
+  double* d_noise = d_lat + 12 * N;
+  double* d_obs = d_noise + 31 * N;
+  double* d_rew = d_obs + 30 * N;
+  int32_t* d_term = (int32_t*)(d_rew + N);
+  int32_t* d_trunc = d_term + N;
+  int32_t* d_self = d_trunc + N;
+  int rc;
+  if ((rc = h2d(b, d_prev, prev_action, 12 * N * 8)) || (rc = h2d(b, d_lat, latest_action, 12 * N * 8)) ||
+      (rc = h2d(b, d_noise, noise, 31 * N * 8)))
+    return rc;
+  rc = hmj_env_obs_reward_dev(b, d_prev, d_lat, noise ? d_noise : nullptr, max_sim_time, d_obs, d_rew, d_term, d_trunc, d_self);
+  if (rc) return rc;
+  if ((rc = d2h(b, obs, d_obs, 30 * N * 8)) || (rc = d2h(b, reward, d_rew, N * 8)) || (rc = d2h(b, terminated, d_term, N * 4)) ||
+      (rc = d2h(b, truncated, d_trunc, N * 4)) || (rc = d2h(b, self_collision, d_self, N * 4)))
+    return rc;
+  CK(cudaStreamSynchronize(b->stream));
+  return HMJ_OK;
+}
+
+// ------------------------------------------------------------------ planner
+extern "C" int hmj_plan_set_task(hmj_batch_t* b, int nterm, const int32_t* dim, const int32_t* norm, const double* weight,
+                                 const double* normprm, double risk, double height_goal) {
+  if (!b || nterm < 0 || nterm > HMJ_NTERM || !dim || !norm || !weight || !normprm) return fail(HMJ_ERR_ARG, "bad argument to set_task%s");
+  int tot = 0;
+  for (int k = 0; k < nterm; k++) tot += dim[k];
+  if (tot != HMJ_NRESIDUAL) return fail(HMJ_ERR_ARG, "cost terms must cover the 28 residuals%s");
+  CK(cudaSetDevice(b->device));
+  hmj_task_t task;
+  memset(&task, 0, sizeof(task));
+  task.nterm = nterm;
+  for (int k = 0; k < nterm; k++) {
+    task.dim[k] = dim[k]; task.norm[k] = norm[k]; task.weight[k] = weight[k];
+    for (int q = 0; q < HMJ_MAXNORMPRM; q++) task.normprm[k][q] = normprm[k * HMJ_MAXNORMPRM + q];
+  }
+  task.risk = risk;
+  task.height_goal = height_goal;
+  CK(cudaMemcpyAsync(b->task_dev, &task, sizeof(task), cudaMemcpyHostToDevice, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  return HMJ_OK;
+}
+
+static int ensure_record(hmj_batch_t* b, int horizon) {
+  if (b->rec_cap >= horizon) { b->rec.horizon = horizon; return HMJ_OK; }
+  const size_t HN = (size_t)horizon * b->n;
+  int rc;
+  if ((rc = alloc_array(b, nullptr, &b->rec.states, HN * HMJ_NSTATE)) || (rc = alloc_array(b, nullptr, &b->rec.actions, HN * HMJ_NU)) ||
+      (rc = alloc_array(b, nullptr, &b->rec.times, HN)) || (rc = alloc_array(b, nullptr, &b->rec.residual, HN * HMJ_NRESIDUAL)) ||
+      (rc = alloc_array(b, nullptr, &b->rec.costs, HN)) || (rc = alloc_array(b, nullptr, &b->rec.trace, HN * 3)))
+    return rc;
+  b->rec_cap = horizon;
+  b->rec.horizon = horizon;
+  return HMJ_OK;
+}
+
+static int enqueue_rollouts(hmj_batch_t* b, const double* state, double time, const double* spline_times,
+                            const double* spline_values_dev, int nnode, int interpolation, int horizon, int record,
+                            double* returns_dev, int32_t* failure_dev) {
+  if (nnode < 0 || nnode > 64 || horizon < 1 || horizon > 512) return fail(HMJ_ERR_ARG, "bad nnode/horizon%s");  // kMaxTrajectoryHorizon
+  CK(cudaMemcpyAsync(b->state_dev, state, HMJ_NSTATE * 8, cudaMemcpyHostToDevice, b->stream));
+  if (nnode) CK(cudaMemcpyAsync(b->spline_times_dev, spline_times, (size_t)nnode * 8, cudaMemcpyHostToDevice, b->stream));
+  if (record) {
+    int rc = ensure_record(b, horizon);
+    if (rc) return rc;
+  }
+  hmj_launch_plan_init(b->buf, b->state_dev, time, b->stream);
+  b->launches += 1;
+  for (int t = 0; t < horizon - 1; t++) {
+    hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, HMJ_PLAN_COST | HMJ_PLAN_POLICY, b->spline_times_dev, spline_values_dev, nnode,
+                      interpolation, 1, b->stream);
+    if (record) { hmj_launch_plan_record(b->buf, b->rec, t, b->stream); b->launches += 1; }
+    hmj_launch_collide(b->tab_dev, b->buf, b->stream);
+    hmj_launch_solve(b->tab_dev, b->buf, 1, b->stream);
+    b->launches += 3;
+  }
+  // final mj_forward: only the sensors/residual matter, ctrl keeps the last action (trajectory.cc:190-206)
+  hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, HMJ_PLAN_COST, nullptr, nullptr, 0, 0, 0, b->stream);
+  if (record) { hmj_launch_plan_record(b->buf, b->rec, horizon - 1, b->stream); b->launches += 1; }
+  hmj_launch_plan_finish(b->buf, horizon, returns_dev, failure_dev, b->stream);
+  b->launches += 2;
+  CK(cudaGetLastError());
+  return HMJ_OK;
+}
+
+extern "C" int hmj_plan_rollouts_dev(hmj_batch_t* b, const double* state, double time, const double* spline_times,
+                                     const double* spline_values_dev, int nnode, int interpolation, int horizon, double* returns_dev) {
+  if (!b || !state || !spline_times || !spline_values_dev) return fail(HMJ_ERR_ARG, "bad argument to plan_rollouts_dev%s");
+  CK(cudaSetDevice(b->device));
+  return enqueue_rollouts(b, state, time, spline_times, spline_values_dev, nnode, interpolation, horizon, 0,
+                          returns_dev ? returns_dev : b->returns_dev, b->failure_dev);
+}
+
+extern "C" int hmj_plan_rollouts(hmj_batch_t* b, const double* state, double time, const double* spline_times,
+                                 const double* spline_values, int nnode, int interpolation, int horizon, int record,
+                                 double* total_return, int32_t* failure) {
+  if (!b || !state || !spline_times || !spline_values || !total_return) return fail(HMJ_ERR_ARG, "bad argument to plan_rollouts%s");
+  CK(cudaSetDevice(b->device));
+  const size_t nvals = (size_t)b->n * nnode * HMJ_NU;
+  if (b->spline_values_cap < nvals) {
+    void* p = nullptr;
+    CK(cudaMalloc(&p, nvals * 8));
+    b->allocs.push_back(p);
+    b->spline_values_dev = (double*)p;
+    b->spline_values_cap = nvals;
+  }
+  CK(cudaMemcpyAsync(b->spline_values_dev, spline_values, nvals * 8, cudaMemcpyHostToDevice, b->stream));
+  int rc = enqueue_rollouts(b, state, time, spline_times, b->spline_values_dev, nnode, interpolation, horizon, record,
+                            b->returns_dev, b->failure_dev);
+  if (rc) return rc;
+  if ((rc = d2h(b, total_return, b->returns_dev, (size_t)b->n * 8)) || (rc = d2h(b, failure, b->failure_dev, (size_t)b->n * 4))) return rc;
+  CK(cudaStreamSynchronize(b->stream));
+  CK(cudaGetLastError());
+  return HMJ_OK;
+}
+
+extern "C" int hmj_plan_argmin(hmj_batch_t* b, double* best_cost, int32_t* best_index) {
+  if (!b) return fail(HMJ_ERR_ARG, "null batch%s");
+  CK(cudaSetDevice(b->device));
+  hmj_launch_argmin(b->returns_dev, b->n, b->argmin_dev, b->stream);
+  b->launches += 1;
+  double out[2];
+  CK(cudaMemcpyAsync(out, b->argmin_dev, sizeof(out), cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  if (best_cost) *best_cost = out[0];
+  if (best_index) *best_index = (int32_t)out[1];
+  return HMJ_OK;
+}
+
+extern "C" int hmj_plan_fetch(hmj_batch_t* b, int sample, int horizon, double* states, double* actions, double* times,
+                              double* residual, double* costs, double* trace) {
+  if (!b || sample < 0 || sample >= b->n || horizon < 1 || horizon > b->rec.horizon || !b->rec.states)
+    return fail(HMJ_ERR_ARG, "no recorded trajectory for this sample/horizon%s");
+  CK(cudaSetDevice(b->device));
+  const size_t N = b->n;
+  auto fetch = [&](double* dst, const double* src, int dim) -> int {
+    if (!dst) return HMJ_OK;
+    CK(cudaMemcpy2DAsync(dst, (size_t)dim * 8, src + (size_t)sample * dim, N * dim * 8, (size_t)dim * 8, horizon,
+                         cudaMemcpyDeviceToHost, b->stream));
+    return HMJ_OK;
+  };
+  int rc;
+  if ((rc = fetch(states, b->rec.states, HMJ_NSTATE)) || (rc = fetch(actions, b->rec.actions, HMJ_NU)) ||
+      (rc = fetch(times, b->rec.times, 1)) || (rc = fetch(residual, b->rec.residual, HMJ_NRESIDUAL)) ||
+      (rc = fetch(costs, b->rec.costs, 1)) || (rc = fetch(trace, b->rec.trace, 3)))
+    return rc;
+  CK(cudaStreamSynchronize(b->stream));
+  if (actions && horizon > 1)  // final action is a copy of the previous one (trajectory.cc:190-192)
+    memcpy(actions + (size_t)(horizon - 1) * HMJ_NU, actions + (size_t)(horizon - 2) * HMJ_NU, HMJ_NU * 8);
+  return HMJ_OK;
+}

@@ -1,0 +1,182 @@
+// hmj_aux.cu — small per-env kernels around the physics step.
+//
+//  * planner bookkeeping of Trajectory::NoisyRollout (mjpc/trajectory.cc:100-210): broadcast of the
+//    shared initial state, optional trajectory recording, total_return = mean of knot costs
+//    (UpdateReturn, trajectory.cc:312-326), local arg-min with lowest-index tie-break;
+//  * the CPUEnv.step prologue/epilogue (simulation/cpu_env.py:656-674, 465-616) and standupReward
+//    (simulation/reward_functions.py:247-374), one thread per environment.
+// These are HBM/L2-bound streaming kernels (a few hundred bytes per env), thread-per-env.
+#include "hmj_dev.cuh"
+
+// ------------------------------------------------------------------ planner
+__global__ void k_plan_init(hmj_buffers_t B, const double* __restrict__ state, double time) {
+  const int env = blockIdx.x * blockDim.x + threadIdx.x;
+  if (env >= B.n) return;
+  for (int k = 0; k < HMJ_NQ; k++) B.qpos[(size_t)env * HMJ_NQ + k] = state[k];
+  for (int k = 0; k < HMJ_NV; k++) {
+    B.qvel[(size_t)env * HMJ_NV + k] = state[HMJ_NQ + k];
+    B.warmstart[(size_t)env * HMJ_NV + k] = 0.0;  // deterministic stand-in for per-thread mjData reuse (planner.cc:374)
+  }
+  for (int k = 0; k < 6; k++) B.xfrc[(size_t)env * 6 + k] = 0.0;
+  B.xfrc_body[env] = 0;
+  B.time[env] = time;
+  B.cost_sum[env] = 0.0;
+  B.status[env] = 0;
+}
+
+__global__ void k_plan_record(hmj_buffers_t B, hmj_record_t R, int t) {
+  const int env = blockIdx.x * blockDim.x + threadIdx.x;
+  if (env >= B.n) return;
+  const size_t row = (size_t)t * B.n + env;
+  for (int k = 0; k < HMJ_NQ; k++) R.states[row * HMJ_NSTATE + k] = B.qpos[(size_t)env * HMJ_NQ + k];
+  for (int k = 0; k < HMJ_NV; k++) R.states[row * HMJ_NSTATE + HMJ_NQ + k] = B.qvel[(size_t)env * HMJ_NV + k];
+  for (int k = 0; k < HMJ_NU; k++) R.actions[row * HMJ_NU + k] = B.ctrl[(size_t)env * HMJ_NU + k];
+  for (int k = 0; k < HMJ_NRESIDUAL; k++) R.residual[row * HMJ_NRESIDUAL + k] = B.residual[(size_t)env * HMJ_NRESIDUAL + k];
+  for (int k = 0; k < 3; k++) R.trace[row * 3 + k] = B.trace[(size_t)env * 3 + k];
+  R.times[row] = B.time[env];
+  R.costs[row] = B.cost_last[env];
+}
+
+__global__ void k_plan_finish(hmj_buffers_t B, int horizon, double* __restrict__ returns, int32_t* __restrict__ failure) {
+  const int env = blockIdx.x * blockDim.x + threadIdx.x;
+  if (env >= B.n) return;
+  const int fail = B.status[env] != 0;
+  returns[env] = fail ? 1.0e6 : B.cost_sum[env] / (double)(horizon > 1 ? horizon : 1);  // kMaxReturnValue
+  if (failure) failure[env] = fail;
+}
+
+// single-CTA arg-min; ties -> lowest index (std::partial_sort leaves ties unspecified)
+__global__ void k_argmin(const double* __restrict__ returns, int n, double* __restrict__ out) {
+  __shared__ double sv[1024];
+  __shared__ int si[1024];
+  double best = INFINITY;
+  int bi = 0x7fffffff;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const double v = returns[i];
+    if (v < best || (v == best && i < bi)) { best = v; bi = i; }
+  }
+  sv[threadIdx.x] = best; si[threadIdx.x] = bi;
+  __syncthreads();
+  for (int s = blockDim.x / 2; s > 0; s >>= 1) {
+    if (threadIdx.x < s) {
+      const double ov = sv[threadIdx.x + s];
+      const int oi = si[threadIdx.x + s];
+      if (ov < sv[threadIdx.x] || (ov == sv[threadIdx.x] && oi < si[threadIdx.x])) { sv[threadIdx.x] = ov; si[threadIdx.x] = oi; }
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) { out[0] = sv[0]; out[1] = (double)si[0]; }
+}
+
+void hmj_launch_plan_init(hmj_buffers_t buf, const double* state_dev, double time, cudaStream_t stream) {
+  k_plan_init<<<(buf.n + 127) / 128, 128, 0, stream>>>(buf, state_dev, time);
+}
+void hmj_launch_plan_record(hmj_buffers_t buf, hmj_record_t rec, int t, cudaStream_t stream) {
+  k_plan_record<<<(buf.n + 127) / 128, 128, 0, stream>>>(buf, rec, t);
+}
+void hmj_launch_plan_finish(hmj_buffers_t buf, int horizon, double* returns_dev, int32_t* failure_dev, cudaStream_t stream) {
+  k_plan_finish<<<(buf.n + 127) / 128, 128, 0, stream>>>(buf, horizon, returns_dev, failure_dev);
+}
+void hmj_launch_argmin(const double* returns_dev, int n, double* out, cudaStream_t stream) {
+  k_argmin<<<1, 1024, 0, stream>>>(returns_dev, n, out);
+}
+
+// ------------------------------------------------------------------ CPUEnv epilogue
+__device__ __forceinline__ double scaled_exp(double x) { return exp(-x / 0.5); }
+
+// inverseRotateVectors(q, (0,0,-1)) with scipy/JAX Rotation semantics (normalises q): -(third row of R(q))
+__device__ __forceinline__ void local_gravity(const double* quat_in, double* g) {
+  double q[4] = {quat_in[0], quat_in[1], quat_in[2], quat_in[3]};
+  const double n = sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+  const double s = 1.0 / n;
+  q[0] *= s; q[1] *= s; q[2] *= s; q[3] *= s;
+  double R[9];
+  d_quat2mat(R, q);
+  g[0] = -R[6]; g[1] = -R[7]; g[2] = -R[8];
+}
+
+__global__ void k_env_obs_reward(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const double* __restrict__ prev_action,
+                                 const double* __restrict__ latest_action, const double* __restrict__ noise, double max_sim_time,
+                                 double* __restrict__ obs, double* __restrict__ reward, int32_t* __restrict__ terminated,
+                                 int32_t* __restrict__ truncated, int32_t* __restrict__ self_collision) {
+  const int env = blockIdx.x * blockDim.x + threadIdx.x;
+  if (env >= B.n) return;
+  const hmj_model_t& M = T->m;
+  const double* qpos = B.qpos + (size_t)env * HMJ_NQ;
+  const double* qvel = B.qvel + (size_t)env * HMJ_NV;
+  const double* sens = B.sens + (size_t)env * SENS_NUM;
+  const double* nz = noise ? noise + (size_t)env * 31 : nullptr;
+  // ---- observation (cpu_env.py:465-571), undelayed; JOINT_NAMES follow the actuator order
+  double* o = obs + (size_t)env * 30;
+  for (int a = 0; a < HMJ_NU; a++) {
+    o[a] = qpos[M.act_qposadr[a]] + (nz ? nz[a] : 0.0);
+    o[12 + a] = qvel[M.act_dofadr[a]] + (nz ? nz[12 + a] : 0.0);
+  }
+  for (int k = 0; k < 3; k++) o[24 + k] = qvel[3 + k] + (nz ? nz[24 + k] : 0.0);
+  const double* tq = sens + SENS_ROOT_XQUAT;  // data.xquat[torso_idx]: one step stale
+  double nq[4] = {tq[0] + (nz ? nz[27] : 0.0), tq[1] + (nz ? nz[28] : 0.0), tq[2] + (nz ? nz[29] : 0.0), tq[3] + (nz ? nz[30] : 0.0)};
+  double g[3];
+  local_gravity(nq, g);
+  o[27] = g[0]; o[28] = g[1]; o[29] = g[2];
+
+  // ---- standupReward (reward_functions.py:247-374)
+  double gl[3];
+  local_gravity(tq, gl);
+  const double z = sens[SENS_ROOT_Z];
+  double r = 0.0;
+  r += 5.0 * scaled_exp(qvel[0] * qvel[0] + qvel[1] * qvel[1]);                 // horizontal velocity (target 0)
+  {
+    const double dx = gl[0], dy = gl[1], dz = gl[2] + 1.0;
+    r += 10.0 * scaled_exp(dx * dx + dy * dy + dz * dz);                        // upright (yaw weight 0)
+  }
+  {
+    const double z0 = -0.6, z1 = -0.375;                                         // np.interp(z, [MIN_Z, TARGET_Z], [0, 15])
+    r += (z <= z0) ? 0.0 : (z >= z1 ? 15.0 : (z - z0) / (z1 - z0) * 15.0);
+  }
+  double tq_sum = 0.0, dc_sum = 0.0, reg_sum = 0.0;
+  double u[HMJ_NU];
+  for (int a = 0; a < HMJ_NU; a++) {
+    const int d = M.act_dofadr[a];
+    const double tau = B.qfrc_constraint[(size_t)env * HMJ_NV + d] + B.qfrc_smooth[(size_t)env * HMJ_NV + d];
+    const double ex = fmax(fabs(tau) - 1.0, 0.0);
+    tq_sum += scaled_exp(ex * ex);
+    const double lat = latest_action[(size_t)env * HMJ_NU + a] / (HMJ_PI / 2);
+    const double prv = prev_action[(size_t)env * HMJ_NU + a] / (HMJ_PI / 2);
+    const double dc = (lat - prv) * 500.0;
+    dc_sum += scaled_exp(dc * dc);
+    reg_sum += scaled_exp(lat * lat);
+    u[a] = lat;
+  }
+  r += 2.5 * tq_sum / 12.0;
+  r += 2.0 * dc_sum / 12.0;
+  r += 0.5 * reg_sum / 12.0;
+  {
+    double sym = 0.0;
+    sym += scaled_exp((u[5] - u[2]) * (u[5] - u[2]));     // elbows equal
+    sym += scaled_exp((u[6] + u[9]) * (u[6] + u[9]));     // hip roll opposite
+    sym += scaled_exp((u[7] + u[10]) * (u[7] + u[10]));   // hip pitch
+    sym += scaled_exp((u[8] + u[11]) * (u[8] + u[11]));   // knee
+    sym += scaled_exp((u[3] + u[0]) * (u[3] + u[0]));     // shoulder pitch
+    sym += scaled_exp((u[4] + u[1]) * (u[4] + u[1]));     // shoulder roll
+    r += 1.0 * sym / 6.0;
+  }
+  int selfc = 0;
+  const int nc = B.ncon[env];
+  for (int c = 0; c < nc; c++)
+    if (B.contact[(size_t)env * HMJ_MAXCON + c].g1 != 0) selfc = 1;
+  if (selfc) r += -20.0;
+  const int term = B.time[env] >= max_sim_time;
+  if (term) r = -100.0;
+  const int upright = fmax(fabs(gl[0]), fabs(gl[1])) < 0.7;
+  reward[env] = r;
+  terminated[env] = term;
+  truncated[env] = (z >= -0.375) && upright;
+  if (self_collision) self_collision[env] = selfc;
+}
+
+void hmj_launch_env_obs_reward(const hmj_tables_t* tab, hmj_buffers_t buf, const double* prev_action, const double* latest_action,
+                               const double* noise, double max_sim_time, double* obs, double* reward, int32_t* terminated,
+                               int32_t* truncated, int32_t* self_collision, cudaStream_t stream) {
+  k_env_obs_reward<<<(buf.n + 127) / 128, 128, 0, stream>>>(tab, buf, prev_action, latest_action, noise, max_sim_time, obs, reward,
+                                                            terminated, truncated, self_collision);
+}

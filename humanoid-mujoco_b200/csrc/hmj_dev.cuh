@@ -1,0 +1,253 @@
+// hmj_dev.cuh — device-side tables, per-batch buffers and small math shared by the sm_100a kernels.
+//
+// Thread mapping everywhere: ONE WARP PER ENVIRONMENT (or per collision query), 4 warps per CTA.
+// Per-env arrays are separate device arrays ("structure of arrays" across fields), each laid out
+// env-major so a warp's read of its environment's row is one contiguous, coalesced segment.
+// All intermediates that cross kernels (geom frames, cdof, qM, qfrc_smooth, contact slots) stay
+// L2-resident: ~13 KB/env, 53 MB at 4096 envs against 126 MB of L2.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/hmj_model.h"
+
+#define HMJ_WARPS_PER_CTA 4
+#define HMJ_NSLOT (9 * HMJ_MAXCONPAIR + 28) /* contact slots per env: 9 hfield pairs x cap + 28 mesh pairs */
+#define HMJ_SLOT_DOUBLES 8                  /* dist, pos[3], normal[3], valid */
+#define HMJ_NFAC 375                        /* LDL update triples (unused by the dense path, kept for tables) */
+#define HMJ_MESH_PAD 32
+
+#define HMJ_MINVAL 1e-15
+#define HMJ_MAXVAL 1e10
+#define HMJ_PI 3.14159265358979323846
+
+// Host-derived lookup tables (built once in hmj_batch_create, read through L1/L2).
+struct hmj_tables_t {
+  hmj_model_t m;
+  // kinematic levels (bodies of equal depth are independent)
+  int32_t nlevel;
+  int32_t level_n[8];
+  int32_t level_body[8][8];
+  int32_t subtree_end[HMJ_NBODY];  // bodies [b, subtree_end[b]) form b's subtree (DFS numbering)
+  // sparse inertia index maps: entry e of qM is M(M_row[e], M_col[e]), col an ancestor-or-self dof of row
+  int32_t M_row[HMJ_NM];
+  int32_t M_col[HMJ_NM];
+  uint32_t body_dofmask[HMJ_NBODY];  // bit d set: dof d moves body b
+  // per-dof joint info
+  int32_t dof_hinge_jnt[HMJ_NV];  // joint id for hinge dofs, -1 for free-joint dofs
+  // collision
+  int32_t pair_slot[HMJ_NPAIR + 1];  // first contact slot of each candidate pair
+  int32_t slot_pair[HMJ_NSLOT];      // inverse map
+  // convex hull vertices, SoA float32, each mesh padded to a multiple of 32 with copies of its vertex 0
+  int32_t mesh_adr[HMJ_NMESH + 1];
+  int32_t mesh_npad[HMJ_NMESH + 1];
+  float vx[HMJ_MAXVERT + HMJ_NMESH * HMJ_MESH_PAD];
+  float vy[HMJ_MAXVERT + HMJ_NMESH * HMJ_MESH_PAD];
+  float vz[HMJ_MAXVERT + HMJ_NMESH * HMJ_MESH_PAD];
+  // lower-triangle index maps for the 18x18 dense routines
+  int32_t tri_i[HMJ_NV * (HMJ_NV + 1) / 2];
+  int32_t tri_j[HMJ_NV * (HMJ_NV + 1) / 2];
+};
+
+// planner task description pushed at plan time (mjpc Task -> numeric tables)
+struct hmj_task_t {
+  int32_t nterm;
+  int32_t dim[HMJ_NTERM + 1];
+  int32_t norm[HMJ_NTERM + 1];
+  double weight[HMJ_NTERM + 1];
+  double normprm[HMJ_NTERM + 1][HMJ_MAXNORMPRM];
+  double risk;
+  double height_goal;
+};
+
+// Device buffers of one batch (all pointers are device pointers; N = n_envs).
+struct hmj_buffers_t {
+  int32_t n;
+  // ---- state
+  double* qpos;       // [N][19]
+  double* qvel;       // [N][18]
+  double* time;       // [N]
+  double* warmstart;  // [N][18]
+  double* ctrl;       // [N][12]
+  double* xfrc;       // [N][6]   Cartesian wrench on one body (cpu_env.py:618-654)
+  int32_t* xfrc_body; // [N]
+  hmj_params_t* params;  // [N]
+  // ---- cross-kernel scratch (L2 resident)
+  double* geom_xpos;  // [N][10][3]
+  double* geom_xmat;  // [N][10][9]
+  double* cdof;       // [N][18][6]
+  double* com;        // [N][3]     subtree_com of the root body
+  double* qM;         // [N][117]
+  double* qfrc_smooth;// [N][18]
+  double* sens;       // [N][16]    torso xpos(3), xquat body1 (4), xpos body1 z, site z..., see SENS_*
+  double* slots;      // [N][NSLOT][8]
+  // ---- outputs
+  double* qacc;            // [N][18]
+  double* qacc_smooth;     // [N][18]
+  double* qfrc_constraint; // [N][18]
+  hmj_contact_t* contact;  // [N][MAXCON]
+  int32_t* ncon;           // [N]
+  int32_t* nefc;           // [N]
+  int32_t* niter;          // [N]
+  int32_t* status;         // [N]
+  // ---- planner accumulators
+  double* residual;   // [N][28] residual of the latest forward pass
+  double* cost_sum;   // [N]     running sum of CostValue(residual_t)
+  double* cost_last;  // [N]     CostValue of the latest forward pass
+  double* trace;      // [N][3]
+};
+
+#define SENS_TORSO_XPOS 0   /* xpos[2] (3) */
+#define SENS_ROOT_XQUAT 3   /* xquat[1] (4) */
+#define SENS_ROOT_Z 7       /* xpos[1][2] */
+#define SENS_NUM 16
+
+// ------------------------------------------------------------------ small math (device)
+__device__ __forceinline__ void d_mul_quat(double* r, const double* a, const double* b) {
+  double t0 = a[0] * b[0] - a[1] * b[1] - a[2] * b[2] - a[3] * b[3];
+  double t1 = a[0] * b[1] + a[1] * b[0] + a[2] * b[3] - a[3] * b[2];
+  double t2 = a[0] * b[2] - a[1] * b[3] + a[2] * b[0] + a[3] * b[1];
+  double t3 = a[0] * b[3] + a[1] * b[2] - a[2] * b[1] + a[3] * b[0];
+  r[0] = t0; r[1] = t1; r[2] = t2; r[3] = t3;
+}
+
+__device__ __forceinline__ void d_quat2mat(double* r, const double* q) {
+  double q00 = q[0] * q[0], q01 = q[0] * q[1], q02 = q[0] * q[2], q03 = q[0] * q[3];
+  double q11 = q[1] * q[1], q12 = q[1] * q[2], q13 = q[1] * q[3];
+  double q22 = q[2] * q[2], q23 = q[2] * q[3], q33 = q[3] * q[3];
+  r[0] = q00 + q11 - q22 - q33;
+  r[4] = q00 - q11 + q22 - q33;
+  r[8] = q00 - q11 - q22 + q33;
+  r[1] = 2 * (q12 - q03);
+  r[2] = 2 * (q13 + q02);
+  r[3] = 2 * (q12 + q03);
+  r[5] = 2 * (q23 - q01);
+  r[6] = 2 * (q13 - q02);
+  r[7] = 2 * (q23 + q01);
+}
+
+__device__ __forceinline__ void d_rot_vec_quat(double* res, const double* v, const double* q) {
+  double t0 = q[0] * v[0] + q[2] * v[2] - q[3] * v[1];
+  double t1 = q[0] * v[1] + q[3] * v[0] - q[1] * v[2];
+  double t2 = q[0] * v[2] + q[1] * v[1] - q[2] * v[0];
+  double r0 = v[0] + 2 * (q[2] * t2 - q[3] * t1);
+  double r1 = v[1] + 2 * (q[3] * t0 - q[1] * t2);
+  double r2 = v[2] + 2 * (q[1] * t1 - q[2] * t0);
+  res[0] = r0; res[1] = r1; res[2] = r2;
+}
+
+__device__ __forceinline__ void d_rot_vec_mat(double* res, const double* v, const double* m) {
+  double r0 = m[0] * v[0] + m[1] * v[1] + m[2] * v[2];
+  double r1 = m[3] * v[0] + m[4] * v[1] + m[5] * v[2];
+  double r2 = m[6] * v[0] + m[7] * v[1] + m[8] * v[2];
+  res[0] = r0; res[1] = r1; res[2] = r2;
+}
+
+__device__ __forceinline__ void d_cross(double* r, const double* a, const double* b) {
+  double r0 = a[1] * b[2] - a[2] * b[1];
+  double r1 = a[2] * b[0] - a[0] * b[2];
+  double r2 = a[0] * b[1] - a[1] * b[0];
+  r[0] = r0; r[1] = r1; r[2] = r2;
+}
+
+__device__ __forceinline__ double d_normalize3(double* v) {
+  double n = sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+  if (n < HMJ_MINVAL) {
+    v[0] = 1; v[1] = 0; v[2] = 0;
+  } else {
+    double s = 1.0 / n;
+    v[0] *= s; v[1] *= s; v[2] *= s;
+  }
+  return n;
+}
+
+__device__ __forceinline__ double d_normalize4(double* q) {
+  double n = sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+  if (n < HMJ_MINVAL) {
+    q[0] = 1; q[1] = 0; q[2] = 0; q[3] = 0;
+  } else if (fabs(n - 1) > HMJ_MINVAL) {
+    double s = 1.0 / n;
+    q[0] *= s; q[1] *= s; q[2] *= s; q[3] *= s;
+  }
+  return n;
+}
+
+__device__ __forceinline__ void d_axis_angle2quat(double* q, const double* axis, double angle) {
+  if (angle == 0) {
+    q[0] = 1; q[1] = 0; q[2] = 0; q[3] = 0;
+  } else {
+    double s, c;
+    sincos(angle * 0.5, &s, &c);
+    q[0] = c; q[1] = axis[0] * s; q[2] = axis[1] * s; q[3] = axis[2] * s;
+  }
+}
+
+__device__ __forceinline__ void d_mul_inert_vec(double* res, const double* i, const double* v) {
+  res[0] = i[0] * v[0] + i[3] * v[1] + i[4] * v[2] - i[8] * v[4] + i[7] * v[5];
+  res[1] = i[3] * v[0] + i[1] * v[1] + i[5] * v[2] + i[8] * v[3] - i[6] * v[5];
+  res[2] = i[4] * v[0] + i[5] * v[1] + i[2] * v[2] - i[7] * v[3] + i[6] * v[4];
+  res[3] = i[8] * v[1] - i[7] * v[2] + i[9] * v[3];
+  res[4] = i[6] * v[2] - i[8] * v[0] + i[9] * v[4];
+  res[5] = i[7] * v[0] - i[6] * v[1] + i[9] * v[5];
+}
+
+__device__ __forceinline__ void d_cross_motion(double* res, const double* vel, const double* v) {
+  res[0] = -vel[2] * v[1] + vel[1] * v[2];
+  res[1] = vel[2] * v[0] - vel[0] * v[2];
+  res[2] = -vel[1] * v[0] + vel[0] * v[1];
+  res[3] = -vel[2] * v[4] + vel[1] * v[5] - vel[5] * v[1] + vel[4] * v[2];
+  res[4] = vel[2] * v[3] - vel[0] * v[5] + vel[5] * v[0] - vel[3] * v[2];
+  res[5] = -vel[1] * v[3] + vel[0] * v[4] - vel[4] * v[0] + vel[3] * v[1];
+}
+
+__device__ __forceinline__ void d_cross_force(double* res, const double* vel, const double* f) {
+  res[0] = -vel[2] * f[1] + vel[1] * f[2] - vel[5] * f[4] + vel[4] * f[5];
+  res[1] = vel[2] * f[0] - vel[0] * f[2] + vel[5] * f[3] - vel[3] * f[5];
+  res[2] = -vel[1] * f[0] + vel[0] * f[1] - vel[4] * f[3] + vel[3] * f[4];
+  res[3] = -vel[2] * f[4] + vel[1] * f[5];
+  res[4] = vel[2] * f[3] - vel[0] * f[5];
+  res[5] = -vel[1] * f[3] + vel[0] * f[4];
+}
+
+__device__ __forceinline__ double d_dot6(const double* a, const double* b) {
+  return a[0] * b[0] + a[1] * b[1] + a[2] * b[2] + a[3] * b[3] + a[4] * b[4] + a[5] * b[5];
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__device__ __forceinline__ bool d_is_bad(double x) { return isnan(x) || x > HMJ_MAXVAL || x < -HMJ_MAXVAL; }
+
+// kernel launchers (defined in the .cu files, called from hmj_api.cu)
+void hmj_launch_smooth(const hmj_tables_t* tab, hmj_buffers_t buf, const hmj_task_t* task, int plan_mode,
+                       const double* spline_times, const double* spline_values, int nnode, int interpolation,
+                       int values_per_env, cudaStream_t stream);
+void hmj_launch_collide(const hmj_tables_t* tab, hmj_buffers_t buf, cudaStream_t stream);
+void hmj_launch_solve(const hmj_tables_t* tab, hmj_buffers_t buf, int integrate, cudaStream_t stream);
+
+// plan_mode bits for hmj_launch_smooth
+#define HMJ_PLAN_COST 1    /* sensors -> residual -> cost accumulation */
+#define HMJ_PLAN_POLICY 2  /* ctrl from the spline policy at data time */
+
+// trajectory recording buffers (optional), layout [H][N][dim]
+struct hmj_record_t {
+  int32_t horizon;
+  double* states;   // [H][N][37]
+  double* actions;  // [H][N][12]
+  double* times;    // [H][N]
+  double* residual; // [H][N][28]
+  double* costs;    // [H][N]
+  double* trace;    // [H][N][3]
+};
+
+void hmj_launch_plan_init(hmj_buffers_t buf, const double* state_dev, double time, cudaStream_t stream);
+void hmj_launch_plan_record(hmj_buffers_t buf, hmj_record_t rec, int t, cudaStream_t stream);
+void hmj_launch_plan_finish(hmj_buffers_t buf, int horizon, double* returns_dev, int32_t* failure_dev, cudaStream_t stream);
+void hmj_launch_argmin(const double* returns_dev, int n, double* out_cost_idx_dev, cudaStream_t stream);
+void hmj_launch_env_obs_reward(const hmj_tables_t* tab, hmj_buffers_t buf, const double* prev_action, const double* latest_action,
+                               const double* noise, double max_sim_time, double* obs, double* reward, int32_t* terminated,
+                               int32_t* truncated, int32_t* self_collision, cudaStream_t stream);

@@ -1,0 +1,500 @@
+// hmj_smooth.cu — kernel 1 of the step: everything in mj_forward that does not depend on contacts.
+//
+//   mj_checkPos/Vel -> [planner: spline policy -> ctrl] -> mj_kinematics -> mj_comPos -> mj_crb
+//   -> mj_comVel -> mj_passive -> mj_rne -> mj_fwdActuation -> qfrc_smooth (+ xfrc_applied)
+//   -> [planner: sensors -> humanoid_cap Stand residual -> norms -> running cost]
+//
+// Restates (B200-first) the stages declared at simulation/mujoco/include/mujoco/mujoco.h:301-304,
+// 310-349,253 and mjpc/planners/sampling/policy.cc:52-59, mjpc/spline/spline.cc:103-156,
+// mjpc/tasks/humanoid_cap/stand/stand.cc:40-99, mjpc/task.cc:71-110, mjpc/norm.cc:50-210.
+//
+// Mapping: one warp per environment; lanes own bodies (15), dofs (18), geoms (10) or sparse-M
+// entries (117); the kinematic tree is walked level by level (bodies of equal depth in
+// parallel); per-env working set (~13 KB) lives in shared memory; subtree reductions use
+// warp shuffles.  Roofline: FP64 FMA pipe / issue-latency bound; HBM traffic is the state row
+// (qpos,qvel,ctrl,params: ~1.7 KB in) and the scratch row (geom frames, cdof, qM: ~3 KB out, L2).
+#include "hmj_dev.cuh"
+
+struct SmoothSmem {
+  double qpos[HMJ_NQ + 1];
+  double qvel[HMJ_NV];
+  double ctrl[HMJ_NU];
+  double xpos[HMJ_NBODY][3];
+  double xquat[HMJ_NBODY][4];
+  double xmat[HMJ_NBODY][9];
+  double xipos[HMJ_NBODY][3];
+  double ximat[HMJ_NBODY][9];
+  double xanchor[HMJ_NJNT][3];
+  double xaxis[HMJ_NJNT][3];
+  double site_xpos[HMJ_NSITE][3];
+  double cinert[HMJ_NBODY][10];
+  double crb[HMJ_NBODY][10];   // later reused for accumulated cfrc
+  double cdof[HMJ_NV][6];
+  double cdof_dot[HMJ_NV][6];
+  double buf[HMJ_NV][6];
+  double cvel[HMJ_NBODY][6];
+  double cacc[HMJ_NBODY][6];
+  double cfrc[HMJ_NBODY][6];
+  double qfrc_passive[HMJ_NV];
+  double qfrc_bias[HMJ_NV];
+  double qfrc_actuator[HMJ_NV];
+  double com[4];
+  double residual[HMJ_NRESIDUAL];
+};
+
+__device__ __forceinline__ void inert_com(double* res, const double* inert, const double* mat, const double* dif, double mass) {
+  double t0 = mat[0] * inert[0], t1 = mat[3] * inert[0], t2 = mat[6] * inert[0];
+  double t3 = mat[1] * inert[1], t4 = mat[4] * inert[1], t5 = mat[7] * inert[1];
+  double t6 = mat[2] * inert[2], t7 = mat[5] * inert[2], t8 = mat[8] * inert[2];
+  res[0] = mat[0] * t0 + mat[1] * t3 + mat[2] * t6 + mass * (dif[1] * dif[1] + dif[2] * dif[2]);
+  res[1] = mat[3] * t1 + mat[4] * t4 + mat[5] * t7 + mass * (dif[0] * dif[0] + dif[2] * dif[2]);
+  res[2] = mat[6] * t2 + mat[7] * t5 + mat[8] * t8 + mass * (dif[0] * dif[0] + dif[1] * dif[1]);
+  res[3] = mat[0] * t1 + mat[1] * t4 + mat[2] * t7 - mass * dif[0] * dif[1];
+  res[4] = mat[0] * t2 + mat[1] * t5 + mat[2] * t8 - mass * dif[0] * dif[2];
+  res[5] = mat[3] * t2 + mat[4] * t5 + mat[5] * t8 - mass * dif[1] * dif[2];
+  res[6] = mass * dif[0]; res[7] = mass * dif[1]; res[8] = mass * dif[2];
+  res[9] = mass;
+}
+
+// TimeSpline::Sample for one value dimension (spline.cc:103-156, Slope :259-277, CubicCoefficients :240-257)
+__device__ double spline_slope(const double* times, const double* vals, int stride, int n, int node) {
+  if (node == 0) return (vals[stride] - vals[0]) / (times[1] - times[0]);
+  const double* v = vals + (size_t)node * stride;
+  if (node == n - 1) return (v[0] - v[-stride]) / (times[node] - times[node - 1]);
+  return 0.5 * (v[stride] - v[0]) / (times[node + 1] - times[node]) + 0.5 * (v[0] - v[-stride]) / (times[node] - times[node - 1]);
+}
+
+__device__ double spline_sample1(const double* times, const double* vals, int stride, int n, int interpolation, double time) {
+  if (n == 0) return 0.0;
+  int upper = 0;
+  while (upper < n && !(time < times[upper])) upper++;
+  if (upper == n) return vals[(size_t)(n - 1) * stride];
+  if (upper == 0) return vals[0];
+  int lower = upper - 1;
+  double dt = times[upper] - times[lower];
+  double t = (time - times[lower]) / dt;
+  double lo = vals[(size_t)lower * stride], up = vals[(size_t)upper * stride];
+  if (interpolation == 0) return lo;
+  if (interpolation == 1) return lo * (1 - t) + up * t;
+  double c0 = 2.0 * t * t * t - 3.0 * t * t + 1.0;
+  double c1 = (t * t * t - 2.0 * t * t + t) * dt;
+  double c2 = -2.0 * t * t * t + 3 * t * t;
+  double c3 = (t * t * t - t * t) * dt;
+  double m0 = spline_slope(times, vals, stride, n, lower);
+  double m1 = spline_slope(times, vals, stride, n, upper);
+  return c0 * lo + c1 * m0 + c2 * up + c3 * m1;
+}
+
+// mjpc Norm, value only (norm.cc:50-210)
+__device__ double norm_value(const double* x, const double* prm, int n, int type) {
+  double y = 0, p = prm[0], q = prm[1];
+  switch (type) {
+    case -1: y = x[0]; break;
+    case 0:
+      for (int i = 0; i < n; i++) y += x[i] * x[i];
+      y *= 0.5;
+      break;
+    case 1: {
+      double c = 0;
+      for (int i = 0; i < n; i++) c += x[i] * x[i];
+      y = pow(pow(c, q / 2) + pow(p, q), 1 / q) - p;
+      break;
+    }
+    case 2: {
+      double c = 0;
+      for (int i = 0; i < n; i++) c += x[i] * x[i];
+      y = sqrt(c + p * p) - p;
+      break;
+    }
+    case 3:
+      for (int i = 0; i < n; i++) y += p * p * (cosh(x[i] / p) - 1.0);
+      break;
+    case 5:
+      for (int i = 0; i < n; i++) y += pow(fabs(x[i]), p);
+      break;
+    case 6:
+      for (int i = 0; i < n; i++) y += sqrt(x[i] * x[i] + p * p) - p;
+      break;
+    case 7:
+      for (int i = 0; i < n; i++) y += pow(pow(fabs(x[i]), q) + pow(p, q), 1 / q) - p;
+      break;
+    case 8:
+      for (int i = 0; i < n; i++) y += (p > 0) ? p * log(1 + exp(x[i] / p)) : (x[i] > 0 ? x[i] : 0);
+      break;
+    default: y = nan("");
+  }
+  return y;
+}
+
+__global__ void __launch_bounds__(32 * HMJ_WARPS_PER_CTA)
+k_smooth(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* __restrict__ task, int plan_mode,
+         const double* __restrict__ spline_times, const double* __restrict__ spline_values, int nnode,
+         int interpolation, int values_per_env) {
+  extern __shared__ double smem_raw[];
+  const int lane = threadIdx.x & 31;
+  const int wib = threadIdx.x >> 5;
+  const int env = blockIdx.x * HMJ_WARPS_PER_CTA + wib;
+  if (env >= B.n) return;  // whole warp exits together
+  SmoothSmem& S = reinterpret_cast<SmoothSmem*>(smem_raw)[wib];
+  const hmj_model_t& M = T->m;
+  const hmj_params_t* P = B.params + env;
+  const unsigned FULL = 0xffffffffu;
+
+  // ---------------- load state, mj_checkPos / mj_checkVel
+  double* g_qpos = B.qpos + (size_t)env * HMJ_NQ;
+  double* g_qvel = B.qvel + (size_t)env * HMJ_NV;
+  double* g_ctrl = B.ctrl + (size_t)env * HMJ_NU;
+  double qp = lane < HMJ_NQ ? g_qpos[lane] : 0.0;
+  double qv = lane < HMJ_NV ? g_qvel[lane] : 0.0;
+  int status = 0;
+  bool badq = __any_sync(FULL, d_is_bad(qp));
+  bool badv = __any_sync(FULL, d_is_bad(qv));
+  if (badq || badv) {  // mj_resetData semantics for this path
+    status |= badq ? HMJ_STATUS_BADQPOS : HMJ_STATUS_BADQVEL;
+    qp = lane < HMJ_NQ ? M.qpos0[lane] : 0.0;
+    qv = 0.0;
+    if (lane < HMJ_NQ) g_qpos[lane] = qp;
+    if (lane < HMJ_NV) { g_qvel[lane] = 0.0; B.warmstart[(size_t)env * HMJ_NV + lane] = 0.0; }
+    if (lane < HMJ_NU) g_ctrl[lane] = 0.0;
+    if (lane < 6) B.xfrc[(size_t)env * 6 + lane] = 0.0;
+    if (lane == 0) B.time[env] = 0.0;
+  }
+  if (lane < HMJ_NQ) S.qpos[lane] = qp;
+  if (lane < HMJ_NV) S.qvel[lane] = qv;
+
+  // ---------------- control: planner spline policy (SamplingPolicy::Action) or caller-provided ctrl
+  double u = 0.0;
+  if (lane < HMJ_NU) {
+    if ((plan_mode & 2) && !(badq || badv)) {
+      const double* vals = spline_values + (values_per_env ? (size_t)env * nnode * HMJ_NU : 0) + lane;
+      u = spline_sample1(spline_times, vals, HMJ_NU, nnode, interpolation, B.time[env]);
+      u = fmin(fmax(u, M.act_ctrlrange[lane][0]), M.act_ctrlrange[lane][1]);  // Clamp (utilities.cc:94-98)
+      g_ctrl[lane] = u;
+    } else {
+      u = g_ctrl[lane];
+    }
+  }
+  if (__any_sync(FULL, lane < HMJ_NU && d_is_bad(u))) {  // mjWARN_BADCTRL: controls zeroed
+    status |= HMJ_STATUS_BADCTRL;
+    u = 0.0;
+    if (lane < HMJ_NU) g_ctrl[lane] = 0.0;
+  }
+  if (lane < HMJ_NU) S.ctrl[lane] = u;
+  if (lane == 0) {
+    S.xpos[0][0] = S.xpos[0][1] = S.xpos[0][2] = 0;
+    S.xquat[0][0] = 1; S.xquat[0][1] = S.xquat[0][2] = S.xquat[0][3] = 0;
+    for (int k = 0; k < 9; k++) S.xmat[0][k] = (k % 4 == 0) ? 1.0 : 0.0;
+    for (int k = 0; k < 6; k++) { S.cvel[0][k] = 0; S.cfrc[0][k] = 0; }
+    S.cacc[0][0] = S.cacc[0][1] = S.cacc[0][2] = 0;
+    S.cacc[0][3] = -M.gravity[0]; S.cacc[0][4] = -M.gravity[1]; S.cacc[0][5] = -M.gravity[2];
+    for (int k = 0; k < 10; k++) S.cinert[0][k] = 0;
+    S.xipos[0][0] = S.xipos[0][1] = S.xipos[0][2] = 0;
+  }
+  __syncwarp();
+
+  // ---------------- mj_kinematics, level by level
+  for (int L = 1; L < T->nlevel; L++) {
+    if (lane < T->level_n[L]) {
+      const int b = T->level_body[L][lane];
+      const int pid = M.body_parentid[b];
+      const int jadr = M.body_jntadr[b];
+      double xpos[3], xquat[4];
+      if (M.body_jntnum[b] == 1 && M.jnt_type[jadr] == HMJ_JNT_FREE) {
+        const int qadr = M.jnt_qposadr[jadr];
+        xpos[0] = S.qpos[qadr]; xpos[1] = S.qpos[qadr + 1]; xpos[2] = S.qpos[qadr + 2];
+        xquat[0] = S.qpos[qadr + 3]; xquat[1] = S.qpos[qadr + 4]; xquat[2] = S.qpos[qadr + 5]; xquat[3] = S.qpos[qadr + 6];
+        d_normalize4(xquat);
+        for (int k = 0; k < 3; k++) { S.xanchor[jadr][k] = xpos[k]; S.xaxis[jadr][k] = M.jnt_axis[jadr][k]; }
+      } else {
+        if (pid) {
+          d_rot_vec_mat(xpos, M.body_pos[b], S.xmat[pid]);
+          xpos[0] += S.xpos[pid][0]; xpos[1] += S.xpos[pid][1]; xpos[2] += S.xpos[pid][2];
+          d_mul_quat(xquat, S.xquat[pid], M.body_quat[b]);
+        } else {
+          for (int k = 0; k < 3; k++) xpos[k] = M.body_pos[b][k];
+          for (int k = 0; k < 4; k++) xquat[k] = M.body_quat[b][k];
+        }
+        if (M.body_jntnum[b] == 1) {  // one hinge
+          const int qadr = M.jnt_qposadr[jadr];
+          double axis[3], anchor[3], qloc[4], vec[3];
+          d_rot_vec_quat(axis, M.jnt_axis[jadr], xquat);
+          d_rot_vec_quat(anchor, M.jnt_pos[jadr], xquat);
+          anchor[0] += xpos[0]; anchor[1] += xpos[1]; anchor[2] += xpos[2];
+          d_axis_angle2quat(qloc, M.jnt_axis[jadr], S.qpos[qadr] - M.qpos0[qadr]);
+          d_mul_quat(xquat, xquat, qloc);
+          d_rot_vec_quat(vec, M.jnt_pos[jadr], xquat);
+          for (int k = 0; k < 3; k++) {
+            xpos[k] = anchor[k] - vec[k];
+            S.xanchor[jadr][k] = anchor[k];
+            S.xaxis[jadr][k] = axis[k];
+          }
+        }
+      }
+      d_normalize4(xquat);
+      for (int k = 0; k < 3; k++) S.xpos[b][k] = xpos[k];
+      for (int k = 0; k < 4; k++) S.xquat[b][k] = xquat[k];
+      d_quat2mat(S.xmat[b], xquat);
+    }
+    __syncwarp();
+  }
+
+  // ---------------- inertial frames (lanes 1..14), geom frames (lanes 16..25), sites (lanes 26,27)
+  if (lane >= 1 && lane < HMJ_NBODY) {
+    const int b = lane;
+    if (M.body_sameframe[b]) {
+      for (int k = 0; k < 3; k++) S.xipos[b][k] = S.xpos[b][k];
+      for (int k = 0; k < 9; k++) S.ximat[b][k] = S.xmat[b][k];
+    } else {
+      double t[4], p[3];
+      d_rot_vec_mat(p, M.body_ipos[b], S.xmat[b]);
+      for (int k = 0; k < 3; k++) S.xipos[b][k] = p[k] + S.xpos[b][k];
+      d_mul_quat(t, S.xquat[b], M.body_iquat[b]);
+      d_quat2mat(S.ximat[b], t);
+    }
+  } else if (lane >= 16 && lane < 16 + HMJ_NGEOM) {
+    const int g = lane - 16, b = M.geom_bodyid[g];
+    double t[4], p[3], mat[9];
+    d_rot_vec_mat(p, M.geom_pos[g], S.xmat[b]);
+    d_mul_quat(t, S.xquat[b], M.geom_quat[g]);
+    d_quat2mat(mat, t);
+    double* gp = B.geom_xpos + ((size_t)env * HMJ_NGEOM + g) * 3;
+    double* gm = B.geom_xmat + ((size_t)env * HMJ_NGEOM + g) * 9;
+    for (int k = 0; k < 3; k++) gp[k] = p[k] + S.xpos[b][k];
+    for (int k = 0; k < 9; k++) gm[k] = mat[k];
+  } else if (lane >= 26 && lane < 26 + HMJ_NSITE) {
+    const int s = lane - 26, b = M.site_bodyid[s];
+    double p[3];
+    d_rot_vec_mat(p, M.site_pos[s], S.xmat[b]);
+    for (int k = 0; k < 3; k++) S.site_xpos[s][k] = p[k] + S.xpos[b][k];
+  }
+  __syncwarp();
+
+  // ---------------- mj_comPos: subtree CoM of the root (all moving bodies share root body 1)
+  const double mass = (lane >= 1 && lane < HMJ_NBODY) ? P->body_mass[lane] : 0.0;
+  {
+    double cx = 0, cy = 0, cz = 0;
+    if (lane >= 1 && lane < HMJ_NBODY) { cx = mass * S.xipos[lane][0]; cy = mass * S.xipos[lane][1]; cz = mass * S.xipos[lane][2]; }
+    cx = warp_sum(cx); cy = warp_sum(cy); cz = warp_sum(cz);
+    const double stm = M.body_subtreemass[1];  // compile-time constant (no mj_setConst after DR)
+    if (stm < HMJ_MINVAL) { cx = S.xipos[1][0]; cy = S.xipos[1][1]; cz = S.xipos[1][2]; }
+    else { double s = 1.0 / fmax(HMJ_MINVAL, stm); cx *= s; cy *= s; cz *= s; }
+    if (lane == 0) {
+      S.com[0] = cx; S.com[1] = cy; S.com[2] = cz;
+      double* gc = B.com + (size_t)env * 3;
+      gc[0] = cx; gc[1] = cy; gc[2] = cz;
+    }
+  }
+  __syncwarp();
+  if (lane >= 1 && lane < HMJ_NBODY) {
+    double off[3] = {S.xipos[lane][0] - S.com[0], S.xipos[lane][1] - S.com[1], S.xipos[lane][2] - S.com[2]};
+    inert_com(S.cinert[lane], M.body_inertia[lane], S.ximat[lane], off, mass);
+  }
+  if (lane < HMJ_NV) {  // cdof, one dof per lane
+    const int d = lane, j = M.dof_jntid[d], bi = M.jnt_bodyid[j];
+    double off[3] = {S.com[0] - S.xanchor[j][0], S.com[1] - S.xanchor[j][1], S.com[2] - S.xanchor[j][2]};
+    double* c = S.cdof[d];
+    if (M.jnt_type[j] == HMJ_JNT_FREE) {
+      const int k = d - M.jnt_dofadr[j];
+      if (k < 3) {
+        for (int q = 0; q < 6; q++) c[q] = 0;
+        c[3 + k] = 1;
+      } else {
+        double ax[3] = {S.xmat[bi][k - 3], S.xmat[bi][k - 3 + 3], S.xmat[bi][k - 3 + 6]};
+        c[0] = ax[0]; c[1] = ax[1]; c[2] = ax[2];
+        d_cross(c + 3, ax, off);
+      }
+    } else {
+      c[0] = S.xaxis[j][0]; c[1] = S.xaxis[j][1]; c[2] = S.xaxis[j][2];
+      d_cross(c + 3, S.xaxis[j], off);
+    }
+    double* gc = B.cdof + ((size_t)env * HMJ_NV + d) * 6;
+    for (int q = 0; q < 6; q++) gc[q] = c[q];
+  }
+  __syncwarp();
+
+  // ---------------- mj_crb: composite inertia = sum of cinert over the body's subtree; sparse M
+  if (lane >= 1 && lane < HMJ_NBODY) {
+    double acc[10];
+    for (int k = 0; k < 10; k++) acc[k] = S.cinert[lane][k];
+    for (int c = lane + 1; c < T->subtree_end[lane]; c++)
+      for (int k = 0; k < 10; k++) acc[k] += S.cinert[c][k];
+    for (int k = 0; k < 10; k++) S.crb[lane][k] = acc[k];
+  }
+  __syncwarp();
+  if (lane < HMJ_NV) d_mul_inert_vec(S.buf[lane], S.crb[M.dof_bodyid[lane]], S.cdof[lane]);
+  __syncwarp();
+  for (int e = lane; e < HMJ_NM; e += 32) {
+    const int i = T->M_row[e], j = T->M_col[e];
+    double v = d_dot6(S.cdof[j], S.buf[i]);
+    if (i == j) v += P->dof_armature[i];
+    B.qM[(size_t)env * HMJ_NM + e] = v;
+  }
+
+  // ---------------- mj_comVel (cvel, cdof_dot) and the acceleration pass of mj_rne, by level
+  for (int L = 1; L < T->nlevel; L++) {
+    if (lane < T->level_n[L]) {
+      const int b = T->level_body[L][lane], pid = M.body_parentid[b];
+      const int bda = M.body_dofadr[b], dn = M.body_dofnum[b];
+      double cvel[6], cacc[6];
+      for (int k = 0; k < 6; k++) { cvel[k] = S.cvel[pid][k]; cacc[k] = S.cacc[pid][k]; }
+      if (dn == 6) {
+        for (int j = 0; j < 3; j++) {
+          for (int k = 0; k < 6; k++) { S.cdof_dot[bda + j][k] = 0; cvel[k] += S.cdof[bda + j][k] * S.qvel[bda + j]; }
+        }
+        for (int j = 3; j < 6; j++) d_cross_motion(S.cdof_dot[bda + j], cvel, S.cdof[bda + j]);
+        for (int j = 3; j < 6; j++)
+          for (int k = 0; k < 6; k++) cvel[k] += S.cdof[bda + j][k] * S.qvel[bda + j];
+      } else {
+        for (int j = 0; j < dn; j++) {
+          d_cross_motion(S.cdof_dot[bda + j], cvel, S.cdof[bda + j]);
+          for (int k = 0; k < 6; k++) cvel[k] += S.cdof[bda + j][k] * S.qvel[bda + j];
+        }
+      }
+      for (int j = 0; j < dn; j++)
+        for (int k = 0; k < 6; k++) cacc[k] += S.cdof_dot[bda + j][k] * S.qvel[bda + j];
+      for (int k = 0; k < 6; k++) { S.cvel[b][k] = cvel[k]; S.cacc[b][k] = cacc[k]; }
+    }
+    __syncwarp();
+  }
+
+  // ---------------- mj_rne: body forces, subtree accumulation, projection on dofs
+  if (lane >= 1 && lane < HMJ_NBODY) {
+    double f[6], t[6], t1[6];
+    d_mul_inert_vec(f, S.cinert[lane], S.cacc[lane]);
+    d_mul_inert_vec(t, S.cinert[lane], S.cvel[lane]);
+    d_cross_force(t1, S.cvel[lane], t);
+    for (int k = 0; k < 6; k++) S.cfrc[lane][k] = f[k] + t1[k];
+  }
+  __syncwarp();
+  if (lane >= 1 && lane < HMJ_NBODY) {
+    double acc[6];
+    for (int k = 0; k < 6; k++) acc[k] = S.cfrc[lane][k];
+    for (int c = lane + 1; c < T->subtree_end[lane]; c++)
+      for (int k = 0; k < 6; k++) acc[k] += S.cfrc[c][k];
+    for (int k = 0; k < 6; k++) S.crb[lane][k] = acc[k];  // reuse crb rows as accumulated cfrc
+  }
+  __syncwarp();
+
+  // ---------------- mj_passive, mj_fwdActuation
+  if (lane < HMJ_NV) {
+    const int d = lane, j = M.dof_jntid[d];
+    const double stiff = P->jnt_stiffness[j];
+    double spring = 0.0;
+    if (stiff != 0) {
+      const int padr = M.jnt_qposadr[j], dadr = M.jnt_dofadr[j];
+      if (M.jnt_type[j] == HMJ_JNT_FREE) {
+        const int k = d - dadr;
+        if (k < 3) {
+          spring = -stiff * (S.qpos[padr + k] - M.qpos_spring[padr + k]);
+        } else {  // mju_subQuat(qpos quat, spring quat) as a 3D velocity
+          double quat[4] = {S.qpos[padr + 3], S.qpos[padr + 4], S.qpos[padr + 5], S.qpos[padr + 6]};
+          double qneg[4] = {M.qpos_spring[padr + 3], -M.qpos_spring[padr + 4], -M.qpos_spring[padr + 5], -M.qpos_spring[padr + 6]};
+          double qdif[4], axis[3];
+          d_normalize4(quat);
+          d_mul_quat(qdif, qneg, quat);
+          axis[0] = qdif[1]; axis[1] = qdif[2]; axis[2] = qdif[3];
+          double sin_a_2 = d_normalize3(axis);
+          double speed = 2 * atan2(sin_a_2, qdif[0]);
+          if (speed > HMJ_PI) speed -= 2 * HMJ_PI;
+          spring = -stiff * (axis[k - 3] * speed);
+        }
+      } else {
+        spring = -stiff * (S.qpos[padr] - M.qpos_spring[padr]);
+      }
+    }
+    S.qfrc_passive[d] = spring + (-M.dof_damping[d] * S.qvel[d]);
+    S.qfrc_bias[d] = d_dot6(S.cdof[d], S.crb[M.dof_bodyid[d]]);
+    S.qfrc_actuator[d] = 0.0;
+  }
+  __syncwarp();
+  if (lane < HMJ_NU) {
+    double c = fmin(fmax(S.ctrl[lane], M.act_ctrlrange[lane][0]), M.act_ctrlrange[lane][1]);
+    double force = P->act_gainprm0[lane] * c;
+    force = fmin(fmax(force, P->act_forcerange[lane][0]), P->act_forcerange[lane][1]);
+    S.qfrc_actuator[M.act_dofadr[lane]] = M.act_gear[lane] * force;
+  }
+  __syncwarp();
+
+  // ---------------- qfrc_smooth = passive - bias + actuator + J' xfrc_applied
+  if (lane < HMJ_NV) {
+    const int d = lane;
+    double f = S.qfrc_passive[d] - S.qfrc_bias[d];
+    f += S.qfrc_actuator[d];
+    const int xb = B.xfrc_body[env];
+    if (xb > 0 && xb < HMJ_NBODY) {
+      const double* w = B.xfrc + (size_t)env * 6;
+      if ((w[0] != 0 || w[1] != 0 || w[2] != 0 || w[3] != 0 || w[4] != 0 || w[5] != 0) && ((T->body_dofmask[xb] >> d) & 1u)) {
+        double off[3] = {S.xipos[xb][0] - S.com[0], S.xipos[xb][1] - S.com[1], S.xipos[xb][2] - S.com[2]};
+        double tmp[3];
+        d_cross(tmp, S.cdof[d], off);
+        f += (S.cdof[d][3] + tmp[0]) * w[0] + (S.cdof[d][4] + tmp[1]) * w[1] + (S.cdof[d][5] + tmp[2]) * w[2];
+        f += S.cdof[d][0] * w[3] + S.cdof[d][1] * w[4] + S.cdof[d][2] * w[5];
+      }
+    }
+    B.qfrc_smooth[(size_t)env * HMJ_NV + d] = f;
+  }
+
+  // ---------------- values the env epilogue reads after the step (one-step-stale by contract)
+  if (lane < 3) B.sens[(size_t)env * SENS_NUM + SENS_TORSO_XPOS + lane] = S.xpos[2][lane];
+  if (lane < 4) B.sens[(size_t)env * SENS_NUM + SENS_ROOT_XQUAT + lane] = S.xquat[1][lane];
+  if (lane == 0) B.sens[(size_t)env * SENS_NUM + SENS_ROOT_Z] = S.xpos[1][2];
+  if (status && lane == 0) atomicOr(&B.status[env], status);
+
+  // ---------------- planner: sensors -> Stand residual -> cost accumulation
+  if (plan_mode & 1) {
+    // mj_subtreeVel for the root: whole-robot CoM velocity (torso_subtreelinvel is attached to body 1)
+    double lx = 0, ly = 0, lz = 0;
+    if (lane >= 1 && lane < HMJ_NBODY) {
+      double dx[3] = {S.xipos[lane][0] - S.com[0], S.xipos[lane][1] - S.com[1], S.xipos[lane][2] - S.com[2]};
+      double dv[3];
+      d_cross(dv, S.cvel[lane], dx);
+      lx = mass * (S.cvel[lane][3] + dv[0]); ly = mass * (S.cvel[lane][4] + dv[1]); lz = mass * (S.cvel[lane][5] + dv[2]);
+    }
+    lx = warp_sum(lx); ly = warp_sum(ly); lz = warp_sum(lz);
+    const double sinv = 1.0 / fmax(HMJ_MINVAL, M.body_subtreemass[1]);
+    lx *= sinv; ly *= sinv; (void)lz;
+    if (lane == 0) {
+      // torso_subtreecom is attached to body torso (no children): m2 * xipos2 / subtreemass2
+      double s2 = M.body_subtreemass[2] < HMJ_MINVAL ? 1.0 : P->body_mass[2] / fmax(HMJ_MINVAL, M.body_subtreemass[2]);
+      double comx = S.xipos[2][0] * s2, comy = S.xipos[2][1] * s2;
+      if (M.body_subtreemass[2] < HMJ_MINVAL) { comx = S.xipos[2][0]; comy = S.xipos[2][1]; }
+      const double* f1 = S.site_xpos[0];
+      const double* f2 = S.site_xpos[1];
+      S.residual[0] = (S.xpos[2][2] - 0.5 * (f1[2] + f2[2])) - task->height_goal;
+      double cpx = comx + lx * 0.2, cpy = comy + ly * 0.2;
+      double fx = (f1[0] + f2[0]) * 0.5 - cpx, fy = (f1[1] + f2[1]) * 0.5 - cpy;
+      S.residual[1] = sqrt(fx * fx + fy * fy);
+      S.residual[2] = lx;
+      S.residual[3] = ly;
+    }
+    if (lane < 12) { S.residual[4 + lane] = S.qvel[6 + lane]; S.residual[16 + lane] = S.ctrl[lane]; }
+    __syncwarp();
+    if (lane < HMJ_NRESIDUAL) B.residual[(size_t)env * HMJ_NRESIDUAL + lane] = S.residual[lane];
+    if (lane < 3) B.trace[(size_t)env * 3 + lane] = S.xpos[2][lane];
+    // CostTerms: one lane per term, then sum in term order (task.cc:71-110)
+    double term = 0.0;
+    if (lane < task->nterm) {
+      int shift = 0;
+      for (int k = 0; k < lane; k++) shift += task->dim[k];
+      term = task->weight[lane] * norm_value(S.residual + shift, task->normprm[lane], task->dim[lane], task->norm[lane]);
+    }
+    double cost = 0.0;
+    for (int k = 0; k < task->nterm; k++) cost += __shfl_sync(FULL, term, k);
+    if (fabs(task->risk) >= 1e-6) cost = (exp(task->risk * cost) - 1.0) / task->risk;
+    if (lane == 0) { B.cost_sum[env] += cost; B.cost_last[env] = cost; }
+  }
+}
+
+void hmj_launch_smooth(const hmj_tables_t* tab, hmj_buffers_t buf, const hmj_task_t* task, int plan_mode,
+                       const double* spline_times, const double* spline_values, int nnode, int interpolation,
+                       int values_per_env, cudaStream_t stream) {
+  static bool configured = false;
+  const size_t smem = sizeof(SmoothSmem) * HMJ_WARPS_PER_CTA;
+  if (!configured) {
+    cudaFuncSetAttribute(k_smooth, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    configured = true;
+  }
+  const int grid = (buf.n + HMJ_WARPS_PER_CTA - 1) / HMJ_WARPS_PER_CTA;
+  k_smooth<<<grid, 32 * HMJ_WARPS_PER_CTA, smem, stream>>>(tab, buf, task, plan_mode, spline_times, spline_values,
+                                                           nnode, interpolation, values_per_env);
+}

@@ -1,0 +1,122 @@
+/* hmj_b200.h — C ABI of the B200-native batched humanoid step / rollout engine.
+ *
+ * Drop-in boundary for the two seams of mcgill-robotics/Humanoid-MuJoCo:
+ *
+ *  B1  Python env:  `mujoco.mj_step(self.model, self.data)` at simulation/cpu_env.py:684 plus the
+ *      reads around it (cpu_env.py:418-440,465-616) -> hmj_batch_* (N lock-step environments).
+ *  B2  mjpc planner: `SamplingPlanner::Rollouts` (mjpc/planners/sampling/planner.cc:342-380) ->
+ *      `Trajectory::Rollout` (mjpc/trajectory.cc:100-210) -> hmj_plan_* (N samples x H knots).
+ *
+ * Plain C: opaque handle, int status codes (0 = ok, <0 = error, see hmj_last_error), caller-owned
+ * buffers, no exceptions and no torch / C++ types across the boundary.  One host thread per handle.
+ * Host pointers unless the name says `_dev`.  All floating-point data is fp64 (mjtNum = double,
+ * simulation/mujoco/include/mujoco/mjtnum.h:27); hfield samples are fp32 (mjmodel.h:908).
+ */
+#ifndef HMJ_B200_H_
+#define HMJ_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#include "hmj_model.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct hmj_batch_ hmj_batch_t;
+
+#define HMJ_OK 0
+#define HMJ_ERR_CUDA (-1)
+#define HMJ_ERR_ARG (-2)
+#define HMJ_ERR_MODEL (-3)
+
+/* stages for hmj_batch_run_stage (one kernel each) */
+#define HMJ_STAGE_SMOOTH 1   /* kinematics .. qfrc_smooth            (mujoco.h:310-349,253) */
+#define HMJ_STAGE_COLLIDE 2  /* mj_collision narrowphase             (mujoco.h:355) */
+#define HMJ_STAGE_SOLVE 3    /* constraints + Newton, no integration (mujoco.h:358,367,259) */
+#define HMJ_STAGE_SOLVE_INTEGRATE 4 /* ... + mj_Euler                (mujoco.h:262) */
+
+const char* hmj_last_error(void);
+int hmj_device_count(void);
+int hmj_version(void);
+
+/* ---- lifecycle.  `model` is the blob written by tools/compile_model.py (replaces
+ * MjModel.from_xml_path, cpu_env.py:86 / mj_loadXML in mjpc/agent.cc). */
+int hmj_batch_create(const hmj_model_t* model, int n_envs, int device, hmj_batch_t** out);
+void hmj_batch_destroy(hmj_batch_t* b);
+int hmj_batch_size(const hmj_batch_t* b);
+int hmj_batch_sync(hmj_batch_t* b);
+
+/* ---- per-env model parameters (the fields CPUEnv.reset randomises, cpu_env.py:189-280) */
+int hmj_default_params(const hmj_model_t* model, hmj_params_t* out);
+int hmj_batch_set_params(hmj_batch_t* b, const hmj_params_t* params, int first, int count);
+int hmj_batch_get_params(hmj_batch_t* b, hmj_params_t* params, int first, int count);
+
+/* ---- state (MjData.qpos/qvel/time/qacc_warmstart/ctrl/xfrc_applied). NULL = leave unchanged. */
+int hmj_batch_set_state(hmj_batch_t* b, const double* qpos, const double* qvel, const double* time,
+                        const double* qacc_warmstart);
+int hmj_batch_get_state(hmj_batch_t* b, double* qpos, double* qvel, double* time, double* qacc_warmstart);
+int hmj_batch_set_ctrl(hmj_batch_t* b, const double* ctrl);
+/* one pushed body per env (cpu_env.py:618-654): body id (0 = none) and a 6-D wrench [force, torque] */
+int hmj_batch_set_xfrc(hmj_batch_t* b, const int32_t* body, const double* wrench);
+
+/* ---- stepping: mj_step x nsteps.  `ctrl` (host, [N][12]) may be NULL to keep the current controls.
+ * hmj_batch_step copies ctrl H2D, runs, and synchronises; hmj_batch_step_dev takes a DEVICE pointer
+ * (or NULL) and only enqueues on the batch stream. */
+int hmj_batch_step(hmj_batch_t* b, const double* ctrl, int nsteps);
+int hmj_batch_step_dev(hmj_batch_t* b, const double* ctrl_dev, int nsteps);
+int hmj_batch_forward(hmj_batch_t* b); /* mj_forward */
+int hmj_batch_run_stage(hmj_batch_t* b, int stage);
+
+/* ---- results */
+int hmj_batch_get_contacts(hmj_batch_t* b, int32_t* ncon, hmj_contact_t* contacts /* [N][HMJ_MAXCON] */);
+/* named array download / upload (row-major [N][...]); names: qpos qvel time warmstart ctrl xfrc
+ * geom_xpos geom_xmat cdof com qM qfrc_smooth qacc_smooth qacc qfrc_constraint sens residual
+ * cost_sum trace (double)  ncon nefc niter status xfrc_body (int32) */
+int hmj_batch_get_array(hmj_batch_t* b, const char* name, void* out, size_t bytes);
+int hmj_batch_set_array(hmj_batch_t* b, const char* name, const void* in, size_t bytes);
+void* hmj_batch_device_ptr(hmj_batch_t* b, const char* name);
+void* hmj_batch_stream(hmj_batch_t* b);
+int hmj_batch_kernel_launches(const hmj_batch_t* b); /* kernels launched since create */
+
+/* ---- CPUEnv.step epilogue on device (cpu_env.py:465-616 + reward_functions.py:247-374):
+ * obs [N][30], reward [N], terminated/truncated/self_collision [N] (int32).  Reads the one-step-stale
+ * xquat/xpos/qfrc/contacts exactly like the reference.
+ * prev_action/latest_action are [N][12] (already divided by nothing; the kernel applies /(pi/2)). */
+int hmj_env_obs_reward(hmj_batch_t* b, const double* prev_action, const double* latest_action,
+                       const double* noise /* [N][31]: q12 qd12 gyro3 quat4, NULL = 0 */,
+                       double max_sim_time, double* obs, double* reward, int32_t* terminated,
+                       int32_t* truncated, int32_t* self_collision);
+
+/* same, all pointers DEVICE pointers, enqueue only on the batch stream */
+int hmj_env_obs_reward_dev(hmj_batch_t* b, const double* prev_action_dev, const double* latest_action_dev,
+                           const double* noise_dev, double max_sim_time, double* obs_dev, double* reward_dev,
+                           int32_t* terminated_dev, int32_t* truncated_dev, int32_t* self_collision_dev);
+
+/* ---- planner rollouts (SamplingPlanner::Rollouts): every env is one sample.
+ * state [37] = qpos,qvel shared by all samples (State::CopyTo, mjpc/states/state.cc:128-135);
+ * spline_times [P], spline_values [N][P][12] = candidate policies (noise already added and clamped
+ * by the caller: AddNoiseToPolicy planner.cc:313-339 is entropy-seeded in the reference, so noise is
+ * an explicit input); interpolation 0/1/2 = zero/linear/cubic (spline.h).  horizon = number of knots
+ * (H-1 steps + 1 forward).  Outputs: total_return [N] (1e6 on failure), failure [N] (int32).
+ * If record != 0 the full trajectories are kept on the device for hmj_plan_fetch. */
+int hmj_plan_set_task(hmj_batch_t* b, int nterm, const int32_t* dim, const int32_t* norm, const double* weight,
+                      const double* normprm /* [nterm][3] */, double risk, double height_goal);
+int hmj_plan_rollouts(hmj_batch_t* b, const double* state, double time, const double* spline_times,
+                      const double* spline_values, int nnode, int interpolation, int horizon, int record,
+                      double* total_return, int32_t* failure);
+/* device-resident variant: spline_values_dev [N][P][12], returns_dev [N]; enqueue only */
+int hmj_plan_rollouts_dev(hmj_batch_t* b, const double* state, double time, const double* spline_times,
+                          const double* spline_values_dev, int nnode, int interpolation, int horizon,
+                          double* returns_dev);
+/* local argmin of the last rollouts (lowest index wins ties): device result {cost, index}; also copied to host */
+int hmj_plan_argmin(hmj_batch_t* b, double* best_cost, int32_t* best_index);
+/* recorded trajectory of one sample (Trajectory buffers, mjpc/trajectory.h:74-86) */
+int hmj_plan_fetch(hmj_batch_t* b, int sample, int horizon, double* states /* [H][37] */, double* actions /* [H][12] */,
+                   double* times /* [H] */, double* residual /* [H][28] */, double* costs /* [H] */, double* trace /* [H][3] */);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HMJ_B200_H_ */

@@ -20,7 +20,7 @@ extern "C" {
 #endif
 
 #define HMJ_MAGIC 0x484d4a31 /* "HMJ1" */
-#define HMJ_VERSION 3
+#define HMJ_VERSION 4
 
 #define HMJ_NBODY 15
 #define HMJ_NJNT 13
@@ -44,8 +44,8 @@ extern "C" {
 #define HMJ_NSTATE (HMJ_NQ + HMJ_NV) /* na = 0 */
 
 /* capacities (per environment) */
-#define HMJ_MAXCON 32               /* contacts kept per env; overflow -> status flag */
-#define HMJ_MAXCONPAIR 4            /* hfield prisms tested per mesh-hfield pair slot */
+#define HMJ_MAXCON 16               /* contacts kept per env; overflow -> HMJ_STATUS_CONTACTFULL */
+#define HMJ_MAXCONPAIR 8            /* contacts kept per mesh-hfield pair (MuJoCo: mjMAXCONPAIR 50) */
 #define HMJ_MAXEFC (12 * 2 + 10 * HMJ_MAXCON)
 
 /* joint types (mjtJoint) */

@@ -534,7 +534,7 @@ static void collide_hfield_mesh(const hmj_model_t* m, const hmj_params_t* p, orc
             if (nrm[0] == 0 && nrm[1] == 0 && nrm[2] == 0) continue;
             if (!add_contact(m, p, d, 0, g2, 0.0 - depth, nrm, cp)) return;
             cnt++;
-            if (cnt >= 50) return; /* mjMAXCONPAIR */
+            if (cnt >= HMJ_MAXCONPAIR) return; /* per-pair cap (MuJoCo mjMAXCONPAIR = 50) */
           }
         }
       }

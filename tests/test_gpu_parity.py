@@ -1,0 +1,143 @@
+"""GPU parity tests proper: CUDA path (through the C ABI) vs the CPU oracle on identical seeded inputs.
+
+Bars (BASELINE.json north_star): contact count and geom-pair indices bit-exact; one-step
+qacc/qpos/qvel within 1e-9 relative; 10-step trajectories within 1e-6; planner winner identical when
+cost gaps exceed 1e-9.
+"""
+import numpy as np
+import pytest
+
+from conftest import make_scenarios, oracle_run
+
+pytestmark = pytest.mark.gpu
+
+REL_1STEP = 1e-9
+TOL_10STEP = 1e-6
+
+
+def rel_err(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1.0))
+
+
+@pytest.fixture(scope="module")
+def hmj():
+    import humanoid_mujoco_b200 as h
+
+    return h
+
+
+@pytest.fixture(scope="module")
+def scen(oracle):
+    return make_scenarios(oracle, 48, seed=11, settle=(0, 500))
+
+
+def make_batch(hmj, scen):
+    qpos, qvel, ws, ctrl, params = scen
+    b = hmj.HumanoidBatch(qpos.shape[0])
+    b.set_params(params)
+    b.set_state(qpos, qvel, np.zeros(qpos.shape[0]), ws)
+    b.set_ctrl(ctrl)
+    return b
+
+
+def test_smooth_stage_matches_oracle(hmj, oracle, scen):
+    b = make_batch(hmj, scen)
+    b.run_stage(1)
+    got = {k: b.get(k) for k in ("geom_xpos", "geom_xmat", "cdof", "com", "qM", "qfrc_smooth")}
+    worst = {}
+    for i in range(b.n):
+        d = oracle_run(oracle, *[s[i] for s in scen], 0, fn="forward")
+        ref = {"geom_xpos": d["geom_xpos"], "geom_xmat": d["geom_xmat"], "cdof": d["cdof"], "com": d["subtree_com"][1],
+               "qM": d["qM"], "qfrc_smooth": d["qfrc_smooth"]}
+        for k, v in ref.items():
+            worst[k] = max(worst.get(k, 0.0), rel_err(got[k][i], v))
+    print("smooth-stage rel err:", worst)
+    for k, v in worst.items():
+        assert v < 1e-11, (k, v)
+    b.close()
+
+
+def test_narrowphase_bit_exact_on_identical_frames(hmj, oracle, scen):
+    """Feed the oracle's geom frames to the collide kernel: contacts must be identical to the last bit."""
+    b = make_batch(hmj, scen)
+    b.run_stage(1)
+    refs = [oracle_run(oracle, *[s[i] for s in scen], 0, fn="forward") for i in range(b.n)]
+    b.set("geom_xpos", np.stack([r["geom_xpos"] for r in refs]))
+    b.set("geom_xmat", np.stack([r["geom_xmat"] for r in refs]))
+    b.run_stage(2)
+    b.run_stage(3)
+    ncon, con = b.contacts()
+    total = 0
+    for i, r in enumerate(refs):
+        assert int(ncon[i]) == int(r["ncon"]), (i, int(ncon[i]), int(r["ncon"]))
+        for c in range(int(ncon[i])):
+            rc = r["contact"][c]
+            assert (int(con[i, c]["geom1"]), int(con[i, c]["geom2"])) == (int(rc["geom1"]), int(rc["geom2"]))
+            assert con[i, c]["dist"] == rc["dist"]
+            assert np.array_equal(con[i, c]["pos"], rc["pos"])
+            assert np.array_equal(con[i, c]["frame"][:3], rc["frame"][:3])
+            total += 1
+    assert total > 20, "scenario set must be contact-rich"
+    b.close()
+
+
+def test_forward_contacts_and_qacc(hmj, oracle, scen):
+    b = make_batch(hmj, scen)
+    b.forward()
+    ncon, con = b.contacts()
+    qacc, nefc = b.get("qacc"), b.get("nefc")
+    qfc = b.get("qfrc_constraint")
+    worst = 0.0
+    for i in range(b.n):
+        r = oracle_run(oracle, *[s[i] for s in scen], 0, fn="forward")
+        assert int(ncon[i]) == int(r["ncon"]) and int(nefc[i]) == int(r["nefc"]), i
+        pairs = [(int(c["geom1"]), int(c["geom2"])) for c in con[i, : ncon[i]]]
+        assert pairs == [(int(c["geom1"]), int(c["geom2"])) for c in r["contact"][: r["ncon"]]]
+        worst = max(worst, rel_err(qacc[i], r["qacc"]), rel_err(qfc[i], r["qfrc_constraint"]))
+    print("forward qacc/qfrc_constraint rel err:", worst)
+    assert worst < REL_1STEP
+    b.close()
+
+
+def test_one_step_and_ten_steps(hmj, oracle, scen):
+    b = make_batch(hmj, scen)
+    b.step(None, 1)
+    q1, v1, t1, w1 = b.get_state()
+    b.step(None, 9)
+    q10, v10, _, _ = b.get_state()
+    assert np.all(b.get("status") == 0)
+    w1e = w10e = 0.0
+    for i in range(b.n):
+        r1 = oracle_run(oracle, *[s[i] for s in scen], 1)
+        w1e = max(w1e, rel_err(q1[i], r1["qpos"]), rel_err(v1[i], r1["qvel"]), rel_err(w1[i], r1["qacc_warmstart"]))
+        assert t1[i] == pytest.approx(r1["time"], abs=1e-15)
+        r10 = oracle_run(oracle, *[s[i] for s in scen], 10)
+        w10e = max(w10e, float(np.max(np.abs(q10[i] - r10["qpos"]))), float(np.max(np.abs(v10[i] - r10["qvel"]))))
+    print("1-step rel err:", w1e, " 10-step abs err:", w10e)
+    assert w1e < REL_1STEP
+    assert w10e < TOL_10STEP
+    b.close()
+
+
+def test_xfrc_and_bad_state(hmj, oracle, scen):
+    qpos, qvel, ws, ctrl, params = scen
+    b = make_batch(hmj, scen)
+    body = np.arange(b.n, dtype=np.int32) % 14 + 1
+    wrench = np.zeros((b.n, 6)); wrench[:, 0] = 7.0; wrench[:, 1] = -3.0
+    b.set_xfrc(body, wrench)
+    b.run_stage(1)
+    qfs = b.get("qfrc_smooth")
+    for i in range(0, b.n, 5):
+        oracle.reset(); oracle.params[0] = params[i]
+        oracle.set_state(qpos[i], qvel[i], ctrl[i], ws[i])
+        oracle.data["xfrc_applied"][0][body[i]] = wrench[i]
+        oracle.forward()
+        assert rel_err(qfs[i], oracle.d["qfrc_smooth"]) < 1e-11
+    bad = qpos.copy(); bad[3, 5] = np.nan
+    b.set_state(bad, qvel, np.zeros(b.n), ws)
+    b.step(None, 1)
+    st = b.get("status")
+    assert st[3] & 1 and np.all(st[np.arange(b.n) != 3] == 0)
+    assert np.all(np.isfinite(b.get_state()[0]))
+    b.close()
