@@ -1,0 +1,358 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the hot path: batched humanoid env-steps/s (BASELINE.json metric).
+
+Workload at N GPUs (weak scaling, one process per GPU): BASELINE.json configs[2] ("C3") per GPU —
+4096 lock-step humanoid environments with rf = 1 domain randomisation (cpu_env.py:189-280 ranges),
+contact-rich start (standup pose + 300 zero-control settle steps), uniform random controls,
+dt = 0.002, one mj_step + observation/reward epilogue per env-step.
+
+  value   env-steps/s with inputs resident in HBM (controls streamed from a device ring larger than L2),
+          K steps timed with CUDA events on the engine's stream, max over ranks;
+  e2e     the same metric through the public API (BatchedHumanoidEnv.step): host actions in pinned
+          memory -> H2D -> step -> D2H of obs/reward/flags every step, wall clock incl. host logic;
+  roofline / fp64   dominant kernel's achieved algorithmic bytes/s (2530 B/env-step) and
+          whole-step achieved fp64 flop/s (oracle counters) against measured peaks;
+  cpu_baseline      the oracle (CPU restatement of the reference's MuJoCo path, kind "port": no MuJoCo
+          binary exists on this box) on all host cores over a bounded sample of the same workload;
+  plan    MJPC predictive-sampling iterations/s (configs[1] and the per-GPU slice of configs[3]).
+
+`--impl reference` times the reference-path CPU implementation (oracle port) on the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+for _p in (REPO, os.path.join(REPO, "tools")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+
+METRIC = "batched humanoid env-steps/sec"
+UNIT = "env-steps/s"
+BYTES_PER_ENV_STEP = 2530  # algorithmic HBM bytes per env-step with per-env DR params (C3)
+SETTLE_STEPS = 300
+ENVS_PER_GPU = 4096
+CPU_SAMPLE_ENVS = 1024
+
+
+def workload_name(envs, n_gpus):
+    return (f"C3: {envs} lockstep humanoid envs/GPU x {n_gpus} GPU, DR rf=1, contact-rich "
+            f"(standup pose + {SETTLE_STEPS} settle steps), U(-1,1) controls, dt=0.002")
+
+
+def load_peaks():
+    try:
+        with open(os.path.join(REPO, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.path = index, None, None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.f = open(self.path, "w")
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        try:
+            self.proc.terminate()
+            self.proc.wait(timeout=5)
+        except Exception:
+            pass
+        try:
+            self.f.close()
+            rows = [r.split(",") for r in open(self.path).read().strip().splitlines() if r.count(",") >= 8]
+            os.unlink(self.path)
+            sm = [float(r[1]) for r in rows]
+            reasons = set()
+            for r in rows:
+                for name, col in (("hw_slowdown", 5), ("hw_thermal_slowdown", 6), ("sw_thermal_slowdown", 7), ("sw_power_cap", 8)):
+                    if "Active" in r[col] and "Not" not in r[col]:
+                        reasons.add(name)
+            if rows:
+                out = {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(rows[0][2]), "reasons": sorted(reasons),
+                       "samples": len(rows), "power_w_max": max(float(r[3]) for r in rows)}
+        except Exception:
+            pass
+        return out
+
+
+# ---------------------------------------------------------------------------------------------- workload
+def make_workload(base_params, qpos0, n, seed):
+    """Per-env DR parameters and start poses of C3 (pure numpy; shared by both arms)."""
+    from humanoid_mujoco_b200.env import randomize_params, standup_start_state
+    rng = np.random.default_rng(seed)
+    params = randomize_params(np.repeat(base_params[:1], n), rng, 1.0)
+    qpos = standup_start_state(qpos0, rng, 1.0, n)
+    return params, qpos
+
+
+# ---------------------------------------------------------------------------------------------- reference arm / CPU baseline
+def cpu_steps_per_s(params, qpos, qvel, ws, ctrl_ring, nsteps, warm, nthreads):
+    """Oracle (CPU port of the reference path) on `nthreads` host threads; returns (env-steps/s, stats)."""
+    sys.path.insert(0, os.path.join(REPO, "oracle"))
+    from oracle_py import OracleBatch  # bench.py's cpu_baseline / --impl reference legs may execute oracle/
+    n = qpos.shape[0]
+    ob = OracleBatch(n)
+    ob.params[:] = params
+    ob.set_state(qpos, qvel, ws)
+    if warm:
+        ob.step(ctrl_ring, warm, nthreads)
+    secs = ob.step(ctrl_ring, nsteps, nthreads)
+    d = ob.data
+    fl = d["flops_smooth"] + d["flops_collision"] + d["flops_constraint"] + d["flops_solver"]
+    stats = {"mean_ncon": float(d["ncon"].mean()), "mean_nefc": float(d["nefc"].mean()),
+             "mean_niter": float(d["solver_niter"].mean()), "flops_per_step": float(fl.mean() / max(1, warm + nsteps)),
+             "bad_status": int((d["status"] != 0).sum())}
+    return n * nsteps / secs, stats, ob
+
+
+def cpu_settled_state(n, seed, nthreads):
+    sys.path.insert(0, os.path.join(REPO, "oracle"))
+    from oracle_py import OracleBatch
+    ob = OracleBatch(n)
+    params, qpos = make_workload(ob.params, ob.model["qpos0"][0], n, seed)
+    ob.params[:] = params
+    ob.set_state(qpos, np.zeros((n, 18)))
+    ob.data["ctrl"][:] = 0.0
+    ob.step(None, SETTLE_STEPS, nthreads)
+    return params, ob.data["qpos"].copy(), ob.data["qvel"].copy(), ob.data["qacc_warmstart"].copy()
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    nthreads = os.cpu_count() or 1
+    n = CPU_SAMPLE_ENVS
+    params, qpos, qvel, ws = cpu_settled_state(n, 1, nthreads)
+    ring = np.random.default_rng(2).uniform(-1, 1, (64, n, 12))
+    t0 = time.perf_counter()
+    value, stats, _ = cpu_steps_per_s(params, qpos, qvel, ws, ring, args.steps, args.warmup, nthreads)
+    wall = time.perf_counter() - t0
+    sample = f"{n} of the {args.envs} envs of C3 (same DR/start/settle/controls distribution), {args.steps} steps each"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * n / value, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_name(args.envs, args.gpus), "step": f"one mj_step over the {n}-env sample"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": nthreads, "kind": "port", "sample": sample, **stats},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": ("MuJoCo 3.1.4 (the reference's physics) is not in /root/reference nor installed on this box: the timed CPU "
+                 "implementation is the repo's fp64 C restatement (oracle/), all host threads"),
+        "wall_s": wall,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ---------------------------------------------------------------------------------------------- GPU arm
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+
+    import humanoid_mujoco_b200 as hmj
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the engine has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier(device_ids=[local])
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    n, K, W = args.envs, args.steps, args.warmup
+    # ---- public API object: the CPUEnv contract over n envs, rf = 1
+    env = hmj.BatchedHumanoidEnv(n, randomization_factor=1.0, device=local, seed=1 + rank)
+    b = env.batch
+    params, qpos = make_workload(b.default_params(), b.model["qpos0"][0], n, 1 + rank)
+    env.params[:] = params
+    b.set_params(params)
+    b.set_state(qpos, np.zeros((n, 18)), np.zeros(n), np.zeros((n, 18)))
+    b.step(np.zeros((n, 12)), SETTLE_STEPS)  # robots fall and lie on the bumpy floor: contact-rich start
+    settled = b.get_state()
+    stream = torch.cuda.ExternalStream(b.stream, device=dev)
+
+    # ---- device-resident inputs: control ring larger than L2 (R x n x 12 fp64), epilogue buffers
+    ring_n = max(8, int(np.ceil(160e6 / (n * 12 * 8))))
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(2 + rank)
+    ring = torch.rand((ring_n, n, 12), dtype=torch.float64, device=dev, generator=gen) * 2 - 1
+    prev = torch.zeros((n, 12), dtype=torch.float64, device=dev)
+    obs = torch.zeros((n, 30), dtype=torch.float64, device=dev)
+    rew = torch.zeros(n, dtype=torch.float64, device=dev)
+    flags = torch.zeros((3, n), dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()
+    lib, h = b.lib, b._h
+    from humanoid_mujoco_b200._lib import check
+
+    def device_step(s):
+        cur = ring[s % ring_n]
+        b.step_dev(cur.data_ptr(), 1)
+        check(lib.hmj_env_obs_reward_dev(h, prev.data_ptr(), cur.data_ptr(), None, 10.0, obs.data_ptr(), rew.data_ptr(),
+                                         flags[0].data_ptr(), flags[1].data_ptr(), flags[2].data_ptr()))
+
+    # ---- kernel-resident throughput (`value`)
+    for s in range(W):
+        device_step(s)
+    b.sync()
+    barrier()
+    torch.cuda.synchronize()
+    clocks = ClockSampler(local)
+    clocks.start()
+    l0 = b.kernel_launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for s in range(K):
+        device_step(W + s)
+    e1.record(stream)
+    b.sync()
+    torch.cuda.synchronize()
+    barrier()
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    launches = b.kernel_launches - l0
+    value = world * n * K / (ms_total * 1e-3)
+    status_bad = int((b.get("status") != 0).sum())
+    ncon = b.get("ncon")
+    nefc = b.get("nefc")
+    niter = b.get("niter")
+
+    # ---- per-kernel device time (CUDA events around every launch on the engine stream), same steps
+    b.profile(True)
+    for s in range(K):
+        device_step(W + K + s)
+    prof = b.profile_read()
+    b.profile(False)
+    kern = {k: prof[k + "_ms"] / prof["steps"] for k in ("smooth", "collide", "solve")}
+    dom = max(kern, key=kern.get)
+    hbm_peak, peak_kind = load_peaks()
+    achieved = BYTES_PER_ENV_STEP * n / (kern[dom] * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "k_" + dom, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                "frac": achieved / hbm_peak, "traffic": None, "peak_kind": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)",
+                "kernel_ms": kern, "algorithmic_bytes_per_env_step": BYTES_PER_ENV_STEP,
+                "note": "path is fp64-issue/latency bound, not HBM bound (SURVEY 8d): see the fp64 object"}
+
+    # ---- end to end through the public API: pinned host actions in, obs/reward/flags out, every step
+    b.set_state(*settled)
+    env.time[:] = settled[2]
+    host_actions = torch.empty((min(ring_n, 64), n, 12), dtype=torch.float64).uniform_(-1, 1).pin_memory()
+    acts = host_actions.numpy()
+    pinned_out = {"obs": torch.zeros((n, 30), dtype=torch.float64).pin_memory(), "reward": torch.zeros(n, dtype=torch.float64).pin_memory(),
+                  "terminated": torch.zeros(n, dtype=torch.int32).pin_memory(), "truncated": torch.zeros(n, dtype=torch.int32).pin_memory(),
+                  "self_collision": torch.zeros(n, dtype=torch.int32).pin_memory(), "time": torch.zeros(n, dtype=torch.float64).pin_memory(),
+                  "root_quat": torch.zeros((n, 4), dtype=torch.float64).pin_memory()}
+    env._out = {k: v.numpy() for k, v in pinned_out.items()}
+    for s in range(W):
+        env.step(acts[s % acts.shape[0]])
+    barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for s in range(K):
+        o, r, term, trunc, _info = env.step(acts[(W + s) % acts.shape[0]])
+    b.sync()
+    t1 = time.perf_counter()
+    e2e_s = max_over_ranks(t1 - t0)
+    e2e_value = world * n * K / e2e_s
+    h2d = n * (12 * 8 + 4 + 6 * 8 + 12 * 8 + 12 * 8 + 31 * 8)
+    d2h = n * (30 * 8 + 8 + 3 * 4 + 8 + 4 * 8)
+    clk = clocks.stop()
+
+    line = None
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": workload_name(n, world), "envs_per_gpu": n, "timestep": 0.002,
+                       "l2": (f"per-step controls stream from a {ring_n}x{n}x12 fp64 device ring "
+                              f"({ring_n * n * 96 / 1e6:.0f} MB > 126 MB L2); the state is each step's own previous output"),
+                       "step": "one mj_step of all envs + obs/reward epilogue"},
+            "roofline": roofline,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": 1e3 * e2e_s / K, "api": "BatchedHumanoidEnv.step (hmj_env_step C-ABI), pinned host buffers"},
+            "gpu_launches": int(launches), "clocks": clk,
+            "contacts": {"mean_ncon": float(ncon.mean()), "max_ncon": int(ncon.max()), "mean_nefc": float(nefc.mean()),
+                         "max_nefc": int(nefc.max()), "mean_newton_iter": float(niter.mean()), "envs_with_bad_status": status_bad},
+        }
+    # ---- FP64 peak + CPU baseline (rank 0, N = 1 only)
+    if rank == 0:
+        import ctypes as C
+        tf = C.c_double(0)
+        lib.hmj_fp64_peak(local, C.byref(tf))
+        line["fp64"] = {"peak_tflops_measured": tf.value}
+    if rank == 0 and world == 1 and not args.no_cpu:
+        nthreads = os.cpu_count() or 1
+        m = min(CPU_SAMPLE_ENVS, n)
+        q, v, _t, ws = settled
+        ring_cpu = np.random.default_rng(2).uniform(-1, 1, (64, m, 12))
+        cpu_value, stats, _ = cpu_steps_per_s(params[:m], q[:m], v[:m], ws[:m], ring_cpu, args.cpu_steps, 10, nthreads)
+        line["cpu_baseline"] = {"value": cpu_value, "unit": UNIT, "cores": nthreads, "kind": "port",
+                                "sample": f"first {m} of the {n} envs (same settled states and DR params), {args.cpu_steps} steps each",
+                                **stats}
+        fl = stats["flops_per_step"]
+        line["fp64"].update({"flops_per_env_step_oracle_counters": fl, "achieved_tflops": value * fl / 1e12,
+                             "frac": (value * fl / 1e12) / tf.value if tf.value else None})
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    env.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--envs", type=int, default=ENVS_PER_GPU, help="environments per GPU")
+    ap.add_argument("--cpu-steps", type=int, default=100, help="steps per env of the bounded CPU-baseline sample")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_gpu(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

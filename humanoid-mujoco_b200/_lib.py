@@ -55,6 +55,11 @@ def load_library() -> C.CDLL:
     lib.hmj_batch_kernel_launches.argtypes = [vp]
     lib.hmj_env_obs_reward.argtypes = [vp, dp, dp, dp, C.c_double, dp, dp, vp, vp, vp]
     lib.hmj_env_obs_reward_dev.argtypes = [vp, dp, dp, dp, C.c_double, dp, dp, vp, vp, vp]
+    lib.hmj_env_step.argtypes = [vp, dp, vp, dp, dp, dp, dp, C.c_double, C.c_int, dp, dp, vp, vp, vp, dp, dp]
+    lib.hmj_batch_profile.argtypes = [vp, C.c_int]
+    lib.hmj_batch_profile_read.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                           C.POINTER(C.c_int)]
+    lib.hmj_fp64_peak.argtypes = [C.c_int, C.POINTER(C.c_double)]
     lib.hmj_plan_set_task.argtypes = [vp, C.c_int, vp, vp, dp, dp, C.c_double, C.c_double]
     lib.hmj_plan_rollouts.argtypes = [vp, dp, C.c_double, dp, dp, C.c_int, C.c_int, C.c_int, C.c_int, dp, vp]
     lib.hmj_plan_rollouts_dev.argtypes = [vp, dp, C.c_double, dp, dp, C.c_int, C.c_int, C.c_int, dp]

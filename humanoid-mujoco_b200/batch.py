@@ -206,6 +206,30 @@ class HumanoidBatch:
             float(max_sim_time), _p(obs), _p(rew), _p(term), _p(trunc), _p(selfc)))
         return obs, rew, term.astype(bool), trunc.astype(bool), selfc.astype(bool)
 
+    def env_step(self, ctrl, xfrc_body, xfrc, prev_action, latest_action, noise=None, max_sim_time=np.inf, nsteps=1, out=None):
+        """CPUEnv.step for all envs in one C call (hmj_env_step).  `out` may hold preallocated (pinned) result arrays."""
+        n = self.n
+        if out is None:
+            out = {"obs": np.zeros((n, 30)), "reward": np.zeros(n), "terminated": np.zeros(n, dtype=np.int32),
+                   "truncated": np.zeros(n, dtype=np.int32), "self_collision": np.zeros(n, dtype=np.int32),
+                   "time": np.zeros(n), "root_quat": np.zeros((n, 4))}
+        body = None if xfrc_body is None else np.ascontiguousarray(np.broadcast_to(np.asarray(xfrc_body, dtype=np.int32), (n,)))
+        check(self.lib.hmj_env_step(
+            self._h, _p(self._f64(ctrl, (NU,))), _p(body), _p(self._f64(xfrc, (6,))), _p(self._f64(prev_action, (NU,))),
+            _p(self._f64(latest_action, (NU,))), _p(self._f64(noise, (31,))), float(max_sim_time), int(nsteps),
+            _p(out["obs"]), _p(out["reward"]), _p(out["terminated"]), _p(out["truncated"]), _p(out["self_collision"]),
+            _p(out["time"]), _p(out["root_quat"])))
+        return out
+
+    # ---- per-kernel timing
+    def profile(self, enable: bool):
+        check(self.lib.hmj_batch_profile(self._h, int(bool(enable))))
+
+    def profile_read(self):
+        a, b, c, n = C.c_double(0), C.c_double(0), C.c_double(0), C.c_int(0)
+        check(self.lib.hmj_batch_profile_read(self._h, C.byref(a), C.byref(b), C.byref(c), C.byref(n)))
+        return {"smooth_ms": a.value, "collide_ms": b.value, "solve_ms": c.value, "steps": n.value}
+
     # ---- planner rollouts
     def plan_rollouts(self, state, time, spline_times, spline_values, horizon, interpolation=2, record=False):
         state = np.ascontiguousarray(state, dtype=np.float64)

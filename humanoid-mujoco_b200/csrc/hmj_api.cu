@@ -49,6 +49,10 @@ struct hmj_batch_ {
   // env scratch
   double* env_stage = nullptr; size_t env_stage_cap = 0;
   int launches = 0;
+  // per-kernel CUDA-event profiling (hmj_batch_profile): events bracket every launch of a step
+  bool profile = false;
+  std::vector<cudaEvent_t> prof_events;  // 4 per step: before smooth, collide, solve, after solve
+  size_t prof_used = 0;
 };
 
 extern "C" const char* hmj_last_error(void) { return g_err; }
@@ -162,6 +166,7 @@ extern "C" void hmj_batch_destroy(hmj_batch_t* b) {
   cudaSetDevice(b->device);
   if (b->stream) cudaStreamSynchronize(b->stream);
   for (void* p : b->allocs) cudaFree(p);
+  for (cudaEvent_t e : b->prof_events) cudaEventDestroy(e);
   if (b->tab_dev) cudaFree(b->tab_dev);
   if (b->task_dev) cudaFree(b->task_dev);
   if (b->stream) cudaStreamDestroy(b->stream);
@@ -335,11 +340,56 @@ extern "C" int hmj_batch_set_xfrc(hmj_batch_t* b, const int32_t* body, const dou
   return HMJ_OK;
 }
 
+static cudaEvent_t prof_event(hmj_batch_t* b) {
+  if (b->prof_used == b->prof_events.size()) {
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    b->prof_events.push_back(e);
+  }
+  cudaEvent_t e = b->prof_events[b->prof_used++];
+  cudaEventRecord(e, b->stream);
+  return e;
+}
+
 static void enqueue_step(hmj_batch_t* b, int integrate) {
+  const bool prof = b->profile;
+  if (prof) prof_event(b);
   hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, b->stream);
+  if (prof) prof_event(b);
   hmj_launch_collide(b->tab_dev, b->buf, b->stream);
+  if (prof) prof_event(b);
   hmj_launch_solve(b->tab_dev, b->buf, integrate, b->stream);
+  if (prof) prof_event(b);
   b->launches += 3;
+}
+
+// Per-kernel device time of the steps enqueued while profiling was on (CUDA events on the batch stream).
+extern "C" int hmj_batch_profile(hmj_batch_t* b, int enable) {
+  if (!b) return fail(HMJ_ERR_ARG, "null batch%s");
+  CK(cudaSetDevice(b->device));
+  CK(cudaStreamSynchronize(b->stream));
+  b->profile = enable != 0;
+  b->prof_used = 0;
+  return HMJ_OK;
+}
+
+extern "C" int hmj_batch_profile_read(hmj_batch_t* b, double* ms_smooth, double* ms_collide, double* ms_solve, int* nsteps) {
+  if (!b) return fail(HMJ_ERR_ARG, "null batch%s");
+  CK(cudaSetDevice(b->device));
+  CK(cudaStreamSynchronize(b->stream));
+  double acc[3] = {0, 0, 0};
+  const size_t n = b->prof_used / 4;
+  for (size_t i = 0; i < n; i++)
+    for (int k = 0; k < 3; k++) {
+      float ms = 0;
+      CK(cudaEventElapsedTime(&ms, b->prof_events[4 * i + k], b->prof_events[4 * i + k + 1]));
+      acc[k] += ms;
+    }
+  if (ms_smooth) *ms_smooth = acc[0];
+  if (ms_collide) *ms_collide = acc[1];
+  if (ms_solve) *ms_solve = acc[2];
+  if (nsteps) *nsteps = (int)n;
+  return HMJ_OK;
 }
 
 extern "C" int hmj_batch_step_dev(hmj_batch_t* b, const double* ctrl_dev, int nsteps) {
@@ -476,6 +526,53 @@ extern "C" int hmj_env_obs_reward(hmj_batch_t* b, const double* prev_action, con
       (rc = d2h(b, truncated, d_trunc, N * 4)) || (rc = d2h(b, self_collision, d_self, N * 4)))
     return rc;
   CK(cudaStreamSynchronize(b->stream));
+  return HMJ_OK;
+}
+
+// CPUEnv.step as ONE call (cpu_env.py:676-693): host controls / push wrench in, nsteps x mj_step, observation and
+// reward epilogue, host results out, one synchronisation.  The per-env staging lives in one device block.
+extern "C" int hmj_env_step(hmj_batch_t* b, const double* ctrl, const int32_t* xfrc_body, const double* xfrc,
+                            const double* prev_action, const double* latest_action, const double* noise, double max_sim_time,
+                            int nsteps, double* obs, double* reward, int32_t* terminated, int32_t* truncated,
+                            int32_t* self_collision, double* time_out, double* root_quat_out) {
+  if (!b || !prev_action || !latest_action || !obs || !reward || !terminated || !truncated || nsteps < 0)
+    return fail(HMJ_ERR_ARG, "bad argument to env_step%s");
+  CK(cudaSetDevice(b->device));
+  const size_t N = b->n;
+  const size_t nd = N * (12 + 12 + 31 + 30 + 1);
+  const size_t bytes = nd * 8 + 3 * N * 4;
+  if (b->env_stage_cap < bytes) {
+    void* p = nullptr;
+    CK(cudaMalloc(&p, bytes));
+    b->allocs.push_back(p);
+    b->env_stage = (double*)p;
+    b->env_stage_cap = bytes;
+  }
+  double* d_prev = b->env_stage;
+  double* d_lat = d_prev + 12 * N;
+  double* d_noise = d_lat + 12 * N;
+  double* d_obs = d_noise + 31 * N;
+  double* d_rew = d_obs + 30 * N;
+  int32_t* d_term = (int32_t*)(d_rew + N);
+  int32_t* d_trunc = d_term + N;
+  int32_t* d_self = d_trunc + N;
+  int rc;
+  if ((rc = h2d(b, b->buf.ctrl, ctrl, N * HMJ_NU * 8)) || (rc = h2d(b, b->buf.xfrc_body, xfrc_body, N * 4)) ||
+      (rc = h2d(b, b->buf.xfrc, xfrc, N * 6 * 8)) || (rc = h2d(b, d_prev, prev_action, 12 * N * 8)) ||
+      (rc = h2d(b, d_lat, latest_action, 12 * N * 8)) || (rc = h2d(b, d_noise, noise, 31 * N * 8)))
+    return rc;
+  for (int s = 0; s < nsteps; s++) enqueue_step(b, 1);
+  hmj_launch_env_obs_reward(b->tab_dev, b->buf, d_prev, d_lat, noise ? d_noise : nullptr, max_sim_time, d_obs, d_rew, d_term,
+                            d_trunc, d_self, b->stream);
+  b->launches += 1;
+  if ((rc = d2h(b, obs, d_obs, 30 * N * 8)) || (rc = d2h(b, reward, d_rew, N * 8)) || (rc = d2h(b, terminated, d_term, N * 4)) ||
+      (rc = d2h(b, truncated, d_trunc, N * 4)) || (rc = d2h(b, self_collision, d_self, N * 4)) ||
+      (rc = d2h(b, time_out, b->buf.time, N * 8)))
+    return rc;
+  if (root_quat_out)
+    CK(cudaMemcpy2DAsync(root_quat_out, 4 * 8, b->buf.sens + SENS_ROOT_XQUAT, SENS_NUM * 8, 4 * 8, N, cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  CK(cudaGetLastError());
   return HMJ_OK;
 }
 

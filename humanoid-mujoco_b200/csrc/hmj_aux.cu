@@ -180,3 +180,40 @@ void hmj_launch_env_obs_reward(const hmj_tables_t* tab, hmj_buffers_t buf, const
   k_env_obs_reward<<<(buf.n + 127) / 128, 128, 0, stream>>>(tab, buf, prev_action, latest_action, noise, max_sim_time, obs, reward,
                                                             terminated, truncated, self_collision);
 }
+
+// ------------------------------------------------------------------ FP64 FMA peak (roofline denominator)
+// MEASURED_PEAKS.json carries no FP64 figure; this micro-benchmark measures the DFMA issue peak of the device:
+// 8 independent FMA chains per thread, 4096 iterations, 148 x 16 CTAs of 256 threads.
+__global__ void k_fp64_peak(double* out, int iters, double a, double b) {
+  double x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+  for (int i = 0; i < iters; i++) {
+    x0 = fma(x0, a, b); x1 = fma(x1, a, b); x2 = fma(x2, a, b); x3 = fma(x3, a, b);
+    x4 = fma(x4, a, b); x5 = fma(x5, a, b); x6 = fma(x6, a, b); x7 = fma(x7, a, b);
+  }
+  out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+}
+
+extern "C" int hmj_fp64_peak(int device, double* tflops) {
+  if (cudaSetDevice(device) != cudaSuccess) return -1;
+  const int grid = 148 * 16, block = 256, iters = 4096;
+  double* out = nullptr;
+  if (cudaMalloc(&out, sizeof(double) * grid * block) != cudaSuccess) return -1;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  double best = 0.0;
+  for (int rep = 0; rep < 6; rep++) {
+    cudaEventRecord(e0);
+    k_fp64_peak<<<grid, block>>>(out, iters, 0.999999, 1e-9);
+    cudaEventRecord(e1);
+    if (cudaEventSynchronize(e1) != cudaSuccess) { cudaFree(out); return -1; }
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    const double fl = 2.0 * 8.0 * iters * (double)grid * block;
+    const double tf = fl / (ms * 1e-3) * 1e-12;
+    if (rep > 0 && tf > best) best = tf;
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  cudaFree(out);
+  if (tflops) *tflops = best;
+  return 0;
+}

@@ -11,6 +11,7 @@
 #include <stdint.h>
 
 #include "../../include/hmj_model.h"
+#include "../../include/hmj_sincos.h"
 
 #define HMJ_WARPS_PER_CTA 4
 #define HMJ_NSLOT (9 * HMJ_MAXCONPAIR + 28) /* contact slots per env: 9 hfield pairs x cap + 28 mesh pairs */
@@ -178,7 +179,7 @@ __device__ __forceinline__ void d_axis_angle2quat(double* q, const double* axis,
     q[0] = 1; q[1] = 0; q[2] = 0; q[3] = 0;
   } else {
     double s, c;
-    sincos(angle * 0.5, &s, &c);
+    hmj_sincos(angle * 0.5, &s, &c);  // shared deterministic sin/cos: same bits as the oracle
     q[0] = c; q[1] = axis[0] * s; q[2] = axis[1] * s; q[3] = axis[2] * s;
   }
 }

@@ -16,6 +16,7 @@
 //     bit-identical sums on all lanes, so all solver control flow is warp-uniform.
 // Roofline: FP64 FMA pipe (J'DJ, Cholesky) and shuffle/issue latency (line search); per-env HBM/L2
 // traffic is ~2.6 KB in (qM, cdof, slots, state) and ~0.6 KB out.
+#include <cstdio>
 #include "hmj_dev.cuh"
 
 #define NV HMJ_NV
@@ -137,16 +138,34 @@ __device__ __forceinline__ void row_impedance(const double* solref_in, const dou
   *Bc = Bv;
 }
 
+// mju_makeFrame.  Written with __dmul_rn/__dadd_rn (never contracted into FMA) so the contact frame is the
+// same IEEE operation sequence as the oracle's (-ffp-contract=off): contact records compare bit-exact.
+__device__ __forceinline__ double nf_dot3(const double* a, const double* b) {
+  return __dadd_rn(__dadd_rn(__dmul_rn(a[0], b[0]), __dmul_rn(a[1], b[1])), __dmul_rn(a[2], b[2]));
+}
+__device__ __forceinline__ void nf_normalize3(double* v) {
+  const double n = sqrt(nf_dot3(v, v));
+  if (n < HMJ_MINVAL) {
+    v[0] = 1; v[1] = 0; v[2] = 0;
+  } else {
+    const double s = 1.0 / n;
+    v[0] = __dmul_rn(v[0], s); v[1] = __dmul_rn(v[1], s); v[2] = __dmul_rn(v[2], s);
+  }
+}
 __device__ __forceinline__ void make_frame(double* frame) {
-  d_normalize3(frame);
-  if (sqrt(frame[3] * frame[3] + frame[4] * frame[4] + frame[5] * frame[5]) < 0.5) {
+  nf_normalize3(frame);
+  if (sqrt(nf_dot3(frame + 3, frame + 3)) < 0.5) {
     frame[3] = frame[4] = frame[5] = 0;
     if (frame[1] < 0.5 && frame[1] > -0.5) frame[4] = 1; else frame[5] = 1;
   }
-  double tmp = frame[0] * frame[3] + frame[1] * frame[4] + frame[2] * frame[5];
-  frame[3] -= tmp * frame[0]; frame[4] -= tmp * frame[1]; frame[5] -= tmp * frame[2];
-  d_normalize3(frame + 3);
-  d_cross(frame + 6, frame, frame + 3);
+  const double tmp = nf_dot3(frame, frame + 3);
+  frame[3] = __dsub_rn(frame[3], __dmul_rn(tmp, frame[0]));
+  frame[4] = __dsub_rn(frame[4], __dmul_rn(tmp, frame[1]));
+  frame[5] = __dsub_rn(frame[5], __dmul_rn(tmp, frame[2]));
+  nf_normalize3(frame + 3);
+  frame[6] = __dsub_rn(__dmul_rn(frame[1], frame[5]), __dmul_rn(frame[2], frame[4]));
+  frame[7] = __dsub_rn(__dmul_rn(frame[2], frame[3]), __dmul_rn(frame[0], frame[5]));
+  frame[8] = __dsub_rn(__dmul_rn(frame[0], frame[4]), __dmul_rn(frame[1], frame[3]));
 }
 
 struct LsPnt { double alpha, cost, d0, d1; };
@@ -356,6 +375,9 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
         rD[k] = 1 / R;
         const double vel = row_value(k);
         rAref[k] = -Bc * vel - KI * (pos - margin);
+#ifdef HMJ_TRACE
+        if (env == HMJ_TRACE) printf("GPU row %d D %.17g aref %.17g vel %.17g pos %.17g\n", r, rD[k], rAref[k], vel, pos);
+#endif
       }
     }
     __syncwarp();
@@ -587,6 +609,9 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
           }
         }
       }
+#ifdef HMJ_TRACE
+      if (env == HMJ_TRACE && lane == 0) printf("GPU it %d alpha %.17g lsiter %d snorm %.17g gtol %.6g cost %.17g\n", niter, alpha, lsiter, snorm, gtol, cost);
+#endif
       if (alpha == 0.0) break;
 
       // ---- move to the new point, re-evaluate, test convergence
@@ -598,6 +623,9 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
       const double improvement = scale * (oldcost - cost);
       const double gradient = scale * sqrt(warp_sum(grad * grad));
       niter++;
+#ifdef HMJ_TRACE
+      if (env == HMJ_TRACE && lane == 0) printf("GPU    -> cost %.17g improvement %.6g gradient %.6g\n", cost, improvement, gradient);
+#endif
       if (improvement < tolerance || gradient < tolerance) break;
       search = -mgrad;
     }

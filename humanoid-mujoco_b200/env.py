@@ -61,6 +61,50 @@ def _smooth_heightfield(rng: np.random.Generator, n: int) -> np.ndarray:
     return sm.reshape(n, 64).astype(np.float32)
 
 
+def randomize_params(base: np.ndarray, rng: np.random.Generator, rf: float, timestep: float = TIMESTEP) -> np.ndarray:
+    """CPUEnv._randomize_dynamics / _randomize_joint_properties / _randomize_floor_heightmap (cpu_env.py:189-280) for a
+    batch: `base` is hmj_params_t[k] holding the un-randomised MjModel fields; returns the randomised copy.  Pure numpy."""
+    k = base.shape[0]
+    p = base.copy()
+    mult = 1.0 * (1.0 - rf) + rng.uniform(FLOOR_FRICTION_MIN_MULTIPLIER, FLOOR_FRICTION_MAX_MULTIPLIER, (k, 1)) * rf
+    p["floor_friction"] = base["floor_friction"] * mult
+    mass = base["body_mass"].copy()
+    mass[:, 1:] = np.maximum(1e-5, mass[:, 1:] + rng.uniform(-MAX_MASS_CHANGE_PER_LIMB * rf, MAX_MASS_CHANGE_PER_LIMB * rf, (k, 14)))
+    extra_body = rng.integers(1, 15, k)
+    mass[np.arange(k), extra_body] += rng.uniform(0, MAX_EXTERNAL_MASS_ADDED * rf, k)
+    p["body_mass"] = mass
+    hinge_dofs = np.arange(6, NV)
+    arm = base["dof_armature"].copy()
+    arm[:, hinge_dofs] += rng.uniform(0, JOINT_ARMATURE_MAX_CHANGE, (k, 12)) * rf
+    p["dof_armature"] = arm
+    stiff = base["jnt_stiffness"].copy()
+    stiff[:, 1:] += rng.uniform(0, JOINT_STIFFNESS_MAX_CHANGE, (k, 12)) * rf
+    p["jnt_stiffness"] = stiff
+    margin = base["jnt_margin"].copy()
+    margin[:, 1:] += rng.uniform(0, JOINT_MARGIN_MAX_CHANGE, (k, 12)) * rf
+    p["jnt_margin"] = margin
+    rngs = base["jnt_range"].copy()
+    rngs[:, 1:, :] += rng.uniform(-JOINT_RANGE_MAX_CHANGE, JOINT_RANGE_MAX_CHANGE, (k, 12, 2)) * rf
+    p["jnt_range"] = rngs
+    p["act_gainprm0"] = JOINT_P_GAIN + rng.uniform(-JOINT_P_GAIN_MAX_CHANGE, JOINT_P_GAIN_MAX_CHANGE, (k, NU)) * rf
+    p["act_forcerange"] = base["act_forcerange"] + rng.uniform(
+        -JOINT_FORCE_LIMIT_MAX_CHANGE, JOINT_FORCE_LIMIT_MAX_CHANGE, (k, NU, 2)) * rf
+    p["hfield_data"] = _smooth_heightfield(rng, k) * np.float32(MAX_FLOOR_BUMP_HEIGHT * rf)
+    p["timestep"] = timestep
+    return p
+
+
+def standup_start_state(qpos0: np.ndarray, rng: np.random.Generator, rf: float, k: int) -> np.ndarray:
+    """_randomize_joint_positions + _randomize_starting_position (cpu_env.py:282-328), standup reward selected."""
+    qpos = np.tile(np.asarray(qpos0, dtype=np.float64), (k, 1))
+    qpos[:, 7:] += rng.uniform(-JOINT_INITIAL_OFFSET_MAX * rf, JOINT_INITIAL_OFFSET_MAX * rf, (k, 12))
+    qpos[:, 0] = 0.0
+    qpos[:, 1] = 0.0
+    qpos[:, 2] = Z_INITIAL_POS_STANDUP + rng.uniform(0, Z_POSITION_INITIAL_OFFSET_MAX * rf, k)
+    qpos[:, 3:7] = np.array(INITIAL_QUAT_STANDUP) + rng.uniform(-QUAT_INITIAL_OFFSET_MAX * rf, QUAT_INITIAL_OFFSET_MAX * rf, (k, 4))
+    return qpos
+
+
 class BatchedHumanoidEnv:
     metadata = {"render_modes": [], "render_fps": 30}
 
@@ -101,34 +145,7 @@ class BatchedHumanoidEnv:
 
     # ------------------------------------------------------------------ randomisers (cpu_env.py:135-362)
     def _randomize_model(self, idx):
-        rf, rng, k = self.randomization_factor, self.rng, len(idx)
-        p = self.base_params[idx].copy()
-        mult = 1.0 * (1.0 - rf) + rng.uniform(FLOOR_FRICTION_MIN_MULTIPLIER, FLOOR_FRICTION_MAX_MULTIPLIER, (k, 1)) * rf
-        p["floor_friction"] = self.base_params["floor_friction"][idx] * mult
-        mass = self.base_params["body_mass"][idx].copy()
-        mass[:, 1:] = np.maximum(1e-5, mass[:, 1:] + rng.uniform(-MAX_MASS_CHANGE_PER_LIMB * rf, MAX_MASS_CHANGE_PER_LIMB * rf, (k, 14)))
-        extra_body = rng.integers(1, 15, k)
-        mass[np.arange(k), extra_body] += rng.uniform(0, MAX_EXTERNAL_MASS_ADDED * rf, k)
-        p["body_mass"] = mass
-        hinge_dofs = np.arange(6, NV)
-        arm = self.base_params["dof_armature"][idx].copy()
-        arm[:, hinge_dofs] += rng.uniform(0, JOINT_ARMATURE_MAX_CHANGE, (k, 12)) * rf
-        p["dof_armature"] = arm
-        stiff = self.base_params["jnt_stiffness"][idx].copy()
-        stiff[:, 1:] += rng.uniform(0, JOINT_STIFFNESS_MAX_CHANGE, (k, 12)) * rf
-        p["jnt_stiffness"] = stiff
-        margin = self.base_params["jnt_margin"][idx].copy()
-        margin[:, 1:] += rng.uniform(0, JOINT_MARGIN_MAX_CHANGE, (k, 12)) * rf
-        p["jnt_margin"] = margin
-        rngs = self.base_params["jnt_range"][idx].copy()
-        rngs[:, 1:, :] += rng.uniform(-JOINT_RANGE_MAX_CHANGE, JOINT_RANGE_MAX_CHANGE, (k, 12, 2)) * rf
-        p["jnt_range"] = rngs
-        p["act_gainprm0"] = JOINT_P_GAIN + rng.uniform(-JOINT_P_GAIN_MAX_CHANGE, JOINT_P_GAIN_MAX_CHANGE, (k, NU)) * rf
-        p["act_forcerange"] = self.base_params["act_forcerange"][idx] + rng.uniform(
-            -JOINT_FORCE_LIMIT_MAX_CHANGE, JOINT_FORCE_LIMIT_MAX_CHANGE, (k, NU, 2)) * rf
-        p["hfield_data"] = _smooth_heightfield(rng, k) * np.float32(MAX_FLOOR_BUMP_HEIGHT * rf)
-        p["timestep"] = self.timestep
-        self.params[idx] = p
+        self.params[idx] = randomize_params(self.base_params[idx], self.rng, self.randomization_factor, self.timestep)
 
     def _randomize_delays(self, idx):
         rf, rng, k = self.randomization_factor, self.rng, len(idx)
@@ -146,14 +163,7 @@ class BatchedHumanoidEnv:
         self.obs_count[idx] = 0
 
     def _start_state(self, idx):
-        rf, rng, k = self.randomization_factor, self.rng, len(idx)
-        qpos = np.tile(np.array(self.model["qpos0"][0]), (k, 1))
-        qpos[:, 7:] += rng.uniform(-JOINT_INITIAL_OFFSET_MAX * rf, JOINT_INITIAL_OFFSET_MAX * rf, (k, 12))
-        qpos[:, 0] = 0.0
-        qpos[:, 1] = 0.0
-        qpos[:, 2] = Z_INITIAL_POS_STANDUP + rng.uniform(0, Z_POSITION_INITIAL_OFFSET_MAX * rf, k)
-        qpos[:, 3:7] = np.array(INITIAL_QUAT_STANDUP) + rng.uniform(-QUAT_INITIAL_OFFSET_MAX * rf, QUAT_INITIAL_OFFSET_MAX * rf, (k, 4))
-        return qpos
+        return standup_start_state(self.model["qpos0"][0], self.rng, self.randomization_factor, len(idx))
 
     # ------------------------------------------------------------------ reset (cpu_env.py:374-416)
     def reset(self, seed=None, options=None, env_ids=None):
@@ -253,13 +263,18 @@ class BatchedHumanoidEnv:
         ids = np.nonzero(active)[0]
         self.xfrc[ids, 0:2] = self.force_direction[ids] * self.force_magnitude[ids, None]
 
-    def _observe(self, only=None):
-        obs_now, reward, term, trunc, selfc = self.batch.obs_reward(
-            self.previous_action, self.latest_action, self.noise_obs, self.max_simulation_time)
+    def _observe(self, only=None, res=None):
+        """_get_obs + _get_reward on the device; `res` = results of a fused hmj_env_step, else a separate epilogue call."""
+        if res is None:
+            obs_now, reward, term, trunc, selfc = self.batch.obs_reward(
+                self.previous_action, self.latest_action, self.noise_obs, self.max_simulation_time)
+            root_quat = self.batch.get("sens")[:, 3:7]
+        else:
+            obs_now, reward, root_quat = res["obs"], res["reward"], res["root_quat"]
+            term, trunc, selfc = res["terminated"].astype(bool), res["truncated"].astype(bool), res["self_collision"].astype(bool)
         sel = np.ones(self.num_envs, dtype=bool) if only is None else only
         ids = np.nonzero(sel)[0]
-        sens = self.batch.get("sens")
-        self.torso_quat[ids] = sens[ids, 3:7] + self.noise_obs[ids, 27:31]
+        self.torso_quat[ids] = root_quat[ids] + self.noise_obs[ids, 27:31]
         # delay FIFOs (joint angles+velocities share a delay; gyro; gravity), cpu_env.py:135-187,528-547
         slot = self.obs_count[ids] % (MAX_DELAY_STEPS + 1)
         self.obs_hist[ids, slot] = obs_now[ids]
@@ -277,10 +292,12 @@ class BatchedHumanoidEnv:
     def _step_impl(self, action, only):
         self._apply_action(action, only)
         self._apply_external_forces(only)
-        self.batch.set_xfrc(self.force_body, self.xfrc)
-        self.batch.step(self.ctrl, 1)  # PHYSICS_STEPS_PER_CONTROL_STEP = 1 (simulation_parameters.py:82)
-        self.time = self.batch.get("time")
-        obs = self._observe(only)
+        # ONE C call: ctrl/xfrc H2D, mj_step (PHYSICS_STEPS_PER_CONTROL_STEP = 1, simulation_parameters.py:82),
+        # obs/reward epilogue, results D2H
+        res = self.batch.env_step(self.ctrl, self.force_body, self.xfrc, self.previous_action, self.latest_action,
+                                  self.noise_obs, self.max_simulation_time, 1, out=getattr(self, "_out", None))
+        self.time = res["time"].copy()
+        obs = self._observe(only, res)
         reward, term, trunc, selfc = self._last
         if self.reward_override is not None:
             reward = np.full(self.num_envs, float(self.reward_override))

@@ -41,6 +41,9 @@ const char* hmj_last_error(void);
 int hmj_device_count(void);
 int hmj_version(void);
 
+/* measured FP64 FMA peak of the device in TFLOP/s (roofline denominator; MEASURED_PEAKS.json has none) */
+int hmj_fp64_peak(int device, double* tflops);
+
 /* ---- lifecycle.  `model` is the blob written by tools/compile_model.py (replaces
  * MjModel.from_xml_path, cpu_env.py:86 / mj_loadXML in mjpc/agent.cc). */
 int hmj_batch_create(const hmj_model_t* model, int n_envs, int device, hmj_batch_t** out);
@@ -93,6 +96,19 @@ int hmj_env_obs_reward(hmj_batch_t* b, const double* prev_action, const double* 
 int hmj_env_obs_reward_dev(hmj_batch_t* b, const double* prev_action_dev, const double* latest_action_dev,
                            const double* noise_dev, double max_sim_time, double* obs_dev, double* reward_dev,
                            int32_t* terminated_dev, int32_t* truncated_dev, int32_t* self_collision_dev);
+
+/* CPUEnv.step (cpu_env.py:676-693) for all N envs in ONE call: ctrl / push wrench H2D (NULL = keep), nsteps x mj_step
+ * (PHYSICS_STEPS_PER_CONTROL_STEP, simulation_parameters.py:82), observation + reward epilogue, results D2H, one sync.
+ * time_out [N] = data.time, root_quat_out [N][4] = data.xquat[1] (one step stale); either may be NULL. */
+int hmj_env_step(hmj_batch_t* b, const double* ctrl, const int32_t* xfrc_body, const double* xfrc,
+                 const double* prev_action, const double* latest_action, const double* noise, double max_sim_time,
+                 int nsteps, double* obs, double* reward, int32_t* terminated, int32_t* truncated,
+                 int32_t* self_collision, double* time_out, double* root_quat_out);
+
+/* ---- per-kernel device timing (CUDA events on the batch stream, one pair around every launch of a step;
+ * MuJoCo's own equivalent is the mjTIMER_* profiler, mjdata.h:68-93).  enable resets the counters. */
+int hmj_batch_profile(hmj_batch_t* b, int enable);
+int hmj_batch_profile_read(hmj_batch_t* b, double* ms_smooth, double* ms_collide, double* ms_solve, int* nsteps);
 
 /* ---- planner rollouts (SamplingPlanner::Rollouts): every env is one sample.
  * state [37] = qpos,qvel shared by all samples (State::CopyTo, mjpc/states/state.cc:128-135);

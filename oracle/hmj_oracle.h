@@ -159,6 +159,13 @@ int orc_rollout(const hmj_model_t* m, const hmj_params_t* p, const double* state
                 int horizon, double* states, double* actions, double* times, double* residual,
                 double* costs, double* trace, double* total_return);
 
+/* multi-threaded drivers (hmj_oracle_batch.c): CPU-baseline timing harness, return wall seconds */
+double orc_step_batch(const hmj_model_t* m, const hmj_params_t* params, orc_data_t* data, int n_envs,
+                      const double* ctrl, int ctrl_steps, int nsteps, int nthreads);
+double orc_rollout_batch(const hmj_model_t* m, const hmj_params_t* p, const double* state, double time,
+                         const double* spline_times, const double* spline_values, int n, int nnode,
+                         int interpolation, int horizon, double* total_return, int32_t* failure, int nthreads);
+
 int orc_sizeof_data(void);
 int orc_sizeof_model(void);
 int orc_sizeof_params(void);

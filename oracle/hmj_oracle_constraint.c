@@ -9,6 +9,7 @@
  * ls_tolerance 0.01, 50 line-search iterations, impratio 1, refsafe on, warmstart on).
  */
 #include <math.h>
+#include <stdio.h>
 #include <string.h>
 
 #include "hmj_oracle_internal.h"
@@ -448,6 +449,10 @@ void orc_fwd_constraint(const hmj_model_t* m, const hmj_params_t* p, orc_data_t*
   }
   ctx_t c;
   int nefc = d->nefc;
+#ifdef ORC_TRACE
+  for (int i = 0; i < nefc; i++) fprintf(stderr, "ORC row %d D %.17g aref %.17g vel %.17g pos %.17g\n", i, d->efc_D[i], d->efc_aref[i], d->efc_vel[i], d->efc_pos[i]);
+  for (int i = 0; i < d->ncon; i++) fprintf(stderr, "ORC con %d g %d %d dist %.17g fric %g %g %g\n", i, d->contact[i].geom1, d->contact[i].geom2, d->contact[i].dist, d->contact[i].friction[0], d->contact[i].friction[2], d->contact[i].friction[3]);
+#endif
   double scale = 1 / (m->meaninertia * (NV > 1 ? NV : 1));
 
   /* efc_b = J*qacc_smooth - aref */
@@ -482,6 +487,9 @@ void orc_fwd_constraint(const hmj_model_t* m, const hmj_params_t* p, orc_data_t*
   while (iter < m->iterations) {
     double alpha = line_search(m, d, &c);
     d->solver_nls += c.LSiter;
+#ifdef ORC_TRACE
+    fprintf(stderr, "ORC it %d alpha %.17g lsiter %d cost %.17g\n", iter, alpha, c.LSiter, c.cost);
+#endif
     if (alpha == 0) break;
     for (int i = 0; i < NV; i++) { d->qacc[i] += alpha * c.search[i]; c.Ma[i] += alpha * c.Mv[i]; }
     for (int i = 0; i < nefc; i++) c.Jaref[i] += alpha * c.Jv[i];
@@ -495,6 +503,9 @@ void orc_fwd_constraint(const hmj_model_t* m, const hmj_params_t* p, orc_data_t*
     for (int i = 0; i < NV; i++) gn += c.grad[i] * c.grad[i];
     double gradient = scale * sqrt(gn);
     iter++;
+#ifdef ORC_TRACE
+    fprintf(stderr, "ORC    -> cost %.17g improvement %.6g gradient %.6g\n", c.cost, improvement, gradient);
+#endif
     if (improvement < m->tolerance || gradient < m->tolerance) break;
     for (int i = 0; i < NV; i++) c.search[i] = -c.Mgrad[i];
   }

@@ -11,6 +11,7 @@
 #include <string.h>
 
 #include "hmj_oracle_internal.h"
+#include "hmj_sincos.h"
 
 /* ------------------------------------------------------------------ small math */
 double orc_normalize3(double* v) {
@@ -96,8 +97,9 @@ static void axis_angle2quat(double* q, const double* axis, double angle) {
   if (angle == 0) {
     q[0] = 1; q[1] = 0; q[2] = 0; q[3] = 0;
   } else {
-    double s = sin(angle * 0.5);
-    q[0] = cos(angle * 0.5);
+    double s, c;
+    hmj_sincos(angle * 0.5, &s, &c); /* shared deterministic sin/cos (include/hmj_sincos.h): same bits as the kernels */
+    q[0] = c;
     q[1] = axis[0] * s; q[2] = axis[1] * s; q[3] = axis[2] * s;
   }
 }

@@ -122,3 +122,55 @@ class Oracle:
         out["total_return"] = tot.value
         out["failure"] = bool(fail)
         return out
+
+
+class OracleBatch:
+    """N oracle environments stepped by the pthread harness (hmj_oracle_batch.c): CPU-baseline timing and
+    bulk generation of oracle outputs.  TEST INFRASTRUCTURE ONLY."""
+
+    def __init__(self, n: int, model_path: str = DEFAULT_MODEL_PATH):
+        self.lib = C.CDLL(build())
+        self.lib.orc_step_batch.restype = C.c_double
+        self.lib.orc_rollout_batch.restype = C.c_double
+        self.n = int(n)
+        self.model = load_model(model_path).copy()
+        self.params = np.zeros(self.n, dtype=PARAMS_DTYPE)
+        p0 = np.zeros(1, dtype=PARAMS_DTYPE)
+        self.lib.orc_default_params(_ptr(self.model), _ptr(p0))
+        self.params[:] = p0[0]
+        self.data = np.zeros(self.n, dtype=DATA_DTYPE)
+        for i in range(self.n):
+            self.lib.orc_reset_data(_ptr(self.model), C.c_void_p(self.data.ctypes.data + i * DATA_DTYPE.itemsize))
+
+    def set_state(self, qpos, qvel, warmstart=None, time=None):
+        self.data["qpos"][:] = qpos
+        self.data["qvel"][:] = qvel
+        if warmstart is not None:
+            self.data["qacc_warmstart"][:] = warmstart
+        if time is not None:
+            self.data["time"][:] = time
+
+    def step(self, ctrl, nsteps: int, nthreads: int) -> float:
+        """ctrl: [S][n][12] (cycled over steps), [n][12] or None (keep data.ctrl).  Returns wall seconds."""
+        cs = 0
+        if ctrl is not None:
+            ctrl = np.ascontiguousarray(ctrl, dtype=np.float64)
+            if ctrl.ndim == 2:
+                ctrl = ctrl[None]
+            assert ctrl.shape[1:] == (self.n, DEFINES["HMJ_NU"]), ctrl.shape
+            cs = ctrl.shape[0]
+        return float(self.lib.orc_step_batch(_ptr(self.model), _ptr(self.params), _ptr(self.data), self.n,
+                                             _ptr(ctrl) if ctrl is not None else None, cs, int(nsteps), int(nthreads)))
+
+    def rollouts(self, state, time, spline_times, spline_values, horizon, interpolation=2, nthreads=1, params=None):
+        state = np.ascontiguousarray(state, dtype=np.float64)
+        st = np.ascontiguousarray(spline_times, dtype=np.float64)
+        sv = np.ascontiguousarray(spline_values, dtype=np.float64)
+        n = sv.shape[0]
+        ret = np.zeros(n)
+        fail = np.zeros(n, dtype=np.int32)
+        p = self.params[:1] if params is None else params
+        secs = float(self.lib.orc_rollout_batch(
+            _ptr(self.model), _ptr(p), _ptr(state), C.c_double(time), _ptr(st), _ptr(sv), n, st.shape[0],
+            int(interpolation), int(horizon), _ptr(ret), _ptr(fail), int(nthreads)))
+        return ret, fail.astype(bool), secs

@@ -52,6 +52,10 @@ def test_smooth_stage_matches_oracle(hmj, oracle, scen):
                "qM": d["qM"], "qfrc_smooth": d["qfrc_smooth"]}
         for k, v in ref.items():
             worst[k] = max(worst.get(k, 0.0), rel_err(got[k][i], v))
+        # kinematics is built contraction-free with the shared sin/cos: geom frames are the oracle's bits,
+        # which is what makes the (ulp-sensitive) MPR narrowphase reproduce the oracle's contacts exactly
+        assert np.array_equal(got["geom_xpos"][i], d["geom_xpos"]), i
+        assert np.array_equal(got["geom_xmat"][i], d["geom_xmat"]), i
     print("smooth-stage rel err:", worst)
     for k, v in worst.items():
         assert v < 1e-11, (k, v)
