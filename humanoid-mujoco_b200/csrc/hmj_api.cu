@@ -139,6 +139,7 @@ static void build_tables(const hmj_model_t* m, hmj_tables_t* t) {
     }
     adr += npad;
   }
+  t->mesh_adr[HMJ_NMESH] = adr;
   int e = 0;
   for (int i = 0; i < HMJ_NV; i++)
     for (int j = 0; j <= i; j++) { t->tri_i[e] = i; t->tri_j[e] = j; e++; }
@@ -221,6 +222,8 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
   ALLOC("qfrc_smooth", qfrc_smooth, N * HMJ_NV);
   ALLOC("sens", sens, N * SENS_NUM);
   ALLOC("slots", slots, N * HMJ_NSLOT * HMJ_SLOT_DOUBLES);
+  ALLOC("wq_count", wq_count, 64);
+  ALLOC("wq_env", wq_env, N * HMJ_NPAIR);
   ALLOC("qacc", qacc, N * HMJ_NV);
   ALLOC("qacc_smooth", qacc_smooth, N * HMJ_NV);
   ALLOC("qfrc_constraint", qfrc_constraint, N * HMJ_NV);
@@ -360,7 +363,7 @@ static void enqueue_step(hmj_batch_t* b, int integrate) {
   if (prof) prof_event(b);
   hmj_launch_solve(b->tab_dev, b->buf, integrate, b->stream);
   if (prof) prof_event(b);
-  b->launches += 3;
+  b->launches += 4;  // smooth, broad, narrow, solve
 }
 
 // Per-kernel device time of the steps enqueued while profiling was on (CUDA events on the batch stream).
@@ -629,7 +632,7 @@ static int enqueue_rollouts(hmj_batch_t* b, const double* state, double time, co
     if (record) { hmj_launch_plan_record(b->buf, b->rec, t, b->stream); b->launches += 1; }
     hmj_launch_collide(b->tab_dev, b->buf, b->stream);
     hmj_launch_solve(b->tab_dev, b->buf, 1, b->stream);
-    b->launches += 3;
+    b->launches += 4;
   }
   // final mj_forward: only the sensors/residual matter, ctrl keeps the last action (trajectory.cc:190-206)
   hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, HMJ_PLAN_COST, nullptr, nullptr, 0, 0, 0, b->stream);

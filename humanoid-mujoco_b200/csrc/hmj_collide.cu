@@ -1,18 +1,25 @@
-// hmj_collide.cu — kernel 2 of the step: narrowphase for the 37 candidate geom pairs.
+// hmj_collide.cu — stage 2 of the step: broadphase + narrowphase for the 37 candidate geom pairs.
 //
 // Restates mj_collision (simulation/mujoco/include/mujoco/mujoco.h:355) for this model:
 // mjc_Convex (mesh-mesh) and mjc_ConvexHField (mesh vs height-field prisms), both via libccd's
 // MPR penetration query (mpr_tolerance 1e-6, mpr_iterations 50: mjmodel.h:413,436).
 //
-// Mapping: one warp per (environment, candidate pair).  The portal logic is scalar and runs
-// redundantly on all 32 lanes (uniform control flow, no divergence); the hull support function
-// -- >90 % of the arithmetic -- is lane-parallel: each lane scans vertices lane, lane+32, ...
-// (SoA float32, coalesced) and a shuffle arg-max with lowest-index tie-break reproduces the
-// serial "first maximum" exactly.
+// Two kernels:
+//   k_broad   thread per (pair, env): bounding-sphere / hfield-box rejection; survivors are appended to a
+//             per-pair work list (warp-aggregated atomics), the pair's contact slots are cleared.
+//   k_narrow  persistent warps; a work item is 32 queries OF THE SAME PAIR, ONE QUERY PER LANE.  Both
+//             hulls are therefore warp-uniform: the exhaustive support scan reads each vertex once per
+//             warp (shared memory broadcast, fp64 SoA) while every lane evaluates it against its own
+//             direction.  MPR is written as a state machine with exactly one support call per trip, so
+//             lanes in different phases (discover / refine / penetration, next prism) stay converged on
+//             the scan, which is >90 % of the arithmetic; the portal logic runs per lane, not redundantly.
 //
 // THIS TRANSLATION UNIT IS COMPILED WITH -fmad=false: contact count and geom pairs must be
 // bit-identical to the reference path, so every expression is the same sequence of IEEE-754
 // operations as the oracle (oracle/hmj_oracle_collision.c, built with -ffp-contract=off).
+// The six axis-aligned support calls of mjc_ConvexHField collapse into one min/max pass: for
+// dir = +-e_r the scanned value IS the returned coordinate minus pos[r], and negating the direction
+// negates every product exactly, so (max, min) of three dot products reproduce all six results.
 // Roofline: FP64 add/mul issue bound (no FMA by contract); HBM/L2 traffic is 120 doubles of
 // geom frames in and <= 8 doubles per contact slot out.
 #include <float.h>
@@ -20,17 +27,9 @@
 #include "hmj_dev.cuh"
 
 #define CCD_EPS DBL_EPSILON
+#define NARROW_THREADS 128
 
 struct Supp { double v[3], v1[3], v2[3]; };
-
-struct MeshObj {
-  const float* vx; const float* vy; const float* vz;
-  int npad;
-  double pos[3];
-  double mat[9];
-};
-
-struct PrismObj { double p[6][3]; };
 
 // ------------------------------------------------------------------ libccd vec3 helpers
 __device__ __forceinline__ bool c_is_zero(double v) { return fabs(v) < CCD_EPS; }
@@ -76,75 +75,96 @@ __device__ __forceinline__ double c_dist2(const double* a, const double* b) {
   return c_dot(ab, ab);
 }
 
+__device__ __forceinline__ void cp3(double* d, const double* s) { d[0] = s[0]; d[1] = s[1]; d[2] = s[2]; }
+__device__ __forceinline__ void cps(Supp& d, const Supp& s) { cp3(d.v, s.v); cp3(d.v1, s.v1); cp3(d.v2, s.v2); }
+
 // ------------------------------------------------------------------ support functions
-__device__ __forceinline__ void mesh_support(const MeshObj& o, const double* dir, double* out, int lane) {
-  const double* mat = o.mat;
+// Hull vertices of all meshes live in shared memory as fp64 SoA (sx|sy|sz), each mesh starting at an even
+// index and padded to a multiple of 4 with copies of its vertex 0 (a copy can never win: ties go to the
+// lowest index).  `base`/`n4` are warp-uniform, so every LDS.128 is a broadcast.
+struct Hull { int base, n4; };
+
+struct Frame { double pos[3]; double mat[9]; };
+
+__device__ __forceinline__ void mesh_support(const double* __restrict__ sx, const double* __restrict__ sy,
+                                             const double* __restrict__ sz, Hull h, const Frame& f, const double* dir,
+                                             double* out) {
+  const double* mat = f.mat;
   const double ld0 = mat[0] * dir[0] + mat[3] * dir[1] + mat[6] * dir[2];
   const double ld1 = mat[1] * dir[0] + mat[4] * dir[1] + mat[7] * dir[2];
   const double ld2 = mat[2] * dir[0] + mat[5] * dir[1] + mat[8] * dir[2];
-  double best = -HMJ_MAXVAL;
-  int ibest = 0x7fffffff;
-  for (int i = lane; i < o.npad; i += 32) {
-    double vd = ld0 * (double)o.vx[i] + ld1 * (double)o.vy[i] + ld2 * (double)o.vz[i];
-    if (vd > best) { best = vd; ibest = i; }
+  // two interleaved "first maximum" chains (even / odd vertices), merged with lowest-index tie-break:
+  // identical to the serial scan `if (vd > best) { best = vd; ibest = i; }`
+  double b0 = -HMJ_MAXVAL, b1 = -HMJ_MAXVAL;
+  int i0 = 0, i1 = 0x7fffffff;
+  const double2* px = reinterpret_cast<const double2*>(sx + h.base);
+  const double2* py = reinterpret_cast<const double2*>(sy + h.base);
+  const double2* pz = reinterpret_cast<const double2*>(sz + h.base);
+  const int n2 = h.n4 >> 1;
+#pragma unroll 2
+  for (int j = 0; j < n2; j++) {
+    const double2 x = px[j], y = py[j], z = pz[j];
+    const double va = ld0 * x.x + ld1 * y.x + ld2 * z.x;
+    const double vb = ld0 * x.y + ld1 * y.y + ld2 * z.y;
+    if (va > b0) { b0 = va; i0 = 2 * j; }
+    if (vb > b1) { b1 = vb; i1 = 2 * j + 1; }
   }
-#pragma unroll
-  for (int s = 16; s > 0; s >>= 1) {
-    double ob = __shfl_xor_sync(0xffffffffu, best, s);
-    int oi = __shfl_xor_sync(0xffffffffu, ibest, s);
-    if (ob > best || (ob == best && oi < ibest)) { best = ob; ibest = oi; }
-  }
-  if (ibest == 0x7fffffff) ibest = 0;
-  const double p0 = (double)o.vx[ibest], p1 = (double)o.vy[ibest], p2 = (double)o.vz[ibest];
-  out[0] = (mat[0] * p0 + mat[1] * p1 + mat[2] * p2) + o.pos[0];
-  out[1] = (mat[3] * p0 + mat[4] * p1 + mat[5] * p2) + o.pos[1];
-  out[2] = (mat[6] * p0 + mat[7] * p1 + mat[8] * p2) + o.pos[2];
+  if (b1 > b0 || (b1 == b0 && i1 < i0)) i0 = i1;
+  const double p0 = sx[h.base + i0], p1 = sy[h.base + i0], p2 = sz[h.base + i0];
+  out[0] = (mat[0] * p0 + mat[1] * p1 + mat[2] * p2) + f.pos[0];
+  out[1] = (mat[3] * p0 + mat[4] * p1 + mat[5] * p2) + f.pos[1];
+  out[2] = (mat[6] * p0 + mat[7] * p1 + mat[8] * p2) + f.pos[2];
 }
 
-__device__ __forceinline__ void prism_support(const PrismObj& o, const double* dir, double* out) {
+// Axis-aligned bounding box of a hull in the frame `f` == the six obj_support(+-e_r) calls of
+// mjc_ConvexHField (see the header comment for why min/max of three dot products is bit-identical).
+__device__ __forceinline__ void mesh_aabb(const double* __restrict__ sx, const double* __restrict__ sy,
+                                          const double* __restrict__ sz, Hull h, const Frame& f, double* lo, double* hi) {
+  const double* mat = f.mat;
+  double mn0 = HMJ_MAXVAL, mn1 = HMJ_MAXVAL, mn2 = HMJ_MAXVAL, mx0 = -HMJ_MAXVAL, mx1 = -HMJ_MAXVAL, mx2 = -HMJ_MAXVAL;
+  const double2* px = reinterpret_cast<const double2*>(sx + h.base);
+  const double2* py = reinterpret_cast<const double2*>(sy + h.base);
+  const double2* pz = reinterpret_cast<const double2*>(sz + h.base);
+  const int n2 = h.n4 >> 1;
+#pragma unroll 2
+  for (int j = 0; j < n2; j++) {
+    const double2 x = px[j], y = py[j], z = pz[j];
+    double d;
+    d = mat[0] * x.x + mat[1] * y.x + mat[2] * z.x; mn0 = fmin(mn0, d); mx0 = fmax(mx0, d);
+    d = mat[3] * x.x + mat[4] * y.x + mat[5] * z.x; mn1 = fmin(mn1, d); mx1 = fmax(mx1, d);
+    d = mat[6] * x.x + mat[7] * y.x + mat[8] * z.x; mn2 = fmin(mn2, d); mx2 = fmax(mx2, d);
+    d = mat[0] * x.y + mat[1] * y.y + mat[2] * z.y; mn0 = fmin(mn0, d); mx0 = fmax(mx0, d);
+    d = mat[3] * x.y + mat[4] * y.y + mat[5] * z.y; mn1 = fmin(mn1, d); mx1 = fmax(mx1, d);
+    d = mat[6] * x.y + mat[7] * y.y + mat[8] * z.y; mn2 = fmin(mn2, d); mx2 = fmax(mx2, d);
+  }
+  lo[0] = mn0 + f.pos[0]; lo[1] = mn1 + f.pos[1]; lo[2] = mn2 + f.pos[2];
+  hi[0] = mx0 + f.pos[0]; hi[1] = mx1 + f.pos[1]; hi[2] = mx2 + f.pos[2];
+}
+
+// Height-field prism: three top vertices (strip order) over a flat bottom at z = zb with the same (x, y).
+struct Prism { double t[3][3]; double zb; };
+
+__device__ __forceinline__ void prism_support(const Prism& o, const double* dir, double* out) {
   const bool top = !(dir[2] < 0);
-  double a[3], b[3], c[3];
-#pragma unroll
-  for (int k = 0; k < 3; k++) {
-    a[k] = top ? o.p[3][k] : o.p[0][k];
-    b[k] = top ? o.p[4][k] : o.p[1][k];
-    c[k] = top ? o.p[5][k] : o.p[2][k];
-  }
-  double best = a[0] * dir[0] + a[1] * dir[1] + a[2] * dir[2];
-  out[0] = a[0]; out[1] = a[1]; out[2] = a[2];
-  double t = b[0] * dir[0] + b[1] * dir[1] + b[2] * dir[2];
-  if (t > best) { best = t; out[0] = b[0]; out[1] = b[1]; out[2] = b[2]; }
-  t = c[0] * dir[0] + c[1] * dir[1] + c[2] * dir[2];
-  if (t > best) { best = t; out[0] = c[0]; out[1] = c[1]; out[2] = c[2]; }
+  const double za = top ? o.t[0][2] : o.zb, zb = top ? o.t[1][2] : o.zb, zc = top ? o.t[2][2] : o.zb;
+  double best = o.t[0][0] * dir[0] + o.t[0][1] * dir[1] + za * dir[2];
+  out[0] = o.t[0][0]; out[1] = o.t[0][1]; out[2] = za;
+  double t = o.t[1][0] * dir[0] + o.t[1][1] * dir[1] + zb * dir[2];
+  if (t > best) { best = t; out[0] = o.t[1][0]; out[1] = o.t[1][1]; out[2] = zb; }
+  t = o.t[2][0] * dir[0] + o.t[2][1] * dir[1] + zc * dir[2];
+  if (t > best) { best = t; out[0] = o.t[2][0]; out[1] = o.t[2][1]; out[2] = zc; }
 }
 
-template <bool PRISM>
-struct Pair {
-  PrismObj prism;  // used when PRISM
-  MeshObj m1;      // used when !PRISM
-  MeshObj m2;
-  int lane;
-
-  __device__ __forceinline__ void center1(double* c) const {
-    if (PRISM) {
-      c[0] = c[1] = c[2] = 0;
+__device__ __forceinline__ void prism_center(const Prism& o, double* c) {
+  c[0] = c[1] = c[2] = 0;
 #pragma unroll
-      for (int i = 0; i < 6; i++) { c[0] += prism.p[i][0]; c[1] += prism.p[i][1]; c[2] += prism.p[i][2]; }
-      c[0] *= 1.0 / 6.0; c[1] *= 1.0 / 6.0; c[2] *= 1.0 / 6.0;
-    } else {
-      c[0] = m1.pos[0]; c[1] = m1.pos[1]; c[2] = m1.pos[2];
-    }
-  }
-  __device__ __forceinline__ void support(const double* dir, Supp& s) const {
-    double nd[3] = {dir[0], dir[1], dir[2]};
-    if (PRISM) prism_support(prism, dir, s.v1); else mesh_support(m1, dir, s.v1, lane);
-    c_scale(nd, -1.0);
-    mesh_support(m2, nd, s.v2, lane);
-    c_sub2(s.v, s.v1, s.v2);
-  }
-};
+  for (int i = 0; i < 3; i++) { c[0] += o.t[i][0]; c[1] += o.t[i][1]; c[2] += o.zb; }  // bottom vertices 0..2
+#pragma unroll
+  for (int i = 0; i < 3; i++) { c[0] += o.t[i][0]; c[1] += o.t[i][1]; c[2] += o.t[i][2]; }  // top vertices 3..5
+  c[0] *= 1.0 / 6.0; c[1] *= 1.0 / 6.0; c[2] *= 1.0 / 6.0;
+}
 
-// ------------------------------------------------------------------ MPR (libccd mpr.c)
+// ------------------------------------------------------------------ MPR pieces (libccd mpr.c)
 __device__ __forceinline__ void portal_dir(const Supp& p1, const Supp& p2, const Supp& p3, double* dir) {
   double v2v1[3], v3v1[3];
   c_sub2(v2v1, p2.v, p1.v);
@@ -162,16 +182,16 @@ __device__ __forceinline__ bool portal_reach_tolerance(const Supp& p1, const Sup
   return c_eq(dot1, tol) || dot1 < tol;
 }
 
-__device__ __forceinline__ void expand_portal(const Supp& p0, Supp& p1, Supp& p2, Supp& p3, const Supp& v4) {
+__device__ __forceinline__ void expand_portal(const double* p0v, Supp& p1, Supp& p2, Supp& p3, const Supp& v4) {
   double v4v0[3];
-  c_cross(v4v0, v4.v, p0.v);
+  c_cross(v4v0, v4.v, p0v);
   double dot = c_dot(p1.v, v4v0);
   if (dot > 0) {
     dot = c_dot(p2.v, v4v0);
-    if (dot > 0) p1 = v4; else p3 = v4;
+    if (dot > 0) cps(p1, v4); else cps(p3, v4);
   } else {
     dot = c_dot(p3.v, v4v0);
-    if (dot > 0) p2 = v4; else p1 = v4;
+    if (dot > 0) cps(p2, v4); else cps(p1, v4);
   }
 }
 
@@ -183,12 +203,12 @@ __device__ __forceinline__ double point_seg_dist2(const double* P, const double*
   t /= c_dot(d, d);
   if (t < 0 || c_is_zero(t)) {
     dist = c_dist2(x0, P);
-    witness[0] = x0[0]; witness[1] = x0[1]; witness[2] = x0[2];
+    cp3(witness, x0);
   } else if (t > 1 || c_eq(t, 1.0)) {
     dist = c_dist2(b, P);
-    witness[0] = b[0]; witness[1] = b[1]; witness[2] = b[2];
+    cp3(witness, b);
   } else {
-    witness[0] = d[0]; witness[1] = d[1]; witness[2] = d[2];
+    cp3(witness, d);
     c_scale(witness, t);
     witness[0] += x0[0]; witness[1] += x0[1]; witness[2] += x0[2];
     dist = c_dist2(witness, P);
@@ -217,27 +237,29 @@ __device__ __forceinline__ double point_tri_dist2(const double* P, const double*
       (c_eq(t + s, 1.0) || t + s < 1)) {
     c_scale(d1, s);
     c_scale(d2, t);
-    witness[0] = x0[0]; witness[1] = x0[1]; witness[2] = x0[2];
+    cp3(witness, x0);
     witness[0] += d1[0]; witness[1] += d1[1]; witness[2] += d1[2];
     witness[0] += d2[0]; witness[1] += d2[1]; witness[2] += d2[2];
     dist = c_dist2(witness, P);
   } else {
     dist = point_seg_dist2(P, x0, Bv, witness);
     dist2 = point_seg_dist2(P, x0, C, witness2);
-    if (dist2 < dist) { dist = dist2; witness[0] = witness2[0]; witness[1] = witness2[1]; witness[2] = witness2[2]; }
+    if (dist2 < dist) { dist = dist2; cp3(witness, witness2); }
     dist2 = point_seg_dist2(P, Bv, C, witness2);
-    if (dist2 < dist) { dist = dist2; witness[0] = witness2[0]; witness[1] = witness2[1]; witness[2] = witness2[2]; }
+    if (dist2 < dist) { dist = dist2; cp3(witness, witness2); }
   }
   return dist;
 }
 
-__device__ __forceinline__ void find_pos(const Supp& p0, const Supp& p1, const Supp& p2, const Supp& p3, double* pos) {
+// p0v/p0v1/p0v2: the interior point of the Minkowski difference and its two witnesses
+__device__ __forceinline__ void find_pos(const double* p0v, const double* p0v1, const double* p0v2, const Supp& p1,
+                                         const Supp& p2, const Supp& p3, double* pos) {
   double dir[3], b0, b1, b2, b3, sum, inv, vec[3], q1[3] = {0, 0, 0}, q2[3] = {0, 0, 0};
   portal_dir(p1, p2, p3, dir);
   c_cross(vec, p1.v, p2.v); b0 = c_dot(vec, p3.v);
-  c_cross(vec, p3.v, p2.v); b1 = c_dot(vec, p0.v);
-  c_cross(vec, p0.v, p1.v); b2 = c_dot(vec, p3.v);
-  c_cross(vec, p2.v, p1.v); b3 = c_dot(vec, p0.v);
+  c_cross(vec, p3.v, p2.v); b1 = c_dot(vec, p0v);
+  c_cross(vec, p0v, p1.v); b2 = c_dot(vec, p3.v);
+  c_cross(vec, p2.v, p1.v); b3 = c_dot(vec, p0v);
   sum = b0 + b1 + b2 + b3;
   if (c_is_zero(sum) || sum < 0) {
     b0 = 0;
@@ -249,7 +271,7 @@ __device__ __forceinline__ void find_pos(const Supp& p0, const Supp& p1, const S
   inv = 1.0 / sum;
 #pragma unroll
   for (int k = 0; k < 3; k++) {
-    q1[k] += p0.v1[k] * b0; q2[k] += p0.v2[k] * b0;
+    q1[k] += p0v1[k] * b0; q2[k] += p0v2[k] * b0;
     q1[k] += p1.v1[k] * b1; q2[k] += p1.v2[k] * b1;
     q1[k] += p2.v1[k] * b2; q2[k] += p2.v2[k] * b2;
     q1[k] += p3.v1[k] * b3; q2[k] += p3.v2[k] * b3;
@@ -260,247 +282,410 @@ __device__ __forceinline__ void find_pos(const Supp& p0, const Supp& p1, const S
   c_scale(pos, 0.5);
 }
 
-// ccdMPRPenetration: returns 0 when penetrating (depth, dir, pos filled), -1 when separated
-template <bool PRISM>
-__device__ int mpr_penetration(const Pair<PRISM>& pr, double tol, int maxit, double* depth, double* pdir, double* pos) {
-  Supp p0, p1, p2, p3, v4;
-  double dir[3], va[3], vb[3], dot;
-  // ---- discoverPortal
-  pr.center1(p0.v1);
-  p0.v2[0] = pr.m2.pos[0]; p0.v2[1] = pr.m2.pos[1]; p0.v2[2] = pr.m2.pos[2];
-  c_sub2(p0.v, p0.v1, p0.v2);
-  if (c_vec_is_origin(p0.v)) p0.v[0] += CCD_EPS * 10.0;
-  dir[0] = p0.v[0]; dir[1] = p0.v[1]; dir[2] = p0.v[2];
-  c_scale(dir, -1.0);
-  c_normalize(dir);
-  pr.support(dir, p1);
-  dot = c_dot(p1.v, dir);
-  if (c_is_zero(dot) || dot < 0) return -1;
+// ------------------------------------------------------------------ MPR as a per-lane state machine
+// ccdMPRPenetration split at its support calls.  `step` consumes the support point `s` computed for the
+// current `dir` and returns 1 (continue: new dir set), 0 (penetration found: depth/pdir/pos set) or -1.
+enum { ST_D1 = 0, ST_D2, ST_D3, ST_REFINE, ST_PENETR };
 
-  c_cross(dir, p0.v, p1.v);
-  if (c_is_zero(c_dot(dir, dir))) {
-    if (c_vec_is_origin(p1.v)) {  // touching contact on v1
-      *depth = 0;
-      pdir[0] = pdir[1] = pdir[2] = 0;
-      for (int k = 0; k < 3; k++) pos[k] = (p1.v1[k] + p1.v2[k]) * 0.5;
-    } else {  // origin on the v0-v1 segment
-      for (int k = 0; k < 3; k++) pos[k] = (p1.v1[k] + p1.v2[k]) * 0.5;
-      pdir[0] = p1.v[0]; pdir[1] = p1.v[1]; pdir[2] = p1.v[2];
-      *depth = sqrt(c_dot(pdir, pdir));
-      c_normalize(pdir);
-    }
-    return 0;
-  }
-  c_normalize(dir);
-  pr.support(dir, p2);
-  dot = c_dot(p2.v, dir);
-  if (c_is_zero(dot) || dot < 0) return -1;
+struct Mpr {
+  Supp p1, p2, p3;
+  double p0v[3], p0v1[3], p0v2[3];
+  double dir[3];
+  int st, guard, iterations;
+  double depth, pdir[3], pos[3];
 
-  c_sub2(va, p1.v, p0.v);
-  c_sub2(vb, p2.v, p0.v);
-  c_cross(dir, va, vb);
-  c_normalize(dir);
-  dot = c_dot(dir, p0.v);
-  if (dot > 0) {
-    Supp t = p1; p1 = p2; p2 = t;
+  // discoverPortal, up to the first support call
+  __device__ __forceinline__ void begin(const double* center1, const double* center2) {
+    cp3(p0v1, center1);
+    cp3(p0v2, center2);
+    c_sub2(p0v, p0v1, p0v2);
+    if (c_vec_is_origin(p0v)) p0v[0] += CCD_EPS * 10.0;
+    cp3(dir, p0v);
     c_scale(dir, -1.0);
+    c_normalize(dir);
+    st = ST_D1;
   }
-  int guard = 0;
-  bool have4 = false;
-  while (!have4) {
+
+  // head of refinePortal's loop: leaves st = ST_REFINE or ST_PENETR with dir set; -1 on the guard
+  __device__ __forceinline__ int refine_head() {
     if (++guard > 1000) return -1;
-    pr.support(dir, p3);
-    dot = c_dot(p3.v, dir);
-    if (c_is_zero(dot) || dot < 0) return -1;
-    bool cont = false;
-    c_cross(va, p1.v, p3.v);
-    dot = c_dot(va, p0.v);
-    if (dot < 0 && !c_is_zero(dot)) { p2 = p3; cont = true; }
-    if (!cont) {
-      c_cross(va, p3.v, p2.v);
-      dot = c_dot(va, p0.v);
-      if (dot < 0 && !c_is_zero(dot)) { p1 = p3; cont = true; }
-    }
-    if (cont) {
-      c_sub2(va, p1.v, p0.v);
-      c_sub2(vb, p2.v, p0.v);
-      c_cross(dir, va, vb);
-      c_normalize(dir);
+    portal_dir(p1, p2, p3, dir);
+    const double dot = c_dot(dir, p1.v);
+    if (c_is_zero(dot) || dot > 0) {  // portal encapsules origin -> findPenetr (same dir)
+      st = ST_PENETR;
+      iterations = 0;
     } else {
-      have4 = true;
+      st = ST_REFINE;
     }
+    return 1;
   }
-  // ---- refinePortal
-  guard = 0;
-  while (true) {
-    if (++guard > 1000) return -1;
-    portal_dir(p1, p2, p3, dir);
-    dot = c_dot(dir, p1.v);
-    if (c_is_zero(dot) || dot > 0) break;  // portal encapsules origin
-    pr.support(dir, v4);
-    dot = c_dot(v4.v, dir);
-    if (!(c_is_zero(dot) || dot > 0) || portal_reach_tolerance(p1, p2, p3, v4, dir, tol)) return -1;
-    expand_portal(p0, p1, p2, p3, v4);
-  }
-  // ---- findPenetr
-  const double origin[3] = {0, 0, 0};
-  unsigned long iterations = 0;
-  while (true) {
-    portal_dir(p1, p2, p3, dir);
-    pr.support(dir, v4);
-    if (portal_reach_tolerance(p1, p2, p3, v4, dir, tol) || iterations > (unsigned long)maxit) {
-      *depth = point_tri_dist2(origin, p1.v, p2.v, p3.v, pdir);
-      *depth = sqrt(*depth);
-      if (c_is_zero(*depth)) {
-        pdir[0] = pdir[1] = pdir[2] = 0;
-      } else {
-        c_normalize(pdir);
+
+  __device__ __forceinline__ int step(const Supp& s, double tol, int maxit) {
+    double va[3], vb[3], dot;
+    switch (st) {
+      case ST_D1: {
+        cps(p1, s);
+        dot = c_dot(p1.v, dir);
+        if (c_is_zero(dot) || dot < 0) return -1;
+        c_cross(dir, p0v, p1.v);
+        if (c_is_zero(c_dot(dir, dir))) {
+          if (c_vec_is_origin(p1.v)) {  // touching contact on v1
+            depth = 0;
+            pdir[0] = pdir[1] = pdir[2] = 0;
+            for (int k = 0; k < 3; k++) pos[k] = (p1.v1[k] + p1.v2[k]) * 0.5;
+          } else {  // origin on the v0-v1 segment
+            for (int k = 0; k < 3; k++) pos[k] = (p1.v1[k] + p1.v2[k]) * 0.5;
+            cp3(pdir, p1.v);
+            depth = sqrt(c_dot(pdir, pdir));
+            c_normalize(pdir);
+          }
+          return 0;
+        }
+        c_normalize(dir);
+        st = ST_D2;
+        return 1;
       }
-      find_pos(p0, p1, p2, p3, pos);
-      return 0;
+      case ST_D2: {
+        cps(p2, s);
+        dot = c_dot(p2.v, dir);
+        if (c_is_zero(dot) || dot < 0) return -1;
+        c_sub2(va, p1.v, p0v);
+        c_sub2(vb, p2.v, p0v);
+        c_cross(dir, va, vb);
+        c_normalize(dir);
+        dot = c_dot(dir, p0v);
+        if (dot > 0) {
+          Supp t;
+          cps(t, p1); cps(p1, p2); cps(p2, t);
+          c_scale(dir, -1.0);
+        }
+        guard = 1;  // first trip of the while(!have4) loop
+        st = ST_D3;
+        return 1;
+      }
+      case ST_D3: {
+        cps(p3, s);
+        dot = c_dot(p3.v, dir);
+        if (c_is_zero(dot) || dot < 0) return -1;
+        bool cont = false;
+        c_cross(va, p1.v, p3.v);
+        dot = c_dot(va, p0v);
+        if (dot < 0 && !c_is_zero(dot)) { cps(p2, p3); cont = true; }
+        if (!cont) {
+          c_cross(va, p3.v, p2.v);
+          dot = c_dot(va, p0v);
+          if (dot < 0 && !c_is_zero(dot)) { cps(p1, p3); cont = true; }
+        }
+        if (cont) {
+          c_sub2(va, p1.v, p0v);
+          c_sub2(vb, p2.v, p0v);
+          c_cross(dir, va, vb);
+          c_normalize(dir);
+          if (++guard > 1000) return -1;
+          return 1;
+        }
+        guard = 0;
+        return refine_head();
+      }
+      case ST_REFINE: {
+        dot = c_dot(s.v, dir);
+        if (!(c_is_zero(dot) || dot > 0) || portal_reach_tolerance(p1, p2, p3, s, dir, tol)) return -1;
+        expand_portal(p0v, p1, p2, p3, s);
+        return refine_head();
+      }
+      default: {  // ST_PENETR
+        if (portal_reach_tolerance(p1, p2, p3, s, dir, tol) || iterations > maxit) {
+          const double origin[3] = {0, 0, 0};
+          depth = point_tri_dist2(origin, p1.v, p2.v, p3.v, pdir);
+          depth = sqrt(depth);
+          if (c_is_zero(depth)) {
+            pdir[0] = pdir[1] = pdir[2] = 0;
+          } else {
+            c_normalize(pdir);
+          }
+          find_pos(p0v, p0v1, p0v2, p1, p2, p3, pos);
+          return 0;
+        }
+        expand_portal(p0v, p1, p2, p3, s);
+        iterations++;
+        portal_dir(p1, p2, p3, dir);
+        return 1;
+      }
     }
-    expand_portal(p0, p1, p2, p3, v4);
-    iterations++;
   }
-}
+};
 
-__device__ __forceinline__ void set_mesh(MeshObj& o, const hmj_tables_t* T, int mesh) {
-  const int adr = T->mesh_adr[mesh];
-  o.vx = T->vx + adr; o.vy = T->vy + adr; o.vz = T->vz + adr;
-  o.npad = T->mesh_npad[mesh];
-}
-
-__device__ __forceinline__ void write_slot(double* slot, double dist, const double* nrm, const double* pos, int lane) {
-  if (lane == 0) {
-    slot[0] = dist;
-    slot[1] = pos[0]; slot[2] = pos[1]; slot[3] = pos[2];
-    slot[4] = nrm[0]; slot[5] = nrm[1]; slot[6] = nrm[2];
-    slot[7] = 1.0;
-  }
-}
-
-__global__ void __launch_bounds__(32 * HMJ_WARPS_PER_CTA)
-k_collide(const hmj_tables_t* __restrict__ T, hmj_buffers_t B) {
+// ------------------------------------------------------------------ broadphase
+// Thread t = k * npad + e (npad = N rounded up to 32, so k is warp-uniform).  Survivors of the cheap
+// rejection tests are appended to pair k's list wq_env[k][...]; every slot of the pair is cleared.
+__global__ void __launch_bounds__(256)
+k_broad(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int npad) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int k = t / npad;
+  const int env = t - k * npad;
+  if (k >= HMJ_NPAIR) return;
   const int lane = threadIdx.x & 31;
-  const long long w = (long long)blockIdx.x * HMJ_WARPS_PER_CTA + (threadIdx.x >> 5);
-  const int env = (int)(w / HMJ_NPAIR);
-  const int k = (int)(w % HMJ_NPAIR);
-  if (env >= B.n) return;
+  const hmj_model_t& M = T->m;
+  bool hit = false;
+  if (env < B.n) {
+    const int g1 = M.pair_geom1[k], g2 = M.pair_geom2[k];
+    const double* gx = B.geom_xpos + (size_t)env * HMJ_NGEOM * 3;
+    if (g1 != 0) {
+      // mesh-mesh: bounding spheres (mjc_Convex is only reached when they overlap)
+      const double dif0 = gx[g1 * 3] - gx[g2 * 3], dif1 = gx[g1 * 3 + 1] - gx[g2 * 3 + 1], dif2 = gx[g1 * 3 + 2] - gx[g2 * 3 + 2];
+      const double bound = M.geom_rbound[g1] + M.geom_rbound[g2];
+      hit = !(dif0 * dif0 + dif1 * dif1 + dif2 * dif2 > bound * bound);
+    } else {
+      // mesh centre in the hfield frame against the hfield box (head of mjc_ConvexHField)
+      const double* mat1 = B.geom_xmat + (size_t)env * HMJ_NGEOM * 9;
+      const double* size1 = M.hfield_size;
+      const double vec[3] = {gx[g2 * 3] - gx[0], gx[g2 * 3 + 1] - gx[1], gx[g2 * 3 + 2] - gx[2]};
+      double pos[3];
+      pos[0] = mat1[0] * vec[0] + mat1[3] * vec[1] + mat1[6] * vec[2];
+      pos[1] = mat1[1] * vec[0] + mat1[4] * vec[1] + mat1[7] * vec[2];
+      pos[2] = mat1[2] * vec[0] + mat1[5] * vec[1] + mat1[8] * vec[2];
+      const double r2 = M.geom_rbound[g2];
+      hit = true;
+      for (int i = 0; i < 2; i++)
+        if ((size1[i] < pos[i] - r2 - 0.0) || (-size1[i] > pos[i] + r2 + 0.0)) hit = false;
+      if (size1[2] < pos[2] - r2 - 0.0) hit = false;
+      if (-size1[3] > pos[2] + r2 + 0.0) hit = false;
+    }
+    const int slot0 = T->pair_slot[k], nslot = T->pair_slot[k + 1] - slot0;
+    double* slots = B.slots + ((size_t)env * HMJ_NSLOT + slot0) * HMJ_SLOT_DOUBLES;
+    for (int s = 0; s < nslot; s++) slots[(size_t)s * HMJ_SLOT_DOUBLES + 7] = 0.0;
+  }
+  const unsigned bal = __ballot_sync(0xffffffffu, hit);
+  if (bal) {
+    int base = 0;
+    if (lane == 0) base = atomicAdd(&B.wq_count[k], __popc(bal));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (hit) B.wq_env[(size_t)k * B.n + base + __popc(bal & ((1u << lane) - 1u))] = env;
+  }
+}
+
+// ------------------------------------------------------------------ narrowphase
+__device__ __forceinline__ void write_slot(double* slot, double dist, const double* nrm, const double* pos) {
+  slot[0] = dist;
+  slot[1] = pos[0]; slot[2] = pos[1]; slot[3] = pos[2];
+  slot[4] = nrm[0]; slot[5] = nrm[1]; slot[6] = nrm[2];
+  slot[7] = 1.0;
+}
+
+// One work item of mesh-mesh pair k: lane <-> one environment whose bounding spheres overlap.
+__device__ __forceinline__ void narrow_mesh_mesh(const hmj_tables_t* __restrict__ T, const hmj_buffers_t& B,
+                                                 const double* sx, const double* sy, const double* sz, int k, int env,
+                                                 bool active) {
   const hmj_model_t& M = T->m;
   const int g1 = M.pair_geom1[k], g2 = M.pair_geom2[k];
-  const int slot0 = T->pair_slot[k];
-  const int nslot = T->pair_slot[k + 1] - slot0;
-  double* slots = B.slots + ((size_t)env * HMJ_NSLOT + slot0) * HMJ_SLOT_DOUBLES;
+  const Hull h1 = {T->mesh_adr[M.geom_meshid[g1]], T->mesh_npad[M.geom_meshid[g1]]};
+  const Hull h2 = {T->mesh_adr[M.geom_meshid[g2]], T->mesh_npad[M.geom_meshid[g2]]};
   const double* gx = B.geom_xpos + (size_t)env * HMJ_NGEOM * 3;
   const double* gm = B.geom_xmat + (size_t)env * HMJ_NGEOM * 9;
+  Frame f1, f2;
+  for (int q = 0; q < 3; q++) { f1.pos[q] = gx[g1 * 3 + q]; f2.pos[q] = gx[g2 * 3 + q]; }
+  for (int q = 0; q < 9; q++) { f1.mat[q] = gm[g1 * 9 + q]; f2.mat[q] = gm[g2 * 9 + q]; }
   const double tol = M.mpr_tolerance;
   const int maxit = M.mpr_iterations;
-  int cnt = 0;
-
-  if (g1 != 0) {
-    // ---------------- mesh-mesh: bounding spheres, then one MPR query (mjc_Convex, multiccd off)
-    const double dif0 = gx[g1 * 3] - gx[g2 * 3], dif1 = gx[g1 * 3 + 1] - gx[g2 * 3 + 1], dif2 = gx[g1 * 3 + 2] - gx[g2 * 3 + 2];
-    const double bound = M.geom_rbound[g1] + M.geom_rbound[g2];
-    if (!(dif0 * dif0 + dif1 * dif1 + dif2 * dif2 > bound * bound)) {
-      Pair<false> pr;
-      pr.lane = lane;
-      set_mesh(pr.m1, T, M.geom_meshid[g1]);
-      set_mesh(pr.m2, T, M.geom_meshid[g2]);
-      for (int q = 0; q < 3; q++) { pr.m1.pos[q] = gx[g1 * 3 + q]; pr.m2.pos[q] = gx[g2 * 3 + q]; }
-      for (int q = 0; q < 9; q++) { pr.m1.mat[q] = gm[g1 * 9 + q]; pr.m2.mat[q] = gm[g2 * 9 + q]; }
-      double depth, dir[3], pos[3];
-      if (mpr_penetration<false>(pr, tol, maxit, &depth, dir, pos) == 0 && !c_vec_is_origin(dir)) {
-        write_slot(slots, 0.0 - depth, dir, pos, lane);
-        cnt = 1;
-      }
-    }
-  } else {
-    // ---------------- height field (geom 0) vs mesh g2: mjc_ConvexHField
-    const double* pos1 = gx;
-    const double* mat1 = gm;
-    const double* size1 = M.hfield_size;
-    const int nrow = M.hfield_nrow, ncol = M.hfield_ncol;
-    const float* data = B.params[env].hfield_data;
-    Pair<true> pr;
-    pr.lane = lane;
-    set_mesh(pr.m2, T, M.geom_meshid[g2]);
-    double vec[3] = {gx[g2 * 3] - pos1[0], gx[g2 * 3 + 1] - pos1[1], gx[g2 * 3 + 2] - pos1[2]};
-    double* pos = pr.m2.pos;
-    pos[0] = mat1[0] * vec[0] + mat1[3] * vec[1] + mat1[6] * vec[2];
-    pos[1] = mat1[1] * vec[0] + mat1[4] * vec[1] + mat1[7] * vec[2];
-    pos[2] = mat1[2] * vec[0] + mat1[5] * vec[1] + mat1[8] * vec[2];
-    const double r2 = M.geom_rbound[g2];
-    bool ok = true;
-    for (int i = 0; i < 2; i++)
-      if ((size1[i] < pos[i] - r2 - 0.0) || (-size1[i] > pos[i] + r2 + 0.0)) ok = false;
-    if (size1[2] < pos[2] - r2 - 0.0) ok = false;
-    if (-size1[3] > pos[2] + r2 + 0.0) ok = false;
-    if (ok) {
-      const double* mat2 = gm + g2 * 9;
-      for (int i = 0; i < 3; i++)
-        for (int j = 0; j < 3; j++)
-          pr.m2.mat[3 * i + j] = mat1[i] * mat2[j] + mat1[3 + i] * mat2[3 + j] + mat1[6 + i] * mat2[6 + j];
-      double out[3], xmin, xmax, ymin, ymax, zmin, zmax;
-      { double dv[3] = {1, 0, 0};  mesh_support(pr.m2, dv, out, lane); xmax = out[0]; }
-      { double dv[3] = {-1, 0, 0}; mesh_support(pr.m2, dv, out, lane); xmin = out[0]; }
-      { double dv[3] = {0, 1, 0};  mesh_support(pr.m2, dv, out, lane); ymax = out[1]; }
-      { double dv[3] = {0, -1, 0}; mesh_support(pr.m2, dv, out, lane); ymin = out[1]; }
-      { double dv[3] = {0, 0, 1};  mesh_support(pr.m2, dv, out, lane); zmax = out[2]; }
-      { double dv[3] = {0, 0, -1}; mesh_support(pr.m2, dv, out, lane); zmin = out[2]; }
-      if (!((xmin > size1[0]) || (xmax < -size1[0]) || (ymin > size1[1]) || (ymax < -size1[1]) ||
-            (zmin > size1[2]) || (zmax < -size1[3]))) {
-        int cmin = (int)floor((xmin + size1[0]) / (2 * size1[0]) * (ncol - 1));
-        int cmax = (int)ceil((xmax + size1[0]) / (2 * size1[0]) * (ncol - 1));
-        int rmin = (int)floor((ymin + size1[1]) / (2 * size1[1]) * (nrow - 1));
-        int rmax = (int)ceil((ymax + size1[1]) / (2 * size1[1]) * (nrow - 1));
-        cmin = max(0, cmin); cmax = min(ncol - 1, cmax);
-        rmin = max(0, rmin); rmax = min(nrow - 1, rmax);
-        const double dx = (2.0 * size1[0]) / (ncol - 1);
-        const double dy = (2.0 * size1[1]) / (nrow - 1);
-        for (int i = 0; i < 6; i++) pr.prism.p[i][0] = pr.prism.p[i][1] = pr.prism.p[i][2] = 0.0;
-        pr.prism.p[0][2] = pr.prism.p[1][2] = pr.prism.p[2][2] = -size1[3];
-        bool full = false;
-        for (int r = rmin; r < rmax && !full; r++) {
-          int nvert = 0;
-          for (int c = cmin; c <= cmax && !full; c++) {
-            for (int i = 0; i < 2 && !full; i++) {
-              const int rr = r + (i == 0 ? 1 : 0);
-              const double x = dx * c - size1[0], y = dy * rr - size1[1];
-              const double z = (double)data[rr * ncol + c] * size1[2] + 0.0;
-#pragma unroll
-              for (int q = 0; q < 3; q++) {
-                pr.prism.p[0][q] = pr.prism.p[1][q]; pr.prism.p[1][q] = pr.prism.p[2][q];
-                pr.prism.p[3][q] = pr.prism.p[4][q]; pr.prism.p[4][q] = pr.prism.p[5][q];
-              }
-              pr.prism.p[2][0] = x; pr.prism.p[2][1] = y;
-              pr.prism.p[5][0] = x; pr.prism.p[5][1] = y; pr.prism.p[5][2] = z;
-              nvert++;
-              if (nvert > 2) {
-                if (pr.prism.p[3][2] < zmin && pr.prism.p[4][2] < zmin && pr.prism.p[5][2] < zmin) continue;
-                double depth, dirv[3], posv[3];
-                if (mpr_penetration<true>(pr, tol, maxit, &depth, dirv, posv) == 0 && !d_is_bad(depth)) {
-                  double nrm[3], cp[3];
-                  d_rot_vec_mat(nrm, dirv, mat1);
-                  d_rot_vec_mat(cp, posv, mat1);
-                  cp[0] += pos1[0]; cp[1] += pos1[1]; cp[2] += pos1[2];
-                  if (nrm[0] == 0 && nrm[1] == 0 && nrm[2] == 0) continue;
-                  write_slot(slots + (size_t)cnt * HMJ_SLOT_DOUBLES, 0.0 - depth, nrm, cp, lane);
-                  cnt++;
-                  if (cnt >= nslot) full = true;  // per-pair cap HMJ_MAXCONPAIR
-                }
-              }
-            }
-          }
+  Mpr m;
+  m.begin(f1.pos, f2.pos);
+  while (__any_sync(0xffffffffu, active)) {
+    Supp s;
+    double nd[3] = {m.dir[0], m.dir[1], m.dir[2]};
+    mesh_support(sx, sy, sz, h1, f1, m.dir, s.v1);
+    c_scale(nd, -1.0);
+    mesh_support(sx, sy, sz, h2, f2, nd, s.v2);
+    c_sub2(s.v, s.v1, s.v2);
+    if (active) {
+      const int res = m.step(s, tol, maxit);
+      if (res != 1) {
+        active = false;
+        if (res == 0 && !c_vec_is_origin(m.pdir)) {
+          double* slot = B.slots + ((size_t)env * HMJ_NSLOT + T->pair_slot[k]) * HMJ_SLOT_DOUBLES;
+          write_slot(slot, 0.0 - m.depth, m.pdir, m.pos);
         }
       }
     }
   }
-  // clear the unused slots of this pair
-  for (int s = cnt + lane; s < nslot; s += 32) slots[(size_t)s * HMJ_SLOT_DOUBLES + 7] = 0.0;
+}
+
+// One work item of hfield-mesh pair k (mjc_ConvexHField): lane <-> one environment; the lane walks the
+// prisms under the mesh's bounding box and runs one MPR query per prism.
+struct PrismWalk {
+  int r, c, i, nvert, rmax, cmin, cmax;
+  // advance the (r, c, i) strip walk until a prism that must be tested is in `p`; false when exhausted
+  __device__ __forceinline__ bool next(Prism& p, const float* __restrict__ data, const double* size1, int ncol, double dx,
+                                       double dy, double zmin) {
+    while (r < rmax) {
+      const int rr = r + (i == 0 ? 1 : 0);
+      const double x = dx * c - size1[0], y = dy * rr - size1[1];
+      const double z = (double)data[rr * ncol + c] * size1[2] + 0.0;
+      cp3(p.t[0], p.t[1]);
+      cp3(p.t[1], p.t[2]);
+      p.t[2][0] = x; p.t[2][1] = y; p.t[2][2] = z;
+      nvert++;
+      const bool test = nvert > 2 && !(p.t[0][2] < zmin && p.t[1][2] < zmin && p.t[2][2] < zmin);
+      if (++i == 2) {
+        i = 0;
+        if (++c > cmax) { c = cmin; r++; nvert = 0; }
+      }
+      if (test) return true;
+    }
+    return false;
+  }
+};
+
+__device__ __forceinline__ void narrow_hfield(const hmj_tables_t* __restrict__ T, const hmj_buffers_t& B, const double* sx,
+                                              const double* sy, const double* sz, int k, int env, bool active) {
+  const hmj_model_t& M = T->m;
+  const int g2 = M.pair_geom2[k];
+  const Hull h2 = {T->mesh_adr[M.geom_meshid[g2]], T->mesh_npad[M.geom_meshid[g2]]};
+  const double* gx = B.geom_xpos + (size_t)env * HMJ_NGEOM * 3;
+  const double* gm = B.geom_xmat + (size_t)env * HMJ_NGEOM * 9;
+  const double* pos1 = gx;
+  const double* mat1 = gm;
+  const double* size1 = M.hfield_size;
+  const int nrow = M.hfield_nrow, ncol = M.hfield_ncol;
+  const float* data = B.params[env].hfield_data;
+  const double tol = M.mpr_tolerance;
+  const int maxit = M.mpr_iterations;
+  const int slot0 = T->pair_slot[k], nslot = T->pair_slot[k + 1] - slot0;
+  double* slots = B.slots + ((size_t)env * HMJ_NSLOT + slot0) * HMJ_SLOT_DOUBLES;
+
+  // mesh frame expressed in the hfield frame
+  Frame f2;
+  {
+    const double vec[3] = {gx[g2 * 3] - pos1[0], gx[g2 * 3 + 1] - pos1[1], gx[g2 * 3 + 2] - pos1[2]};
+    f2.pos[0] = mat1[0] * vec[0] + mat1[3] * vec[1] + mat1[6] * vec[2];
+    f2.pos[1] = mat1[1] * vec[0] + mat1[4] * vec[1] + mat1[7] * vec[2];
+    f2.pos[2] = mat1[2] * vec[0] + mat1[5] * vec[1] + mat1[8] * vec[2];
+    const double* mat2 = gm + g2 * 9;
+    for (int i = 0; i < 3; i++)
+      for (int j = 0; j < 3; j++)
+        f2.mat[3 * i + j] = mat1[i] * mat2[j] + mat1[3 + i] * mat2[3 + j] + mat1[6 + i] * mat2[6 + j];
+  }
+  double lo[3], hi[3];
+  mesh_aabb(sx, sy, sz, h2, f2, lo, hi);
+  if ((lo[0] > size1[0]) || (hi[0] < -size1[0]) || (lo[1] > size1[1]) || (hi[1] < -size1[1]) || (lo[2] > size1[2]) ||
+      (hi[2] < -size1[3]))
+    active = false;
+  PrismWalk w;
+  {
+    int cmin = (int)floor((lo[0] + size1[0]) / (2 * size1[0]) * (ncol - 1));
+    int cmax = (int)ceil((hi[0] + size1[0]) / (2 * size1[0]) * (ncol - 1));
+    int rmin = (int)floor((lo[1] + size1[1]) / (2 * size1[1]) * (nrow - 1));
+    int rmax = (int)ceil((hi[1] + size1[1]) / (2 * size1[1]) * (nrow - 1));
+    w.cmin = max(0, cmin); w.cmax = min(ncol - 1, cmax);
+    w.r = max(0, rmin); w.rmax = min(nrow - 1, rmax);
+    w.c = w.cmin; w.i = 0; w.nvert = 0;
+    if (w.cmin > w.cmax) active = false;  // empty column range: the strip loops never produce a prism
+  }
+  const double zmin = lo[2];
+  const double dx = (2.0 * size1[0]) / (ncol - 1);
+  const double dy = (2.0 * size1[1]) / (nrow - 1);
+  Prism p;
+  for (int a = 0; a < 3; a++) p.t[a][0] = p.t[a][1] = p.t[a][2] = 0.0;
+  p.zb = -size1[3];
+  int cnt = 0;
+  Mpr m;
+  m.st = ST_D1;
+  m.dir[0] = 1.0; m.dir[1] = 0.0; m.dir[2] = 0.0;
+  if (active) active = w.next(p, data, size1, ncol, dx, dy, zmin);
+  if (active) {
+    double c1[3];
+    prism_center(p, c1);
+    m.begin(c1, f2.pos);
+  }
+  while (__any_sync(0xffffffffu, active)) {
+    Supp s;
+    double nd[3] = {m.dir[0], m.dir[1], m.dir[2]};
+    prism_support(p, m.dir, s.v1);
+    c_scale(nd, -1.0);
+    mesh_support(sx, sy, sz, h2, f2, nd, s.v2);
+    c_sub2(s.v, s.v1, s.v2);
+    if (active) {
+      const int res = m.step(s, tol, maxit);
+      if (res != 1) {
+        if (res == 0 && !d_is_bad(m.depth)) {
+          double nrm[3], cp[3];
+          d_rot_vec_mat(nrm, m.pdir, mat1);
+          d_rot_vec_mat(cp, m.pos, mat1);
+          cp[0] += pos1[0]; cp[1] += pos1[1]; cp[2] += pos1[2];
+          if (!(nrm[0] == 0 && nrm[1] == 0 && nrm[2] == 0)) {
+            write_slot(slots + (size_t)cnt * HMJ_SLOT_DOUBLES, 0.0 - m.depth, nrm, cp);
+            cnt++;
+          }
+        }
+        active = (cnt < nslot) && w.next(p, data, size1, ncol, dx, dy, zmin);  // per-pair cap HMJ_MAXCONPAIR
+        if (active) {
+          double c1[3];
+          prism_center(p, c1);
+          m.begin(c1, f2.pos);
+        }
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(NARROW_THREADS, 2)
+k_narrow(const hmj_tables_t* __restrict__ T, hmj_buffers_t B) {
+  __shared__ __align__(16) double sx[HMJ_NVERT_SMEM];
+  __shared__ __align__(16) double sy[HMJ_NVERT_SMEM];
+  __shared__ __align__(16) double sz[HMJ_NVERT_SMEM];
+  const int nvert = T->mesh_adr[HMJ_NMESH];
+  for (int i = threadIdx.x; i < nvert; i += blockDim.x) {
+    sx[i] = (double)T->vx[i]; sy[i] = (double)T->vy[i]; sz[i] = (double)T->vz[i];
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int warps_per_cta = blockDim.x >> 5;
+  const int gwarp = blockIdx.x * warps_per_cta + (threadIdx.x >> 5);
+  const int nwarp = gridDim.x * warps_per_cta;
+  // work items: pair k contributes ceil(count[k] / 32); lane k holds the exclusive prefix of pair k
+  // (pairs are numbered across TWO registers per lane: k = lane and k = lane + 32)
+  const int c0 = B.wq_count[lane];
+  const int c1 = (lane + 32 < HMJ_NPAIR) ? B.wq_count[lane + 32] : 0;
+  const int n0 = (c0 + 31) >> 5, n1 = (c1 + 31) >> 5;
+  int inc0 = n0;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, inc0, o); if (lane >= o) inc0 += v; }
+  const int tot0 = __shfl_sync(0xffffffffu, inc0, 31);
+  int inc1 = n1;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, inc1, o); if (lane >= o) inc1 += v; }
+  inc1 += tot0;
+  const int total = __shfl_sync(0xffffffffu, inc1, 31);
+  for (int item = gwarp; item < total; item += nwarp) {
+    // pair = number of pairs whose inclusive prefix is <= item
+    const int k = __popc(__ballot_sync(0xffffffffu, inc0 <= item)) + __popc(__ballot_sync(0xffffffffu, inc1 <= item));
+    const int excl = (k == 0) ? 0 : (k <= 32 ? __shfl_sync(0xffffffffu, inc0, (k - 1) & 31) : __shfl_sync(0xffffffffu, inc1, (k - 1) & 31));
+    const int cnt = (k < 32) ? __shfl_sync(0xffffffffu, c0, k & 31) : __shfl_sync(0xffffffffu, c1, k & 31);
+    const int q0 = (item - excl) * 32;
+    const int q = q0 + lane;
+    const bool valid = q < cnt;
+    const int env = B.wq_env[(size_t)k * B.n + (valid ? q : q0)];  // idle lanes shadow the item's first query
+    if (T->m.pair_geom1[k] != 0) narrow_mesh_mesh(T, B, sx, sy, sz, k, env, valid);
+    else narrow_hfield(T, B, sx, sy, sz, k, env, valid);
+  }
 }
 
 void hmj_launch_collide(const hmj_tables_t* tab, hmj_buffers_t buf, cudaStream_t stream) {
-  const long long nwarp = (long long)buf.n * HMJ_NPAIR;
-  const int grid = (int)((nwarp + HMJ_WARPS_PER_CTA - 1) / HMJ_WARPS_PER_CTA);
-  k_collide<<<grid, 32 * HMJ_WARPS_PER_CTA, 0, stream>>>(tab, buf);
+  static int narrow_grid = 0;
+  if (!narrow_grid) {
+    int dev = 0, sms = 148, per_sm = 2;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_narrow, NARROW_THREADS, 0);
+    narrow_grid = sms * (per_sm > 0 ? per_sm : 1);
+  }
+  cudaMemsetAsync(buf.wq_count, 0, 64 * sizeof(int32_t), stream);
+  const int npad = (buf.n + 31) / 32 * 32;
+  const long long nthread = (long long)npad * HMJ_NPAIR;
+  k_broad<<<(int)((nthread + 255) / 256), 256, 0, stream>>>(tab, buf, npad);
+  // no more CTAs than work items in the worst case (every query of every pair active)
+  const long long max_items = (long long)HMJ_NPAIR * ((buf.n + 31) / 32);
+  const int wpc = NARROW_THREADS / 32;
+  int grid = (int)((max_items + wpc - 1) / wpc);
+  if (grid > narrow_grid) grid = narrow_grid;
+  k_narrow<<<grid, NARROW_THREADS, 0, stream>>>(tab, buf);
 }
