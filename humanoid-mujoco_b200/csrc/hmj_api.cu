@@ -125,6 +125,24 @@ static void build_tables(const hmj_model_t* m, hmj_tables_t* t) {
     slot += n;
   }
   t->pair_slot[m->npair] = slot;
+  {  // narrowphase task groups and their capacities (units of N tasks)
+    int cap[64] = {0};
+    int nmm = 0;
+    for (int k = 0; k < m->npair; k++) {
+      if (m->pair_geom1[k] == 0) {
+        const int g = m->geom_meshid[m->pair_geom2[k]];
+        t->pair_group[k] = g;
+        cap[g] += HMJ_MAXCONPAIR;
+      } else {
+        const int g = HMJ_NMESH + nmm++;
+        t->pair_group[k] = g;
+        cap[g] = 1;
+      }
+    }
+    int base = 0;
+    for (int g = 0; g < HMJ_NGROUP; g++) { t->group_base[g] = base; base += cap[g]; }
+    t->group_base[HMJ_NGROUP] = base;
+  }
   int adr = 0;
   for (int k = 0; k < HMJ_NMESH; k++) {
     int nv = m->mesh_vertnum[k], va = m->mesh_vertadr[k];
@@ -223,7 +241,7 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
   ALLOC("sens", sens, N * SENS_NUM);
   ALLOC("slots", slots, N * HMJ_NSLOT * HMJ_SLOT_DOUBLES);
   ALLOC("wq_count", wq_count, 64);
-  ALLOC("wq_env", wq_env, N * HMJ_NPAIR);
+  ALLOC("wq_task", wq_task, N * (size_t)b->tab_host->group_base[HMJ_NGROUP]);
   ALLOC("qacc", qacc, N * HMJ_NV);
   ALLOC("qacc_smooth", qacc_smooth, N * HMJ_NV);
   ALLOC("qfrc_constraint", qfrc_constraint, N * HMJ_NV);

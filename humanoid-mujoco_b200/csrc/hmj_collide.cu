@@ -5,14 +5,19 @@
 // MPR penetration query (mpr_tolerance 1e-6, mpr_iterations 50: mjmodel.h:413,436).
 //
 // Two kernels:
-//   k_broad   thread per (pair, env): bounding-sphere / hfield-box rejection; survivors are appended to a
-//             per-pair work list (warp-aggregated atomics), the pair's contact slots are cleared.
-//   k_narrow  persistent warps; a work item is 32 queries OF THE SAME PAIR, ONE QUERY PER LANE.  Both
-//             hulls are therefore warp-uniform: the exhaustive support scan reads each vertex once per
+//   k_broad   thread per (pair, env), pair warp-uniform.  Mesh-mesh: bounding spheres.  Hfield-mesh: box test,
+//             hull AABB, strip walk over the prisms under the AABB, and the FIRST support call of every prism's
+//             MPR query (where 64 % of them end).  Survivors are appended to task lists grouped by hull
+//             (warp-aggregated atomics); every contact slot of the pair is cleared.
+//   k_narrow  persistent warps; a work item is 32 tasks OF THE SAME GROUP, ONE MPR QUERY PER LANE.  The
+//             hull(s) are therefore warp-uniform: the exhaustive support scan reads each vertex once per
 //             warp (shared memory broadcast, fp64 SoA) while every lane evaluates it against its own
 //             direction.  MPR is written as a state machine with exactly one support call per trip, so
-//             lanes in different phases (discover / refine / penetration, next prism) stay converged on
-//             the scan, which is >90 % of the arithmetic; the portal logic runs per lane, not redundantly.
+//             lanes in different phases (discover / refine / penetration) stay converged on the scan,
+//             which is >90 % of the arithmetic; the portal logic runs per lane, not redundantly.  When few
+//             lanes of a warp are still iterating, the scan switches to a 32-lane cooperative arg-max per
+//             remaining query.  A contact's slot is fixed by (pair, prism ordinal), so the contact order
+//             k_solve compacts is MuJoCo's regardless of which warp produced it.
 //
 // THIS TRANSLATION UNIT IS COMPILED WITH -fmad=false: contact count and geom pairs must be
 // bit-identical to the reference path, so every expression is the same sequence of IEEE-754
@@ -28,6 +33,10 @@
 
 #define CCD_EPS DBL_EPSILON
 #define NARROW_THREADS 128
+#define BROAD_THREADS 128
+#ifndef NARROW_MIN_CTAS
+#define NARROW_MIN_CTAS 2
+#endif
 
 struct Supp { double v[3], v1[3], v2[3]; };
 
@@ -115,6 +124,45 @@ __device__ __forceinline__ void mesh_support(const double* __restrict__ sx, cons
   out[1] = (mat[3] * p0 + mat[4] * p1 + mat[5] * p2) + f.pos[1];
   out[2] = (mat[6] * p0 + mat[7] * p1 + mat[8] * p2) + f.pos[2];
 }
+
+// Cooperative variant for sparsely populated warps: all 32 lanes scan the hull for lane `src`'s direction
+// (lane l takes vertices l, l + 32, ...; xor-butterfly arg-max with lowest-index tie-break == the serial
+// "first maximum").  Only lane `src` receives `out`.  Bit-identical to mesh_support.
+__device__ __forceinline__ void mesh_support_coop(const double* __restrict__ sx, const double* __restrict__ sy,
+                                                  const double* __restrict__ sz, Hull h, const Frame& f, const double* dir,
+                                                  double* out, int src, int lane) {
+  const unsigned FULL = 0xffffffffu;
+  const double* mat = f.mat;
+  double ld0 = mat[0] * dir[0] + mat[3] * dir[1] + mat[6] * dir[2];
+  double ld1 = mat[1] * dir[0] + mat[4] * dir[1] + mat[7] * dir[2];
+  double ld2 = mat[2] * dir[0] + mat[5] * dir[1] + mat[8] * dir[2];
+  ld0 = __shfl_sync(FULL, ld0, src);
+  ld1 = __shfl_sync(FULL, ld1, src);
+  ld2 = __shfl_sync(FULL, ld2, src);
+  double best = -HMJ_MAXVAL;
+  int ibest = 0x7fffffff;
+  for (int i = lane; i < h.n4; i += 32) {
+    const double vd = ld0 * sx[h.base + i] + ld1 * sy[h.base + i] + ld2 * sz[h.base + i];
+    if (vd > best) { best = vd; ibest = i; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double ob = __shfl_xor_sync(FULL, best, o);
+    const int oi = __shfl_xor_sync(FULL, ibest, o);
+    if (ob > best || (ob == best && oi < ibest)) { best = ob; ibest = oi; }
+  }
+  if (ibest == 0x7fffffff) ibest = 0;
+  if (lane == src) {
+    const double p0 = sx[h.base + ibest], p1 = sy[h.base + ibest], p2 = sz[h.base + ibest];
+    out[0] = (mat[0] * p0 + mat[1] * p1 + mat[2] * p2) + f.pos[0];
+    out[1] = (mat[3] * p0 + mat[4] * p1 + mat[5] * p2) + f.pos[1];
+    out[2] = (mat[6] * p0 + mat[7] * p1 + mat[8] * p2) + f.pos[2];
+  }
+}
+
+// Lane count below which the cooperative scan is cheaper than the lane-serial one for a hull of n vertices:
+// serial ~ 12 n issue cycles per trip for the whole warp, cooperative ~ (12 n / 32 + 70) per active lane.
+__device__ __forceinline__ int coop_threshold(int n) { return (12 * n) / ((12 * n) / 32 + 70) + 1; }
 
 // Axis-aligned bounding box of a hull in the frame `f` == the six obj_support(+-e_r) calls of
 // mjc_ConvexHField (see the header comment for why min/max of three dot products is bit-identical).
@@ -415,52 +463,182 @@ struct Mpr {
   }
 };
 
-// ------------------------------------------------------------------ broadphase
-// Thread t = k * npad + e (npad = N rounded up to 32, so k is warp-uniform).  Survivors of the cheap
-// rejection tests are appended to pair k's list wq_env[k][...]; every slot of the pair is cleared.
-__global__ void __launch_bounds__(256)
+// ------------------------------------------------------------------ height-field strip walk
+// mjc_ConvexHField walks, for every grid row r in [rmin, rmax), the strip of vertices
+// (c, r+1), (c, r), (c+1, r+1), (c+1, r), ... ; every three consecutive strip vertices are the top of a prism.
+__device__ __forceinline__ void strip_vertex(double* v, int r, int cmin, int s, const float* __restrict__ data,
+                                             const double* size1, int ncol, double dx, double dy) {
+  const int c = cmin + (s >> 1), i = s & 1;
+  const int rr = r + (i == 0 ? 1 : 0);
+  v[0] = dx * c - size1[0];
+  v[1] = dy * rr - size1[1];
+  v[2] = (double)data[rr * ncol + c] * size1[2] + 0.0;
+}
+
+struct PrismWalk {
+  int r, s, nvert, rmax, cmin, smax;  // smax = strip vertices per row
+  int pr, ps;                          // row / strip index of the newest vertex of the prism just produced
+  // advance until a prism that must be tested is in `p`; false when exhausted
+  __device__ __forceinline__ bool next(Prism& p, const float* __restrict__ data, const double* size1, int ncol, double dx,
+                                       double dy, double zmin) {
+    while (r < rmax) {
+      cp3(p.t[0], p.t[1]);
+      cp3(p.t[1], p.t[2]);
+      strip_vertex(p.t[2], r, cmin, s, data, size1, ncol, dx, dy);
+      nvert++;
+      const bool test = nvert > 2 && !(p.t[0][2] < zmin && p.t[1][2] < zmin && p.t[2][2] < zmin);
+      pr = r; ps = s;
+      if (++s == smax) { s = 0; r++; nvert = 0; }
+      if (test) return true;
+    }
+    return false;
+  }
+};
+
+// mesh g2 expressed in the frame of the height field (geom 0)
+__device__ __forceinline__ void hfield_rel_frame(Frame& f2, const double* gx, const double* gm, int g2) {
+  const double* pos1 = gx;
+  const double* mat1 = gm;
+  const double vec[3] = {gx[g2 * 3] - pos1[0], gx[g2 * 3 + 1] - pos1[1], gx[g2 * 3 + 2] - pos1[2]};
+  f2.pos[0] = mat1[0] * vec[0] + mat1[3] * vec[1] + mat1[6] * vec[2];
+  f2.pos[1] = mat1[1] * vec[0] + mat1[4] * vec[1] + mat1[7] * vec[2];
+  f2.pos[2] = mat1[2] * vec[0] + mat1[5] * vec[1] + mat1[8] * vec[2];
+  const double* mat2 = gm + g2 * 9;
+  for (int i = 0; i < 3; i++)
+    for (int j = 0; j < 3; j++)
+      f2.mat[3 * i + j] = mat1[i] * mat2[j] + mat1[3 + i] * mat2[3 + j] + mat1[6 + i] * mat2[6 + j];
+}
+
+// task word: pair k (6 bits) | slot ordinal (3) | strip row (3) | cmin (3) | strip index of the newest vertex (5)
+__device__ __forceinline__ int pack_task(int k, int ord, int r, int cmin, int s) {
+  return k | (ord << 6) | (r << 9) | (cmin << 12) | (s << 15);
+}
+
+__device__ __forceinline__ void stage_hulls(const hmj_tables_t* __restrict__ T, double* sx, double* sy, double* sz) {
+  const int nvert = T->mesh_adr[HMJ_NMESH];
+  for (int i = threadIdx.x; i < nvert; i += blockDim.x) {
+    sx[i] = (double)T->vx[i]; sy[i] = (double)T->vy[i]; sz[i] = (double)T->vz[i];
+  }
+  __syncthreads();
+}
+
+// warp-aggregated append of (env, word) to task group g for the lanes with `hit`
+__device__ __forceinline__ void push_tasks(const hmj_tables_t* __restrict__ T, const hmj_buffers_t& B, int g, bool hit,
+                                           int env, int word, int lane) {
+  const unsigned bal = __ballot_sync(0xffffffffu, hit);
+  if (!bal) return;
+  int base = 0;
+  if (lane == __ffs(bal) - 1) base = atomicAdd(&B.wq_count[g], __popc(bal));
+  base = __shfl_sync(0xffffffffu, base, __ffs(bal) - 1);
+  if (hit) B.wq_task[(size_t)T->group_base[g] * B.n + base + __popc(bal & ((1u << lane) - 1u))] = make_int2(env, word);
+}
+
+// ------------------------------------------------------------------ broadphase + midphase
+// Thread t = k * npad + e (npad = N rounded up to 32, so the pair k is warp-uniform).
+//  * mesh-mesh pair: bounding spheres; survivors become one MPR task.
+//  * hfield-mesh pair (head of mjc_ConvexHField): box test, hull AABB in the hfield frame, strip walk; every
+//    prism that must be tested gets its slot ordinal and is pre-screened with the FIRST support call of
+//    ccdMPRPenetration's discoverPortal (64 % of all queries end there: dot(v1, dir) <= 0 -> no contact);
+//    survivors become MPR tasks, which restart the query from the top in k_narrow (same arithmetic).
+// Every contact slot of the pair is cleared here; k_narrow only sets the ones it fills.
+__global__ void __launch_bounds__(BROAD_THREADS)
 k_broad(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int npad) {
+  __shared__ __align__(16) double sx[HMJ_NVERT_SMEM];
+  __shared__ __align__(16) double sy[HMJ_NVERT_SMEM];
+  __shared__ __align__(16) double sz[HMJ_NVERT_SMEM];
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  const int k = t / npad;
-  const int env = t - k * npad;
-  if (k >= HMJ_NPAIR) return;
+  const int k = t / npad;  // warp-uniform; whole CTAs can be past the last pair
+  const int e = t - k * npad;
   const int lane = threadIdx.x & 31;
   const hmj_model_t& M = T->m;
-  bool hit = false;
-  if (env < B.n) {
-    const int g1 = M.pair_geom1[k], g2 = M.pair_geom2[k];
-    const double* gx = B.geom_xpos + (size_t)env * HMJ_NGEOM * 3;
-    if (g1 != 0) {
-      // mesh-mesh: bounding spheres (mjc_Convex is only reached when they overlap)
-      const double dif0 = gx[g1 * 3] - gx[g2 * 3], dif1 = gx[g1 * 3 + 1] - gx[g2 * 3 + 1], dif2 = gx[g1 * 3 + 2] - gx[g2 * 3 + 2];
-      const double bound = M.geom_rbound[g1] + M.geom_rbound[g2];
-      hit = !(dif0 * dif0 + dif1 * dif1 + dif2 * dif2 > bound * bound);
-    } else {
-      // mesh centre in the hfield frame against the hfield box (head of mjc_ConvexHField)
-      const double* mat1 = B.geom_xmat + (size_t)env * HMJ_NGEOM * 9;
-      const double* size1 = M.hfield_size;
-      const double vec[3] = {gx[g2 * 3] - gx[0], gx[g2 * 3 + 1] - gx[1], gx[g2 * 3 + 2] - gx[2]};
-      double pos[3];
-      pos[0] = mat1[0] * vec[0] + mat1[3] * vec[1] + mat1[6] * vec[2];
-      pos[1] = mat1[1] * vec[0] + mat1[4] * vec[1] + mat1[7] * vec[2];
-      pos[2] = mat1[2] * vec[0] + mat1[5] * vec[1] + mat1[8] * vec[2];
-      const double r2 = M.geom_rbound[g2];
-      hit = true;
-      for (int i = 0; i < 2; i++)
-        if ((size1[i] < pos[i] - r2 - 0.0) || (-size1[i] > pos[i] + r2 + 0.0)) hit = false;
-      if (size1[2] < pos[2] - r2 - 0.0) hit = false;
-      if (-size1[3] > pos[2] + r2 + 0.0) hit = false;
-    }
-    const int slot0 = T->pair_slot[k], nslot = T->pair_slot[k + 1] - slot0;
-    double* slots = B.slots + ((size_t)env * HMJ_NSLOT + slot0) * HMJ_SLOT_DOUBLES;
+  if (k >= HMJ_NPAIR) return;  // npad * NPAIR is a multiple of 32: whole warps leave together (before any barrier use)
+  const bool in = e < B.n;
+  const int env = in ? e : B.n - 1;
+  const int g1 = M.pair_geom1[k], g2 = M.pair_geom2[k];
+  const double* gx = B.geom_xpos + (size_t)env * HMJ_NGEOM * 3;
+  const double* gm = B.geom_xmat + (size_t)env * HMJ_NGEOM * 9;
+  const int slot0 = T->pair_slot[k], nslot = T->pair_slot[k + 1] - slot0;
+  double* slots = B.slots + ((size_t)env * HMJ_NSLOT + slot0) * HMJ_SLOT_DOUBLES;
+  if (in)
     for (int s = 0; s < nslot; s++) slots[(size_t)s * HMJ_SLOT_DOUBLES + 7] = 0.0;
+
+  if (g1 != 0) {
+    const double dif0 = gx[g1 * 3] - gx[g2 * 3], dif1 = gx[g1 * 3 + 1] - gx[g2 * 3 + 1], dif2 = gx[g1 * 3 + 2] - gx[g2 * 3 + 2];
+    const double bound = M.geom_rbound[g1] + M.geom_rbound[g2];
+    const bool hit = in && !(dif0 * dif0 + dif1 * dif1 + dif2 * dif2 > bound * bound);
+    push_tasks(T, B, T->pair_group[k], hit, env, pack_task(k, 0, 0, 0, 0), lane);
+    return;
   }
-  const unsigned bal = __ballot_sync(0xffffffffu, hit);
-  if (bal) {
-    int base = 0;
-    if (lane == 0) base = atomicAdd(&B.wq_count[k], __popc(bal));
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (hit) B.wq_env[(size_t)k * B.n + base + __popc(bal & ((1u << lane) - 1u))] = env;
+  // ---- hfield pair.  NOTE: k_broad is launched with hfield pairs in their own CTAs (npad is a multiple of
+  // BROAD_THREADS), so the barrier inside stage_hulls is reached by whole CTAs only.
+  stage_hulls(T, sx, sy, sz);
+  const double* size1 = M.hfield_size;
+  const int nrow = M.hfield_nrow, ncol = M.hfield_ncol;
+  const float* data = B.params[env].hfield_data;
+  const Hull h2 = {T->mesh_adr[M.geom_meshid[g2]], T->mesh_npad[M.geom_meshid[g2]]};
+  Frame f2;
+  hfield_rel_frame(f2, gx, gm, g2);
+  bool active = in;
+  {
+    const double r2 = M.geom_rbound[g2];
+    for (int i = 0; i < 2; i++)
+      if ((size1[i] < f2.pos[i] - r2 - 0.0) || (-size1[i] > f2.pos[i] + r2 + 0.0)) active = false;
+    if (size1[2] < f2.pos[2] - r2 - 0.0) active = false;
+    if (-size1[3] > f2.pos[2] + r2 + 0.0) active = false;
+  }
+  if (!__any_sync(0xffffffffu, active)) return;
+  double lo[3], hi[3];
+  mesh_aabb(sx, sy, sz, h2, f2, lo, hi);
+  if ((lo[0] > size1[0]) || (hi[0] < -size1[0]) || (lo[1] > size1[1]) || (hi[1] < -size1[1]) || (lo[2] > size1[2]) ||
+      (hi[2] < -size1[3]))
+    active = false;
+  PrismWalk w;
+  {
+    int cmin = (int)floor((lo[0] + size1[0]) / (2 * size1[0]) * (ncol - 1));
+    int cmax = (int)ceil((hi[0] + size1[0]) / (2 * size1[0]) * (ncol - 1));
+    int rmin = (int)floor((lo[1] + size1[1]) / (2 * size1[1]) * (nrow - 1));
+    int rmax = (int)ceil((hi[1] + size1[1]) / (2 * size1[1]) * (nrow - 1));
+    cmin = max(0, cmin); cmax = min(ncol - 1, cmax);
+    w.cmin = cmin;
+    w.smax = 2 * (cmax - cmin + 1);
+    w.r = max(0, rmin); w.rmax = min(nrow - 1, rmax);
+    w.s = 0; w.nvert = 0; w.pr = w.ps = 0;
+    if (cmin > cmax) active = false;  // empty column range: the strip loops never produce a prism
+  }
+  const double zmin = lo[2];
+  const double dx = (2.0 * size1[0]) / (ncol - 1);
+  const double dy = (2.0 * size1[1]) / (nrow - 1);
+  Prism p;
+  for (int a = 0; a < 3; a++) p.t[a][0] = p.t[a][1] = p.t[a][2] = 0.0;
+  p.zb = -size1[3];
+  const int g = T->pair_group[k];
+  int ord = 0;
+  while (true) {
+    const bool has = active && w.next(p, data, size1, ncol, dx, dy, zmin);
+    if (!__any_sync(0xffffffffu, has)) break;
+    active = has;
+    // discoverPortal up to its first exit test
+    double c1[3], p0v[3], dir[3], v1[3], v2[3], v[3], nd[3];
+    prism_center(p, c1);
+    c_sub2(p0v, c1, f2.pos);
+    if (c_vec_is_origin(p0v)) p0v[0] += CCD_EPS * 10.0;
+    cp3(dir, p0v);
+    c_scale(dir, -1.0);
+    c_normalize(dir);
+    prism_support(p, dir, v1);
+    cp3(nd, dir);
+    c_scale(nd, -1.0);
+    mesh_support(sx, sy, sz, h2, f2, nd, v2);
+    c_sub2(v, v1, v2);
+    const double dot = c_dot(v, dir);
+    bool survive = has && !(c_is_zero(dot) || dot < 0);
+    if (has && ord >= nslot) {  // more tested prisms than slots: cannot happen for this model's geometry (<= 8)
+      survive = false;
+      active = false;
+      atomicOr(&B.status[env], HMJ_STATUS_CONTACTFULL);
+    }
+    push_tasks(T, B, g, survive, env, pack_task(k, ord, w.pr, w.cmin, w.ps), lane);
+    if (has) ord++;
   }
 }
 
@@ -472,11 +650,12 @@ __device__ __forceinline__ void write_slot(double* slot, double dist, const doub
   slot[7] = 1.0;
 }
 
-// One work item of mesh-mesh pair k: lane <-> one environment whose bounding spheres overlap.
+// 32 mesh-mesh tasks of one pair (mjc_Convex, multiccd off): lane <-> environment.
 __device__ __forceinline__ void narrow_mesh_mesh(const hmj_tables_t* __restrict__ T, const hmj_buffers_t& B,
-                                                 const double* sx, const double* sy, const double* sz, int k, int env,
-                                                 bool active) {
+                                                 const double* sx, const double* sy, const double* sz, int2 task,
+                                                 bool active, int lane) {
   const hmj_model_t& M = T->m;
+  const int env = task.x, k = task.y & 63;
   const int g1 = M.pair_geom1[k], g2 = M.pair_geom2[k];
   const Hull h1 = {T->mesh_adr[M.geom_meshid[g1]], T->mesh_npad[M.geom_meshid[g1]]};
   const Hull h2 = {T->mesh_adr[M.geom_meshid[g2]], T->mesh_npad[M.geom_meshid[g2]]};
@@ -489,12 +668,23 @@ __device__ __forceinline__ void narrow_mesh_mesh(const hmj_tables_t* __restrict_
   const int maxit = M.mpr_iterations;
   Mpr m;
   m.begin(f1.pos, f2.pos);
-  while (__any_sync(0xffffffffu, active)) {
+  const int thr = coop_threshold(h1.n4 + h2.n4);
+  while (true) {
+    const unsigned am = __ballot_sync(0xffffffffu, active);
+    if (!am) break;
     Supp s;
     double nd[3] = {m.dir[0], m.dir[1], m.dir[2]};
-    mesh_support(sx, sy, sz, h1, f1, m.dir, s.v1);
     c_scale(nd, -1.0);
-    mesh_support(sx, sy, sz, h2, f2, nd, s.v2);
+    if (__popc(am) >= thr) {
+      mesh_support(sx, sy, sz, h1, f1, m.dir, s.v1);
+      mesh_support(sx, sy, sz, h2, f2, nd, s.v2);
+    } else {
+      for (unsigned mm = am; mm; mm &= mm - 1) {
+        const int src = __ffs(mm) - 1;
+        mesh_support_coop(sx, sy, sz, h1, f1, m.dir, s.v1, src, lane);
+        mesh_support_coop(sx, sy, sz, h2, f2, nd, s.v2, src, lane);
+      }
+    }
     c_sub2(s.v, s.v1, s.v2);
     if (active) {
       const int res = m.step(s, tol, maxit);
@@ -509,142 +699,82 @@ __device__ __forceinline__ void narrow_mesh_mesh(const hmj_tables_t* __restrict_
   }
 }
 
-// One work item of hfield-mesh pair k (mjc_ConvexHField): lane <-> one environment; the lane walks the
-// prisms under the mesh's bounding box and runs one MPR query per prism.
-struct PrismWalk {
-  int r, c, i, nvert, rmax, cmin, cmax;
-  // advance the (r, c, i) strip walk until a prism that must be tested is in `p`; false when exhausted
-  __device__ __forceinline__ bool next(Prism& p, const float* __restrict__ data, const double* size1, int ncol, double dx,
-                                       double dy, double zmin) {
-    while (r < rmax) {
-      const int rr = r + (i == 0 ? 1 : 0);
-      const double x = dx * c - size1[0], y = dy * rr - size1[1];
-      const double z = (double)data[rr * ncol + c] * size1[2] + 0.0;
-      cp3(p.t[0], p.t[1]);
-      cp3(p.t[1], p.t[2]);
-      p.t[2][0] = x; p.t[2][1] = y; p.t[2][2] = z;
-      nvert++;
-      const bool test = nvert > 2 && !(p.t[0][2] < zmin && p.t[1][2] < zmin && p.t[2][2] < zmin);
-      if (++i == 2) {
-        i = 0;
-        if (++c > cmax) { c = cmin; r++; nvert = 0; }
-      }
-      if (test) return true;
-    }
-    return false;
-  }
-};
-
+// 32 prism-vs-hull tasks of one hull (pairs may differ per lane): lane <-> one pre-screened prism of
+// mjc_ConvexHField; the query restarts from the top (same arithmetic as the screen in k_broad).
 __device__ __forceinline__ void narrow_hfield(const hmj_tables_t* __restrict__ T, const hmj_buffers_t& B, const double* sx,
-                                              const double* sy, const double* sz, int k, int env, bool active) {
+                                              const double* sy, const double* sz, Hull h2, int2 task, bool active, int lane) {
   const hmj_model_t& M = T->m;
+  const int env = task.x;
+  const int k = task.y & 63, ord = (task.y >> 6) & 7, r = (task.y >> 9) & 7, cmin = (task.y >> 12) & 7, ps = (task.y >> 15) & 31;
   const int g2 = M.pair_geom2[k];
-  const Hull h2 = {T->mesh_adr[M.geom_meshid[g2]], T->mesh_npad[M.geom_meshid[g2]]};
   const double* gx = B.geom_xpos + (size_t)env * HMJ_NGEOM * 3;
   const double* gm = B.geom_xmat + (size_t)env * HMJ_NGEOM * 9;
-  const double* pos1 = gx;
-  const double* mat1 = gm;
   const double* size1 = M.hfield_size;
   const int nrow = M.hfield_nrow, ncol = M.hfield_ncol;
   const float* data = B.params[env].hfield_data;
   const double tol = M.mpr_tolerance;
   const int maxit = M.mpr_iterations;
-  const int slot0 = T->pair_slot[k], nslot = T->pair_slot[k + 1] - slot0;
-  double* slots = B.slots + ((size_t)env * HMJ_NSLOT + slot0) * HMJ_SLOT_DOUBLES;
-
-  // mesh frame expressed in the hfield frame
   Frame f2;
-  {
-    const double vec[3] = {gx[g2 * 3] - pos1[0], gx[g2 * 3 + 1] - pos1[1], gx[g2 * 3 + 2] - pos1[2]};
-    f2.pos[0] = mat1[0] * vec[0] + mat1[3] * vec[1] + mat1[6] * vec[2];
-    f2.pos[1] = mat1[1] * vec[0] + mat1[4] * vec[1] + mat1[7] * vec[2];
-    f2.pos[2] = mat1[2] * vec[0] + mat1[5] * vec[1] + mat1[8] * vec[2];
-    const double* mat2 = gm + g2 * 9;
-    for (int i = 0; i < 3; i++)
-      for (int j = 0; j < 3; j++)
-        f2.mat[3 * i + j] = mat1[i] * mat2[j] + mat1[3 + i] * mat2[3 + j] + mat1[6 + i] * mat2[6 + j];
-  }
-  double lo[3], hi[3];
-  mesh_aabb(sx, sy, sz, h2, f2, lo, hi);
-  if ((lo[0] > size1[0]) || (hi[0] < -size1[0]) || (lo[1] > size1[1]) || (hi[1] < -size1[1]) || (lo[2] > size1[2]) ||
-      (hi[2] < -size1[3]))
-    active = false;
-  PrismWalk w;
-  {
-    int cmin = (int)floor((lo[0] + size1[0]) / (2 * size1[0]) * (ncol - 1));
-    int cmax = (int)ceil((hi[0] + size1[0]) / (2 * size1[0]) * (ncol - 1));
-    int rmin = (int)floor((lo[1] + size1[1]) / (2 * size1[1]) * (nrow - 1));
-    int rmax = (int)ceil((hi[1] + size1[1]) / (2 * size1[1]) * (nrow - 1));
-    w.cmin = max(0, cmin); w.cmax = min(ncol - 1, cmax);
-    w.r = max(0, rmin); w.rmax = min(nrow - 1, rmax);
-    w.c = w.cmin; w.i = 0; w.nvert = 0;
-    if (w.cmin > w.cmax) active = false;  // empty column range: the strip loops never produce a prism
-  }
-  const double zmin = lo[2];
+  hfield_rel_frame(f2, gx, gm, g2);
   const double dx = (2.0 * size1[0]) / (ncol - 1);
   const double dy = (2.0 * size1[1]) / (nrow - 1);
   Prism p;
-  for (int a = 0; a < 3; a++) p.t[a][0] = p.t[a][1] = p.t[a][2] = 0.0;
   p.zb = -size1[3];
-  int cnt = 0;
+#pragma unroll
+  for (int a = 0; a < 3; a++) strip_vertex(p.t[a], r, cmin, max(ps - 2 + a, 0), data, size1, ncol, dx, dy);
   Mpr m;
-  m.st = ST_D1;
-  m.dir[0] = 1.0; m.dir[1] = 0.0; m.dir[2] = 0.0;
-  if (active) active = w.next(p, data, size1, ncol, dx, dy, zmin);
-  if (active) {
+  {
     double c1[3];
     prism_center(p, c1);
     m.begin(c1, f2.pos);
   }
-  while (__any_sync(0xffffffffu, active)) {
+  const int thr = coop_threshold(h2.n4);
+  while (true) {
+    const unsigned am = __ballot_sync(0xffffffffu, active);
+    if (!am) break;
     Supp s;
     double nd[3] = {m.dir[0], m.dir[1], m.dir[2]};
     prism_support(p, m.dir, s.v1);
     c_scale(nd, -1.0);
-    mesh_support(sx, sy, sz, h2, f2, nd, s.v2);
+    if (__popc(am) >= thr) {
+      mesh_support(sx, sy, sz, h2, f2, nd, s.v2);
+    } else {
+      for (unsigned mm = am; mm; mm &= mm - 1)
+        mesh_support_coop(sx, sy, sz, h2, f2, nd, s.v2, __ffs(mm) - 1, lane);
+    }
     c_sub2(s.v, s.v1, s.v2);
     if (active) {
       const int res = m.step(s, tol, maxit);
       if (res != 1) {
+        active = false;
         if (res == 0 && !d_is_bad(m.depth)) {
+          const double* pos1 = gx;
+          const double* mat1 = gm;
           double nrm[3], cp[3];
           d_rot_vec_mat(nrm, m.pdir, mat1);
           d_rot_vec_mat(cp, m.pos, mat1);
           cp[0] += pos1[0]; cp[1] += pos1[1]; cp[2] += pos1[2];
           if (!(nrm[0] == 0 && nrm[1] == 0 && nrm[2] == 0)) {
-            write_slot(slots + (size_t)cnt * HMJ_SLOT_DOUBLES, 0.0 - m.depth, nrm, cp);
-            cnt++;
+            double* slot = B.slots + ((size_t)env * HMJ_NSLOT + T->pair_slot[k] + ord) * HMJ_SLOT_DOUBLES;
+            write_slot(slot, 0.0 - m.depth, nrm, cp);
           }
-        }
-        active = (cnt < nslot) && w.next(p, data, size1, ncol, dx, dy, zmin);  // per-pair cap HMJ_MAXCONPAIR
-        if (active) {
-          double c1[3];
-          prism_center(p, c1);
-          m.begin(c1, f2.pos);
         }
       }
     }
   }
 }
 
-__global__ void __launch_bounds__(NARROW_THREADS, 2)
+// Persistent warps over the task groups (7 hfield groups keyed by hull, 28 mesh-mesh groups keyed by pair);
+// a work item is 32 consecutive tasks of one group, so the hull(s) a warp scans are uniform.
+__global__ void __launch_bounds__(NARROW_THREADS, NARROW_MIN_CTAS)
 k_narrow(const hmj_tables_t* __restrict__ T, hmj_buffers_t B) {
   __shared__ __align__(16) double sx[HMJ_NVERT_SMEM];
   __shared__ __align__(16) double sy[HMJ_NVERT_SMEM];
   __shared__ __align__(16) double sz[HMJ_NVERT_SMEM];
-  const int nvert = T->mesh_adr[HMJ_NMESH];
-  for (int i = threadIdx.x; i < nvert; i += blockDim.x) {
-    sx[i] = (double)T->vx[i]; sy[i] = (double)T->vy[i]; sz[i] = (double)T->vz[i];
-  }
-  __syncthreads();
   const int lane = threadIdx.x & 31;
-  const int warps_per_cta = blockDim.x >> 5;
-  const int gwarp = blockIdx.x * warps_per_cta + (threadIdx.x >> 5);
-  const int nwarp = gridDim.x * warps_per_cta;
-  // work items: pair k contributes ceil(count[k] / 32); lane k holds the exclusive prefix of pair k
-  // (pairs are numbered across TWO registers per lane: k = lane and k = lane + 32)
+  // work items: group g contributes ceil(count[g] / 32); groups are numbered across TWO registers per lane
   const int c0 = B.wq_count[lane];
-  const int c1 = (lane + 32 < HMJ_NPAIR) ? B.wq_count[lane + 32] : 0;
+  const int c1 = (lane + 32 < HMJ_NGROUP) ? B.wq_count[lane + 32] : 0;
   const int n0 = (c0 + 31) >> 5, n1 = (c1 + 31) >> 5;
   int inc0 = n0;
 #pragma unroll
@@ -655,17 +785,25 @@ k_narrow(const hmj_tables_t* __restrict__ T, hmj_buffers_t B) {
   for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, inc1, o); if (lane >= o) inc1 += v; }
   inc1 += tot0;
   const int total = __shfl_sync(0xffffffffu, inc1, 31);
+  const int gwarp = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;  // consecutive items (same group, similar cost) land on different SMs
+  if (blockIdx.x >= total) return;  // whole CTA idle (its first warp has the smallest item index)
+  stage_hulls(T, sx, sy, sz);
+  const int nwarp = gridDim.x * (blockDim.x >> 5);
   for (int item = gwarp; item < total; item += nwarp) {
-    // pair = number of pairs whose inclusive prefix is <= item
-    const int k = __popc(__ballot_sync(0xffffffffu, inc0 <= item)) + __popc(__ballot_sync(0xffffffffu, inc1 <= item));
-    const int excl = (k == 0) ? 0 : (k <= 32 ? __shfl_sync(0xffffffffu, inc0, (k - 1) & 31) : __shfl_sync(0xffffffffu, inc1, (k - 1) & 31));
-    const int cnt = (k < 32) ? __shfl_sync(0xffffffffu, c0, k & 31) : __shfl_sync(0xffffffffu, c1, k & 31);
+    // group = number of groups whose inclusive prefix is <= item
+    const int g = __popc(__ballot_sync(0xffffffffu, inc0 <= item)) + __popc(__ballot_sync(0xffffffffu, inc1 <= item));
+    const int excl = (g == 0) ? 0 : (g <= 32 ? __shfl_sync(0xffffffffu, inc0, (g - 1) & 31) : __shfl_sync(0xffffffffu, inc1, (g - 1) & 31));
+    const int cnt = (g < 32) ? __shfl_sync(0xffffffffu, c0, g & 31) : __shfl_sync(0xffffffffu, c1, g & 31);
     const int q0 = (item - excl) * 32;
     const int q = q0 + lane;
     const bool valid = q < cnt;
-    const int env = B.wq_env[(size_t)k * B.n + (valid ? q : q0)];  // idle lanes shadow the item's first query
-    if (T->m.pair_geom1[k] != 0) narrow_mesh_mesh(T, B, sx, sy, sz, k, env, valid);
-    else narrow_hfield(T, B, sx, sy, sz, k, env, valid);
+    const int2 task = B.wq_task[(size_t)T->group_base[g] * B.n + (valid ? q : q0)];  // idle lanes shadow the item's first task
+    if (g < HMJ_NMESH) {
+      const Hull h2 = {T->mesh_adr[g], T->mesh_npad[g]};
+      narrow_hfield(T, B, sx, sy, sz, h2, task, valid, lane);
+    } else {
+      narrow_mesh_mesh(T, B, sx, sy, sz, task, valid, lane);
+    }
   }
 }
 
@@ -679,13 +817,8 @@ void hmj_launch_collide(const hmj_tables_t* tab, hmj_buffers_t buf, cudaStream_t
     narrow_grid = sms * (per_sm > 0 ? per_sm : 1);
   }
   cudaMemsetAsync(buf.wq_count, 0, 64 * sizeof(int32_t), stream);
-  const int npad = (buf.n + 31) / 32 * 32;
+  const int npad = (buf.n + BROAD_THREADS - 1) / BROAD_THREADS * BROAD_THREADS;  // CTAs are pair-uniform
   const long long nthread = (long long)npad * HMJ_NPAIR;
-  k_broad<<<(int)((nthread + 255) / 256), 256, 0, stream>>>(tab, buf, npad);
-  // no more CTAs than work items in the worst case (every query of every pair active)
-  const long long max_items = (long long)HMJ_NPAIR * ((buf.n + 31) / 32);
-  const int wpc = NARROW_THREADS / 32;
-  int grid = (int)((max_items + wpc - 1) / wpc);
-  if (grid > narrow_grid) grid = narrow_grid;
-  k_narrow<<<grid, NARROW_THREADS, 0, stream>>>(tab, buf);
+  k_broad<<<(int)(nthread / BROAD_THREADS), BROAD_THREADS, 0, stream>>>(tab, buf, npad);
+  k_narrow<<<narrow_grid, NARROW_THREADS, 0, stream>>>(tab, buf);
 }

@@ -18,6 +18,7 @@
 #define HMJ_SLOT_DOUBLES 8                  /* dist, pos[3], normal[3], valid */
 #define HMJ_NFAC 375                        /* LDL update triples (unused by the dense path, kept for tables) */
 #define HMJ_MESH_PAD 4
+#define HMJ_NGROUP (HMJ_NMESH + 28)           /* narrowphase task groups: 7 hulls (hfield prisms) + 28 mesh-mesh pairs */
 #define HMJ_NVERT_SMEM (HMJ_MAXVERT + HMJ_NMESH * HMJ_MESH_PAD)
 
 #define HMJ_MINVAL 1e-15
@@ -41,6 +42,8 @@ struct hmj_tables_t {
   // collision
   int32_t pair_slot[HMJ_NPAIR + 1];  // first contact slot of each candidate pair
   int32_t slot_pair[HMJ_NSLOT];      // inverse map
+  int32_t pair_group[HMJ_NPAIR + 1]; // narrowphase task group of each pair (hfield pairs: mesh id of geom2)
+  int32_t group_base[64];            // first task of group g in wq_task, in units of N; group_base[NGROUP] = total
   // convex hull vertices, SoA float32, each mesh padded to a multiple of 4 with copies of its vertex 0;
   // mesh_adr[HMJ_NMESH] = total padded count (k_narrow stages them in shared memory as fp64)
   int32_t mesh_adr[HMJ_NMESH + 1];
@@ -85,8 +88,8 @@ struct hmj_buffers_t {
   double* qfrc_smooth;// [N][18]
   double* sens;       // [N][16]    torso xpos(3), xquat body1 (4), xpos body1 z, site z..., see SENS_*
   double* slots;      // [N][NSLOT][8]
-  int32_t* wq_count;  // [64]       narrowphase work list: queries per candidate pair (zeroed every step)
-  int32_t* wq_env;    // [NPAIR][N] environments whose pair k survived the broadphase
+  int32_t* wq_count;  // [64]       narrowphase tasks per group (zeroed every step)
+  int2* wq_task;      // [group_base[NGROUP] * N]  (env, packed pair / slot ordinal / prism position)
   // ---- outputs
   double* qacc;            // [N][18]
   double* qacc_smooth;     // [N][18]

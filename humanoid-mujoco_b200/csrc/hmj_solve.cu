@@ -20,6 +20,12 @@
 #include "hmj_dev.cuh"
 
 #define NV HMJ_NV
+#ifndef SOLVE_MIN_CTAS
+#define SOLVE_MIN_CTAS 8
+#endif
+#ifndef SOLVE_WARPS
+#define SOLVE_WARPS 1           /* one environment per CTA: a slow Newton solve never holds idle neighbours resident */
+#endif
 #define LD 19                   /* padded row stride of the dense 18x18 matrices */
 #define NROWREG 6               /* ceil(HMJ_MAXEFC / 32) rows per lane */
 #define NLIMMAX 24
@@ -48,29 +54,41 @@ struct SolveSmem {
 };
 
 // ---------------------------------------------------------------- dense helpers (warp cooperative)
-__device__ __forceinline__ void chol_factor(double* H, double* invd, const hmj_tables_t* T, int lane) {
+// In-register right-looking Cholesky: lane i holds row i of the lower triangle (fully unrolled, static
+// register indices); column j is scaled by rsqrt(d_j) computed redundantly on every lane and the rank-1
+// update pulls l_kj from lane k with one shuffle per (j, k) pair: 153 shuffles + 153 FMAs, no shared
+// memory traffic or barriers inside the factorisation.  Entries above the diagonal carry garbage.
+__device__ __noinline__ void chol_factor(double* H, double* invd, const hmj_tables_t*, int lane) {
+  const unsigned FULL = 0xffffffffu;
+  const int row = lane < NV ? lane : NV - 1;
+  double a[NV];
+  __syncwarp();
+#pragma unroll
+  for (int k = 0; k < NV; k++) a[k] = H[row * LD + k];
+#pragma unroll
   for (int j = 0; j < NV; j++) {
-    double dj = H[j * LD + j];
+    double dj = __shfl_sync(FULL, a[j], j);
     if (dj < HMJ_MINVAL) dj = HMJ_MINVAL;
-    const double ljj = sqrt(dj);
-    const double inv = 1.0 / ljj;
-    __syncwarp();
-    if (lane == 0) { H[j * LD + j] = ljj; invd[j] = inv; }
-    const int i = j + 1 + lane;
-    if (i < NV) H[i * LD + j] *= inv;
-    __syncwarp();
-    const int n1 = NV - 1 - j;
-    const int cnt = n1 * (n1 + 1) / 2;
-    for (int t = lane; t < cnt; t += 32) {
-      const int a = j + 1 + T->tri_i[t], b = j + 1 + T->tri_j[t];
-      H[a * LD + b] -= H[a * LD + j] * H[b * LD + j];
+    const double inv = rsqrt(dj);
+    const double lij = (lane == j) ? dj * inv : a[j] * inv;
+    a[j] = lij;
+    if (lane == j) invd[j] = inv;
+#pragma unroll
+    for (int k = j + 1; k < NV; k++) {
+      const double lkj = __shfl_sync(FULL, lij, k);
+      a[k] -= lij * lkj;
     }
-    __syncwarp();
   }
+  if (lane < NV) {
+#pragma unroll
+    for (int k = 0; k < NV; k++)
+      if (k <= lane) H[lane * LD + k] = a[k];
+  }
+  __syncwarp();
 }
 
 // x (one entry per lane, lanes >= NV ignored) <- H^-1 x with H = L L'
-__device__ __forceinline__ double chol_solve(const double* H, const double* invd, double x, int lane) {
+__device__ __noinline__ double chol_solve(const double* H, const double* invd, double x, int lane) {
   const unsigned FULL = 0xffffffffu;
   for (int k = 0; k < NV; k++) {
     const double xk = __shfl_sync(FULL, x, k) * invd[k];
@@ -170,12 +188,12 @@ __device__ __forceinline__ void make_frame(double* frame) {
 
 struct LsPnt { double alpha, cost, d0, d1; };
 
-__global__ void __launch_bounds__(32 * HMJ_WARPS_PER_CTA)
+__global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MIN_CTAS)
 k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
   extern __shared__ double smem_raw[];
   const int lane = threadIdx.x & 31;
   const int wib = threadIdx.x >> 5;
-  const int env = blockIdx.x * HMJ_WARPS_PER_CTA + wib;
+  const int env = blockIdx.x * SOLVE_WARPS + wib;
   if (env >= B.n) return;
   SolveSmem& S = reinterpret_cast<SolveSmem*>(smem_raw)[wib];
   const hmj_model_t& M = T->m;
@@ -687,11 +705,11 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
 
 void hmj_launch_solve(const hmj_tables_t* tab, hmj_buffers_t buf, int integrate, cudaStream_t stream) {
   static bool configured = false;
-  const size_t smem = sizeof(SolveSmem) * HMJ_WARPS_PER_CTA;
+  const size_t smem = sizeof(SolveSmem) * SOLVE_WARPS;
   if (!configured) {
     cudaFuncSetAttribute(k_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     configured = true;
   }
-  const int grid = (buf.n + HMJ_WARPS_PER_CTA - 1) / HMJ_WARPS_PER_CTA;
-  k_solve<<<grid, 32 * HMJ_WARPS_PER_CTA, smem, stream>>>(tab, buf, integrate);
+  const int grid = (buf.n + SOLVE_WARPS - 1) / SOLVE_WARPS;
+  k_solve<<<grid, 32 * SOLVE_WARPS, smem, stream>>>(tab, buf, integrate);
 }

@@ -359,8 +359,8 @@ static void find_penetr(const cobj_t* o1, const cobj_t* o2, supp_t* p, double to
 }
 
 /* ccdMPRPenetration: 0 = penetrating (depth, dir, pos filled), -1 = separated */
-static int mpr_penetration(const cobj_t* o1, const cobj_t* o2, double tol, int maxit,
-                           double* depth, double* dir, double* pos) {
+static int mpr_penetration_impl(const cobj_t* o1, const cobj_t* o2, double tol, int maxit,
+                                double* depth, double* dir, double* pos) {
   supp_t p[4];
   if (o1->d) o1->d->n_mpr += 1;
   int res = discover_portal(o1, o2, p);
@@ -380,6 +380,20 @@ static int mpr_penetration(const cobj_t* o1, const cobj_t* o2, double tol, int m
     find_penetr(o1, o2, p, tol, maxit, depth, dir, pos);
   }
   return 0;
+}
+
+/* statistics hook (single-threaded use): histogram of Minkowski support calls per MPR query, split by outcome */
+long long orc_mpr_hist[2][128];
+static int mpr_penetration(const cobj_t* o1, const cobj_t* o2, double tol, int maxit,
+                           double* depth, double* dir, double* pos) {
+  const double before = o2->d ? o2->d->n_support : 0;
+  const int res = mpr_penetration_impl(o1, o2, tol, maxit, depth, dir, pos);
+  if (o2->d) {
+    int n = (int)((o2->d->n_support - before) / 2);
+    if (n > 127) n = 127;
+    orc_mpr_hist[res == 0][n] += 1;
+  }
+  return res;
 }
 
 /* ------------------------------------------------------------------ contact helpers */
