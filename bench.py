@@ -271,16 +271,12 @@ def run_gpu(args):
                 "kernel_ms": kern, "algorithmic_bytes_per_env_step": BYTES_PER_ENV_STEP,
                 "note": "path is fp64-issue/latency bound, not HBM bound (SURVEY 8d): see the fp64 object"}
 
-    # ---- end to end through the public API: pinned host actions in, obs/reward/flags out, every step
+    # ---- end to end through the public API: host actions in, obs/reward/flags out, every step.
+    # BatchedHumanoidEnv.step writes the actions into the engine's pinned IO block (one H2D copy), runs the prologue,
+    # the physics step and the epilogue on the device, and reads the results from the same pinned block (one D2H copy).
     b.set_state(*settled)
-    env.time[:] = settled[2]
-    host_actions = torch.empty((min(ring_n, 64), n, 12), dtype=torch.float64).uniform_(-1, 1).pin_memory()
-    acts = host_actions.numpy()
-    pinned_out = {"obs": torch.zeros((n, 30), dtype=torch.float64).pin_memory(), "reward": torch.zeros(n, dtype=torch.float64).pin_memory(),
-                  "terminated": torch.zeros(n, dtype=torch.int32).pin_memory(), "truncated": torch.zeros(n, dtype=torch.int32).pin_memory(),
-                  "self_collision": torch.zeros(n, dtype=torch.int32).pin_memory(), "time": torch.zeros(n, dtype=torch.float64).pin_memory(),
-                  "root_quat": torch.zeros((n, 4), dtype=torch.float64).pin_memory()}
-    env._out = {k: v.numpy() for k, v in pinned_out.items()}
+    host_actions = np.random.default_rng(5 + rank).uniform(-1, 1, (min(ring_n, 64), n, 12))
+    acts = host_actions
     for s in range(W):
         env.step(acts[s % acts.shape[0]])
     barrier()
@@ -292,8 +288,8 @@ def run_gpu(args):
     t1 = time.perf_counter()
     e2e_s = max_over_ranks(t1 - t0)
     e2e_value = world * n * K / e2e_s
-    h2d = n * (12 * 8 + 4 + 6 * 8 + 12 * 8 + 12 * 8 + 31 * 8)
-    d2h = n * (30 * 8 + 8 + 3 * 4 + 8 + 4 * 8)
+    h2d = n * 12 * 8
+    d2h = n * ((30 + 1 + 1 + 4) * 8 + 3 * 4)
     clk = clocks.stop()
 
     line = None
@@ -308,7 +304,7 @@ def run_gpu(args):
                        "step": "one mj_step of all envs + obs/reward epilogue"},
             "roofline": roofline,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": 1e3 * e2e_s / K, "api": "BatchedHumanoidEnv.step (hmj_env_step C-ABI), pinned host buffers"},
+                    "ms_per_step": 1e3 * e2e_s / K, "api": "BatchedHumanoidEnv.step (hmj_env_step_fused C-ABI: pinned IO block, device-resident env bookkeeping)"},
             "gpu_launches": int(launches), "clocks": clk,
             "contacts": {"mean_ncon": float(ncon.mean()), "max_ncon": int(ncon.max()), "mean_nefc": float(nefc.mean()),
                          "max_nefc": int(nefc.max()), "mean_newton_iter": float(niter.mean()), "envs_with_bad_status": status_bad},

@@ -13,7 +13,8 @@ class HmjError(RuntimeError):
 
 
 def lib_path() -> str:
-    return os.path.join(_HERE, "lib", "libhmj_b200.so")
+    # HMJ_B200_LIB: developer override to A/B-test an alternative build of the same engine
+    return os.environ.get("HMJ_B200_LIB") or os.path.join(_HERE, "lib", "libhmj_b200.so")
 
 
 def load_library() -> C.CDLL:
@@ -56,6 +57,8 @@ def load_library() -> C.CDLL:
     lib.hmj_env_obs_reward.argtypes = [vp, dp, dp, dp, C.c_double, dp, dp, vp, vp, vp]
     lib.hmj_env_obs_reward_dev.argtypes = [vp, dp, dp, dp, C.c_double, dp, dp, vp, vp, vp]
     lib.hmj_env_step.argtypes = [vp, dp, vp, dp, dp, dp, dp, C.c_double, C.c_int, dp, dp, vp, vp, vp, dp, dp]
+    lib.hmj_env_io.argtypes = [vp] + [C.POINTER(vp)] * 9
+    lib.hmj_env_step_fused.argtypes = [vp, C.c_int, C.c_int, C.c_double, C.c_double, C.c_ulonglong, C.c_int]
     lib.hmj_batch_profile.argtypes = [vp, C.c_int]
     lib.hmj_batch_profile_read.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double),
                                            C.POINTER(C.c_int)]

@@ -59,7 +59,13 @@ _ARRAY_SHAPES = {
     "qM": (DEFINES["HMJ_NM"],), "qfrc_smooth": (NV,), "qacc_smooth": (NV,), "qacc": (NV,), "qfrc_constraint": (NV,),
     "sens": (16,), "residual": (DEFINES["HMJ_NRESIDUAL"],), "cost_sum": (), "cost_last": (), "trace": (3,), "returns": (),
 }
-_INT_ARRAYS = {"ncon", "nefc", "niter", "status", "xfrc_body"}
+_ARRAY_SHAPES.update({
+    "env_act_noise": (NU,), "env_obs_noise": (31,), "env_prev_action": (NU,), "env_latest_action": (NU,),
+    "env_force_sched": (5,), "env_torso_quat": (4,),
+})
+_INT_ARRAYS = {"ncon", "nefc", "niter", "status", "xfrc_body", "env_act_delay", "env_act_count", "env_obs_count",
+               "env_force_body", "env_force_draws"}
+_INT_SHAPES = {"env_obs_delay": (3,)}
 
 
 def load_model(path: str = MODEL_PATH) -> np.ndarray:
@@ -165,14 +171,23 @@ class HumanoidBatch:
     def get(self, name: str) -> np.ndarray:
         if name in _INT_ARRAYS:
             out = np.zeros(self.n, dtype=np.int32)
+        elif name in _INT_SHAPES:
+            out = np.zeros((self.n,) + _INT_SHAPES[name], dtype=np.int32)
         else:
             out = np.zeros((self.n,) + _ARRAY_SHAPES[name])
+        check(self.lib.hmj_batch_get_array(self._h, name.encode(), _p(out), out.nbytes))
+        return out
+
+    def get_raw(self, name: str, dtype, shape) -> np.ndarray:
+        out = np.zeros(shape, dtype=dtype)
         check(self.lib.hmj_batch_get_array(self._h, name.encode(), _p(out), out.nbytes))
         return out
 
     def set(self, name: str, value):
         if name in _INT_ARRAYS:
             a = np.ascontiguousarray(np.broadcast_to(np.asarray(value, dtype=np.int32), (self.n,)))
+        elif name in _INT_SHAPES:
+            a = np.ascontiguousarray(np.broadcast_to(np.asarray(value, dtype=np.int32), (self.n,) + _INT_SHAPES[name]))
         else:
             a = self._f64(value, _ARRAY_SHAPES[name])
         check(self.lib.hmj_batch_set_array(self._h, name.encode(), _p(a), a.nbytes))
@@ -220,6 +235,28 @@ class HumanoidBatch:
             _p(out["obs"]), _p(out["reward"]), _p(out["terminated"]), _p(out["truncated"]), _p(out["self_collision"]),
             _p(out["time"]), _p(out["root_quat"])))
         return out
+
+    def env_io(self):
+        """numpy views of the pinned host IO block of the fused control step (hmj_env_io)."""
+        if getattr(self, "_io", None) is None:
+            ptrs = [C.c_void_p() for _ in range(9)]
+            check(self.lib.hmj_env_io(self._h, *[C.byref(p) for p in ptrs]))
+            n = self.n
+            spec = [("action", np.float64, (n, NU)), ("mask", np.int32, (n,)), ("obs", np.float64, (n, 30)),
+                    ("reward", np.float64, (n,)), ("time", np.float64, (n,)), ("torso_quat", np.float64, (n, 4)),
+                    ("terminated", np.int32, (n,)), ("truncated", np.int32, (n,)), ("self_collision", np.int32, (n,))]
+            io = {}
+            for p, (name, dt, shape) in zip(ptrs, spec):
+                cnt = int(np.prod(shape))
+                ct = C.c_double if dt is np.float64 else C.c_int32
+                io[name] = np.ctypeslib.as_array((ct * cnt).from_address(p.value)).reshape(shape)
+            self._io = io
+        return self._io
+
+    def env_step_fused(self, has_action: bool, has_mask: bool, rf: float, max_sim_time: float, seed: int, nsteps: int = 1):
+        """CPUEnv.step with device-resident bookkeeping (hmj_env_step_fused); inputs/outputs live in env_io()."""
+        mst = 1e300 if not np.isfinite(max_sim_time) else float(max_sim_time)
+        check(self.lib.hmj_env_step_fused(self._h, int(has_action), int(has_mask), float(rf), mst, int(seed) & (2**64 - 1), int(nsteps)))
 
     # ---- per-kernel timing
     def profile(self, enable: bool):

@@ -48,6 +48,11 @@ struct hmj_batch_ {
   int rec_cap = 0;
   // env scratch
   double* env_stage = nullptr; size_t env_stage_cap = 0;
+  // device-resident CPUEnv bookkeeping + one pinned host / device IO block for the fused control step
+  hmj_envstate_t env{};
+  char* io_host = nullptr;   // pinned: [in: action N*12 f64 | mask N i32][out: obs N*30, reward N, time N, quat N*4 f64 | term, trunc, selfc N i32]
+  char* io_dev = nullptr;
+  size_t io_in_bytes = 0, io_out_bytes = 0;
   int launches = 0;
   // per-kernel CUDA-event profiling (hmj_batch_profile): events bracket every launch of a step
   bool profile = false;
@@ -149,6 +154,13 @@ static void build_tables(const hmj_model_t* m, hmj_tables_t* t) {
     int npad = (nv + HMJ_MESH_PAD - 1) / HMJ_MESH_PAD * HMJ_MESH_PAD;
     t->mesh_adr[k] = adr;
     t->mesh_npad[k] = npad;
+    for (int q = 0; q < 3; q++) { t->mesh_lo[k][q] = 1e30; t->mesh_hi[k][q] = -1e30; }
+    for (int i = 0; i < nv; i++)
+      for (int q = 0; q < 3; q++) {
+        const double c = m->mesh_vert[va + i][q];
+        if (c < t->mesh_lo[k][q]) t->mesh_lo[k][q] = c;
+        if (c > t->mesh_hi[k][q]) t->mesh_hi[k][q] = c;
+      }
     for (int i = 0; i < npad; i++) {
       int src = i < nv ? i : 0;
       t->vx[adr + i] = m->mesh_vert[va + src][0];
@@ -186,6 +198,7 @@ extern "C" void hmj_batch_destroy(hmj_batch_t* b) {
   if (b->stream) cudaStreamSynchronize(b->stream);
   for (void* p : b->allocs) cudaFree(p);
   for (cudaEvent_t e : b->prof_events) cudaEventDestroy(e);
+  if (b->io_host) cudaFreeHost(b->io_host);
   if (b->tab_dev) cudaFree(b->tab_dev);
   if (b->task_dev) cudaFree(b->task_dev);
   if (b->stream) cudaStreamDestroy(b->stream);
@@ -262,6 +275,32 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
       hmj_batch_destroy(b);
       return rc;
     }
+  }
+  {  // CPUEnv bookkeeping arrays (named, so the host side sets them at reset with hmj_batch_set_array)
+    int rc = 0;
+#define EALLOC(name, field, count) if (!rc) rc = alloc_array(b, name, &b->env.field, (size_t)(count))
+    EALLOC("env_act_noise", act_noise, N * HMJ_NU);
+    EALLOC("env_obs_noise", obs_noise, N * 31);
+    EALLOC("env_act_delay", act_delay, N);
+    EALLOC("env_obs_delay", obs_delay, N * 3);
+    EALLOC("env_act_count", act_count, N);
+    EALLOC("env_obs_count", obs_count, N);
+    EALLOC("env_act_hist", act_hist, N * HMJ_ENV_HIST * HMJ_NU);
+    EALLOC("env_obs_hist", obs_hist, N * HMJ_ENV_HIST * 30);
+    EALLOC("env_prev_action", prev_action, N * HMJ_NU);
+    EALLOC("env_latest_action", latest_action, N * HMJ_NU);
+    EALLOC("env_force_sched", force_sched, N * 5);
+    EALLOC("env_force_body", force_body, N);
+    EALLOC("env_force_draws", force_draws, N);
+    EALLOC("env_torso_quat", torso_quat, N * 4);
+#undef EALLOC
+    b->io_in_bytes = N * HMJ_NU * 8 + N * 4;
+    b->io_in_bytes = (b->io_in_bytes + 63) / 64 * 64;
+    b->io_out_bytes = N * (30 + 1 + 1 + 4) * 8 + 3 * N * 4;
+    if (!rc && cudaHostAlloc((void**)&b->io_host, b->io_in_bytes + b->io_out_bytes, cudaHostAllocDefault) != cudaSuccess)
+      rc = fail(HMJ_ERR_CUDA, "cudaHostAlloc failed%s");
+    if (!rc) { memset(b->io_host, 0, b->io_in_bytes + b->io_out_bytes); rc = alloc_array(b, nullptr, &b->io_dev, b->io_in_bytes + b->io_out_bytes); }
+    if (rc) { hmj_batch_destroy(b); return rc; }
   }
   // default params and state (qpos0) for every env
   {
@@ -592,6 +631,60 @@ extern "C" int hmj_env_step(hmj_batch_t* b, const double* ctrl, const int32_t* x
     return rc;
   if (root_quat_out)
     CK(cudaMemcpy2DAsync(root_quat_out, 4 * 8, b->buf.sens + SENS_ROOT_XQUAT, SENS_NUM * 8, 4 * 8, N, cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  CK(cudaGetLastError());
+  return HMJ_OK;
+}
+
+// Pinned host IO block of the fused control step (views for the host language; valid until hmj_batch_destroy).
+extern "C" int hmj_env_io(hmj_batch_t* b, double** action, int32_t** mask, double** obs, double** reward, double** time,
+                          double** torso_quat, int32_t** terminated, int32_t** truncated, int32_t** self_collision) {
+  if (!b || !b->io_host) return fail(HMJ_ERR_ARG, "null batch%s");
+  const size_t N = b->n;
+  char* in = b->io_host;
+  char* out = b->io_host + b->io_in_bytes;
+  if (action) *action = (double*)in;
+  if (mask) *mask = (int32_t*)(in + N * HMJ_NU * 8);
+  double* o = (double*)out;
+  if (obs) *obs = o;
+  if (reward) *reward = o + N * 30;
+  if (time) *time = o + N * 31;
+  if (torso_quat) *torso_quat = o + N * 32;
+  int32_t* f = (int32_t*)(o + N * 36);
+  if (terminated) *terminated = f;
+  if (truncated) *truncated = f + N;
+  if (self_collision) *self_collision = f + 2 * N;
+  return HMJ_OK;
+}
+
+// CPUEnv.step (cpu_env.py:676-693) with ALL per-step bookkeeping on the device: action noise + delay FIFO, push
+// scheduler, nsteps x mj_step, observation / reward, observation delay FIFOs.  Inputs are read from / results
+// written to the pinned IO block of hmj_env_io: one H2D copy, one D2H copy, one synchronisation per control step.
+// has_action == 0 replays data.ctrl (CPUEnv.step(None)); has_mask != 0 restricts the bookkeeping to mask[env] != 0
+// (physics is lock-step for everyone; CPUEnv.reset uses this for its first-step rejection loop).
+extern "C" int hmj_env_step_fused(hmj_batch_t* b, int has_action, int has_mask, double rf, double max_sim_time,
+                                  unsigned long long seed, int nsteps) {
+  if (!b) return fail(HMJ_ERR_ARG, "bad argument to env_step_fused%s");  // nsteps < 0: observation only (no prologue, no physics)
+  CK(cudaSetDevice(b->device));
+  const size_t N = b->n;
+  double* d_action = (double*)b->io_dev;
+  int32_t* d_mask = (int32_t*)(b->io_dev + N * HMJ_NU * 8);
+  double* d_out = (double*)(b->io_dev + b->io_in_bytes);
+  double* d_obs = d_out;
+  double* d_rew = d_out + N * 30;
+  double* d_time = d_out + N * 31;
+  double* d_quat = d_out + N * 32;
+  int32_t* d_flags = (int32_t*)(d_out + N * 36);
+  if (has_action || has_mask)
+    CK(cudaMemcpyAsync(b->io_dev, b->io_host, has_mask ? N * HMJ_NU * 8 + N * 4 : N * HMJ_NU * 8, cudaMemcpyHostToDevice, b->stream));
+  const int32_t* mask = has_mask ? d_mask : nullptr;
+  if (nsteps >= 0) hmj_launch_env_pre(b->buf, b->env, has_action ? d_action : nullptr, mask, rf, seed, b->stream);
+  for (int s = 0; s < nsteps; s++) enqueue_step(b, 1);
+  hmj_launch_env_obs_reward(b->tab_dev, b->buf, b->env.prev_action, b->env.latest_action, b->env.obs_noise, max_sim_time, d_obs,
+                            d_rew, d_flags, d_flags + N, d_flags + 2 * N, b->stream);
+  hmj_launch_env_post(b->buf, b->env, mask, d_obs, d_time, d_quat, b->stream);
+  b->launches += 3;
+  CK(cudaMemcpyAsync(b->io_host + b->io_in_bytes, d_out, b->io_out_bytes, cudaMemcpyDeviceToHost, b->stream));
   CK(cudaStreamSynchronize(b->stream));
   CK(cudaGetLastError());
   return HMJ_OK;

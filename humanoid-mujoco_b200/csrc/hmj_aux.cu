@@ -181,6 +181,95 @@ void hmj_launch_env_obs_reward(const hmj_tables_t* tab, hmj_buffers_t buf, const
                                                             terminated, truncated, self_collision);
 }
 
+// ------------------------------------------------------------------ CPUEnv prologue / delay FIFOs on the device
+// CPUEnv._apply_action (cpu_env.py:656-674) + _apply_external_forces (:618-654), one thread per environment.
+__global__ void k_env_pre(hmj_buffers_t B, hmj_envstate_t E, const double* __restrict__ action, const int32_t* __restrict__ mask,
+                          double rf, unsigned long long seed) {
+  const int env = blockIdx.x * blockDim.x + threadIdx.x;
+  if (env >= B.n || (mask && !mask[env])) return;
+  // ---- action: + constant noise, delay FIFO, NO clipping (cpu_env.py:670-671); action == NULL re-sends data.ctrl
+  const int cnt = E.act_count[env];
+  const int d = E.act_delay[env];
+  double* hist = E.act_hist + (size_t)env * HMJ_ENV_HIST * HMJ_NU;
+  double* ctrl = B.ctrl + (size_t)env * HMJ_NU;
+  const int slot = cnt % HMJ_ENV_HIST;
+  const int src = ((cnt - d) % HMJ_ENV_HIST + HMJ_ENV_HIST) % HMJ_ENV_HIST;
+  for (int a = 0; a < HMJ_NU; a++) {
+    const double v = action ? action[(size_t)env * HMJ_NU + a] + E.act_noise[(size_t)env * HMJ_NU + a] : ctrl[a];
+    hist[slot * HMJ_NU + a] = v;
+  }
+  for (int a = 0; a < HMJ_NU; a++) {
+    const double take = (cnt >= d) ? hist[src * HMJ_NU + a] : 0.0;
+    ctrl[a] = take;
+    E.prev_action[(size_t)env * HMJ_NU + a] = E.latest_action[(size_t)env * HMJ_NU + a];
+    E.latest_action[(size_t)env * HMJ_NU + a] = take;
+  }
+  E.act_count[env] = cnt + 1;
+  // ---- random pushes: every U(1,3) s, for U(.05,.15) s, U(5,15) rf N along a random horizontal direction on a random body
+  double* fs = E.force_sched + (size_t)env * 5;
+  double* xf = B.xfrc + (size_t)env * 6;
+  const double t = B.time[env];
+  if (t >= fs[0] + fs[1]) {
+    const uint32_t c = (uint32_t)E.force_draws[env] * 8u;
+    // contraction-free (__dmul_rn / __dadd_rn): the numpy restatement in env.py must see the same bits
+    fs[0] = __dadd_rn(t, __dadd_rn(1.0, __dmul_rn(2.0, hmj_rand_u01(seed, env, c + 0))));
+    fs[1] = __dadd_rn(0.05, __dmul_rn(0.10, hmj_rand_u01(seed, env, c + 1)));
+    fs[2] = __dadd_rn(5.0 * rf, __dmul_rn(15.0 * rf - 5.0 * rf, hmj_rand_u01(seed, env, c + 2)));
+    double dx = __dadd_rn(-1.0, __dmul_rn(2.0, hmj_rand_u01(seed, env, c + 3)));
+    double dy = __dadd_rn(-1.0, __dmul_rn(2.0, hmj_rand_u01(seed, env, c + 4)));
+    const double nrm = sqrt(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
+    if (nrm == 0) { dx = 1.0; dy = 0.0; } else { dx /= nrm; dy /= nrm; }
+    fs[3] = dx; fs[4] = dy;
+    xf[0] = 0.0; xf[1] = 0.0;
+    int body = 1 + (int)(14.0 * hmj_rand_u01(seed, env, c + 5));
+    if (body > 14) body = 14;
+    E.force_body[env] = body;
+    E.force_draws[env] += 1;
+  }
+  if (t > fs[0] && t < fs[0] + fs[1]) { xf[0] = fs[3] * fs[2]; xf[1] = fs[4] * fs[2]; }
+  B.xfrc_body[env] = E.force_body[env];
+}
+
+// Observation delay FIFOs of CPUEnv._get_obs (cpu_env.py:528-547): `obs` holds the undelayed observation on entry,
+// the delayed one on exit; also CPUEnv.torso_quat (:516).
+__global__ void k_env_post(hmj_buffers_t B, hmj_envstate_t E, const int32_t* __restrict__ mask, double* __restrict__ obs,
+                           double* __restrict__ time_out, double* __restrict__ quat_out) {
+  const int env = blockIdx.x * blockDim.x + threadIdx.x;
+  if (env >= B.n) return;
+  if (time_out) time_out[env] = B.time[env];
+  if (mask && !mask[env]) {
+    if (quat_out) for (int k = 0; k < 4; k++) quat_out[(size_t)env * 4 + k] = E.torso_quat[(size_t)env * 4 + k];
+    return;
+  }
+  const double* sens = B.sens + (size_t)env * SENS_NUM;
+  for (int k = 0; k < 4; k++) {
+    const double v = sens[SENS_ROOT_XQUAT + k] + E.obs_noise[(size_t)env * 31 + 27 + k];
+    E.torso_quat[(size_t)env * 4 + k] = v;
+    if (quat_out) quat_out[(size_t)env * 4 + k] = v;
+  }
+  const int cnt = E.obs_count[env];
+  double* hist = E.obs_hist + (size_t)env * HMJ_ENV_HIST * 30;
+  double* o = obs + (size_t)env * 30;
+  const int slot = cnt % HMJ_ENV_HIST;
+  for (int k = 0; k < 30; k++) hist[slot * 30 + k] = o[k];
+  const int lo[3] = {0, 24, 27}, hi[3] = {24, 27, 30};
+  for (int g = 0; g < 3; g++) {
+    const int d = E.obs_delay[(size_t)env * 3 + g];
+    const int src = ((cnt - d) % HMJ_ENV_HIST + HMJ_ENV_HIST) % HMJ_ENV_HIST;
+    for (int k = lo[g]; k < hi[g]; k++) o[k] = (cnt >= d) ? hist[src * 30 + k] : ((k == 29) ? -1.0 : 0.0);
+  }
+  E.obs_count[env] = cnt + 1;
+}
+
+void hmj_launch_env_pre(hmj_buffers_t buf, hmj_envstate_t env, const double* action, const int32_t* mask, double rf,
+                        unsigned long long seed, cudaStream_t stream) {
+  k_env_pre<<<(buf.n + 127) / 128, 128, 0, stream>>>(buf, env, action, mask, rf, seed);
+}
+void hmj_launch_env_post(hmj_buffers_t buf, hmj_envstate_t env, const int32_t* mask, double* obs, double* time_out, double* quat_out,
+                         cudaStream_t stream) {
+  k_env_post<<<(buf.n + 127) / 128, 128, 0, stream>>>(buf, env, mask, obs, time_out, quat_out);
+}
+
 // ------------------------------------------------------------------ FP64 FMA peak (roofline denominator)
 // MEASURED_PEAKS.json carries no FP64 figure; this micro-benchmark measures the DFMA issue peak of the device:
 // 8 independent FMA chains per thread, 4096 iterations, 148 x 16 CTAs of 256 threads.

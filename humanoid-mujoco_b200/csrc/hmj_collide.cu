@@ -125,44 +125,72 @@ __device__ __forceinline__ void mesh_support(const double* __restrict__ sx, cons
   out[2] = (mat[6] * p0 + mat[7] * p1 + mat[8] * p2) + f.pos[2];
 }
 
-// Cooperative variant for sparsely populated warps: all 32 lanes scan the hull for lane `src`'s direction
-// (lane l takes vertices l, l + 32, ...; xor-butterfly arg-max with lowest-index tie-break == the serial
-// "first maximum").  Only lane `src` receives `out`.  Bit-identical to mesh_support.
+// Cooperative variant for sparsely populated warps: all 32 lanes scan the hull for the directions of up to
+// four still-active lanes at once (lane l takes vertices l, l + 32, ...; four independent arg-max chains keep
+// the FP64 pipe and the shuffle unit busy; xor-butterfly with lowest-index tie-break == the serial "first
+// maximum").  Only the source lanes receive `out`.  Bit-identical to mesh_support.
+#define COOP_G 4
 __device__ __forceinline__ void mesh_support_coop(const double* __restrict__ sx, const double* __restrict__ sy,
                                                   const double* __restrict__ sz, Hull h, const Frame& f, const double* dir,
-                                                  double* out, int src, int lane) {
+                                                  double* out, const int* src, int lane) {
   const unsigned FULL = 0xffffffffu;
   const double* mat = f.mat;
-  double ld0 = mat[0] * dir[0] + mat[3] * dir[1] + mat[6] * dir[2];
-  double ld1 = mat[1] * dir[0] + mat[4] * dir[1] + mat[7] * dir[2];
-  double ld2 = mat[2] * dir[0] + mat[5] * dir[1] + mat[8] * dir[2];
-  ld0 = __shfl_sync(FULL, ld0, src);
-  ld1 = __shfl_sync(FULL, ld1, src);
-  ld2 = __shfl_sync(FULL, ld2, src);
-  double best = -HMJ_MAXVAL;
-  int ibest = 0x7fffffff;
+  const double my0 = mat[0] * dir[0] + mat[3] * dir[1] + mat[6] * dir[2];
+  const double my1 = mat[1] * dir[0] + mat[4] * dir[1] + mat[7] * dir[2];
+  const double my2 = mat[2] * dir[0] + mat[5] * dir[1] + mat[8] * dir[2];
+  double ld0[COOP_G], ld1[COOP_G], ld2[COOP_G], best[COOP_G];
+  int ibest[COOP_G];
+#pragma unroll
+  for (int g = 0; g < COOP_G; g++) {
+    ld0[g] = __shfl_sync(FULL, my0, src[g]);
+    ld1[g] = __shfl_sync(FULL, my1, src[g]);
+    ld2[g] = __shfl_sync(FULL, my2, src[g]);
+    best[g] = -HMJ_MAXVAL;
+    ibest[g] = 0x7fffffff;
+  }
   for (int i = lane; i < h.n4; i += 32) {
-    const double vd = ld0 * sx[h.base + i] + ld1 * sy[h.base + i] + ld2 * sz[h.base + i];
-    if (vd > best) { best = vd; ibest = i; }
+    const double x = sx[h.base + i], y = sy[h.base + i], z = sz[h.base + i];
+#pragma unroll
+    for (int g = 0; g < COOP_G; g++) {
+      const double vd = ld0[g] * x + ld1[g] * y + ld2[g] * z;
+      if (vd > best[g]) { best[g] = vd; ibest[g] = i; }
+    }
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
-    const double ob = __shfl_xor_sync(FULL, best, o);
-    const int oi = __shfl_xor_sync(FULL, ibest, o);
-    if (ob > best || (ob == best && oi < ibest)) { best = ob; ibest = oi; }
+#pragma unroll
+    for (int g = 0; g < COOP_G; g++) {
+      const double ob = __shfl_xor_sync(FULL, best[g], o);
+      const int oi = __shfl_xor_sync(FULL, ibest[g], o);
+      if (ob > best[g] || (ob == best[g] && oi < ibest[g])) { best[g] = ob; ibest[g] = oi; }
+    }
   }
-  if (ibest == 0x7fffffff) ibest = 0;
-  if (lane == src) {
-    const double p0 = sx[h.base + ibest], p1 = sy[h.base + ibest], p2 = sz[h.base + ibest];
+  int mine = -1;
+#pragma unroll
+  for (int g = 0; g < COOP_G; g++)
+    if (lane == src[g]) mine = ibest[g];
+  if (mine >= 0) {
+    if (mine == 0x7fffffff) mine = 0;
+    const double p0 = sx[h.base + mine], p1 = sy[h.base + mine], p2 = sz[h.base + mine];
     out[0] = (mat[0] * p0 + mat[1] * p1 + mat[2] * p2) + f.pos[0];
     out[1] = (mat[3] * p0 + mat[4] * p1 + mat[5] * p2) + f.pos[1];
     out[2] = (mat[6] * p0 + mat[7] * p1 + mat[8] * p2) + f.pos[2];
   }
 }
 
-// Lane count below which the cooperative scan is cheaper than the lane-serial one for a hull of n vertices:
-// serial ~ 12 n issue cycles per trip for the whole warp, cooperative ~ (12 n / 32 + 70) per active lane.
-__device__ __forceinline__ int coop_threshold(int n) { return (12 * n) / ((12 * n) / 32 + 70) + 1; }
+// the next (up to) COOP_G active lanes of `mm`, removed from it; short groups repeat their last lane
+__device__ __forceinline__ void coop_take(unsigned& mm, int* src) {
+#pragma unroll
+  for (int g = 0; g < COOP_G; g++) {
+    if (mm) { src[g] = __ffs(mm) - 1; mm &= mm - 1; }
+    else src[g] = src[g - (g > 0)];
+  }
+}
+
+// Lane count below which the cooperative scan is cheaper than the lane-serial one for hull(s) of n vertices.
+// Both are latency bound at the occupancy this kernel runs at: a serial trip costs ~25 n cycles for the whole
+// warp, a cooperative pass ~(n + 700) cycles per group of COOP_G lanes (measured, profiles/).
+__device__ __forceinline__ int coop_threshold(int n) { return (COOP_G * 25 * n) / (n + 700) + 1; }
 
 // Axis-aligned bounding box of a hull in the frame `f` == the six obj_support(+-e_r) calls of
 // mjc_ConvexHField (see the header comment for why min/max of three dot products is bit-identical).
@@ -565,7 +593,34 @@ k_broad(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int npad) {
   if (g1 != 0) {
     const double dif0 = gx[g1 * 3] - gx[g2 * 3], dif1 = gx[g1 * 3 + 1] - gx[g2 * 3 + 1], dif2 = gx[g1 * 3 + 2] - gx[g2 * 3 + 2];
     const double bound = M.geom_rbound[g1] + M.geom_rbound[g2];
-    const bool hit = in && !(dif0 * dif0 + dif1 * dif1 + dif2 * dif2 > bound * bound);
+    bool hit = in && !(dif0 * dif0 + dif1 * dif1 + dif2 * dif2 > bound * bound);
+    if (hit) {
+      // Conservative pre-screen of ccdMPRPenetration's first exit (dot(support(dir), dir) <= 0 along the
+      // centre line): the hulls' local bounding boxes bound both supports, so a box gap larger than the
+      // rounding noise proves the exact test fails too.  Never rejects a query MPR would continue.
+      const double* gm = B.geom_xmat + (size_t)env * HMJ_NGEOM * 9;
+      const double n2 = dif0 * dif0 + dif1 * dif1 + dif2 * dif2;
+      if (n2 > 1e-12) {
+        const double inv = rsqrt(n2);
+        const double d[3] = {-dif0 * inv, -dif1 * inv, -dif2 * inv};  // from geom1's centre towards geom2's
+        const double* m1 = gm + g1 * 9;
+        const double* m2 = gm + g2 * 9;
+        const double* lo1 = T->mesh_lo[M.geom_meshid[g1]];
+        const double* hi1 = T->mesh_hi[M.geom_meshid[g1]];
+        const double* lo2 = T->mesh_lo[M.geom_meshid[g2]];
+        const double* hi2 = T->mesh_hi[M.geom_meshid[g2]];
+        double max1 = d[0] * gx[g1 * 3] + d[1] * gx[g1 * 3 + 1] + d[2] * gx[g1 * 3 + 2];
+        double min2 = d[0] * gx[g2 * 3] + d[1] * gx[g2 * 3 + 1] + d[2] * gx[g2 * 3 + 2];
+#pragma unroll
+        for (int q = 0; q < 3; q++) {
+          const double l1 = m1[q] * d[0] + m1[3 + q] * d[1] + m1[6 + q] * d[2];
+          const double l2 = m2[q] * d[0] + m2[3 + q] * d[1] + m2[6 + q] * d[2];
+          max1 += fmax(l1 * lo1[q], l1 * hi1[q]);
+          min2 += fmin(l2 * lo2[q], l2 * hi2[q]);
+        }
+        if (max1 - min2 < -1e-9) hit = false;
+      }
+    }
     push_tasks(T, B, T->pair_group[k], hit, env, pack_task(k, 0, 0, 0, 0), lane);
     return;
   }
@@ -679,8 +734,9 @@ __device__ __forceinline__ void narrow_mesh_mesh(const hmj_tables_t* __restrict_
       mesh_support(sx, sy, sz, h1, f1, m.dir, s.v1);
       mesh_support(sx, sy, sz, h2, f2, nd, s.v2);
     } else {
-      for (unsigned mm = am; mm; mm &= mm - 1) {
-        const int src = __ffs(mm) - 1;
+      for (unsigned mm = am; mm;) {
+        int src[COOP_G];
+        coop_take(mm, src);
         mesh_support_coop(sx, sy, sz, h1, f1, m.dir, s.v1, src, lane);
         mesh_support_coop(sx, sy, sz, h2, f2, nd, s.v2, src, lane);
       }
@@ -739,8 +795,11 @@ __device__ __forceinline__ void narrow_hfield(const hmj_tables_t* __restrict__ T
     if (__popc(am) >= thr) {
       mesh_support(sx, sy, sz, h2, f2, nd, s.v2);
     } else {
-      for (unsigned mm = am; mm; mm &= mm - 1)
-        mesh_support_coop(sx, sy, sz, h2, f2, nd, s.v2, __ffs(mm) - 1, lane);
+      for (unsigned mm = am; mm;) {
+        int src[COOP_G];
+        coop_take(mm, src);
+        mesh_support_coop(sx, sy, sz, h2, f2, nd, s.v2, src, lane);
+      }
     }
     c_sub2(s.v, s.v1, s.v2);
     if (active) {

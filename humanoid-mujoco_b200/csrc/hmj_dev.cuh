@@ -51,6 +51,8 @@ struct hmj_tables_t {
   float vx[HMJ_MAXVERT + HMJ_NMESH * HMJ_MESH_PAD];
   float vy[HMJ_MAXVERT + HMJ_NMESH * HMJ_MESH_PAD];
   float vz[HMJ_MAXVERT + HMJ_NMESH * HMJ_MESH_PAD];
+  double mesh_lo[HMJ_NMESH + 1][3];  // local bounding box of each hull (exact min / max of its vertices)
+  double mesh_hi[HMJ_NMESH + 1][3];
   // lower-triangle index maps for the 18x18 dense routines
   int32_t tri_i[HMJ_NV * (HMJ_NV + 1) / 2];
   int32_t tri_j[HMJ_NV * (HMJ_NV + 1) / 2];
@@ -105,6 +107,40 @@ struct hmj_buffers_t {
   double* cost_last;  // [N]     CostValue of the latest forward pass
   double* trace;      // [N][3]
 };
+
+// Device-resident CPUEnv bookkeeping (simulation/cpu_env.py:135-187 delays, :618-674 pushes / action path):
+// the per-step host logic of CPUEnv.step lives here so a control step is H2D(actions) -> kernels -> D2H(results).
+#define HMJ_ENV_HIST 26  /* delay FIFO depth: MAX_DELAY / TIMESTEP + 1 */
+struct hmj_envstate_t {
+  double* act_noise;     // [N][12]  per-episode constant action noise (the JAX key is never split, cpu_env.py:664)
+  double* obs_noise;     // [N][31]  q12 qd12 gyro3 quat4
+  int32_t* act_delay;    // [N]      action delay in steps
+  int32_t* obs_delay;    // [N][3]   joint (angles+velocities) / gyro / gravity delays in steps
+  int32_t* act_count;    // [N]
+  int32_t* obs_count;    // [N]
+  double* act_hist;      // [N][HIST][12]
+  double* obs_hist;      // [N][HIST][30]
+  double* prev_action;   // [N][12]
+  double* latest_action; // [N][12]
+  double* force_sched;   // [N][5]   start, duration, magnitude, dir x, dir y
+  int32_t* force_body;   // [N]
+  int32_t* force_draws;  // [N]      renewals so far (counter of the per-env random stream)
+  double* torso_quat;    // [N][4]   noisy root quaternion (CPUEnv.torso_quat, read by controllers/mpc_in_env.py:25)
+};
+
+// Counter-based uniform in [0, 1): splitmix64 of (seed, env, counter).  Restated in numpy by env.py for the
+// host mirror; replaces the reference's unseeded Python `random` stream (unpinned).
+__host__ __device__ __forceinline__ uint64_t hmj_splitmix64(uint64_t x) {
+  x += 0x9E3779B97F4A7C15ull;
+  uint64_t z = x;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+__host__ __device__ __forceinline__ double hmj_rand_u01(uint64_t seed, uint32_t env, uint32_t counter) {
+  const uint64_t h = hmj_splitmix64(seed ^ hmj_splitmix64(((uint64_t)env << 32) | counter));
+  return (double)(h >> 11) * (1.0 / 9007199254740992.0);
+}
 
 #define SENS_TORSO_XPOS 0   /* xpos[2] (3) */
 #define SENS_ROOT_XQUAT 3   /* xquat[1] (4) */
@@ -259,3 +295,7 @@ void hmj_launch_argmin(const double* returns_dev, int n, double* out_cost_idx_de
 void hmj_launch_env_obs_reward(const hmj_tables_t* tab, hmj_buffers_t buf, const double* prev_action, const double* latest_action,
                                const double* noise, double max_sim_time, double* obs, double* reward, int32_t* terminated,
                                int32_t* truncated, int32_t* self_collision, cudaStream_t stream);
+void hmj_launch_env_pre(hmj_buffers_t buf, hmj_envstate_t env, const double* action, const int32_t* mask, double rf,
+                        unsigned long long seed, cudaStream_t stream);
+void hmj_launch_env_post(hmj_buffers_t buf, hmj_envstate_t env, const int32_t* mask, double* obs, double* time_out, double* quat_out,
+                         cudaStream_t stream);

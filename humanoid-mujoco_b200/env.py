@@ -11,8 +11,15 @@ is never split, cpu_env.py:471-513,664), un-clipped actions (:670-671), DR witho
 (:253-265), `gainprm[0] = 2 +- 0.5 rf` even at rf = 0 (:215-221), the reset rejection loop on
 first-step contact (:411-414), "terminated" = time-out with reward -100, "truncated" = success.
 Differences, documented: Python `random` / `perlin_noise` / JAX threefry draws are replaced by a
-seeded numpy Generator (those streams are unpinned in the reference: unseeded `random`, JAX absent
-here); Rotation math is fp64 instead of JAX's default fp32.
+seeded numpy Generator at reset and by a counter-based splitmix64 stream for the pushes (those streams
+are unpinned in the reference: unseeded `random`, JAX absent here); Rotation math is fp64 instead of
+JAX's default fp32.
+
+Where the work happens: `step` is ONE C call (hmj_env_step_fused) — actions are written into a pinned host
+block, the action-noise / delay FIFO / push scheduler prologue, the physics step, the observation / reward
+epilogue and the observation delay FIFOs all run as CUDA kernels on per-env state that lives on the device,
+and the results come back in the same pinned block.  `step_host` is the numpy restatement of that
+bookkeeping (the reference's own control flow, vectorised) kept as the checker for the device kernels.
 """
 from __future__ import annotations
 
@@ -45,6 +52,24 @@ MAX_SIM_TIME_STANDUP = 10.0
 Z_INITIAL_POS_STANDUP = -0.6
 INITIAL_QUAT_STANDUP = [-0.5, -0.5, 0.5, 0.5]
 MAX_DELAY_STEPS = 25
+
+_M64 = np.uint64(0xFFFFFFFFFFFFFFFF)
+
+
+def _splitmix64(x: np.ndarray) -> np.ndarray:
+    with np.errstate(over="ignore"):
+        x = (x + np.uint64(0x9E3779B97F4A7C15)) & _M64
+        z = x
+        z = ((z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)) & _M64
+        z = ((z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)) & _M64
+        return z ^ (z >> np.uint64(31))
+
+
+def rand_u01(seed: int, env: np.ndarray, counter: np.ndarray) -> np.ndarray:
+    """hmj_rand_u01 (csrc/hmj_dev.cuh): counter-based uniform in [0, 1), identical bits on host and device."""
+    key = (np.asarray(env, dtype=np.uint64) << np.uint64(32)) | np.asarray(counter, dtype=np.uint64)
+    h = _splitmix64(np.uint64(seed & 0xFFFFFFFFFFFFFFFF) ^ _splitmix64(key))
+    return (h >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0)
 
 
 def _smooth_heightfield(rng: np.random.Generator, n: int) -> np.ndarray:
@@ -108,6 +133,13 @@ def standup_start_state(qpos0: np.ndarray, rng: np.random.Generator, rf: float, 
 class BatchedHumanoidEnv:
     metadata = {"render_modes": [], "render_fps": 30}
 
+    # per-env bookkeeping that lives on the device (csrc/hmj_dev.cuh: hmj_envstate_t) <-> host mirror attribute
+    _DEVICE_STATE = (("env_act_noise", "noise_action"), ("env_obs_noise", "noise_obs"), ("env_act_delay", "action_delay"),
+                     ("env_obs_delay", "obs_delay"), ("env_act_count", "action_count"), ("env_obs_count", "obs_count"),
+                     ("env_prev_action", "previous_action"), ("env_latest_action", "latest_action"),
+                     ("env_force_sched", "force_sched"), ("env_force_body", "force_body"),
+                     ("env_force_draws", "force_draws"), ("ctrl", "ctrl"), ("xfrc", "xfrc"))
+
     def __init__(self, n_envs: int, randomization_factor: float = 0.0, use_potential_rewards: bool = False,
                  max_simulation_time_override=None, reward_override=None, device: int = 0, seed: int = 0):
         self.num_envs = int(n_envs)
@@ -117,8 +149,10 @@ class BatchedHumanoidEnv:
         self.timestep = TIMESTEP
         mst = MAX_SIM_TIME_STANDUP if max_simulation_time_override is None else max_simulation_time_override
         self.max_simulation_time = np.inf if mst < 0 else float(mst)
+        self.seed = int(seed)
         self.rng = np.random.default_rng(seed)
         self.batch = HumanoidBatch(self.num_envs, device)
+        self.io = self.batch.env_io()
         self.model = self.batch.model
         self.base_params = self.batch.default_params()
         self.action_shape = (self.num_envs, NU)
@@ -130,18 +164,34 @@ class BatchedHumanoidEnv:
         self.ctrl = np.zeros((n, NU))
         self.noise_action = np.zeros((n, NU))
         self.noise_obs = np.zeros((n, 31))
-        self.action_delay = np.zeros(n, dtype=np.int64)
-        self.obs_delay = np.zeros((n, 3), dtype=np.int64)  # joint, gyro, gravity
+        self.action_delay = np.zeros(n, dtype=np.int32)
+        self.obs_delay = np.zeros((n, 3), dtype=np.int32)  # joint, gyro, gravity
         self.action_hist = np.zeros((n, MAX_DELAY_STEPS + 1, NU))
         self.obs_hist = np.zeros((n, MAX_DELAY_STEPS + 1, 30))
-        self.action_count = np.zeros(n, dtype=np.int64)
-        self.obs_count = np.zeros(n, dtype=np.int64)
+        self.action_count = np.zeros(n, dtype=np.int32)
+        self.obs_count = np.zeros(n, dtype=np.int32)
         self.previous_reward = np.zeros(n)
-        self.force_start = np.zeros(n); self.force_duration = np.zeros(n); self.force_magnitude = np.zeros(n)
-        self.force_direction = np.zeros((n, 2)); self.force_body = np.zeros(n, dtype=np.int32)
+        self.force_sched = np.zeros((n, 5))  # start, duration, magnitude, dir x, dir y
+        self.force_body = np.zeros(n, dtype=np.int32)
+        self.force_draws = np.zeros(n, dtype=np.int32)
         self.xfrc = np.zeros((n, 6))
         self.torso_quat = np.zeros((n, 4))
         self.time = np.zeros(n)
+        self._empty_info = {}
+
+    # ------------------------------------------------------------------ host mirror <-> device state
+    def _push_state(self):
+        for dev, host in self._DEVICE_STATE:
+            self.batch.set(dev, getattr(self, host))
+
+    def _pull_state(self):
+        """Bring the host mirrors up to date (before a partial reset, or to continue with `step_host`)."""
+        for dev, host in self._DEVICE_STATE:
+            setattr(self, host, self.batch.get(dev))
+        n = self.num_envs
+        self.action_hist = self.batch.get_raw("env_act_hist", np.float64, (n, MAX_DELAY_STEPS + 1, NU))
+        self.obs_hist = self.batch.get_raw("env_obs_hist", np.float64, (n, MAX_DELAY_STEPS + 1, 30))
+        self.time = self.batch.get("time")
 
     # ------------------------------------------------------------------ randomisers (cpu_env.py:135-362)
     def _randomize_model(self, idx):
@@ -149,16 +199,14 @@ class BatchedHumanoidEnv:
 
     def _randomize_delays(self, idx):
         rf, rng, k = self.randomization_factor, self.rng, len(idx)
-        draw = lambda: np.rint(rng.uniform(MIN_DELAY * rf, MAX_DELAY * rf, k) / self.timestep).astype(np.int64)  # noqa: E731
+        draw = lambda: np.rint(rng.uniform(MIN_DELAY * rf, MAX_DELAY * rf, k) / self.timestep).astype(np.int32)  # noqa: E731
         self.action_delay[idx] = draw()
         self.obs_delay[idx, 0] = draw()  # joint angles + velocities
         self.obs_delay[idx, 1] = draw()  # gyro
         draw()                           # torso_local_velocity_delay (drawn, unused by the observation)
         self.obs_delay[idx, 2] = draw()  # gravity vector
         draw()                           # contact_sensor_delay (unused)
-        self.action_hist[idx] = 0.0
-        self.obs_hist[idx] = 0.0
-        self.obs_hist[idx, :, 27:30] = [0, 0, -1]
+        # the FIFOs need no clearing: a slot is always written before the first read that can reach it
         self.action_count[idx] = 0
         self.obs_count[idx] = 0
 
@@ -168,8 +216,11 @@ class BatchedHumanoidEnv:
     # ------------------------------------------------------------------ reset (cpu_env.py:374-416)
     def reset(self, seed=None, options=None, env_ids=None):
         if seed is not None:
+            self.seed = int(seed)
             self.rng = np.random.default_rng(seed)
         idx = np.arange(self.num_envs) if env_ids is None else np.asarray(env_ids, dtype=np.int64)
+        if env_ids is not None:
+            self._pull_state()
         pending = idx
         obs_out = np.zeros((self.num_envs, 30))
         for _attempt in range(100):
@@ -195,12 +246,12 @@ class BatchedHumanoidEnv:
             self.batch.set_state(qpos, qvel, time, ws)
             self.ctrl[pending] = 0.0
             self.previous_action[pending] = 0.0; self.latest_action[pending] = 0.0
-            self.force_start[pending] = 0; self.force_duration[pending] = 0; self.force_magnitude[pending] = 0
-            self.force_direction[pending] = 0; self.force_body[pending] = 0; self.xfrc[pending] = 0
+            self.force_sched[pending] = 0.0; self.force_body[pending] = 0; self.xfrc[pending] = 0.0
             self.previous_reward[pending] = 0.0
+            self._push_state()
             # first step with action=None; reject starts that touch anything or end the episode
             mask = np.zeros(self.num_envs, dtype=bool); mask[pending] = True
-            obs, _, term, trunc, _ = self._step_impl(None, only=mask)
+            _obs, _, term, trunc, _ = self._step_device(None, only=mask)
             if not mask.all():  # the lock-step call advanced everyone: put the bystanders back
                 q2, v2, t2, w2 = self.batch.get_state()
                 keep = ~mask
@@ -211,15 +262,63 @@ class BatchedHumanoidEnv:
             bad = mask & ((ncon > 0) | term | trunc)
             accepted = mask & ~bad
             if accepted.any():
-                obs2 = self._observe(only=accepted)  # reset returns a SECOND _get_obs() (cpu_env.py:416)
+                obs2 = self._observe_device(accepted)  # reset returns a SECOND _get_obs() (cpu_env.py:416)
                 obs_out[accepted] = obs2[accepted]
             pending = np.nonzero(bad)[0]
+            if len(pending):
+                self._pull_state()
         if len(pending):
             raise RuntimeError(f"reset: {len(pending)} environments still in contact after 100 attempts")
         return (obs_out if env_ids is None else obs_out[idx]), {}
 
     # ------------------------------------------------------------------ step (cpu_env.py:676-693)
     def step(self, action=None):
+        """One control step of every environment.  Returns views of the pinned result block (valid until the next
+        call): obs [N][30], reward [N], terminated [N], truncated [N], infos (list; `is_success` on episode end)."""
+        obs, reward, term, trunc, _ = self._step_device(action, only=None)
+        infos = [self._empty_info] * self.num_envs
+        done = term | trunc
+        if done.any():
+            for i in np.nonzero(done)[0]:
+                infos[i] = {"is_success": bool(trunc[i])}
+        return obs, reward, term, trunc, infos
+
+    def _step_device(self, action, only):
+        io = self.io
+        if action is not None:
+            io["action"][...] = np.asarray(action, dtype=np.float64).reshape(self.num_envs, NU)
+        if only is not None:
+            io["mask"][...] = only
+        # ONE C call: action H2D, prologue, mj_step (PHYSICS_STEPS_PER_CONTROL_STEP = 1, simulation_parameters.py:82),
+        # obs/reward epilogue + delay FIFOs, results D2H
+        self.batch.env_step_fused(action is not None, only is not None, self.randomization_factor, self.max_simulation_time,
+                                  self.seed, 1)
+        self.time = io["time"]
+        self.torso_quat = io["torso_quat"]
+        return self._finish(io["obs"], io["reward"], io["terminated"].astype(bool), io["truncated"].astype(bool),
+                            io["self_collision"].astype(bool))
+
+    def _finish(self, obs, reward, term, trunc, selfc):
+        if self.reward_override is not None:
+            reward = np.full(self.num_envs, float(self.reward_override))
+        elif self.use_potential_rewards:
+            r = reward - self.previous_reward
+            self.previous_reward = reward.copy()
+            reward = r
+        return obs, reward, term, trunc, selfc
+
+    def _observe_device(self, only):
+        """A second _get_obs() on the current state (reset's return value): epilogue + delay FIFOs, no physics."""
+        io = self.io
+        io["mask"][...] = only
+        self.batch.env_step_fused(False, True, self.randomization_factor, self.max_simulation_time, self.seed, -1)
+        return io["obs"].copy()
+
+    # ------------------------------------------------------------------ numpy restatement of the device bookkeeping
+    # (the reference's control flow, vectorised; the checker for k_env_pre / k_env_post — tests/test_gpu_env.py)
+    def step_host(self, action=None):
+        """Same contract as `step`, bookkeeping in numpy on the host mirrors (call `_pull_state()` first when the
+        device path ran before).  The device bookkeeping arrays are NOT updated by this path."""
         obs, reward, term, trunc, _ = self._step_impl(action, only=None)
         infos = [({"is_success": bool(trunc[i])} if (term[i] or trunc[i]) else {}) for i in range(self.num_envs)]
         return obs, reward, term, trunc, infos
@@ -243,69 +342,60 @@ class BatchedHumanoidEnv:
         self.latest_action[ids] = take
 
     def _apply_external_forces(self, only):
-        rf, rng = self.randomization_factor, self.rng
+        rf = self.randomization_factor
         sel = np.ones(self.num_envs, dtype=bool) if only is None else only
         t = self.time
-        renew = sel & (t >= self.force_start + self.force_duration)
-        k = int(renew.sum())
-        if k:
+        fs = self.force_sched
+        renew = sel & (t >= fs[:, 0] + fs[:, 1])
+        if renew.any():
             ids = np.nonzero(renew)[0]
-            self.force_start[ids] = t[ids] + rng.uniform(MIN_EXTERNAL_FORCE_INTERVAL, MAX_EXTERNAL_FORCE_INTERVAL, k)
-            self.force_duration[ids] = rng.uniform(MIN_EXTERNAL_FORCE_DURATION, MAX_EXTERNAL_FORCE_DURATION, k)
-            self.force_magnitude[ids] = rng.uniform(MIN_EXTERNAL_FORCE_MAGNITUDE * rf, MAX_EXTERNAL_FORCE_MAGNITUDE * rf, k)
-            dirs = rng.uniform(-1, 1, (k, 2))
-            nrm = np.linalg.norm(dirs, axis=1, keepdims=True)
-            dirs = np.where(nrm == 0, np.array([[1.0, 0.0]]), dirs / np.maximum(nrm, 1e-300))
-            self.force_direction[ids] = dirs
+            c = self.force_draws[ids].astype(np.uint64) * np.uint64(8)
+            u = [rand_u01(self.seed, ids, c + np.uint64(j)) for j in range(6)]
+            fs[ids, 0] = t[ids] + (MIN_EXTERNAL_FORCE_INTERVAL + (MAX_EXTERNAL_FORCE_INTERVAL - MIN_EXTERNAL_FORCE_INTERVAL) * u[0])
+            fs[ids, 1] = MIN_EXTERNAL_FORCE_DURATION + 0.10 * u[1]
+            fs[ids, 2] = 5.0 * rf + (15.0 * rf - 5.0 * rf) * u[2]
+            dx, dy = -1.0 + 2.0 * u[3], -1.0 + 2.0 * u[4]
+            nrm = np.sqrt(dx * dx + dy * dy)
+            zero = nrm == 0
+            nrm = np.where(zero, 1.0, nrm)
+            fs[ids, 3] = np.where(zero, 1.0, dx / nrm)
+            fs[ids, 4] = np.where(zero, 0.0, dy / nrm)
             self.xfrc[ids, 0:2] = 0.0
-            self.force_body[ids] = rng.integers(1, 15, k)
-        active = sel & (t > self.force_start) & (t < self.force_start + self.force_duration)
+            self.force_body[ids] = np.minimum(1 + (14.0 * u[5]).astype(np.int32), 14)
+            self.force_draws[ids] += 1
+        active = sel & (t > fs[:, 0]) & (t < fs[:, 0] + fs[:, 1])
         ids = np.nonzero(active)[0]
-        self.xfrc[ids, 0:2] = self.force_direction[ids] * self.force_magnitude[ids, None]
+        self.xfrc[ids, 0:2] = fs[ids, 3:5] * fs[ids, 2:3]
 
     def _observe(self, only=None, res=None):
-        """_get_obs + _get_reward on the device; `res` = results of a fused hmj_env_step, else a separate epilogue call."""
-        if res is None:
-            obs_now, reward, term, trunc, selfc = self.batch.obs_reward(
-                self.previous_action, self.latest_action, self.noise_obs, self.max_simulation_time)
-            root_quat = self.batch.get("sens")[:, 3:7]
-        else:
-            obs_now, reward, root_quat = res["obs"], res["reward"], res["root_quat"]
-            term, trunc, selfc = res["terminated"].astype(bool), res["truncated"].astype(bool), res["self_collision"].astype(bool)
+        """_get_obs + _get_reward; `res` = results of hmj_env_step (undelayed observation from the epilogue kernel)."""
+        obs_now, reward, root_quat = res["obs"], res["reward"], res["root_quat"]
+        term, trunc, selfc = res["terminated"].astype(bool), res["truncated"].astype(bool), res["self_collision"].astype(bool)
         sel = np.ones(self.num_envs, dtype=bool) if only is None else only
         ids = np.nonzero(sel)[0]
+        self.torso_quat = np.array(self.torso_quat)
         self.torso_quat[ids] = root_quat[ids] + self.noise_obs[ids, 27:31]
         # delay FIFOs (joint angles+velocities share a delay; gyro; gravity), cpu_env.py:135-187,528-547
         slot = self.obs_count[ids] % (MAX_DELAY_STEPS + 1)
         self.obs_hist[ids, slot] = obs_now[ids]
         out = obs_now.copy()
-        init = np.zeros(30); init[27:30] = [0, 0, -1]
+        init = np.zeros(30); init[29] = -1.0
         for grp, cols in ((0, slice(0, 24)), (1, slice(24, 27)), (2, slice(27, 30))):
             d = self.obs_delay[ids, grp]
             src = (self.obs_count[ids] - d) % (MAX_DELAY_STEPS + 1)
             val = self.obs_hist[ids, src][:, cols]
             out[ids, cols] = np.where((self.obs_count[ids] >= d)[:, None], val, init[cols][None, :])
         self.obs_count[ids] += 1
-        self._last = (reward, term, trunc, selfc)
-        return out
+        return out, reward, term, trunc, selfc
 
     def _step_impl(self, action, only):
         self._apply_action(action, only)
         self._apply_external_forces(only)
-        # ONE C call: ctrl/xfrc H2D, mj_step (PHYSICS_STEPS_PER_CONTROL_STEP = 1, simulation_parameters.py:82),
-        # obs/reward epilogue, results D2H
         res = self.batch.env_step(self.ctrl, self.force_body, self.xfrc, self.previous_action, self.latest_action,
-                                  self.noise_obs, self.max_simulation_time, 1, out=getattr(self, "_out", None))
+                                  self.noise_obs, self.max_simulation_time, 1)
         self.time = res["time"].copy()
-        obs = self._observe(only, res)
-        reward, term, trunc, selfc = self._last
-        if self.reward_override is not None:
-            reward = np.full(self.num_envs, float(self.reward_override))
-        elif self.use_potential_rewards:
-            r = reward - self.previous_reward
-            self.previous_reward = reward.copy()
-            reward = r
-        return obs, reward, term, trunc, selfc
+        obs, reward, term, trunc, selfc = self._observe(only, res)
+        return self._finish(obs, reward, term, trunc, selfc)
 
     def close(self):
         self.batch.close()

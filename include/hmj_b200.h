@@ -105,6 +105,21 @@ int hmj_env_step(hmj_batch_t* b, const double* ctrl, const int32_t* xfrc_body, c
                  int nsteps, double* obs, double* reward, int32_t* terminated, int32_t* truncated,
                  int32_t* self_collision, double* time_out, double* root_quat_out);
 
+/* ---- CPUEnv.step with the per-step bookkeeping ON THE DEVICE (cpu_env.py:656-674 action noise + delay FIFO,
+ * :618-654 push scheduler, :528-547 observation delay FIFOs, :516 torso_quat).  The per-env bookkeeping arrays are
+ * named device arrays ("env_act_noise" [N][12], "env_obs_noise" [N][31], "env_act_delay" [N] i32, "env_obs_delay"
+ * [N][3] i32, "env_act_count" / "env_obs_count" [N] i32, "env_prev_action" / "env_latest_action" [N][12],
+ * "env_force_sched" [N][5], "env_force_body" / "env_force_draws" [N] i32), written by the host at reset through
+ * hmj_batch_set_array.  hmj_env_io returns views into ONE pinned host block: inputs action [N][12], mask [N] i32;
+ * outputs obs [N][30], reward [N], time [N], torso_quat [N][4], terminated / truncated / self_collision [N] i32.
+ * hmj_env_step_fused: one H2D copy, k_env_pre, nsteps x mj_step, obs/reward, delay FIFOs, one D2H copy, one sync.
+ * has_action = 0 replays data.ctrl (CPUEnv.step(None)); has_mask != 0 limits the bookkeeping to mask[env] != 0.
+ * Pushes draw from a counter-based stream splitmix64(seed, env, draw) instead of the reference's unseeded `random`. */
+int hmj_env_io(hmj_batch_t* b, double** action, int32_t** mask, double** obs, double** reward, double** time,
+               double** torso_quat, int32_t** terminated, int32_t** truncated, int32_t** self_collision);
+int hmj_env_step_fused(hmj_batch_t* b, int has_action, int has_mask, double rf, double max_sim_time,
+                       unsigned long long seed, int nsteps);
+
 /* ---- per-kernel device timing (CUDA events on the batch stream, one pair around every launch of a step;
  * MuJoCo's own equivalent is the mjTIMER_* profiler, mjdata.h:68-93).  enable resets the counters. */
 int hmj_batch_profile(hmj_batch_t* b, int enable);
