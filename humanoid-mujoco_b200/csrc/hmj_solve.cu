@@ -188,6 +188,15 @@ __device__ __forceinline__ void make_frame(double* frame) {
 
 struct LsPnt { double alpha, cost, d0, d1; };
 
+// HMJ_PHASE_PROF: per-phase latency accounting (developer build only): lane 0 adds the cycles since the previous
+// mark to hmj_phase_cycles[phase]; read back with cudaMemcpyFromSymbol through hmj_debug_phase_cycles.
+#ifdef HMJ_PHASE_PROF
+__device__ unsigned long long hmj_phase_cycles[16];
+#define PH(i) do { const long long t_ = clock64(); if (lane == 0) atomicAdd(&hmj_phase_cycles[i], (unsigned long long)(t_ - ph_t0)); ph_t0 = clock64(); } while (0)
+#else
+#define PH(i) do { } while (0)
+#endif
+
 __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MIN_CTAS)
 k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
   extern __shared__ double smem_raw[];
@@ -200,6 +209,9 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
   const hmj_params_t* P = B.params + env;
   const unsigned FULL = 0xffffffffu;
   const double h = P->timestep;
+#ifdef HMJ_PHASE_PROF
+  long long ph_t0 = clock64();
+#endif
 
   // ---------------- load: dense M, qfrc_smooth, state
   for (int t = lane; t < NV * LD; t += 32) S.M[t] = 0.0;
@@ -227,6 +239,7 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
   const double qas = chol_solve(S.H, S.invd, qfs, lane);
   if (lane < NV) { S.qas[lane] = qas; B.qacc_smooth[(size_t)env * NV + lane] = qas; }
 
+  PH(1);
   // ---------------- contacts: ordered compaction of the narrowphase slots (slot order == MuJoCo contact order)
   int ncon = 0;
   int status = 0;
@@ -312,6 +325,7 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
   int niter = 0;
 
   if (nefc > 0) {
+    PH(2);
     // ---------------- contact-frame Jacobian basis Jb[c][k][d] (mj_jacDifPair rotated into the contact frame)
     for (int t = lane; t < ncon * NV; t += 32) {
       const int c = t / NV, d = t - c * NV;
@@ -419,6 +433,7 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
       return warp_sum(s);
     };
 
+    PH(3);
     // ---------------- warmstart: best of (qacc_warmstart, qacc_smooth)
     {
       double jar[NROWREG];
@@ -437,6 +452,7 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
       __syncwarp();
     }
 
+    PH(4);
     // ---------------- Newton iterations (mj_solNewton, primal)
     const double scale = 1.0 / (M.meaninertia * (double)NV);
     const double tolerance = M.tolerance;
@@ -491,7 +507,9 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
         S.H[i * LD + j] = acc;
       }
       __syncwarp();
+      PH(12);
       chol_factor(S.H, S.invd, T, lane);
+      PH(13);
 
       // ---- qfrc_constraint = J' f: publish row forces, gather on the contact basis
 #pragma unroll
@@ -527,6 +545,7 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
 
       // ---- gradient and Newton direction
       grad = (lane < NV) ? Ma - qfs - qfc : 0.0;
+      PH(14);
       mgrad = chol_solve(S.H, S.invd, grad, lane);
       return cost_c + gauss;
     };
@@ -536,6 +555,7 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
     Ma = mat_vec(S.M, S.vec, lane);
     jaref_of(rJaref);
     double cost = evaluate();
+    PH(5);
     double search = -mgrad;
 
     while (niter < M.iterations) {
@@ -563,6 +583,7 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
           rq2[k] = 0.5 * (rJv[k] * rD[k] * rJv[k]);
         }
       }
+      PH(6);
       int lsiter = 0;
       auto ls_eval = [&](LsPnt& p) {
         double a0 = 0, a1 = 0, a2 = 0;
@@ -630,6 +651,7 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
 #ifdef HMJ_TRACE
       if (env == HMJ_TRACE && lane == 0) printf("GPU it %d alpha %.17g lsiter %d snorm %.17g gtol %.6g cost %.17g\n", niter, alpha, lsiter, snorm, gtol, cost);
 #endif
+      PH(7);
       if (alpha == 0.0) break;
 
       // ---- move to the new point, re-evaluate, test convergence
@@ -638,6 +660,7 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
       for (int k = 0; k < NROWREG; k++) rJaref[k] += alpha * rJv[k];
       const double oldcost = cost;
       cost = evaluate();
+      PH(8);
       const double improvement = scale * (oldcost - cost);
       const double gradient = scale * sqrt(warp_sum(grad * grad));
       niter++;
@@ -649,6 +672,7 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
     }
   }
 
+  PH(9);
   // ---------------- results of mj_fwdConstraint
   if (lane < NV) {
     B.qacc[(size_t)env * NV + lane] = qacc;
@@ -669,6 +693,7 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
   if (status && lane == 0) atomicOr(&B.status[env], status);
   if (!integrate) return;
 
+  PH(10);
   // ---------------- mj_Euler with implicit joint damping: (M + h diag(b)) a = qfrc_smooth + qfrc_constraint
   __syncwarp();
   for (int t = lane; t < NV * LD; t += 32) S.H[t] = S.M[t];
@@ -677,6 +702,7 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
   __syncwarp();
   chol_factor(S.H, S.invd, T, lane);
   const double qacc_e = chol_solve(S.H, S.invd, qfs + qfc, lane);
+  PH(11);
   if (lane < NV) {
     qvel += h * qacc_e;
     B.qvel[(size_t)env * NV + lane] = qvel;
@@ -713,3 +739,12 @@ void hmj_launch_solve(const hmj_tables_t* tab, hmj_buffers_t buf, int integrate,
   const int grid = (buf.n + SOLVE_WARPS - 1) / SOLVE_WARPS;
   k_solve<<<grid, 32 * SOLVE_WARPS, smem, stream>>>(tab, buf, integrate);
 }
+
+#ifdef HMJ_PHASE_PROF
+extern "C" int hmj_debug_phase_cycles(unsigned long long* out, int reset) {
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out, hmj_phase_cycles, sizeof(unsigned long long) * 16);
+  if (reset) { unsigned long long z[16] = {0}; cudaMemcpyToSymbol(hmj_phase_cycles, z, sizeof(z)); }
+  return 0;
+}
+#endif
