@@ -267,17 +267,10 @@ class SamplingPlanner:
         if self.world > 1:
             import torch
             import torch.distributed as dist
+            from .dist import exchange_winner
             dev = torch.device("cuda", self._device) if dist.get_backend() == "nccl" else torch.device("cpu")
-            mine = torch.tensor([cost, float(idx), self.nominal_return], dtype=torch.float64, device=dev)
-            allv = [torch.zeros_like(mine) for _ in range(self.world)]
-            dist.all_gather(allv, mine)
-            costs = [float(v[0]) for v in allv]
-            owner = int(np.argmin(costs))  # first minimum: lowest rank, then lowest local index
-            self.nominal_return = float(allv[0][2])
-            spline = torch.tensor(win_values, dtype=torch.float64, device=dev)
-            dist.broadcast(spline, src=owner)
-            win_values = spline.cpu().numpy()
-            cost, idx = costs[owner], int(allv[owner][1]) + owner * self.num_trajectory_
+            cost, idx, self.nominal_return, win_values = exchange_winner(
+                cost, idx, self.nominal_return, win_values, self.rank * self.num_trajectory_, dev)
         self.winner = int(idx)
         self.winner_return = float(cost)
         self._winner_values = np.array(win_values, dtype=np.float64)
