@@ -54,6 +54,7 @@ struct hmj_batch_ {
   char* io_dev = nullptr;
   size_t io_in_bytes = 0, io_out_bytes = 0;
   int launches = 0;
+  hmj_solve_ctx_t solve_ctx{};       // side streams + events that overlap the solver classes
   // per-kernel CUDA-event profiling (hmj_batch_profile): events bracket every launch of a step
   bool profile = false;
   std::vector<cudaEvent_t> prof_events;  // 4 per step: before smooth, collide, solve, after solve
@@ -201,6 +202,11 @@ extern "C" void hmj_batch_destroy(hmj_batch_t* b) {
   if (b->io_host) cudaFreeHost(b->io_host);
   if (b->tab_dev) cudaFree(b->tab_dev);
   if (b->task_dev) cudaFree(b->task_dev);
+  for (int k = 0; k < 2; k++) {
+    if (b->solve_ctx.side[k]) cudaStreamDestroy(b->solve_ctx.side[k]);
+    if (b->solve_ctx.join[k]) cudaEventDestroy(b->solve_ctx.join[k]);
+  }
+  if (b->solve_ctx.fork) cudaEventDestroy(b->solve_ctx.fork);
   if (b->stream) cudaStreamDestroy(b->stream);
   delete b->tab_host;
   delete b;
@@ -220,6 +226,11 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
   b->device = device;
   b->buf.n = n_envs;
   CK(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
+  for (int k = 0; k < 2; k++) {
+    CK(cudaStreamCreateWithFlags(&b->solve_ctx.side[k], cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&b->solve_ctx.join[k], cudaEventDisableTiming));
+  }
+  CK(cudaEventCreateWithFlags(&b->solve_ctx.fork, cudaEventDisableTiming));
   b->tab_host = new hmj_tables_t;
   build_tables(model, b->tab_host);
   CK(cudaMalloc((void**)&b->tab_dev, sizeof(hmj_tables_t)));
@@ -255,6 +266,8 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
   ALLOC("slots", slots, N * HMJ_NSLOT * HMJ_SLOT_DOUBLES);
   ALLOC("wq_count", wq_count, 64);
   ALLOC("wq_task", wq_task, N * (size_t)b->tab_host->group_base[HMJ_NGROUP]);
+  ALLOC("solve_count", solve_count, 4);
+  ALLOC("solve_list", solve_list, 3 * N);
   ALLOC("qacc", qacc, N * HMJ_NV);
   ALLOC("qacc_smooth", qacc_smooth, N * HMJ_NV);
   ALLOC("qfrc_constraint", qfrc_constraint, N * HMJ_NV);
@@ -418,9 +431,9 @@ static void enqueue_step(hmj_batch_t* b, int integrate) {
   if (prof) prof_event(b);
   hmj_launch_collide(b->tab_dev, b->buf, b->stream);
   if (prof) prof_event(b);
-  hmj_launch_solve(b->tab_dev, b->buf, integrate, b->stream);
+  hmj_launch_solve(b->tab_dev, b->buf, integrate, b->stream, &b->solve_ctx);
   if (prof) prof_event(b);
-  b->launches += 4;  // smooth, broad, narrow, solve
+  b->launches += 7;  // smooth, broad, narrow, classify, solve x 3 classes
 }
 
 // Per-kernel device time of the steps enqueued while profiling was on (CUDA events on the batch stream).
@@ -488,8 +501,8 @@ extern "C" int hmj_batch_run_stage(hmj_batch_t* b, int stage) {
   switch (stage) {
     case HMJ_STAGE_SMOOTH: hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, b->stream); break;
     case HMJ_STAGE_COLLIDE: hmj_launch_collide(b->tab_dev, b->buf, b->stream); break;
-    case HMJ_STAGE_SOLVE: hmj_launch_solve(b->tab_dev, b->buf, 0, b->stream); break;
-    case HMJ_STAGE_SOLVE_INTEGRATE: hmj_launch_solve(b->tab_dev, b->buf, 1, b->stream); break;
+    case HMJ_STAGE_SOLVE: hmj_launch_solve(b->tab_dev, b->buf, 0, b->stream, &b->solve_ctx); break;
+    case HMJ_STAGE_SOLVE_INTEGRATE: hmj_launch_solve(b->tab_dev, b->buf, 1, b->stream, &b->solve_ctx); break;
     default: return fail(HMJ_ERR_ARG, "unknown stage%s");
   }
   b->launches += 1;
@@ -742,8 +755,8 @@ static int enqueue_rollouts(hmj_batch_t* b, const double* state, double time, co
                       interpolation, 1, b->stream);
     if (record) { hmj_launch_plan_record(b->buf, b->rec, t, b->stream); b->launches += 1; }
     hmj_launch_collide(b->tab_dev, b->buf, b->stream);
-    hmj_launch_solve(b->tab_dev, b->buf, 1, b->stream);
-    b->launches += 4;
+    hmj_launch_solve(b->tab_dev, b->buf, 1, b->stream, &b->solve_ctx);
+    b->launches += 7;
   }
   // final mj_forward: only the sensors/residual matter, ctrl keeps the last action (trajectory.cc:190-206)
   hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, HMJ_PLAN_COST, nullptr, nullptr, 0, 0, 0, b->stream);

@@ -18,6 +18,9 @@ __global__ void k_plan_init(hmj_buffers_t B, const double* __restrict__ state, d
     B.warmstart[(size_t)env * HMJ_NV + k] = 0.0;  // deterministic stand-in for per-thread mjData reuse (planner.cc:374)
   }
   for (int k = 0; k < 6; k++) B.xfrc[(size_t)env * 6 + k] = 0.0;
+  // fresh mjData: ctrl = 0 (only visible to a horizon-1 rollout, whose single mj_forward runs before any policy call;
+  // the reference leaves the worker's stale ctrl there, trajectory.cc:186-198)
+  for (int k = 0; k < HMJ_NU; k++) B.ctrl[(size_t)env * HMJ_NU + k] = 0.0;
   B.xfrc_body[env] = 0;
   B.time[env] = time;
   B.cost_sum[env] = 0.0;

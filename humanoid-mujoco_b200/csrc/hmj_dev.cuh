@@ -92,6 +92,8 @@ struct hmj_buffers_t {
   double* slots;      // [N][NSLOT][8]
   int32_t* wq_count;  // [64]       narrowphase tasks per group (zeroed every step)
   int2* wq_task;      // [group_base[NGROUP] * N]  (env, packed pair / slot ordinal / prism position)
+  int32_t* solve_count; // [4]     envs per solver class (zeroed every step)
+  int32_t* solve_list;  // [3][N]  env ids of each solver class
   // ---- outputs
   double* qacc;            // [N][18]
   double* qacc_smooth;     // [N][18]
@@ -271,7 +273,14 @@ void hmj_launch_smooth(const hmj_tables_t* tab, hmj_buffers_t buf, const hmj_tas
                        const double* spline_times, const double* spline_values, int nnode, int interpolation,
                        int values_per_env, cudaStream_t stream);
 void hmj_launch_collide(const hmj_tables_t* tab, hmj_buffers_t buf, cudaStream_t stream);
-void hmj_launch_solve(const hmj_tables_t* tab, hmj_buffers_t buf, int integrate, cudaStream_t stream);
+// Side streams of hmj_launch_solve: the three solver classes are independent, so the (few, long) many-contact solves
+// and the (many, short) unconstrained ones run beside the main class instead of after it.  Null -> one stream.
+struct hmj_solve_ctx_t {
+  cudaStream_t side[2];
+  cudaEvent_t fork, join[2];
+};
+void hmj_launch_solve(const hmj_tables_t* tab, hmj_buffers_t buf, int integrate, cudaStream_t stream,
+                      const hmj_solve_ctx_t* ctx = nullptr);
 
 // plan_mode bits for hmj_launch_smooth
 #define HMJ_PLAN_COST 1    /* sensors -> residual -> cost accumulation */

@@ -1,4 +1,4 @@
-// hmj_solve.cu — kernel 3 of the step: contacts -> constraints -> Newton solver -> Euler integrator.
+// hmj_solve.cu — last stage of the step: contacts -> constraints -> Newton solver -> Euler integrator.
 //
 // Restates mj_fwdAcceleration's solve (mujoco.h:256), mj_makeConstraint (:358),
 // mj_referenceConstraint (:367), mj_fwdConstraint with the Newton solver (:259), mj_checkAcc (:307)
@@ -6,62 +6,72 @@
 // mjmodel.h:403-444: pyramidal cones, condim 6 -> 10 rows per contact, tolerance 1e-8, 100 iterations,
 // exact line search with ls_tolerance 0.01 / 50 iterations, refsafe, warmstart).
 //
-// Mapping: one warp per environment, 4 warps per CTA.
-//   * dense 18x18 M and Hessian factor in shared memory (row stride 19: conflict-free fp64 columns);
-//     right-looking warp Cholesky, triangular solves in registers with shuffles;
+// Launch structure (one step):
+//   k_classify   warp per env: counts contact slots and active joint limits, appends the env to one of three
+//                work lists — class 0: no constraint rows, class 1: <= SOLVE_SMALL_CON contacts, class 2: the rest;
+//   k_solve<C>   one warp (= one CTA) per listed env, one instantiation per class.  The classes differ only in
+//                the shared-memory footprint (contact basis + per-row arrays sized for the class), which is what
+//                bounds residency: class 0 keeps ~6 KB per env, class 1 ~15 KB, class 2 ~32 KB.
+// Mapping inside k_solve: lane d owns dof d for all 18-vectors; constraint rows are strided over lanes
+// (row r -> lane r % 32) with their scalars in shared memory; reductions are xor-butterfly shuffles, which give
+// bit-identical sums on all lanes, so all solver control flow is warp-uniform.
+//   * dense 18x18 M and Hessian factor in shared memory (row stride 19), rolled right-looking warp Cholesky;
 //   * the 10 pyramid-edge rows of a contact are never materialised: only the 6 contact-frame basis rows
-//     Jb[c][6][18] are stored (J_edge = Jn +- mu_k Jk), so J.v, J'.f and J'DJ all work on the basis;
-//   * per-row scalars (D, aref, Jaref, Jv, line-search quadratics) live in the registers of the lane
-//     that owns the row (row r -> lane r % 32), reductions are xor-butterfly shuffles, which give
-//     bit-identical sums on all lanes, so all solver control flow is warp-uniform.
-// Roofline: FP64 FMA pipe (J'DJ, Cholesky) and shuffle/issue latency (line search); per-env HBM/L2
-// traffic is ~2.6 KB in (qM, cdof, slots, state) and ~0.6 KB out.
+//     Jb[c][6][18] are stored (J_edge = Jn +- mu_k Jk), so J.v, J'.f and J'DJ all work on the basis.
+// Every loop is rolled and the line-search / evaluation bodies exist once: the whole kernel is a few thousand
+// SASS instructions and stays in the instruction cache (the unrolled predecessor was 300 KB of code and spent
+// more than half of its stall cycles on instruction fetch: profiles/r1b_ncu_full_summary.csv).
+// Roofline: FP64 latency (Cholesky pivots, line-search reductions); per-env HBM/L2 traffic is ~2.6 KB in
+// (qM, cdof, slots, state) and ~0.6 KB out.
 #include <cstdio>
 #include "hmj_dev.cuh"
 
 #define NV HMJ_NV
-#ifndef SOLVE_MIN_CTAS
-#define SOLVE_MIN_CTAS 8
-#endif
-#ifndef SOLVE_WARPS
-#define SOLVE_WARPS 1           /* one environment per CTA: a slow Newton solve never holds idle neighbours resident */
-#endif
 #define LD 19                   /* padded row stride of the dense 18x18 matrices */
-#define NROWREG 6               /* ceil(HMJ_MAXEFC / 32) rows per lane */
 #define NLIMMAX 24
-#define ST_QUAD 1
+#define NTRI (NV * (NV + 1) / 2)
+#define SOLVE_SMALL_CON 4       /* class 1 holds envs with at most this many contacts */
 
+template <int MAXC>
 struct SolveSmem {
+  static constexpr int MC = MAXC > 0 ? MAXC : 1;
+  static constexpr int NL = MAXC > 0 ? NLIMMAX : 1;
+  static constexpr int MR = MAXC > 0 ? NLIMMAX + 10 * MAXC : 1;
   double M[NV * LD];
   double H[NV * LD];
-  double invd[NV + 1];
-  double Jb[HMJ_MAXCON][6][LD];
-  double jbv[HMJ_MAXCON][6];
-  double rowbuf[HMJ_MAXEFC];
-  double cpos[HMJ_MAXCON][3];
-  double cframe[HMJ_MAXCON][9];
-  double cfric[HMJ_MAXCON][5];
-  double vec[NV + 1];           // vector being multiplied (search / qacc / qvel)
-  double qfs[NV + 1];           // qfrc_smooth
-  double qas[NV + 1];           // qacc_smooth
-  double qfc[NV + 1];           // qfrc_constraint
+  double vec[NV + 2];           // vector being multiplied (search / qacc / qvel)
+  double qfs[NV + 2];           // qfrc_smooth
   double com[4];
-  int32_t cslot[HMJ_MAXCON];
-  int32_t cb1[HMJ_MAXCON], cb2[HMJ_MAXCON];
-  int32_t lim_dof[NLIMMAX];
-  double lim_sign[NLIMMAX], lim_pos[NLIMMAX], lim_margin[NLIMMAX];
-  int32_t lim_jnt[NLIMMAX];
+  unsigned char tri[NTRI][2];   // (i, j <= i) of the t-th lower-triangle entry, row-major
+  // ---- constrained classes only
+  double Jb[MC][6][LD];
+  double jbv[MC][6];
+  double W[MC][12];             // per-contact 6x6 weight in the basis: Wnn, Wnk[5], Wkk[5]
+  double rowbuf[MR];
+  double rD[MR], rAref[MR], rJaref[MR], rJv[MR];
+  double cpos[MC][3];
+  double cframe[MC][9];
+  double cfric[MC][5];
+  double cprm[MC][8];            // dist, solref[2], solimp[5]
+  double lim_sign[NL], lim_pos[NL], lim_margin[NL];
+  int32_t cslot[MC], cb1[MC], cb2[MC];
+  int32_t lim_dof[NL], lim_jnt[NL];
 };
 
 // ---------------------------------------------------------------- dense helpers (warp cooperative)
-// In-register right-looking Cholesky: lane i holds row i of the lower triangle (fully unrolled, static
-// register indices); column j is scaled by rsqrt(d_j) computed redundantly on every lane and the rank-1
-// update pulls l_kj from lane k with one shuffle per (j, k) pair: 153 shuffles + 153 FMAs, no shared
-// memory traffic or barriers inside the factorisation.  Entries above the diagonal carry garbage.
-__device__ __noinline__ void chol_factor(double* H, double* invd, const hmj_tables_t*, int lane) {
+// x <- H^-1 x for the SPD matrix whose lower triangle sits in shared memory (H = L L').  One fused routine:
+//   * right-looking Cholesky with lane i holding row i in registers (static indices, fully unrolled): per pivot j
+//     every lane forms rsqrt(d_j) redundantly, scales its entry of column j and pulls l_kj from lane k with one
+//     shuffle per trailing column — 153 shuffle+FMA pairs, no shared-memory traffic or barriers on the chain;
+//   * the forward substitution rides along (column j of L is final when pivot j is done);
+//   * L is then published to shared memory once, because the backward substitution walks columns
+//     (lane i needs l_ki for every k > i), which the row-per-lane registers cannot provide.
+// The routine exists once (noinline) and is the only large straight-line block of the kernel (~20 KB of SASS).
+// On return H holds L (lower triangle; entries above the diagonal are garbage).
+__device__ __noinline__ double chol_factor_solve(double* H, double x, int lane) {
   const unsigned FULL = 0xffffffffu;
   const int row = lane < NV ? lane : NV - 1;
-  double a[NV];
+  double a[NV], invs[NV];
   __syncwarp();
 #pragma unroll
   for (int k = 0; k < NV; k++) a[k] = H[row * LD + k];
@@ -70,43 +80,41 @@ __device__ __noinline__ void chol_factor(double* H, double* invd, const hmj_tabl
     double dj = __shfl_sync(FULL, a[j], j);
     if (dj < HMJ_MINVAL) dj = HMJ_MINVAL;
     const double inv = rsqrt(dj);
+    invs[j] = inv;
     const double lij = (lane == j) ? dj * inv : a[j] * inv;
     a[j] = lij;
-    if (lane == j) invd[j] = inv;
 #pragma unroll
     for (int k = j + 1; k < NV; k++) {
       const double lkj = __shfl_sync(FULL, lij, k);
       a[k] -= lij * lkj;
     }
+    // forward substitution step j: y_j = x_j / l_jj, then x_i -= l_ij y_j for i > j
+    const double xj = __shfl_sync(FULL, x, j) * inv;
+    const double xu = x - lij * xj;
+    x = (lane > j) ? xu : x;
+    x = (lane == j) ? xj : x;
   }
+  __syncwarp();
   if (lane < NV) {
 #pragma unroll
     for (int k = 0; k < NV; k++)
       if (k <= lane) H[lane * LD + k] = a[k];
   }
   __syncwarp();
-}
-
-// x (one entry per lane, lanes >= NV ignored) <- H^-1 x with H = L L'
-__device__ __noinline__ double chol_solve(const double* H, const double* invd, double x, int lane) {
-  const unsigned FULL = 0xffffffffu;
-  for (int k = 0; k < NV; k++) {
-    const double xk = __shfl_sync(FULL, x, k) * invd[k];
-    if (lane == k) x = xk;
-    else if (lane > k && lane < NV) x -= H[lane * LD + k] * xk;
-  }
+#pragma unroll
   for (int k = NV - 1; k >= 0; k--) {
-    const double xk = __shfl_sync(FULL, x, k) * invd[k];
-    if (lane == k) x = xk;
-    else if (lane < k) x -= H[k * LD + lane] * xk;
+    const double xk = __shfl_sync(FULL, x, k) * invs[k];
+    const double xu = x - H[k * LD + row] * xk;
+    x = (lane < k) ? xu : x;
+    x = (lane == k) ? xk : x;
   }
-  return x;
+  return lane < NV ? x : 0.0;
 }
 
-__device__ __forceinline__ double mat_vec(const double* A, const double* v, int lane) {
+__device__ __noinline__ double mat_vec(const double* A, const double* v, int lane) {
   double s = 0.0;
   if (lane < NV) {
-#pragma unroll
+#pragma unroll 6
     for (int j = 0; j < NV; j++) s += A[lane * LD + j] * v[j];
   }
   return s;
@@ -197,14 +205,103 @@ __device__ unsigned long long hmj_phase_cycles[16];
 #define PH(i) do { } while (0)
 #endif
 
-__global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MIN_CTAS)
-k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
-  extern __shared__ double smem_raw[];
+// Geometry of the constraint rows of one env: limit rows first, then 10 pyramid edges per contact.
+struct RowMap {
+  int nlim, nefc, ncon;
+  const double* lim_sign;
+  const int32_t* lim_dof;
+  const double (*cfric)[5];
+  const double (*jbv)[6];
+  const double* vec;
+};
+
+// (J v)_r from the basis products jbv = Jb v (contacts) or the single +-1 entry (limits)
+__device__ __forceinline__ double row_value(const RowMap& R, int r) {
+  if (r < R.nlim) return R.lim_sign[r] * R.vec[R.lim_dof[r]];
+  const int q = r - R.nlim, c = q / 10, e = q - 10 * c, kk = 1 + (e >> 1);
+  const double mu = (e & 1) ? -R.cfric[c][kk - 1] : R.cfric[c][kk - 1];
+  return R.jbv[c][0] + mu * R.jbv[c][kk];
+}
+
+// jbv[c][k] = Jb[c][k] . vec
+__device__ __noinline__ void basis_dot(const double (*Jb)[6][LD], const double* vec, double (*jbv)[6], int ncon, int lane) {
+  __syncwarp();
+#pragma unroll 1
+  for (int t = lane; t < ncon * 6; t += 32) {
+    const int c = t / 6, kk = t - c * 6;
+    double s = 0.0;
+#pragma unroll 6
+    for (int d = 0; d < NV; d++) s += Jb[c][kk][d] * vec[d];
+    jbv[c][kk] = s;
+  }
+  __syncwarp();
+}
+
+// One evaluation of the line-search objective and its derivatives at p.alpha (mj_solver PrimalEval): the quadratic
+// of every row that is active at alpha, summed over the warp, plus the Gauss term (qg).
+__device__ __noinline__ void ls_eval(LsPnt& p, const double* rD, const double* rJaref, const double* rJv, int nefc,
+                                     double qg0, double qg1, double qg2, int lane) {
+  double a0 = 0, a1 = 0, a2 = 0;
+#pragma unroll 1
+  for (int r = lane; r < nefc; r += 32) {
+    const double ja = rJaref[r], jv = rJv[r];
+    if (ja + p.alpha * jv < 0) {
+      const double D = rD[r], DJ0 = D * ja;
+      a0 += 0.5 * (ja * DJ0);
+      a1 += jv * DJ0;
+      a2 += 0.5 * (jv * D * jv);
+    }
+  }
+  const double q0 = qg0 + warp_sum(a0), q1 = qg1 + warp_sum(a1), q2 = qg2 + warp_sum(a2);
+  p.cost = p.alpha * p.alpha * q2 + p.alpha * q1 + q0;
+  p.d0 = 2 * p.alpha * q2 + q1;
+  p.d1 = 2 * q2;
+  if (p.d1 <= 0) p.d1 = HMJ_MINVAL;
+}
+
+// ---------------------------------------------------------------- classification
+// Warp per env: number of valid contact slots and whether any joint limit is active -> work class.
+// Class lists are filled with atomics (order is irrelevant: envs are independent); counters live in
+// B.solve_count[0..2] and are zeroed by hmj_launch_solve before this kernel.
+__global__ void __launch_bounds__(128) k_classify(const hmj_tables_t* __restrict__ T, hmj_buffers_t B) {
   const int lane = threadIdx.x & 31;
-  const int wib = threadIdx.x >> 5;
-  const int env = blockIdx.x * SOLVE_WARPS + wib;
+  const int env = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (env >= B.n) return;
-  SolveSmem& S = reinterpret_cast<SolveSmem*>(smem_raw)[wib];
+  const unsigned FULL = 0xffffffffu;
+  const hmj_model_t& M = T->m;
+  const hmj_params_t* P = B.params + env;
+  const double* slots = B.slots + (size_t)env * HMJ_NSLOT * HMJ_SLOT_DOUBLES;
+  int ncon = 0;
+  for (int base = 0; base < HMJ_NSLOT; base += 32) {
+    const int s = base + lane;
+    const bool valid = (s < HMJ_NSLOT) && (slots[(size_t)s * HMJ_SLOT_DOUBLES + 7] != 0.0);
+    ncon += __popc(__ballot_sync(FULL, valid));
+  }
+  bool lim = false;
+  const int j = lane + 1;
+  if (j < HMJ_NJNT && M.jnt_limited[j]) {
+    const double margin = P->jnt_margin[j];
+    const double value = B.qpos[(size_t)env * HMJ_NQ + M.jnt_qposadr[j]];
+    lim = (-(P->jnt_range[j][0] - value) < margin) || (P->jnt_range[j][1] - value < margin);
+  }
+  const bool anylim = __any_sync(FULL, lim);
+  if (lane == 0) {
+    const int cls = (ncon == 0 && !anylim) ? 0 : (ncon <= SOLVE_SMALL_CON ? 1 : 2);
+    const int at = atomicAdd(&B.solve_count[cls], 1);
+    B.solve_list[(size_t)cls * B.n + at] = env;
+  }
+}
+
+// ---------------------------------------------------------------- the solver
+template <int MAXC>
+__global__ void __launch_bounds__(32, MAXC == 0 ? 24 : (MAXC <= SOLVE_SMALL_CON ? 14 : 6))
+k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
+  using Smem = SolveSmem<MAXC>;
+  extern __shared__ double smem_raw[];
+  if ((int)blockIdx.x >= B.solve_count[MAXC == 0 ? 0 : (MAXC <= SOLVE_SMALL_CON ? 1 : 2)]) return;
+  const int lane = threadIdx.x & 31;
+  const int env = B.solve_list[(size_t)(MAXC == 0 ? 0 : (MAXC <= SOLVE_SMALL_CON ? 1 : 2)) * B.n + blockIdx.x];
+  Smem& S = *reinterpret_cast<Smem*>(smem_raw);
   const hmj_model_t& M = T->m;
   const hmj_params_t* P = B.params + env;
   const unsigned FULL = 0xffffffffu;
@@ -215,6 +312,7 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
 
   // ---------------- load: dense M, qfrc_smooth, state
   for (int t = lane; t < NV * LD; t += 32) S.M[t] = 0.0;
+  for (int t = lane; t < NTRI; t += 32) { S.tri[t][0] = (unsigned char)T->tri_i[t]; S.tri[t][1] = (unsigned char)T->tri_j[t]; }
   __syncwarp();
   for (int e = lane; e < HMJ_NM; e += 32) {
     const double v = B.qM[(size_t)env * HMJ_NM + e];
@@ -234,452 +332,410 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
 
   // ---------------- qacc_smooth = M^-1 qfrc_smooth (dense Cholesky instead of the sparse L'DL: same result to rounding)
   for (int t = lane; t < NV * LD; t += 32) S.H[t] = S.M[t];
-  __syncwarp();
-  chol_factor(S.H, S.invd, T, lane);
-  const double qas = chol_solve(S.H, S.invd, qfs, lane);
-  if (lane < NV) { S.qas[lane] = qas; B.qacc_smooth[(size_t)env * NV + lane] = qas; }
-
+  const double qas = chol_factor_solve(S.H, qfs, lane);
+  if (lane < NV) B.qacc_smooth[(size_t)env * NV + lane] = qas;
   PH(1);
-  // ---------------- contacts: ordered compaction of the narrowphase slots (slot order == MuJoCo contact order)
-  int ncon = 0;
-  int status = 0;
-  {
-    const double* slots = B.slots + (size_t)env * HMJ_NSLOT * HMJ_SLOT_DOUBLES;
-    for (int base = 0; base < HMJ_NSLOT; base += 32) {
-      const int s = base + lane;
-      const bool valid = (s < HMJ_NSLOT) && (slots[(size_t)s * HMJ_SLOT_DOUBLES + 7] != 0.0);
-      const unsigned bal = __ballot_sync(FULL, valid);
-      const int idx = ncon + __popc(bal & ((1u << lane) - 1u));
-      if (valid && idx < HMJ_MAXCON) S.cslot[idx] = s;
-      ncon += __popc(bal);
-    }
-    if (ncon > HMJ_MAXCON) { ncon = HMJ_MAXCON; status |= HMJ_STATUS_CONTACTFULL; }
-  }
-  __syncwarp();
-  if (lane < ncon) {  // lane c owns contact c: parameters, frame (mj_contactParam, mju_makeFrame)
-    const int s = S.cslot[lane];
-    const double* sl = B.slots + ((size_t)env * HMJ_NSLOT + s) * HMJ_SLOT_DOUBLES;
-    const int k = T->slot_pair[s];
-    const int g1 = M.pair_geom1[k], g2 = M.pair_geom2[k];
-    hmj_contact_t* C = B.contact + (size_t)env * HMJ_MAXCON + lane;
-    double frame[9] = {sl[4], sl[5], sl[6], 0, 0, 0, 0, 0, 0};
-    make_frame(frame);
-    const double* f1 = (g1 == 0) ? P->floor_friction : M.geom_friction[g1];
-    const double* f2 = (g2 == 0) ? P->floor_friction : M.geom_friction[g2];
-    const double fr0 = fmax(f1[0], f2[0]), fr1 = fmax(f1[1], f2[1]), fr2 = fmax(f1[2], f2[2]);
-    const double fric[5] = {fr0, fr0, fr1, fr2, fr2};
-    double mix;
-    const double s1 = M.geom_solmix[g1], s2 = M.geom_solmix[g2];
-    if (s1 >= HMJ_MINVAL && s2 >= HMJ_MINVAL) mix = s1 / (s1 + s2);
-    else if (s1 < HMJ_MINVAL && s2 < HMJ_MINVAL) mix = 0.5;
-    else if (s1 < HMJ_MINVAL) mix = 0.0;
-    else mix = 1.0;
-    for (int q = 0; q < 2; q++)
-      C->solref[q] = (M.geom_solref[g1][0] > 0 && M.geom_solref[g2][0] > 0)
-                         ? mix * M.geom_solref[g1][q] + (1 - mix) * M.geom_solref[g2][q]
-                         : fmin(M.geom_solref[g1][q], M.geom_solref[g2][q]);
-    for (int q = 0; q < 5; q++) C->solimp[q] = mix * M.geom_solimp[g1][q] + (1 - mix) * M.geom_solimp[g2][q];
-    C->dist = sl[0];
-    for (int q = 0; q < 3; q++) { C->pos[q] = sl[1 + q]; S.cpos[lane][q] = sl[1 + q]; }
-    for (int q = 0; q < 9; q++) { C->frame[q] = frame[q]; S.cframe[lane][q] = frame[q]; }
-    for (int q = 0; q < 5; q++) { C->friction[q] = fric[q]; S.cfric[lane][q] = fric[q]; }
-    C->g1 = g1; C->g2 = g2;
-    C->geom1 = M.geom_mjid[g1]; C->geom2 = M.geom_mjid[g2];
-    S.cb1[lane] = M.geom_bodyid[g1]; S.cb2[lane] = M.geom_bodyid[g2];
-  }
-
-  // ---------------- joint-limit rows (mj_instantiateLimit): lane j-1 tests hinge joint j, lower then upper side
-  int nlim = 0;
-  {
-    bool act0 = false, act1 = false;
-    double dist0 = 0, dist1 = 0, margin = 0;
-    const int j = lane + 1;
-    if (j < HMJ_NJNT && M.jnt_limited[j]) {
-      margin = P->jnt_margin[j];
-      const double value = B.qpos[(size_t)env * HMJ_NQ + M.jnt_qposadr[j]];
-      dist0 = -(P->jnt_range[j][0] - value);  // side = -1
-      dist1 = P->jnt_range[j][1] - value;     // side = +1
-      act0 = dist0 < margin;
-      act1 = dist1 < margin;
-    }
-    const unsigned b0 = __ballot_sync(FULL, act0), b1 = __ballot_sync(FULL, act1);
-    const unsigned below = (1u << lane) - 1u;
-    const int before = __popc(b0 & below) + __popc(b1 & below);
-    if (act0) {
-      S.lim_dof[before] = M.jnt_dofadr[j]; S.lim_sign[before] = 1.0; S.lim_pos[before] = dist0;
-      S.lim_margin[before] = margin; S.lim_jnt[before] = j;
-    }
-    if (act1) {
-      const int r = before + (act0 ? 1 : 0);
-      S.lim_dof[r] = M.jnt_dofadr[j]; S.lim_sign[r] = -1.0; S.lim_pos[r] = dist1;
-      S.lim_margin[r] = margin; S.lim_jnt[r] = j;
-    }
-    nlim = __popc(b0) + __popc(b1);
-  }
-  const int nefc = nlim + 10 * ncon;
-  __syncwarp();
-  if (lane == 0) { B.ncon[env] = ncon; B.nefc[env] = nefc; }
 
   double qacc = qas;  // lanes < NV
   double qfc = 0.0;
-  int niter = 0;
+  int niter = 0, ncon = 0, nefc = 0, status = 0;
 
-  if (nefc > 0) {
-    PH(2);
-    // ---------------- contact-frame Jacobian basis Jb[c][k][d] (mj_jacDifPair rotated into the contact frame)
-    for (int t = lane; t < ncon * NV; t += 32) {
-      const int c = t / NV, d = t - c * NV;
-      const double sgn = (double)((T->body_dofmask[S.cb2[c]] >> d) & 1u) - (double)((T->body_dofmask[S.cb1[c]] >> d) & 1u);
-      double jp[3] = {0, 0, 0}, jr[3] = {0, 0, 0};
-      if (sgn != 0.0) {
-        const double* cd = B.cdof + ((size_t)env * NV + d) * 6;
-        const double cdv[6] = {cd[0], cd[1], cd[2], cd[3], cd[4], cd[5]};
-        const double off[3] = {S.cpos[c][0] - S.com[0], S.cpos[c][1] - S.com[1], S.cpos[c][2] - S.com[2]};
-        double tmp[3];
-        d_cross(tmp, cdv, off);
-        jp[0] = sgn * (cdv[3] + tmp[0]); jp[1] = sgn * (cdv[4] + tmp[1]); jp[2] = sgn * (cdv[5] + tmp[2]);
-        jr[0] = sgn * cdv[0]; jr[1] = sgn * cdv[1]; jr[2] = sgn * cdv[2];
+  if constexpr (MAXC > 0) {
+    // ---------------- contacts: ordered compaction of the narrowphase slots (slot order == MuJoCo contact order)
+    {
+      const double* slots = B.slots + (size_t)env * HMJ_NSLOT * HMJ_SLOT_DOUBLES;
+      for (int base = 0; base < HMJ_NSLOT; base += 32) {
+        const int s = base + lane;
+        const bool valid = (s < HMJ_NSLOT) && (slots[(size_t)s * HMJ_SLOT_DOUBLES + 7] != 0.0);
+        const unsigned bal = __ballot_sync(FULL, valid);
+        const int idx = ncon + __popc(bal & ((1u << lane) - 1u));
+        if (valid && idx < MAXC) S.cslot[idx] = s;
+        ncon += __popc(bal);
       }
-      const double* fr = S.cframe[c];
-#pragma unroll
-      for (int r = 0; r < 3; r++) {
-        S.Jb[c][r][d] = fr[3 * r] * jp[0] + fr[3 * r + 1] * jp[1] + fr[3 * r + 2] * jp[2];
-        S.Jb[c][3 + r][d] = fr[3 * r] * jr[0] + fr[3 * r + 1] * jr[1] + fr[3 * r + 2] * jr[2];
-      }
+      if (ncon > MAXC) { ncon = MAXC; status |= HMJ_STATUS_CONTACTFULL; }  // only reachable for MAXC == HMJ_MAXCON
     }
     __syncwarp();
+    if (lane < ncon) {  // lane c owns contact c: parameters, frame (mj_contactParam, mju_makeFrame)
+      const int s = S.cslot[lane];
+      const double* sl = B.slots + ((size_t)env * HMJ_NSLOT + s) * HMJ_SLOT_DOUBLES;
+      const int k = T->slot_pair[s];
+      const int g1 = M.pair_geom1[k], g2 = M.pair_geom2[k];
+      hmj_contact_t* C = B.contact + (size_t)env * HMJ_MAXCON + lane;
+      double frame[9] = {sl[4], sl[5], sl[6], 0, 0, 0, 0, 0, 0};
+      make_frame(frame);
+      const double* f1 = (g1 == 0) ? P->floor_friction : M.geom_friction[g1];
+      const double* f2 = (g2 == 0) ? P->floor_friction : M.geom_friction[g2];
+      const double fr0 = fmax(f1[0], f2[0]), fr1 = fmax(f1[1], f2[1]), fr2 = fmax(f1[2], f2[2]);
+      const double fric[5] = {fr0, fr0, fr1, fr2, fr2};
+      double mix;
+      const double s1 = M.geom_solmix[g1], s2 = M.geom_solmix[g2];
+      if (s1 >= HMJ_MINVAL && s2 >= HMJ_MINVAL) mix = s1 / (s1 + s2);
+      else if (s1 < HMJ_MINVAL && s2 < HMJ_MINVAL) mix = 0.5;
+      else if (s1 < HMJ_MINVAL) mix = 0.0;
+      else mix = 1.0;
+      for (int q = 0; q < 2; q++)
+        C->solref[q] = (M.geom_solref[g1][0] > 0 && M.geom_solref[g2][0] > 0)
+                           ? mix * M.geom_solref[g1][q] + (1 - mix) * M.geom_solref[g2][q]
+                           : fmin(M.geom_solref[g1][q], M.geom_solref[g2][q]);
+      for (int q = 0; q < 5; q++) C->solimp[q] = mix * M.geom_solimp[g1][q] + (1 - mix) * M.geom_solimp[g2][q];
+      C->dist = sl[0];
+      S.cprm[lane][0] = sl[0];
+      for (int q = 0; q < 2; q++) S.cprm[lane][1 + q] = C->solref[q];
+      for (int q = 0; q < 5; q++) S.cprm[lane][3 + q] = C->solimp[q];
+      for (int q = 0; q < 3; q++) { C->pos[q] = sl[1 + q]; S.cpos[lane][q] = sl[1 + q]; }
+      for (int q = 0; q < 9; q++) { C->frame[q] = frame[q]; S.cframe[lane][q] = frame[q]; }
+      for (int q = 0; q < 5; q++) { C->friction[q] = fric[q]; S.cfric[lane][q] = fric[q]; }
+      C->g1 = g1; C->g2 = g2;
+      C->geom1 = M.geom_mjid[g1]; C->geom2 = M.geom_mjid[g2];
+      S.cb1[lane] = M.geom_bodyid[g1]; S.cb2[lane] = M.geom_bodyid[g2];
+    }
 
-    // ---------------- per-row constants in the owning lane's registers
-    double rD[NROWREG], rAref[NROWREG], rMu[NROWREG], rJaref[NROWREG], rJv[NROWREG];
-    double rq0[NROWREG], rq1[NROWREG], rq2[NROWREG];
-    int rInfo[NROWREG];  // limit: dof | 0x100 ; contact: c*8 + k
-#pragma unroll
-    for (int k = 0; k < NROWREG; k++) { rD[k] = 0; rAref[k] = 0; rMu[k] = 0; rJaref[k] = 0; rJv[k] = 0; rq0[k] = rq1[k] = rq2[k] = 0; rInfo[k] = 0; }
+    // ---------------- joint-limit rows (mj_instantiateLimit): lane j-1 tests hinge joint j, lower then upper side
+    int nlim = 0;
+    {
+      bool act0 = false, act1 = false;
+      double dist0 = 0, dist1 = 0, margin = 0;
+      const int j = lane + 1;
+      if (j < HMJ_NJNT && M.jnt_limited[j]) {
+        margin = P->jnt_margin[j];
+        const double value = B.qpos[(size_t)env * HMJ_NQ + M.jnt_qposadr[j]];
+        dist0 = -(P->jnt_range[j][0] - value);  // side = -1
+        dist1 = P->jnt_range[j][1] - value;     // side = +1
+        act0 = dist0 < margin;
+        act1 = dist1 < margin;
+      }
+      const unsigned b0 = __ballot_sync(FULL, act0), b1 = __ballot_sync(FULL, act1);
+      const unsigned below = (1u << lane) - 1u;
+      const int before = __popc(b0 & below) + __popc(b1 & below);
+      if (act0) {
+        S.lim_dof[before] = M.jnt_dofadr[j]; S.lim_sign[before] = 1.0; S.lim_pos[before] = dist0;
+        S.lim_margin[before] = margin; S.lim_jnt[before] = j;
+      }
+      if (act1) {
+        const int r = before + (act0 ? 1 : 0);
+        S.lim_dof[r] = M.jnt_dofadr[j]; S.lim_sign[r] = -1.0; S.lim_pos[r] = dist1;
+        S.lim_margin[r] = margin; S.lim_jnt[r] = j;
+      }
+      nlim = __popc(b0) + __popc(b1);
+    }
+    nefc = nlim + 10 * ncon;
+    __syncwarp();
+    PH(2);
 
-    // basis products with a vector held in S.vec
-    auto basis_dot = [&]() {
-      for (int t = lane; t < ncon * 6; t += 32) {
-        const int c = t / 6, kk = t - c * 6;
-        double s = 0.0;
+    if (nefc > 0) {
+      // ---------------- contact-frame Jacobian basis Jb[c][k][d] (mj_jacDifPair rotated into the contact frame)
+#pragma unroll 1
+      for (int t = lane; t < ncon * NV; t += 32) {
+        const int c = t / NV, d = t - c * NV;
+        const double sgn = (double)((T->body_dofmask[S.cb2[c]] >> d) & 1u) - (double)((T->body_dofmask[S.cb1[c]] >> d) & 1u);
+        double jp[3] = {0, 0, 0}, jr[3] = {0, 0, 0};
+        if (sgn != 0.0) {
+          const double* cd = B.cdof + ((size_t)env * NV + d) * 6;
+          const double cdv[6] = {cd[0], cd[1], cd[2], cd[3], cd[4], cd[5]};
+          const double off[3] = {S.cpos[c][0] - S.com[0], S.cpos[c][1] - S.com[1], S.cpos[c][2] - S.com[2]};
+          double tmp[3];
+          d_cross(tmp, cdv, off);
+          jp[0] = sgn * (cdv[3] + tmp[0]); jp[1] = sgn * (cdv[4] + tmp[1]); jp[2] = sgn * (cdv[5] + tmp[2]);
+          jr[0] = sgn * cdv[0]; jr[1] = sgn * cdv[1]; jr[2] = sgn * cdv[2];
+        }
+        const double* fr = S.cframe[c];
 #pragma unroll
-        for (int d = 0; d < NV; d++) s += S.Jb[c][kk][d] * S.vec[d];
-        S.jbv[c][kk] = s;
+        for (int r = 0; r < 3; r++) {
+          S.Jb[c][r][d] = fr[3 * r] * jp[0] + fr[3 * r + 1] * jp[1] + fr[3 * r + 2] * jp[2];
+          S.Jb[c][3 + r][d] = fr[3 * r] * jr[0] + fr[3 * r + 1] * jr[1] + fr[3 * r + 2] * jr[2];
+        }
       }
       __syncwarp();
-    };
-    auto row_value = [&](int k) -> double {  // (J v)_r for the row in register slot k, after basis_dot()
-      const int info = rInfo[k];
-      if (info & 0x100) return rMu[k] * S.vec[info & 0xff];
-      const int c = info >> 3, kk = info & 7;
-      return S.jbv[c][0] + rMu[k] * S.jbv[c][kk];
-    };
 
-    // efc_vel = J qvel  -> aref ; D
-    if (lane < NV) S.vec[lane] = qvel;
-    __syncwarp();
-    basis_dot();
-#pragma unroll
-    for (int k = 0; k < NROWREG; k++) {
-      const int r = lane + 32 * k;
-      if (r < nefc) {
-        double R, KI, Bc, pos, margin;
+      RowMap R;
+      R.nlim = nlim; R.nefc = nefc; R.ncon = ncon;
+      R.lim_sign = S.lim_sign; R.lim_dof = S.lim_dof; R.cfric = S.cfric; R.jbv = S.jbv; R.vec = S.vec;
+
+      // ---------------- efc_vel = J qvel -> aref ; D  (mj_makeImpedance, mj_referenceConstraint)
+      if (lane < NV) S.vec[lane] = qvel;
+      basis_dot(S.Jb, S.vec, S.jbv, ncon, lane);
+#pragma unroll 1
+      for (int r = lane; r < nefc; r += 32) {
+        double Rr, KI, Bc, pos, margin, diag, scaleR;
+        const double *solref, *solimp;
         if (r < nlim) {
           const int j = S.lim_jnt[r];
-          rInfo[k] = 0x100 | S.lim_dof[r];
-          rMu[k] = S.lim_sign[r];
           pos = S.lim_pos[r]; margin = S.lim_margin[r];
-          row_impedance(M.jnt_solref[j], M.jnt_solimp[j], pos, margin, M.dof_invweight0[S.lim_dof[r]], h, &R, &KI, &Bc);
+          solref = M.jnt_solref[j]; solimp = M.jnt_solimp[j];
+          diag = M.dof_invweight0[S.lim_dof[r]];
+          scaleR = 1.0;
         } else {
-          const int c = (r - nlim) / 10, e = (r - nlim) - 10 * c;
-          const int kk = 1 + (e >> 1);
-          rInfo[k] = (c << 3) | kk;
-          rMu[k] = (e & 1) ? -S.cfric[c][kk - 1] : S.cfric[c][kk - 1];
-          const hmj_contact_t* C = B.contact + (size_t)env * HMJ_MAXCON + c;
-          pos = C->dist; margin = 0.0;
-          const int b1 = S.cb1[c], b2 = S.cb2[c];
-          const double tran = M.body_invweight0[b1][0] + M.body_invweight0[b2][0];
+          const int c = (r - nlim) / 10;
+          pos = S.cprm[c][0]; margin = 0.0;
+          solref = &S.cprm[c][1]; solimp = &S.cprm[c][3];
+          const double tran = M.body_invweight0[S.cb1[c]][0] + M.body_invweight0[S.cb2[c]][0];
           const double mu0 = S.cfric[c][0];
           // all edges share Rpy = 2 mu0^2 R(first edge); first edge: diagApprox = tran + mu0^2 tran
-          double R0;
-          row_impedance(C->solref, C->solimp, pos, margin, tran + mu0 * mu0 * tran, h, &R0, &KI, &Bc);
-          R = 2 * mu0 * mu0 * R0;
+          diag = tran + mu0 * mu0 * tran;
+          scaleR = 2 * mu0 * mu0;
         }
-        rD[k] = 1 / R;
-        const double vel = row_value(k);
-        rAref[k] = -Bc * vel - KI * (pos - margin);
-#ifdef HMJ_TRACE
-        if (env == HMJ_TRACE) printf("GPU row %d D %.17g aref %.17g vel %.17g pos %.17g\n", r, rD[k], rAref[k], vel, pos);
-#endif
-      }
-    }
-    __syncwarp();
-
-    // helpers that need the row registers
-    auto jaref_of = [&](double* out) {  // out[k] = (J * S.vec)_r - aref_r
-      basis_dot();
-#pragma unroll
-      for (int k = 0; k < NROWREG; k++) {
-        const int r = lane + 32 * k;
-        out[k] = (r < nefc) ? row_value(k) - rAref[k] : 0.0;
-      }
-    };
-    auto constraint_cost = [&](const double* jar) -> double {
-      double s = 0.0;
-#pragma unroll
-      for (int k = 0; k < NROWREG; k++) {
-        const int r = lane + 32 * k;
-        if (r < nefc && jar[k] < 0) s += 0.5 * rD[k] * jar[k] * jar[k];
-      }
-      return warp_sum(s);
-    };
-
-    PH(3);
-    // ---------------- warmstart: best of (qacc_warmstart, qacc_smooth)
-    {
-      double jar[NROWREG];
-      if (lane < NV) S.vec[lane] = qws;
-      __syncwarp();
-      jaref_of(jar);
-      double cost_ws = constraint_cost(jar);
-      const double Ma_ws = mat_vec(S.M, S.vec, lane);
-      cost_ws += warp_sum(lane < NV ? 0.5 * (Ma_ws - qfs) * (qws - qas) : 0.0);
-      __syncwarp();
-      if (lane < NV) S.vec[lane] = qas;
-      __syncwarp();
-      jaref_of(jar);
-      const double cost_sm = constraint_cost(jar);
-      qacc = (cost_ws > cost_sm) ? qas : qws;
-      __syncwarp();
-    }
-
-    PH(4);
-    // ---------------- Newton iterations (mj_solNewton, primal)
-    const double scale = 1.0 / (M.meaninertia * (double)NV);
-    const double tolerance = M.tolerance;
-    double Ma, gauss = 0.0, grad = 0.0, mgrad = 0.0;
-
-    // Everything that depends on the current point: active set, cost, Hessian factor,
-    // qfrc_constraint, gradient and Newton direction.  Returns the total cost.
-    auto evaluate = [&]() -> double {
-      // ---- mj_constraintUpdate: cost, active set, forces
-      double s = 0.0;
-      double rF[NROWREG];
-#pragma unroll
-      for (int k = 0; k < NROWREG; k++) {
-        const int r = lane + 32 * k;
-        rF[k] = 0.0;
-        if (r < nefc) {
-          const double jar = rJaref[k];
-          const bool act = jar < 0;
-          if (act) { s += 0.5 * rD[k] * jar * jar; rF[k] = -rD[k] * jar; }
-          S.rowbuf[r] = act ? rD[k] : 0.0;
-        }
-      }
-      const double cost_c = warp_sum(s);
-      gauss = warp_sum(lane < NV ? 0.5 * (Ma - qfs) * (qacc - qas) : 0.0);
-      __syncwarp();
-
-      // ---- H = M + J' Dact J from the contact basis (lower triangle), then Cholesky
-      for (int t = lane; t < NV * (NV + 1) / 2; t += 32) {
-        const int i = T->tri_i[t], j = T->tri_j[t];
-        double acc = S.M[i * LD + j];
-        for (int c = 0; c < ncon; c++) {
-          const double* Da = S.rowbuf + nlim + 10 * c;
-          const double* fr = S.cfric[c];
-          const double Jni = S.Jb[c][0][i], Jnj = S.Jb[c][0][j];
-          double Wn = 0.0, tj = 0.0, ti = 0.0;
-#pragma unroll
-          for (int kk = 1; kk < 6; kk++) {
-            const double dp = Da[2 * (kk - 1)], dm = Da[2 * (kk - 1) + 1];
-            const double mu = fr[kk - 1];
-            const double wk = mu * (dp - dm), wkk = mu * mu * (dp + dm);
-            const double Jki = S.Jb[c][kk][i], Jkj = S.Jb[c][kk][j];
-            Wn += dp + dm;
-            tj += wk * Jkj;
-            ti += Jki * (wk * Jnj + wkk * Jkj);
-          }
-          acc += Jni * (Wn * Jnj + tj) + ti;
-        }
-        if (i == j) {
-          for (int r = 0; r < nlim; r++)
-            if (S.lim_dof[r] == i) acc += S.rowbuf[r];
-        }
-        S.H[i * LD + j] = acc;
-      }
-      __syncwarp();
-      PH(12);
-      chol_factor(S.H, S.invd, T, lane);
-      PH(13);
-
-      // ---- qfrc_constraint = J' f: publish row forces, gather on the contact basis
-#pragma unroll
-      for (int k = 0; k < NROWREG; k++) {
-        const int r = lane + 32 * k;
-        if (r < nefc) S.rowbuf[r] = rF[k];
-      }
-      __syncwarp();
-      for (int t = lane; t < ncon * 6; t += 32) {
-        const int c = t / 6, kk = t - c * 6;
-        const double* f = S.rowbuf + nlim + 10 * c;
-        double v;
-        if (kk == 0) {
-          v = 0.0;
-#pragma unroll
-          for (int e = 0; e < 10; e++) v += f[e];
-        } else {
-          v = S.cfric[c][kk - 1] * (f[2 * (kk - 1)] - f[2 * (kk - 1) + 1]);
-        }
-        S.jbv[c][kk] = v;
-      }
-      __syncwarp();
-      qfc = 0.0;
-      if (lane < NV) {
-        for (int c = 0; c < ncon; c++) {
-#pragma unroll
-          for (int kk = 0; kk < 6; kk++) qfc += S.Jb[c][kk][lane] * S.jbv[c][kk];
-        }
-        for (int r = 0; r < nlim; r++)
-          if (S.lim_dof[r] == lane) qfc += S.lim_sign[r] * S.rowbuf[r];
+        row_impedance(solref, solimp, pos, margin, diag, h, &Rr, &KI, &Bc);
+        if (r >= nlim) Rr = scaleR * Rr;
+        S.rD[r] = 1 / Rr;
+        const double vel = row_value(R, r);
+        S.rAref[r] = -Bc * vel - KI * (pos - margin);
       }
       __syncwarp();
 
-      // ---- gradient and Newton direction
-      grad = (lane < NV) ? Ma - qfs - qfc : 0.0;
-      PH(14);
-      mgrad = chol_solve(S.H, S.invd, grad, lane);
-      return cost_c + gauss;
-    };
-
-    if (lane < NV) S.vec[lane] = qacc;
-    __syncwarp();
-    Ma = mat_vec(S.M, S.vec, lane);
-    jaref_of(rJaref);
-    double cost = evaluate();
-    PH(5);
-    double search = -mgrad;
-
-    while (niter < M.iterations) {
-      // ---- exact line search along `search` (PrimalSearch)
-      double alpha = 0.0;
-      const double snorm = sqrt(warp_sum(lane < NV ? search * search : 0.0));
-      if (snorm < HMJ_MINVAL) break;
-      const double gtol = tolerance * M.ls_tolerance * snorm / scale;
-      __syncwarp();
-      if (lane < NV) S.vec[lane] = search;
-      __syncwarp();
-      const double Mv = mat_vec(S.M, S.vec, lane);
-      basis_dot();
-      const double qg0 = gauss;
-      const double qg1 = warp_sum(lane < NV ? search * Ma - qfs * search : 0.0);
-      const double qg2 = 0.5 * warp_sum(lane < NV ? search * Mv : 0.0);
-#pragma unroll
-      for (int k = 0; k < NROWREG; k++) {
-        const int r = lane + 32 * k;
-        if (r < nefc) {
-          rJv[k] = row_value(k);
-          const double DJ0 = rD[k] * rJaref[k];
-          rq0[k] = 0.5 * (rJaref[k] * DJ0);
-          rq1[k] = rJv[k] * DJ0;
-          rq2[k] = 0.5 * (rJv[k] * rD[k] * rJv[k]);
-        }
-      }
-      PH(6);
-      int lsiter = 0;
-      auto ls_eval = [&](LsPnt& p) {
-        double a0 = 0, a1 = 0, a2 = 0;
-#pragma unroll
-        for (int k = 0; k < NROWREG; k++) {
-          const int r = lane + 32 * k;
-          if (r < nefc && (rJaref[k] + p.alpha * rJv[k]) < 0) { a0 += rq0[k]; a1 += rq1[k]; a2 += rq2[k]; }
-        }
-        const double q0 = qg0 + warp_sum(a0), q1 = qg1 + warp_sum(a1), q2 = qg2 + warp_sum(a2);
-        p.cost = p.alpha * p.alpha * q2 + p.alpha * q1 + q0;
-        p.d0 = 2 * p.alpha * q2 + q1;
-        p.d1 = 2 * q2;
-        if (p.d1 <= 0) p.d1 = HMJ_MINVAL;
-        lsiter++;
+      // Jaref = J * S.vec - aref for every row
+      auto jaref_of = [&]() {
+        basis_dot(S.Jb, S.vec, S.jbv, ncon, lane);
+#pragma unroll 1
+        for (int r = lane; r < nefc; r += 32) S.rJaref[r] = row_value(R, r) - S.rAref[r];
       };
+      auto constraint_cost = [&]() -> double {
+        double s = 0.0;
+#pragma unroll 1
+        for (int r = lane; r < nefc; r += 32) {
+          const double jar = S.rJaref[r];
+          if (jar < 0) s += 0.5 * S.rD[r] * jar * jar;
+        }
+        return warp_sum(s);
+      };
+
+      PH(3);
+      // ---------------- warmstart: best of (qacc_warmstart, qacc_smooth)
       {
-        const int ls_iterations = M.ls_iterations;
-        LsPnt p0, p1, p2, pmid, p1next, p2next;
-        p0.alpha = 0; ls_eval(p0);
-        p1.alpha = p0.alpha - p0.d0 / p0.d1; ls_eval(p1);
-        if (p0.cost < p1.cost) p1 = p0;
-        bool found = false;
-        if (fabs(p1.d0) < gtol) { alpha = p1.alpha; found = true; }
-        if (!found) {
-          const int dir = (p1.d0 < 0 ? +1 : -1);
-          bool p2update = false;
-          p2 = p1;
-          while (p1.d0 * dir <= -gtol && lsiter < ls_iterations) {
-            p2 = p1; p2update = true;
-            p1.alpha -= p1.d0 / p1.d1; ls_eval(p1);
-            if (fabs(p1.d0) < gtol) { alpha = p1.alpha; found = true; break; }
+        __syncwarp();
+        if (lane < NV) S.vec[lane] = qws;
+        __syncwarp();
+        jaref_of();
+        double cost_ws = constraint_cost();
+        const double Ma_ws = mat_vec(S.M, S.vec, lane);
+        cost_ws += warp_sum(lane < NV ? 0.5 * (Ma_ws - qfs) * (qws - qas) : 0.0);
+        __syncwarp();
+        if (lane < NV) S.vec[lane] = qas;
+        __syncwarp();
+        jaref_of();
+        const double cost_sm = constraint_cost();
+        qacc = (cost_ws > cost_sm) ? qas : qws;
+        __syncwarp();
+      }
+      PH(4);
+
+      // ---------------- Newton iterations (mj_solNewton, primal)
+      const double scale = 1.0 / (M.meaninertia * (double)NV);
+      const double tolerance = M.tolerance;
+      const int max_iter = M.iterations, ls_iterations = M.ls_iterations;
+      const double ls_tolerance = M.ls_tolerance;
+      double Ma, Mv = 0.0, gauss = 0.0, grad = 0.0, mgrad = 0.0, search = 0.0, cost = 0.0, oldcost = 0.0;
+
+      __syncwarp();
+      if (lane < NV) S.vec[lane] = qacc;
+      __syncwarp();
+      Ma = mat_vec(S.M, S.vec, lane);
+      jaref_of();
+      bool first = true;
+#pragma unroll 1
+      for (;;) {
+        // ======== everything that depends on the current point: active set, cost, Hessian factor,
+        // qfrc_constraint, gradient and Newton direction
+        {
+          // ---- mj_constraintUpdate: cost and active set
+          double s = 0.0;
+          __syncwarp();
+#pragma unroll 1
+          for (int r = lane; r < nefc; r += 32) {
+            const double jar = S.rJaref[r], D = S.rD[r];
+            const bool act = jar < 0;
+            if (act) s += 0.5 * D * jar * jar;
+            S.rowbuf[r] = act ? D : 0.0;
           }
-          if (!found && (lsiter >= ls_iterations || !p2update)) { alpha = p1.alpha; found = true; }
-          if (!found) {
-            p2next = p1;
-            p1next.alpha = p1.alpha - p1.d0 / p1.d1; ls_eval(p1next);
-            while (lsiter < ls_iterations && !found) {
-              pmid.alpha = 0.5 * (p1.alpha + p2.alpha); ls_eval(pmid);
-              const LsPnt cand[3] = {p1next, p2next, pmid};
-              double bestcost = 0; int bestind = -1;
-              for (int i = 0; i < 3; i++)
-                if (fabs(cand[i].d0) < gtol && (bestind == -1 || cand[i].cost < bestcost)) { bestcost = cand[i].cost; bestind = i; }
-              if (bestind >= 0) { alpha = cand[bestind].alpha; found = true; break; }
-              int b1 = 0, b2 = 0;
-              for (int i = 0; i < 3; i++) {
-                if (p1.d0 < 0 && cand[i].d0 < 0 && p1.d0 < cand[i].d0) { p1 = cand[i]; b1 = 1; }
-                else if (p1.d0 > 0 && cand[i].d0 > 0 && p1.d0 > cand[i].d0) { p1 = cand[i]; b1 = 2; }
+          const double cost_c = warp_sum(s);
+          gauss = warp_sum(lane < NV ? 0.5 * (Ma - qfs) * (qacc - qas) : 0.0);
+          __syncwarp();
+          // ---- per-contact weights of the active edges in the 6-row basis
+#pragma unroll 1
+          for (int t = lane; t < ncon * 5; t += 32) {
+            const int c = t / 5, kk = 1 + (t - c * 5);
+            const double* Da = S.rowbuf + nlim + 10 * c;
+            const double dp = Da[2 * (kk - 1)], dm = Da[2 * (kk - 1) + 1], mu = S.cfric[c][kk - 1];
+            S.W[c][kk] = mu * (dp - dm);
+            S.W[c][5 + kk] = mu * mu * (dp + dm);
+          }
+          if (lane < ncon) {
+            const double* Da = S.rowbuf + nlim + 10 * lane;
+            double Wn = 0.0;
+#pragma unroll
+            for (int kk = 1; kk < 6; kk++) Wn += Da[2 * (kk - 1)] + Da[2 * (kk - 1) + 1];
+            S.W[lane][0] = Wn;
+          }
+          __syncwarp();
+          // ---- H = M + J' Dact J from the contact basis (lower triangle), then Cholesky
+#pragma unroll 1
+          for (int t = lane; t < NTRI; t += 32) {
+            const int i = S.tri[t][0], j = S.tri[t][1];
+            double acc = S.M[i * LD + j];
+#pragma unroll 1
+            for (int c = 0; c < ncon; c++) {
+              const double* Wc = S.W[c];
+              const double Jni = S.Jb[c][0][i], Jnj = S.Jb[c][0][j];
+              double tj = 0.0, ti = 0.0;
+#pragma unroll
+              for (int kk = 1; kk < 6; kk++) {
+                const double wk = Wc[kk], wkk = Wc[5 + kk];
+                const double Jki = S.Jb[c][kk][i], Jkj = S.Jb[c][kk][j];
+                tj += wk * Jkj;
+                ti += Jki * (wk * Jnj + wkk * Jkj);
               }
-              if (b1) { p1next.alpha = p1.alpha - p1.d0 / p1.d1; ls_eval(p1next); }
-              for (int i = 0; i < 3; i++) {
-                if (p2.d0 < 0 && cand[i].d0 < 0 && p2.d0 < cand[i].d0) { p2 = cand[i]; b2 = 1; }
-                else if (p2.d0 > 0 && cand[i].d0 > 0 && p2.d0 > cand[i].d0) { p2 = cand[i]; b2 = 2; }
-              }
-              if (b2) { p2next.alpha = p2.alpha - p2.d0 / p2.d1; ls_eval(p2next); }
-              if (!b1 && !b2) { alpha = pmid.alpha; found = true; break; }
+              acc += Jni * (Wc[0] * Jnj + tj) + ti;
             }
+            if (i == j) {
+#pragma unroll 1
+              for (int r = 0; r < nlim; r++)
+                if (S.lim_dof[r] == i) acc += S.rowbuf[r];
+            }
+            S.H[i * LD + j] = acc;
+          }
+          PH(12);
+          // ---- qfrc_constraint = J' f: publish row forces, gather on the contact basis
+#pragma unroll 1
+          for (int r = lane; r < nefc; r += 32) {
+            const double jar = S.rJaref[r];
+            S.rowbuf[r] = (jar < 0) ? -S.rD[r] * jar : 0.0;
+          }
+          __syncwarp();
+#pragma unroll 1
+          for (int t = lane; t < ncon * 6; t += 32) {
+            const int c = t / 6, kk = t - c * 6;
+            const double* f = S.rowbuf + nlim + 10 * c;
+            double v;
+            if (kk == 0) {
+              v = 0.0;
+#pragma unroll
+              for (int e = 0; e < 10; e++) v += f[e];
+            } else {
+              v = S.cfric[c][kk - 1] * (f[2 * (kk - 1)] - f[2 * (kk - 1) + 1]);
+            }
+            S.jbv[c][kk] = v;
+          }
+          __syncwarp();
+          qfc = 0.0;
+          if (lane < NV) {
+#pragma unroll 1
+            for (int c = 0; c < ncon; c++) {
+#pragma unroll
+              for (int kk = 0; kk < 6; kk++) qfc += S.Jb[c][kk][lane] * S.jbv[c][kk];
+            }
+#pragma unroll 1
+            for (int r = 0; r < nlim; r++)
+              if (S.lim_dof[r] == lane) qfc += S.lim_sign[r] * S.rowbuf[r];
+          }
+          __syncwarp();
+          // ---- gradient and Newton direction
+          grad = (lane < NV) ? Ma - qfs - qfc : 0.0;
+          PH(14);
+          mgrad = chol_factor_solve(S.H, grad, lane);
+          PH(13);
+          cost = cost_c + gauss;
+        }
+        if (!first) {
+          PH(8);
+          const double improvement = scale * (oldcost - cost);
+          const double gradient = scale * sqrt(warp_sum(grad * grad));
+          niter++;
+          if (improvement < tolerance || gradient < tolerance) break;
+        } else {
+          PH(5);
+        }
+        first = false;
+        search = -mgrad;
+        if (niter >= max_iter) break;
+
+        // ======== exact line search along `search` (PrimalSearch)
+        double alpha = 0.0;
+        const double snorm = sqrt(warp_sum(lane < NV ? search * search : 0.0));
+        if (snorm < HMJ_MINVAL) break;
+        const double gtol = tolerance * ls_tolerance * snorm / scale;
+        __syncwarp();
+        if (lane < NV) S.vec[lane] = search;
+        __syncwarp();
+        Mv = mat_vec(S.M, S.vec, lane);
+        basis_dot(S.Jb, S.vec, S.jbv, ncon, lane);
+        const double qg0 = gauss;
+        const double qg1 = warp_sum(lane < NV ? search * Ma - qfs * search : 0.0);
+        const double qg2 = 0.5 * warp_sum(lane < NV ? search * Mv : 0.0);
+#pragma unroll 1
+        for (int r = lane; r < nefc; r += 32) S.rJv[r] = row_value(R, r);
+        __syncwarp();
+        PH(6);
+        int lsiter = 0;
+        auto EV = [&](LsPnt& p) { ls_eval(p, S.rD, S.rJaref, S.rJv, nefc, qg0, qg1, qg2, lane); lsiter++; };
+        {
+          LsPnt p0, p1, p2, pmid, p1next, p2next;
+          p0.alpha = 0; EV(p0);
+          p1.alpha = p0.alpha - p0.d0 / p0.d1; EV(p1);
+          if (p0.cost < p1.cost) p1 = p0;
+          bool found = false;
+          if (fabs(p1.d0) < gtol) { alpha = p1.alpha; found = true; }
+          if (!found) {
+            const int dir = (p1.d0 < 0 ? +1 : -1);
+            bool p2update = false;
+            p2 = p1;
+#pragma unroll 1
+            while (p1.d0 * dir <= -gtol && lsiter < ls_iterations) {
+              p2 = p1; p2update = true;
+              p1.alpha -= p1.d0 / p1.d1; EV(p1);
+              if (fabs(p1.d0) < gtol) { alpha = p1.alpha; found = true; break; }
+            }
+            if (!found && (lsiter >= ls_iterations || !p2update)) { alpha = p1.alpha; found = true; }
             if (!found) {
-              if (p1.cost <= p2.cost && p1.cost < p0.cost) alpha = p1.alpha;
-              else if (p2.cost <= p1.cost && p2.cost < p0.cost) alpha = p2.alpha;
-              else alpha = 0.0;
+              p2next = p1;
+              p1next.alpha = p1.alpha - p1.d0 / p1.d1; EV(p1next);
+#pragma unroll 1
+              while (lsiter < ls_iterations && !found) {
+                pmid.alpha = 0.5 * (p1.alpha + p2.alpha); EV(pmid);
+                const LsPnt cand[3] = {p1next, p2next, pmid};
+                double bestcost = 0; int bestind = -1;
+                for (int i = 0; i < 3; i++)
+                  if (fabs(cand[i].d0) < gtol && (bestind == -1 || cand[i].cost < bestcost)) { bestcost = cand[i].cost; bestind = i; }
+                if (bestind >= 0) { alpha = cand[bestind].alpha; found = true; break; }
+                int b1 = 0, b2 = 0;
+                for (int i = 0; i < 3; i++) {
+                  if (p1.d0 < 0 && cand[i].d0 < 0 && p1.d0 < cand[i].d0) { p1 = cand[i]; b1 = 1; }
+                  else if (p1.d0 > 0 && cand[i].d0 > 0 && p1.d0 > cand[i].d0) { p1 = cand[i]; b1 = 2; }
+                }
+                if (b1) { p1next.alpha = p1.alpha - p1.d0 / p1.d1; EV(p1next); }
+                for (int i = 0; i < 3; i++) {
+                  if (p2.d0 < 0 && cand[i].d0 < 0 && p2.d0 < cand[i].d0) { p2 = cand[i]; b2 = 1; }
+                  else if (p2.d0 > 0 && cand[i].d0 > 0 && p2.d0 > cand[i].d0) { p2 = cand[i]; b2 = 2; }
+                }
+                if (b2) { p2next.alpha = p2.alpha - p2.d0 / p2.d1; EV(p2next); }
+                if (!b1 && !b2) { alpha = pmid.alpha; found = true; break; }
+              }
+              if (!found) {
+                if (p1.cost <= p2.cost && p1.cost < p0.cost) alpha = p1.alpha;
+                else if (p2.cost <= p1.cost && p2.cost < p0.cost) alpha = p2.alpha;
+                else alpha = 0.0;
+              }
             }
           }
         }
-      }
-#ifdef HMJ_TRACE
-      if (env == HMJ_TRACE && lane == 0) printf("GPU it %d alpha %.17g lsiter %d snorm %.17g gtol %.6g cost %.17g\n", niter, alpha, lsiter, snorm, gtol, cost);
-#endif
-      PH(7);
-      if (alpha == 0.0) break;
+        PH(7);
+        if (alpha == 0.0) break;
 
-      // ---- move to the new point, re-evaluate, test convergence
-      if (lane < NV) { qacc += alpha * search; Ma += alpha * Mv; }
-#pragma unroll
-      for (int k = 0; k < NROWREG; k++) rJaref[k] += alpha * rJv[k];
-      const double oldcost = cost;
-      cost = evaluate();
-      PH(8);
-      const double improvement = scale * (oldcost - cost);
-      const double gradient = scale * sqrt(warp_sum(grad * grad));
-      niter++;
-#ifdef HMJ_TRACE
-      if (env == HMJ_TRACE && lane == 0) printf("GPU    -> cost %.17g improvement %.6g gradient %.6g\n", cost, improvement, gradient);
-#endif
-      if (improvement < tolerance || gradient < tolerance) break;
-      search = -mgrad;
+        // ======== move to the new point
+        if (lane < NV) { qacc += alpha * search; Ma += alpha * Mv; }
+#pragma unroll 1
+        for (int r = lane; r < nefc; r += 32) S.rJaref[r] += alpha * S.rJv[r];
+        oldcost = cost;
+      }
     }
   }
 
   PH(9);
   // ---------------- results of mj_fwdConstraint
+  if (lane == 0) { B.ncon[env] = ncon; B.nefc[env] = nefc; B.niter[env] = niter; }
   if (lane < NV) {
     B.qacc[(size_t)env * NV + lane] = qacc;
     B.qfrc_constraint[(size_t)env * NV + lane] = qfc;
     B.warmstart[(size_t)env * NV + lane] = qacc;
   }
-  if (lane == 0) B.niter[env] = niter;
 
   // ---------------- mj_checkAcc
   if (__any_sync(FULL, lane < NV && d_is_bad(qacc))) {
@@ -699,9 +755,7 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
   for (int t = lane; t < NV * LD; t += 32) S.H[t] = S.M[t];
   __syncwarp();
   if (lane < NV) S.H[lane * LD + lane] += h * M.dof_damping[lane];
-  __syncwarp();
-  chol_factor(S.H, S.invd, T, lane);
-  const double qacc_e = chol_solve(S.H, S.invd, qfs + qfc, lane);
+  const double qacc_e = chol_factor_solve(S.H, qfs + qfc, lane);
   PH(11);
   if (lane < NV) {
     qvel += h * qacc_e;
@@ -729,15 +783,39 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
   if (lane == 0) B.time[env] += h;
 }
 
-void hmj_launch_solve(const hmj_tables_t* tab, hmj_buffers_t buf, int integrate, cudaStream_t stream) {
+template <int MAXC>
+static void launch_class(const hmj_tables_t* tab, hmj_buffers_t buf, int integrate, cudaStream_t stream) {
   static bool configured = false;
-  const size_t smem = sizeof(SolveSmem) * SOLVE_WARPS;
+  const size_t smem = sizeof(SolveSmem<MAXC>);
   if (!configured) {
-    cudaFuncSetAttribute(k_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(k_solve<MAXC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     configured = true;
   }
-  const int grid = (buf.n + SOLVE_WARPS - 1) / SOLVE_WARPS;
-  k_solve<<<grid, 32 * SOLVE_WARPS, smem, stream>>>(tab, buf, integrate);
+  k_solve<MAXC><<<buf.n, 32, smem, stream>>>(tab, buf, integrate);
+}
+
+// Four launches: classification, then one solver launch per class.  With side streams the many-contact class and the
+// unconstrained class run concurrently with the main class; otherwise the heavy class goes first.
+void hmj_launch_solve(const hmj_tables_t* tab, hmj_buffers_t buf, int integrate, cudaStream_t stream,
+                      const hmj_solve_ctx_t* ctx) {
+  cudaMemsetAsync(buf.solve_count, 0, 4 * sizeof(int32_t), stream);
+  k_classify<<<(buf.n + 3) / 4, 128, 0, stream>>>(tab, buf);
+  if (!ctx) {
+    launch_class<HMJ_MAXCON>(tab, buf, integrate, stream);
+    launch_class<SOLVE_SMALL_CON>(tab, buf, integrate, stream);
+    launch_class<0>(tab, buf, integrate, stream);
+    return;
+  }
+  cudaEventRecord(ctx->fork, stream);
+  cudaStreamWaitEvent(ctx->side[0], ctx->fork, 0);
+  cudaStreamWaitEvent(ctx->side[1], ctx->fork, 0);
+  launch_class<HMJ_MAXCON>(tab, buf, integrate, ctx->side[0]);
+  launch_class<SOLVE_SMALL_CON>(tab, buf, integrate, stream);
+  launch_class<0>(tab, buf, integrate, ctx->side[1]);
+  cudaEventRecord(ctx->join[0], ctx->side[0]);
+  cudaEventRecord(ctx->join[1], ctx->side[1]);
+  cudaStreamWaitEvent(stream, ctx->join[0], 0);
+  cudaStreamWaitEvent(stream, ctx->join[1], 0);
 }
 
 #ifdef HMJ_PHASE_PROF

