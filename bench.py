@@ -172,6 +172,71 @@ def run_reference(args):
     return 0
 
 
+
+# ---------------------------------------------------------------------------------------------- planner (metric M2)
+def plan_start_state(timestep=0.02, nsteps=50):
+    """C2/C4 start: qpos0, qvel = 0, 50 zero-control steps at the agent timestep, produced on the GPU."""
+    import humanoid_mujoco_b200 as hmj
+    b = hmj.HumanoidBatch(1)
+    p = b.default_params()
+    p["timestep"] = timestep
+    b.set_params(p)
+    b.set_state(np.array(b.model["qpos0"][0])[None], np.zeros((1, 18)), np.zeros(1), np.zeros((1, 18)))
+    b.step(np.zeros((1, 12)), nsteps)
+    q, v, t, _ = b.get_state()
+    b.close()
+    return q[0].copy(), v[0].copy(), float(t[0])
+
+
+def plan_bench(local, rank, world, iters, cpu):
+    """MJPC predictive-sampling iterations/s: one iteration = SamplingPlanner.OptimizePolicy (resample nominal, noise,
+    N rollouts of H-1 steps + 1 forward with fused policy/residual/cost, device argmin, winner exchange over the
+    process group, policy update).  C2: 10 x H=18 on one GPU; C4: 8192/8 = 1024 samples per GPU x H=100."""
+    import torch
+    import humanoid_mujoco_b200 as hmj
+    q, v, t = plan_start_state()
+    out = {}
+    for name, n_local, horizon, nit in (("C2", 10, 18, 5 * iters), ("C4_slice", 1024, 100, iters)):
+        if name == "C2" and (world > 1 and rank > 0):
+            continue
+        pl = hmj.SamplingPlanner(num_trajectory=n_local, device=local, seed=100 + rank)
+        if name == "C2":
+            pl.rank, pl.world = 0, 1   # the reference's own 10-rollout case is single-GPU by definition
+        pl.SetState(q, v, t)
+        for _ in range(3):
+            pl.OptimizePolicy(horizon)
+        l0 = pl.batch.kernel_launches
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(nit):
+            pl.OptimizePolicy(horizon)
+        pl.batch.sync()
+        dt = time.perf_counter() - t0
+        n_glob = n_local * (pl.world if name != "C2" else 1)
+        out[name] = {"iterations_per_s": nit / dt, "ms_per_iteration": 1e3 * dt / nit, "samples": n_glob, "horizon": horizon,
+                     "sample_steps_per_s": n_glob * (horizon - 1) * nit / dt, "iterations": nit,
+                     "kernel_launches_per_iteration": (pl.batch.kernel_launches - l0) / nit,
+                     "winner": int(pl.winner), "winner_return": float(pl.winner_return),
+                     "exchange": "none" if n_glob == n_local else "all_gather(cost,idx) + broadcast(winner spline) over NCCL"}
+        if cpu and rank == 0:
+            sys.path.insert(0, os.path.join(REPO, "oracle"))
+            from oracle_py import OracleBatch   # cpu_baseline leg: the oracle is the timed CPU implementation
+            nthreads = os.cpu_count() or 1
+            m = n_local if name == "C2" else 4 * nthreads
+            ob = OracleBatch(1)
+            ob.params["timestep"] = pl.timestep
+            state = np.concatenate([q, v])
+            vals = pl.candidate_values[:m] if pl.candidate_values.shape[0] >= m else np.resize(pl.candidate_values, (m,) + pl.candidate_values.shape[1:])
+            ob.rollouts(state, t, pl.candidate_times, vals, horizon, pl.interpolation_, nthreads)
+            reps = 20 if name == "C2" else 1
+            secs = sum(ob.rollouts(state, t, pl.candidate_times, vals, horizon, pl.interpolation_, nthreads)[2] for _ in range(reps)) / reps
+            cpu_it = (m / secs) / n_glob if name != "C2" else 1.0 / secs
+            out[name]["cpu_baseline"] = {"iterations_per_s": cpu_it, "cores": nthreads, "kind": "port",
+                                         "sample": f"{m} rollouts x H={horizon} on {nthreads} threads"
+                                                   + ("" if name == "C2" else f", scaled to {n_glob} samples per iteration")}
+        pl.batch.close()
+    return out
+
 # ---------------------------------------------------------------------------------------------- GPU arm
 def run_gpu(args):
     import torch
@@ -327,9 +392,13 @@ def run_gpu(args):
         fl = stats["flops_per_step"]
         line["fp64"].update({"flops_per_env_step_oracle_counters": fl, "achieved_tflops": value * fl / 1e12,
                              "frac": (value * fl / 1e12) / tf.value if tf.value else None})
+    env.close()
+    if not args.no_plan:
+        plan = plan_bench(local, rank, world, args.plan_iters, cpu=(world == 1 and not args.no_cpu))
+        if rank == 0:
+            line["plan"] = plan
     if rank == 0:
         print(json.dumps(line), flush=True)
-    env.close()
     if world > 1:
         dist.destroy_process_group()
     return 0
@@ -344,6 +413,8 @@ def main():
     ap.add_argument("--envs", type=int, default=ENVS_PER_GPU, help="environments per GPU")
     ap.add_argument("--cpu-steps", type=int, default=100, help="steps per env of the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-plan", action="store_true", help="skip the planner (M2) measurement")
+    ap.add_argument("--plan-iters", type=int, default=20, help="timed planner iterations of the C4 slice (C2 runs 5x as many)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

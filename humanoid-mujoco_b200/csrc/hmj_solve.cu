@@ -32,6 +32,13 @@
 #define NTRI (NV * (NV + 1) / 2)
 #define SOLVE_SMALL_CON 4       /* class 1 holds envs with at most this many contacts */
 
+// staging rows of chol_factor_solve (below)
+struct CholScratch {
+  double col[2][32 + NV];   // staged column of the current pivot, double-buffered by pivot parity (tail: read padding)
+  double xb[2][32];         // staged right-hand side
+  double invd[NV + 2];
+};
+
 template <int MAXC>
 struct SolveSmem {
   static constexpr int MC = MAXC > 0 ? MAXC : 1;
@@ -42,6 +49,7 @@ struct SolveSmem {
   double vec[NV + 2];           // vector being multiplied (search / qacc / qvel)
   double qfs[NV + 2];           // qfrc_smooth
   double com[4];
+  CholScratch chol;
   unsigned char tri[NTRI][2];   // (i, j <= i) of the t-th lower-triangle entry, row-major
   // ---- constrained classes only
   double Jb[MC][6][LD];
@@ -60,15 +68,66 @@ struct SolveSmem {
 
 // ---------------------------------------------------------------- dense helpers (warp cooperative)
 // x <- H^-1 x for the SPD matrix whose lower triangle sits in shared memory (H = L L').  One fused routine:
-//   * right-looking Cholesky with lane i holding row i in registers (static indices, fully unrolled): per pivot j
-//     every lane forms rsqrt(d_j) redundantly, scales its entry of column j and pulls l_kj from lane k with one
-//     shuffle per trailing column — 153 shuffle+FMA pairs, no shared-memory traffic or barriers on the chain;
-//   * the forward substitution rides along (column j of L is final when pivot j is done);
-//   * L is then published to shared memory once, because the backward substitution walks columns
-//     (lane i needs l_ki for every k > i), which the row-per-lane registers cannot provide.
-// The routine exists once (noinline) and is the only large straight-line block of the kernel (~20 KB of SASS).
-// On return H holds L (lower triangle; entries above the diagonal are garbage).
-__device__ __noinline__ double chol_factor_solve(double* H, double x, int lane) {
+//   * right-looking Cholesky with lane i holding row i in registers.  The pivot loop is ROLLED: the register row is
+//     rotated by one column per pivot (the rank-1 update writes a[m-1] <- a[m] - l_ij l_kj), so the pivot column is
+//     always a[0] and one ~110-instruction body serves all 18 pivots and stays in the L0 instruction cache (the fully
+//     unrolled form was 20 KB of straight-line code and lost ~40 % of its issue slots to instruction fetch:
+//     profiles/r1g_solve_lines.txt).  Late pivots update columns past 17, which only touch garbage registers.
+//   * the scaled column j is broadcast through a shared-memory staging row (one store + 17 broadcast loads per pivot
+//     instead of 34 shuffles);
+//   * the forward substitution rides along (column j of L is final when pivot j is done); L is published to shared
+//     memory for the backward substitution, which walks columns.
+// On return H holds L (lower triangle; entries above the diagonal are garbage), S.invd the reciprocal diagonal.
+__device__ __noinline__ double chol_factor_solve(double* H, CholScratch* C, double x, int lane) {
+  const unsigned FULL = 0xffffffffu;
+  const int row = lane < NV ? lane : NV - 1;
+  double a[NV];
+  __syncwarp();
+#pragma unroll
+  for (int k = 0; k < NV; k++) a[k] = H[row * LD + k];
+  double yv = 0.0;
+  double dj = __shfl_sync(FULL, a[0], 0);
+#pragma unroll 1
+  for (int j = 0; j < NV; j++) {
+    if (dj < HMJ_MINVAL) dj = HMJ_MINVAL;
+    const double inv = rsqrt(dj);
+    const double lij = (lane == j) ? dj * inv : a[0] * inv;   // a[0] is this row's entry of column j
+    // next pivot's diagonal, formed by its owner lane (j + 1) ahead of the column broadcast: this shuffle -> rsqrt ->
+    // scale -> FMA is the only loop-carried chain; the staged broadcast below runs beside the next rsqrt
+    const double dnext = a[1] - lij * lij;
+    dj = __shfl_sync(FULL, dnext, (j + 1) & 31);
+    double* col = C->col[j & 1];
+    double* xb = C->xb[j & 1];
+    col[lane] = lij;
+    xb[lane] = x;
+    if (lane >= j && lane < NV) H[lane * LD + j] = lij;
+    if (lane == 0) C->invd[j] = inv;
+    __syncwarp();
+    const double* cj = col + j;                                // cj[m] = l(j + m, j)
+#pragma unroll
+    for (int m = 1; m < NV; m++) a[m - 1] = a[m] - lij * cj[m];
+    // forward substitution step j: y_j = x_j / l_jj, then x_i -= l_ij y_j for i > j
+    const double xj = xb[j] * inv;
+    yv = (lane == j) ? xj : yv;
+    const double lm = (lane > j) ? lij : 0.0;
+    x = x - lm * xj;
+  }
+  __syncwarp();
+  // backward substitution: lane k publishes x_k = y_k / l_kk, lanes below it eliminate column k
+  x = yv;
+  double res = 0.0;
+#pragma unroll 3
+  for (int k = NV - 1; k >= 0; k--) {
+    const double xk = __shfl_sync(FULL, x, k) * C->invd[k];
+    res = (lane == k) ? xk : res;
+    const double l = (lane < k) ? H[k * LD + lane] : 0.0;
+    x = x - l * xk;
+  }
+  return lane < NV ? res : 0.0;
+}
+
+// Variant with the row held in statically indexed registers and shuffles for the column broadcast (fully unrolled).
+__device__ __noinline__ double chol_factor_solve_shfl(double* H, CholScratch* C, double x, int lane) {
   const unsigned FULL = 0xffffffffu;
   const int row = lane < NV ? lane : NV - 1;
   double a[NV], invs[NV];
@@ -88,7 +147,6 @@ __device__ __noinline__ double chol_factor_solve(double* H, double x, int lane) 
       const double lkj = __shfl_sync(FULL, lij, k);
       a[k] -= lij * lkj;
     }
-    // forward substitution step j: y_j = x_j / l_jj, then x_i -= l_ij y_j for i > j
     const double xj = __shfl_sync(FULL, x, j) * inv;
     const double xu = x - lij * xj;
     x = (lane > j) ? xu : x;
@@ -332,7 +390,7 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
 
   // ---------------- qacc_smooth = M^-1 qfrc_smooth (dense Cholesky instead of the sparse L'DL: same result to rounding)
   for (int t = lane; t < NV * LD; t += 32) S.H[t] = S.M[t];
-  const double qas = chol_factor_solve(S.H, qfs, lane);
+  const double qas = chol_factor_solve(S.H, &S.chol, qfs, lane);
   if (lane < NV) B.qacc_smooth[(size_t)env * NV + lane] = qas;
   PH(1);
 
@@ -630,7 +688,7 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
           // ---- gradient and Newton direction
           grad = (lane < NV) ? Ma - qfs - qfc : 0.0;
           PH(14);
-          mgrad = chol_factor_solve(S.H, grad, lane);
+          mgrad = chol_factor_solve(S.H, &S.chol, grad, lane);
           PH(13);
           cost = cost_c + gauss;
         }
@@ -755,7 +813,7 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
   for (int t = lane; t < NV * LD; t += 32) S.H[t] = S.M[t];
   __syncwarp();
   if (lane < NV) S.H[lane * LD + lane] += h * M.dof_damping[lane];
-  const double qacc_e = chol_factor_solve(S.H, qfs + qfc, lane);
+  const double qacc_e = chol_factor_solve(S.H, &S.chol, qfs + qfc, lane);
   PH(11);
   if (lane < NV) {
     qvel += h * qacc_e;

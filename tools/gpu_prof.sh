@@ -3,7 +3,7 @@
 # usage: tools/gpu_prof.sh <tag>   (run on the GPU box through gpurun; outputs under gpurun_out/)
 TAG=${1:-prof}
 mkdir -p gpurun_out
-CMD="python bench.py --steps 3 --warmup 3 --no-cpu"
+CMD="python bench.py --steps 3 --warmup 3 --no-cpu --no-plan"
 $CMD > gpurun_out/${TAG}_plain.log 2>&1 || { echo "plain run failed"; tail -5 gpurun_out/${TAG}_plain.log; exit 1; }
 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:'^k_' -s 2124 -c 96 --csv --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu1.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:'^k_(smooth|broad|narrow|classify|solve)' -s 2148 -c 16 -o gpurun_out/${TAG}_step $CMD > gpurun_out/${TAG}_ncu2.log 2>&1
