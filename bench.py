@@ -331,8 +331,14 @@ def run_gpu(args):
     dom = max(kern, key=kern.get)
     hbm_peak, peak_kind = load_peaks()
     achieved = BYTES_PER_ENV_STEP * n / (kern[dom] * 1e-3) / 1e9
+    traffic = None
+    try:   # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture (same 4096-env launch)
+        with open(os.path.join(REPO, "profiles", "traffic.json")) as f:
+            traffic = json.load(f).get("k_" + dom) if n == ENVS_PER_GPU else None
+    except Exception:
+        pass
     roofline = {"bound": "hbm", "kernel": "k_" + dom, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                "frac": achieved / hbm_peak, "traffic": None, "peak_kind": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)",
+                "frac": achieved / hbm_peak, "traffic": traffic, "peak_kind": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)",
                 "kernel_ms": kern, "algorithmic_bytes_per_env_step": BYTES_PER_ENV_STEP,
                 "note": "path is fp64-issue/latency bound, not HBM bound (SURVEY 8d): see the fp64 object"}
 
