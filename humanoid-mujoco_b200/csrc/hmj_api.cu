@@ -55,6 +55,17 @@ struct hmj_batch_ {
   size_t io_in_bytes = 0, io_out_bytes = 0;
   int launches = 0;
   hmj_solve_ctx_t solve_ctx{};       // side streams + events that overlap the solver classes
+  // Pipes: the physics chain of a step (smooth -> collide -> solve) is enqueued once per contiguous block of envs, each on
+  // its own stream, forked from / joined to the main stream inside the call.  Every stage is a single wave whose length is
+  // its slowest env, so stages of different pipes fill each other's tails (envs are independent: no data-path exchange).
+  struct Pipe {
+    hmj_buffers_t view{};
+    cudaStream_t stream = nullptr;
+    cudaEvent_t done = nullptr;
+    hmj_solve_ctx_t ctx{};
+  };
+  std::vector<Pipe> pipes;
+  cudaEvent_t pipe_fork = nullptr;
   // per-kernel CUDA-event profiling (hmj_batch_profile): events bracket every launch of a step
   bool profile = false;
   std::vector<cudaEvent_t> prof_events;  // 4 per step: before smooth, collide, solve, after solve
@@ -193,6 +204,58 @@ static int alloc_array(hmj_batch_* b, const char* name, Tp** out, size_t count) 
     if (rc_) { hmj_batch_destroy(b); return rc_; }                  \
   } while (0)
 
+
+// Buffers of envs [start, start + count) as a batch of their own (every per-env array is env-major).
+static hmj_buffers_t pipe_view(const hmj_buffers_t& B, int start, int count, int pipe, int group_total) {
+  hmj_buffers_t V = B;
+  const size_t s = (size_t)start;
+  V.n = count;
+  V.qpos += s * HMJ_NQ; V.qvel += s * HMJ_NV; V.time += s; V.warmstart += s * HMJ_NV; V.ctrl += s * HMJ_NU;
+  V.xfrc += s * 6; V.xfrc_body += s; V.params += s;
+  V.geom_xpos += s * HMJ_NGEOM * 3; V.geom_xmat += s * HMJ_NGEOM * 9; V.cdof += s * HMJ_NV * 6; V.com += s * 3;
+  V.qM += s * HMJ_NM; V.qfrc_smooth += s * HMJ_NV; V.sens += s * SENS_NUM; V.slots += s * HMJ_NSLOT * HMJ_SLOT_DOUBLES;
+  V.wq_count += 64 * pipe; V.wq_task += s * group_total;
+  V.solve_count += 4 * pipe; V.solve_list += 3 * s;
+  V.qacc += s * HMJ_NV; V.qacc_smooth += s * HMJ_NV; V.qfrc_constraint += s * HMJ_NV; V.contact += s * HMJ_MAXCON;
+  V.ncon += s; V.nefc += s; V.niter += s; V.status += s;
+  V.residual += s * HMJ_NRESIDUAL; V.cost_sum += s; V.cost_last += s; V.trace += s * 3;
+  return V;
+}
+
+#define HMJ_MAX_PIPES 8
+static int pipe_count_for(int n) {
+  const char* e = getenv("HMJ_PIPES");   // developer override
+  int p = e ? atoi(e) : (n >= 2048 ? 2 : 1);   // measured at 4096 envs: 2 pipes +4 %, 4 and 8 none (profiles/README.md)
+  if (p < 1) p = 1;
+  if (p > HMJ_MAX_PIPES) p = HMJ_MAX_PIPES;
+  while (p > 1 && n / p < 128) p--;
+  return p;
+}
+
+static int make_pipes(hmj_batch_* b) {
+  const int P = pipe_count_for(b->n);
+  if (P <= 1) return HMJ_OK;
+  const int group_total = b->tab_host->group_base[HMJ_NGROUP];
+  CK(cudaEventCreateWithFlags(&b->pipe_fork, cudaEventDisableTiming));
+  b->pipes.resize(P);
+  const int base = b->n / P, rem = b->n % P;
+  int start = 0;
+  for (int p = 0; p < P; p++) {
+    hmj_batch_::Pipe& pp = b->pipes[p];
+    const int count = base + (p < rem ? 1 : 0);
+    pp.view = pipe_view(b->buf, start, count, p, group_total);
+    start += count;
+    CK(cudaStreamCreateWithFlags(&pp.stream, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&pp.done, cudaEventDisableTiming));
+    for (int k = 0; k < 2; k++) {
+      CK(cudaStreamCreateWithFlags(&pp.ctx.side[k], cudaStreamNonBlocking));
+      CK(cudaEventCreateWithFlags(&pp.ctx.join[k], cudaEventDisableTiming));
+    }
+    CK(cudaEventCreateWithFlags(&pp.ctx.fork, cudaEventDisableTiming));
+  }
+  return HMJ_OK;
+}
+
 extern "C" void hmj_batch_destroy(hmj_batch_t* b) {
   if (!b) return;
   cudaSetDevice(b->device);
@@ -202,6 +265,16 @@ extern "C" void hmj_batch_destroy(hmj_batch_t* b) {
   if (b->io_host) cudaFreeHost(b->io_host);
   if (b->tab_dev) cudaFree(b->tab_dev);
   if (b->task_dev) cudaFree(b->task_dev);
+  for (auto& pp : b->pipes) {
+    for (int k = 0; k < 2; k++) {
+      if (pp.ctx.side[k]) cudaStreamDestroy(pp.ctx.side[k]);
+      if (pp.ctx.join[k]) cudaEventDestroy(pp.ctx.join[k]);
+    }
+    if (pp.ctx.fork) cudaEventDestroy(pp.ctx.fork);
+    if (pp.done) cudaEventDestroy(pp.done);
+    if (pp.stream) cudaStreamDestroy(pp.stream);
+  }
+  if (b->pipe_fork) cudaEventDestroy(b->pipe_fork);
   for (int k = 0; k < 2; k++) {
     if (b->solve_ctx.side[k]) cudaStreamDestroy(b->solve_ctx.side[k]);
     if (b->solve_ctx.join[k]) cudaEventDestroy(b->solve_ctx.join[k]);
@@ -264,9 +337,9 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
   ALLOC("qfrc_smooth", qfrc_smooth, N * HMJ_NV);
   ALLOC("sens", sens, N * SENS_NUM);
   ALLOC("slots", slots, N * HMJ_NSLOT * HMJ_SLOT_DOUBLES);
-  ALLOC("wq_count", wq_count, 64);
+  ALLOC("wq_count", wq_count, 64 * HMJ_MAX_PIPES);
   ALLOC("wq_task", wq_task, N * (size_t)b->tab_host->group_base[HMJ_NGROUP]);
-  ALLOC("solve_count", solve_count, 4);
+  ALLOC("solve_count", solve_count, 4 * HMJ_MAX_PIPES);
   ALLOC("solve_list", solve_list, 3 * N);
   ALLOC("qacc", qacc, N * HMJ_NV);
   ALLOC("qacc_smooth", qacc_smooth, N * HMJ_NV);
@@ -325,6 +398,10 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
     for (size_t i = 0; i < N; i++) memcpy(&q[i * HMJ_NQ], model->qpos0, sizeof(model->qpos0));
     CK(cudaMemcpyAsync(b->buf.qpos, q.data(), q.size() * sizeof(double), cudaMemcpyHostToDevice, b->stream));
     CK(cudaStreamSynchronize(b->stream));
+  }
+  {
+    int rc = make_pipes(b);
+    if (rc) { hmj_batch_destroy(b); return rc; }
   }
   *out = b;
   return HMJ_OK;
@@ -436,6 +513,28 @@ static void enqueue_step(hmj_batch_t* b, int integrate) {
   b->launches += 7;  // smooth, broad, narrow, classify, solve x 3 classes
 }
 
+// nsteps physics steps of the whole batch.  With pipes, every block of envs runs its own smooth -> collide -> solve
+// chain on its own stream for all nsteps; the main stream forks them and waits for all of them before anything else.
+static void enqueue_steps(hmj_batch_t* b, int integrate, int nsteps) {
+  if (nsteps <= 0) return;
+  if (b->profile || b->pipes.empty()) {
+    for (int s = 0; s < nsteps; s++) enqueue_step(b, integrate);
+    return;
+  }
+  cudaEventRecord(b->pipe_fork, b->stream);
+  for (auto& pp : b->pipes) cudaStreamWaitEvent(pp.stream, b->pipe_fork, 0);
+  for (int s = 0; s < nsteps; s++) {
+    for (auto& pp : b->pipes) hmj_launch_smooth(b->tab_dev, pp.view, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, pp.stream);
+    for (auto& pp : b->pipes) hmj_launch_collide(b->tab_dev, pp.view, pp.stream);
+    for (auto& pp : b->pipes) hmj_launch_solve(b->tab_dev, pp.view, integrate, pp.stream, &pp.ctx);
+    b->launches += 7 * (int)b->pipes.size();
+  }
+  for (auto& pp : b->pipes) {
+    cudaEventRecord(pp.done, pp.stream);
+    cudaStreamWaitEvent(b->stream, pp.done, 0);
+  }
+}
+
 // Per-kernel device time of the steps enqueued while profiling was on (CUDA events on the batch stream).
 extern "C" int hmj_batch_profile(hmj_batch_t* b, int enable) {
   if (!b) return fail(HMJ_ERR_ARG, "null batch%s");
@@ -470,7 +569,7 @@ extern "C" int hmj_batch_step_dev(hmj_batch_t* b, const double* ctrl_dev, int ns
   CK(cudaSetDevice(b->device));
   if (ctrl_dev && ctrl_dev != b->buf.ctrl)
     CK(cudaMemcpyAsync(b->buf.ctrl, ctrl_dev, (size_t)b->n * HMJ_NU * 8, cudaMemcpyDeviceToDevice, b->stream));
-  for (int s = 0; s < nsteps; s++) enqueue_step(b, 1);
+  enqueue_steps(b, 1, nsteps);
   CK(cudaGetLastError());
   return HMJ_OK;
 }
@@ -480,7 +579,7 @@ extern "C" int hmj_batch_step(hmj_batch_t* b, const double* ctrl, int nsteps) {
   CK(cudaSetDevice(b->device));
   int rc = h2d(b, b->buf.ctrl, ctrl, (size_t)b->n * HMJ_NU * 8);
   if (rc) return rc;
-  for (int s = 0; s < nsteps; s++) enqueue_step(b, 1);
+  enqueue_steps(b, 1, nsteps);
   CK(cudaStreamSynchronize(b->stream));
   CK(cudaGetLastError());
   return HMJ_OK;
@@ -489,7 +588,7 @@ extern "C" int hmj_batch_step(hmj_batch_t* b, const double* ctrl, int nsteps) {
 extern "C" int hmj_batch_forward(hmj_batch_t* b) {
   if (!b) return fail(HMJ_ERR_ARG, "null batch%s");
   CK(cudaSetDevice(b->device));
-  enqueue_step(b, 0);
+  enqueue_steps(b, 0, 1);
   CK(cudaStreamSynchronize(b->stream));
   CK(cudaGetLastError());
   return HMJ_OK;
@@ -634,7 +733,7 @@ extern "C" int hmj_env_step(hmj_batch_t* b, const double* ctrl, const int32_t* x
       (rc = h2d(b, b->buf.xfrc, xfrc, N * 6 * 8)) || (rc = h2d(b, d_prev, prev_action, 12 * N * 8)) ||
       (rc = h2d(b, d_lat, latest_action, 12 * N * 8)) || (rc = h2d(b, d_noise, noise, 31 * N * 8)))
     return rc;
-  for (int s = 0; s < nsteps; s++) enqueue_step(b, 1);
+  enqueue_steps(b, 1, nsteps);
   hmj_launch_env_obs_reward(b->tab_dev, b->buf, d_prev, d_lat, noise ? d_noise : nullptr, max_sim_time, d_obs, d_rew, d_term,
                             d_trunc, d_self, b->stream);
   b->launches += 1;
@@ -692,7 +791,7 @@ extern "C" int hmj_env_step_fused(hmj_batch_t* b, int has_action, int has_mask, 
     CK(cudaMemcpyAsync(b->io_dev, b->io_host, has_mask ? N * HMJ_NU * 8 + N * 4 : N * HMJ_NU * 8, cudaMemcpyHostToDevice, b->stream));
   const int32_t* mask = has_mask ? d_mask : nullptr;
   if (nsteps >= 0) hmj_launch_env_pre(b->buf, b->env, has_action ? d_action : nullptr, mask, rf, seed, b->stream);
-  for (int s = 0; s < nsteps; s++) enqueue_step(b, 1);
+  enqueue_steps(b, 1, nsteps);
   hmj_launch_env_obs_reward(b->tab_dev, b->buf, b->env.prev_action, b->env.latest_action, b->env.obs_noise, max_sim_time, d_obs,
                             d_rew, d_flags, d_flags + N, d_flags + 2 * N, b->stream);
   hmj_launch_env_post(b->buf, b->env, mask, d_obs, d_time, d_quat, b->stream);

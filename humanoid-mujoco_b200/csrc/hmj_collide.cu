@@ -824,17 +824,30 @@ __device__ __forceinline__ void narrow_hfield(const hmj_tables_t* __restrict__ T
 }
 
 // Persistent warps over the task groups (7 hfield groups keyed by hull, 28 mesh-mesh groups keyed by pair);
-// a work item is 32 consecutive tasks of one group, so the hull(s) a warp scans are uniform.
+// a work item is up to 32 consecutive tasks of one group, so the hull(s) a warp scans are uniform.
 __global__ void __launch_bounds__(NARROW_THREADS, NARROW_MIN_CTAS)
 k_narrow(const hmj_tables_t* __restrict__ T, hmj_buffers_t B) {
   __shared__ __align__(16) double sx[HMJ_NVERT_SMEM];
   __shared__ __align__(16) double sy[HMJ_NVERT_SMEM];
   __shared__ __align__(16) double sz[HMJ_NVERT_SMEM];
   const int lane = threadIdx.x & 31;
-  // work items: group g contributes ceil(count[g] / 32); groups are numbered across TWO registers per lane
+  // work items: group g contributes ceil(count[g] / isz); groups are numbered across TWO registers per lane.
+  // The item size isz (tasks per warp) is the smallest of 4 / 8 / 16 / 32 that still gives every item its own warp:
+  // a step has a few thousand queries against 1184 resident warps, and an MPR trip costs the whole warp ~25 n cycles
+  // lane-serial but only ~(n + 700) per 4 queries with the cooperative scan, so short items cut the query-chain
+  // latency that bounds this kernel.  Every query is independent: the item size never changes a result bit.
   const int c0 = B.wq_count[lane];
   const int c1 = (lane + 32 < HMJ_NGROUP) ? B.wq_count[lane + 32] : 0;
-  const int n0 = (c0 + 31) >> 5, n1 = (c1 + 31) >> 5;
+  const int nwarp = gridDim.x * (blockDim.x >> 5);
+  int shift = 2;
+  for (; shift < 5; shift++) {
+    int items = ((c0 + (1 << shift) - 1) >> shift) + ((c1 + (1 << shift) - 1) >> shift);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) items += __shfl_xor_sync(0xffffffffu, items, o);
+    if (items <= nwarp) break;
+  }
+  const int isz = 1 << shift;
+  const int n0 = (c0 + isz - 1) >> shift, n1 = (c1 + isz - 1) >> shift;
   int inc0 = n0;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, inc0, o); if (lane >= o) inc0 += v; }
@@ -847,15 +860,14 @@ k_narrow(const hmj_tables_t* __restrict__ T, hmj_buffers_t B) {
   const int gwarp = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;  // consecutive items (same group, similar cost) land on different SMs
   if (blockIdx.x >= total) return;  // whole CTA idle (its first warp has the smallest item index)
   stage_hulls(T, sx, sy, sz);
-  const int nwarp = gridDim.x * (blockDim.x >> 5);
   for (int item = gwarp; item < total; item += nwarp) {
     // group = number of groups whose inclusive prefix is <= item
     const int g = __popc(__ballot_sync(0xffffffffu, inc0 <= item)) + __popc(__ballot_sync(0xffffffffu, inc1 <= item));
     const int excl = (g == 0) ? 0 : (g <= 32 ? __shfl_sync(0xffffffffu, inc0, (g - 1) & 31) : __shfl_sync(0xffffffffu, inc1, (g - 1) & 31));
     const int cnt = (g < 32) ? __shfl_sync(0xffffffffu, c0, g & 31) : __shfl_sync(0xffffffffu, c1, g & 31);
-    const int q0 = (item - excl) * 32;
+    const int q0 = (item - excl) << shift;
     const int q = q0 + lane;
-    const bool valid = q < cnt;
+    const bool valid = lane < isz && q < cnt;
     const int2 task = B.wq_task[(size_t)T->group_base[g] * B.n + (valid ? q : q0)];  // idle lanes shadow the item's first task
     if (g < HMJ_NMESH) {
       const Hull h2 = {T->mesh_adr[g], T->mesh_npad[g]};
