@@ -213,7 +213,7 @@ static hmj_buffers_t pipe_view(const hmj_buffers_t& B, int start, int count, int
   V.qpos += s * HMJ_NQ; V.qvel += s * HMJ_NV; V.time += s; V.warmstart += s * HMJ_NV; V.ctrl += s * HMJ_NU;
   V.xfrc += s * 6; V.xfrc_body += s; V.params += s;
   V.geom_xpos += s * HMJ_NGEOM * 3; V.geom_xmat += s * HMJ_NGEOM * 9; V.cdof += s * HMJ_NV * 6; V.com += s * 3;
-  V.qM += s * HMJ_NM; V.qfrc_smooth += s * HMJ_NV; V.sens += s * SENS_NUM; V.slots += s * HMJ_NSLOT * HMJ_SLOT_DOUBLES;
+  V.qM += s * HMJ_NM; V.qfrc_smooth += s * HMJ_NV; V.sens += s * SENS_NUM; V.slots += s * HMJ_NSLOT * HMJ_SLOT_DOUBLES; V.slot_mask += s * 4;
   V.wq_count += 64 * pipe; V.wq_task += s * group_total;
   V.solve_count += 4 * pipe; V.solve_list += 3 * s;
   V.qacc += s * HMJ_NV; V.qacc_smooth += s * HMJ_NV; V.qfrc_constraint += s * HMJ_NV; V.contact += s * HMJ_MAXCON;
@@ -337,6 +337,7 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
   ALLOC("qfrc_smooth", qfrc_smooth, N * HMJ_NV);
   ALLOC("sens", sens, N * SENS_NUM);
   ALLOC("slots", slots, N * HMJ_NSLOT * HMJ_SLOT_DOUBLES);
+  ALLOC("slot_mask", slot_mask, N * 4);
   ALLOC("wq_count", wq_count, 64 * HMJ_MAX_PIPES);
   ALLOC("wq_task", wq_task, N * (size_t)b->tab_host->group_base[HMJ_NGROUP]);
   ALLOC("solve_count", solve_count, 4 * HMJ_MAX_PIPES);

@@ -8,7 +8,7 @@
 //   k_broad   thread per (pair, env), pair warp-uniform.  Mesh-mesh: bounding spheres.  Hfield-mesh: box test,
 //             hull AABB, strip walk over the prisms under the AABB, and the FIRST support call of every prism's
 //             MPR query (where 64 % of them end).  Survivors are appended to task lists grouped by hull
-//             (warp-aggregated atomics); every contact slot of the pair is cleared.
+//             (warp-aggregated atomics); the per-env slot bitmask (zeroed before the launch) marks the slots k_narrow fills.
 //   k_narrow  persistent warps; a work item is 32 tasks OF THE SAME GROUP, ONE MPR QUERY PER LANE.  The
 //             hull(s) are therefore warp-uniform: the exhaustive support scan reads each vertex once per
 //             warp (shared memory broadcast, fp64 SoA) while every lane evaluates it against its own
@@ -568,7 +568,7 @@ __device__ __forceinline__ void push_tasks(const hmj_tables_t* __restrict__ T, c
 //    prism that must be tested gets its slot ordinal and is pre-screened with the FIRST support call of
 //    ccdMPRPenetration's discoverPortal (64 % of all queries end there: dot(v1, dir) <= 0 -> no contact);
 //    survivors become MPR tasks, which restart the query from the top in k_narrow (same arithmetic).
-// Every contact slot of the pair is cleared here; k_narrow only sets the ones it fills.
+// The per-env slot bitmask is zeroed before this kernel; k_narrow sets the bits of the slots it fills.
 __global__ void __launch_bounds__(BROAD_THREADS)
 k_broad(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int npad) {
   __shared__ __align__(16) double sx[HMJ_NVERT_SMEM];
@@ -585,10 +585,7 @@ k_broad(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int npad) {
   const int g1 = M.pair_geom1[k], g2 = M.pair_geom2[k];
   const double* gx = B.geom_xpos + (size_t)env * HMJ_NGEOM * 3;
   const double* gm = B.geom_xmat + (size_t)env * HMJ_NGEOM * 9;
-  const int slot0 = T->pair_slot[k], nslot = T->pair_slot[k + 1] - slot0;
-  double* slots = B.slots + ((size_t)env * HMJ_NSLOT + slot0) * HMJ_SLOT_DOUBLES;
-  if (in)
-    for (int s = 0; s < nslot; s++) slots[(size_t)s * HMJ_SLOT_DOUBLES + 7] = 0.0;
+  const int nslot = T->pair_slot[k + 1] - T->pair_slot[k];
 
   if (g1 != 0) {
     const double dif0 = gx[g1 * 3] - gx[g2 * 3], dif1 = gx[g1 * 3 + 1] - gx[g2 * 3 + 1], dif2 = gx[g1 * 3 + 2] - gx[g2 * 3 + 2];
@@ -698,11 +695,12 @@ k_broad(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int npad) {
 }
 
 // ------------------------------------------------------------------ narrowphase
-__device__ __forceinline__ void write_slot(double* slot, double dist, const double* nrm, const double* pos) {
+__device__ __forceinline__ void write_slot(const hmj_buffers_t& B, int env, int s, double dist, const double* nrm, const double* pos) {
+  double* slot = B.slots + ((size_t)env * HMJ_NSLOT + s) * HMJ_SLOT_DOUBLES;
   slot[0] = dist;
   slot[1] = pos[0]; slot[2] = pos[1]; slot[3] = pos[2];
   slot[4] = nrm[0]; slot[5] = nrm[1]; slot[6] = nrm[2];
-  slot[7] = 1.0;
+  atomicOr(&B.slot_mask[(size_t)env * 4 + (s >> 5)], 1u << (s & 31));
 }
 
 // 32 mesh-mesh tasks of one pair (mjc_Convex, multiccd off): lane <-> environment.
@@ -747,8 +745,7 @@ __device__ __forceinline__ void narrow_mesh_mesh(const hmj_tables_t* __restrict_
       if (res != 1) {
         active = false;
         if (res == 0 && !c_vec_is_origin(m.pdir)) {
-          double* slot = B.slots + ((size_t)env * HMJ_NSLOT + T->pair_slot[k]) * HMJ_SLOT_DOUBLES;
-          write_slot(slot, 0.0 - m.depth, m.pdir, m.pos);
+          write_slot(B, env, T->pair_slot[k], 0.0 - m.depth, m.pdir, m.pos);
         }
       }
     }
@@ -814,8 +811,7 @@ __device__ __forceinline__ void narrow_hfield(const hmj_tables_t* __restrict__ T
           d_rot_vec_mat(cp, m.pos, mat1);
           cp[0] += pos1[0]; cp[1] += pos1[1]; cp[2] += pos1[2];
           if (!(nrm[0] == 0 && nrm[1] == 0 && nrm[2] == 0)) {
-            double* slot = B.slots + ((size_t)env * HMJ_NSLOT + T->pair_slot[k] + ord) * HMJ_SLOT_DOUBLES;
-            write_slot(slot, 0.0 - m.depth, nrm, cp);
+            write_slot(B, env, T->pair_slot[k] + ord, 0.0 - m.depth, nrm, cp);
           }
         }
       }
@@ -888,6 +884,7 @@ void hmj_launch_collide(const hmj_tables_t* tab, hmj_buffers_t buf, cudaStream_t
     narrow_grid = sms * (per_sm > 0 ? per_sm : 1);
   }
   cudaMemsetAsync(buf.wq_count, 0, 64 * sizeof(int32_t), stream);
+  cudaMemsetAsync(buf.slot_mask, 0, (size_t)buf.n * 4 * sizeof(uint32_t), stream);
   const int npad = (buf.n + BROAD_THREADS - 1) / BROAD_THREADS * BROAD_THREADS;  // CTAs are pair-uniform
   const long long nthread = (long long)npad * HMJ_NPAIR;
   k_broad<<<(int)(nthread / BROAD_THREADS), BROAD_THREADS, 0, stream>>>(tab, buf, npad);

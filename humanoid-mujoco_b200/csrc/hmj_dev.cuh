@@ -89,7 +89,8 @@ struct hmj_buffers_t {
   double* qM;         // [N][117]
   double* qfrc_smooth;// [N][18]
   double* sens;       // [N][16]    torso xpos(3), xquat body1 (4), xpos body1 z, site z..., see SENS_*
-  double* slots;      // [N][NSLOT][8]
+  double* slots;      // [N][NSLOT][8]  dist, pos[3], normal[3], (unused)
+  uint32_t* slot_mask;// [N][4]         bit s set: slot s holds a contact of this step (zeroed before k_broad)
   int32_t* wq_count;  // [64]       narrowphase tasks per group (zeroed every step)
   int2* wq_task;      // [group_base[NGROUP] * N]  (env, packed pair / slot ordinal / prism position)
   int32_t* solve_count; // [4]     envs per solver class (zeroed every step)

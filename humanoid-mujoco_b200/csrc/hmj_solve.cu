@@ -328,13 +328,11 @@ __global__ void __launch_bounds__(128) k_classify(const hmj_tables_t* __restrict
   const unsigned FULL = 0xffffffffu;
   const hmj_model_t& M = T->m;
   const hmj_params_t* P = B.params + env;
-  const double* slots = B.slots + (size_t)env * HMJ_NSLOT * HMJ_SLOT_DOUBLES;
-  int ncon = 0;
-  for (int base = 0; base < HMJ_NSLOT; base += 32) {
-    const int s = base + lane;
-    const bool valid = (s < HMJ_NSLOT) && (slots[(size_t)s * HMJ_SLOT_DOUBLES + 7] != 0.0);
-    ncon += __popc(__ballot_sync(FULL, valid));
-  }
+  const uint32_t mw = lane < 4 ? B.slot_mask[(size_t)env * 4 + lane] : 0u;
+  int ncon = __popc(mw);
+#pragma unroll
+  for (int o = 2; o > 0; o >>= 1) ncon += __shfl_xor_sync(FULL, ncon, o);
+  ncon = __shfl_sync(FULL, ncon, 0);
   bool lim = false;
   const int j = lane + 1;
   if (j < HMJ_NJNT && M.jnt_limited[j]) {
@@ -401,13 +399,13 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
   if constexpr (MAXC > 0) {
     // ---------------- contacts: ordered compaction of the narrowphase slots (slot order == MuJoCo contact order)
     {
-      const double* slots = B.slots + (size_t)env * HMJ_NSLOT * HMJ_SLOT_DOUBLES;
-      for (int base = 0; base < HMJ_NSLOT; base += 32) {
-        const int s = base + lane;
-        const bool valid = (s < HMJ_NSLOT) && (slots[(size_t)s * HMJ_SLOT_DOUBLES + 7] != 0.0);
-        const unsigned bal = __ballot_sync(FULL, valid);
+      const uint32_t mw = lane < 4 ? B.slot_mask[(size_t)env * 4 + lane] : 0u;
+#pragma unroll
+      for (int w = 0; w < 4; w++) {
+        const unsigned bal = __shfl_sync(FULL, mw, w);   // slots 32 w .. 32 w + 31
+        const bool valid = (bal >> lane) & 1u;
         const int idx = ncon + __popc(bal & ((1u << lane) - 1u));
-        if (valid && idx < MAXC) S.cslot[idx] = s;
+        if (valid && idx < MAXC) S.cslot[idx] = 32 * w + lane;
         ncon += __popc(bal);
       }
       if (ncon > MAXC) { ncon = MAXC; status |= HMJ_STATUS_CONTACTFULL; }  // only reachable for MAXC == HMJ_MAXCON
