@@ -66,6 +66,10 @@ struct hmj_batch_ {
   };
   std::vector<Pipe> pipes;
   cudaEvent_t pipe_fork = nullptr;
+  // step graphs: [0] forward only, [1] with integration
+  cudaGraphExec_t step_graph[2] = {nullptr, nullptr};
+  int graph_mode = 1;
+  bool warmed = false;
   // per-kernel CUDA-event profiling (hmj_batch_profile): events bracket every launch of a step
   bool profile = false;
   std::vector<cudaEvent_t> prof_events;  // 4 per step: before smooth, collide, solve, after solve
@@ -265,6 +269,8 @@ extern "C" void hmj_batch_destroy(hmj_batch_t* b) {
   if (b->io_host) cudaFreeHost(b->io_host);
   if (b->tab_dev) cudaFree(b->tab_dev);
   if (b->task_dev) cudaFree(b->task_dev);
+  for (int k = 0; k < 2; k++)
+    if (b->step_graph[k]) cudaGraphExecDestroy(b->step_graph[k]);
   for (auto& pp : b->pipes) {
     for (int k = 0; k < 2; k++) {
       if (pp.ctx.side[k]) cudaStreamDestroy(pp.ctx.side[k]);
@@ -400,6 +406,7 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
     CK(cudaMemcpyAsync(b->buf.qpos, q.data(), q.size() * sizeof(double), cudaMemcpyHostToDevice, b->stream));
     CK(cudaStreamSynchronize(b->stream));
   }
+  if (const char* e = getenv("HMJ_GRAPH")) b->graph_mode = atoi(e);   // developer override: 0 = direct launches
   {
     int rc = make_pipes(b);
     if (rc) { hmj_batch_destroy(b); return rc; }
@@ -514,25 +521,68 @@ static void enqueue_step(hmj_batch_t* b, int integrate) {
   b->launches += 7;  // smooth, broad, narrow, classify, solve x 3 classes
 }
 
-// nsteps physics steps of the whole batch.  With pipes, every block of envs runs its own smooth -> collide -> solve
-// chain on its own stream for all nsteps; the main stream forks them and waits for all of them before anything else.
-static void enqueue_steps(hmj_batch_t* b, int integrate, int nsteps) {
-  if (nsteps <= 0) return;
-  if (b->profile || b->pipes.empty()) {
-    for (int s = 0; s < nsteps; s++) enqueue_step(b, integrate);
+// The launches of ONE physics step of the whole batch, on the main stream (forking pipes / side streams and joining
+// them back before returning): this is what gets captured into the step graph.
+static void enqueue_one_step(hmj_batch_t* b, int integrate) {
+  if (b->pipes.empty()) {
+    hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, b->stream);
+    hmj_launch_collide(b->tab_dev, b->buf, b->stream);
+    hmj_launch_solve(b->tab_dev, b->buf, integrate, b->stream, &b->solve_ctx);
     return;
   }
   cudaEventRecord(b->pipe_fork, b->stream);
   for (auto& pp : b->pipes) cudaStreamWaitEvent(pp.stream, b->pipe_fork, 0);
-  for (int s = 0; s < nsteps; s++) {
-    for (auto& pp : b->pipes) hmj_launch_smooth(b->tab_dev, pp.view, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, pp.stream);
-    for (auto& pp : b->pipes) hmj_launch_collide(b->tab_dev, pp.view, pp.stream);
-    for (auto& pp : b->pipes) hmj_launch_solve(b->tab_dev, pp.view, integrate, pp.stream, &pp.ctx);
-    b->launches += 7 * (int)b->pipes.size();
-  }
+  for (auto& pp : b->pipes) hmj_launch_smooth(b->tab_dev, pp.view, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, pp.stream);
+  for (auto& pp : b->pipes) hmj_launch_collide(b->tab_dev, pp.view, pp.stream);
+  for (auto& pp : b->pipes) hmj_launch_solve(b->tab_dev, pp.view, integrate, pp.stream, &pp.ctx);
   for (auto& pp : b->pipes) {
     cudaEventRecord(pp.done, pp.stream);
     cudaStreamWaitEvent(b->stream, pp.done, 0);
+  }
+}
+
+// nsteps physics steps of the whole batch.  The step chain (7 kernels + 3 memsets per pipe, forks and joins) is
+// captured once per `integrate` flavour into a CUDA graph and replayed: one launch per step instead of ~15 API calls,
+// and the inter-kernel gaps shrink to the graph's dependency latency.  The first step of a batch runs un-captured
+// (it performs the launchers' one-time attribute / occupancy queries, which must not happen inside a capture).
+static void enqueue_steps(hmj_batch_t* b, int integrate, int nsteps) {
+  if (nsteps <= 0) return;
+  if (b->profile) {
+    for (int s = 0; s < nsteps; s++) enqueue_step(b, integrate);
+    return;
+  }
+  const int per_step = 7 * (b->pipes.empty() ? 1 : (int)b->pipes.size());
+  const int f = integrate ? 1 : 0;
+  for (int s = 0; s < nsteps; s++) {
+    b->launches += per_step;
+    if (b->graph_mode == 0 || !b->warmed) {   // graphs disabled, or first step ever
+      enqueue_one_step(b, integrate);
+      b->warmed = true;
+      continue;
+    }
+    if (!b->step_graph[f]) {
+      cudaGraph_t g = nullptr;
+      if (cudaStreamBeginCapture(b->stream, cudaStreamCaptureModeThreadLocal) == cudaSuccess) {
+        enqueue_one_step(b, integrate);
+        if (cudaStreamEndCapture(b->stream, &g) == cudaSuccess && g &&
+            cudaGraphInstantiate(&b->step_graph[f], g, 0) == cudaSuccess) {
+          cudaGraphDestroy(g);
+        } else {
+          if (g) cudaGraphDestroy(g);
+          b->step_graph[f] = nullptr;
+          b->graph_mode = 0;   // capture unavailable: keep launching directly
+          cudaGetLastError();
+          enqueue_one_step(b, integrate);
+          continue;
+        }
+      } else {
+        b->graph_mode = 0;
+        cudaGetLastError();
+        enqueue_one_step(b, integrate);
+        continue;
+      }
+    }
+    cudaGraphLaunch(b->step_graph[f], b->stream);
   }
 }
 
