@@ -98,31 +98,62 @@ __device__ __forceinline__ void local_gravity(const double* quat_in, double* g) 
   g[0] = -R[6]; g[1] = -R[7]; g[2] = -R[8];
 }
 
-__global__ void k_env_obs_reward(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const double* __restrict__ prev_action,
-                                 const double* __restrict__ latest_action, const double* __restrict__ noise, double max_sim_time,
-                                 double* __restrict__ obs, double* __restrict__ reward, int32_t* __restrict__ terminated,
-                                 int32_t* __restrict__ truncated, int32_t* __restrict__ self_collision) {
-  const int env = blockIdx.x * blockDim.x + threadIdx.x;
+// One warp per environment: lanes 0..11 own one actuator each (its two observation entries and its three exp() reward
+// terms), lanes 0..5 then the six symmetry terms, lane 12 the noisy-quaternion gravity of the observation, lane 0 the
+// remaining scalar terms and the final sum.  Every sum is formed by lane 0 in the reference's order (a = 0..11), so the
+// result is the same bits as the one-thread-per-env form; the 45 exp() calls are what made that form ~20 us of latency.
+#define OBS_WARPS 4
+__global__ void __launch_bounds__(32 * OBS_WARPS)
+k_env_obs_reward(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const double* __restrict__ prev_action,
+                 const double* __restrict__ latest_action, const double* __restrict__ noise, double max_sim_time,
+                 double* __restrict__ obs, double* __restrict__ reward, int32_t* __restrict__ terminated,
+                 int32_t* __restrict__ truncated, int32_t* __restrict__ self_collision) {
+  __shared__ double st[OBS_WARPS][5][HMJ_NU];   // tq, dc, reg, u per actuator; sym terms
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int env = blockIdx.x * OBS_WARPS + w;
   if (env >= B.n) return;
   const hmj_model_t& M = T->m;
   const double* qpos = B.qpos + (size_t)env * HMJ_NQ;
   const double* qvel = B.qvel + (size_t)env * HMJ_NV;
   const double* sens = B.sens + (size_t)env * SENS_NUM;
   const double* nz = noise ? noise + (size_t)env * 31 : nullptr;
-  // ---- observation (cpu_env.py:465-571), undelayed; JOINT_NAMES follow the actuator order
+  const double* tq = sens + SENS_ROOT_XQUAT;  // data.xquat[torso_idx]: one step stale (SURVEY App. C.1)
   double* o = obs + (size_t)env * 30;
-  for (int a = 0; a < HMJ_NU; a++) {
+  // ---- observation (cpu_env.py:465-571), undelayed; JOINT_NAMES follow the actuator order
+  if (lane < HMJ_NU) {
+    const int a = lane;
     o[a] = qpos[M.act_qposadr[a]] + (nz ? nz[a] : 0.0);
     o[12 + a] = qvel[M.act_dofadr[a]] + (nz ? nz[12 + a] : 0.0);
+    // ---- per-actuator terms of standupReward (reward_functions.py:247-374)
+    const int d = M.act_dofadr[a];
+    const double tau = B.qfrc_constraint[(size_t)env * HMJ_NV + d] + B.qfrc_smooth[(size_t)env * HMJ_NV + d];
+    const double ex = fmax(fabs(tau) - 1.0, 0.0);
+    const double lat = latest_action[(size_t)env * HMJ_NU + a] / (HMJ_PI / 2);
+    const double prv = prev_action[(size_t)env * HMJ_NU + a] / (HMJ_PI / 2);
+    const double dc = (lat - prv) * 500.0;
+    st[w][0][a] = scaled_exp(ex * ex);
+    st[w][1][a] = scaled_exp(dc * dc);
+    st[w][2][a] = scaled_exp(lat * lat);
+    st[w][3][a] = lat;
+  } else if (lane < HMJ_NU + 3) {
+    const int k = lane - HMJ_NU;
+    o[24 + k] = qvel[3 + k] + (nz ? nz[24 + k] : 0.0);
+  } else if (lane == HMJ_NU + 3) {
+    double nq[4] = {tq[0] + (nz ? nz[27] : 0.0), tq[1] + (nz ? nz[28] : 0.0), tq[2] + (nz ? nz[29] : 0.0), tq[3] + (nz ? nz[30] : 0.0)};
+    double g[3];
+    local_gravity(nq, g);
+    o[27] = g[0]; o[28] = g[1]; o[29] = g[2];
   }
-  for (int k = 0; k < 3; k++) o[24 + k] = qvel[3 + k] + (nz ? nz[24 + k] : 0.0);
-  const double* tq = sens + SENS_ROOT_XQUAT;  // data.xquat[torso_idx]: one step stale (SURVEY App. C.1)
-  double nq[4] = {tq[0] + (nz ? nz[27] : 0.0), tq[1] + (nz ? nz[28] : 0.0), tq[2] + (nz ? nz[29] : 0.0), tq[3] + (nz ? nz[30] : 0.0)};
-  double g[3];
-  local_gravity(nq, g);
-  o[27] = g[0]; o[28] = g[1]; o[29] = g[2];
-
-  // ---- standupReward (reward_functions.py:247-374)
+  __syncwarp();
+  if (lane < 6) {
+    const double* u = st[w][3];
+    // elbows equal; hip roll / hip pitch / knee / shoulder pitch / shoulder roll opposite
+    const int i1[6] = {5, 6, 7, 8, 3, 4}, i2[6] = {2, 9, 10, 11, 0, 1};
+    const double v = (lane == 0) ? (u[i1[0]] - u[i2[0]]) : (u[i1[lane]] + u[i2[lane]]);
+    st[w][4][lane] = scaled_exp(v * v);
+  }
+  __syncwarp();
+  if (lane != 0) return;
   double gl[3];
   local_gravity(tq, gl);
   const double z = sens[SENS_ROOT_Z];
@@ -137,30 +168,13 @@ __global__ void k_env_obs_reward(const hmj_tables_t* __restrict__ T, hmj_buffers
     r += (z <= z0) ? 0.0 : (z >= z1 ? 15.0 : (z - z0) / (z1 - z0) * 15.0);
   }
   double tq_sum = 0.0, dc_sum = 0.0, reg_sum = 0.0;
-  double u[HMJ_NU];
-  for (int a = 0; a < HMJ_NU; a++) {
-    const int d = M.act_dofadr[a];
-    const double tau = B.qfrc_constraint[(size_t)env * HMJ_NV + d] + B.qfrc_smooth[(size_t)env * HMJ_NV + d];
-    const double ex = fmax(fabs(tau) - 1.0, 0.0);
-    tq_sum += scaled_exp(ex * ex);
-    const double lat = latest_action[(size_t)env * HMJ_NU + a] / (HMJ_PI / 2);
-    const double prv = prev_action[(size_t)env * HMJ_NU + a] / (HMJ_PI / 2);
-    const double dc = (lat - prv) * 500.0;
-    dc_sum += scaled_exp(dc * dc);
-    reg_sum += scaled_exp(lat * lat);
-    u[a] = lat;
-  }
+  for (int a = 0; a < HMJ_NU; a++) { tq_sum += st[w][0][a]; dc_sum += st[w][1][a]; reg_sum += st[w][2][a]; }
   r += 2.5 * tq_sum / 12.0;
   r += 2.0 * dc_sum / 12.0;
   r += 0.5 * reg_sum / 12.0;
   {
     double sym = 0.0;
-    sym += scaled_exp((u[5] - u[2]) * (u[5] - u[2]));     // elbows equal
-    sym += scaled_exp((u[6] + u[9]) * (u[6] + u[9]));     // hip roll opposite
-    sym += scaled_exp((u[7] + u[10]) * (u[7] + u[10]));   // hip pitch
-    sym += scaled_exp((u[8] + u[11]) * (u[8] + u[11]));   // knee
-    sym += scaled_exp((u[3] + u[0]) * (u[3] + u[0]));     // shoulder pitch
-    sym += scaled_exp((u[4] + u[1]) * (u[4] + u[1]));     // shoulder roll
+    for (int k = 0; k < 6; k++) sym += st[w][4][k];
     r += 1.0 * sym / 6.0;
   }
   int selfc = 0;
@@ -180,8 +194,9 @@ __global__ void k_env_obs_reward(const hmj_tables_t* __restrict__ T, hmj_buffers
 void hmj_launch_env_obs_reward(const hmj_tables_t* tab, hmj_buffers_t buf, const double* prev_action, const double* latest_action,
                                const double* noise, double max_sim_time, double* obs, double* reward, int32_t* terminated,
                                int32_t* truncated, int32_t* self_collision, cudaStream_t stream) {
-  k_env_obs_reward<<<(buf.n + 127) / 128, 128, 0, stream>>>(tab, buf, prev_action, latest_action, noise, max_sim_time, obs, reward,
-                                                            terminated, truncated, self_collision);
+  k_env_obs_reward<<<(buf.n + OBS_WARPS - 1) / OBS_WARPS, 32 * OBS_WARPS, 0, stream>>>(tab, buf, prev_action, latest_action, noise,
+                                                                                       max_sim_time, obs, reward, terminated,
+                                                                                       truncated, self_collision);
 }
 
 // ------------------------------------------------------------------ CPUEnv prologue / delay FIFOs on the device
