@@ -589,10 +589,10 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
       bool first = true;
 #pragma unroll 1
       for (;;) {
-        // ======== everything that depends on the current point: active set, cost, Hessian factor,
-        // qfrc_constraint, gradient and Newton direction
+        // ======== part A of the evaluation at the current point (mj_constraintUpdate): cost, row forces,
+        // qfrc_constraint and the gradient.  The convergence test needs nothing else, so the Hessian of the point
+        // that ends the solve is never assembled or factorised (one factorisation per iteration, not per evaluation).
         {
-          // ---- mj_constraintUpdate: cost and active set
           double s = 0.0;
           __syncwarp();
 #pragma unroll 1
@@ -600,62 +600,12 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
             const double jar = S.rJaref[r], D = S.rD[r];
             const bool act = jar < 0;
             if (act) s += 0.5 * D * jar * jar;
-            S.rowbuf[r] = act ? D : 0.0;
+            S.rowbuf[r] = act ? -D * jar : 0.0;
           }
           const double cost_c = warp_sum(s);
           gauss = warp_sum(lane < NV ? 0.5 * (Ma - qfs) * (qacc - qas) : 0.0);
           __syncwarp();
-          // ---- per-contact weights of the active edges in the 6-row basis
-#pragma unroll 1
-          for (int t = lane; t < ncon * 5; t += 32) {
-            const int c = t / 5, kk = 1 + (t - c * 5);
-            const double* Da = S.rowbuf + nlim + 10 * c;
-            const double dp = Da[2 * (kk - 1)], dm = Da[2 * (kk - 1) + 1], mu = S.cfric[c][kk - 1];
-            S.W[c][kk] = mu * (dp - dm);
-            S.W[c][5 + kk] = mu * mu * (dp + dm);
-          }
-          if (lane < ncon) {
-            const double* Da = S.rowbuf + nlim + 10 * lane;
-            double Wn = 0.0;
-#pragma unroll
-            for (int kk = 1; kk < 6; kk++) Wn += Da[2 * (kk - 1)] + Da[2 * (kk - 1) + 1];
-            S.W[lane][0] = Wn;
-          }
-          __syncwarp();
-          // ---- H = M + J' Dact J from the contact basis (lower triangle), then Cholesky
-#pragma unroll 1
-          for (int t = lane; t < NTRI; t += 32) {
-            const int i = S.tri[t][0], j = S.tri[t][1];
-            double acc = S.M[i * LD + j];
-#pragma unroll 1
-            for (int c = 0; c < ncon; c++) {
-              const double* Wc = S.W[c];
-              const double Jni = S.Jb[c][0][i], Jnj = S.Jb[c][0][j];
-              double tj = 0.0, ti = 0.0;
-#pragma unroll
-              for (int kk = 1; kk < 6; kk++) {
-                const double wk = Wc[kk], wkk = Wc[5 + kk];
-                const double Jki = S.Jb[c][kk][i], Jkj = S.Jb[c][kk][j];
-                tj += wk * Jkj;
-                ti += Jki * (wk * Jnj + wkk * Jkj);
-              }
-              acc += Jni * (Wc[0] * Jnj + tj) + ti;
-            }
-            if (i == j) {
-#pragma unroll 1
-              for (int r = 0; r < nlim; r++)
-                if (S.lim_dof[r] == i) acc += S.rowbuf[r];
-            }
-            S.H[i * LD + j] = acc;
-          }
-          PH(12);
-          // ---- qfrc_constraint = J' f: publish row forces, gather on the contact basis
-#pragma unroll 1
-          for (int r = lane; r < nefc; r += 32) {
-            const double jar = S.rJaref[r];
-            S.rowbuf[r] = (jar < 0) ? -S.rD[r] * jar : 0.0;
-          }
-          __syncwarp();
+          // ---- qfrc_constraint = J' f: gather the row forces on the contact basis
 #pragma unroll 1
           for (int t = lane; t < ncon * 6; t += 32) {
             const int c = t / 6, kk = t - c * 6;
@@ -682,26 +632,73 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
             for (int r = 0; r < nlim; r++)
               if (S.lim_dof[r] == lane) qfc += S.lim_sign[r] * S.rowbuf[r];
           }
-          __syncwarp();
-          // ---- gradient and Newton direction
           grad = (lane < NV) ? Ma - qfs - qfc : 0.0;
-          PH(14);
-          mgrad = chol_factor_solve(S.H, &S.chol, grad, lane);
-          PH(13);
           cost = cost_c + gauss;
+          PH(14);
         }
         if (!first) {
-          PH(8);
           const double improvement = scale * (oldcost - cost);
           const double gradient = scale * sqrt(warp_sum(grad * grad));
           niter++;
           if (improvement < tolerance || gradient < tolerance) break;
-        } else {
-          PH(5);
         }
         first = false;
-        search = -mgrad;
         if (niter >= max_iter) break;
+
+        // ======== part B: Hessian of the active set, factorisation, Newton direction
+        {
+          __syncwarp();
+#pragma unroll 1
+          for (int r = lane; r < nefc; r += 32) S.rowbuf[r] = (S.rJaref[r] < 0) ? S.rD[r] : 0.0;
+          __syncwarp();
+          // ---- per-contact weights of the active edges in the 6-row basis
+#pragma unroll 1
+          for (int t = lane; t < ncon * 5; t += 32) {
+            const int c = t / 5, kk = 1 + (t - c * 5);
+            const double* Da = S.rowbuf + nlim + 10 * c;
+            const double dp = Da[2 * (kk - 1)], dm = Da[2 * (kk - 1) + 1], mu = S.cfric[c][kk - 1];
+            S.W[c][kk] = mu * (dp - dm);
+            S.W[c][5 + kk] = mu * mu * (dp + dm);
+          }
+          if (lane < ncon) {
+            const double* Da = S.rowbuf + nlim + 10 * lane;
+            double Wn = 0.0;
+#pragma unroll
+            for (int kk = 1; kk < 6; kk++) Wn += Da[2 * (kk - 1)] + Da[2 * (kk - 1) + 1];
+            S.W[lane][0] = Wn;
+          }
+          __syncwarp();
+          // ---- H = M + J' Dact J from the contact basis (lower triangle)
+#pragma unroll 1
+          for (int t = lane; t < NTRI; t += 32) {
+            const int i = S.tri[t][0], j = S.tri[t][1];
+            double acc = S.M[i * LD + j];
+#pragma unroll 1
+            for (int c = 0; c < ncon; c++) {
+              const double* Wc = S.W[c];
+              const double Jni = S.Jb[c][0][i], Jnj = S.Jb[c][0][j];
+              double tj = 0.0, ti = 0.0;
+#pragma unroll
+              for (int kk = 1; kk < 6; kk++) {
+                const double wk = Wc[kk], wkk = Wc[5 + kk];
+                const double Jki = S.Jb[c][kk][i], Jkj = S.Jb[c][kk][j];
+                tj += wk * Jkj;
+                ti += Jki * (wk * Jnj + wkk * Jkj);
+              }
+              acc += Jni * (Wc[0] * Jnj + tj) + ti;
+            }
+            if (i == j) {
+#pragma unroll 1
+              for (int r = 0; r < nlim; r++)
+                if (S.lim_dof[r] == i) acc += S.rowbuf[r];
+            }
+            S.H[i * LD + j] = acc;
+          }
+          PH(12);
+          mgrad = chol_factor_solve(S.H, &S.chol, grad, lane);
+          PH(13);
+        }
+        search = -mgrad;
 
         // ======== exact line search along `search` (PrimalSearch)
         double alpha = 0.0;
