@@ -217,7 +217,7 @@ static hmj_buffers_t pipe_view(const hmj_buffers_t& B, int start, int count, int
   V.qpos += s * HMJ_NQ; V.qvel += s * HMJ_NV; V.time += s; V.warmstart += s * HMJ_NV; V.ctrl += s * HMJ_NU;
   V.xfrc += s * 6; V.xfrc_body += s; V.params += s;
   V.geom_xpos += s * HMJ_NGEOM * 3; V.geom_xmat += s * HMJ_NGEOM * 9; V.cdof += s * HMJ_NV * 6; V.com += s * 3;
-  V.qM += s * HMJ_NM; V.qfrc_smooth += s * HMJ_NV; V.sens += s * SENS_NUM; V.slots += s * HMJ_NSLOT * HMJ_SLOT_DOUBLES; V.slot_mask += s * 4;
+  V.qM += s * HMJ_NM; V.qfrc_smooth += s * HMJ_NV; V.euler_factor += s * HMJ_FAC_DOUBLES; V.sens += s * SENS_NUM; V.slots += s * HMJ_NSLOT * HMJ_SLOT_DOUBLES; V.slot_mask += s * 4;
   V.wq_count += 64 * pipe; V.wq_task += s * group_total;
   V.solve_count += 4 * pipe; V.solve_list += 3 * s;
   V.qacc += s * HMJ_NV; V.qacc_smooth += s * HMJ_NV; V.qfrc_constraint += s * HMJ_NV; V.contact += s * HMJ_MAXCON;
@@ -256,6 +256,8 @@ static int make_pipes(hmj_batch_* b) {
       CK(cudaEventCreateWithFlags(&pp.ctx.join[k], cudaEventDisableTiming));
     }
     CK(cudaEventCreateWithFlags(&pp.ctx.fork, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&pp.ctx.fac_fork, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&pp.ctx.fac_done, cudaEventDisableTiming));
   }
   return HMJ_OK;
 }
@@ -277,6 +279,8 @@ extern "C" void hmj_batch_destroy(hmj_batch_t* b) {
       if (pp.ctx.join[k]) cudaEventDestroy(pp.ctx.join[k]);
     }
     if (pp.ctx.fork) cudaEventDestroy(pp.ctx.fork);
+    if (pp.ctx.fac_fork) cudaEventDestroy(pp.ctx.fac_fork);
+    if (pp.ctx.fac_done) cudaEventDestroy(pp.ctx.fac_done);
     if (pp.done) cudaEventDestroy(pp.done);
     if (pp.stream) cudaStreamDestroy(pp.stream);
   }
@@ -286,6 +290,8 @@ extern "C" void hmj_batch_destroy(hmj_batch_t* b) {
     if (b->solve_ctx.join[k]) cudaEventDestroy(b->solve_ctx.join[k]);
   }
   if (b->solve_ctx.fork) cudaEventDestroy(b->solve_ctx.fork);
+  if (b->solve_ctx.fac_fork) cudaEventDestroy(b->solve_ctx.fac_fork);
+  if (b->solve_ctx.fac_done) cudaEventDestroy(b->solve_ctx.fac_done);
   if (b->stream) cudaStreamDestroy(b->stream);
   delete b->tab_host;
   delete b;
@@ -310,6 +316,8 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
     CK(cudaEventCreateWithFlags(&b->solve_ctx.join[k], cudaEventDisableTiming));
   }
   CK(cudaEventCreateWithFlags(&b->solve_ctx.fork, cudaEventDisableTiming));
+  CK(cudaEventCreateWithFlags(&b->solve_ctx.fac_fork, cudaEventDisableTiming));
+  CK(cudaEventCreateWithFlags(&b->solve_ctx.fac_done, cudaEventDisableTiming));
   b->tab_host = new hmj_tables_t;
   build_tables(model, b->tab_host);
   CK(cudaMalloc((void**)&b->tab_dev, sizeof(hmj_tables_t)));
@@ -341,6 +349,7 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
   ALLOC("com", com, N * 3);
   ALLOC("qM", qM, N * HMJ_NM);
   ALLOC("qfrc_smooth", qfrc_smooth, N * HMJ_NV);
+  ALLOC("euler_factor", euler_factor, N * HMJ_FAC_DOUBLES);
   ALLOC("sens", sens, N * SENS_NUM);
   ALLOC("slots", slots, N * HMJ_NSLOT * HMJ_SLOT_DOUBLES);
   ALLOC("slot_mask", slot_mask, N * 4);
@@ -514,11 +523,12 @@ static void enqueue_step(hmj_batch_t* b, int integrate) {
   if (prof) prof_event(b);
   hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, b->stream);
   if (prof) prof_event(b);
+  hmj_launch_factor(b->tab_dev, b->buf, b->stream, &b->solve_ctx);
   hmj_launch_collide(b->tab_dev, b->buf, b->stream);
   if (prof) prof_event(b);
   hmj_launch_solve(b->tab_dev, b->buf, integrate, b->stream, &b->solve_ctx);
   if (prof) prof_event(b);
-  b->launches += 7;  // smooth, broad, narrow, classify, solve x 3 classes
+  b->launches += 8;  // smooth, factor, broad, narrow, classify, solve x 3 classes
 }
 
 // The launches of ONE physics step of the whole batch, on the main stream (forking pipes / side streams and joining
@@ -526,6 +536,7 @@ static void enqueue_step(hmj_batch_t* b, int integrate) {
 static void enqueue_one_step(hmj_batch_t* b, int integrate) {
   if (b->pipes.empty()) {
     hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, b->stream);
+    hmj_launch_factor(b->tab_dev, b->buf, b->stream, &b->solve_ctx);
     hmj_launch_collide(b->tab_dev, b->buf, b->stream);
     hmj_launch_solve(b->tab_dev, b->buf, integrate, b->stream, &b->solve_ctx);
     return;
@@ -533,6 +544,7 @@ static void enqueue_one_step(hmj_batch_t* b, int integrate) {
   cudaEventRecord(b->pipe_fork, b->stream);
   for (auto& pp : b->pipes) cudaStreamWaitEvent(pp.stream, b->pipe_fork, 0);
   for (auto& pp : b->pipes) hmj_launch_smooth(b->tab_dev, pp.view, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, pp.stream);
+  for (auto& pp : b->pipes) hmj_launch_factor(b->tab_dev, pp.view, pp.stream, &pp.ctx);
   for (auto& pp : b->pipes) hmj_launch_collide(b->tab_dev, pp.view, pp.stream);
   for (auto& pp : b->pipes) hmj_launch_solve(b->tab_dev, pp.view, integrate, pp.stream, &pp.ctx);
   for (auto& pp : b->pipes) {
@@ -551,7 +563,7 @@ static void enqueue_steps(hmj_batch_t* b, int integrate, int nsteps) {
     for (int s = 0; s < nsteps; s++) enqueue_step(b, integrate);
     return;
   }
-  const int per_step = 7 * (b->pipes.empty() ? 1 : (int)b->pipes.size());
+  const int per_step = 8 * (b->pipes.empty() ? 1 : (int)b->pipes.size());
   const int f = integrate ? 1 : 0;
   for (int s = 0; s < nsteps; s++) {
     b->launches += per_step;
@@ -651,8 +663,11 @@ extern "C" int hmj_batch_run_stage(hmj_batch_t* b, int stage) {
   switch (stage) {
     case HMJ_STAGE_SMOOTH: hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, b->stream); break;
     case HMJ_STAGE_COLLIDE: hmj_launch_collide(b->tab_dev, b->buf, b->stream); break;
-    case HMJ_STAGE_SOLVE: hmj_launch_solve(b->tab_dev, b->buf, 0, b->stream, &b->solve_ctx); break;
-    case HMJ_STAGE_SOLVE_INTEGRATE: hmj_launch_solve(b->tab_dev, b->buf, 1, b->stream, &b->solve_ctx); break;
+    case HMJ_STAGE_SOLVE:
+    case HMJ_STAGE_SOLVE_INTEGRATE:
+      hmj_launch_factor(b->tab_dev, b->buf, b->stream, &b->solve_ctx);
+      hmj_launch_solve(b->tab_dev, b->buf, stage == HMJ_STAGE_SOLVE_INTEGRATE ? 1 : 0, b->stream, &b->solve_ctx);
+      break;
     default: return fail(HMJ_ERR_ARG, "unknown stage%s");
   }
   b->launches += 1;
@@ -904,9 +919,10 @@ static int enqueue_rollouts(hmj_batch_t* b, const double* state, double time, co
     hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, HMJ_PLAN_COST | HMJ_PLAN_POLICY, b->spline_times_dev, spline_values_dev, nnode,
                       interpolation, 1, b->stream);
     if (record) { hmj_launch_plan_record(b->buf, b->rec, t, b->stream); b->launches += 1; }
+    hmj_launch_factor(b->tab_dev, b->buf, b->stream, &b->solve_ctx);
     hmj_launch_collide(b->tab_dev, b->buf, b->stream);
     hmj_launch_solve(b->tab_dev, b->buf, 1, b->stream, &b->solve_ctx);
-    b->launches += 7;
+    b->launches += 8;
   }
   // final mj_forward: only the sensors/residual matter, ctrl keeps the last action (trajectory.cc:190-206)
   hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, HMJ_PLAN_COST, nullptr, nullptr, 0, 0, 0, b->stream);

@@ -16,6 +16,7 @@
 #define HMJ_WARPS_PER_CTA 4
 #define HMJ_NSLOT (9 * HMJ_MAXCONPAIR + 28) /* contact slots per env: 9 hfield pairs x cap + 28 mesh pairs */
 #define HMJ_SLOT_DOUBLES 8                  /* dist, pos[3], normal[3], valid */
+#define HMJ_FAC_DOUBLES 192                 /* per-env Euler factor: 171 lower-triangle entries + 18 reciprocal pivots, padded */
 #define HMJ_NFAC 375                        /* LDL update triples (unused by the dense path, kept for tables) */
 #define HMJ_MESH_PAD 4
 #define HMJ_NGROUP (HMJ_NMESH + 28)           /* narrowphase task groups: 7 hulls (hfield prisms) + 28 mesh-mesh pairs */
@@ -88,6 +89,7 @@ struct hmj_buffers_t {
   double* com;        // [N][3]     subtree_com of the root body
   double* qM;         // [N][117]
   double* qfrc_smooth;// [N][18]
+  double* euler_factor; // [N][192]   Cholesky factor of M + h diag(damping): lower triangle, reciprocal diagonal
   double* sens;       // [N][16]    torso xpos(3), xquat body1 (4), xpos body1 z, site z..., see SENS_*
   double* slots;      // [N][NSLOT][8]  dist, pos[3], normal[3], (unused)
   uint32_t* slot_mask;// [N][4]         bit s set: slot s holds a contact of this step (zeroed before k_broad)
@@ -279,7 +281,10 @@ void hmj_launch_collide(const hmj_tables_t* tab, hmj_buffers_t buf, cudaStream_t
 struct hmj_solve_ctx_t {
   cudaStream_t side[2];
   cudaEvent_t fork, join[2];
+  cudaEvent_t fac_fork, fac_done;   // k_factor on side[0], forked after k_smooth, joined by hmj_launch_solve
 };
+// Contact-independent factorisations (qacc_smooth, Euler factor): call after hmj_launch_smooth, before hmj_launch_solve.
+void hmj_launch_factor(const hmj_tables_t* tab, hmj_buffers_t buf, cudaStream_t stream, const hmj_solve_ctx_t* ctx = nullptr);
 void hmj_launch_solve(const hmj_tables_t* tab, hmj_buffers_t buf, int integrate, cudaStream_t stream,
                       const hmj_solve_ctx_t* ctx = nullptr);
 

@@ -317,6 +317,84 @@ __device__ __noinline__ void ls_eval(LsPnt& p, const double* rD, const double* r
   if (p.d1 <= 0) p.d1 = HMJ_MINVAL;
 }
 
+// x <- (L L')^-1 x for a factor already in shared memory (lower triangle of H, reciprocal diagonal in invd)
+__device__ __noinline__ double chol_solve_only(const double* H, const double* invd, double x, int lane) {
+  const unsigned FULL = 0xffffffffu;
+  double yv = 0.0;
+#pragma unroll 3
+  for (int j = 0; j < NV; j++) {
+    const double xj = __shfl_sync(FULL, x, j) * invd[j];
+    yv = (lane == j) ? xj : yv;
+    const double l = (lane > j && lane < NV) ? H[lane * LD + j] : 0.0;
+    x = x - l * xj;
+  }
+  x = yv;
+  double res = 0.0;
+#pragma unroll 3
+  for (int k = NV - 1; k >= 0; k--) {
+    const double xk = __shfl_sync(FULL, x, k) * invd[k];
+    res = (lane == k) ? xk : res;
+    const double l = (lane < k) ? H[k * LD + lane] : 0.0;
+    x = x - l * xk;
+  }
+  return lane < NV ? res : 0.0;
+}
+
+// ---------------------------------------------------------------- factorisations that do not depend on contacts
+// Warp per env, launched on a side stream right after k_smooth so it runs beside the collision kernels:
+//   qacc_smooth = M^-1 qfrc_smooth  (dense Cholesky instead of the sparse L'DL: same result to rounding), and
+//   the factor of M + h diag(damping) that mj_Euler's implicit-damping solve needs after the constraint solve.
+// Both were the first / last thing every k_solve warp did; hoisting them removes two factorisations from each env's
+// serial chain and the start-up burst in which every resident warp factorised at once.
+#define FAC_DOUBLES HMJ_FAC_DOUBLES   /* lower triangle of L (tri order), reciprocal diagonal, padding */
+static_assert(FAC_DOUBLES >= NTRI + NV, "Euler factor record too small");
+struct FactorSmem {
+  double M[NV * LD];
+  double H[NV * LD];
+  CholScratch chol;
+};
+__global__ void __launch_bounds__(32) k_factor(const hmj_tables_t* __restrict__ T, hmj_buffers_t B) {
+  __shared__ FactorSmem S;
+  const int lane = threadIdx.x & 31;
+  const int env = blockIdx.x;
+  if (env >= B.n) return;
+  const hmj_model_t& M = T->m;
+  const double h = B.params[env].timestep;
+  for (int t = lane; t < NV * LD; t += 32) S.M[t] = 0.0;
+  __syncwarp();
+  for (int e = lane; e < HMJ_NM; e += 32) {
+    const double v = B.qM[(size_t)env * HMJ_NM + e];
+    const int i = T->M_row[e], j = T->M_col[e];
+    S.M[i * LD + j] = v;
+    S.M[j * LD + i] = v;
+  }
+  const double qfs = lane < NV ? B.qfrc_smooth[(size_t)env * NV + lane] : 0.0;
+  __syncwarp();
+  for (int t = lane; t < NV * LD; t += 32) S.H[t] = S.M[t];
+  const double qas = chol_factor_solve(S.H, &S.chol, qfs, lane);
+  if (lane < NV) B.qacc_smooth[(size_t)env * NV + lane] = qas;
+  __syncwarp();
+  for (int t = lane; t < NV * LD; t += 32) S.H[t] = S.M[t];
+  __syncwarp();
+  if (lane < NV) S.H[lane * LD + lane] += h * M.dof_damping[lane];
+  chol_factor_solve(S.H, &S.chol, 0.0, lane);
+  __syncwarp();
+  double* F = B.euler_factor + (size_t)env * FAC_DOUBLES;
+  for (int t = lane; t < NTRI; t += 32) F[t] = S.H[T->tri_i[t] * LD + T->tri_j[t]];
+  if (lane < NV) F[NTRI + lane] = S.chol.invd[lane];
+}
+
+void hmj_launch_factor(const hmj_tables_t* tab, hmj_buffers_t buf, cudaStream_t stream, const hmj_solve_ctx_t* ctx) {
+  if (!ctx) {
+    k_factor<<<buf.n, 32, 0, stream>>>(tab, buf);
+    return;
+  }
+  cudaEventRecord(ctx->fac_fork, stream);
+  cudaStreamWaitEvent(ctx->side[0], ctx->fac_fork, 0);
+  k_factor<<<buf.n, 32, 0, ctx->side[0]>>>(tab, buf);
+  cudaEventRecord(ctx->fac_done, ctx->side[0]);
+}
+
 // ---------------------------------------------------------------- classification
 // Warp per env: number of valid contact slots and whether any joint limit is active -> work class.
 // Class lists are filled with atomics (order is irrelevant: envs are independent); counters live in
@@ -366,30 +444,28 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
   long long ph_t0 = clock64();
 #endif
 
-  // ---------------- load: dense M, qfrc_smooth, state
-  for (int t = lane; t < NV * LD; t += 32) S.M[t] = 0.0;
+  // ---------------- load: dense M (constrained classes only), qfrc_smooth, state, qacc_smooth from k_factor
   for (int t = lane; t < NTRI; t += 32) { S.tri[t][0] = (unsigned char)T->tri_i[t]; S.tri[t][1] = (unsigned char)T->tri_j[t]; }
-  __syncwarp();
-  for (int e = lane; e < HMJ_NM; e += 32) {
-    const double v = B.qM[(size_t)env * HMJ_NM + e];
-    const int i = T->M_row[e], j = T->M_col[e];
-    S.M[i * LD + j] = v;
-    S.M[j * LD + i] = v;
+  if constexpr (MAXC > 0) {
+    for (int t = lane; t < NV * LD; t += 32) S.M[t] = 0.0;
+    __syncwarp();
+    for (int e = lane; e < HMJ_NM; e += 32) {
+      const double v = B.qM[(size_t)env * HMJ_NM + e];
+      const int i = T->M_row[e], j = T->M_col[e];
+      S.M[i * LD + j] = v;
+      S.M[j * LD + i] = v;
+    }
   }
-  double qfs = 0, qvel = 0, qws = 0;
+  double qfs = 0, qvel = 0, qws = 0, qas = 0;
   if (lane < NV) {
     qfs = B.qfrc_smooth[(size_t)env * NV + lane];
     qvel = B.qvel[(size_t)env * NV + lane];
     qws = B.warmstart[(size_t)env * NV + lane];
+    qas = B.qacc_smooth[(size_t)env * NV + lane];
     S.qfs[lane] = qfs;
   }
   if (lane < 3) S.com[lane] = B.com[(size_t)env * 3 + lane];
   __syncwarp();
-
-  // ---------------- qacc_smooth = M^-1 qfrc_smooth (dense Cholesky instead of the sparse L'DL: same result to rounding)
-  for (int t = lane; t < NV * LD; t += 32) S.H[t] = S.M[t];
-  const double qas = chol_factor_solve(S.H, &S.chol, qfs, lane);
-  if (lane < NV) B.qacc_smooth[(size_t)env * NV + lane] = qas;
   PH(1);
 
   double qacc = qas;  // lanes < NV
@@ -803,12 +879,16 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
   if (!integrate) return;
 
   PH(10);
-  // ---------------- mj_Euler with implicit joint damping: (M + h diag(b)) a = qfrc_smooth + qfrc_constraint
+  // ---------------- mj_Euler with implicit joint damping: (M + h diag(b)) a = qfrc_smooth + qfrc_constraint,
+  // with the factor k_factor left in B.euler_factor
   __syncwarp();
-  for (int t = lane; t < NV * LD; t += 32) S.H[t] = S.M[t];
+  {
+    const double* F = B.euler_factor + (size_t)env * FAC_DOUBLES;
+    for (int t = lane; t < NTRI; t += 32) S.H[S.tri[t][0] * LD + S.tri[t][1]] = F[t];
+    if (lane < NV) S.chol.invd[lane] = F[NTRI + lane];
+  }
   __syncwarp();
-  if (lane < NV) S.H[lane * LD + lane] += h * M.dof_damping[lane];
-  const double qacc_e = chol_factor_solve(S.H, &S.chol, qfs + qfc, lane);
+  const double qacc_e = chol_solve_only(S.H, S.chol.invd, qfs + qfc, lane);
   PH(11);
   if (lane < NV) {
     qvel += h * qacc_e;
@@ -851,6 +931,7 @@ static void launch_class(const hmj_tables_t* tab, hmj_buffers_t buf, int integra
 // unconstrained class run concurrently with the main class; otherwise the heavy class goes first.
 void hmj_launch_solve(const hmj_tables_t* tab, hmj_buffers_t buf, int integrate, cudaStream_t stream,
                       const hmj_solve_ctx_t* ctx) {
+  if (ctx) cudaStreamWaitEvent(stream, ctx->fac_done, 0);   // k_factor ran on side[0] beside the collision kernels
   cudaMemsetAsync(buf.solve_count, 0, 4 * sizeof(int32_t), stream);
   k_classify<<<(buf.n + 3) / 4, 128, 0, stream>>>(tab, buf);
   if (!ctx) {
