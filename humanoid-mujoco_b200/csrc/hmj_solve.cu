@@ -884,8 +884,16 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
   __syncwarp();
   {
     const double* F = B.euler_factor + (size_t)env * FAC_DOUBLES;
-    for (int t = lane; t < NTRI; t += 32) S.H[S.tri[t][0] * LD + S.tri[t][1]] = F[t];
-    if (lane < NV) S.chol.invd[lane] = F[NTRI + lane];
+    double fe[(NTRI + 31) / 32];
+    const double fi = F[NTRI + (lane < NV ? lane : 0)];
+#pragma unroll
+    for (int k = 0; k < (NTRI + 31) / 32; k++) fe[k] = (lane + 32 * k < NTRI) ? F[lane + 32 * k] : 0.0;   // all loads in flight at once
+#pragma unroll
+    for (int k = 0; k < (NTRI + 31) / 32; k++) {
+      const int t = lane + 32 * k;
+      if (t < NTRI) S.H[S.tri[t][0] * LD + S.tri[t][1]] = fe[k];
+    }
+    if (lane < NV) S.chol.invd[lane] = fi;
   }
   __syncwarp();
   const double qacc_e = chol_solve_only(S.H, S.chol.invd, qfs + qfc, lane);
