@@ -3,6 +3,7 @@
 Host-side mirror of the two reference seams:
   * `BatchedHumanoidEnv` — the CPUEnv reset/step/observation contract (simulation/cpu_env.py) over N
     lock-step environments;
+  * `B200VecEnv` — the `DummyVecEnv` seam (rl/train.py:134-151): auto-reset, `terminal_observation`, `set_attr`;
   * `SamplingPlanner` — mjpc's predictive-sampling planner (mjpc/planners/sampling/planner.cc) with
     `Rollouts` running as a CUDA grid over samples.
 Both call the same C ABI (include/hmj_b200.h) through ctypes.  There is no CPU fallback: importing the
@@ -15,8 +16,9 @@ from ._lib import HmjError, lib_path, load_library  # noqa: F401
 from .batch import HumanoidBatch, default_params, load_model  # noqa: F401
 from .env import BatchedHumanoidEnv  # noqa: F401
 from .planner import SamplingPlanner, SamplingPolicy, TimeSpline  # noqa: F401
+from .vec_env import B200VecEnv  # noqa: F401
 
 __all__ = [
     "HmjError", "load_library", "lib_path", "HumanoidBatch", "default_params", "load_model",
-    "BatchedHumanoidEnv", "SamplingPlanner", "SamplingPolicy", "TimeSpline",
+    "BatchedHumanoidEnv", "B200VecEnv", "SamplingPlanner", "SamplingPolicy", "TimeSpline",
 ]
