@@ -174,10 +174,10 @@ def run_reference(args):
 
 
 # ---------------------------------------------------------------------------------------------- planner (metric M2)
-def plan_start_state(timestep=0.02, nsteps=50):
+def plan_start_state(device=0, timestep=0.02, nsteps=50):
     """C2/C4 start: qpos0, qvel = 0, 50 zero-control steps at the agent timestep, produced on the GPU."""
     import humanoid_mujoco_b200 as hmj
-    b = hmj.HumanoidBatch(1)
+    b = hmj.HumanoidBatch(1, device=device)
     p = b.default_params()
     p["timestep"] = timestep
     b.set_params(p)
@@ -194,7 +194,7 @@ def plan_bench(local, rank, world, iters, cpu):
     process group, policy update).  C2: 10 x H=18 on one GPU; C4: 8192/8 = 1024 samples per GPU x H=100."""
     import torch
     import humanoid_mujoco_b200 as hmj
-    q, v, t = plan_start_state()
+    q, v, t = plan_start_state(local)
     out = {}
     for name, n_local, horizon, nit in (("C2", 10, 18, 5 * iters), ("C4_slice", 1024, 100, iters)):
         if name == "C2" and (world > 1 and rank > 0):
