@@ -78,7 +78,7 @@ struct SolveSmem {
 //   * the forward substitution rides along (column j of L is final when pivot j is done); L is published to shared
 //     memory for the backward substitution, which walks columns.
 // On return H holds L (lower triangle; entries above the diagonal are garbage), S.invd the reciprocal diagonal.
-__device__ __noinline__ double chol_factor_solve(double* H, CholScratch* C, double x, int lane) {
+__device__ __forceinline__ double chol_factor_solve(double* H, CholScratch* C, double x, int lane) {
   const unsigned FULL = 0xffffffffu;
   const int row = lane < NV ? lane : NV - 1;
   double a[NV];
@@ -258,7 +258,9 @@ struct LsPnt { double alpha, cost, d0, d1; };
 // mark to hmj_phase_cycles[phase]; read back with cudaMemcpyFromSymbol through hmj_debug_phase_cycles.
 #ifdef HMJ_PHASE_PROF
 __device__ unsigned long long hmj_phase_cycles[16];
-#define PH(i) do { const long long t_ = clock64(); if (lane == 0) atomicAdd(&hmj_phase_cycles[i], (unsigned long long)(t_ - ph_t0)); ph_t0 = clock64(); } while (0)
+__device__ unsigned int hmj_phase_env[16384][16];   // the same, per env (the tail is what bounds a single-wave launch)
+#define PH(i) do { const long long t_ = clock64(); if (lane == 0) { atomicAdd(&hmj_phase_cycles[i], (unsigned long long)(t_ - ph_t0)); \
+    hmj_phase_env[env & 16383][i] += (unsigned int)(t_ - ph_t0); } ph_t0 = clock64(); } while (0)
 #else
 #define PH(i) do { } while (0)
 #endif
@@ -297,7 +299,7 @@ __device__ __noinline__ void basis_dot(const double (*Jb)[6][LD], const double* 
 
 // One evaluation of the line-search objective and its derivatives at p.alpha (mj_solver PrimalEval): the quadratic
 // of every row that is active at alpha, summed over the warp, plus the Gauss term (qg).
-__device__ __noinline__ void ls_eval(LsPnt& p, const double* rD, const double* rJaref, const double* rJv, int nefc,
+__device__ __forceinline__ void ls_eval(LsPnt& p, const double* rD, const double* rJaref, const double* rJv, int nefc,
                                      double qg0, double qg1, double qg2, int lane) {
   double a0 = 0, a1 = 0, a2 = 0;
 #pragma unroll 1
@@ -428,7 +430,10 @@ __global__ void __launch_bounds__(128) k_classify(const hmj_tables_t* __restrict
 
 // ---------------------------------------------------------------- the solver
 template <int MAXC>
-__global__ void __launch_bounds__(32, MAXC == 0 ? 24 : (MAXC <= SOLVE_SMALL_CON ? 14 : 6))
+#ifndef HMJ_SOLVE4_WARPS
+#define HMJ_SOLVE4_WARPS 14
+#endif
+__global__ void __launch_bounds__(32, MAXC == 0 ? 24 : (MAXC <= SOLVE_SMALL_CON ? HMJ_SOLVE4_WARPS : 6))
 k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
   using Smem = SolveSmem<MAXC>;
   extern __shared__ double smem_raw[];
@@ -773,6 +778,10 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
           PH(12);
           mgrad = chol_factor_solve(S.H, &S.chol, grad, lane);
           PH(13);
+#ifdef HMJ_PHASE_PROF_CHOL2   // developer experiment: the same routine again, back to back (H holds L by now: timing only)
+          { const double again = chol_factor_solve(S.H, &S.chol, grad, lane); if (again == 1.2345e300) mgrad = again; }
+          PH(8);
+#endif
         }
         search = -mgrad;
 
@@ -819,21 +828,19 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
 #pragma unroll 1
               while (lsiter < ls_iterations && !found) {
                 pmid.alpha = 0.5 * (p1.alpha + p2.alpha); EV(pmid);
-                const LsPnt cand[3] = {p1next, p2next, pmid};
-                double bestcost = 0; int bestind = -1;
-                for (int i = 0; i < 3; i++)
-                  if (fabs(cand[i].d0) < gtol && (bestind == -1 || cand[i].cost < bestcost)) { bestcost = cand[i].cost; bestind = i; }
-                if (bestind >= 0) { alpha = cand[bestind].alpha; found = true; break; }
+                // the three candidates stay in registers (c0..c2 are copies: p1next / p2next are re-evaluated below)
+                const LsPnt c0 = p1next, c1 = p2next, c2 = pmid;
+                double bestcost = 0, bestalpha = 0; bool have = false;
+#define HMJ_LS_BEST(c) if (fabs(c.d0) < gtol && (!have || c.cost < bestcost)) { bestcost = c.cost; bestalpha = c.alpha; have = true; }
+                HMJ_LS_BEST(c0) HMJ_LS_BEST(c1) HMJ_LS_BEST(c2)
+#undef HMJ_LS_BEST
+                if (have) { alpha = bestalpha; found = true; break; }
                 int b1 = 0, b2 = 0;
-                for (int i = 0; i < 3; i++) {
-                  if (p1.d0 < 0 && cand[i].d0 < 0 && p1.d0 < cand[i].d0) { p1 = cand[i]; b1 = 1; }
-                  else if (p1.d0 > 0 && cand[i].d0 > 0 && p1.d0 > cand[i].d0) { p1 = cand[i]; b1 = 2; }
-                }
+#define HMJ_LS_BRACKET(p, b, c) if (p.d0 < 0 && c.d0 < 0 && p.d0 < c.d0) { p = c; b = 1; } else if (p.d0 > 0 && c.d0 > 0 && p.d0 > c.d0) { p = c; b = 2; }
+                HMJ_LS_BRACKET(p1, b1, c0) HMJ_LS_BRACKET(p1, b1, c1) HMJ_LS_BRACKET(p1, b1, c2)
                 if (b1) { p1next.alpha = p1.alpha - p1.d0 / p1.d1; EV(p1next); }
-                for (int i = 0; i < 3; i++) {
-                  if (p2.d0 < 0 && cand[i].d0 < 0 && p2.d0 < cand[i].d0) { p2 = cand[i]; b2 = 1; }
-                  else if (p2.d0 > 0 && cand[i].d0 > 0 && p2.d0 > cand[i].d0) { p2 = cand[i]; b2 = 2; }
-                }
+                HMJ_LS_BRACKET(p2, b2, c0) HMJ_LS_BRACKET(p2, b2, c1) HMJ_LS_BRACKET(p2, b2, c2)
+#undef HMJ_LS_BRACKET
                 if (b2) { p2next.alpha = p2.alpha - p2.d0 / p2.d1; EV(p2next); }
                 if (!b1 && !b2) { alpha = pmid.alpha; found = true; break; }
               }
@@ -965,6 +972,12 @@ extern "C" int hmj_debug_phase_cycles(unsigned long long* out, int reset) {
   cudaDeviceSynchronize();
   cudaMemcpyFromSymbol(out, hmj_phase_cycles, sizeof(unsigned long long) * 16);
   if (reset) { unsigned long long z[16] = {0}; cudaMemcpyToSymbol(hmj_phase_cycles, z, sizeof(z)); }
+  return 0;
+}
+extern "C" int hmj_debug_phase_env(unsigned int* out, int n, int reset) {
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out, hmj_phase_env, sizeof(unsigned int) * 16 * (size_t)n);
+  if (reset) { void* p = nullptr; cudaGetSymbolAddress(&p, hmj_phase_env); cudaMemset(p, 0, sizeof(unsigned int) * 16 * 16384); }
   return 0;
 }
 #endif
