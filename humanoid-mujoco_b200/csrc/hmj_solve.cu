@@ -749,32 +749,67 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
             S.W[lane][0] = Wn;
           }
           __syncwarp();
-          // ---- H = M + J' Dact J from the contact basis (lower triangle)
+          PH(5);
+          // ---- H = M + J' Dact J from the contact basis (lower triangle), in two passes per chunk of 3 contacts:
+          //   T_c = W_c Jb_c (6 x NV; W_c is the arrow-shaped 6x6 weight: Wnn, Wnk, diag Wkk), staged in the storage of H
+          //   (dead until the end of the assembly: 3 x 6 x LD doubles is exactly NV x LD), then
+          //   H_ij += sum_k Jb_c[k][i] T_c[k][j] with the six entries of a lane as independent accumulators.
+          constexpr int NQ = (NTRI + 31) / 32;
+          double acc[NQ];
+          int oi[NQ], oj[NQ];
+#pragma unroll
+          for (int q = 0; q < NQ; q++) {
+            const int t = min(lane + 32 * q, NTRI - 1);
+            oi[q] = S.tri[t][0]; oj[q] = S.tri[t][1];
+            acc[q] = S.M[oi[q] * LD + oj[q]];
+          }
+          // diagonal of the active limit rows: lane d sums the rows of dof d (uniform loop, broadcast loads), added last
+          double dd = 0.0;
+#pragma unroll 4
+          for (int r = 0; r < nlim; r++) {
+            const int ld = S.lim_dof[r];
+            const double rb = S.rowbuf[r];
+            dd += (ld == lane) ? rb : 0.0;
+          }
+          PH(8);
+          double (*Tc)[6][LD] = reinterpret_cast<double (*)[6][LD]>(S.H);
 #pragma unroll 1
-          for (int t = lane; t < NTRI; t += 32) {
-            const int i = S.tri[t][0], j = S.tri[t][1];
-            double acc = S.M[i * LD + j];
+          for (int c0 = 0; c0 < ncon; c0 += 3) {
+            const int nc = min(3, ncon - c0);
+            __syncwarp();
 #pragma unroll 1
-            for (int c = 0; c < ncon; c++) {
-              const double* Wc = S.W[c];
-              const double Jni = S.Jb[c][0][i], Jnj = S.Jb[c][0][j];
-              double tj = 0.0, ti = 0.0;
+            for (int e = lane; e < nc * NV; e += 32) {
+              const int cc = e / NV, d = e - cc * NV;
+              const double* Wc = S.W[c0 + cc];
+              const double (*J)[LD] = S.Jb[c0 + cc];
+              double jk[6];
+#pragma unroll
+              for (int kk = 0; kk < 6; kk++) jk[kk] = J[kk][d];
+              double t0 = Wc[0] * jk[0];
 #pragma unroll
               for (int kk = 1; kk < 6; kk++) {
-                const double wk = Wc[kk], wkk = Wc[5 + kk];
-                const double Jki = S.Jb[c][kk][i], Jkj = S.Jb[c][kk][j];
-                tj += wk * Jkj;
-                ti += Jki * (wk * Jnj + wkk * Jkj);
+                t0 += Wc[kk] * jk[kk];
+                Tc[cc][kk][d] = Wc[kk] * jk[0] + Wc[5 + kk] * jk[kk];
               }
-              acc += Jni * (Wc[0] * Jnj + tj) + ti;
+              Tc[cc][0][d] = t0;
             }
-            if (i == j) {
+            __syncwarp();
 #pragma unroll 1
-              for (int r = 0; r < nlim; r++)
-                if (S.lim_dof[r] == i) acc += S.rowbuf[r];
+            for (int cc = 0; cc < nc; cc++) {
+              const double (*J)[LD] = S.Jb[c0 + cc];
+#pragma unroll
+              for (int kk = 0; kk < 6; kk++) {
+#pragma unroll
+                for (int q = 0; q < NQ; q++) acc[q] += J[kk][oi[q]] * Tc[cc][kk][oj[q]];
+              }
             }
-            S.H[i * LD + j] = acc;
           }
+          __syncwarp();
+#pragma unroll
+          for (int q = 0; q < NQ; q++)
+            if (lane + 32 * q < NTRI) S.H[oi[q] * LD + oj[q]] = acc[q];
+          __syncwarp();
+          if (lane < NV) S.H[lane * LD + lane] += dd;
           PH(12);
           mgrad = chol_factor_solve(S.H, &S.chol, grad, lane);
           PH(13);

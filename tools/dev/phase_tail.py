@@ -16,7 +16,7 @@ b.step(np.zeros((n, 12)), 300)
 rng = np.random.default_rng(2)
 for _ in range(20):
     b.step(rng.uniform(-1, 1, (n, 12)), 1)
-names = {1: "load", 2: "contacts+limits", 3: "Jb+rows", 4: "warmstart", 6: "newton-pre", 7: "line search", 8: "chol again", 9: "post-newton",
+names = {1: "load", 2: "contacts+limits", 3: "Jb+rows", 4: "warmstart", 6: "newton-pre", 7: "line search", 5: "test+W", 8: "H init", 9: "post-newton",
          10: "results", 11: "euler", 12: "H assembly", 13: "chol+solve", 14: "cost/qfc/grad"}
 out = np.zeros((n, 16), dtype=np.uint32)
 b.lib.hmj_debug_phase_env.argtypes = [C.c_void_p, C.c_int, C.c_int]
