@@ -350,7 +350,8 @@ def run_gpu(args):
     # BatchedHumanoidEnv.step writes the actions into the engine's pinned IO block (one H2D copy), runs the prologue,
     # the physics step and the epilogue on the device, and reads the results from the same pinned block (one D2H copy).
     b.set_state(*settled)
-    host_actions = np.random.default_rng(5 + rank).uniform(-1, 1, (min(ring_n, 64), n, 12))
+    host_actions = hmj.pinned_empty((min(ring_n, 64), n, 12))   # the policy's output buffer: page-locked host memory
+    host_actions[...] = np.random.default_rng(5 + rank).uniform(-1, 1, host_actions.shape)
     acts = host_actions
     for s in range(W):
         env.step(acts[s % acts.shape[0]])
@@ -379,7 +380,7 @@ def run_gpu(args):
                        "step": "one mj_step of all envs + obs/reward epilogue"},
             "roofline": roofline,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": 1e3 * e2e_s / K, "api": "BatchedHumanoidEnv.step (hmj_env_step_fused C-ABI: pinned IO block, device-resident env bookkeeping)"},
+                    "ms_per_step": 1e3 * e2e_s / K, "api": "BatchedHumanoidEnv.step (hmj_env_step_fused_from C-ABI: actions DMA'd from the caller's pinned array, results into the pinned IO block, device-resident env bookkeeping)"},
             "gpu_launches": int(launches), "clocks": clk,
             "contacts": {"mean_ncon": float(ncon.mean()), "max_ncon": int(ncon.max()), "mean_nefc": float(nefc.mean()),
                          "max_nefc": int(nefc.max()), "mean_newton_iter": float(niter.mean()), "envs_with_bad_status": status_bad},

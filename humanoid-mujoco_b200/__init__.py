@@ -13,7 +13,7 @@ The directory name has a hyphen (it is the name the build contract asks for); im
 `humanoid_mujoco_b200` (see humanoid_mujoco_b200.py at the repo root).
 """
 from ._lib import HmjError, lib_path, load_library  # noqa: F401
-from .batch import HumanoidBatch, default_params, load_model  # noqa: F401
+from .batch import HumanoidBatch, default_params, load_model, pinned_empty  # noqa: F401
 from .env import BatchedHumanoidEnv  # noqa: F401
 from .planner import SamplingPlanner, SamplingPolicy, TimeSpline  # noqa: F401
 from .vec_env import B200VecEnv  # noqa: F401

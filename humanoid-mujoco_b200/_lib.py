@@ -59,6 +59,9 @@ def load_library() -> C.CDLL:
     lib.hmj_env_step.argtypes = [vp, dp, vp, dp, dp, dp, dp, C.c_double, C.c_int, dp, dp, vp, vp, vp, dp, dp]
     lib.hmj_env_io.argtypes = [vp] + [C.POINTER(vp)] * 9
     lib.hmj_env_step_fused.argtypes = [vp, C.c_int, C.c_int, C.c_double, C.c_double, C.c_ulonglong, C.c_int]
+    lib.hmj_env_step_fused_from.argtypes = [vp, vp, C.c_int, C.c_double, C.c_double, C.c_ulonglong, C.c_int]
+    lib.hmj_pinned_alloc.argtypes = [C.c_size_t, C.POINTER(vp)]
+    lib.hmj_pinned_free.argtypes = [vp]
     lib.hmj_batch_profile.argtypes = [vp, C.c_int]
     lib.hmj_batch_profile_read.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double),
                                            C.POINTER(C.c_int)]

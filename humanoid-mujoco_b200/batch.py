@@ -253,10 +253,21 @@ class HumanoidBatch:
             self._io = io
         return self._io
 
-    def env_step_fused(self, has_action: bool, has_mask: bool, rf: float, max_sim_time: float, seed: int, nsteps: int = 1):
-        """CPUEnv.step with device-resident bookkeeping (hmj_env_step_fused); inputs/outputs live in env_io()."""
+    def env_step_fused(self, action, has_mask: bool, rf: float, max_sim_time: float, seed: int, nsteps: int = 1):
+        """CPUEnv.step with device-resident bookkeeping (hmj_env_step_fused[_from]); results land in env_io().
+        `action`: True = the controls are in env_io()["action"], False / None = replay data.ctrl, or a C-contiguous
+        float64 [N][12] host array that is copied to the device straight from where it lies (pinned memory, e.g.
+        `pinned_empty`, makes that a plain DMA)."""
         mst = 1e300 if not np.isfinite(max_sim_time) else float(max_sim_time)
-        check(self.lib.hmj_env_step_fused(self._h, int(has_action), int(has_mask), float(rf), mst, int(seed) & (2**64 - 1), int(nsteps)))
+        if isinstance(action, np.ndarray):
+            if action.dtype != np.float64 or not action.flags.c_contiguous or action.size != self.n * NU:
+                raise ValueError("env_step_fused: action must be a C-contiguous float64 [N][12] array")
+            ptr = action.ctypes.data
+        elif action:
+            ptr = self.env_io()["action"].ctypes.data
+        else:
+            ptr = None
+        check(self.lib.hmj_env_step_fused_from(self._h, ptr, int(has_mask), float(rf), mst, int(seed) & (2**64 - 1), int(nsteps)))
 
     # ---- per-kernel timing
     def profile(self, enable: bool):
@@ -291,3 +302,21 @@ class HumanoidBatch:
         check(self.lib.hmj_plan_fetch(self._h, int(sample), int(horizon), _p(out["states"]), _p(out["actions"]), _p(out["times"]),
                                       _p(out["residual"]), _p(out["costs"]), _p(out["trace"])))
         return out
+
+
+def pinned_empty(shape, dtype=np.float64):
+    """A numpy array in page-locked host memory (hmj_pinned_alloc): step inputs placed here reach the device by DMA
+    with no staging copy.  The memory is released when the array (and every view of it) is garbage collected."""
+    import weakref
+
+    from ._lib import load_library
+
+    lib = load_library()
+    dt = np.dtype(dtype)
+    count = int(np.prod(shape))
+    p = C.c_void_p()
+    check(lib.hmj_pinned_alloc(max(count * dt.itemsize, 1), C.byref(p)))
+    raw = (C.c_char * max(count * dt.itemsize, 1)).from_address(p.value)
+    arr = np.frombuffer(raw, dtype=dt, count=count).reshape(shape)
+    weakref.finalize(raw, lib.hmj_pinned_free, p.value)
+    return arr

@@ -840,11 +840,12 @@ extern "C" int hmj_env_io(hmj_batch_t* b, double** action, int32_t** mask, doubl
 // written to the pinned IO block of hmj_env_io: one H2D copy, one D2H copy, one synchronisation per control step.
 // has_action == 0 replays data.ctrl (CPUEnv.step(None)); has_mask != 0 restricts the bookkeeping to mask[env] != 0
 // (physics is lock-step for everyone; CPUEnv.reset uses this for its first-step rejection loop).
-extern "C" int hmj_env_step_fused(hmj_batch_t* b, int has_action, int has_mask, double rf, double max_sim_time,
-                                  unsigned long long seed, int nsteps) {
+extern "C" int hmj_env_step_fused_from(hmj_batch_t* b, const double* action_host, int has_mask, double rf, double max_sim_time,
+                                       unsigned long long seed, int nsteps) {
   if (!b) return fail(HMJ_ERR_ARG, "bad argument to env_step_fused%s");  // nsteps < 0: observation only (no prologue, no physics)
   CK(cudaSetDevice(b->device));
   const size_t N = b->n;
+  const int has_action = action_host != nullptr;
   double* d_action = (double*)b->io_dev;
   int32_t* d_mask = (int32_t*)(b->io_dev + N * HMJ_NU * 8);
   double* d_out = (double*)(b->io_dev + b->io_in_bytes);
@@ -853,8 +854,12 @@ extern "C" int hmj_env_step_fused(hmj_batch_t* b, int has_action, int has_mask, 
   double* d_time = d_out + N * 31;
   double* d_quat = d_out + N * 32;
   int32_t* d_flags = (int32_t*)(d_out + N * 36);
-  if (has_action || has_mask)
-    CK(cudaMemcpyAsync(b->io_dev, b->io_host, has_mask ? N * HMJ_NU * 8 + N * 4 : N * HMJ_NU * 8, cudaMemcpyHostToDevice, b->stream));
+  if (has_action && has_mask && (const char*)action_host == b->io_host) {
+    CK(cudaMemcpyAsync(b->io_dev, b->io_host, N * HMJ_NU * 8 + N * 4, cudaMemcpyHostToDevice, b->stream));  // action + mask in one copy
+  } else {
+    if (has_action) CK(cudaMemcpyAsync(d_action, action_host, N * HMJ_NU * 8, cudaMemcpyHostToDevice, b->stream));
+    if (has_mask) CK(cudaMemcpyAsync(d_mask, b->io_host + N * HMJ_NU * 8, N * 4, cudaMemcpyHostToDevice, b->stream));
+  }
   const int32_t* mask = has_mask ? d_mask : nullptr;
   if (nsteps >= 0) hmj_launch_env_pre(b->buf, b->env, has_action ? d_action : nullptr, mask, rf, seed, b->stream);
   enqueue_steps(b, 1, nsteps);
@@ -865,6 +870,23 @@ extern "C" int hmj_env_step_fused(hmj_batch_t* b, int has_action, int has_mask, 
   CK(cudaMemcpyAsync(b->io_host + b->io_in_bytes, d_out, b->io_out_bytes, cudaMemcpyDeviceToHost, b->stream));
   CK(cudaStreamSynchronize(b->stream));
   CK(cudaGetLastError());
+  return HMJ_OK;
+}
+
+extern "C" int hmj_env_step_fused(hmj_batch_t* b, int has_action, int has_mask, double rf, double max_sim_time,
+                                  unsigned long long seed, int nsteps) {
+  if (!b) return fail(HMJ_ERR_ARG, "bad argument to env_step_fused%s");
+  return hmj_env_step_fused_from(b, has_action ? (const double*)b->io_host : nullptr, has_mask, rf, max_sim_time, seed, nsteps);
+}
+
+extern "C" int hmj_pinned_alloc(size_t bytes, void** out) {
+  if (!out || bytes == 0) return fail(HMJ_ERR_ARG, "bad argument to pinned_alloc%s");
+  CK(cudaHostAlloc(out, bytes, cudaHostAllocDefault));
+  return HMJ_OK;
+}
+
+extern "C" int hmj_pinned_free(void* p) {
+  if (p) CK(cudaFreeHost(p));
   return HMJ_OK;
 }
 

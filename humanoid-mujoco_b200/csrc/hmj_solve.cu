@@ -888,6 +888,9 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
           }
         }
         PH(7);
+#ifdef HMJ_PHASE_PROF
+        if (lane == 0) hmj_phase_env[env & 16383][15] += lsiter;
+#endif
         if (alpha == 0.0) break;
 
         // ======== move to the new point

@@ -23,6 +23,8 @@ bookkeeping (the reference's own control flow, vectorised) kept as the checker f
 """
 from __future__ import annotations
 
+from collections.abc import Sequence
+
 import numpy as np
 
 from .batch import DEFINES, NQ, NU, NV, HumanoidBatch
@@ -130,6 +132,32 @@ def standup_start_state(qpos0: np.ndarray, rng: np.random.Generator, rf: float, 
     return qpos
 
 
+class SparseInfos(Sequence):
+    """The per-env `info` dicts of one batched step as a read-only sequence of length N: only the envs whose episode
+    ended carry an entry, everyone else shares one empty dict (building N dicts per step would cost more host time
+    than the device step saves at 4096 envs)."""
+
+    __slots__ = ("_n", "_entries")
+    _EMPTY: dict = {}
+
+    def __init__(self, n, entries):
+        self._n = int(n)
+        self._entries = entries
+
+    def __len__(self):
+        return self._n
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return [self[j] for j in range(*i.indices(self._n))]
+        i = int(i)
+        if i < 0:
+            i += self._n
+        if not 0 <= i < self._n:
+            raise IndexError(i)
+        return self._entries.get(i, self._EMPTY)
+
+
 class BatchedHumanoidEnv:
     metadata = {"render_modes": [], "render_fps": 30}
 
@@ -178,6 +206,9 @@ class BatchedHumanoidEnv:
         self.torso_quat = np.zeros((n, 4))
         self.time = np.zeros(n)
         self._empty_info = {}
+        self._no_infos = SparseInfos(self.num_envs, {})
+        self._all_false = np.zeros(self.num_envs, dtype=bool)
+        self._all_false.flags.writeable = False
 
     # ------------------------------------------------------------------ host mirror <-> device state
     def _push_state(self):
@@ -274,29 +305,34 @@ class BatchedHumanoidEnv:
     # ------------------------------------------------------------------ step (cpu_env.py:676-693)
     def step(self, action=None):
         """One control step of every environment.  Returns views of the pinned result block (valid until the next
-        call): obs [N][30], reward [N], terminated [N], truncated [N], infos (list; `is_success` on episode end)."""
+        call): obs [N][30], reward [N], terminated [N], truncated [N], infos (a sequence of N dicts, `is_success` on episode end: SparseInfos)."""
         obs, reward, term, trunc, _ = self._step_device(action, only=None)
-        infos = [self._empty_info] * self.num_envs
-        done = term | trunc
-        if done.any():
-            for i in np.nonzero(done)[0]:
-                infos[i] = {"is_success": bool(trunc[i])}
-        return obs, reward, term, trunc, infos
+        if term is self._all_false and trunc is self._all_false:
+            return obs, reward, term, trunc, self._no_infos      # nothing ended: shared (read-only) flags and infos
+        ended = {int(i): {"is_success": bool(trunc[i])} for i in np.nonzero(term | trunc)[0]}
+        return obs, reward, term, trunc, SparseInfos(self.num_envs, ended)
 
     def _step_device(self, action, only):
         io = self.io
+        act = None
         if action is not None:
-            io["action"][...] = np.asarray(action, dtype=np.float64).reshape(self.num_envs, NU)
+            # copied to the device from where it lies (no host staging copy); pinned arrays (hmj.pinned_empty) go by DMA
+            act = np.ascontiguousarray(action, dtype=np.float64)
+            if act.size != self.num_envs * NU:
+                raise ValueError(f"action must hold {self.num_envs} x {NU} values")
         if only is not None:
             io["mask"][...] = only
         # ONE C call: action H2D, prologue, mj_step (PHYSICS_STEPS_PER_CONTROL_STEP = 1, simulation_parameters.py:82),
         # obs/reward epilogue + delay FIFOs, results D2H
-        self.batch.env_step_fused(action is not None, only is not None, self.randomization_factor, self.max_simulation_time,
-                                  self.seed, 1)
+        self.batch.env_step_fused(act, only is not None, self.randomization_factor, self.max_simulation_time, self.seed, 1)
         self.time = io["time"]
         self.torso_quat = io["torso_quat"]
-        return self._finish(io["obs"], io["reward"], io["terminated"].astype(bool), io["truncated"].astype(bool),
-                            io["self_collision"].astype(bool))
+        return self._finish(io["obs"], io["reward"], self._flags(io["terminated"]), self._flags(io["truncated"]),
+                            self._flags(io["self_collision"]))
+
+    def _flags(self, raw):
+        """int32 device flags -> bool array; the all-clear case (almost every step) hands out one shared read-only array."""
+        return raw.astype(bool) if raw.any() else self._all_false
 
     def _finish(self, obs, reward, term, trunc, selfc):
         if self.reward_override is not None:

@@ -39,6 +39,7 @@ class B200VecEnv:
         self.observation_space = _box(-10.0, 10.0, (30,))
         self.action_space = _box(-1.0, 1.0, (12,))
         self._actions = None
+        self._running_info = {"TimeLimit.truncated": False}
         self.reset_infos = [{} for _ in range(self.num_envs)]
 
     # ------------------------------------------------------------------ VecEnv contract
@@ -51,17 +52,19 @@ class B200VecEnv:
         self._actions = np.asarray(actions, dtype=np.float64).reshape(self.num_envs, 12)
 
     def step_wait(self):
-        obs, reward, term, trunc, infos = self.env.step(self._actions)
+        obs, reward, term, trunc, raw = self.env.step(self._actions)
         obs = np.array(obs, copy=True)
         reward = np.array(reward, copy=True)
         dones = np.asarray(term | trunc)
-        infos = [dict(i) for i in infos]
-        for i in range(self.num_envs):
-            infos[i]["TimeLimit.truncated"] = bool(trunc[i] and not term[i])
+        # envs still running share one `{"TimeLimit.truncated": False}` (treat it as read-only); ended envs get their own dict
+        infos = [self._running_info] * self.num_envs
         ended = np.nonzero(dones)[0]
         if len(ended):
             for i in ended:
-                infos[i]["terminal_observation"] = obs[i].copy()
+                d = dict(raw[i])
+                d["TimeLimit.truncated"] = bool(trunc[i] and not term[i])
+                d["terminal_observation"] = obs[i].copy()
+                infos[i] = d
             new_obs, _ = self.env.reset(env_ids=ended)
             obs[ended] = new_obs
         return obs, reward, dones, infos

@@ -119,6 +119,15 @@ int hmj_env_io(hmj_batch_t* b, double** action, int32_t** mask, double** obs, do
                double** torso_quat, int32_t** terminated, int32_t** truncated, int32_t** self_collision);
 int hmj_env_step_fused(hmj_batch_t* b, int has_action, int has_mask, double rf, double max_sim_time,
                        unsigned long long seed, int nsteps);
+/* The same step with the controls read straight from the caller's host array (action_host [N][12], NULL = replay
+ * data.ctrl) instead of the IO block: no staging copy on the host.  Pinned memory (hmj_pinned_alloc, or any
+ * cudaHostRegister'ed / framework-pinned buffer) makes the H2D copy a plain DMA; pageable memory works and is staged
+ * by the CUDA driver.  The array must stay valid until the call returns (it synchronises). */
+int hmj_env_step_fused_from(hmj_batch_t* b, const double* action_host, int has_mask, double rf, double max_sim_time,
+                            unsigned long long seed, int nsteps);
+/* Page-locked host memory for step inputs (cudaHostAlloc / cudaFreeHost). */
+int hmj_pinned_alloc(size_t bytes, void** out);
+int hmj_pinned_free(void* p);
 
 /* ---- per-kernel device timing (CUDA events on the batch stream, one pair around every launch of a step;
  * MuJoCo's own equivalent is the mjTIMER_* profiler, mjdata.h:68-93).  enable resets the counters. */

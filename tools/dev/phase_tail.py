@@ -24,10 +24,10 @@ for rep in range(3):
     b.lib.hmj_debug_phase_env(out.ctypes.data, n, 1)
     b.step(rng.uniform(-1, 1, (n, 12)), 1)
     b.lib.hmj_debug_phase_env(out.ctypes.data, n, 0)
-    tot = out.sum(1)
+    tot = out[:, :15].sum(1)
     niter, ncon, nefc = b.get("niter"), b.get("ncon"), b.get("nefc")
     order = np.argsort(-tot.astype(np.int64))
     print(f"step {rep}: cycles per env  max {tot.max()}  p99 {np.percentile(tot, 99):.0f}  p90 {np.percentile(tot, 90):.0f}  median {np.median(tot):.0f}")
     for e in order[:6]:
         ph = ", ".join(f"{names[i]} {out[e, i]}" for i in names if out[e, i] > 0.03 * tot[e])
-        print(f"  env {e}: total {tot[e]}  niter {niter[e]} ncon {ncon[e]} nefc {nefc[e]} | {ph}")
+        print(f"  env {e}: total {tot[e]}  niter {niter[e]} ncon {ncon[e]} nefc {nefc[e]} ls evals {out[e, 15]} | {ph}")
