@@ -104,8 +104,11 @@ __device__ __forceinline__ double chol_factor_solve(double* H, CholScratch* C, d
     if (lane == 0) C->invd[j] = inv;
     __syncwarp();
     const double* cj = col + j;                                // cj[m] = l(j + m, j)
+    double cm[NV - 1];                                         // all 17 broadcast loads in flight before the first FMA
 #pragma unroll
-    for (int m = 1; m < NV; m++) a[m - 1] = a[m] - lij * cj[m];
+    for (int m = 1; m < NV; m++) cm[m - 1] = cj[m];
+#pragma unroll
+    for (int m = 1; m < NV; m++) a[m - 1] = a[m] - lij * cm[m - 1];
     // forward substitution step j: y_j = x_j / l_jj, then x_i -= l_ij y_j for i > j
     const double xj = xb[j] * inv;
     yv = (lane == j) ? xj : yv;
