@@ -200,10 +200,14 @@ void hmj_launch_env_obs_reward(const hmj_tables_t* tab, hmj_buffers_t buf, const
 }
 
 // ------------------------------------------------------------------ CPUEnv prologue / delay FIFOs on the device
-// CPUEnv._apply_action (cpu_env.py:656-674) + _apply_external_forces (:618-654), one thread per environment.
-__global__ void k_env_pre(hmj_buffers_t B, hmj_envstate_t E, const double* __restrict__ action, const int32_t* __restrict__ mask,
-                          double rf, unsigned long long seed) {
-  const int env = blockIdx.x * blockDim.x + threadIdx.x;
+// CPUEnv._apply_action (cpu_env.py:656-674) + _apply_external_forces (:618-654).  Warp per environment: lane a < 12 owns
+// actuator a (coalesced rows of the FIFO), lane 0 runs the push scheduler.
+#define ENV_WARPS 4
+__global__ void __launch_bounds__(32 * ENV_WARPS)
+k_env_pre(hmj_buffers_t B, hmj_envstate_t E, const double* __restrict__ action, const int32_t* __restrict__ mask,
+          double rf, unsigned long long seed) {
+  const int lane = threadIdx.x & 31;
+  const int env = blockIdx.x * ENV_WARPS + (threadIdx.x >> 5);
   if (env >= B.n || (mask && !mask[env])) return;
   // ---- action: + constant noise, delay FIFO, NO clipping (cpu_env.py:670-671); action == NULL re-sends data.ctrl
   const int cnt = E.act_count[env];
@@ -212,16 +216,17 @@ __global__ void k_env_pre(hmj_buffers_t B, hmj_envstate_t E, const double* __res
   double* ctrl = B.ctrl + (size_t)env * HMJ_NU;
   const int slot = cnt % HMJ_ENV_HIST;
   const int src = ((cnt - d) % HMJ_ENV_HIST + HMJ_ENV_HIST) % HMJ_ENV_HIST;
-  for (int a = 0; a < HMJ_NU; a++) {
+  if (lane < HMJ_NU) {
+    const int a = lane;
     const double v = action ? action[(size_t)env * HMJ_NU + a] + E.act_noise[(size_t)env * HMJ_NU + a] : ctrl[a];
     hist[slot * HMJ_NU + a] = v;
-  }
-  for (int a = 0; a < HMJ_NU; a++) {
-    const double take = (cnt >= d) ? hist[src * HMJ_NU + a] : 0.0;
+    const double take = (cnt >= d) ? (src == slot ? v : hist[src * HMJ_NU + a]) : 0.0;
     ctrl[a] = take;
     E.prev_action[(size_t)env * HMJ_NU + a] = E.latest_action[(size_t)env * HMJ_NU + a];
     E.latest_action[(size_t)env * HMJ_NU + a] = take;
   }
+  __syncwarp();
+  if (lane != 0) return;
   E.act_count[env] = cnt + 1;
   // ---- random pushes: every U(1,3) s, for U(.05,.15) s, U(5,15) rf N along a random horizontal direction on a random body
   double* fs = E.force_sched + (size_t)env * 5;
@@ -250,42 +255,47 @@ __global__ void k_env_pre(hmj_buffers_t B, hmj_envstate_t E, const double* __res
 
 // Observation delay FIFOs of CPUEnv._get_obs (cpu_env.py:528-547): `obs` holds the undelayed observation on entry,
 // the delayed one on exit; also CPUEnv.torso_quat (:516).
-__global__ void k_env_post(hmj_buffers_t B, hmj_envstate_t E, const int32_t* __restrict__ mask, double* __restrict__ obs,
-                           double* __restrict__ time_out, double* __restrict__ quat_out) {
-  const int env = blockIdx.x * blockDim.x + threadIdx.x;
+// Warp per environment, lane k < 30 owns observation element k.
+__global__ void __launch_bounds__(32 * ENV_WARPS)
+k_env_post(hmj_buffers_t B, hmj_envstate_t E, const int32_t* __restrict__ mask, double* __restrict__ obs,
+           double* __restrict__ time_out, double* __restrict__ quat_out) {
+  const int lane = threadIdx.x & 31;
+  const int env = blockIdx.x * ENV_WARPS + (threadIdx.x >> 5);
   if (env >= B.n) return;
-  if (time_out) time_out[env] = B.time[env];
+  if (lane == 0 && time_out) time_out[env] = B.time[env];
   if (mask && !mask[env]) {
-    if (quat_out) for (int k = 0; k < 4; k++) quat_out[(size_t)env * 4 + k] = E.torso_quat[(size_t)env * 4 + k];
+    if (quat_out && lane < 4) quat_out[(size_t)env * 4 + lane] = E.torso_quat[(size_t)env * 4 + lane];
     return;
   }
-  const double* sens = B.sens + (size_t)env * SENS_NUM;
-  for (int k = 0; k < 4; k++) {
-    const double v = sens[SENS_ROOT_XQUAT + k] + E.obs_noise[(size_t)env * 31 + 27 + k];
-    E.torso_quat[(size_t)env * 4 + k] = v;
-    if (quat_out) quat_out[(size_t)env * 4 + k] = v;
+  if (lane < 4) {
+    const double v = B.sens[(size_t)env * SENS_NUM + SENS_ROOT_XQUAT + lane] + E.obs_noise[(size_t)env * 31 + 27 + lane];
+    E.torso_quat[(size_t)env * 4 + lane] = v;
+    if (quat_out) quat_out[(size_t)env * 4 + lane] = v;
   }
   const int cnt = E.obs_count[env];
-  double* hist = E.obs_hist + (size_t)env * HMJ_ENV_HIST * 30;
-  double* o = obs + (size_t)env * 30;
-  const int slot = cnt % HMJ_ENV_HIST;
-  for (int k = 0; k < 30; k++) hist[slot * 30 + k] = o[k];
-  const int lo[3] = {0, 24, 27}, hi[3] = {24, 27, 30};
-  for (int g = 0; g < 3; g++) {
+  if (lane < 30) {
+    const int k = lane;
+    double* hist = E.obs_hist + (size_t)env * HMJ_ENV_HIST * 30;
+    double* o = obs + (size_t)env * 30;
+    const int slot = cnt % HMJ_ENV_HIST;
+    const double v = o[k];
+    hist[slot * 30 + k] = v;
+    const int g = k < 24 ? 0 : (k < 27 ? 1 : 2);   // joint pos+vel / angular velocity / gravity groups
     const int d = E.obs_delay[(size_t)env * 3 + g];
     const int src = ((cnt - d) % HMJ_ENV_HIST + HMJ_ENV_HIST) % HMJ_ENV_HIST;
-    for (int k = lo[g]; k < hi[g]; k++) o[k] = (cnt >= d) ? hist[src * 30 + k] : ((k == 29) ? -1.0 : 0.0);
+    o[k] = (cnt >= d) ? (src == slot ? v : hist[src * 30 + k]) : ((k == 29) ? -1.0 : 0.0);
   }
-  E.obs_count[env] = cnt + 1;
+  __syncwarp();
+  if (lane == 0) E.obs_count[env] = cnt + 1;
 }
 
 void hmj_launch_env_pre(hmj_buffers_t buf, hmj_envstate_t env, const double* action, const int32_t* mask, double rf,
                         unsigned long long seed, cudaStream_t stream) {
-  k_env_pre<<<(buf.n + 127) / 128, 128, 0, stream>>>(buf, env, action, mask, rf, seed);
+  k_env_pre<<<(buf.n + ENV_WARPS - 1) / ENV_WARPS, 32 * ENV_WARPS, 0, stream>>>(buf, env, action, mask, rf, seed);
 }
 void hmj_launch_env_post(hmj_buffers_t buf, hmj_envstate_t env, const int32_t* mask, double* obs, double* time_out, double* quat_out,
                          cudaStream_t stream) {
-  k_env_post<<<(buf.n + 127) / 128, 128, 0, stream>>>(buf, env, mask, obs, time_out, quat_out);
+  k_env_post<<<(buf.n + ENV_WARPS - 1) / ENV_WARPS, 32 * ENV_WARPS, 0, stream>>>(buf, env, mask, obs, time_out, quat_out);
 }
 
 // ------------------------------------------------------------------ FP64 FMA peak (roofline denominator)
