@@ -163,6 +163,26 @@ static void build_tables(const hmj_model_t* m, hmj_tables_t* t) {
     int base = 0;
     for (int g = 0; g < HMJ_NGROUP; g++) { t->group_base[g] = base; base += cap[g]; }
     t->group_base[HMJ_NGROUP] = base;
+    // cost of one MPR trip of a group ~ vertices scanned per support pair; order groups by it (descending) and cap the
+    // item size of the expensive ones so that their items stay short (k_narrow's header explains the schedule)
+    int verts[64] = {0};
+    for (int k = 0; k < m->npair; k++) {
+      const int g = t->pair_group[k];
+      const int g1 = m->pair_geom1[k], g2 = m->pair_geom2[k];
+      verts[g] = (g1 == 0 ? 0 : m->mesh_vertnum[m->geom_meshid[g1]]) + m->mesh_vertnum[m->geom_meshid[g2]];
+    }
+    for (int g = 0; g < 64; g++) { t->group_order[g] = g; t->group_shiftcap[g] = 5; }
+    for (int a = 1; a < HMJ_NGROUP; a++) {   // insertion sort, stable
+      const int g = t->group_order[a];
+      int bpos = a;
+      while (bpos > 0 && verts[t->group_order[bpos - 1]] < verts[g]) { t->group_order[bpos] = t->group_order[bpos - 1]; bpos--; }
+      t->group_order[bpos] = g;
+    }
+    int thr[3] = {250, 180, 50}, capv[3] = {2, 3, 4};
+    if (const char* e = getenv("HMJ_NARROW_CAP"))   // developer override: "v0:s0,v1:s1,v2:s2" (vertex threshold : log2 item size)
+      sscanf(e, "%d:%d,%d:%d,%d:%d", &thr[0], &capv[0], &thr[1], &capv[1], &thr[2], &capv[2]);
+    for (int g = 0; g < HMJ_NGROUP; g++)
+      t->group_shiftcap[g] = verts[g] >= thr[0] ? capv[0] : (verts[g] >= thr[1] ? capv[1] : (verts[g] >= thr[2] ? capv[2] : 5));
   }
   int adr = 0;
   for (int k = 0; k < HMJ_NMESH; k++) {

@@ -694,6 +694,27 @@ k_broad(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int npad) {
   }
 }
 
+#ifdef HMJ_PHASE_PROF
+// developer build: per-group item statistics of k_narrow {items, sum cycles, max cycles, sum trips, max trips} and the
+// per-warp busy time {max cycles, sum cycles, warps, staging cycles}
+__device__ unsigned long long hmj_narrow_prof[64][5];
+__device__ unsigned long long hmj_narrow_warp[12];   // [4 + shift]: launches that ran with item size 1 << shift; [10]: sum of total items, [11]: sum of queries
+__device__ int hmj_narrow_trips;   // scratch written by the narrow_* routines (lane 0 of the running warp reads its own)
+extern "C" int hmj_debug_narrow_prof(unsigned long long* out, unsigned long long* warp, int reset) {
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out, hmj_narrow_prof, sizeof(unsigned long long) * 64 * 5);
+  cudaMemcpyFromSymbol(warp, hmj_narrow_warp, sizeof(unsigned long long) * 12);
+  if (reset) {
+    void* p = nullptr;
+    cudaGetSymbolAddress(&p, hmj_narrow_prof); cudaMemset(p, 0, sizeof(unsigned long long) * 64 * 5);
+    cudaGetSymbolAddress(&p, hmj_narrow_warp); cudaMemset(p, 0, sizeof(unsigned long long) * 12);
+  }
+  return 0;
+}
+#define NP_TRIP() do { trips_++; } while (0)
+#else
+#define NP_TRIP() do { } while (0)
+#endif
 // ------------------------------------------------------------------ narrowphase
 __device__ __forceinline__ void write_slot(const hmj_buffers_t& B, int env, int s, double dist, const double* nrm, const double* pos) {
   double* slot = B.slots + ((size_t)env * HMJ_NSLOT + s) * HMJ_SLOT_DOUBLES;
@@ -706,7 +727,7 @@ __device__ __forceinline__ void write_slot(const hmj_buffers_t& B, int env, int 
 // 32 mesh-mesh tasks of one pair (mjc_Convex, multiccd off): lane <-> environment.
 __device__ __forceinline__ void narrow_mesh_mesh(const hmj_tables_t* __restrict__ T, const hmj_buffers_t& B,
                                                  const double* sx, const double* sy, const double* sz, int2 task,
-                                                 bool active, int lane) {
+                                                 bool active, int lane, int& trips_) {
   const hmj_model_t& M = T->m;
   const int env = task.x, k = task.y & 63;
   const int g1 = M.pair_geom1[k], g2 = M.pair_geom2[k];
@@ -725,6 +746,7 @@ __device__ __forceinline__ void narrow_mesh_mesh(const hmj_tables_t* __restrict_
   while (true) {
     const unsigned am = __ballot_sync(0xffffffffu, active);
     if (!am) break;
+    NP_TRIP();
     Supp s;
     double nd[3] = {m.dir[0], m.dir[1], m.dir[2]};
     c_scale(nd, -1.0);
@@ -755,7 +777,7 @@ __device__ __forceinline__ void narrow_mesh_mesh(const hmj_tables_t* __restrict_
 // 32 prism-vs-hull tasks of one hull (pairs may differ per lane): lane <-> one pre-screened prism of
 // mjc_ConvexHField; the query restarts from the top (same arithmetic as the screen in k_broad).
 __device__ __forceinline__ void narrow_hfield(const hmj_tables_t* __restrict__ T, const hmj_buffers_t& B, const double* sx,
-                                              const double* sy, const double* sz, Hull h2, int2 task, bool active, int lane) {
+                                              const double* sy, const double* sz, Hull h2, int2 task, bool active, int lane, int& trips_) {
   const hmj_model_t& M = T->m;
   const int env = task.x;
   const int k = task.y & 63, ord = (task.y >> 6) & 7, r = (task.y >> 9) & 7, cmin = (task.y >> 12) & 7, ps = (task.y >> 15) & 31;
@@ -785,6 +807,7 @@ __device__ __forceinline__ void narrow_hfield(const hmj_tables_t* __restrict__ T
   while (true) {
     const unsigned am = __ballot_sync(0xffffffffu, active);
     if (!am) break;
+    NP_TRIP();
     Supp s;
     double nd[3] = {m.dir[0], m.dir[1], m.dir[2]};
     prism_support(p, m.dir, s.v1);
@@ -832,9 +855,17 @@ k_narrow(const hmj_tables_t* __restrict__ T, hmj_buffers_t B) {
   // a step has a few thousand queries against 1184 resident warps, and an MPR trip costs the whole warp ~25 n cycles
   // lane-serial but only ~(n + 700) per 4 queries with the cooperative scan, so short items cut the query-chain
   // latency that bounds this kernel.  Every query is independent: the item size never changes a result bit.
-  const int c0 = B.wq_count[lane];
-  const int c1 = (lane + 32 < HMJ_NGROUP) ? B.wq_count[lane + 32] : 0;
+  // Lane l holds schedule positions l and l + 32; position p is group T->group_order[p] (most expensive first).
+  const int ga = T->group_order[lane];
+  const int gb = (lane + 32 < HMJ_NGROUP) ? T->group_order[lane + 32] : 0;
+  const int c0 = B.wq_count[ga];
+  const int c1 = (lane + 32 < HMJ_NGROUP) ? B.wq_count[gb] : 0;
+  const int cap0 = T->group_shiftcap[ga], cap1 = T->group_shiftcap[gb];
   const int nwarp = gridDim.x * (blockDim.x >> 5);
+  // base item size: the smallest of 4 / 8 / 16 / 32 that gives every item its own warp (small batches: every query
+  // chain as short as it can be).  When even 32 is not enough the kernel is in its throughput regime: groups with big
+  // hulls keep short items (their cap), so that no warp is stuck with a 32-query item of 400-vertex scans while the
+  // others idle, and the items are handed out dynamically, expensive groups first.
   int shift = 2;
   for (; shift < 5; shift++) {
     int items = ((c0 + (1 << shift) - 1) >> shift) + ((c1 + (1 << shift) - 1) >> shift);
@@ -842,8 +873,8 @@ k_narrow(const hmj_tables_t* __restrict__ T, hmj_buffers_t B) {
     for (int o = 16; o > 0; o >>= 1) items += __shfl_xor_sync(0xffffffffu, items, o);
     if (items <= nwarp) break;
   }
-  const int isz = 1 << shift;
-  const int n0 = (c0 + isz - 1) >> shift, n1 = (c1 + isz - 1) >> shift;
+  const int s0 = min(shift, cap0), s1 = min(shift, cap1);
+  const int n0 = (c0 + (1 << s0) - 1) >> s0, n1 = (c1 + (1 << s1) - 1) >> s1;
   int inc0 = n0;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, inc0, o); if (lane >= o) inc0 += v; }
@@ -853,25 +884,65 @@ k_narrow(const hmj_tables_t* __restrict__ T, hmj_buffers_t B) {
   for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, inc1, o); if (lane >= o) inc1 += v; }
   inc1 += tot0;
   const int total = __shfl_sync(0xffffffffu, inc1, 31);
-  const int gwarp = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;  // consecutive items (same group, similar cost) land on different SMs
-  if (blockIdx.x >= total) return;  // whole CTA idle (its first warp has the smallest item index)
+  if (blockIdx.x >= total) return;  // more CTAs than items: the first `total` CTAs hold enough warps
+#ifdef HMJ_PHASE_PROF
+  if (blockIdx.x == 0 && threadIdx.x < 32) {
+    int qsum = c0 + c1;
+    for (int o = 16; o > 0; o >>= 1) qsum += __shfl_xor_sync(0xffffffffu, qsum, o);
+    if (threadIdx.x == 0) { atomicAdd(&hmj_narrow_warp[4 + shift], 1ull); atomicAdd(&hmj_narrow_warp[10], (unsigned long long)total); atomicAdd(&hmj_narrow_warp[11], (unsigned long long)qsum); }
+  }
+#endif
+#ifdef HMJ_PHASE_PROF
+  const long long w_t0 = clock64();
+#endif
   stage_hulls(T, sx, sy, sz);
-  for (int item = gwarp; item < total; item += nwarp) {
-    // group = number of groups whose inclusive prefix is <= item
-    const int g = __popc(__ballot_sync(0xffffffffu, inc0 <= item)) + __popc(__ballot_sync(0xffffffffu, inc1 <= item));
-    const int excl = (g == 0) ? 0 : (g <= 32 ? __shfl_sync(0xffffffffu, inc0, (g - 1) & 31) : __shfl_sync(0xffffffffu, inc1, (g - 1) & 31));
-    const int cnt = (g < 32) ? __shfl_sync(0xffffffffu, c0, g & 31) : __shfl_sync(0xffffffffu, c1, g & 31);
-    const int q0 = (item - excl) << shift;
+#ifdef HMJ_PHASE_PROF
+  const long long w_t1 = clock64();
+#endif
+  int trips_ = 0;
+  for (;;) {
+    // dynamic hand-out (wq_count[63] is the item counter of this launch, zeroed with the group counts)
+    int item = 0;
+    if (lane == 0) item = atomicAdd(&B.wq_count[63], 1);
+    item = __shfl_sync(0xffffffffu, item, 0);
+    if (item >= total) break;
+#ifdef HMJ_PHASE_PROF
+    const long long i_t0 = clock64();
+    trips_ = 0;
+#endif
+    // schedule position = number of positions whose inclusive prefix is <= item
+    const int pos = __popc(__ballot_sync(0xffffffffu, inc0 <= item)) + __popc(__ballot_sync(0xffffffffu, inc1 <= item));
+    const int excl = (pos == 0) ? 0 : (pos <= 32 ? __shfl_sync(0xffffffffu, inc0, (pos - 1) & 31) : __shfl_sync(0xffffffffu, inc1, (pos - 1) & 31));
+    const int cnt = (pos < 32) ? __shfl_sync(0xffffffffu, c0, pos & 31) : __shfl_sync(0xffffffffu, c1, pos & 31);
+    const int g = (pos < 32) ? __shfl_sync(0xffffffffu, ga, pos & 31) : __shfl_sync(0xffffffffu, gb, pos & 31);
+    const int ishift = (pos < 32) ? __shfl_sync(0xffffffffu, s0, pos & 31) : __shfl_sync(0xffffffffu, s1, pos & 31);
+    const int isz = 1 << ishift;
+    const int q0 = (item - excl) << ishift;
     const int q = q0 + lane;
     const bool valid = lane < isz && q < cnt;
     const int2 task = B.wq_task[(size_t)T->group_base[g] * B.n + (valid ? q : q0)];  // idle lanes shadow the item's first task
     if (g < HMJ_NMESH) {
       const Hull h2 = {T->mesh_adr[g], T->mesh_npad[g]};
-      narrow_hfield(T, B, sx, sy, sz, h2, task, valid, lane);
+      narrow_hfield(T, B, sx, sy, sz, h2, task, valid, lane, trips_);
     } else {
-      narrow_mesh_mesh(T, B, sx, sy, sz, task, valid, lane);
+      narrow_mesh_mesh(T, B, sx, sy, sz, task, valid, lane, trips_);
     }
+#ifdef HMJ_PHASE_PROF
+    if (lane == 0) {
+      const unsigned long long dt = (unsigned long long)(clock64() - i_t0);
+      atomicAdd(&hmj_narrow_prof[g][0], 1ull); atomicAdd(&hmj_narrow_prof[g][1], dt); atomicMax(&hmj_narrow_prof[g][2], dt);
+      atomicAdd(&hmj_narrow_prof[g][3], (unsigned long long)trips_); atomicMax(&hmj_narrow_prof[g][4], (unsigned long long)trips_);
+    }
+#endif
   }
+#ifdef HMJ_PHASE_PROF
+  if (lane == 0) {
+    const unsigned long long dt = (unsigned long long)(clock64() - w_t0);
+    atomicMax(&hmj_narrow_warp[0], dt); atomicAdd(&hmj_narrow_warp[1], dt); atomicAdd(&hmj_narrow_warp[2], 1ull);
+    atomicMax(&hmj_narrow_warp[3], (unsigned long long)(w_t1 - w_t0));
+  }
+#endif
+  (void)trips_;
 }
 
 void hmj_launch_collide(const hmj_tables_t* tab, hmj_buffers_t buf, cudaStream_t stream) {
