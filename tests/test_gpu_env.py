@@ -89,3 +89,57 @@ def test_step_none_replays_ctrl_and_potential_rewards():
     assert np.allclose(env.batch.get("ctrl"), 0.3)  # rf = 0: no noise, no delay
     assert np.all(np.abs(r2) < np.abs(r1) + 50)      # potential reward = difference of consecutive rewards
     env.close()
+
+
+def test_action_source_does_not_change_results():
+    """The controls reach the device from wherever the caller keeps them (hmj_env_step_fused_from): a page-locked array
+    (hmj.pinned_empty), a pageable array, a non-contiguous view and a float32 array must give bit-identical steps."""
+    import humanoid_mujoco_b200 as hmj
+
+    rng = np.random.default_rng(4)
+    acts = rng.uniform(-1, 1, (6, N, 12)).astype(np.float32).astype(np.float64)   # exactly representable in float32
+    runs = []
+    for kind in ("pinned", "pageable", "strided", "float32"):
+        env, _ = make_env(hmj, seed=9)
+        pin = hmj.pinned_empty((N, 12))
+        out = []
+        for s in range(acts.shape[0]):
+            if kind == "pinned":
+                pin[...] = acts[s]
+                a = pin
+            elif kind == "pageable":
+                a = acts[s].copy()
+            elif kind == "strided":
+                wide = np.zeros((N, 24))
+                wide[:, ::2] = acts[s]
+                a = wide[:, ::2]
+            else:
+                a = acts[s].astype(np.float32)
+            o, r, term, trunc, infos = env.step(a)
+            out.append((o.copy(), r.copy(), term.copy(), trunc.copy()))
+        runs.append(out)
+        env.close()
+    for other in runs[1:]:
+        for a, b in zip(runs[0], other):
+            for x, y in zip(a, b):
+                assert np.array_equal(x, y)
+    with pytest.raises(ValueError):
+        env2, _ = make_env(hmj, seed=9)
+        env2.step(np.zeros((N, 11)))
+
+
+def test_infos_are_sparse_and_flags_shared_when_nothing_ends():
+    import humanoid_mujoco_b200 as hmj
+    from humanoid_mujoco_b200.env import SparseInfos
+
+    env, _ = make_env(hmj, seed=2, rf=0.0)
+    o, r, term, trunc, infos = env.step(np.zeros((N, 12)))
+    assert isinstance(infos, SparseInfos) and len(infos) == N and infos[0] == {} and infos[-1] == {}
+    assert not term.any() and not trunc.any()
+    with pytest.raises(ValueError):
+        term[0] = True            # the all-clear flags are one shared read-only array
+    env.max_simulation_time = 0.0  # every episode is over at the next step: terminated everywhere (cpu_env.py:684)
+    o, r, term, trunc, infos = env.step(np.zeros((N, 12)))
+    assert term.all() and all("is_success" in infos[i] for i in range(N))
+    assert [i for i in infos][3] == infos[3] and infos[1:3] == [infos[1], infos[2]]
+    env.close()
