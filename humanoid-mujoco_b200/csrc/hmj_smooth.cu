@@ -146,6 +146,15 @@ k_smooth(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* 
   double* g_ctrl = B.ctrl + (size_t)env * HMJ_NU;
   double qp = lane < HMJ_NQ ? g_qpos[lane] : 0.0;
   double qv = lane < HMJ_NV ? g_qvel[lane] : 0.0;
+  // Per-env parameters (domain randomisation) and step inputs this lane needs later, requested now: every one of them is
+  // an L2 round trip, and left at its point of use each would stall the warp on its own (they were 9 % of the samples).
+  const double pf_mass = (lane >= 1 && lane < HMJ_NBODY) ? P->body_mass[lane] : 0.0;
+  const double pf_arm = lane < HMJ_NV ? P->dof_armature[lane] : 0.0;
+  const double pf_stiff = lane < HMJ_NV ? P->jnt_stiffness[M.dof_jntid[lane]] : 0.0;
+  const double pf_gain = lane < HMJ_NU ? P->act_gainprm0[lane] : 0.0;
+  const double pf_fr0 = lane < HMJ_NU ? P->act_forcerange[lane][0] : 0.0;
+  const double pf_fr1 = lane < HMJ_NU ? P->act_forcerange[lane][1] : 0.0;
+  const int pf_xb = B.xfrc_body[env];
   int status = 0;
   bool badq = __any_sync(FULL, d_is_bad(qp));
   bool badv = __any_sync(FULL, d_is_bad(qv));
@@ -270,7 +279,7 @@ k_smooth(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* 
   __syncwarp();
 
   // ---------------- mj_comPos: subtree CoM of the root (all moving bodies share root body 1)
-  const double mass = (lane >= 1 && lane < HMJ_NBODY) ? P->body_mass[lane] : 0.0;
+  const double mass = pf_mass;
   {
     double cx = 0, cy = 0, cz = 0;
     if (lane >= 1 && lane < HMJ_NBODY) { cx = mass * S.xipos[lane][0]; cy = mass * S.xipos[lane][1]; cz = mass * S.xipos[lane][2]; }
@@ -323,11 +332,17 @@ k_smooth(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* 
   __syncwarp();
   if (lane < HMJ_NV) d_mul_inert_vec(S.buf[lane], S.crb[M.dof_bodyid[lane]], S.cdof[lane]);
   __syncwarp();
-  for (int e = lane; e < HMJ_NM; e += 32) {
-    const int i = T->M_row[e], j = T->M_col[e];
-    double v = d_dot6(S.cdof[j], S.buf[i]);
-    if (i == j) v += P->dof_armature[i];
-    B.qM[(size_t)env * HMJ_NM + e] = v;
+#pragma unroll
+  for (int kk = 0; kk < (HMJ_NM + 31) / 32; kk++) {   // uniform trip count: the armature comes from its owner lane
+    const int e = lane + 32 * kk;
+    const bool ok = e < HMJ_NM;
+    const int i = ok ? T->M_row[e] : 0, j = ok ? T->M_col[e] : 0;
+    const double arm = __shfl_sync(FULL, pf_arm, i);
+    if (ok) {
+      double v = d_dot6(S.cdof[j], S.buf[i]);
+      if (i == j) v += arm;
+      B.qM[(size_t)env * HMJ_NM + e] = v;
+    }
   }
 
   // ---------------- mj_comVel (cvel, cdof_dot) and the acceleration pass of mj_rne, by level
@@ -378,7 +393,7 @@ k_smooth(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* 
   // ---------------- mj_passive, mj_fwdActuation
   if (lane < HMJ_NV) {
     const int d = lane, j = M.dof_jntid[d];
-    const double stiff = P->jnt_stiffness[j];
+    const double stiff = pf_stiff;
     double spring = 0.0;
     if (stiff != 0) {
       const int padr = M.jnt_qposadr[j], dadr = M.jnt_dofadr[j];
@@ -409,8 +424,8 @@ k_smooth(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* 
   __syncwarp();
   if (lane < HMJ_NU) {
     double c = fmin(fmax(S.ctrl[lane], M.act_ctrlrange[lane][0]), M.act_ctrlrange[lane][1]);
-    double force = P->act_gainprm0[lane] * c;
-    force = fmin(fmax(force, P->act_forcerange[lane][0]), P->act_forcerange[lane][1]);
+    double force = pf_gain * c;
+    force = fmin(fmax(force, pf_fr0), pf_fr1);
     S.qfrc_actuator[M.act_dofadr[lane]] = M.act_gear[lane] * force;
   }
   __syncwarp();
@@ -420,7 +435,7 @@ k_smooth(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* 
     const int d = lane;
     double f = S.qfrc_passive[d] - S.qfrc_bias[d];
     f += S.qfrc_actuator[d];
-    const int xb = B.xfrc_body[env];
+    const int xb = pf_xb;
     if (xb > 0 && xb < HMJ_NBODY) {
       const double* w = B.xfrc + (size_t)env * 6;
       if ((w[0] != 0 || w[1] != 0 || w[2] != 0 || w[3] != 0 || w[4] != 0 || w[5] != 0) && ((T->body_dofmask[xb] >> d) & 1u)) {
