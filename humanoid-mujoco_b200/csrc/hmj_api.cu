@@ -557,23 +557,23 @@ static void enqueue_one_step(hmj_batch_t* b, int integrate) {
   if (b->pipes.empty()) {
     hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, b->stream);
     hmj_launch_factor(b->tab_dev, b->buf, b->stream, &b->solve_ctx);
-    hmj_launch_collide(b->tab_dev, b->buf, b->stream);
-    hmj_launch_solve(b->tab_dev, b->buf, integrate, b->stream, &b->solve_ctx);
+    hmj_launch_collide(b->tab_dev, b->buf, b->stream, false);
+    hmj_launch_solve(b->tab_dev, b->buf, integrate, b->stream, &b->solve_ctx, false);
     return;
   }
   cudaEventRecord(b->pipe_fork, b->stream);
   for (auto& pp : b->pipes) cudaStreamWaitEvent(pp.stream, b->pipe_fork, 0);
   for (auto& pp : b->pipes) hmj_launch_smooth(b->tab_dev, pp.view, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, pp.stream);
   for (auto& pp : b->pipes) hmj_launch_factor(b->tab_dev, pp.view, pp.stream, &pp.ctx);
-  for (auto& pp : b->pipes) hmj_launch_collide(b->tab_dev, pp.view, pp.stream);
-  for (auto& pp : b->pipes) hmj_launch_solve(b->tab_dev, pp.view, integrate, pp.stream, &pp.ctx);
+  for (auto& pp : b->pipes) hmj_launch_collide(b->tab_dev, pp.view, pp.stream, false);
+  for (auto& pp : b->pipes) hmj_launch_solve(b->tab_dev, pp.view, integrate, pp.stream, &pp.ctx, false);
   for (auto& pp : b->pipes) {
     cudaEventRecord(pp.done, pp.stream);
     cudaStreamWaitEvent(b->stream, pp.done, 0);
   }
 }
 
-// nsteps physics steps of the whole batch.  The step chain (7 kernels + 3 memsets per pipe, forks and joins) is
+// nsteps physics steps of the whole batch.  The step chain (8 kernels per pipe, forks and joins; the per-step counters are zeroed inside k_smooth) is
 // captured once per `integrate` flavour into a CUDA graph and replayed: one launch per step instead of ~15 API calls,
 // and the inter-kernel gaps shrink to the graph's dependency latency.  The first step of a batch runs un-captured
 // (it performs the launchers' one-time attribute / occupancy queries, which must not happen inside a capture).

@@ -945,7 +945,7 @@ k_narrow(const hmj_tables_t* __restrict__ T, hmj_buffers_t B) {
   (void)trips_;
 }
 
-void hmj_launch_collide(const hmj_tables_t* tab, hmj_buffers_t buf, cudaStream_t stream) {
+void hmj_launch_collide(const hmj_tables_t* tab, hmj_buffers_t buf, cudaStream_t stream, bool zero) {
   static int narrow_grid = 0;
   if (!narrow_grid) {
     int dev = 0, sms = 148, per_sm = 2;
@@ -954,8 +954,10 @@ void hmj_launch_collide(const hmj_tables_t* tab, hmj_buffers_t buf, cudaStream_t
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_narrow, NARROW_THREADS, 0);
     narrow_grid = sms * (per_sm > 0 ? per_sm : 1);
   }
-  cudaMemsetAsync(buf.wq_count, 0, 64 * sizeof(int32_t), stream);
-  cudaMemsetAsync(buf.slot_mask, 0, (size_t)buf.n * 4 * sizeof(uint32_t), stream);
+  if (zero) {   // callers whose k_smooth ran just before on this stream skip this: k_smooth zeroes both
+    cudaMemsetAsync(buf.wq_count, 0, 64 * sizeof(int32_t), stream);
+    cudaMemsetAsync(buf.slot_mask, 0, (size_t)buf.n * 4 * sizeof(uint32_t), stream);
+  }
   const int npad = (buf.n + BROAD_THREADS - 1) / BROAD_THREADS * BROAD_THREADS;  // CTAs are pair-uniform
   const long long nthread = (long long)npad * HMJ_NPAIR;
   k_broad<<<(int)(nthread / BROAD_THREADS), BROAD_THREADS, 0, stream>>>(tab, buf, npad);

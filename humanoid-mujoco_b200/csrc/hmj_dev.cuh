@@ -277,7 +277,7 @@ __device__ __forceinline__ bool d_is_bad(double x) { return isnan(x) || x > HMJ_
 void hmj_launch_smooth(const hmj_tables_t* tab, hmj_buffers_t buf, const hmj_task_t* task, int plan_mode,
                        const double* spline_times, const double* spline_values, int nnode, int interpolation,
                        int values_per_env, cudaStream_t stream);
-void hmj_launch_collide(const hmj_tables_t* tab, hmj_buffers_t buf, cudaStream_t stream);
+void hmj_launch_collide(const hmj_tables_t* tab, hmj_buffers_t buf, cudaStream_t stream, bool zero = true);
 // Side streams of hmj_launch_solve: the three solver classes are independent, so the (few, long) many-contact solves
 // and the (many, short) unconstrained ones run beside the main class instead of after it.  Null -> one stream.
 struct hmj_solve_ctx_t {
@@ -288,7 +288,7 @@ struct hmj_solve_ctx_t {
 // Contact-independent factorisations (qacc_smooth, Euler factor): call after hmj_launch_smooth, before hmj_launch_solve.
 void hmj_launch_factor(const hmj_tables_t* tab, hmj_buffers_t buf, cudaStream_t stream, const hmj_solve_ctx_t* ctx = nullptr);
 void hmj_launch_solve(const hmj_tables_t* tab, hmj_buffers_t buf, int integrate, cudaStream_t stream,
-                      const hmj_solve_ctx_t* ctx = nullptr);
+                      const hmj_solve_ctx_t* ctx = nullptr, bool zero = true);
 
 // plan_mode bits for hmj_launch_smooth
 #define HMJ_PLAN_COST 1    /* sensors -> residual -> cost accumulation */

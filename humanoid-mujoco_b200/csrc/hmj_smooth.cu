@@ -134,7 +134,13 @@ k_smooth(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* 
   const int lane = threadIdx.x & 31;
   const int wib = threadIdx.x >> 5;
   const int env = blockIdx.x * HMJ_WARPS_PER_CTA + wib;
+  // Zero the per-step work counters of the stages that follow on this stream (narrowphase task counts and item counter,
+  // contact-slot bitmask, solver class counts): three memset nodes less in every step's dependency chain.  The previous
+  // step's consumers of these arrays finished before this kernel started (stream order).
+  if (blockIdx.x == 0 && threadIdx.x < 64) B.wq_count[threadIdx.x] = 0;
+  if (blockIdx.x == 0 && threadIdx.x < 4) B.solve_count[threadIdx.x] = 0;
   if (env >= B.n) return;  // whole warp exits together
+  if (lane < 4) B.slot_mask[(size_t)env * 4 + lane] = 0u;
   SmoothSmem& S = reinterpret_cast<SmoothSmem*>(smem_raw)[wib];
   const hmj_model_t& M = T->m;
   const hmj_params_t* P = B.params + env;

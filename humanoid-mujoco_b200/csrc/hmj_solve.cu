@@ -986,9 +986,9 @@ static void launch_class(const hmj_tables_t* tab, hmj_buffers_t buf, int integra
 // Four launches: classification, then one solver launch per class.  With side streams the many-contact class and the
 // unconstrained class run concurrently with the main class; otherwise the heavy class goes first.
 void hmj_launch_solve(const hmj_tables_t* tab, hmj_buffers_t buf, int integrate, cudaStream_t stream,
-                      const hmj_solve_ctx_t* ctx) {
+                      const hmj_solve_ctx_t* ctx, bool zero) {
   if (ctx) cudaStreamWaitEvent(stream, ctx->fac_done, 0);   // k_factor ran on side[0] beside the collision kernels
-  cudaMemsetAsync(buf.solve_count, 0, 4 * sizeof(int32_t), stream);
+  if (zero) cudaMemsetAsync(buf.solve_count, 0, 4 * sizeof(int32_t), stream);   // else: zeroed by this step's k_smooth
   k_classify<<<(buf.n + 3) / 4, 128, 0, stream>>>(tab, buf);
   if (!ctx) {
     launch_class<HMJ_MAXCON>(tab, buf, integrate, stream);
