@@ -63,15 +63,19 @@ class ClockSampler:
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, index):
-        self.index, self.proc, self.path = index, None, None
+    def __init__(self, indices):
+        """`indices`: the GPUs of the job (one nvidia-smi process on rank 0 watches all of them); empty = no sampling."""
+        self.index = ",".join(str(i) for i in indices)
+        self.proc, self.path = None, None
 
     def start(self):
+        if not self.index:
+            return
         try:
             fd, self.path = tempfile.mkstemp(suffix=".csv")
             os.close(fd)
             self.f = open(self.path, "w")
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", self.index, f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
@@ -306,7 +310,7 @@ def run_gpu(args):
     b.sync()
     barrier()
     torch.cuda.synchronize()
-    clocks = ClockSampler(local)
+    clocks = ClockSampler(range(world) if rank == 0 else [])   # ranks are local GPUs 0..world-1 of one node
     clocks.start()
     l0 = b.kernel_launches
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
