@@ -156,19 +156,38 @@ __device__ __forceinline__ void mesh_support_coop(const double* __restrict__ sx,
       if (vd > best[g]) { best[g] = vd; ibest[g] = i; }
     }
   }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-#pragma unroll
-    for (int g = 0; g < COOP_G; g++) {
-      const double ob = __shfl_xor_sync(FULL, best[g], o);
-      const int oi = __shfl_xor_sync(FULL, ibest[g], o);
-      if (ob > best[g] || (ob == best[g] && oi < ibest[g])) { best[g] = ob; ibest[g] = oi; }
-    }
+  // Transposing butterfly: the four arg-max problems are merged across the warp with 6 exchanges instead of 20.
+  // Round xor-16 leaves each half-warp with two of the groups, round xor-8 leaves each quarter with one, three plain
+  // rounds finish it; group g's result then sits in the lanes with (bit4, bit3) == (g >> 1, g & 1).  The merge (larger
+  // value, lowest index on ties) is associative and commutative: same bits as four full butterflies.
+  static_assert(COOP_G == 4, "the transposing merge is written for four groups");
+  auto merge = [](double& b, int& i, double ob, int oi) { if (ob > b || (ob == b && oi < i)) { b = ob; i = oi; } };
+  const bool hi16 = lane & 16, hi8 = lane & 8;
+  double k0 = hi16 ? best[2] : best[0], k1 = hi16 ? best[3] : best[1];
+  int j0 = hi16 ? ibest[2] : ibest[0], j1 = hi16 ? ibest[3] : ibest[1];
+  {
+    const double s0 = hi16 ? best[0] : best[2], s1 = hi16 ? best[1] : best[3];
+    const int t0 = hi16 ? ibest[0] : ibest[2], t1 = hi16 ? ibest[1] : ibest[3];
+    const double r0 = __shfl_xor_sync(FULL, s0, 16), r1 = __shfl_xor_sync(FULL, s1, 16);
+    const int u0 = __shfl_xor_sync(FULL, t0, 16), u1 = __shfl_xor_sync(FULL, t1, 16);
+    merge(k0, j0, r0, u0);
+    merge(k1, j1, r1, u1);
   }
+  double kb = hi8 ? k1 : k0;
+  int jb = hi8 ? j1 : j0;
+  {
+    const double sb = hi8 ? k0 : k1;
+    const int tb = hi8 ? j0 : j1;
+    merge(kb, jb, __shfl_xor_sync(FULL, sb, 8), __shfl_xor_sync(FULL, tb, 8));
+  }
+#pragma unroll
+  for (int o = 4; o > 0; o >>= 1) merge(kb, jb, __shfl_xor_sync(FULL, kb, o), __shfl_xor_sync(FULL, jb, o));
   int mine = -1;
 #pragma unroll
-  for (int g = 0; g < COOP_G; g++)
-    if (lane == src[g]) mine = ibest[g];
+  for (int g = 0; g < COOP_G; g++) {
+    const int ig = __shfl_sync(FULL, jb, (g >> 1) * 16 + (g & 1) * 8);
+    if (lane == src[g]) mine = ig;
+  }
   if (mine >= 0) {
     if (mine == 0x7fffffff) mine = 0;
     const double p0 = sx[h.base + mine], p1 = sy[h.base + mine], p2 = sz[h.base + mine];
