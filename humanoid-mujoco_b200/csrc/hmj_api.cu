@@ -178,6 +178,19 @@ static void build_tables(const hmj_model_t* m, hmj_tables_t* t) {
       while (bpos > 0 && verts[t->group_order[bpos - 1]] < verts[g]) { t->group_order[bpos] = t->group_order[bpos - 1]; bpos--; }
       t->group_order[bpos] = g;
     }
+    {  // k_broad's CTA order: the expensive (pair, 128-env) CTAs first, so that the round-robin CTA placement gives every
+       // SM one of them before the cheap ones fill the remaining slots
+      int cost[HMJ_NPAIR + 1];
+      for (int k = 0; k < m->npair; k++)
+        cost[k] = (m->pair_geom1[k] == 0 ? 100000 + m->mesh_vertnum[m->geom_meshid[m->pair_geom2[k]]] : 0);
+      for (int k = 0; k <= HMJ_NPAIR; k++) t->broad_order[k] = k;
+      for (int a = 1; a < m->npair; a++) {
+        const int k = t->broad_order[a];
+        int bpos = a;
+        while (bpos > 0 && cost[t->broad_order[bpos - 1]] < cost[k]) { t->broad_order[bpos] = t->broad_order[bpos - 1]; bpos--; }
+        t->broad_order[bpos] = k;
+      }
+    }
     int thr[3] = {250, 180, 50}, capv[3] = {2, 3, 4};
     if (const char* e = getenv("HMJ_NARROW_CAP"))   // developer override: "v0:s0,v1:s1,v2:s2" (vertex threshold : log2 item size)
       sscanf(e, "%d:%d,%d:%d,%d:%d", &thr[0], &capv[0], &thr[1], &capv[1], &thr[2], &capv[2]);

@@ -594,11 +594,12 @@ k_broad(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int npad) {
   __shared__ __align__(16) double sy[HMJ_NVERT_SMEM];
   __shared__ __align__(16) double sz[HMJ_NVERT_SMEM];
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  const int k = t / npad;  // warp-uniform; whole CTAs can be past the last pair
-  const int e = t - k * npad;
+  const int kpos = t / npad;  // warp-uniform; whole CTAs can be past the last pair
+  const int e = t - kpos * npad;
   const int lane = threadIdx.x & 31;
   const hmj_model_t& M = T->m;
-  if (k >= HMJ_NPAIR) return;  // npad * NPAIR is a multiple of 32: whole warps leave together (before any barrier use)
+  if (kpos >= HMJ_NPAIR) return;  // npad * NPAIR is a multiple of 32: whole warps leave together (before any barrier use)
+  const int k = T->broad_order[kpos];   // expensive pairs first (hmj_api.cu: build of the tables)
   const bool in = e < B.n;
   const int env = in ? e : B.n - 1;
   const int g1 = M.pair_geom1[k], g2 = M.pair_geom2[k];

@@ -45,6 +45,7 @@ struct hmj_tables_t {
   int32_t slot_pair[HMJ_NSLOT];      // inverse map
   int32_t pair_group[HMJ_NPAIR + 1]; // narrowphase task group of each pair (hfield pairs: mesh id of geom2)
   int32_t group_base[64];            // first task of group g in wq_task, in units of N; group_base[NGROUP] = total
+  int32_t broad_order[HMJ_NPAIR + 1]; // k_broad serves the pairs in this order: height-field pairs by hull size (descending), then mesh-mesh
   int32_t group_order[64];           // k_narrow hands out items group by group in this order: most expensive hull(s) first (LPT)
   int32_t group_shiftcap[64];        // log2 of the largest item (queries per warp) of group g: 2 for big hulls ... 5 for small ones
   // convex hull vertices, SoA float32, each mesh padded to a multiple of 4 with copies of its vertex 0;
