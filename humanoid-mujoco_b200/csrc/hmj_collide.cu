@@ -33,7 +33,9 @@
 
 #define CCD_EPS DBL_EPSILON
 #define NARROW_THREADS 128
+#ifndef BROAD_THREADS
 #define BROAD_THREADS 128
+#endif
 #ifndef NARROW_MIN_CTAS
 #define NARROW_MIN_CTAS 2
 #endif
