@@ -60,13 +60,29 @@ def load_peaks():
 
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+    Q = ("timestamp,index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, indices):
         """`indices`: the GPUs of the job (one nvidia-smi process on rank 0 watches all of them); empty = no sampling."""
         self.index = ",".join(str(i) for i in indices)
-        self.proc, self.path = None, None
+        self.proc, self.path, self.t_region = None, None, None
+
+    def wait_first(self, timeout=3.0):
+        """Block until nvidia-smi has printed its first poll (its start-up takes longer than a short timed region)."""
+        t_end = time.time() + timeout
+        while self.proc is not None and time.time() < t_end:
+            try:
+                if os.path.getsize(self.path) > 0:
+                    return
+            except OSError:
+                return
+            time.sleep(0.02)
+
+    def mark(self):
+        """Start of the timed region: rows stamped before this moment are dropped (the sampler is started ahead of the
+        warm-up so that nvidia-smi's start-up latency does not eat the region)."""
+        self.t_region = time.time()
 
     def start(self):
         if not self.index:
@@ -75,7 +91,9 @@ class ClockSampler:
             fd, self.path = tempfile.mkstemp(suffix=".csv")
             os.close(fd)
             self.f = open(self.path, "w")
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", self.index, f"--query-gpu={self.Q}",
+            import shutil
+            pre = ["stdbuf", "-oL"] if shutil.which("stdbuf") else []   # line-buffered rows (stdio buffers fully into a file)
+            self.proc = subprocess.Popen(pre + ["nvidia-smi", "-i", self.index, f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
@@ -91,8 +109,23 @@ class ClockSampler:
             pass
         try:
             self.f.close()
-            rows = [r.split(",") for r in open(self.path).read().strip().splitlines() if r.count(",") >= 8]
+            rows = [[c.strip() for c in r.split(",")] for r in open(self.path).read().strip().splitlines() if r.count(",") >= 9]
             os.unlink(self.path)
+
+            def stamp(r):
+                import datetime
+                try:
+                    return datetime.datetime.strptime(r[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                except ValueError:
+                    return 0.0
+
+            inside = [r for r in rows if self.t_region is None or stamp(r) >= self.t_region - 0.05]
+            note = None
+            if not inside and rows:   # region shorter than one poll of all GPUs: the last poll stands in
+                last = stamp(rows[-1])
+                inside = [r for r in rows if stamp(r) >= last - 0.05]
+                note = "no poll fell inside the timed region; nearest poll reported"
+            rows = [r[1:] for r in inside]
             sm = [float(r[1]) for r in rows]
             reasons = set()
             for r in rows:
@@ -102,6 +135,8 @@ class ClockSampler:
             if rows:
                 out = {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(rows[0][2]), "reasons": sorted(reasons),
                        "samples": len(rows), "power_w_max": max(float(r[3]) for r in rows)}
+                if note:
+                    out["note"] = note
         except Exception:
             pass
         return out
@@ -305,13 +340,15 @@ def run_gpu(args):
                                          flags[0].data_ptr(), flags[1].data_ptr(), flags[2].data_ptr()))
 
     # ---- kernel-resident throughput (`value`)
+    clocks = ClockSampler(range(world) if rank == 0 else [])   # ranks are local GPUs 0..world-1 of one node
+    clocks.start()
+    clocks.wait_first()
     for s in range(W):
         device_step(s)
     b.sync()
     barrier()
     torch.cuda.synchronize()
-    clocks = ClockSampler(range(world) if rank == 0 else [])   # ranks are local GPUs 0..world-1 of one node
-    clocks.start()
+    clocks.mark()
     l0 = b.kernel_launches
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
