@@ -183,6 +183,11 @@ class HumanoidBatch:
         check(self.lib.hmj_batch_get_array(self._h, name.encode(), _p(out), out.nbytes))
         return out
 
+    def set_raw(self, name: str, value: np.ndarray):
+        """Upload a named device array from a host array of exactly its size (e.g. "contact": CONTACT_DTYPE [n][MAXCON])."""
+        a = np.ascontiguousarray(value)
+        check(self.lib.hmj_batch_set_array(self._h, name.encode(), _p(a), a.nbytes))
+
     def set(self, name: str, value):
         if name in _INT_ARRAYS:
             a = np.ascontiguousarray(np.broadcast_to(np.asarray(value, dtype=np.int32), (self.n,)))

@@ -132,6 +132,53 @@ def standup_start_state(qpos0: np.ndarray, rng: np.random.Generator, rf: float, 
     return qpos
 
 
+def local_gravity_host(quat: np.ndarray) -> np.ndarray:
+    """inverseRotateVectors(q, (0, 0, -1)) (cpu_env.py:26-28) for rows of wxyz quaternions: Rotation.from_quat
+    normalises, so this is minus the third row of R(q / |q|).  numpy mirror of `local_gravity` in csrc/hmj_aux.cu."""
+    q = np.asarray(quat, dtype=np.float64)
+    q = q / np.linalg.norm(q, axis=-1, keepdims=True)
+    w, x, y, z = q[..., 0], q[..., 1], q[..., 2], q[..., 3]
+    return -np.stack([2 * (x * z - w * y), 2 * (y * z + w * x), w * w - x * x - y * y + z * z], axis=-1)
+
+
+def observation_host(qpos, qvel, root_quat, noise, act_qposadr, act_dofadr) -> np.ndarray:
+    """The undelayed observation of CPUEnv._get_obs (cpu_env.py:465-571) for a batch: noisy joint angles and
+    velocities in JOINT_NAMES (= actuator) order, noisy world-frame angular velocity, local gravity of the noisy
+    quaternion.  numpy mirror of the observation half of k_env_obs_reward."""
+    nz = np.zeros((qpos.shape[0], 31)) if noise is None else np.asarray(noise)
+    return np.concatenate([qpos[:, act_qposadr] + nz[:, 0:12], qvel[:, act_dofadr] + nz[:, 12:24],
+                           qvel[:, 3:6] + nz[:, 24:27], local_gravity_host(root_quat + nz[:, 27:31])], axis=1)
+
+
+def standup_reward_host(qvel, root_quat, root_z, joint_torques, prev_action, latest_action, self_collision, time,
+                        max_sim_time):
+    """standupReward (reward_functions.py:247-374) for a batch, weights and joint pairs as selected there.
+    `prev_action` / `latest_action` are the env's raw actions (the /(pi/2) of cpu_env.py:601-602 happens here).
+    Returns (reward, terminated, truncated).  numpy mirror of the reward half of k_env_obs_reward; pinned against the
+    reference's own function by tests/golden/env_golden.npz."""
+    se = lambda x: np.exp(-x / 0.5)  # noqa: E731  scaled_exp
+    g = local_gravity_host(root_quat)
+    lat = np.asarray(latest_action) / (np.pi / 2)
+    prv = np.asarray(prev_action) / (np.pi / 2)
+    r = 5.0 * se(qvel[:, 0] ** 2 + qvel[:, 1] ** 2)
+    r = r + 10.0 * se(g[:, 0] ** 2 + g[:, 1] ** 2 + (g[:, 2] + 1.0) ** 2)
+    r = r + np.interp(root_z, [-0.6, -0.375], [0.0, 15.0])
+    r = r + 2.5 * se(np.clip(np.abs(joint_torques) - 1.0, 0, np.inf) ** 2).sum(axis=1) / 12.0
+    r = r + 2.0 * se(((lat - prv) * 500.0) ** 2).sum(axis=1) / 12.0
+    r = r + 0.5 * se(lat ** 2).sum(axis=1) / 12.0
+    # JOINT_NAMES order: R sh pitch, R sh roll, R elbow, L sh pitch, L sh roll, L elbow, L hip roll, L hip pitch, L knee,
+    # R hip roll, R hip pitch, R knee; elbows equal, the other pairs opposite
+    sym = se((lat[:, 5] - lat[:, 2]) ** 2)
+    for i, j in ((6, 9), (7, 10), (8, 11), (3, 0), (4, 1)):
+        sym = sym + se((lat[:, i] + lat[:, j]) ** 2)
+    r = r + sym / 6.0
+    r = r + np.where(self_collision, -20.0, 0.0)
+    term = np.asarray(time) >= max_sim_time
+    r = np.where(term, -100.0, r)
+    trunc = (np.asarray(root_z) >= -0.375) & (np.max(np.abs(g[:, :2]), axis=1) < 0.7)
+    return r, term, trunc
+
+
 class SparseInfos(Sequence):
     """The per-env `info` dicts of one batched step as a read-only sequence of length N: only the envs whose episode
     ended carry an entry, everyone else shares one empty dict (building N dicts per step would cost more host time
