@@ -228,12 +228,22 @@ template <typename Tp>
 static int alloc_array(hmj_batch_* b, const char* name, Tp** out, size_t count) {
   void* p = nullptr;
   CK(cudaMalloc(&p, count * sizeof(Tp)));
-  CK(cudaMemsetAsync(p, 0, count * sizeof(Tp), b->stream));
   b->allocs.push_back(p);
+  CK(cudaMemsetAsync(p, 0, count * sizeof(Tp), b->stream));
   if (name) b->arrays[name] = ArrayInfo{p, count * sizeof(Tp)};
   *out = (Tp*)p;
   return HMJ_OK;
 }
+
+// inside hmj_batch_create after `b` exists: a failure must release what was built so far
+#define CKB(call)                                                                   \
+  do {                                                                              \
+    cudaError_t e_ = (call);                                                        \
+    if (e_ != cudaSuccess) {                                                        \
+      hmj_batch_destroy(b);                                                         \
+      return fail(HMJ_ERR_CUDA, "CUDA error: %s", cudaGetErrorString(e_));          \
+    }                                                                               \
+  } while (0)
 
 #define ALLOC(name, field, count)                                   \
   do {                                                              \
@@ -343,18 +353,18 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
   b->n = n_envs;
   b->device = device;
   b->buf.n = n_envs;
-  CK(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
+  CKB(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
   for (int k = 0; k < 2; k++) {
-    CK(cudaStreamCreateWithFlags(&b->solve_ctx.side[k], cudaStreamNonBlocking));
-    CK(cudaEventCreateWithFlags(&b->solve_ctx.join[k], cudaEventDisableTiming));
+    CKB(cudaStreamCreateWithFlags(&b->solve_ctx.side[k], cudaStreamNonBlocking));
+    CKB(cudaEventCreateWithFlags(&b->solve_ctx.join[k], cudaEventDisableTiming));
   }
-  CK(cudaEventCreateWithFlags(&b->solve_ctx.fork, cudaEventDisableTiming));
-  CK(cudaEventCreateWithFlags(&b->solve_ctx.fac_fork, cudaEventDisableTiming));
-  CK(cudaEventCreateWithFlags(&b->solve_ctx.fac_done, cudaEventDisableTiming));
+  CKB(cudaEventCreateWithFlags(&b->solve_ctx.fork, cudaEventDisableTiming));
+  CKB(cudaEventCreateWithFlags(&b->solve_ctx.fac_fork, cudaEventDisableTiming));
+  CKB(cudaEventCreateWithFlags(&b->solve_ctx.fac_done, cudaEventDisableTiming));
   b->tab_host = new hmj_tables_t;
   build_tables(model, b->tab_host);
-  CK(cudaMalloc((void**)&b->tab_dev, sizeof(hmj_tables_t)));
-  CK(cudaMemcpyAsync(b->tab_dev, b->tab_host, sizeof(hmj_tables_t), cudaMemcpyHostToDevice, b->stream));
+  CKB(cudaMalloc((void**)&b->tab_dev, sizeof(hmj_tables_t)));
+  CKB(cudaMemcpyAsync(b->tab_dev, b->tab_host, sizeof(hmj_tables_t), cudaMemcpyHostToDevice, b->stream));
   hmj_task_t task;
   memset(&task, 0, sizeof(task));
   task.nterm = model->task_nterm;
@@ -364,8 +374,8 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
   }
   task.risk = model->task_risk;
   task.height_goal = model->task_height_goal;
-  CK(cudaMalloc((void**)&b->task_dev, sizeof(hmj_task_t)));
-  CK(cudaMemcpyAsync(b->task_dev, &task, sizeof(task), cudaMemcpyHostToDevice, b->stream));
+  CKB(cudaMalloc((void**)&b->task_dev, sizeof(hmj_task_t)));
+  CKB(cudaMemcpyAsync(b->task_dev, &task, sizeof(task), cudaMemcpyHostToDevice, b->stream));
 
   const size_t N = (size_t)n_envs;
   ALLOC("qpos", qpos, N * HMJ_NQ);
@@ -442,11 +452,11 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
     std::vector<hmj_params_t> hp(N);
     hmj_default_params(model, &hp[0]);
     for (size_t i = 1; i < N; i++) hp[i] = hp[0];
-    CK(cudaMemcpyAsync(b->buf.params, hp.data(), N * sizeof(hmj_params_t), cudaMemcpyHostToDevice, b->stream));
+    CKB(cudaMemcpyAsync(b->buf.params, hp.data(), N * sizeof(hmj_params_t), cudaMemcpyHostToDevice, b->stream));
     std::vector<double> q(N * HMJ_NQ);
     for (size_t i = 0; i < N; i++) memcpy(&q[i * HMJ_NQ], model->qpos0, sizeof(model->qpos0));
-    CK(cudaMemcpyAsync(b->buf.qpos, q.data(), q.size() * sizeof(double), cudaMemcpyHostToDevice, b->stream));
-    CK(cudaStreamSynchronize(b->stream));
+    CKB(cudaMemcpyAsync(b->buf.qpos, q.data(), q.size() * sizeof(double), cudaMemcpyHostToDevice, b->stream));
+    CKB(cudaStreamSynchronize(b->stream));
   }
   if (const char* e = getenv("HMJ_GRAPH")) b->graph_mode = atoi(e);   // developer override: 0 = direct launches
   {
@@ -947,6 +957,17 @@ extern "C" int hmj_plan_set_task(hmj_batch_t* b, int nterm, const int32_t* dim, 
 
 static int ensure_record(hmj_batch_t* b, int horizon) {
   if (b->rec_cap >= horizon) { b->rec.horizon = horizon; return HMJ_OK; }
+  if (b->rec_cap > 0) {   // the horizon grew: release the superseded buffers (no kernel uses them: the stream is drained)
+    CK(cudaStreamSynchronize(b->stream));
+    double* old[6] = {b->rec.states, b->rec.actions, b->rec.times, b->rec.residual, b->rec.costs, b->rec.trace};
+    for (double* p : old) {
+      for (size_t k = 0; k < b->allocs.size(); k++)
+        if (b->allocs[k] == (void*)p) { b->allocs.erase(b->allocs.begin() + k); break; }
+      cudaFree(p);
+    }
+    b->rec = hmj_record_t{};
+    b->rec_cap = 0;
+  }
   const size_t HN = (size_t)horizon * b->n;
   int rc;
   if ((rc = alloc_array(b, nullptr, &b->rec.states, HN * HMJ_NSTATE)) || (rc = alloc_array(b, nullptr, &b->rec.actions, HN * HMJ_NU)) ||

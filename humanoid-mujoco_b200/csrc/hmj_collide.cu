@@ -968,14 +968,15 @@ k_narrow(const hmj_tables_t* __restrict__ T, hmj_buffers_t B) {
 }
 
 void hmj_launch_collide(const hmj_tables_t* tab, hmj_buffers_t buf, cudaStream_t stream, bool zero) {
-  static int narrow_grid = 0;
-  if (!narrow_grid) {
-    int dev = 0, sms = 148, per_sm = 2;
-    cudaGetDevice(&dev);
+  static int narrow_grids[HMJ_MAX_DEVICES] = {0};   // persistent grid = SMs x resident CTAs of the current device
+  const int dev = hmj_current_device();
+  if (!narrow_grids[dev]) {
+    int sms = 148, per_sm = 2;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_narrow, NARROW_THREADS, 0);
-    narrow_grid = sms * (per_sm > 0 ? per_sm : 1);
+    narrow_grids[dev] = sms * (per_sm > 0 ? per_sm : 1);
   }
+  const int narrow_grid = narrow_grids[dev];
   if (zero) {   // callers whose k_smooth ran just before on this stream skip this: k_smooth zeroes both
     cudaMemsetAsync(buf.wq_count, 0, 64 * sizeof(int32_t), stream);
     cudaMemsetAsync(buf.slot_mask, 0, (size_t)buf.n * 4 * sizeof(uint32_t), stream);

@@ -17,10 +17,16 @@
 #define HMJ_NSLOT (9 * HMJ_MAXCONPAIR + 28) /* contact slots per env: 9 hfield pairs x cap + 28 mesh pairs */
 #define HMJ_SLOT_DOUBLES 8                  /* dist, pos[3], normal[3], valid */
 #define HMJ_FAC_DOUBLES 192                 /* per-env Euler factor: 171 lower-triangle entries + 18 reciprocal pivots, padded */
-#define HMJ_NFAC 375                        /* LDL update triples (unused by the dense path, kept for tables) */
 #define HMJ_MESH_PAD 4
 #define HMJ_NGROUP (HMJ_NMESH + 28)           /* narrowphase task groups: 7 hulls (hfield prisms) + 28 mesh-mesh pairs */
 #define HMJ_NVERT_SMEM (HMJ_MAXVERT + HMJ_NMESH * HMJ_MESH_PAD)
+
+#define HMJ_MAX_DEVICES 64
+static inline int hmj_current_device() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return (dev >= 0 && dev < HMJ_MAX_DEVICES) ? dev : 0;
+}
 
 #define HMJ_MINVAL 1e-15
 #define HMJ_MAXVAL 1e10

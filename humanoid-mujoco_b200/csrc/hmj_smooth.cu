@@ -509,11 +509,12 @@ k_smooth(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* 
 void hmj_launch_smooth(const hmj_tables_t* tab, hmj_buffers_t buf, const hmj_task_t* task, int plan_mode,
                        const double* spline_times, const double* spline_values, int nnode, int interpolation,
                        int values_per_env, cudaStream_t stream) {
-  static bool configured = false;
+  static bool configured[HMJ_MAX_DEVICES] = {false};   // function attributes are per device
   const size_t smem = sizeof(SmoothSmem) * HMJ_WARPS_PER_CTA;
-  if (!configured) {
+  const int dev = hmj_current_device();
+  if (!configured[dev]) {
     cudaFuncSetAttribute(k_smooth, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    configured = true;
+    configured[dev] = true;
   }
   const int grid = (buf.n + HMJ_WARPS_PER_CTA - 1) / HMJ_WARPS_PER_CTA;
   k_smooth<<<grid, 32 * HMJ_WARPS_PER_CTA, smem, stream>>>(tab, buf, task, plan_mode, spline_times, spline_values,

@@ -129,49 +129,6 @@ __device__ __forceinline__ double chol_factor_solve(double* H, CholScratch* C, d
   return lane < NV ? res : 0.0;
 }
 
-// Variant with the row held in statically indexed registers and shuffles for the column broadcast (fully unrolled).
-__device__ __noinline__ double chol_factor_solve_shfl(double* H, CholScratch* C, double x, int lane) {
-  const unsigned FULL = 0xffffffffu;
-  const int row = lane < NV ? lane : NV - 1;
-  double a[NV], invs[NV];
-  __syncwarp();
-#pragma unroll
-  for (int k = 0; k < NV; k++) a[k] = H[row * LD + k];
-#pragma unroll
-  for (int j = 0; j < NV; j++) {
-    double dj = __shfl_sync(FULL, a[j], j);
-    if (dj < HMJ_MINVAL) dj = HMJ_MINVAL;
-    const double inv = rsqrt(dj);
-    invs[j] = inv;
-    const double lij = (lane == j) ? dj * inv : a[j] * inv;
-    a[j] = lij;
-#pragma unroll
-    for (int k = j + 1; k < NV; k++) {
-      const double lkj = __shfl_sync(FULL, lij, k);
-      a[k] -= lij * lkj;
-    }
-    const double xj = __shfl_sync(FULL, x, j) * inv;
-    const double xu = x - lij * xj;
-    x = (lane > j) ? xu : x;
-    x = (lane == j) ? xj : x;
-  }
-  __syncwarp();
-  if (lane < NV) {
-#pragma unroll
-    for (int k = 0; k < NV; k++)
-      if (k <= lane) H[lane * LD + k] = a[k];
-  }
-  __syncwarp();
-#pragma unroll
-  for (int k = NV - 1; k >= 0; k--) {
-    const double xk = __shfl_sync(FULL, x, k) * invs[k];
-    const double xu = x - H[k * LD + row] * xk;
-    x = (lane < k) ? xu : x;
-    x = (lane == k) ? xk : x;
-  }
-  return lane < NV ? x : 0.0;
-}
-
 __device__ __noinline__ double mat_vec(const double* A, const double* v, int lane) {
   double s = 0.0;
   if (lane < NV) {
@@ -974,11 +931,12 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
 
 template <int MAXC>
 static void launch_class(const hmj_tables_t* tab, hmj_buffers_t buf, int integrate, cudaStream_t stream) {
-  static bool configured = false;
+  static bool configured[HMJ_MAX_DEVICES] = {false};   // function attributes are per device
   const size_t smem = sizeof(SolveSmem<MAXC>);
-  if (!configured) {
+  const int dev = hmj_current_device();
+  if (!configured[dev]) {
     cudaFuncSetAttribute(k_solve<MAXC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    configured = true;
+    configured[dev] = true;
   }
   k_solve<MAXC><<<buf.n, 32, smem, stream>>>(tab, buf, integrate);
 }

@@ -375,18 +375,23 @@ class BatchedHumanoidEnv:
         self.time = io["time"]
         self.torso_quat = io["torso_quat"]
         return self._finish(io["obs"], io["reward"], self._flags(io["terminated"]), self._flags(io["truncated"]),
-                            self._flags(io["self_collision"]))
+                            self._flags(io["self_collision"]), only)
 
     def _flags(self, raw):
         """int32 device flags -> bool array; the all-clear case (almost every step) hands out one shared read-only array."""
         return raw.astype(bool) if raw.any() else self._all_false
 
-    def _finish(self, obs, reward, term, trunc, selfc):
+    def _finish(self, obs, reward, term, trunc, selfc, only=None):
+        """reward_override / potential rewards (cpu_env.py:606-614).  `only`: the envs this step belongs to (reset's probe
+        step of a subset) — the potential-reward memory of the others must not move."""
         if self.reward_override is not None:
             reward = np.full(self.num_envs, float(self.reward_override))
         elif self.use_potential_rewards:
             r = reward - self.previous_reward
-            self.previous_reward = reward.copy()
+            if only is None:
+                self.previous_reward = reward.copy()
+            else:
+                self.previous_reward = np.where(only, reward, self.previous_reward)
             reward = r
         return obs, reward, term, trunc, selfc
 
@@ -478,7 +483,7 @@ class BatchedHumanoidEnv:
                                   self.noise_obs, self.max_simulation_time, 1)
         self.time = res["time"].copy()
         obs, reward, term, trunc, selfc = self._observe(only, res)
-        return self._finish(obs, reward, term, trunc, selfc)
+        return self._finish(obs, reward, term, trunc, selfc, only)
 
     def close(self):
         self.batch.close()

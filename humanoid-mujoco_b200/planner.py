@@ -151,7 +151,6 @@ class SamplingPlanner:
         self._device = device
         self._model_override = model
         self._requested = num_trajectory
-        self.rng = np.random.default_rng(seed)
         self.rank, self.world = 0, 1
         try:
             import torch.distributed as dist
@@ -159,6 +158,9 @@ class SamplingPlanner:
                 self.rank, self.world = dist.get_rank(), dist.get_world_size()
         except Exception:
             pass
+        # every rank draws its own candidates: the per-rank noise stream is (seed, rank), so equal seeds on all ranks
+        # do not duplicate samples
+        self.rng = np.random.default_rng([int(seed), self.rank])
         self.Initialize()
         self.Allocate()
         self.Reset(0)

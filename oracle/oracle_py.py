@@ -24,8 +24,25 @@ _structs, ORC_DEFINES = oracle_dtypes()
 DATA_DTYPE = _structs["orc_data_t"]
 
 
+def _host_key() -> str:
+    """The oracle is built -march=native: identify the host CPU so a library built elsewhere is rebuilt here."""
+    import hashlib
+    try:
+        flags = next(ln for ln in open("/proc/cpuinfo") if ln.startswith("flags"))
+    except Exception:
+        flags = "unknown"
+    return hashlib.sha1(flags.encode()).hexdigest()
+
+
 def build(force: bool = False) -> str:
-    if force or not os.path.exists(LIB_PATH):
+    stamp = os.path.join(_HERE, "_build", "host.key")
+    key = _host_key()
+    have = open(stamp).read().strip() if os.path.exists(stamp) else ""
+    if force or not os.path.exists(LIB_PATH) or have != key:
+        subprocess.check_call(["make", "-B", "-C", _HERE, "_build/libhmj_oracle.so"], stdout=subprocess.DEVNULL)
+        with open(stamp, "w") as f:
+            f.write(key)
+    else:
         subprocess.check_call(["make", "-C", _HERE, "_build/libhmj_oracle.so"], stdout=subprocess.DEVNULL)
     return LIB_PATH
 

@@ -21,12 +21,12 @@ with open(sys.argv[2], "w", newline="") as f:
         w.writerow(rr)
 if len(sys.argv) > 3:
     ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
-    unit = rows[1][ir]
-    scale = {"Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0, "Gbyte": 1e9}.get(unit, 1e6)
+    units = {"Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0, "Gbyte": 1e9}
+    sr, sw = units.get(rows[1][ir], 1e6), units.get(rows[1][iw], 1e6)   # each column carries its own unit
     agg = {}
     for r in rows[2:]:
         k = r[hdr.index("Kernel Name")].split("(")[0].replace("void ", "").strip()
-        agg.setdefault(k, []).append((float(r[ir]) + float(r[iw])) * scale)
+        agg.setdefault(k, []).append(float(r[ir]) * sr + float(r[iw]) * sw)
     out = {k: sum(v) / len(v) for k, v in agg.items()}
     out["k_solve"] = sum(v for k, v in out.items() if k.startswith("k_solve") or k == "k_classify")
     out["k_collide"] = out.get("k_broad", 0) + out.get("k_narrow", 0)
