@@ -244,7 +244,7 @@ def plan_bench(local, rank, world, iters, cpu):
         pl.SetState(q, v, t)
         for _ in range(3):
             pl.OptimizePolicy(horizon)
-        l0 = pl.batch.kernel_launches
+        l0, h0 = pl.batch.kernel_launches, pl.batch.host_launches
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         for _ in range(nit):
@@ -254,7 +254,9 @@ def plan_bench(local, rank, world, iters, cpu):
         n_glob = n_local * (pl.world if name != "C2" else 1)
         out[name] = {"iterations_per_s": nit / dt, "ms_per_iteration": 1e3 * dt / nit, "samples": n_glob, "horizon": horizon,
                      "sample_steps_per_s": n_glob * (horizon - 1) * nit / dt, "iterations": nit,
-                     "kernel_launches_per_iteration": (pl.batch.kernel_launches - l0) / nit,
+                     "kernel_launches_per_iteration": (pl.batch.host_launches - h0) / nit,
+                     "kernel_nodes_per_iteration": (pl.batch.kernel_launches - l0) / nit,
+                     "rollouts": "one CUDA-graph launch per iteration (candidates, rollouts, arg-min on the device)",
                      "winner": int(pl.winner), "winner_return": float(pl.winner_return),
                      "exchange": "none" if n_glob == n_local else "all_gather(cost,idx) + broadcast(winner spline) over NCCL"}
         if cpu and rank == 0:

@@ -71,6 +71,14 @@ def load_library() -> C.CDLL:
     lib.hmj_plan_rollouts_dev.argtypes = [vp, dp, C.c_double, dp, dp, C.c_int, C.c_int, C.c_int, dp]
     lib.hmj_plan_argmin.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_int32)]
     lib.hmj_plan_fetch.argtypes = [vp, C.c_int, C.c_int, dp, dp, dp, dp, dp, dp]
+    lib.hmj_plan_iterate.argtypes = [vp, dp, C.c_double, dp, dp, C.c_int, C.c_int, C.c_int, dp, C.c_double, C.c_double,
+                                     C.c_ulonglong, C.c_ulonglong, C.c_int, vp]
+    lib.hmj_plan_record_size.argtypes = [C.c_int]
+    lib.hmj_plan_record_ptr.argtypes = [vp]
+    lib.hmj_plan_record_ptr.restype = vp
+    lib.hmj_plan_select.argtypes = [vp, vp, C.c_int, C.c_int, dp]
+    lib.hmj_plan_population.argtypes = [vp, C.c_int, dp, vp, dp]
+    lib.hmj_batch_host_launches.argtypes = [vp]
     _LIB = lib
     return lib
 

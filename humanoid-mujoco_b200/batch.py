@@ -295,6 +295,38 @@ class HumanoidBatch:
                                          int(horizon), int(bool(record)), _p(ret), _p(fail)))
         return ret, fail.astype(bool)
 
+    def plan_iterate(self, state, time, spline_times, nominal_values, horizon, interpolation=2, noise=None, noise_std=0.0,
+                     noise_std2=0.0, seed=0, iteration=0, first_global=0, record_dev: int | None = None):
+        """Device half of one OptimizePolicy iteration (hmj_plan_iterate): enqueue only."""
+        state = np.ascontiguousarray(state, dtype=np.float64)
+        st = np.ascontiguousarray(spline_times, dtype=np.float64)
+        nv = np.ascontiguousarray(nominal_values, dtype=np.float64)
+        assert nv.shape == (st.shape[0], NU), nv.shape
+        nz = None
+        if noise is not None:
+            nz = np.ascontiguousarray(noise, dtype=np.float64)
+            assert nz.shape == (self.n, st.shape[0], NU), nz.shape
+        check(self.lib.hmj_plan_iterate(self._h, _p(state), float(time), _p(st), _p(nv), st.shape[0], int(interpolation),
+                                        int(horizon), _p(nz) if nz is not None else None, float(noise_std), float(noise_std2),
+                                        int(seed) & (2**64 - 1), int(iteration), int(first_global), record_dev))
+
+    def plan_select(self, nnode: int, gathered_dev: int | None = None, nranks: int = 1) -> np.ndarray:
+        """Global winner record {cost, global index, nominal return, spline values [nnode][12]} (hmj_plan_select)."""
+        rec = np.zeros(self.lib.hmj_plan_record_size(int(nnode)))
+        check(self.lib.hmj_plan_select(self._h, gathered_dev, int(nranks), int(nnode), _p(rec)))
+        return rec
+
+    def plan_population(self, nnode: int, values: bool = True):
+        ret = np.zeros(self.n)
+        fail = np.zeros(self.n, dtype=np.int32)
+        vals = np.zeros((self.n, int(nnode), NU)) if values else None
+        check(self.lib.hmj_plan_population(self._h, int(nnode), _p(ret), _p(fail), _p(vals) if values else None))
+        return ret, fail.astype(bool), vals
+
+    @property
+    def host_launches(self) -> int:
+        return int(self.lib.hmj_batch_host_launches(self._h))
+
     def plan_argmin(self):
         cost, idx = C.c_double(0), C.c_int32(0)
         check(self.lib.hmj_plan_argmin(self._h, C.byref(cost), C.byref(idx)))

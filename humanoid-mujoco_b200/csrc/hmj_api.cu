@@ -7,6 +7,7 @@
 #include <cstring>
 #include <map>
 #include <string>
+#include <tuple>
 #include <vector>
 
 #include "../../include/hmj_b200.h"
@@ -44,6 +45,22 @@ struct hmj_batch_ {
   double* returns_dev = nullptr;     // [N]
   int32_t* failure_dev = nullptr;    // [N]
   double* argmin_dev = nullptr;      // [2]
+  double* nominal_dev = nullptr;     // [64][12] nominal spline values of hmj_plan_iterate
+  double* noise_dev = nullptr;       // [N][nnode][12] caller-provided noise (same capacity as spline_values_dev)
+  double* record_dev = nullptr;      // [3 + 64*12] this rank's winner record
+  double* select_dev = nullptr;      // [3 + 64*12] global winner record
+  double* plan_stage = nullptr;      // pinned [2048]: state|time @0, spline times @64, nominal @128, record out @1024
+  int plan_nnode = 0;
+  int host_launches = 0;             // API-level launches (a graph replay counts once)
+  struct RolloutKey {
+    int nnode, interp, horizon, record;
+    const void* values; void* returns; void* failure; void* rec;
+    bool operator<(const RolloutKey& o) const {
+      return std::tie(nnode, interp, horizon, record, values, returns, failure, rec) <
+             std::tie(o.nnode, o.interp, o.horizon, o.record, o.values, o.returns, o.failure, o.rec);
+    }
+  };
+  std::map<RolloutKey, cudaGraphExec_t> rollout_graphs;
   hmj_record_t rec{};
   int rec_cap = 0;
   // env scratch
@@ -312,6 +329,8 @@ extern "C" void hmj_batch_destroy(hmj_batch_t* b) {
   for (void* p : b->allocs) cudaFree(p);
   for (cudaEvent_t e : b->prof_events) cudaEventDestroy(e);
   if (b->io_host) cudaFreeHost(b->io_host);
+  if (b->plan_stage) cudaFreeHost(b->plan_stage);
+  for (auto& kv : b->rollout_graphs) cudaGraphExecDestroy(kv.second);
   if (b->tab_dev) cudaFree(b->tab_dev);
   if (b->task_dev) cudaFree(b->task_dev);
   for (int k = 0; k < 2; k++)
@@ -414,7 +433,8 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
   ALLOC("trace", trace, N * 3);
   {
     int rc;
-    if ((rc = alloc_array(b, nullptr, &b->state_dev, HMJ_NSTATE)) || (rc = alloc_array(b, nullptr, &b->spline_times_dev, 64)) ||
+    if ((rc = alloc_array(b, nullptr, &b->state_dev, HMJ_NSTATE + 1)) || (rc = alloc_array(b, nullptr, &b->nominal_dev, 64 * HMJ_NU)) ||
+        (rc = alloc_array(b, nullptr, &b->record_dev, 3 + 64 * HMJ_NU)) || (rc = alloc_array(b, nullptr, &b->select_dev, 3 + 64 * HMJ_NU)) || (rc = alloc_array(b, nullptr, &b->spline_times_dev, 64)) ||
         (rc = alloc_array(b, "returns", &b->returns_dev, N)) || (rc = alloc_array(b, nullptr, &b->failure_dev, N)) ||
         (rc = alloc_array(b, "argmin", &b->argmin_dev, 2))) {
       hmj_batch_destroy(b);
@@ -445,6 +465,8 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
     if (!rc && cudaHostAlloc((void**)&b->io_host, b->io_in_bytes + b->io_out_bytes, cudaHostAllocDefault) != cudaSuccess)
       rc = fail(HMJ_ERR_CUDA, "cudaHostAlloc failed%s");
     if (!rc) { memset(b->io_host, 0, b->io_in_bytes + b->io_out_bytes); rc = alloc_array(b, nullptr, &b->io_dev, b->io_in_bytes + b->io_out_bytes); }
+    if (!rc && cudaHostAlloc((void**)&b->plan_stage, 2048 * sizeof(double), cudaHostAllocDefault) != cudaSuccess)
+      rc = fail(HMJ_ERR_CUDA, "cudaHostAlloc failed%s");
     if (rc) { hmj_batch_destroy(b); return rc; }
   }
   // default params and state (qpos0) for every env
@@ -469,6 +491,7 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
 
 extern "C" int hmj_batch_size(const hmj_batch_t* b) { return b ? b->n : 0; }
 extern "C" int hmj_batch_kernel_launches(const hmj_batch_t* b) { return b ? b->launches : 0; }
+extern "C" int hmj_batch_host_launches(const hmj_batch_t* b) { return b ? b->host_launches : 0; }
 extern "C" void* hmj_batch_stream(hmj_batch_t* b) { return b ? (void*)b->stream : nullptr; }
 
 extern "C" int hmj_batch_sync(hmj_batch_t* b) {
@@ -571,7 +594,7 @@ static void enqueue_step(hmj_batch_t* b, int integrate) {
   if (prof) prof_event(b);
   hmj_launch_solve(b->tab_dev, b->buf, integrate, b->stream, &b->solve_ctx);
   if (prof) prof_event(b);
-  b->launches += 8;  // smooth, factor, broad, narrow, classify, solve x 3 classes
+  b->launches += 8; b->host_launches += 8;  // smooth, factor, broad, narrow, classify, solve x 3 classes
 }
 
 // The launches of ONE physics step of the whole batch, on the main stream (forking pipes / side streams and joining
@@ -611,6 +634,7 @@ static void enqueue_steps(hmj_batch_t* b, int integrate, int nsteps) {
   for (int s = 0; s < nsteps; s++) {
     b->launches += per_step;
     if (b->graph_mode == 0 || !b->warmed) {   // graphs disabled, or first step ever
+      b->host_launches += per_step;
       enqueue_one_step(b, integrate);
       b->warmed = true;
       continue;
@@ -638,6 +662,7 @@ static void enqueue_steps(hmj_batch_t* b, int integrate, int nsteps) {
       }
     }
     cudaGraphLaunch(b->step_graph[f], b->stream);
+    b->host_launches += 1;
   }
 }
 
@@ -713,7 +738,7 @@ extern "C" int hmj_batch_run_stage(hmj_batch_t* b, int stage) {
       break;
     default: return fail(HMJ_ERR_ARG, "unknown stage%s");
   }
-  b->launches += 1;
+  b->launches += 1; b->host_launches += 1;
   CK(cudaStreamSynchronize(b->stream));
   CK(cudaGetLastError());
   return HMJ_OK;
@@ -767,7 +792,7 @@ extern "C" int hmj_env_obs_reward_dev(hmj_batch_t* b, const double* prev_action_
   CK(cudaSetDevice(b->device));
   hmj_launch_env_obs_reward(b->tab_dev, b->buf, prev_action_dev, latest_action_dev, noise_dev, max_sim_time, obs_dev, reward_dev,
                             terminated_dev, truncated_dev, self_collision_dev, b->stream);
-  b->launches += 1;
+  b->launches += 1; b->host_launches += 1;
   CK(cudaGetLastError());
   return HMJ_OK;
 }
@@ -845,7 +870,7 @@ extern "C" int hmj_env_step(hmj_batch_t* b, const double* ctrl, const int32_t* x
   enqueue_steps(b, 1, nsteps);
   hmj_launch_env_obs_reward(b->tab_dev, b->buf, d_prev, d_lat, noise ? d_noise : nullptr, max_sim_time, d_obs, d_rew, d_term,
                             d_trunc, d_self, b->stream);
-  b->launches += 1;
+  b->launches += 1; b->host_launches += 1;
   if ((rc = d2h(b, obs, d_obs, 30 * N * 8)) || (rc = d2h(b, reward, d_rew, N * 8)) || (rc = d2h(b, terminated, d_term, N * 4)) ||
       (rc = d2h(b, truncated, d_trunc, N * 4)) || (rc = d2h(b, self_collision, d_self, N * 4)) ||
       (rc = d2h(b, time_out, b->buf.time, N * 8)))
@@ -909,7 +934,7 @@ extern "C" int hmj_env_step_fused_from(hmj_batch_t* b, const double* action_host
   hmj_launch_env_obs_reward(b->tab_dev, b->buf, b->env.prev_action, b->env.latest_action, b->env.obs_noise, max_sim_time, d_obs,
                             d_rew, d_flags, d_flags + N, d_flags + 2 * N, b->stream);
   hmj_launch_env_post(b->buf, b->env, mask, d_obs, d_time, d_quat, b->stream);
-  b->launches += 3;
+  b->launches += 3; b->host_launches += 3;
   CK(cudaMemcpyAsync(b->io_host + b->io_in_bytes, d_out, b->io_out_bytes, cudaMemcpyDeviceToHost, b->stream));
   CK(cudaStreamSynchronize(b->stream));
   CK(cudaGetLastError());
@@ -979,33 +1004,103 @@ static int ensure_record(hmj_batch_t* b, int horizon) {
   return HMJ_OK;
 }
 
+// The launches of one batch of rollouts (Trajectory::NoisyRollout for every sample, trajectory.cc:100-210), no host data:
+// init from the state block, H-1 x [policy + smooth + residual/cost -> factor || collide -> solve + Euler], the final
+// mj_forward (sensors/residual only; ctrl keeps the last action, trajectory.cc:190-206), returns.
+static void enqueue_rollout_chain(hmj_batch_t* b, const double* values_dev, int nnode, int interpolation, int horizon, int record,
+                                  double* returns_dev, int32_t* failure_dev) {
+  hmj_launch_plan_init(b->buf, b->state_dev, b->stream);
+  for (int t = 0; t < horizon - 1; t++) {
+    hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, HMJ_PLAN_COST | HMJ_PLAN_POLICY, b->spline_times_dev, values_dev, nnode,
+                      interpolation, 1, b->stream);
+    if (record) hmj_launch_plan_record(b->buf, b->rec, t, b->stream);
+    hmj_launch_factor(b->tab_dev, b->buf, b->stream, &b->solve_ctx);
+    hmj_launch_collide(b->tab_dev, b->buf, b->stream, false);
+    hmj_launch_solve(b->tab_dev, b->buf, 1, b->stream, &b->solve_ctx, false);
+  }
+  hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, HMJ_PLAN_COST, nullptr, nullptr, 0, 0, 0, b->stream);
+  if (record) hmj_launch_plan_record(b->buf, b->rec, horizon - 1, b->stream);
+  hmj_launch_plan_finish(b->buf, horizon, returns_dev, failure_dev, b->stream);
+}
+
+// One batch of rollouts = ONE graph launch.  Everything that changes between planning iterations (state, time, spline
+// nodes, candidate values) lives in device buffers at fixed addresses, so the chain is captured once per
+// (nnode, interpolation, horizon, record, buffers) and replayed; a horizon of 100 is ~800 kernel nodes that would
+// otherwise be ~1500 API calls per iteration.
+static int launch_rollouts(hmj_batch_t* b, const double* values_dev, int nnode, int interpolation, int horizon, int record,
+                           double* returns_dev, int32_t* failure_dev) {
+  b->launches += 1 + (horizon - 1) * (8 + (record ? 1 : 0)) + 1 + (record ? 1 : 0) + 1;
+  if (b->graph_mode == 0 || !b->warmed) {   // first use of the launchers performs their one-time attribute queries
+    enqueue_rollout_chain(b, values_dev, nnode, interpolation, horizon, record, returns_dev, failure_dev);
+    b->warmed = true;
+    b->host_launches += 1 + (horizon - 1) * (8 + (record ? 1 : 0)) + 1 + (record ? 1 : 0) + 1;
+    CK(cudaGetLastError());
+    return HMJ_OK;
+  }
+  const hmj_batch_::RolloutKey key{nnode, interpolation, horizon, record, (const void*)values_dev, (void*)returns_dev,
+                                   (void*)failure_dev, (void*)b->rec.states};
+  auto it = b->rollout_graphs.find(key);
+  if (it == b->rollout_graphs.end()) {
+    if (b->rollout_graphs.size() >= 32) {   // callers that sweep horizons: drop the cache rather than grow without bound
+      for (auto& kv : b->rollout_graphs) cudaGraphExecDestroy(kv.second);
+      b->rollout_graphs.clear();
+    }
+    cudaGraph_t g = nullptr;
+    cudaGraphExec_t ge = nullptr;
+    CK(cudaStreamBeginCapture(b->stream, cudaStreamCaptureModeThreadLocal));
+    enqueue_rollout_chain(b, values_dev, nnode, interpolation, horizon, record, returns_dev, failure_dev);
+    cudaError_t e = cudaStreamEndCapture(b->stream, &g);
+    if (e == cudaSuccess && g) e = cudaGraphInstantiate(&ge, g, 0);
+    if (g) cudaGraphDestroy(g);
+    if (e != cudaSuccess || !ge) return fail(HMJ_ERR_CUDA, "rollout graph capture failed: %s", cudaGetErrorString(e));
+    it = b->rollout_graphs.emplace(key, ge).first;
+  }
+  CK(cudaGraphLaunch(it->second, b->stream));
+  b->host_launches += 1;
+  return HMJ_OK;
+}
+
+static int upload_plan_inputs(hmj_batch_t* b, const double* state, double time, const double* spline_times, int nnode, int horizon) {
+  if (nnode < 0 || nnode > 64 || horizon < 1 || horizon > 512) return fail(HMJ_ERR_ARG, "bad nnode/horizon%s");  // kMaxTrajectoryHorizon
+  double* st = b->plan_stage;   // pinned: state | time | spline times
+  memcpy(st, state, HMJ_NSTATE * 8);
+  st[HMJ_NSTATE] = time;
+  CK(cudaMemcpyAsync(b->state_dev, st, (HMJ_NSTATE + 1) * 8, cudaMemcpyHostToDevice, b->stream));
+  if (nnode) {
+    memcpy(st + 64, spline_times, (size_t)nnode * 8);
+    CK(cudaMemcpyAsync(b->spline_times_dev, st + 64, (size_t)nnode * 8, cudaMemcpyHostToDevice, b->stream));
+  }
+  return HMJ_OK;
+}
+
 static int enqueue_rollouts(hmj_batch_t* b, const double* state, double time, const double* spline_times,
                             const double* spline_values_dev, int nnode, int interpolation, int horizon, int record,
                             double* returns_dev, int32_t* failure_dev) {
-  if (nnode < 0 || nnode > 64 || horizon < 1 || horizon > 512) return fail(HMJ_ERR_ARG, "bad nnode/horizon%s");  // kMaxTrajectoryHorizon
-  CK(cudaMemcpyAsync(b->state_dev, state, HMJ_NSTATE * 8, cudaMemcpyHostToDevice, b->stream));
-  if (nnode) CK(cudaMemcpyAsync(b->spline_times_dev, spline_times, (size_t)nnode * 8, cudaMemcpyHostToDevice, b->stream));
-  if (record) {
-    int rc = ensure_record(b, horizon);
-    if (rc) return rc;
+  // the pinned staging block is reused by the next call: wait for the previous copies out of it
+  CK(cudaStreamSynchronize(b->stream));
+  int rc = upload_plan_inputs(b, state, time, spline_times, nnode, horizon);
+  if (rc) return rc;
+  if (record && (rc = ensure_record(b, horizon))) return rc;
+  return launch_rollouts(b, spline_values_dev, nnode, interpolation, horizon, record, returns_dev, failure_dev);
+}
+
+static int ensure_values(hmj_batch_t* b, int nnode) {
+  const size_t nvals = (size_t)b->n * nnode * HMJ_NU;
+  if (b->spline_values_cap >= nvals) return HMJ_OK;
+  CK(cudaStreamSynchronize(b->stream));
+  for (void** pp : {(void**)&b->spline_values_dev, (void**)&b->noise_dev}) {
+    if (*pp) {
+      for (size_t k = 0; k < b->allocs.size(); k++)
+        if (b->allocs[k] == *pp) { b->allocs.erase(b->allocs.begin() + k); break; }
+      cudaFree(*pp);
+      *pp = nullptr;
+    }
+    void* p = nullptr;
+    CK(cudaMalloc(&p, nvals * 8));
+    b->allocs.push_back(p);
+    *pp = p;
   }
-  hmj_launch_plan_init(b->buf, b->state_dev, time, b->stream);
-  b->launches += 1;
-  for (int t = 0; t < horizon - 1; t++) {
-    hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, HMJ_PLAN_COST | HMJ_PLAN_POLICY, b->spline_times_dev, spline_values_dev, nnode,
-                      interpolation, 1, b->stream);
-    if (record) { hmj_launch_plan_record(b->buf, b->rec, t, b->stream); b->launches += 1; }
-    hmj_launch_factor(b->tab_dev, b->buf, b->stream, &b->solve_ctx);
-    hmj_launch_collide(b->tab_dev, b->buf, b->stream);
-    hmj_launch_solve(b->tab_dev, b->buf, 1, b->stream, &b->solve_ctx);
-    b->launches += 8;
-  }
-  // final mj_forward: only the sensors/residual matter, ctrl keeps the last action (trajectory.cc:190-206)
-  hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, HMJ_PLAN_COST, nullptr, nullptr, 0, 0, 0, b->stream);
-  if (record) { hmj_launch_plan_record(b->buf, b->rec, horizon - 1, b->stream); b->launches += 1; }
-  hmj_launch_plan_finish(b->buf, horizon, returns_dev, failure_dev, b->stream);
-  b->launches += 2;
-  CK(cudaGetLastError());
+  b->spline_values_cap = nvals;
   return HMJ_OK;
 }
 
@@ -1022,17 +1117,12 @@ extern "C" int hmj_plan_rollouts(hmj_batch_t* b, const double* state, double tim
                                  double* total_return, int32_t* failure) {
   if (!b || !state || !spline_times || !spline_values || !total_return) return fail(HMJ_ERR_ARG, "bad argument to plan_rollouts%s");
   CK(cudaSetDevice(b->device));
+  int rc = ensure_values(b, nnode);
+  if (rc) return rc;
   const size_t nvals = (size_t)b->n * nnode * HMJ_NU;
-  if (b->spline_values_cap < nvals) {
-    void* p = nullptr;
-    CK(cudaMalloc(&p, nvals * 8));
-    b->allocs.push_back(p);
-    b->spline_values_dev = (double*)p;
-    b->spline_values_cap = nvals;
-  }
   CK(cudaMemcpyAsync(b->spline_values_dev, spline_values, nvals * 8, cudaMemcpyHostToDevice, b->stream));
-  int rc = enqueue_rollouts(b, state, time, spline_times, b->spline_values_dev, nnode, interpolation, horizon, record,
-                            b->returns_dev, b->failure_dev);
+  rc = enqueue_rollouts(b, state, time, spline_times, b->spline_values_dev, nnode, interpolation, horizon, record,
+                        b->returns_dev, b->failure_dev);
   if (rc) return rc;
   if ((rc = d2h(b, total_return, b->returns_dev, (size_t)b->n * 8)) || (rc = d2h(b, failure, b->failure_dev, (size_t)b->n * 4))) return rc;
   CK(cudaStreamSynchronize(b->stream));
@@ -1040,11 +1130,85 @@ extern "C" int hmj_plan_rollouts(hmj_batch_t* b, const double* state, double tim
   return HMJ_OK;
 }
 
+// ---- one predictive-sampling iteration with the candidates built on the device (SamplingPlanner::OptimizePolicy's
+// device half, planner.cc:190-208, 313-380): candidates = clamp(nominal + noise), N rollouts (one graph launch), local
+// arg-min, winner record.  Nothing is read back: the caller all-gathers the record (hmj_plan_record_size doubles at
+// `record_dev`, or the batch's own buffer when NULL) over its communicator ON hmj_batch_stream and finishes with
+// hmj_plan_select.  noise == NULL draws the noise on the device (seed, iteration, global sample index).
+extern "C" int hmj_plan_iterate(hmj_batch_t* b, const double* state, double time, const double* spline_times,
+                                const double* nominal_values, int nnode, int interpolation, int horizon, const double* noise,
+                                double noise_std, double noise_std2, unsigned long long seed, unsigned long long iteration,
+                                int first_global, double* record_dev) {
+  if (!b || !state || !spline_times || !nominal_values || nnode < 1) return fail(HMJ_ERR_ARG, "bad argument to plan_iterate%s");
+  CK(cudaSetDevice(b->device));
+  int rc = ensure_values(b, nnode);
+  if (rc) return rc;
+  CK(cudaStreamSynchronize(b->stream));   // pinned staging reuse
+  if ((rc = upload_plan_inputs(b, state, time, spline_times, nnode, horizon))) return rc;
+  double* nom = b->plan_stage + 128;
+  memcpy(nom, nominal_values, (size_t)nnode * HMJ_NU * 8);
+  CK(cudaMemcpyAsync(b->nominal_dev, nom, (size_t)nnode * HMJ_NU * 8, cudaMemcpyHostToDevice, b->stream));
+  const size_t nvals = (size_t)b->n * nnode * HMJ_NU;
+  if (noise) CK(cudaMemcpyAsync(b->noise_dev, noise, nvals * 8, cudaMemcpyHostToDevice, b->stream));
+  hmj_launch_plan_candidates(b->tab_dev, b->n, nnode, b->nominal_dev, noise ? b->noise_dev : nullptr, noise_std, noise_std2, seed,
+                             iteration, first_global, b->spline_values_dev, b->stream);
+  if ((rc = launch_rollouts(b, b->spline_values_dev, nnode, interpolation, horizon, 0, b->returns_dev, b->failure_dev))) return rc;
+  hmj_launch_plan_winner(b->returns_dev, b->n, b->spline_values_dev, nnode, first_global, b->argmin_dev,
+                         record_dev ? record_dev : b->record_dev, b->stream);
+  b->launches += 2;
+  b->host_launches += 2;
+  b->plan_nnode = nnode;
+  CK(cudaGetLastError());
+  return HMJ_OK;
+}
+
+extern "C" int hmj_plan_record_size(int nnode) { return 3 + nnode * HMJ_NU; }
+extern "C" void* hmj_plan_record_ptr(hmj_batch_t* b) { return b ? (void*)b->record_dev : nullptr; }
+
+// Second half of the exchange (the parallel form of the partial_sort + CopyCandidateToPolicy pair, planner.cc:151-187,
+// 525-534): `gathered_dev` = nranks winner records, rank-major (NULL / nranks <= 1: this batch's own record).  Picks the
+// global winner on the batch stream and returns its record to the host: {cost, global index, nominal return, spline values}.
+extern "C" int hmj_plan_select(hmj_batch_t* b, const double* gathered_dev, int nranks, int nnode, double* record_host) {
+  if (!b || !record_host || nnode < 1 || nnode > 64) return fail(HMJ_ERR_ARG, "bad argument to plan_select%s");
+  CK(cudaSetDevice(b->device));
+  const int stride = hmj_plan_record_size(nnode);
+  const double* src = b->record_dev;
+  if (gathered_dev && nranks > 1) {
+    hmj_launch_plan_select(gathered_dev, nranks, stride, b->select_dev, b->stream);
+    b->launches += 1;
+    b->host_launches += 1;
+    src = b->select_dev;
+  } else if (gathered_dev) {
+    src = gathered_dev;
+  }
+  double* out = b->plan_stage + 1024;
+  CK(cudaMemcpyAsync(out, src, (size_t)stride * 8, cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  CK(cudaGetLastError());
+  memcpy(record_host, out, (size_t)stride * 8);
+  return HMJ_OK;
+}
+
+// Returns / failure flags / candidate values of the last hmj_plan_iterate (any may be NULL), for callers that want the
+// whole population (the reference keeps trajectory[i].total_return).
+extern "C" int hmj_plan_population(hmj_batch_t* b, int nnode, double* total_return, int32_t* failure, double* values) {
+  if (!b) return fail(HMJ_ERR_ARG, "null batch%s");
+  CK(cudaSetDevice(b->device));
+  int rc;
+  if ((rc = d2h(b, total_return, b->returns_dev, (size_t)b->n * 8)) || (rc = d2h(b, failure, b->failure_dev, (size_t)b->n * 4))) return rc;
+  if (values) {
+    if ((size_t)b->n * nnode * HMJ_NU > b->spline_values_cap) return fail(HMJ_ERR_ARG, "no candidates of that size%s");
+    if ((rc = d2h(b, values, b->spline_values_dev, (size_t)b->n * nnode * HMJ_NU * 8))) return rc;
+  }
+  CK(cudaStreamSynchronize(b->stream));
+  return HMJ_OK;
+}
+
 extern "C" int hmj_plan_argmin(hmj_batch_t* b, double* best_cost, int32_t* best_index) {
   if (!b) return fail(HMJ_ERR_ARG, "null batch%s");
   CK(cudaSetDevice(b->device));
   hmj_launch_argmin(b->returns_dev, b->n, b->argmin_dev, b->stream);
-  b->launches += 1;
+  b->launches += 1; b->host_launches += 1;
   double out[2];
   CK(cudaMemcpyAsync(out, b->argmin_dev, sizeof(out), cudaMemcpyDeviceToHost, b->stream));
   CK(cudaStreamSynchronize(b->stream));

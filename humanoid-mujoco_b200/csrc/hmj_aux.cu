@@ -9,9 +9,12 @@
 #include "hmj_dev.cuh"
 
 // ------------------------------------------------------------------ planner
-__global__ void k_plan_init(hmj_buffers_t B, const double* __restrict__ state, double time) {
+// `state` = qpos | qvel | time (HMJ_NSTATE + 1 doubles on the device: no by-value argument changes between planning
+// iterations, so the whole rollout replays as one CUDA graph)
+__global__ void k_plan_init(hmj_buffers_t B, const double* __restrict__ state) {
   const int env = blockIdx.x * blockDim.x + threadIdx.x;
   if (env >= B.n) return;
+  const double time = state[HMJ_NSTATE];
   for (int k = 0; k < HMJ_NQ; k++) B.qpos[(size_t)env * HMJ_NQ + k] = state[k];
   for (int k = 0; k < HMJ_NV; k++) {
     B.qvel[(size_t)env * HMJ_NV + k] = state[HMJ_NQ + k];
@@ -71,8 +74,8 @@ __global__ void k_argmin(const double* __restrict__ returns, int n, double* __re
   if (threadIdx.x == 0) { out[0] = sv[0]; out[1] = (double)si[0]; }
 }
 
-void hmj_launch_plan_init(hmj_buffers_t buf, const double* state_dev, double time, cudaStream_t stream) {
-  k_plan_init<<<(buf.n + 127) / 128, 128, 0, stream>>>(buf, state_dev, time);
+void hmj_launch_plan_init(hmj_buffers_t buf, const double* state_dev, cudaStream_t stream) {
+  k_plan_init<<<(buf.n + 127) / 128, 128, 0, stream>>>(buf, state_dev);
 }
 void hmj_launch_plan_record(hmj_buffers_t buf, hmj_record_t rec, int t, cudaStream_t stream) {
   k_plan_record<<<(buf.n + 127) / 128, 128, 0, stream>>>(buf, rec, t);
@@ -82,6 +85,106 @@ void hmj_launch_plan_finish(hmj_buffers_t buf, int horizon, double* returns_dev,
 }
 void hmj_launch_argmin(const double* returns_dev, int n, double* out, cudaStream_t stream) {
   k_argmin<<<1, 1024, 0, stream>>>(returns_dev, n, out);
+}
+
+// ------------------------------------------------------------------ one planning iteration on the device
+// SamplingPlanner::AddNoiseToPolicy (mjpc/planners/sampling/planner.cc:313-339): candidate s = clamp(nominal + noise_s);
+// the sample with GLOBAL index 0 keeps the nominal (planner.cc:361).  `noise` != NULL: caller-provided values (parity
+// tests inject them); NULL: drawn here from the counter-based stream (seed, iteration, global sample, element) with
+// Box-Muller — the reference draws absl::Gaussian from an entropy-seeded BitGen (unpinned by construction).
+// std_s = std1 with probability 0.2 when std1 > 0 (planner.cc:324-329), else std0.  Thread per (sample, node, actuator).
+__global__ void k_plan_candidates(const hmj_tables_t* __restrict__ T, int n, int nnode, const double* __restrict__ nominal,
+                                  const double* __restrict__ noise, double std0, double std1, unsigned long long seed,
+                                  unsigned long long iteration, int first_global, double* __restrict__ values) {
+  const int per = nnode * HMJ_NU;
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (long long)n * per) return;
+  const int s = (int)(t / per), e = (int)(t - (long long)s * per), a = e % HMJ_NU;
+  const double lo = T->m.act_ctrlrange[a][0], hi = T->m.act_ctrlrange[a][1];
+  double z = 0.0;
+  if (first_global + s != 0) {
+    if (noise) {
+      z = noise[t];
+    } else {
+      const uint64_t key = hmj_splitmix64(seed ^ hmj_splitmix64(iteration + 0x632BE59BD9B4E019ull));
+      const uint32_t gs = (uint32_t)(first_global + s);
+      double sd = std0;
+      if (std1 > 0 && hmj_rand_u01(key, gs, 0xFFFFFFFFu) < 0.2) sd = std1;
+      const double u1 = 1.0 - hmj_rand_u01(key, gs, 2u * (uint32_t)e);        // (0, 1]
+      const double u2 = hmj_rand_u01(key, gs, 2u * (uint32_t)e + 1u);
+      z = sqrt(-2.0 * log(u1)) * cospi(2.0 * u2) * (0.5 * (hi - lo)) * sd;
+    }
+  }
+  const double v = nominal[e] + z;
+  values[t] = fmin(fmax(v, lo), hi);
+}
+
+// Local arg-min of the returns (lowest index wins ties) and the winner record this rank contributes to the exchange:
+// rec = { cost, GLOBAL index, return of local sample 0 (the nominal on the rank that owns global sample 0), winner spline
+// values [nnode][12] }.  Single CTA.
+__global__ void k_plan_winner(const double* __restrict__ returns, int n, const double* __restrict__ values, int nnode,
+                              int first_global, double* __restrict__ argmin_out, double* __restrict__ rec) {
+  __shared__ double sv[1024];
+  __shared__ int si[1024];
+  double best = INFINITY;
+  int bi = 0x7fffffff;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const double v = returns[i];
+    if (v < best || (v == best && i < bi)) { best = v; bi = i; }
+  }
+  sv[threadIdx.x] = best; si[threadIdx.x] = bi;
+  __syncthreads();
+  for (int s = blockDim.x / 2; s > 0; s >>= 1) {
+    if (threadIdx.x < s) {
+      const double ov = sv[threadIdx.x + s];
+      const int oi = si[threadIdx.x + s];
+      if (ov < sv[threadIdx.x] || (ov == sv[threadIdx.x] && oi < si[threadIdx.x])) { sv[threadIdx.x] = ov; si[threadIdx.x] = oi; }
+    }
+    __syncthreads();
+  }
+  const int w = si[0] == 0x7fffffff ? 0 : si[0];   // every return NaN: sample 0 stands
+  if (threadIdx.x == 0) {
+    argmin_out[0] = sv[0]; argmin_out[1] = (double)w;
+    rec[0] = returns[w]; rec[1] = (double)(first_global + w); rec[2] = returns[0];
+  }
+  for (int e = threadIdx.x; e < nnode * HMJ_NU; e += blockDim.x) rec[3 + e] = values[(size_t)w * nnode * HMJ_NU + e];
+}
+
+// The exchange's reduction: `gathered` holds one winner record per rank (stride doubles each).  The global winner is the
+// lexicographic minimum of (cost, global index) — NaN costs never win unless all are NaN — and the nominal return is rank
+// 0's (it owns global sample 0).  One warp; equals dist.select_winner on the host (tests/test_dist_gloo.py).
+__global__ void k_plan_select(const double* __restrict__ gathered, int nranks, int stride, double* __restrict__ out) {
+  const int lane = threadIdx.x;
+  double best = INFINITY, bidx = INFINITY;
+  int br = 0x7fffffff;
+  for (int r = lane; r < nranks; r += 32) {
+    double c = gathered[(size_t)r * stride];
+    if (!(c == c)) c = INFINITY;
+    const double ix = gathered[(size_t)r * stride + 1];
+    if (c < best || (c == best && ix < bidx) || br == 0x7fffffff) { best = c; bidx = ix; br = r; }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    const double ob = __shfl_xor_sync(0xffffffffu, best, o), oi = __shfl_xor_sync(0xffffffffu, bidx, o);
+    const int orr = __shfl_xor_sync(0xffffffffu, br, o);
+    if (orr != 0x7fffffff && (br == 0x7fffffff || ob < best || (ob == best && oi < bidx))) { best = ob; bidx = oi; br = orr; }
+  }
+  const double* src = gathered + (size_t)br * stride;
+  for (int e = lane; e < stride; e += 32) out[e] = (e == 2) ? gathered[2] : src[e];
+}
+
+void hmj_launch_plan_candidates(const hmj_tables_t* tab, int n, int nnode, const double* nominal_dev, const double* noise_dev,
+                                double std0, double std1, unsigned long long seed, unsigned long long iteration, int first_global,
+                                double* values_dev, cudaStream_t stream) {
+  const long long tot = (long long)n * nnode * HMJ_NU;
+  k_plan_candidates<<<(int)((tot + 255) / 256), 256, 0, stream>>>(tab, n, nnode, nominal_dev, noise_dev, std0, std1, seed, iteration,
+                                                                  first_global, values_dev);
+}
+void hmj_launch_plan_winner(const double* returns_dev, int n, const double* values_dev, int nnode, int first_global,
+                            double* argmin_dev, double* rec_dev, cudaStream_t stream) {
+  k_plan_winner<<<1, 1024, 0, stream>>>(returns_dev, n, values_dev, nnode, first_global, argmin_dev, rec_dev);
+}
+void hmj_launch_plan_select(const double* gathered_dev, int nranks, int stride, double* out_dev, cudaStream_t stream) {
+  k_plan_select<<<1, 32, 0, stream>>>(gathered_dev, nranks, stride, out_dev);
 }
 
 // ------------------------------------------------------------------ CPUEnv epilogue

@@ -312,7 +312,13 @@ struct hmj_record_t {
   double* trace;    // [H][N][3]
 };
 
-void hmj_launch_plan_init(hmj_buffers_t buf, const double* state_dev, double time, cudaStream_t stream);
+void hmj_launch_plan_init(hmj_buffers_t buf, const double* state_time_dev, cudaStream_t stream);
+void hmj_launch_plan_candidates(const hmj_tables_t* tab, int n, int nnode, const double* nominal_dev, const double* noise_dev,
+                                double std0, double std1, unsigned long long seed, unsigned long long iteration, int first_global,
+                                double* values_dev, cudaStream_t stream);
+void hmj_launch_plan_winner(const double* returns_dev, int n, const double* values_dev, int nnode, int first_global,
+                            double* argmin_dev, double* rec_dev, cudaStream_t stream);
+void hmj_launch_plan_select(const double* gathered_dev, int nranks, int stride, double* out_dev, cudaStream_t stream);
 void hmj_launch_plan_record(hmj_buffers_t buf, hmj_record_t rec, int t, cudaStream_t stream);
 void hmj_launch_plan_finish(hmj_buffers_t buf, int horizon, double* returns_dev, int32_t* failure_dev, cudaStream_t stream);
 void hmj_launch_argmin(const double* returns_dev, int n, double* out_cost_idx_dev, cudaStream_t stream);

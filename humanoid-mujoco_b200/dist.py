@@ -31,6 +31,42 @@ def shard_range(n_total: int, rank: int, world_size: int):
     return lo, lo + base + (1 if rank < rem else 0)
 
 
+def select_winner(records: np.ndarray) -> np.ndarray:
+    """Host statement of the device reduction `k_plan_select` (csrc/hmj_aux.cu): `records` [W][3 + P*12] holds one
+    winner record per rank {cost, global index, return of the rank's sample 0, spline values}.  The global winner is
+    the lexicographic minimum of (cost, global index); NaN costs never win unless every rank holds NaN; the nominal
+    return is rank 0's (it owns global sample 0)."""
+    records = np.asarray(records, dtype=np.float64)
+    key = np.where(np.isnan(records[:, 0]), np.inf, records[:, 0])
+    owner = int(np.lexsort((records[:, 1], key))[0])
+    out = records[owner].copy()
+    out[2] = records[0, 2]
+    return out
+
+
+def exchange_records(record: np.ndarray, batch=None, rec_local=None, rec_all=None) -> np.ndarray:
+    """The planner's one exchange step.  NCCL: `rec_local` / `rec_all` are torch CUDA tensors ([R] written by
+    hmj_plan_iterate, [W][R]); the all-gather is issued on the batch's own stream and the selection runs on the device
+    right behind it (hmj_plan_select) — one synchronisation, no host copy between collective and selection.  Other
+    backends (gloo in the CPU tests): the host record is all-gathered and `select_winner` picks."""
+    import torch
+    import torch.distributed as dist
+
+    rank, ws = world()
+    if ws == 1:
+        return record
+    if rec_all is not None and dist.get_backend() == "nccl":
+        stream = torch.cuda.ExternalStream(batch.stream, device=rec_all.device)
+        with torch.cuda.stream(stream):
+            dist.all_gather_into_tensor(rec_all, rec_local)
+        nnode = (rec_local.numel() - 3) // 12
+        return batch.plan_select(nnode, rec_all.data_ptr(), ws)
+    mine = torch.from_numpy(np.ascontiguousarray(record, dtype=np.float64))
+    parts = [torch.zeros_like(mine) for _ in range(ws)]
+    dist.all_gather(parts, mine)
+    return select_winner(torch.stack(parts).numpy())
+
+
 def exchange_winner(cost: float, local_index: int, nominal_return: float, win_values: np.ndarray, first_global: int,
                     device=None):
     """All ranks call this with their local best.  Returns (cost, global_index, nominal_return_of_rank0, values) of

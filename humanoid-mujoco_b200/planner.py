@@ -161,6 +161,9 @@ class SamplingPlanner:
         # every rank draws its own candidates: the per-rank noise stream is (seed, rank), so equal seeds on all ranks
         # do not duplicate samples
         self.rng = np.random.default_rng([int(seed), self.rank])
+        self.seed, self.iteration = int(seed), 0    # device noise stream: (seed, iteration, GLOBAL sample index)
+        self._rec_bufs = None
+        self._population, self._population_nnode = None, None
         self.Initialize()
         self.Allocate()
         self.Reset(0)
@@ -256,27 +259,80 @@ class SamplingPlanner:
         values = np.broadcast_to(nominal, (self.num_trajectory_,) + nominal.shape).copy()
         values = self.AddNoiseToPolicy(values, noise)
         self.candidate_times, self.candidate_values = times, values
-        self.total_return, self.failure = self.batch.plan_rollouts(
-            self.state, self.time, times, values, horizon, self.interpolation_, record)
+        ret, fail = self.batch.plan_rollouts(self.state, self.time, times, values, horizon, self.interpolation_, record)
+        self.total_return, self.failure = ret, fail   # host copies (the setters switch off the lazy device read-back)
         self._horizon = horizon
 
     def OptimizePolicyCandidates(self, ncandidates: int, horizon: int, noise: np.ndarray | None = None):
-        self.Rollouts(horizon, noise)
-        # local arg-min on the device, lowest index wins ties
-        cost, idx = self.batch.plan_argmin()
-        self.nominal_return = float(self.total_return[0])
-        win_values = self.candidate_values[idx]
+        """Candidates, rollouts and arg-min on the device (hmj_plan_iterate: one CUDA-graph launch for all rollouts), then
+        the winner exchange.  `noise` [n][P][12] injects the perturbations (parity tests); None draws them on the device
+        from the counter-based stream (seed, iteration, global sample index)."""
+        times, nominal = self.policy.plan.arrays()
+        P = times.shape[0]
+        first_global = self.rank * self.num_trajectory_
+        rec_local = rec_all = None
         if self.world > 1:
             import torch
             import torch.distributed as dist
-            from .dist import exchange_winner
-            dev = torch.device("cuda", self._device) if dist.get_backend() == "nccl" else torch.device("cpu")
-            cost, idx, self.nominal_return, win_values = exchange_winner(
-                cost, idx, self.nominal_return, win_values, self.rank * self.num_trajectory_, dev)
-        self.winner = int(idx)
-        self.winner_return = float(cost)
-        self._winner_values = np.array(win_values, dtype=np.float64)
+            if dist.get_backend() == "nccl":
+                R = 3 + P * NU
+                if self._rec_bufs is None or self._rec_bufs[0].numel() != R:
+                    dev = torch.device("cuda", self._device)
+                    self._rec_bufs = (torch.zeros(R, dtype=torch.float64, device=dev),
+                                      torch.zeros((self.world, R), dtype=torch.float64, device=dev))
+                rec_local, rec_all = self._rec_bufs
+        self.batch.plan_iterate(self.state, self.time, times, nominal, horizon, self.interpolation_, noise=noise,
+                                noise_std=self.noise_exploration[0], noise_std2=self.noise_exploration[1], seed=self.seed,
+                                iteration=self.iteration, first_global=first_global,
+                                record_dev=rec_local.data_ptr() if rec_local is not None else None)
+        self.iteration += 1
+        self.candidate_times = times
+        self._population = None          # fetched on demand (total_return / failure / candidate_values)
+        self._population_nnode = P
+        self._horizon = horizon
+        if rec_all is not None:
+            from .dist import exchange_records
+            rec = exchange_records(None, self.batch, rec_local, rec_all)
+        else:
+            rec = self.batch.plan_select(P)
+            if self.world > 1:
+                from .dist import exchange_records
+                rec = exchange_records(rec)
+        self.winner_return = float(rec[0])
+        self.winner = int(rec[1])
+        self.nominal_return = float(rec[2])
+        self._winner_values = rec[3:].reshape(P, NU).copy()
         return 1
+
+    # population of the last iteration, read back only when somebody asks (the reference keeps trajectory[i].total_return)
+    def _fetch_population(self):
+        if self._population is None:
+            self._population = self.batch.plan_population(self._population_nnode)
+        return self._population
+
+    @property
+    def total_return(self):
+        return self._total_return if self._population_nnode is None else self._fetch_population()[0]
+
+    @total_return.setter
+    def total_return(self, v):
+        self._total_return, self._population_nnode = v, None
+
+    @property
+    def failure(self):
+        return self._failure if self._population_nnode is None else self._fetch_population()[1]
+
+    @failure.setter
+    def failure(self, v):
+        self._failure = v
+
+    @property
+    def candidate_values(self):
+        return self._candidate_values if self._population_nnode is None else self._fetch_population()[2]
+
+    @candidate_values.setter
+    def candidate_values(self, v):
+        self._candidate_values = v
 
     def CopyCandidateToPolicy(self, candidate: int = 0):
         self.previous_policy.CopyFrom(self.policy)

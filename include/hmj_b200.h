@@ -156,6 +156,30 @@ int hmj_plan_argmin(hmj_batch_t* b, double* best_cost, int32_t* best_index);
 int hmj_plan_fetch(hmj_batch_t* b, int sample, int horizon, double* states /* [H][37] */, double* actions /* [H][12] */,
                    double* times /* [H] */, double* residual /* [H][28] */, double* costs /* [H] */, double* trace /* [H][3] */);
 
+/* ---- one predictive-sampling iteration, candidates built on the device (SamplingPlanner::OptimizePolicy's device half:
+ * AddNoiseToPolicy planner.cc:313-339, Rollouts :342-380, the arg-min of :151-187).  nominal_values [P][12] is the
+ * resampled nominal spline (UpdateNominalPolicy stays on the host: P x 12 numbers).  noise [N][P][12] is added as given
+ * (NULL: drawn on the device from the counter-based stream (seed, iteration, global sample); std = noise_std, or
+ * noise_std2 with probability 0.2 when noise_std2 > 0, scaled by half the control range).  The sample with GLOBAL index
+ * first_global + s == 0 keeps the nominal (planner.cc:361).  The whole batch of rollouts replays as ONE CUDA graph.
+ * Enqueue only: the result is this rank's winner record {cost, global index, return of local sample 0, winner spline
+ * values [P][12]} = hmj_plan_record_size(P) doubles at record_dev (NULL: hmj_plan_record_ptr(b)).
+ * Multi-GPU: all-gather the records of all ranks ON hmj_batch_stream(b) (ncclAllGather, or the built-in
+ * hmj_comm_allgather below), then hmj_plan_select picks the global winner on the device (lexicographic (cost, global
+ * index); NaN never wins) and returns its record to the host — one synchronisation per iteration, no host round trip
+ * between the collective and the selection.  gathered_dev == NULL / nranks <= 1: single-GPU, selects the local record. */
+int hmj_plan_iterate(hmj_batch_t* b, const double* state, double time, const double* spline_times,
+                     const double* nominal_values, int nnode, int interpolation, int horizon, const double* noise,
+                     double noise_std, double noise_std2, unsigned long long seed, unsigned long long iteration,
+                     int first_global, double* record_dev);
+int hmj_plan_record_size(int nnode);
+void* hmj_plan_record_ptr(hmj_batch_t* b);
+int hmj_plan_select(hmj_batch_t* b, const double* gathered_dev, int nranks, int nnode, double* record_host);
+/* returns [N] / failure flags [N] / candidate values [N][P][12] of the last hmj_plan_iterate (any may be NULL) */
+int hmj_plan_population(hmj_batch_t* b, int nnode, double* total_return, int32_t* failure, double* values);
+/* API-level launches so far (a CUDA-graph replay counts once; hmj_batch_kernel_launches counts kernel nodes) */
+int hmj_batch_host_launches(const hmj_batch_t* b);
+
 #ifdef __cplusplus
 }
 #endif

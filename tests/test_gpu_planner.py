@@ -201,3 +201,91 @@ def test_rollout_edge_cases(hmj, oracle):
     pl.Rollouts(5)
     ref, ref_fail = oracle_returns(oracle, bad, time, pl.candidate_times, pl.candidate_values, 5, 2)
     assert np.array_equal(pl.failure, ref_fail)
+
+
+def test_device_iteration_equals_host_built_candidates(hmj, oracle):
+    """hmj_plan_iterate (candidates = clamp(nominal + noise) built on the device, rollouts replayed as one CUDA graph,
+    device arg-min + winner record) against the host-built path (`Rollouts` + `plan_argmin`): same bits."""
+    state, time = settled_task_state(oracle)
+    n = 64
+    pl = hmj.SamplingPlanner(num_trajectory=n, device=0, seed=11)
+    pl.SetState(state[:19], state[19:], time)
+    H = pl.steps()
+    rng = np.random.default_rng(21)
+    scale = 0.5 * (pl.ctrlrange[:, 1] - pl.ctrlrange[:, 0])
+    for it in range(3):     # iteration 0 runs un-captured, 1 captures the graph, 2 replays it
+        pl.UpdateNominalPolicy(H)
+        noise = rng.standard_normal((n, 3, 12)) * scale * (0.05 if it < 2 else 5.0)   # last one saturates the clamp
+        pl.Rollouts(H, noise=noise)
+        ret_host, vals_host = pl.total_return.copy(), pl.candidate_values.copy()
+        cost_h, idx_h = pl.batch.plan_argmin()
+        l0 = pl.batch.host_launches
+        pl.OptimizePolicyCandidates(1, H, noise=noise)
+        host_launches = pl.batch.host_launches - l0
+        assert np.array_equal(pl.candidate_values, vals_host)
+        assert np.array_equal(pl.total_return, ret_host)
+        assert pl.winner == idx_h and pl.winner_return == cost_h and pl.nominal_return == ret_host[0]
+        assert np.array_equal(pl._winner_values, vals_host[idx_h])
+        if it > 0:
+            assert host_launches <= 4, host_launches     # candidates, ONE graph launch for all rollouts, winner
+
+
+def test_device_noise_stream(hmj, oracle):
+    """Device-drawn exploration noise (counter-based, Box-Muller): sample 0 is the nominal, values are clamped, the
+    perturbations have the requested scale, differ between iterations and do not depend on how samples are sharded."""
+    state, time = settled_task_state(oracle)
+    n = 512
+    pl = hmj.SamplingPlanner(num_trajectory=n, device=0, seed=5)
+    pl.SetState(state[:19], state[19:], time)
+    pl.policy.Reset(0, np.zeros(12))
+    pl.UpdateNominalPolicy(3)
+    _, nominal = pl.policy.plan.arrays()
+    pl.OptimizePolicyCandidates(1, 3)
+    v0 = pl.candidate_values.copy()
+    assert np.array_equal(v0[0], nominal)
+    assert v0.min() >= pl.ctrlrange[:, 0].min() and v0.max() <= pl.ctrlrange[:, 1].max()
+    scale = 0.5 * (pl.ctrlrange[:, 1] - pl.ctrlrange[:, 0])
+    z = (v0[1:] - nominal) / (scale * pl.noise_exploration[0])
+    assert abs(z.mean()) < 0.02 and abs(z.std() - 1.0) < 0.02, (z.mean(), z.std())
+    pl.policy.Reset(0, np.zeros(12))
+    pl.UpdateNominalPolicy(3)
+    pl.OptimizePolicyCandidates(1, 3)
+    assert not np.array_equal(pl.candidate_values[1:], v0[1:])           # next iteration, new draw
+    # a second planner owning global samples [256, 512) draws exactly the second half of the first iteration
+    p2 = hmj.SamplingPlanner(num_trajectory=256, device=0, seed=5)
+    p2.rank, p2.world = 1, 1          # shard offset only; no process group in this test
+    p2.SetState(state[:19], state[19:], time)
+    p2.policy.Reset(0, np.zeros(12))
+    p2.UpdateNominalPolicy(3)
+    p2.OptimizePolicyCandidates(1, 3)
+    assert np.array_equal(p2.candidate_values, v0[256:])
+
+
+def test_device_select_matches_host_select(hmj):
+    """k_plan_select (the reduction behind the all-gather) against dist.select_winner on fabricated records: ties go to
+    the lowest global index, NaN never wins, the nominal return is rank 0's."""
+    import torch
+
+    from humanoid_mujoco_b200.dist import select_winner
+
+    b = hmj.HumanoidBatch(4, device=0)
+    P, R = 3, 39
+    rng = np.random.default_rng(3)
+    for case in range(6):
+        W = (2, 8, 8, 8, 33, 3)[case]
+        recs = rng.standard_normal((W, R))
+        recs[:, 0] = rng.uniform(1, 2, W)
+        recs[:, 1] = np.arange(W) * 1024 + rng.integers(0, 1024, W)
+        if case == 2:
+            recs[5, 0] = recs[2, 0] = 0.5
+        if case == 3:
+            recs[0, 0] = np.nan
+            recs[4, 0] = np.nan
+        if case == 5:
+            recs[:, 0] = np.nan
+        g = torch.tensor(recs, dtype=torch.float64, device="cuda:0")
+        torch.cuda.synchronize()
+        got = b.plan_select(P, g.data_ptr(), W)
+        want = select_winner(recs)
+        assert np.array_equal(got, want, equal_nan=True), case
+    b.close()
