@@ -45,8 +45,9 @@ CPU_SAMPLE_ENVS = 1024
 
 
 def workload_name(envs, n_gpus):
-    return (f"C3: {envs} lockstep humanoid envs/GPU x {n_gpus} GPU, DR rf=1, contact-rich "
-            f"(standup pose + {SETTLE_STEPS} settle steps), U(-1,1) controls, dt=0.002")
+    return (f"C3: {envs} lockstep humanoid envs/GPU x {n_gpus} GPU, DR rf=1 (cpu_env.py:189-280 ranges), starts through "
+            f"reset's no-contact rejection, {SETTLE_STEPS} zero-control settle steps, then iid U(-1,1) controls at their "
+            f"steady state (150 untimed lead-in steps), dt=0.002; second regime C3-settled = 0.02 x U(-1,1) in `workloads`")
 
 
 def load_peaks():
@@ -143,73 +144,136 @@ class ClockSampler:
 
 
 # ---------------------------------------------------------------------------------------------- workload
-def make_workload(base_params, qpos0, n, seed):
-    """Per-env DR parameters and start poses of C3 (pure numpy; shared by both arms)."""
+# Two control regimes on the SAME environments (same DR draw, same accepted start poses, same settle):
+#   C3          iid U(-1,1) position targets every 2 ms (BASELINE.json configs[2] as specified): the robots thrash, the
+#               steady state has ~0.5 contacts per env (limits dominate the constraint rows);
+#   C3-settled  0.02 x U(-1,1): the robots stay on the floor, ~3.5 contacts / ~36 constraint rows / ~4 Newton iterations
+#               per env — the regime a policy that actually stands up lives in (zero controls: 4.4 / 48 / 2.9).
+# `pre` untimed steps take each regime to its steady state, so that a 20-step and a 200-step timed region sample the
+# same contact statistics (the driver runs --steps 20).
+WORKLOADS = (("C3", 1.0, 150), ("C3-settled", 0.02, 50))
+
+
+def make_workload(base_params, qpos0, n, seed, probe):
+    """Per-env DR parameters and start poses of C3 (numpy; shared by both arms), through CPUEnv.reset's rejection loop
+    (cpu_env.py:411-414): `probe(params, qpos) -> bool[n]` runs the first zero-control step on the arm's own engine and
+    reports the envs that touch anything; those are re-drawn (model and pose, as the reference's recursive reset does).
+    Contacts are bit-exact between the engines, so both arms accept the same draws."""
     from humanoid_mujoco_b200.env import randomize_params, standup_start_state
     rng = np.random.default_rng(seed)
     params = randomize_params(np.repeat(base_params[:1], n), rng, 1.0)
     qpos = standup_start_state(qpos0, rng, 1.0, n)
-    return params, qpos
+    attempts = 1
+    for _ in range(100):
+        bad = np.nonzero(probe(params, qpos))[0]
+        if len(bad) == 0:
+            break
+        attempts += 1
+        params[bad] = randomize_params(np.repeat(base_params[:1], len(bad)), rng, 1.0)
+        qpos[bad] = standup_start_state(qpos0, rng, 1.0, len(bad))
+    else:
+        raise RuntimeError("make_workload: start poses still in contact after 100 attempts")
+    return params, qpos, attempts
+
+
+def control_ring(rank, entries, n):
+    """[entries][n][12] iid U(-1,1): a prefix of the same numpy stream whatever `entries` is."""
+    return np.random.default_rng(2 + rank).uniform(-1, 1, (entries, n, 12))
+
+
+def contact_stats(ncon, nefc, niter, status=None):
+    out = {"mean_ncon": float(np.mean(ncon)), "max_ncon": int(np.max(ncon)), "frac_no_contact": float(np.mean(np.asarray(ncon) == 0)),
+           "mean_nefc": float(np.mean(nefc)), "max_nefc": int(np.max(nefc)), "mean_newton_iter": float(np.mean(niter)),
+           "ncon_hist": np.bincount(np.minimum(ncon, 16), minlength=17).tolist(),
+           "nefc_hist_by_10": np.bincount(np.minimum(np.asarray(nefc) // 10, 12), minlength=13).tolist(),
+           "niter_hist": np.bincount(np.minimum(niter, 12), minlength=13).tolist()}
+    if status is not None:
+        out["envs_with_bad_status"] = int((np.asarray(status) != 0).sum())
+    return out
 
 
 # ---------------------------------------------------------------------------------------------- reference arm / CPU baseline
-def cpu_steps_per_s(params, qpos, qvel, ws, ctrl_ring, nsteps, warm, nthreads):
-    """Oracle (CPU port of the reference path) on `nthreads` host threads; returns (env-steps/s, stats)."""
+def _oracle_batch(n):
     sys.path.insert(0, os.path.join(REPO, "oracle"))
     from oracle_py import OracleBatch  # bench.py's cpu_baseline / --impl reference legs may execute oracle/
+    return OracleBatch(n)
+
+
+def cpu_steps_per_s(params, qpos, qvel, ws, ctrl_ring, nsteps, warm, nthreads):
+    """Oracle (CPU port of the reference path) on `nthreads` host threads; returns (env-steps/s, stats, batch)."""
     n = qpos.shape[0]
-    ob = OracleBatch(n)
+    ob = _oracle_batch(n)
     ob.params[:] = params
     ob.set_state(qpos, qvel, ws)
+    d = ob.data
     if warm:
         ob.step(ctrl_ring, warm, nthreads)
+    fl0 = (d["flops_smooth"] + d["flops_collision"] + d["flops_constraint"] + d["flops_solver"]).copy()
+    start = contact_stats(d["ncon"], d["nefc"], d["solver_niter"])
     secs = ob.step(ctrl_ring, nsteps, nthreads)
-    d = ob.data
-    fl = d["flops_smooth"] + d["flops_collision"] + d["flops_constraint"] + d["flops_solver"]
-    stats = {"mean_ncon": float(d["ncon"].mean()), "mean_nefc": float(d["nefc"].mean()),
-             "mean_niter": float(d["solver_niter"].mean()), "flops_per_step": float(fl.mean() / max(1, warm + nsteps)),
-             "bad_status": int((d["status"] != 0).sum())}
+    fl = d["flops_smooth"] + d["flops_collision"] + d["flops_constraint"] + d["flops_solver"] - fl0
+    end = contact_stats(d["ncon"], d["nefc"], d["solver_niter"], d["status"])
+    stats = {"mean_ncon": end["mean_ncon"], "mean_nefc": end["mean_nefc"], "mean_niter": end["mean_newton_iter"],
+             "flops_per_step": float(fl.mean() / max(1, nsteps)), "bad_status": end["envs_with_bad_status"],
+             "seconds": secs, "contacts_start": {k: start[k] for k in ("mean_ncon", "mean_nefc", "mean_newton_iter")}}
     return n * nsteps / secs, stats, ob
 
 
-def cpu_settled_state(n, seed, nthreads):
-    sys.path.insert(0, os.path.join(REPO, "oracle"))
-    from oracle_py import OracleBatch
-    ob = OracleBatch(n)
-    params, qpos = make_workload(ob.params, ob.model["qpos0"][0], n, seed)
-    ob.params[:] = params
-    ob.set_state(qpos, np.zeros((n, 18)))
-    ob.data["ctrl"][:] = 0.0
-    ob.step(None, SETTLE_STEPS, nthreads)
-    return params, ob.data["qpos"].copy(), ob.data["qvel"].copy(), ob.data["qacc_warmstart"].copy()
+REF_SUBSTEPS = 16   # one reference-arm "step" = 16 mj_steps of the 1024-env sample (16384 env-steps; the GPU step is 4096)
 
 
 def run_reference(args):
+    """The reference path's CPU implementation (oracle port: MuJoCo itself is not available here) on all host threads, on
+    the first 1024 of the SAME 4096 envs the GPU arm builds with seed 1 (same DR draws, same accepted starts, same
+    settle, same controls stream, same steady-state lead-in), both control regimes."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
     nthreads = os.cpu_count() or 1
-    n = CPU_SAMPLE_ENVS
-    params, qpos, qvel, ws = cpu_settled_state(n, 1, nthreads)
-    ring = np.random.default_rng(2).uniform(-1, 1, (64, n, 12))
+    n_all, m = args.envs, min(CPU_SAMPLE_ENVS, args.envs)
+    ob_all = _oracle_batch(n_all)
+
+    def probe(params, qpos):
+        ob_all.params[:] = params
+        ob_all.set_state(qpos, np.zeros((n_all, 18)), np.zeros((n_all, 18)), np.zeros(n_all))
+        ob_all.data["ctrl"][:] = 0.0
+        ob_all.step(None, 1, nthreads)
+        return ob_all.data["ncon"] > 0
+
     t0 = time.perf_counter()
-    value, stats, _ = cpu_steps_per_s(params, qpos, qvel, ws, ring, args.steps, args.warmup, nthreads)
+    params, qpos, attempts = make_workload(ob_all.params, ob_all.model["qpos0"][0], n_all, 1, probe)
+    ob = _oracle_batch(m)
+    ob.params[:] = params[:m]
+    ob.set_state(qpos[:m], np.zeros((m, 18)), np.zeros((m, 18)), np.zeros(m))
+    ob.data["ctrl"][:] = 0.0
+    ob.step(None, SETTLE_STEPS, nthreads)
+    settled = (ob.data["qpos"].copy(), ob.data["qvel"].copy(), ob.data["qacc_warmstart"].copy())
+    ring = control_ring(0, 64, n_all)[:, :m].copy()
+    res = {}
+    for name, scale, pre in WORKLOADS:
+        value, stats, _ = cpu_steps_per_s(params[:m], *settled, ring * scale, args.steps * REF_SUBSTEPS,
+                                          pre + args.warmup * REF_SUBSTEPS, nthreads)
+        res[name] = (value, stats)
     wall = time.perf_counter() - t0
-    sample = f"{n} of the {args.envs} envs of C3 (same DR/start/settle/controls distribution), {args.steps} steps each"
+    value, stats = res["C3"]
+    sample = (f"first {m} of the {n_all} envs of C3 (seed 1: same DR draws / accepted starts / settle / control stream as the "
+              f"GPU arm), {args.steps} x {REF_SUBSTEPS} mj_steps each after the steady-state lead-in")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * n / value, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": 1e3 * m * REF_SUBSTEPS / value, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload_name(args.envs, args.gpus), "step": f"one mj_step over the {n}-env sample"},
+        "config": {"workload": workload_name(args.envs, args.gpus),
+                   "step": f"{REF_SUBSTEPS} mj_steps over the {m}-env sample ({m * REF_SUBSTEPS} env-steps)"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": nthreads, "kind": "port", "sample": sample, **stats},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "workloads": {k: {"value": v, "unit": UNIT, **st} for k, (v, st) in res.items()},
+        "reset_attempts": attempts,
         "note": ("MuJoCo 3.1.4 (the reference's physics) is not in /root/reference nor installed on this box: the timed CPU "
-                 "implementation is the repo's fp64 C restatement (oracle/), all host threads"),
+                 "implementation is the repo's fp64 C restatement (oracle/, -O3 -march=native -ffp-contract=off), all host threads"),
         "wall_s": wall,
     }
     print(json.dumps(line), flush=True)
     return 0
-
 
 
 # ---------------------------------------------------------------------------------------------- planner (metric M2)
@@ -314,19 +378,26 @@ def run_gpu(args):
     # ---- public API object: the CPUEnv contract over n envs, rf = 1
     env = hmj.BatchedHumanoidEnv(n, randomization_factor=1.0, device=local, seed=1 + rank)
     b = env.batch
-    params, qpos = make_workload(b.default_params(), b.model["qpos0"][0], n, 1 + rank)
-    env.params[:] = params
-    b.set_params(params)
-    b.set_state(qpos, np.zeros((n, 18)), np.zeros(n), np.zeros((n, 18)))
-    b.step(np.zeros((n, 12)), SETTLE_STEPS)  # robots fall and lie on the bumpy floor: contact-rich start
-    settled = b.get_state()
+    zeros18 = np.zeros((n, 18))
+
+    def probe(params, qpos):   # first zero-control step on the engine: who touches anything?
+        b.set_params(params)
+        b.set_state(qpos, zeros18, np.zeros(n), zeros18)
+        b.step(np.zeros((n, 12)), 1)
+        return b.get("ncon") > 0
+
+    params, qpos, attempts = make_workload(b.default_params(), b.model["qpos0"][0], n, 1 + rank, probe)
+    b.set("status", np.zeros(n, dtype=np.int32))
+    env.reset_to(params, qpos)          # delays / constant noise vectors / trackers of the public API
+    b.step(np.zeros((n, 12)), SETTLE_STEPS)  # robots fall and lie on the bumpy floor
+    q_s, v_s, _t, ws_s = b.get_state()
+    settled = (q_s, v_s, np.zeros(n), ws_s)
     stream = torch.cuda.ExternalStream(b.stream, device=dev)
 
     # ---- device-resident inputs: control ring larger than L2 (R x n x 12 fp64), epilogue buffers
     ring_n = max(8, int(np.ceil(160e6 / (n * 12 * 8))))
-    gen = torch.Generator(device=dev)
-    gen.manual_seed(2 + rank)
-    ring = torch.rand((ring_n, n, 12), dtype=torch.float64, device=dev, generator=gen) * 2 - 1
+    ring_host = control_ring(rank, ring_n, n)
+    ring1 = torch.from_numpy(ring_host).to(dev)
     prev = torch.zeros((n, 12), dtype=torch.float64, device=dev)
     obs = torch.zeros((n, 30), dtype=torch.float64, device=dev)
     rew = torch.zeros(n, dtype=torch.float64, device=dev)
@@ -334,49 +405,105 @@ def run_gpu(args):
     torch.cuda.synchronize()
     lib, h = b.lib, b._h
     from humanoid_mujoco_b200._lib import check
-
-    def device_step(s):
-        cur = ring[s % ring_n]
-        b.step_dev(cur.data_ptr(), 1)
-        check(lib.hmj_env_obs_reward_dev(h, prev.data_ptr(), cur.data_ptr(), None, 10.0, obs.data_ptr(), rew.data_ptr(),
-                                         flags[0].data_ptr(), flags[1].data_ptr(), flags[2].data_ptr()))
-
-    # ---- kernel-resident throughput (`value`)
+    host_actions = hmj.pinned_empty((min(ring_n, 64), n, 12))   # the policy's output buffer: page-locked host memory
+    hbm_peak, peak_kind = load_peaks()
+    import ctypes as C
+    tf = C.c_double(0)
+    lib.hmj_fp64_peak(local, C.byref(tf))
+    nthreads = os.cpu_count() or 1
     clocks = ClockSampler(range(world) if rank == 0 else [])   # ranks are local GPUs 0..world-1 of one node
     clocks.start()
     clocks.wait_first()
-    for s in range(W):
-        device_step(s)
-    b.sync()
-    barrier()
-    torch.cuda.synchronize()
-    clocks.mark()
-    l0 = b.kernel_launches
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(stream)
-    for s in range(K):
-        device_step(W + s)
-    e1.record(stream)
-    b.sync()
-    torch.cuda.synchronize()
-    barrier()
-    ms_total = max_over_ranks(e0.elapsed_time(e1))
-    launches = b.kernel_launches - l0
-    value = world * n * K / (ms_total * 1e-3)
-    status_bad = int((b.get("status") != 0).sum())
-    ncon = b.get("ncon")
-    nefc = b.get("nefc")
-    niter = b.get("niter")
 
-    # ---- per-kernel device time (CUDA events around every launch on the engine stream), same steps
-    b.profile(True)
-    for s in range(K):
-        device_step(W + K + s)
-    prof = b.profile_read()
-    b.profile(False)
-    kern = {k: prof[k + "_ms"] / prof["steps"] for k in ("smooth", "collide", "solve")}
+    def measure(name, scale, pre, sample_clocks):
+        """One control regime: lead-in to the steady state, W warm-up steps, K timed steps (device resident), K profiled
+        steps, then W + K steps end to end through BatchedHumanoidEnv.step."""
+        ring = ring1 if scale == 1.0 else ring1 * scale
+
+        def device_step(s):
+            cur = ring[s % ring_n]
+            b.step_dev(cur.data_ptr(), 1)
+            check(lib.hmj_env_obs_reward_dev(h, prev.data_ptr(), cur.data_ptr(), None, 10.0, obs.data_ptr(), rew.data_ptr(),
+                                             flags[0].data_ptr(), flags[1].data_ptr(), flags[2].data_ptr()))
+
+        def stats():
+            return contact_stats(b.get("ncon"), b.get("nefc"), b.get("niter"), b.get("status"))
+
+        b.set_state(*settled)
+        for s in range(pre + W):
+            device_step(s)
+        b.sync()
+        st_start = stats()
+        start_state = b.get_state()
+        barrier()
+        torch.cuda.synchronize()
+        if sample_clocks:
+            clocks.mark()
+        l0 = b.kernel_launches
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for s in range(K):
+            device_step(pre + W + s)
+        e1.record(stream)
+        b.sync()
+        torch.cuda.synchronize()
+        barrier()
+        ms_total = max_over_ranks(e0.elapsed_time(e1))
+        launches = b.kernel_launches - l0
+        st_end = stats()
+        # per-kernel device time (CUDA events around every launch on the engine stream), the next K steps
+        b.profile(True)
+        for s in range(K):
+            device_step(pre + W + K + s)
+        prof = b.profile_read()
+        b.profile(False)
+        kern = {k: prof[k + "_ms"] / prof["steps"] for k in ("smooth", "collide", "solve")}
+        # end to end through the public API: host actions in, obs/reward/flags out, every step.  BatchedHumanoidEnv.step
+        # DMAs the actions from the caller's pinned array, runs prologue, physics step and epilogue on the device and
+        # reads the results from the pinned IO block (one D2H copy).
+        host_actions[...] = np.random.default_rng(5 + rank).uniform(-scale, scale, host_actions.shape)
+        for s in range(W):
+            env.step(host_actions[s % host_actions.shape[0]])
+        barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for s in range(K):
+            env.step(host_actions[(W + s) % host_actions.shape[0]])
+        b.sync()
+        e2e_s = max_over_ranks(time.perf_counter() - t0)
+        out = {"value": world * n * K / (ms_total * 1e-3), "unit": UNIT, "ms_per_step": ms_total / K,
+               "controls": f"{scale} x U(-1,1)", "lead_in_steps": pre,
+               "e2e": {"value": world * n * K / e2e_s, "unit": UNIT, "ms_per_step": 1e3 * e2e_s / K},
+               "kernel_ms": kern, "contacts_start": st_start, "contacts_end": st_end}
+        out["_start_state"] = start_state
+        return out, launches
+
+    results = {}
+    launches = 0
+    for name, scale, pre in WORKLOADS:
+        results[name], ln = measure(name, scale, pre, sample_clocks=(name == "C3"))
+        if name == "C3":
+            launches = ln
+            clk = clocks.stop()
+    # ---- CPU baseline legs (rank 0, N = 1 only): the oracle on the first 1024 envs, from the GPU arm's own states
+    for name, scale, pre in WORKLOADS:
+        out = results[name]
+        start_state = out.pop("_start_state")
+        if rank == 0 and world == 1 and not args.no_cpu:
+            m = min(CPU_SAMPLE_ENVS, n)
+            q, v, _tt, ws = start_state
+            cpu_value, cst, _ = cpu_steps_per_s(params[:m], q[:m], v[:m], ws[:m], ring_host[:64, :m] * scale, args.cpu_steps, 0,
+                                                nthreads)
+            out["cpu_baseline"] = {"value": cpu_value, "unit": UNIT, "cores": nthreads, "kind": "port",
+                                   "sample": (f"first {m} of the {n} envs from the GPU arm's own state at the start of the "
+                                              f"timed region, same DR params and control stream, {args.cpu_steps} steps each"),
+                                   **cst}
+            fl = cst["flops_per_step"]
+            out["fp64"] = {"flops_per_env_step_oracle_counters": fl, "achieved_tflops": out["value"] * fl / 1e12,
+                           "peak_tflops": tf.value, "frac": (out["value"] * fl / 1e12) / tf.value if tf.value else None}
+    main = results["C3"]
+    kern = main["kernel_ms"]
     dom = max(kern, key=kern.get)
-    hbm_peak, peak_kind = load_peaks()
     achieved = BYTES_PER_ENV_STEP * n / (kern[dom] * 1e-3) / 1e9
     traffic = None
     try:   # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture (same 4096-env launch)
@@ -387,65 +514,37 @@ def run_gpu(args):
     roofline = {"bound": "hbm", "kernel": "k_" + dom, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                 "frac": achieved / hbm_peak, "traffic": traffic, "peak_kind": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)",
                 "kernel_ms": kern, "algorithmic_bytes_per_env_step": BYTES_PER_ENV_STEP,
-                "note": "path is fp64-issue/latency bound, not HBM bound (SURVEY 8d): see the fp64 object"}
-
-    # ---- end to end through the public API: host actions in, obs/reward/flags out, every step.
-    # BatchedHumanoidEnv.step writes the actions into the engine's pinned IO block (one H2D copy), runs the prologue,
-    # the physics step and the epilogue on the device, and reads the results from the same pinned block (one D2H copy).
-    b.set_state(*settled)
-    host_actions = hmj.pinned_empty((min(ring_n, 64), n, 12))   # the policy's output buffer: page-locked host memory
-    host_actions[...] = np.random.default_rng(5 + rank).uniform(-1, 1, host_actions.shape)
-    acts = host_actions
-    for s in range(W):
-        env.step(acts[s % acts.shape[0]])
-    barrier()
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    for s in range(K):
-        o, r, term, trunc, _info = env.step(acts[(W + s) % acts.shape[0]])
-    b.sync()
-    t1 = time.perf_counter()
-    e2e_s = max_over_ranks(t1 - t0)
-    e2e_value = world * n * K / e2e_s
+                "note": "path is fp64-issue/latency bound, not HBM bound (SURVEY 8d): see roofline_fp64"}
     h2d = n * 12 * 8
     d2h = n * ((30 + 1 + 1 + 4) * 8 + 3 * 4)
-    clk = clocks.stop()
 
     line = None
     if rank == 0:
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
-            "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "metric": METRIC, "value": main["value"], "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": main["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
             "config": {"workload": workload_name(n, world), "envs_per_gpu": n, "timestep": 0.002,
+                       "reset_attempts": attempts,
                        "l2": (f"per-step controls stream from a {ring_n}x{n}x12 fp64 device ring "
                               f"({ring_n * n * 96 / 1e6:.0f} MB > 126 MB L2); the state is each step's own previous output"),
                        "step": "one mj_step of all envs + obs/reward epilogue"},
             "roofline": roofline,
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": 1e3 * e2e_s / K, "api": "BatchedHumanoidEnv.step (hmj_env_step_fused_from C-ABI: actions DMA'd from the caller's pinned array, results into the pinned IO block, device-resident env bookkeeping)"},
+            "roofline_fp64": {"bound": "fp64", "peak": tf.value, "unit": "TFLOP/s",
+                              "peak_kind": "builder-measured hmj_fp64_peak (DFMA issue peak, 8 chains/thread)",
+                              **({k: main["fp64"][k] for k in ("achieved_tflops", "frac", "flops_per_env_step_oracle_counters")}
+                                 if "fp64" in main else {})},
+            "e2e": {"value": main["e2e"]["value"], "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": main["e2e"]["ms_per_step"],
+                    "api": "BatchedHumanoidEnv.step (hmj_env_step_fused_from C-ABI: actions DMA'd from the caller's pinned array, results into the pinned IO block, device-resident env bookkeeping)"},
             "gpu_launches": int(launches), "clocks": clk,
-            "contacts": {"mean_ncon": float(ncon.mean()), "max_ncon": int(ncon.max()), "mean_nefc": float(nefc.mean()),
-                         "max_nefc": int(nefc.max()), "mean_newton_iter": float(niter.mean()), "envs_with_bad_status": status_bad},
+            "contacts": {"start": {k: v for k, v in main["contacts_start"].items() if not k.endswith("hist") and "hist" not in k},
+                         "end": {k: v for k, v in main["contacts_end"].items() if "hist" not in k}},
+            "workloads": results,
         }
-    # ---- FP64 peak + CPU baseline (rank 0, N = 1 only)
-    if rank == 0:
-        import ctypes as C
-        tf = C.c_double(0)
-        lib.hmj_fp64_peak(local, C.byref(tf))
-        line["fp64"] = {"peak_tflops_measured": tf.value}
-    if rank == 0 and world == 1 and not args.no_cpu:
-        nthreads = os.cpu_count() or 1
-        m = min(CPU_SAMPLE_ENVS, n)
-        q, v, _t, ws = settled
-        ring_cpu = np.random.default_rng(2).uniform(-1, 1, (64, m, 12))
-        cpu_value, stats, _ = cpu_steps_per_s(params[:m], q[:m], v[:m], ws[:m], ring_cpu, args.cpu_steps, 10, nthreads)
-        line["cpu_baseline"] = {"value": cpu_value, "unit": UNIT, "cores": nthreads, "kind": "port",
-                                "sample": f"first {m} of the {n} envs (same settled states and DR params), {args.cpu_steps} steps each",
-                                **stats}
-        fl = stats["flops_per_step"]
-        line["fp64"].update({"flops_per_env_step_oracle_counters": fl, "achieved_tflops": value * fl / 1e12,
-                             "frac": (value * fl / 1e12) / tf.value if tf.value else None})
+        if "cpu_baseline" in main:
+            line["cpu_baseline"] = main["cpu_baseline"]
+            line["fp64"] = main["fp64"]
     env.close()
     if not args.no_plan:
         plan = plan_bench(local, rank, world, args.plan_iters, cpu=(world == 1 and not args.no_cpu))
@@ -467,7 +566,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--envs", type=int, default=ENVS_PER_GPU, help="environments per GPU")
-    ap.add_argument("--cpu-steps", type=int, default=100, help="steps per env of the bounded CPU-baseline sample")
+    ap.add_argument("--cpu-steps", type=int, default=300, help="steps per env of the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-plan", action="store_true", help="skip the planner (M2) measurement")
     ap.add_argument("--plan-iters", type=int, default=20, help="timed planner iterations of the C4 slice (C2 runs 5x as many)")

@@ -349,6 +349,28 @@ class BatchedHumanoidEnv:
             raise RuntimeError(f"reset: {len(pending)} environments still in contact after 100 attempts")
         return (obs_out if env_ids is None else obs_out[idx]), {}
 
+    def reset_to(self, params: np.ndarray, qpos: np.ndarray, qvel=None):
+        """Start every episode from GIVEN model parameters and poses (a workload built elsewhere, e.g. bench.py): the
+        per-episode draws that do not touch the physics (delays, constant noise vectors) and the trackers are
+        initialised as in `reset`; no DR of the model, no first-step probe."""
+        n, rf = self.num_envs, self.randomization_factor
+        ids = np.arange(n)
+        self.params[:] = params
+        self.batch.set_params(self.params)
+        self._randomize_delays(ids)
+        self.noise_action[:] = rf * np.deg2rad(JOINT_ACTION_NOISE_STDDEV) * self.rng.standard_normal((n, NU))
+        same12 = self.rng.standard_normal((n, NU))
+        self.noise_obs[:, 0:12] = rf * np.deg2rad(JOINT_ANGLE_NOISE_STDDEV) * same12
+        self.noise_obs[:, 12:24] = rf * np.deg2rad(JOINT_VELOCITY_NOISE_STDDEV) * same12
+        self.noise_obs[:, 24:27] = rf * np.deg2rad(GYRO_NOISE_STDDEV) * self.rng.standard_normal((n, 3))
+        self.noise_obs[:, 27:31] = rf * np.deg2rad(IMU_NOISE_STDDEV) * self.rng.standard_normal((n, 4))
+        self.batch.set_state(qpos, np.zeros((n, NV)) if qvel is None else qvel, np.zeros(n), np.zeros((n, NV)))
+        self.ctrl[:] = 0.0
+        self.previous_action[:] = 0.0; self.latest_action[:] = 0.0
+        self.force_sched[:] = 0.0; self.force_body[:] = 0; self.xfrc[:] = 0.0
+        self.previous_reward[:] = 0.0
+        self._push_state()
+
     # ------------------------------------------------------------------ step (cpu_env.py:676-693)
     def step(self, action=None):
         """One control step of every environment.  Returns views of the pinned result block (valid until the next
