@@ -1239,3 +1239,106 @@ extern "C" int hmj_plan_fetch(hmj_batch_t* b, int sample, int horizon, double* s
     memcpy(actions + (size_t)(horizon - 1) * HMJ_NU, actions + (size_t)(horizon - 2) * HMJ_NU, HMJ_NU * 8);
   return HMJ_OK;
 }
+
+// ------------------------------------------------------------------ built-in winner exchange over NCCL
+// A C++ SamplingPlanner shards its samples over GPUs without Python: one communicator per process (NCCL is loaded at
+// run time with dlopen — the library itself links only cudart — so single-GPU users never need it), and the planner's
+// ONE exchange per iteration is an all-gather of the winner records on the batch stream followed by the device selection.
+#include <dlfcn.h>
+struct hmj_nccl_id { char internal[128]; };
+typedef int (*nccl_get_id_fn)(hmj_nccl_id*);
+typedef int (*nccl_init_rank_fn)(void**, int, hmj_nccl_id, int);
+typedef int (*nccl_destroy_fn)(void*);
+typedef int (*nccl_allgather_fn)(const void*, void*, size_t, int, void*, cudaStream_t);
+typedef const char* (*nccl_errstr_fn)(int);
+static struct {
+  void* handle;
+  nccl_get_id_fn get_id;
+  nccl_init_rank_fn init_rank;
+  nccl_destroy_fn destroy;
+  nccl_allgather_fn allgather;
+  nccl_errstr_fn errstr;
+} g_nccl;
+
+static int load_nccl() {
+  if (g_nccl.handle) return HMJ_OK;
+  const char* names[] = {getenv("HMJ_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+  void* h = nullptr;
+  for (const char* nm : names)
+    if (nm && (h = dlopen(nm, RTLD_NOW | RTLD_GLOBAL))) break;
+  if (!h) return fail(HMJ_ERR_CUDA, "NCCL not found (dlopen libnccl.so.2): %s", dlerror());
+  g_nccl.get_id = (nccl_get_id_fn)dlsym(h, "ncclGetUniqueId");
+  g_nccl.init_rank = (nccl_init_rank_fn)dlsym(h, "ncclCommInitRank");
+  g_nccl.destroy = (nccl_destroy_fn)dlsym(h, "ncclCommDestroy");
+  g_nccl.allgather = (nccl_allgather_fn)dlsym(h, "ncclAllGather");
+  g_nccl.errstr = (nccl_errstr_fn)dlsym(h, "ncclGetErrorString");
+  if (!g_nccl.get_id || !g_nccl.init_rank || !g_nccl.destroy || !g_nccl.allgather) {
+    dlclose(h);
+    return fail(HMJ_ERR_CUDA, "NCCL library lacks the expected symbols%s");
+  }
+  g_nccl.handle = h;
+  return HMJ_OK;
+}
+
+struct hmj_comm_ {
+  void* comm = nullptr;
+  int rank = 0, nranks = 1, device = 0;
+  double* gathered = nullptr;   // [nranks][3 + 64*12]
+};
+
+#define NCK(call)                                                                                         \
+  do {                                                                                                    \
+    int r_ = (call);                                                                                      \
+    if (r_ != 0) return fail(HMJ_ERR_CUDA, "NCCL error: %s", g_nccl.errstr ? g_nccl.errstr(r_) : "?");   \
+  } while (0)
+
+extern "C" int hmj_comm_unique_id(void* id128) {
+  if (!id128) return fail(HMJ_ERR_ARG, "null id%s");
+  int rc = load_nccl();
+  if (rc) return rc;
+  NCK(g_nccl.get_id((hmj_nccl_id*)id128));
+  return HMJ_OK;
+}
+
+extern "C" int hmj_comm_create(const void* id128, int rank, int nranks, int device, hmj_comm_t** out) {
+  if (!id128 || !out || nranks < 1 || rank < 0 || rank >= nranks) return fail(HMJ_ERR_ARG, "bad argument to comm_create%s");
+  int rc = load_nccl();
+  if (rc) return rc;
+  CK(cudaSetDevice(device));
+  hmj_comm_* c = new hmj_comm_();
+  c->rank = rank; c->nranks = nranks; c->device = device;
+  hmj_nccl_id id;
+  memcpy(&id, id128, sizeof(id));
+  int r = g_nccl.init_rank(&c->comm, nranks, id, rank);
+  if (r != 0) { delete c; return fail(HMJ_ERR_CUDA, "ncclCommInitRank: %s", g_nccl.errstr ? g_nccl.errstr(r) : "?"); }
+  if (cudaMalloc((void**)&c->gathered, (size_t)nranks * (3 + 64 * HMJ_NU) * 8) != cudaSuccess) {
+    g_nccl.destroy(c->comm);
+    delete c;
+    return fail(HMJ_ERR_CUDA, "cudaMalloc failed%s");
+  }
+  *out = c;
+  return HMJ_OK;
+}
+
+extern "C" void hmj_comm_destroy(hmj_comm_t* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  if (c->gathered) cudaFree(c->gathered);
+  if (c->comm && g_nccl.destroy) g_nccl.destroy(c->comm);
+  delete c;
+}
+
+extern "C" int hmj_comm_rank(const hmj_comm_t* c) { return c ? c->rank : 0; }
+extern "C" int hmj_comm_size(const hmj_comm_t* c) { return c ? c->nranks : 1; }
+
+// all-gather of this rank's winner record (written by hmj_plan_iterate) on the batch stream + device selection:
+// the whole exchange of one planning iteration.  comm == NULL: single process.
+extern "C" int hmj_plan_exchange(hmj_batch_t* b, hmj_comm_t* c, int nnode, double* record_host) {
+  if (!b || !record_host || nnode < 1 || nnode > 64) return fail(HMJ_ERR_ARG, "bad argument to plan_exchange%s");
+  if (!c || c->nranks == 1) return hmj_plan_select(b, nullptr, 1, nnode, record_host);
+  if (c->device != b->device) return fail(HMJ_ERR_ARG, "communicator and batch live on different devices%s");
+  CK(cudaSetDevice(b->device));
+  const int stride = hmj_plan_record_size(nnode);
+  NCK(g_nccl.allgather(b->record_dev, c->gathered, (size_t)stride, /*ncclFloat64*/ 8, c->comm, b->stream));
+  return hmj_plan_select(b, c->gathered, c->nranks, nnode, record_host);
+}

@@ -175,6 +175,18 @@ int hmj_plan_iterate(hmj_batch_t* b, const double* state, double time, const dou
 int hmj_plan_record_size(int nnode);
 void* hmj_plan_record_ptr(hmj_batch_t* b);
 int hmj_plan_select(hmj_batch_t* b, const double* gathered_dev, int nranks, int nnode, double* record_host);
+/* ---- built-in winner exchange for hosts without a communicator of their own (a C++ SamplingPlanner): NCCL is
+ * dlopen'ed at run time (libnccl.so.2; HMJ_NCCL_LIB overrides).  Rank 0 calls hmj_comm_unique_id (128 bytes) and hands
+ * the id to the other processes by any means; every process calls hmj_comm_create with its rank and device.
+ * hmj_plan_exchange = ncclAllGather of the winner records on hmj_batch_stream + hmj_plan_select: the planner's one
+ * collective per iteration (the parallel form of planner.cc:151-187 + CopyCandidateToPolicy :525-534). */
+typedef struct hmj_comm_ hmj_comm_t;
+int hmj_comm_unique_id(void* id128);
+int hmj_comm_create(const void* id128, int rank, int nranks, int device, hmj_comm_t** out);
+void hmj_comm_destroy(hmj_comm_t* c);
+int hmj_comm_rank(const hmj_comm_t* c);
+int hmj_comm_size(const hmj_comm_t* c);
+int hmj_plan_exchange(hmj_batch_t* b, hmj_comm_t* c, int nnode, double* record_host);
 /* returns [N] / failure flags [N] / candidate values [N][P][12] of the last hmj_plan_iterate (any may be NULL) */
 int hmj_plan_population(hmj_batch_t* b, int nnode, double* total_return, int32_t* failure, double* values);
 /* API-level launches so far (a CUDA-graph replay counts once; hmj_batch_kernel_launches counts kernel nodes) */
