@@ -71,6 +71,10 @@ def load_library() -> C.CDLL:
     lib.hmj_plan_rollouts_dev.argtypes = [vp, dp, C.c_double, dp, dp, C.c_int, C.c_int, C.c_int, dp]
     lib.hmj_plan_argmin.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_int32)]
     lib.hmj_plan_fetch.argtypes = [vp, C.c_int, C.c_int, dp, dp, dp, dp, dp, dp]
+    lib.hmj_env_pool_config.argtypes = [vp, C.c_int, C.c_double, C.c_double, C.c_ulonglong, C.c_double]
+    lib.hmj_env_reset.argtypes = [vp, vp, C.c_int]
+    lib.hmj_env_reset_io.argtypes = [vp] + [C.POINTER(vp)] * 3
+    lib.hmj_batch_spare_rows.argtypes = [vp]
     lib.hmj_plan_iterate.argtypes = [vp, dp, C.c_double, dp, dp, C.c_int, C.c_int, C.c_int, dp, C.c_double, C.c_double,
                                      C.c_ulonglong, C.c_ulonglong, C.c_int, vp]
     lib.hmj_plan_record_size.argtypes = [C.c_int]

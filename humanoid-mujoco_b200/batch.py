@@ -274,6 +274,34 @@ class HumanoidBatch:
             ptr = None
         check(self.lib.hmj_env_step_fused_from(self._h, ptr, int(has_mask), float(rf), mst, int(seed) & (2**64 - 1), int(nsteps)))
 
+    # ---- episode pool: CPUEnv.reset / auto-reset on the device
+    @property
+    def spare_rows(self) -> int:
+        return int(self.lib.hmj_batch_spare_rows(self._h))
+
+    def env_pool_config(self, enable: bool, rf: float, max_sim_time: float, seed: int, timestep: float):
+        mst = 1e300 if not np.isfinite(max_sim_time) else float(max_sim_time)
+        check(self.lib.hmj_env_pool_config(self._h, int(bool(enable)), float(rf), mst, int(seed) & (2**64 - 1), float(timestep)))
+
+    def env_reset(self, ids=None):
+        """CPUEnv.reset of the listed envs (None: all) on the device; their first observations land in env_io()."""
+        if ids is None:
+            check(self.lib.hmj_env_reset(self._h, None, 0))
+        else:
+            a = np.ascontiguousarray(ids, dtype=np.int32)
+            check(self.lib.hmj_env_reset(self._h, a.ctypes.data, int(a.size)))
+
+    def env_reset_io(self):
+        """Views of the pool's per-step result block: counts[8], ended_ids[64], term_obs[64][30] (hmj_env_reset_io)."""
+        if getattr(self, "_rio", None) is None:
+            ptrs = [C.c_void_p() for _ in range(3)]
+            check(self.lib.hmj_env_reset_io(self._h, *[C.byref(p) for p in ptrs]))
+            self._rio = {
+                "counts": np.ctypeslib.as_array((C.c_int32 * 8).from_address(ptrs[0].value)),
+                "ended_ids": np.ctypeslib.as_array((C.c_int32 * 64).from_address(ptrs[1].value)),
+                "term_obs": np.ctypeslib.as_array((C.c_double * (64 * 30)).from_address(ptrs[2].value)).reshape(64, 30)}
+        return self._rio
+
     # ---- per-kernel timing
     def profile(self, enable: bool):
         check(self.lib.hmj_batch_profile(self._h, int(bool(enable))))

@@ -71,6 +71,20 @@ struct hmj_batch_ {
   char* io_dev = nullptr;
   size_t io_in_bytes = 0, io_out_bytes = 0;
   int launches = 0;
+  // episode pool (hmj_reset.cu): S spare rows behind the N envs, generated on their own stream
+  int n_spare = 0;
+  hmj_buffers_t spare{};             // view of rows [N, N + S)
+  hmj_envstate_t env_spare{};
+  hmj_pool_t pool{};
+  cudaStream_t spare_stream = nullptr;
+  hmj_solve_ctx_t spare_ctx{};
+  cudaEvent_t ev_main = nullptr, round_done = nullptr;
+  cudaGraphExec_t round_graph = nullptr;
+  bool pool_on = false, round_inflight = false, pool_need_round = true;
+  long long step_idx = 0, round_start = 0;
+  double pool_rf = 0, pool_max_sim_time = 0, pool_timestep = 0.002;
+  unsigned long long pool_seed = 0;
+  size_t io_ext_offset = 0;          // byte offset of the pool's result block inside the IO out block
   hmj_solve_ctx_t solve_ctx{};       // side streams + events that overlap the solver classes
   // Pipes: the physics chain of a step (smooth -> collide -> solve) is enqueued once per contiguous block of envs, each on
   // its own stream, forked from / joined to the main stream inside the call.  Every stage is a single wave whose length is
@@ -92,6 +106,10 @@ struct hmj_batch_ {
   std::vector<cudaEvent_t> prof_events;  // 4 per step: before smooth, collide, solve, after solve
   size_t prof_used = 0;
 };
+
+static int pool_step(hmj_batch_t* b, const int32_t* term, const int32_t* trunc, bool drain);
+static int pool_drain(hmj_batch_t* b);
+static int32_t* io_counts_host(hmj_batch_t* b);
 
 extern "C" const char* hmj_last_error(void) { return g_err; }
 extern "C" int hmj_version(void) { return HMJ_VERSION; }
@@ -241,13 +259,16 @@ static void build_tables(const hmj_model_t* m, hmj_tables_t* t) {
     for (int j = 0; j <= i; j++) { t->tri_i[e] = i; t->tri_j[e] = j; e++; }
 }
 
+// `count` elements (per-env arrays pass rows x width with rows = N + S: the spare rows of the episode pool sit behind the
+// N envs; the named-array accessors see the first N rows only).
 template <typename Tp>
-static int alloc_array(hmj_batch_* b, const char* name, Tp** out, size_t count) {
+static int alloc_array(hmj_batch_* b, const char* name, Tp** out, size_t count, bool per_env = true) {
   void* p = nullptr;
   CK(cudaMalloc(&p, count * sizeof(Tp)));
   b->allocs.push_back(p);
   CK(cudaMemsetAsync(p, 0, count * sizeof(Tp), b->stream));
-  if (name) b->arrays[name] = ArrayInfo{p, count * sizeof(Tp)};
+  const size_t rows = (size_t)b->n + b->n_spare;
+  if (name) b->arrays[name] = ArrayInfo{p, per_env ? count / rows * (size_t)b->n * sizeof(Tp) : count * sizeof(Tp)};
   *out = (Tp*)p;
   return HMJ_OK;
 }
@@ -266,6 +287,11 @@ static int alloc_array(hmj_batch_* b, const char* name, Tp** out, size_t count) 
   do {                                                              \
     int rc_ = alloc_array(b, name, &b->buf.field, (size_t)(count)); \
     if (rc_) { hmj_batch_destroy(b); return rc_; }                  \
+  } while (0)
+#define ALLOC_FLAT(name, field, count)                                     \
+  do {                                                                     \
+    int rc_ = alloc_array(b, name, &b->buf.field, (size_t)(count), false); \
+    if (rc_) { hmj_batch_destroy(b); return rc_; }                         \
   } while (0)
 
 
@@ -347,6 +373,18 @@ extern "C" void hmj_batch_destroy(hmj_batch_t* b) {
     if (pp.stream) cudaStreamDestroy(pp.stream);
   }
   if (b->pipe_fork) cudaEventDestroy(b->pipe_fork);
+  if (b->spare_stream) cudaStreamSynchronize(b->spare_stream);
+  if (b->round_graph) cudaGraphExecDestroy(b->round_graph);
+  for (int k = 0; k < 2; k++) {
+    if (b->spare_ctx.side[k]) cudaStreamDestroy(b->spare_ctx.side[k]);
+    if (b->spare_ctx.join[k]) cudaEventDestroy(b->spare_ctx.join[k]);
+  }
+  if (b->spare_ctx.fork) cudaEventDestroy(b->spare_ctx.fork);
+  if (b->spare_ctx.fac_fork) cudaEventDestroy(b->spare_ctx.fac_fork);
+  if (b->spare_ctx.fac_done) cudaEventDestroy(b->spare_ctx.fac_done);
+  if (b->ev_main) cudaEventDestroy(b->ev_main);
+  if (b->round_done) cudaEventDestroy(b->round_done);
+  if (b->spare_stream) cudaStreamDestroy(b->spare_stream);
   for (int k = 0; k < 2; k++) {
     if (b->solve_ctx.side[k]) cudaStreamDestroy(b->solve_ctx.side[k]);
     if (b->solve_ctx.join[k]) cudaEventDestroy(b->solve_ctx.join[k]);
@@ -396,7 +434,15 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
   CKB(cudaMalloc((void**)&b->task_dev, sizeof(hmj_task_t)));
   CKB(cudaMemcpyAsync(b->task_dev, &task, sizeof(task), cudaMemcpyHostToDevice, b->stream));
 
-  const size_t N = (size_t)n_envs;
+  {   // spare rows of the episode pool: N / 8 clamped to [32, 1024] (HMJ_SPARE overrides; 0 = no pool)
+    int S = n_envs / 8;
+    S = S < 32 ? 32 : (S > 1024 ? 1024 : S);
+    if (const char* e = getenv("HMJ_SPARE")) S = atoi(e);
+    if (S < 0) S = 0;
+    if (S > 1024) S = 1024;
+    b->n_spare = S;
+  }
+  const size_t N = (size_t)n_envs + b->n_spare;   // rows of every per-env array
   ALLOC("qpos", qpos, N * HMJ_NQ);
   ALLOC("qvel", qvel, N * HMJ_NV);
   ALLOC("time", time, N);
@@ -415,9 +461,9 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
   ALLOC("sens", sens, N * SENS_NUM);
   ALLOC("slots", slots, N * HMJ_NSLOT * HMJ_SLOT_DOUBLES);
   ALLOC("slot_mask", slot_mask, N * 4);
-  ALLOC("wq_count", wq_count, 64 * HMJ_MAX_PIPES);
+  ALLOC_FLAT("wq_count", wq_count, 64 * (HMJ_MAX_PIPES + 1));
   ALLOC("wq_task", wq_task, N * (size_t)b->tab_host->group_base[HMJ_NGROUP]);
-  ALLOC("solve_count", solve_count, 4 * HMJ_MAX_PIPES);
+  ALLOC_FLAT("solve_count", solve_count, 4 * (HMJ_MAX_PIPES + 1));
   ALLOC("solve_list", solve_list, 3 * N);
   ALLOC("qacc", qacc, N * HMJ_NV);
   ALLOC("qacc_smooth", qacc_smooth, N * HMJ_NV);
@@ -433,10 +479,10 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
   ALLOC("trace", trace, N * 3);
   {
     int rc;
-    if ((rc = alloc_array(b, nullptr, &b->state_dev, HMJ_NSTATE + 1)) || (rc = alloc_array(b, nullptr, &b->nominal_dev, 64 * HMJ_NU)) ||
-        (rc = alloc_array(b, nullptr, &b->record_dev, 3 + 64 * HMJ_NU)) || (rc = alloc_array(b, nullptr, &b->select_dev, 3 + 64 * HMJ_NU)) || (rc = alloc_array(b, nullptr, &b->spline_times_dev, 64)) ||
+    if ((rc = alloc_array(b, nullptr, &b->state_dev, HMJ_NSTATE + 1, false)) || (rc = alloc_array(b, nullptr, &b->nominal_dev, 64 * HMJ_NU, false)) ||
+        (rc = alloc_array(b, nullptr, &b->record_dev, 3 + 64 * HMJ_NU, false)) || (rc = alloc_array(b, nullptr, &b->select_dev, 3 + 64 * HMJ_NU, false)) || (rc = alloc_array(b, nullptr, &b->spline_times_dev, 64, false)) ||
         (rc = alloc_array(b, "returns", &b->returns_dev, N)) || (rc = alloc_array(b, nullptr, &b->failure_dev, N)) ||
-        (rc = alloc_array(b, "argmin", &b->argmin_dev, 2))) {
+        (rc = alloc_array(b, "argmin", &b->argmin_dev, 2, false))) {
       hmj_batch_destroy(b);
       return rc;
     }
@@ -459,14 +505,51 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
     EALLOC("env_force_draws", force_draws, N);
     EALLOC("env_torso_quat", torso_quat, N * 4);
 #undef EALLOC
-    b->io_in_bytes = N * HMJ_NU * 8 + N * 4;
+    const size_t NE = (size_t)n_envs;
+    b->io_in_bytes = NE * HMJ_NU * 8 + NE * 4;
     b->io_in_bytes = (b->io_in_bytes + 63) / 64 * 64;
-    b->io_out_bytes = N * (30 + 1 + 1 + 4) * 8 + 3 * N * 4;
+    b->io_out_bytes = NE * (30 + 1 + 1 + 4) * 8 + 3 * NE * 4;
+    // the episode pool's per-step result block rides behind the flags: counts[8] i32 | ended_ids[64] i32 | term_obs[64][30] f64
+    b->io_ext_offset = (b->io_out_bytes + 7) / 8 * 8;
+    b->io_out_bytes = b->io_ext_offset + 8 * 4 + HMJ_POOL_MAXTERM * 4 + HMJ_POOL_MAXTERM * 30 * 8;
     if (!rc && cudaHostAlloc((void**)&b->io_host, b->io_in_bytes + b->io_out_bytes, cudaHostAllocDefault) != cudaSuccess)
       rc = fail(HMJ_ERR_CUDA, "cudaHostAlloc failed%s");
     if (!rc) { memset(b->io_host, 0, b->io_in_bytes + b->io_out_bytes); rc = alloc_array(b, nullptr, &b->io_dev, b->io_in_bytes + b->io_out_bytes); }
     if (!rc && cudaHostAlloc((void**)&b->plan_stage, 2048 * sizeof(double), cudaHostAllocDefault) != cudaSuccess)
       rc = fail(HMJ_ERR_CUDA, "cudaHostAlloc failed%s");
+    if (!rc && b->n_spare > 0) {   // episode pool
+      const size_t S = (size_t)b->n_spare;
+      hmj_pool_t& P = b->pool;
+      P.S = (int32_t)S;
+#define PALLOC(field, count) if (!rc) rc = alloc_array(b, nullptr, &P.field, (size_t)(count), false)
+      PALLOC(state, S); PALLOC(active, S); PALLOC(gen, S); PALLOC(obs, S * 30); PALLOC(reward, S);
+      PALLOC(term, S); PALLOC(trunc, S); PALLOC(selfc, S);
+      PALLOC(pending, NE); PALLOC(assign, NE); PALLOC(served_list, NE);
+      PALLOC(ended_ids_full, NE); PALLOC(term_obs_full, NE * 30);
+#undef PALLOC
+      if (!rc) rc = alloc_array(b, "env_episode_src", &P.episode_src, N);
+      if (!rc) {
+        char* ext = b->io_dev + b->io_in_bytes + b->io_ext_offset;
+        P.counts = (int32_t*)ext;
+        P.ended_ids = P.counts + 8;
+        P.term_obs = (double*)(ext + 8 * 4 + HMJ_POOL_MAXTERM * 4);
+        b->arrays["env_terminal_obs_compact"] = ArrayInfo{P.term_obs_full, NE * 30 * 8};
+        b->arrays["env_ended_ids_compact"] = ArrayInfo{P.ended_ids_full, NE * 4};
+        b->arrays["pool_state"] = ArrayInfo{P.state, S * 4};
+      }
+      if (!rc && (cudaStreamCreateWithFlags(&b->spare_stream, cudaStreamNonBlocking) != cudaSuccess ||
+                  cudaEventCreateWithFlags(&b->ev_main, cudaEventDisableTiming) != cudaSuccess ||
+                  cudaEventCreateWithFlags(&b->round_done, cudaEventDisableTiming) != cudaSuccess))
+        rc = fail(HMJ_ERR_CUDA, "stream/event creation failed%s");
+      for (int k = 0; k < 2 && !rc; k++)
+        if (cudaStreamCreateWithFlags(&b->spare_ctx.side[k], cudaStreamNonBlocking) != cudaSuccess ||
+            cudaEventCreateWithFlags(&b->spare_ctx.join[k], cudaEventDisableTiming) != cudaSuccess)
+          rc = fail(HMJ_ERR_CUDA, "stream/event creation failed%s");
+      if (!rc && (cudaEventCreateWithFlags(&b->spare_ctx.fork, cudaEventDisableTiming) != cudaSuccess ||
+                  cudaEventCreateWithFlags(&b->spare_ctx.fac_fork, cudaEventDisableTiming) != cudaSuccess ||
+                  cudaEventCreateWithFlags(&b->spare_ctx.fac_done, cudaEventDisableTiming) != cudaSuccess))
+        rc = fail(HMJ_ERR_CUDA, "stream/event creation failed%s");
+    }
     if (rc) { hmj_batch_destroy(b); return rc; }
   }
   // default params and state (qpos0) for every env
@@ -484,6 +567,16 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
   {
     int rc = make_pipes(b);
     if (rc) { hmj_batch_destroy(b); return rc; }
+  }
+  if (b->n_spare > 0) {   // the spare rows as a batch of their own, masked to the rows a generation round works on
+    b->spare = pipe_view(b->buf, b->n, b->n_spare, HMJ_MAX_PIPES, b->tab_host->group_base[HMJ_NGROUP]);
+    b->spare.active = b->pool.active;
+    const size_t s0 = (size_t)b->n;
+    hmj_envstate_t& E = b->env_spare;
+    E = b->env;
+    E.act_noise += s0 * HMJ_NU; E.obs_noise += s0 * 31; E.act_delay += s0; E.obs_delay += s0 * 3; E.act_count += s0; E.obs_count += s0;
+    E.act_hist += s0 * HMJ_ENV_HIST * HMJ_NU; E.obs_hist += s0 * HMJ_ENV_HIST * 30; E.prev_action += s0 * HMJ_NU;
+    E.latest_action += s0 * HMJ_NU; E.force_sched += s0 * 5; E.force_body += s0; E.force_draws += s0; E.torso_quat += s0 * 4;
   }
   *out = b;
   return HMJ_OK;
@@ -935,9 +1028,26 @@ extern "C" int hmj_env_step_fused_from(hmj_batch_t* b, const double* action_host
                             d_rew, d_flags, d_flags + N, d_flags + 2 * N, b->stream);
   hmj_launch_env_post(b->buf, b->env, mask, d_obs, d_time, d_quat, b->stream);
   b->launches += 3; b->host_launches += 3;
-  CK(cudaMemcpyAsync(b->io_host + b->io_in_bytes, d_out, b->io_out_bytes, cudaMemcpyDeviceToHost, b->stream));
+  const bool pool = b->pool_on && nsteps >= 0 && !has_mask;
+  if (pool) {
+    int rc = pool_step(b, d_flags, d_flags + N, false);
+    if (rc) return rc;
+  }
+  CK(cudaMemcpyAsync(b->io_host + b->io_in_bytes, d_out, pool ? b->io_out_bytes : b->io_ext_offset, cudaMemcpyDeviceToHost, b->stream));
   CK(cudaStreamSynchronize(b->stream));
   CK(cudaGetLastError());
+  if (pool) {
+    int32_t* counts = io_counts_host(b);
+    b->pool_need_round = counts[6] > 0;
+    if (counts[2] > 0) {   // more episodes ended than the pool held: serve the rest now, then refresh their result rows
+      const int32_t needed = counts[0], ended_now = counts[4];
+      int rc = pool_drain(b);
+      if (rc) return rc;
+      CK(cudaMemcpyAsync(b->io_host + b->io_in_bytes, d_out, b->io_ext_offset, cudaMemcpyDeviceToHost, b->stream));
+      CK(cudaStreamSynchronize(b->stream));
+      counts[0] = needed; counts[4] = ended_now;
+    }
+  }
   return HMJ_OK;
 }
 
@@ -957,6 +1067,163 @@ extern "C" int hmj_pinned_free(void* p) {
   if (p) CK(cudaFreeHost(p));
   return HMJ_OK;
 }
+
+// ------------------------------------------------------------------ episode pool: CPUEnv.reset / DummyVecEnv auto-reset on the device
+// (kernels and the design: hmj_reset.cu)
+#define HMJ_POOL_JOIN_LAG 2   /* a round launched behind step t is joined (and its rows promoted) at step t + 2 */
+
+// One generation round on the spare stream: draw episodes into the EMPTY rows, CPUEnv.reset's probe step() with action
+// None, the second _get_obs() that reset returns, the rejection rule.
+static void enqueue_round_chain(hmj_batch_t* b) {
+  cudaStream_t s = b->spare_stream;
+  const hmj_buffers_t& V = b->spare;
+  const hmj_envstate_t& E = b->env_spare;
+  hmj_launch_env_reset(b->tab_dev, V, E, b->pool, b->pool_rf, b->pool_timestep, b->pool_seed, b->n, s);
+  hmj_launch_env_pre(V, E, nullptr, b->pool.active, b->pool_rf, b->pool_seed, s, b->n);
+  hmj_launch_smooth(b->tab_dev, V, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, s);
+  hmj_launch_factor(b->tab_dev, V, s, &b->spare_ctx);
+  hmj_launch_collide(b->tab_dev, V, s, false);
+  hmj_launch_solve(b->tab_dev, V, 1, s, &b->spare_ctx, false);
+  for (int k = 0; k < 2; k++) {
+    hmj_launch_env_obs_reward(b->tab_dev, V, E.prev_action, E.latest_action, E.obs_noise, b->pool_max_sim_time, b->pool.obs,
+                              b->pool.reward, b->pool.term, b->pool.trunc, b->pool.selfc, s);
+    hmj_launch_env_post(V, E, b->pool.active, b->pool.obs, nullptr, nullptr, s);
+  }
+  hmj_launch_pool_validate(V, b->pool, s);
+}
+
+// Launch a round behind everything the main stream has enqueued so far (the rows emptied by this step's copies are seen).
+static int launch_round(hmj_batch_t* b) {
+  CK(cudaEventRecord(b->ev_main, b->stream));
+  CK(cudaStreamWaitEvent(b->spare_stream, b->ev_main, 0));
+  b->launches += 15;
+  if (b->graph_mode == 0 || !b->warmed) {
+    enqueue_round_chain(b);
+    b->warmed = true;
+    b->host_launches += 15;
+  } else {
+    if (!b->round_graph) {
+      cudaGraph_t g = nullptr;
+      CK(cudaStreamBeginCapture(b->spare_stream, cudaStreamCaptureModeThreadLocal));
+      enqueue_round_chain(b);
+      cudaError_t e = cudaStreamEndCapture(b->spare_stream, &g);
+      if (e == cudaSuccess && g) e = cudaGraphInstantiate(&b->round_graph, g, 0);
+      if (g) cudaGraphDestroy(g);
+      if (e != cudaSuccess || !b->round_graph) return fail(HMJ_ERR_CUDA, "pool round graph capture failed: %s", cudaGetErrorString(e));
+    }
+    CK(cudaGraphLaunch(b->round_graph, b->spare_stream));
+    b->host_launches += 1;
+  }
+  CK(cudaEventRecord(b->round_done, b->spare_stream));
+  b->round_inflight = true;
+  b->round_start = b->step_idx;
+  return HMJ_OK;
+}
+
+static double* io_out_dev(hmj_batch_t* b) { return (double*)(b->io_dev + b->io_in_bytes); }
+static int32_t* io_counts_host(hmj_batch_t* b) { return (int32_t*)(b->io_host + b->io_in_bytes + b->io_ext_offset); }
+
+// Inside a control step, after the epilogue: join a due round, hand ready episodes to the envs that ended, start the
+// next round.  Every decision uses host-known numbers only (step index, the previous step's counts): deterministic.
+static int pool_step(hmj_batch_t* b, const int32_t* term, const int32_t* trunc, bool drain) {
+  const size_t N = b->n;
+  double* d_out = io_out_dev(b);
+  int promote = 0;
+  if (b->round_inflight && (drain || b->step_idx - b->round_start >= HMJ_POOL_JOIN_LAG)) {
+    CK(cudaStreamWaitEvent(b->stream, b->round_done, 0));
+    b->round_inflight = false;
+    promote = 1;
+  }
+  const bool launching = !b->round_inflight && (b->pool_need_round || drain);
+  hmj_launch_autoreset(b->buf, b->env, b->spare, b->env_spare, b->pool, term, trunc, d_out, d_out + N * 31, d_out + N * 32,
+                       promote | (drain ? 2 : 0) | (launching ? 4 : 0), b->stream);
+  b->launches += 2; b->host_launches += 2;
+  if (launching) {
+    int rc = launch_round(b);
+    if (rc) return rc;
+  }
+  if (!drain) b->step_idx++;
+  return HMJ_OK;
+}
+
+// Serve every env that still waits for an episode (a burst larger than the pool: the first reset of a run, the
+// curriculum's reset-everything, a mass time-out): generation rounds back to back, blocking.
+static int pool_drain(hmj_batch_t* b) {
+  int32_t* counts = io_counts_host(b);
+  for (int it = 0; it < 100000; it++) {
+    int rc = pool_step(b, nullptr, nullptr, true);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(counts, b->pool.counts, 8 * sizeof(int32_t), cudaMemcpyDeviceToHost, b->stream));
+    CK(cudaStreamSynchronize(b->stream));
+    if (counts[2] == 0) {
+      b->pool_need_round = counts[6] > 0;
+      return HMJ_OK;
+    }
+  }
+  return fail(HMJ_ERR_CUDA, "episode pool: environments still waiting after 100000 generation rounds%s");
+}
+
+/* CPUEnv.reset + DummyVecEnv auto-reset on the device.  enable != 0: hmj_env_step_fused[_from] (without mask) replaces
+ * every env whose episode ended (terminated | truncated) with a fresh pre-validated episode inside the same call. */
+extern "C" int hmj_env_pool_config(hmj_batch_t* b, int enable, double rf, double max_sim_time, unsigned long long seed,
+                                   double timestep) {
+  if (!b) return fail(HMJ_ERR_ARG, "null batch%s");
+  if (b->n_spare <= 0) return fail(HMJ_ERR_ARG, "this batch was created without spare rows (HMJ_SPARE=0)%s");
+  CK(cudaSetDevice(b->device));
+  CK(cudaStreamSynchronize(b->stream));
+  CK(cudaStreamSynchronize(b->spare_stream));
+  const bool changed = rf != b->pool_rf || max_sim_time != b->pool_max_sim_time || seed != b->pool_seed || timestep != b->pool_timestep;
+  if (changed) {
+    if (b->round_graph) { cudaGraphExecDestroy(b->round_graph); b->round_graph = nullptr; }
+    b->pool_rf = rf; b->pool_max_sim_time = max_sim_time; b->pool_seed = seed; b->pool_timestep = timestep;
+    // episodes drawn under the old settings are discarded (the curriculum raises rf and resets everything)
+    CK(cudaMemsetAsync(b->pool.state, 0, (size_t)b->n_spare * 4, b->stream));
+    CK(cudaMemsetAsync(b->pool.active, 0, (size_t)b->n_spare * 4, b->stream));
+    CK(cudaStreamSynchronize(b->stream));
+    b->round_inflight = false;
+    b->pool_need_round = true;
+  }
+  b->pool_on = enable != 0;
+  return HMJ_OK;
+}
+
+/* CPUEnv.reset for the listed envs (ids == NULL: all): blocking.  The first observation of each new episode lands in
+ * the IO block's obs / time / torso_quat rows of those envs (hmj_env_io); other rows are untouched. */
+extern "C" int hmj_env_reset(hmj_batch_t* b, const int32_t* ids, int count) {
+  if (!b || (ids && count < 0)) return fail(HMJ_ERR_ARG, "bad argument to env_reset%s");
+  if (b->n_spare <= 0) return fail(HMJ_ERR_ARG, "this batch was created without spare rows (HMJ_SPARE=0)%s");
+  CK(cudaSetDevice(b->device));
+  for (int i = 0; ids && i < count; i++)
+    if (ids[i] < 0 || ids[i] >= b->n) return fail(HMJ_ERR_ARG, "env id out of range%s");
+  const int32_t* ids_dev = nullptr;
+  if (ids) {
+    if (count == 0) return HMJ_OK;
+    CK(cudaMemcpyAsync(b->pool.served_list, ids, (size_t)count * 4, cudaMemcpyHostToDevice, b->stream));   // staging: rewritten by the next assign
+    ids_dev = b->pool.served_list;
+  }
+  hmj_launch_pool_mark_pending(b->pool, ids_dev, count, b->n, b->stream);
+  b->launches += 1; b->host_launches += 1;
+  int rc = pool_drain(b);
+  if (rc) return rc;
+  CK(cudaMemcpyAsync(b->io_host + b->io_in_bytes, io_out_dev(b), b->io_out_bytes, cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  CK(cudaGetLastError());
+  return HMJ_OK;
+}
+
+/* Views of the pool's per-step result block (pinned): counts[8] = {needed, served, still waiting (0 after the call),
+ * ready rows left, ended this step, S, empty rows, 0}; ended_ids[64] / term_obs[64][30] = the first 64 envs that ended
+ * this step in env order with their terminal observations (more: named arrays "env_ended_ids_compact" /
+ * "env_terminal_obs_compact", N rows). */
+extern "C" int hmj_env_reset_io(hmj_batch_t* b, int32_t** counts, int32_t** ended_ids, double** term_obs) {
+  if (!b || !b->io_host) return fail(HMJ_ERR_ARG, "null batch%s");
+  char* ext = b->io_host + b->io_in_bytes + b->io_ext_offset;
+  if (counts) *counts = (int32_t*)ext;
+  if (ended_ids) *ended_ids = (int32_t*)ext + 8;
+  if (term_obs) *term_obs = (double*)(ext + 8 * 4 + HMJ_POOL_MAXTERM * 4);
+  return HMJ_OK;
+}
+extern "C" int hmj_batch_spare_rows(const hmj_batch_t* b) { return b ? b->n_spare : 0; }
 
 // ------------------------------------------------------------------ planner
 extern "C" int hmj_plan_set_task(hmj_batch_t* b, int nterm, const int32_t* dim, const int32_t* norm, const double* weight,

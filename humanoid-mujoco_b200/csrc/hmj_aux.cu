@@ -215,6 +215,7 @@ k_env_obs_reward(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const doub
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int env = blockIdx.x * OBS_WARPS + w;
   if (env >= B.n) return;
+  if (B.active && !B.active[env]) return;
   const hmj_model_t& M = T->m;
   const double* qpos = B.qpos + (size_t)env * HMJ_NQ;
   const double* qvel = B.qvel + (size_t)env * HMJ_NV;
@@ -308,7 +309,7 @@ void hmj_launch_env_obs_reward(const hmj_tables_t* tab, hmj_buffers_t buf, const
 #define ENV_WARPS 4
 __global__ void __launch_bounds__(32 * ENV_WARPS)
 k_env_pre(hmj_buffers_t B, hmj_envstate_t E, const double* __restrict__ action, const int32_t* __restrict__ mask,
-          double rf, unsigned long long seed) {
+          double rf, unsigned long long seed, int sid0) {
   const int lane = threadIdx.x & 31;
   const int env = blockIdx.x * ENV_WARPS + (threadIdx.x >> 5);
   if (env >= B.n || (mask && !mask[env])) return;
@@ -338,16 +339,16 @@ k_env_pre(hmj_buffers_t B, hmj_envstate_t E, const double* __restrict__ action, 
   if (t >= fs[0] + fs[1]) {
     const uint32_t c = (uint32_t)E.force_draws[env] * 8u;
     // contraction-free (__dmul_rn / __dadd_rn): the numpy restatement in env.py must see the same bits
-    fs[0] = __dadd_rn(t, __dadd_rn(1.0, __dmul_rn(2.0, hmj_rand_u01(seed, env, c + 0))));
-    fs[1] = __dadd_rn(0.05, __dmul_rn(0.10, hmj_rand_u01(seed, env, c + 1)));
-    fs[2] = __dadd_rn(5.0 * rf, __dmul_rn(15.0 * rf - 5.0 * rf, hmj_rand_u01(seed, env, c + 2)));
-    double dx = __dadd_rn(-1.0, __dmul_rn(2.0, hmj_rand_u01(seed, env, c + 3)));
-    double dy = __dadd_rn(-1.0, __dmul_rn(2.0, hmj_rand_u01(seed, env, c + 4)));
+    fs[0] = __dadd_rn(t, __dadd_rn(1.0, __dmul_rn(2.0, hmj_rand_u01(seed, sid0 + env, c + 0))));
+    fs[1] = __dadd_rn(0.05, __dmul_rn(0.10, hmj_rand_u01(seed, sid0 + env, c + 1)));
+    fs[2] = __dadd_rn(5.0 * rf, __dmul_rn(15.0 * rf - 5.0 * rf, hmj_rand_u01(seed, sid0 + env, c + 2)));
+    double dx = __dadd_rn(-1.0, __dmul_rn(2.0, hmj_rand_u01(seed, sid0 + env, c + 3)));
+    double dy = __dadd_rn(-1.0, __dmul_rn(2.0, hmj_rand_u01(seed, sid0 + env, c + 4)));
     const double nrm = sqrt(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
     if (nrm == 0) { dx = 1.0; dy = 0.0; } else { dx /= nrm; dy /= nrm; }
     fs[3] = dx; fs[4] = dy;
     xf[0] = 0.0; xf[1] = 0.0;
-    int body = 1 + (int)(14.0 * hmj_rand_u01(seed, env, c + 5));
+    int body = 1 + (int)(14.0 * hmj_rand_u01(seed, sid0 + env, c + 5));
     if (body > 14) body = 14;
     E.force_body[env] = body;
     E.force_draws[env] += 1;
@@ -393,8 +394,8 @@ k_env_post(hmj_buffers_t B, hmj_envstate_t E, const int32_t* __restrict__ mask, 
 }
 
 void hmj_launch_env_pre(hmj_buffers_t buf, hmj_envstate_t env, const double* action, const int32_t* mask, double rf,
-                        unsigned long long seed, cudaStream_t stream) {
-  k_env_pre<<<(buf.n + ENV_WARPS - 1) / ENV_WARPS, 32 * ENV_WARPS, 0, stream>>>(buf, env, action, mask, rf, seed);
+                        unsigned long long seed, cudaStream_t stream, int stream_id_offset) {
+  k_env_pre<<<(buf.n + ENV_WARPS - 1) / ENV_WARPS, 32 * ENV_WARPS, 0, stream>>>(buf, env, action, mask, rf, seed, stream_id_offset);
 }
 void hmj_launch_env_post(hmj_buffers_t buf, hmj_envstate_t env, const int32_t* mask, double* obs, double* time_out, double* quat_out,
                          cudaStream_t stream) {

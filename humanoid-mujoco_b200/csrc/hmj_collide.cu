@@ -602,8 +602,8 @@ k_broad(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int npad) {
   const hmj_model_t& M = T->m;
   if (kpos >= HMJ_NPAIR) return;  // npad * NPAIR is a multiple of 32: whole warps leave together (before any barrier use)
   const int k = T->broad_order[kpos];   // expensive pairs first (hmj_api.cu: build of the tables)
-  const bool in = e < B.n;
-  const int env = in ? e : B.n - 1;
+  const bool in = e < B.n && (!B.active || B.active[e]);
+  const int env = e < B.n ? e : B.n - 1;
   const int g1 = M.pair_geom1[k], g2 = M.pair_geom2[k];
   const double* gx = B.geom_xpos + (size_t)env * HMJ_NGEOM * 3;
   const double* gm = B.geom_xmat + (size_t)env * HMJ_NGEOM * 9;

@@ -82,6 +82,7 @@ struct hmj_task_t {
 // Device buffers of one batch (all pointers are device pointers; N = n_envs).
 struct hmj_buffers_t {
   int32_t n;
+  const int32_t* active;  // optional [N]: rows with 0 are skipped by every stage (episode-pool rows that are not being generated)
   // ---- state
   double* qpos;       // [N][19]
   double* qvel;       // [N][18]
@@ -140,6 +141,37 @@ struct hmj_envstate_t {
   int32_t* force_body;   // [N]
   int32_t* force_draws;  // [N]      renewals so far (counter of the per-env random stream)
   double* torso_quat;    // [N][4]   noisy root quaternion (CPUEnv.torso_quat, read by controllers/mpc_in_env.py:25)
+};
+
+// Episode pool (hmj_reset.cu): S spare rows behind the N envs of a batch hold pre-validated fresh episodes.
+#define HMJ_POOL_EMPTY 0     /* row free: the next generation round draws a new episode into it */
+#define HMJ_POOL_PROBING 1   /* being generated: the round's kernels run on it (active mask) */
+#define HMJ_POOL_PENDING 2   /* accepted by the rejection rule; becomes READY when the main stream joins the round */
+#define HMJ_POOL_READY 3     /* can be taken by an env whose episode ended */
+#define HMJ_POOL_TAKEN 4     /* assigned this step, being copied */
+#define HMJ_POOL_FREED 5     /* consumed; becomes EMPTY at the step that launches the next round (deterministic membership) */
+#define HMJ_POOL_REJECTED 6  /* failed the rejection rule; becomes EMPTY at the step that launches the next round */
+#define HMJ_POOL_MAXTERM 64  /* terminal observations carried in the per-step host block (more: fetched on demand) */
+struct hmj_pool_t {
+  int32_t S;
+  int32_t* state;        // [S]
+  int32_t* active;       // [S]  the spare view's `active` mask
+  int32_t* gen;          // [S]  episodes drawn so far in this row (counter block of the random stream)
+  double* obs;           // [S][30] reset's return value (second _get_obs) of the pooled episode
+  double* reward;        // [S]  scratch of the probe step's epilogue
+  int32_t* term;         // [S]
+  int32_t* trunc;        // [S]
+  int32_t* selfc;        // [S]
+  int32_t* pending;      // [N]  env waits for a fresh episode
+  int32_t* assign;       // [N]  spare row taken this step, -1 none
+  int32_t* served_list;  // [N]  envs served this step, in order
+  int32_t* episode_src;  // [N]  row | generation << 16 of the env's current episode
+  int32_t* ended_ids_full; // [N]  envs that needed an episode this step, in env order
+  double* term_obs_full;   // [N][30] their terminal observations
+  // host block extension (device mirror of the pinned block): counts[8], ended_ids[64], term_obs[64][30]
+  int32_t* counts;
+  int32_t* ended_ids;
+  double* term_obs;
 };
 
 // Counter-based uniform in [0, 1): splitmix64 of (seed, env, counter).  Restated in numpy by env.py for the
@@ -326,6 +358,13 @@ void hmj_launch_env_obs_reward(const hmj_tables_t* tab, hmj_buffers_t buf, const
                                const double* noise, double max_sim_time, double* obs, double* reward, int32_t* terminated,
                                int32_t* truncated, int32_t* self_collision, cudaStream_t stream);
 void hmj_launch_env_pre(hmj_buffers_t buf, hmj_envstate_t env, const double* action, const int32_t* mask, double rf,
-                        unsigned long long seed, cudaStream_t stream);
+                        unsigned long long seed, cudaStream_t stream, int stream_id_offset = 0);
+void hmj_launch_env_reset(const hmj_tables_t* tab, hmj_buffers_t spare, hmj_envstate_t spare_env, hmj_pool_t pool, double rf,
+                          double timestep, unsigned long long seed, int row0_global, cudaStream_t stream);
+void hmj_launch_pool_validate(hmj_buffers_t spare, hmj_pool_t pool, cudaStream_t stream);
+void hmj_launch_autoreset(hmj_buffers_t buf, hmj_envstate_t env, hmj_buffers_t spare, hmj_envstate_t spare_env, hmj_pool_t pool,
+                          const int32_t* term, const int32_t* trunc, double* obs, double* time_out, double* quat_out, int flags /* 1 promote, 2 drain, 4 a round is launched right behind this step */,
+                          cudaStream_t stream);
+void hmj_launch_pool_mark_pending(hmj_pool_t pool, const int32_t* ids_dev, int count, int n, cudaStream_t stream);
 void hmj_launch_env_post(hmj_buffers_t buf, hmj_envstate_t env, const int32_t* mask, double* obs, double* time_out, double* quat_out,
                          cudaStream_t stream);

@@ -140,6 +140,7 @@ k_smooth(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* 
   if (blockIdx.x == 0 && threadIdx.x < 64) B.wq_count[threadIdx.x] = 0;
   if (blockIdx.x == 0 && threadIdx.x < 4) B.solve_count[threadIdx.x] = 0;
   if (env >= B.n) return;  // whole warp exits together
+  if (B.active && !B.active[env]) return;
   if (lane < 4) B.slot_mask[(size_t)env * 4 + lane] = 0u;
   SmoothSmem& S = reinterpret_cast<SmoothSmem*>(smem_raw)[wib];
   const hmj_model_t& M = T->m;

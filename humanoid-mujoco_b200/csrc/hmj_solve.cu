@@ -320,6 +320,7 @@ __global__ void __launch_bounds__(32) k_factor(const hmj_tables_t* __restrict__ 
   const int lane = threadIdx.x & 31;
   const int env = blockIdx.x;
   if (env >= B.n) return;
+  if (B.active && !B.active[env]) return;
   const hmj_model_t& M = T->m;
   const double h = B.params[env].timestep;
   for (int t = lane; t < NV * LD; t += 32) S.M[t] = 0.0;
@@ -365,6 +366,7 @@ __global__ void __launch_bounds__(128) k_classify(const hmj_tables_t* __restrict
   const int lane = threadIdx.x & 31;
   const int env = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (env >= B.n) return;
+  if (B.active && !B.active[env]) return;
   const unsigned FULL = 0xffffffffu;
   const hmj_model_t& M = T->m;
   const hmj_params_t* P = B.params + env;

@@ -132,6 +132,83 @@ def standup_start_state(qpos0: np.ndarray, rng: np.random.Generator, rf: float, 
     return qpos
 
 
+# draw offsets of k_env_reset (csrc/hmj_reset.cu), one block of 512 counters per generation of a pool row
+_RD = dict(FRICTION=0, MASS=1, EXTRA_BODY=15, EXTRA_MASS=16, ARMATURE=17, MARGIN=29, RANGE=41, GAIN=65, FORCERANGE=77,
+           HF_COARSE=101, HF_FINE=117, DELAY=181, N_ACT=187, N_SAME=211, N_GYRO=235, N_IMU=241, JOINT=249, Z=261, QUAT=262)
+
+
+def device_reset_draws(model: np.ndarray, base: np.ndarray, seed: int, rows, gens, rf: float, timestep: float = TIMESTEP):
+    """numpy restatement of k_env_reset (csrc/hmj_reset.cu), the checker of the device-side CPUEnv.reset draws
+    (cpu_env.py:135-328): the episode that pool row `rows[i]` (GLOBAL row index: N + spare row) holds in its generation
+    `gens[i]`.  Same counter-based stream, same IEEE operation order (the kernel uses __dmul_rn / __dadd_rn).  Returns
+    (params hmj_params_t[k], qpos [k][19], act_delay [k], obs_delay [k][3], act_noise [k][12], obs_noise [k][31])."""
+    rows = np.asarray(rows, dtype=np.uint64)
+    gens = np.asarray(gens, dtype=np.uint64)
+    k = rows.shape[0]
+    key = int(_splitmix64(np.uint64(seed & 0xFFFFFFFFFFFFFFFF) ^ np.uint64(0x5EED5EEDC0FFEE11)))
+
+    def u(off, count=1):
+        c = (gens * np.uint64(512))[:, None] + np.uint64(off) + np.arange(count, dtype=np.uint64)[None, :]
+        return rand_u01(key, np.broadcast_to(rows[:, None], c.shape), c)
+
+    def lerp(lo, hi, x):
+        return lo + (hi - lo) * x
+
+    def normal(off, count):
+        uu = u(off, 2 * count)
+        return np.sqrt(-2.0 * np.log(1.0 - uu[:, 0::2])) * np.cos(2.0 * np.pi * uu[:, 1::2])
+
+    p = np.repeat(base[:1], k).copy()
+    p["timestep"] = timestep
+    a = lerp(0.5, 1.0, u(_RD["FRICTION"]))
+    mult = (1.0 - rf) + a * rf
+    p["floor_friction"] = np.asarray(model["geom_friction"][0][0])[None, :] * mult
+    mass = np.tile(np.asarray(model["body_mass"][0]), (k, 1))
+    mass[:, 1:] = np.maximum(1e-5, mass[:, 1:] + lerp(-0.05 * rf, 0.05 * rf, u(_RD["MASS"], 14)))
+    eb = np.minimum(1 + (14.0 * u(_RD["EXTRA_BODY"])[:, 0]).astype(np.int64), 14)
+    mass[np.arange(k), eb] += (0.2 * rf) * u(_RD["EXTRA_MASS"])[:, 0]
+    p["body_mass"] = mass
+    arm = np.tile(np.asarray(model["dof_armature"][0]), (k, 1))
+    arm[:, 6:] += (0.0005 * u(_RD["ARMATURE"], 12)) * rf
+    p["dof_armature"] = arm
+    p["jnt_stiffness"] = np.asarray(model["jnt_stiffness"][0])[None, :]
+    margin = np.tile(np.asarray(model["jnt_margin"][0]), (k, 1))
+    margin[:, 1:] += (0.05 * u(_RD["MARGIN"], 12)) * rf
+    p["jnt_margin"] = margin
+    rng_ = np.tile(np.asarray(model["jnt_range"][0]), (k, 1, 1))
+    rng_[:, 1:, :] += (lerp(-0.1, 0.1, u(_RD["RANGE"], 24)) * rf).reshape(k, 12, 2)
+    p["jnt_range"] = rng_
+    p["act_gainprm0"] = 2.0 + lerp(-0.5, 0.5, u(_RD["GAIN"], 12)) * rf
+    p["act_forcerange"] = np.asarray(model["act_forcerange"][0])[None] + (lerp(-0.05, 0.05, u(_RD["FORCERANGE"], 24)) * rf).reshape(k, 12, 2)
+    coarse = u(_RD["HF_COARSE"], 16).reshape(k, 4, 4)
+    up = np.repeat(np.repeat(coarse, 2, axis=1), 2, axis=2)
+    pad = np.pad(up, ((0, 0), (1, 1), (1, 1)), mode="edge")
+    kk = np.array([0.25, 0.5, 0.25])
+    sm = np.zeros((k, 8, 8))
+    for i in range(3):
+        for j in range(3):
+            sm = sm + (kk[i] * kk[j]) * pad[:, i:i + 8, j:j + 8]
+    sm = sm + 0.05 * u(_RD["HF_FINE"], 64).reshape(k, 8, 8)
+    mn = sm.min(axis=(1, 2), keepdims=True)
+    span = np.maximum(sm.max(axis=(1, 2), keepdims=True) - mn, 1e-12)
+    p["hfield_data"] = ((sm - mn) / span).astype(np.float32).reshape(k, 64) * np.float32(0.1 * rf)
+    dl = np.rint(lerp(0.01 * rf, 0.05 * rf, u(_RD["DELAY"], 6)) / timestep).astype(np.int32)
+    act_delay = dl[:, 0]
+    obs_delay = np.stack([dl[:, 1], dl[:, 2], dl[:, 4]], axis=1)
+    d2r = np.pi / 180.0
+    act_noise = rf * (0.5 * d2r) * normal(_RD["N_ACT"], 12)
+    same = normal(_RD["N_SAME"], 12)
+    obs_noise = np.concatenate([rf * (2.0 * d2r) * same, rf * (5.0 * d2r) * same, rf * (2.0 * d2r) * normal(_RD["N_GYRO"], 3),
+                                rf * (5.0 * d2r) * normal(_RD["N_IMU"], 4)], axis=1)
+    qpos = np.tile(np.asarray(model["qpos0"][0], dtype=np.float64), (k, 1))
+    qpos[:, 7:] += lerp(-0.2 * rf, 0.2 * rf, u(_RD["JOINT"], 12))
+    qpos[:, 0] = 0.0
+    qpos[:, 1] = 0.0
+    qpos[:, 2] = -0.6 + (0.1 * rf) * u(_RD["Z"])[:, 0]
+    qpos[:, 3:7] = np.array(INITIAL_QUAT_STANDUP) + lerp(-0.1 * rf, 0.1 * rf, u(_RD["QUAT"], 4))
+    return p, qpos, act_delay, obs_delay, act_noise, obs_noise
+
+
 def local_gravity_host(quat: np.ndarray) -> np.ndarray:
     """inverseRotateVectors(q, (0, 0, -1)) (cpu_env.py:26-28) for rows of wxyz quaternions: Rotation.from_quat
     normalises, so this is minus the third row of R(q / |q|).  numpy mirror of `local_gravity` in csrc/hmj_aux.cu."""
@@ -227,6 +304,10 @@ class BatchedHumanoidEnv:
         self.seed = int(seed)
         self.rng = np.random.default_rng(seed)
         self.batch = HumanoidBatch(self.num_envs, device)
+        self.device_reset = self.batch.spare_rows > 0   # CPUEnv.reset on the device (episode pool); False: numpy path
+        self.auto_reset = False                         # DummyVecEnv semantics inside step() (B200VecEnv switches it on)
+        self._pool_cfg = None
+        self.last_terminal = (np.zeros(0, dtype=np.int64), np.zeros((0, 30)))
         self.io = self.batch.env_io()
         self.model = self.batch.model
         self.base_params = self.batch.default_params()
@@ -292,7 +373,38 @@ class BatchedHumanoidEnv:
         return standup_start_state(self.model["qpos0"][0], self.rng, self.randomization_factor, len(idx))
 
     # ------------------------------------------------------------------ reset (cpu_env.py:374-416)
+    def _pool_settings(self):
+        return (bool(self.auto_reset), self.randomization_factor, self.max_simulation_time, self.seed, self.timestep)
+
+    def _configure_pool(self):
+        cur = self._pool_settings()
+        if cur != self._pool_cfg:
+            self.batch.env_pool_config(*cur)
+            self._pool_cfg = cur
+
     def reset(self, seed=None, options=None, env_ids=None):
+        """CPUEnv.reset for all envs (or `env_ids`).  With `device_reset` (default) the domain randomisation, delays, noise
+        vectors, start pose, probe step and the rejection loop run on the device (episode pool, csrc/hmj_reset.cu): no
+        bystander is touched and nothing but the new observations crosses the bus.  `reset_host` is the numpy path with
+        full state round trips, kept as the checker."""
+        if not self.device_reset:
+            return self.reset_host(seed, options, env_ids)
+        if seed is not None:
+            self.seed = int(seed)
+            self.rng = np.random.default_rng(seed)
+        self._configure_pool()
+        ids = None if env_ids is None else np.asarray(env_ids, dtype=np.int32)
+        self.batch.env_reset(ids)
+        io = self.io
+        self.time = io["time"]
+        self.torso_quat = io["torso_quat"]
+        if ids is None:
+            self.previous_reward[:] = 0.0
+            return io["obs"].copy(), {}
+        self.previous_reward[ids] = 0.0
+        return io["obs"][ids].copy(), {}
+
+    def reset_host(self, seed=None, options=None, env_ids=None):
         if seed is not None:
             self.seed = int(seed)
             self.rng = np.random.default_rng(seed)
@@ -375,10 +487,27 @@ class BatchedHumanoidEnv:
     def step(self, action=None):
         """One control step of every environment.  Returns views of the pinned result block (valid until the next
         call): obs [N][30], reward [N], terminated [N], truncated [N], infos (a sequence of N dicts, `is_success` on episode end: SparseInfos)."""
+        if self.device_reset:
+            self._configure_pool()
         obs, reward, term, trunc, _ = self._step_device(action, only=None)
         if term is self._all_false and trunc is self._all_false:
             return obs, reward, term, trunc, self._no_infos      # nothing ended: shared (read-only) flags and infos
-        ended = {int(i): {"is_success": bool(trunc[i])} for i in np.nonzero(term | trunc)[0]}
+        ids = np.nonzero(term | trunc)[0]
+        ended = {int(i): {"is_success": bool(trunc[i])} for i in ids}
+        if self.auto_reset and self.device_reset:
+            # the ended envs already run their next episode (obs rows = its first observation); the terminal
+            # observations come back in the pool's result block (first 64) or are fetched (a mass ending)
+            rio = self.batch.env_reset_io()
+            cnt = int(rio["counts"][0])
+            if cnt <= 64:
+                tid, tobs = rio["ended_ids"][:cnt].astype(np.int64), rio["term_obs"][:cnt].copy()
+            else:
+                n = self.num_envs
+                tid = self.batch.get_raw("env_ended_ids_compact", np.int32, (n,)).astype(np.int64)[:cnt]
+                tobs = self.batch.get_raw("env_terminal_obs_compact", np.float64, (n, 30))[:cnt]
+            self.last_terminal = (tid, tobs)
+            if self.use_potential_rewards:
+                self.previous_reward[ids] = 0.0
         return obs, reward, term, trunc, SparseInfos(self.num_envs, ended)
 
     def _step_device(self, action, only):

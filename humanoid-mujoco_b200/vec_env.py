@@ -36,6 +36,7 @@ class B200VecEnv:
                                       max_simulation_time_override=max_simulation_time_override,
                                       reward_override=reward_override, device=device, seed=seed)
         self.num_envs = int(n_envs)
+        self.env.auto_reset = self.env.device_reset   # auto-reset inside the device step (episode pool)
         self.observation_space = _box(-10.0, 10.0, (30,))
         self.action_space = _box(-1.0, 1.0, (12,))
         self._actions = None
@@ -60,13 +61,22 @@ class B200VecEnv:
         infos = [self._running_info] * self.num_envs
         ended = np.nonzero(dones)[0]
         if len(ended):
-            for i in ended:
-                d = dict(raw[i])
-                d["TimeLimit.truncated"] = bool(trunc[i] and not term[i])
-                d["terminal_observation"] = obs[i].copy()
-                infos[i] = d
-            new_obs, _ = self.env.reset(env_ids=ended)
-            obs[ended] = new_obs
+            if self.env.auto_reset:   # the device already swapped in the next episodes: obs rows are their first observations
+                tid, tobs = self.env.last_terminal
+                where = {int(e): k for k, e in enumerate(tid)}
+                for i in ended:
+                    d = dict(raw[i])
+                    d["TimeLimit.truncated"] = bool(trunc[i] and not term[i])
+                    d["terminal_observation"] = tobs[where[int(i)]].copy()
+                    infos[i] = d
+            else:
+                for i in ended:
+                    d = dict(raw[i])
+                    d["TimeLimit.truncated"] = bool(trunc[i] and not term[i])
+                    d["terminal_observation"] = obs[i].copy()
+                    infos[i] = d
+                new_obs, _ = self.env.reset(env_ids=ended)
+                obs[ended] = new_obs
         return obs, reward, dones, infos
 
     def step(self, actions):

@@ -125,6 +125,20 @@ int hmj_env_step_fused(hmj_batch_t* b, int has_action, int has_mask, double rf, 
  * by the CUDA driver.  The array must stay valid until the call returns (it synchronises). */
 int hmj_env_step_fused_from(hmj_batch_t* b, const double* action_host, int has_mask, double rf, double max_sim_time,
                             unsigned long long seed, int nsteps);
+/* ---- CPUEnv.reset (cpu_env.py:374-416) and DummyVecEnv's auto-reset (rl/train.py:134-151) ON THE DEVICE.
+ * A batch owns S spare rows behind its N envs (hmj_batch_spare_rows; N/8 clamped to [32, 1024]).  Fresh episodes —
+ * domain randomisation of the model (:189-280), delays (:135-187), constant noise vectors, start pose (:282-328), the
+ * probe step with action None and the reference's rejection rule (:411-414: first-step contact / terminated /
+ * truncated -> draw again) — are generated into the spare rows in the background on a side stream, from the
+ * counter-based stream (seed, row, generation).  hmj_env_pool_config(enable=1, ...) makes hmj_env_step_fused[_from]
+ * replace every env whose episode ended (terminated | truncated) with a ready episode inside the same call: its obs /
+ * time / torso_quat rows then hold the FIRST observation of the new episode (reward and flags stay the ended
+ * episode's), and the terminal observations come back through hmj_env_reset_io.  No bystander env is stepped or
+ * copied.  hmj_env_reset resets the listed envs now (ids == NULL: all) and blocks until every one is served. */
+int hmj_env_pool_config(hmj_batch_t* b, int enable, double rf, double max_sim_time, unsigned long long seed, double timestep);
+int hmj_env_reset(hmj_batch_t* b, const int32_t* ids, int count);
+int hmj_env_reset_io(hmj_batch_t* b, int32_t** counts, int32_t** ended_ids, double** term_obs);
+int hmj_batch_spare_rows(const hmj_batch_t* b);
 /* Page-locked host memory for step inputs (cudaHostAlloc / cudaFreeHost). */
 int hmj_pinned_alloc(size_t bytes, void** out);
 int hmj_pinned_free(void* p);
