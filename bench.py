@@ -342,6 +342,100 @@ def plan_bench(local, rank, world, iters, cpu):
         pl.batch.close()
     return out
 
+# ---------------------------------------------------------------------------------------------- C5 / C1 (BASELINE.json configs[4], [0])
+def c5_bench(local, rank, world, steps, barrier, max_over_ranks):
+    """rl/train.py rollout collection (rl/train.py:134-151): 16384 envs in total (STRONG scaling: 16384 / world per GPU),
+    rf = 0 (RANDOMIZATION_FACTOR_INIT), random actions, DummyVecEnv semantics with the auto-reset inside the timed region.
+    Two numbers: `BatchedHumanoidEnv.step` with auto_reset (the C-ABI call: host actions in, obs/reward/flags out) and
+    `B200VecEnv.step` (adds SB3's per-step copies and info dicts).  Plus the auto-reset cost itself: the same envs with a
+    0.2 s time limit and staggered clocks, so that ~1 % of the envs end in EVERY step, against the run where none ends."""
+    import humanoid_mujoco_b200 as hmj
+    total = 16384
+    n = total // world
+    out = {"envs_total": total, "envs_per_gpu": n, "steps": steps, "scaling": "strong", "randomization_factor": 0.0}
+    acts = hmj.pinned_empty((16, n, 12))
+    acts[...] = np.random.default_rng(40 + rank).uniform(-1, 1, acts.shape)
+    v = hmj.B200VecEnv(n, randomization_factor=0.0, device=local, seed=20 + rank)
+    t0 = time.perf_counter()
+    v.reset()
+    out["reset_all_ms"] = 1e3 * max_over_ranks(time.perf_counter() - t0)
+    env = v.env
+    for s in range(10):
+        env.step(acts[s % 16])
+    barrier()
+    ended = 0
+    t0 = time.perf_counter()
+    for s in range(steps):
+        _o, _r, term, trunc, _i = env.step(acts[s % 16])
+        if term is not env._all_false or trunc is not env._all_false:
+            ended += int((term | trunc).sum())
+    env.batch.sync()
+    dt = max_over_ranks(time.perf_counter() - t0)
+    out.update({"value": total * steps / dt, "unit": UNIT, "ms_per_step": 1e3 * dt / steps, "episodes_ended_rank0": ended,
+                "api": "BatchedHumanoidEnv.step, auto_reset on (episode pool on the device)"})
+    vsteps = max(50, steps // 5)
+    barrier()
+    t0 = time.perf_counter()
+    for s in range(vsteps):
+        v.step(acts[s % 16])
+    dt = max_over_ranks(time.perf_counter() - t0)
+    out["vecenv"] = {"value": total * vsteps / dt, "unit": UNIT, "ms_per_step": 1e3 * dt / vsteps, "steps": vsteps,
+                     "api": "B200VecEnv.step (DummyVecEnv contract: copies of obs/reward, dones, infos)"}
+    v.close()
+    # ---- what an auto-reset costs: ~1 % of the envs end every step vs nobody ends
+    res = {}
+    for name, limit in (("none_ending", None), ("one_percent_ending_per_step", 0.2)):
+        e = hmj.BatchedHumanoidEnv(n, randomization_factor=0.0, max_simulation_time_override=limit, device=local, seed=20 + rank)
+        e.auto_reset = True
+        e.reset()
+        if limit is not None:   # stagger the clocks over one episode length (100 steps): n / 100 envs time out per step
+            t = e.batch.get("time")
+            t += (np.arange(n) % 100) * 0.002
+            e.batch.set("time", t)
+        for s in range(120):
+            e.step(acts[s % 16])
+        barrier()
+        k, cnt = 200, 0
+        t0 = time.perf_counter()
+        for s in range(k):
+            _o, _r, term, trunc, _i = e.step(acts[s % 16])
+            if term is not e._all_false:
+                cnt += int(term.sum())
+        e.batch.sync()
+        dt = max_over_ranks(time.perf_counter() - t0)
+        res[name] = {"ms_per_step": 1e3 * dt / k, "endings_per_step_rank0": cnt / k}
+        e.close()
+    res["overhead_frac"] = res["one_percent_ending_per_step"]["ms_per_step"] / res["none_ending"]["ms_per_step"] - 1.0
+    out["autoreset_cost"] = res
+    return out
+
+
+def c1_bench(local, cpu):
+    """simulation/benchmark.py:28-55: ONE env (rf = 1) behind DummyVecEnv, 1000 random-action steps, seconds per step."""
+    import humanoid_mujoco_b200 as hmj
+    v = hmj.B200VecEnv(1, randomization_factor=1.0, device=local, seed=3)
+    v.reset()
+    rng = np.random.default_rng(0)
+    acts = rng.uniform(-1, 1, (1000, 1, 12))
+    for s in range(20):
+        v.step(acts[s])
+    t0 = time.perf_counter()
+    for s in range(1000):
+        v.step(acts[s])
+    dt = time.perf_counter() - t0
+    out = {"steps": 1000, "seconds_per_step": dt / 1000, "value": 1000 / dt, "unit": UNIT,
+           "api": "B200VecEnv(1).step — one env is one warp: the GPU path is latency-bound here by construction"}
+    if cpu:
+        e = v.env
+        q, vel, _t, ws = e.batch.get_state()
+        value, st, _ = cpu_steps_per_s(e.batch.get_params()[:1], q[:1], vel[:1], ws[:1], acts[:64, :1], 1000, 20, 1)
+        out["cpu_baseline"] = {"value": value, "unit": UNIT, "cores": 1, "kind": "port", "seconds_per_step": 1.0 / value,
+                               "sample": "the same env (DR params and state after the warm-up), 1000 mj_steps on one thread; the "
+                                         "reference adds CPUEnv's Python/JAX per-step work on top of mj_step"}
+    v.close()
+    return out
+
+
 # ---------------------------------------------------------------------------------------------- GPU arm
 def run_gpu(args):
     import torch
@@ -546,6 +640,11 @@ def run_gpu(args):
             line["cpu_baseline"] = main["cpu_baseline"]
             line["fp64"] = main["fp64"]
     env.close()
+    if not args.no_c5:
+        c5 = c5_bench(local, rank, world, args.c5_steps, barrier, max_over_ranks)
+        if rank == 0:
+            line["c5"] = c5
+            line["c1"] = c1_bench(local, cpu=(world == 1 and not args.no_cpu))
     if not args.no_plan:
         plan = plan_bench(local, rank, world, args.plan_iters, cpu=(world == 1 and not args.no_cpu))
         if rank == 0:
@@ -569,6 +668,8 @@ def main():
     ap.add_argument("--cpu-steps", type=int, default=300, help="steps per env of the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-plan", action="store_true", help="skip the planner (M2) measurement")
+    ap.add_argument("--no-c5", action="store_true", help="skip the C5 (16384-env rollout collection, strong scaling) and C1 legs")
+    ap.add_argument("--c5-steps", type=int, default=1000)
     ap.add_argument("--plan-iters", type=int, default=20, help="timed planner iterations of the C4 slice (C2 runs 5x as many)")
     args = ap.parse_args()
     if args.impl == "reference":

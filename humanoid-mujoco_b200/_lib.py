@@ -75,6 +75,8 @@ def load_library() -> C.CDLL:
     lib.hmj_env_reset.argtypes = [vp, vp, C.c_int]
     lib.hmj_env_reset_io.argtypes = [vp] + [C.POINTER(vp)] * 3
     lib.hmj_batch_spare_rows.argtypes = [vp]
+    lib.hmj_env_terminal.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(C.c_int32)]
+    lib.hmj_env_pool_stats.argtypes = [vp, vp]
     lib.hmj_plan_iterate.argtypes = [vp, dp, C.c_double, dp, dp, C.c_int, C.c_int, C.c_int, dp, C.c_double, C.c_double,
                                      C.c_ulonglong, C.c_ulonglong, C.c_int, vp]
     lib.hmj_plan_record_size.argtypes = [C.c_int]

@@ -291,6 +291,17 @@ class HumanoidBatch:
             a = np.ascontiguousarray(ids, dtype=np.int32)
             check(self.lib.hmj_env_reset(self._h, a.ctypes.data, int(a.size)))
 
+    def env_terminal(self):
+        """(env ids, terminal observations [count][30]) of the episodes that ended in the last pooled step (copies)."""
+        ids, obs, cnt = C.c_void_p(), C.c_void_p(), C.c_int32(0)
+        check(self.lib.hmj_env_terminal(self._h, C.byref(ids), C.byref(obs), C.byref(cnt)))
+        k = cnt.value
+        if k == 0:
+            return np.zeros(0, dtype=np.int64), np.zeros((0, 30))
+        i = np.ctypeslib.as_array((C.c_int32 * k).from_address(ids.value)).astype(np.int64)
+        o = np.ctypeslib.as_array((C.c_double * (k * 30)).from_address(obs.value)).reshape(k, 30).copy()
+        return i, o
+
     def env_reset_io(self):
         """Views of the pool's per-step result block: counts[8], ended_ids[64], term_obs[64][30] (hmj_env_reset_io)."""
         if getattr(self, "_rio", None) is None:

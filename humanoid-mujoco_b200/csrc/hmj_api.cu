@@ -84,6 +84,8 @@ struct hmj_batch_ {
   long long step_idx = 0, round_start = 0;
   double pool_rf = 0, pool_max_sim_time = 0, pool_timestep = 0.002;
   unsigned long long pool_seed = 0;
+  long long pool_rounds = 0, pool_drains = 0, pool_drain_iters = 0;
+  char* term_host = nullptr;         // pinned: terminal observations [N][30] f64 | env ids [N] i32 of a step with more than 64 endings
   size_t io_ext_offset = 0;          // byte offset of the pool's result block inside the IO out block
   hmj_solve_ctx_t solve_ctx{};       // side streams + events that overlap the solver classes
   // Pipes: the physics chain of a step (smooth -> collide -> solve) is enqueued once per contiguous block of envs, each on
@@ -356,6 +358,7 @@ extern "C" void hmj_batch_destroy(hmj_batch_t* b) {
   for (cudaEvent_t e : b->prof_events) cudaEventDestroy(e);
   if (b->io_host) cudaFreeHost(b->io_host);
   if (b->plan_stage) cudaFreeHost(b->plan_stage);
+  if (b->term_host) cudaFreeHost(b->term_host);
   for (auto& kv : b->rollout_graphs) cudaGraphExecDestroy(kv.second);
   if (b->tab_dev) cudaFree(b->tab_dev);
   if (b->task_dev) cudaFree(b->task_dev);
@@ -528,6 +531,8 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
       PALLOC(ended_ids_full, NE); PALLOC(term_obs_full, NE * 30);
 #undef PALLOC
       if (!rc) rc = alloc_array(b, "env_episode_src", &P.episode_src, N);
+      if (!rc && cudaHostAlloc((void**)&b->term_host, NE * (30 * 8 + 4), cudaHostAllocDefault) != cudaSuccess)
+        rc = fail(HMJ_ERR_CUDA, "cudaHostAlloc failed%s");
       if (!rc) {
         char* ext = b->io_dev + b->io_in_bytes + b->io_ext_offset;
         P.counts = (int32_t*)ext;
@@ -537,12 +542,16 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
         b->arrays["env_ended_ids_compact"] = ArrayInfo{P.ended_ids_full, NE * 4};
         b->arrays["pool_state"] = ArrayInfo{P.state, S * 4};
       }
-      if (!rc && (cudaStreamCreateWithFlags(&b->spare_stream, cudaStreamNonBlocking) != cudaSuccess ||
+      // highest stream priority: a round is a chain of ~15 small kernels that must get SM slots ahead of the main batch's
+      // large grids, or its latency under load (not its work) would stall the step that joins it
+      int prio_lo = 0, prio_hi = 0;
+      cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+      if (!rc && (cudaStreamCreateWithPriority(&b->spare_stream, cudaStreamNonBlocking, prio_hi) != cudaSuccess ||
                   cudaEventCreateWithFlags(&b->ev_main, cudaEventDisableTiming) != cudaSuccess ||
                   cudaEventCreateWithFlags(&b->round_done, cudaEventDisableTiming) != cudaSuccess))
         rc = fail(HMJ_ERR_CUDA, "stream/event creation failed%s");
       for (int k = 0; k < 2 && !rc; k++)
-        if (cudaStreamCreateWithFlags(&b->spare_ctx.side[k], cudaStreamNonBlocking) != cudaSuccess ||
+        if (cudaStreamCreateWithPriority(&b->spare_ctx.side[k], cudaStreamNonBlocking, prio_hi) != cudaSuccess ||
             cudaEventCreateWithFlags(&b->spare_ctx.join[k], cudaEventDisableTiming) != cudaSuccess)
           rc = fail(HMJ_ERR_CUDA, "stream/event creation failed%s");
       if (!rc && (cudaEventCreateWithFlags(&b->spare_ctx.fork, cudaEventDisableTiming) != cudaSuccess ||
@@ -1039,6 +1048,12 @@ extern "C" int hmj_env_step_fused_from(hmj_batch_t* b, const double* action_host
   if (pool) {
     int32_t* counts = io_counts_host(b);
     b->pool_need_round = counts[6] > 0;
+    if (counts[0] > HMJ_POOL_MAXTERM) {   // more endings than the result block carries: fetch exactly those rows
+      const size_t cnt = (size_t)counts[0];
+      CK(cudaMemcpyAsync(b->term_host, b->pool.term_obs_full, cnt * 30 * 8, cudaMemcpyDeviceToHost, b->stream));
+      CK(cudaMemcpyAsync(b->term_host + N * 30 * 8, b->pool.ended_ids_full, cnt * 4, cudaMemcpyDeviceToHost, b->stream));
+      CK(cudaStreamSynchronize(b->stream));
+    }
     if (counts[2] > 0) {   // more episodes ended than the pool held: serve the rest now, then refresh their result rows
       const int32_t needed = counts[0], ended_now = counts[4];
       int rc = pool_drain(b);
@@ -1115,6 +1130,7 @@ static int launch_round(hmj_batch_t* b) {
     b->host_launches += 1;
   }
   CK(cudaEventRecord(b->round_done, b->spare_stream));
+  b->pool_rounds++;
   b->round_inflight = true;
   b->round_start = b->step_idx;
   return HMJ_OK;
@@ -1150,7 +1166,9 @@ static int pool_step(hmj_batch_t* b, const int32_t* term, const int32_t* trunc, 
 // curriculum's reset-everything, a mass time-out): generation rounds back to back, blocking.
 static int pool_drain(hmj_batch_t* b) {
   int32_t* counts = io_counts_host(b);
+  b->pool_drains++;
   for (int it = 0; it < 100000; it++) {
+    b->pool_drain_iters++;
     int rc = pool_step(b, nullptr, nullptr, true);
     if (rc) return rc;
     CK(cudaMemcpyAsync(counts, b->pool.counts, 8 * sizeof(int32_t), cudaMemcpyDeviceToHost, b->stream));
@@ -1223,7 +1241,25 @@ extern "C" int hmj_env_reset_io(hmj_batch_t* b, int32_t** counts, int32_t** ende
   if (term_obs) *term_obs = (double*)(ext + 8 * 4 + HMJ_POOL_MAXTERM * 4);
   return HMJ_OK;
 }
+/* The envs that ended in the last pooled control step (env order) and their terminal observations: `count` entries
+ * (pinned host memory, valid until the next step). */
+extern "C" int hmj_env_terminal(hmj_batch_t* b, int32_t** ids, double** obs, int32_t* count) {
+  if (!b || !b->io_host || !b->term_host) return fail(HMJ_ERR_ARG, "no episode pool%s");
+  const int32_t* counts = io_counts_host(b);
+  char* ext = b->io_host + b->io_in_bytes + b->io_ext_offset;
+  const bool big = counts[0] > HMJ_POOL_MAXTERM;
+  if (ids) *ids = big ? (int32_t*)(b->term_host + (size_t)b->n * 30 * 8) : (int32_t*)ext + 8;
+  if (obs) *obs = big ? (double*)b->term_host : (double*)(ext + 8 * 4 + HMJ_POOL_MAXTERM * 4);
+  if (count) *count = counts[0];
+  return HMJ_OK;
+}
 extern "C" int hmj_batch_spare_rows(const hmj_batch_t* b) { return b ? b->n_spare : 0; }
+/* host-side counters of the pool: generation rounds launched, blocking drains, drain iterations, control steps */
+extern "C" int hmj_env_pool_stats(const hmj_batch_t* b, long long* out4) {
+  if (!b || !out4) return fail(HMJ_ERR_ARG, "null argument%s");
+  out4[0] = b->pool_rounds; out4[1] = b->pool_drains; out4[2] = b->pool_drain_iters; out4[3] = b->step_idx;
+  return HMJ_OK;
+}
 
 // ------------------------------------------------------------------ planner
 extern "C" int hmj_plan_set_task(hmj_batch_t* b, int nterm, const int32_t* dim, const int32_t* norm, const double* weight,

@@ -258,15 +258,21 @@ def standup_reward_host(qvel, root_quat, root_z, joint_torques, prev_action, lat
 
 class SparseInfos(Sequence):
     """The per-env `info` dicts of one batched step as a read-only sequence of length N: only the envs whose episode
-    ended carry an entry, everyone else shares one empty dict (building N dicts per step would cost more host time
-    than the device step saves at 4096 envs)."""
+    ended carry an entry (`is_success`), built when somebody looks at it; everyone else shares one empty dict (building
+    N dicts per step would cost more host time than the device step saves at 4096 envs)."""
 
-    __slots__ = ("_n", "_entries")
+    __slots__ = ("_n", "_ids", "_success", "_entries")
     _EMPTY: dict = {}
 
-    def __init__(self, n, entries):
+    def __init__(self, n, entries=None, ids=None, success=None):
         self._n = int(n)
         self._entries = entries
+        self._ids, self._success = ids, success
+
+    def _build(self):
+        if self._entries is None:
+            self._entries = {int(i): {"is_success": bool(s)} for i, s in zip(self._ids, self._success)}
+        return self._entries
 
     def __len__(self):
         return self._n
@@ -279,7 +285,7 @@ class SparseInfos(Sequence):
             i += self._n
         if not 0 <= i < self._n:
             raise IndexError(i)
-        return self._entries.get(i, self._EMPTY)
+        return self._build().get(i, self._EMPTY)
 
 
 class BatchedHumanoidEnv:
@@ -493,22 +499,15 @@ class BatchedHumanoidEnv:
         if term is self._all_false and trunc is self._all_false:
             return obs, reward, term, trunc, self._no_infos      # nothing ended: shared (read-only) flags and infos
         ids = np.nonzero(term | trunc)[0]
-        ended = {int(i): {"is_success": bool(trunc[i])} for i in ids}
+        infos = SparseInfos(self.num_envs, ids=ids, success=trunc[ids])
         if self.auto_reset and self.device_reset:
             # the ended envs already run their next episode (obs rows = its first observation); the terminal
             # observations come back in the pool's result block (first 64) or are fetched (a mass ending)
-            rio = self.batch.env_reset_io()
-            cnt = int(rio["counts"][0])
-            if cnt <= 64:
-                tid, tobs = rio["ended_ids"][:cnt].astype(np.int64), rio["term_obs"][:cnt].copy()
-            else:
-                n = self.num_envs
-                tid = self.batch.get_raw("env_ended_ids_compact", np.int32, (n,)).astype(np.int64)[:cnt]
-                tobs = self.batch.get_raw("env_terminal_obs_compact", np.float64, (n, 30))[:cnt]
+            tid, tobs = self.batch.env_terminal()
             self.last_terminal = (tid, tobs)
             if self.use_potential_rewards:
                 self.previous_reward[ids] = 0.0
-        return obs, reward, term, trunc, SparseInfos(self.num_envs, ended)
+        return obs, reward, term, trunc, infos
 
     def _step_device(self, action, only):
         io = self.io

@@ -138,7 +138,12 @@ int hmj_env_step_fused_from(hmj_batch_t* b, const double* action_host, int has_m
 int hmj_env_pool_config(hmj_batch_t* b, int enable, double rf, double max_sim_time, unsigned long long seed, double timestep);
 int hmj_env_reset(hmj_batch_t* b, const int32_t* ids, int count);
 int hmj_env_reset_io(hmj_batch_t* b, int32_t** counts, int32_t** ended_ids, double** term_obs);
+/* the envs that ended in the last pooled control step (env order) + their terminal observations [count][30]; pinned
+ * host memory owned by the batch, valid until the next step */
+int hmj_env_terminal(hmj_batch_t* b, int32_t** ids, double** obs, int32_t* count);
 int hmj_batch_spare_rows(const hmj_batch_t* b);
+/* host-side counters: generation rounds launched, blocking drains, drain iterations, pooled control steps */
+int hmj_env_pool_stats(const hmj_batch_t* b, long long* out4);
 /* Page-locked host memory for step inputs (cudaHostAlloc / cudaFreeHost). */
 int hmj_pinned_alloc(size_t bytes, void** out);
 int hmj_pinned_free(void* p);
