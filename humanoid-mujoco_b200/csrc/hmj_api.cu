@@ -305,9 +305,10 @@ static hmj_buffers_t pipe_view(const hmj_buffers_t& B, int start, int count, int
   V.qpos += s * HMJ_NQ; V.qvel += s * HMJ_NV; V.time += s; V.warmstart += s * HMJ_NV; V.ctrl += s * HMJ_NU;
   V.xfrc += s * 6; V.xfrc_body += s; V.params += s;
   V.geom_xpos += s * HMJ_NGEOM * 3; V.geom_xmat += s * HMJ_NGEOM * 9; V.cdof += s * HMJ_NV * 6; V.com += s * 3;
+  V.xipos += s * HMJ_NBODY * 3; V.ximat += s * HMJ_NBODY * 9;
   V.qM += s * HMJ_NM; V.qfrc_smooth += s * HMJ_NV; V.euler_factor += s * HMJ_FAC_DOUBLES; V.sens += s * SENS_NUM; V.slots += s * HMJ_NSLOT * HMJ_SLOT_DOUBLES; V.slot_mask += s * 4;
   V.wq_count += 64 * pipe; V.wq_task += s * group_total;
-  V.solve_count += 4 * pipe; V.solve_list += 3 * s;
+  V.solve_count += 4 * pipe; V.solve_list += 4 * s;
   V.qacc += s * HMJ_NV; V.qacc_smooth += s * HMJ_NV; V.qfrc_constraint += s * HMJ_NV; V.contact += s * HMJ_MAXCON;
   V.ncon += s; V.nefc += s; V.niter += s; V.status += s;
   V.residual += s * HMJ_NRESIDUAL; V.cost_sum += s; V.cost_last += s; V.trace += s * 3;
@@ -458,6 +459,8 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
   ALLOC("geom_xmat", geom_xmat, N * HMJ_NGEOM * 9);
   ALLOC("cdof", cdof, N * HMJ_NV * 6);
   ALLOC("com", com, N * 3);
+  ALLOC("xipos", xipos, N * HMJ_NBODY * 3);
+  ALLOC("ximat", ximat, N * HMJ_NBODY * 9);
   ALLOC("qM", qM, N * HMJ_NM);
   ALLOC("qfrc_smooth", qfrc_smooth, N * HMJ_NV);
   ALLOC("euler_factor", euler_factor, N * HMJ_FAC_DOUBLES);
@@ -467,7 +470,7 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
   ALLOC_FLAT("wq_count", wq_count, 64 * (HMJ_MAX_PIPES + 1));
   ALLOC("wq_task", wq_task, N * (size_t)b->tab_host->group_base[HMJ_NGROUP]);
   ALLOC_FLAT("solve_count", solve_count, 4 * (HMJ_MAX_PIPES + 1));
-  ALLOC("solve_list", solve_list, 3 * N);
+  ALLOC("solve_list", solve_list, 4 * N);
   ALLOC("qacc", qacc, N * HMJ_NV);
   ALLOC("qacc_smooth", qacc_smooth, N * HMJ_NV);
   ALLOC("qfrc_constraint", qfrc_constraint, N * HMJ_NV);
@@ -689,21 +692,21 @@ static cudaEvent_t prof_event(hmj_batch_t* b) {
 static void enqueue_step(hmj_batch_t* b, int integrate) {
   const bool prof = b->profile;
   if (prof) prof_event(b);
-  hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, b->stream);
+  hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, b->stream, &b->solve_ctx);
   if (prof) prof_event(b);
   hmj_launch_factor(b->tab_dev, b->buf, b->stream, &b->solve_ctx);
   hmj_launch_collide(b->tab_dev, b->buf, b->stream);
   if (prof) prof_event(b);
   hmj_launch_solve(b->tab_dev, b->buf, integrate, b->stream, &b->solve_ctx);
   if (prof) prof_event(b);
-  b->launches += 8; b->host_launches += 8;  // smooth, factor, broad, narrow, classify, solve x 3 classes
+  b->launches += 10; b->host_launches += 10;  // kin, dyn, factor, broad, narrow, classify, solve x 4 classes
 }
 
 // The launches of ONE physics step of the whole batch, on the main stream (forking pipes / side streams and joining
 // them back before returning): this is what gets captured into the step graph.
 static void enqueue_one_step(hmj_batch_t* b, int integrate) {
   if (b->pipes.empty()) {
-    hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, b->stream);
+    hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, b->stream, &b->solve_ctx);
     hmj_launch_factor(b->tab_dev, b->buf, b->stream, &b->solve_ctx);
     hmj_launch_collide(b->tab_dev, b->buf, b->stream, false);
     hmj_launch_solve(b->tab_dev, b->buf, integrate, b->stream, &b->solve_ctx, false);
@@ -711,7 +714,7 @@ static void enqueue_one_step(hmj_batch_t* b, int integrate) {
   }
   cudaEventRecord(b->pipe_fork, b->stream);
   for (auto& pp : b->pipes) cudaStreamWaitEvent(pp.stream, b->pipe_fork, 0);
-  for (auto& pp : b->pipes) hmj_launch_smooth(b->tab_dev, pp.view, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, pp.stream);
+  for (auto& pp : b->pipes) hmj_launch_smooth(b->tab_dev, pp.view, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, pp.stream, &pp.ctx);
   for (auto& pp : b->pipes) hmj_launch_factor(b->tab_dev, pp.view, pp.stream, &pp.ctx);
   for (auto& pp : b->pipes) hmj_launch_collide(b->tab_dev, pp.view, pp.stream, false);
   for (auto& pp : b->pipes) hmj_launch_solve(b->tab_dev, pp.view, integrate, pp.stream, &pp.ctx, false);
@@ -731,7 +734,7 @@ static void enqueue_steps(hmj_batch_t* b, int integrate, int nsteps) {
     for (int s = 0; s < nsteps; s++) enqueue_step(b, integrate);
     return;
   }
-  const int per_step = 8 * (b->pipes.empty() ? 1 : (int)b->pipes.size());
+  const int per_step = 10 * (b->pipes.empty() ? 1 : (int)b->pipes.size());
   const int f = integrate ? 1 : 0;
   for (int s = 0; s < nsteps; s++) {
     b->launches += per_step;
@@ -1095,7 +1098,7 @@ static void enqueue_round_chain(hmj_batch_t* b) {
   const hmj_envstate_t& E = b->env_spare;
   hmj_launch_env_reset(b->tab_dev, V, E, b->pool, b->pool_rf, b->pool_timestep, b->pool_seed, b->n, s);
   hmj_launch_env_pre(V, E, nullptr, b->pool.active, b->pool_rf, b->pool_seed, s, b->n);
-  hmj_launch_smooth(b->tab_dev, V, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, s);
+  hmj_launch_smooth(b->tab_dev, V, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, s, &b->spare_ctx);
   hmj_launch_factor(b->tab_dev, V, s, &b->spare_ctx);
   hmj_launch_collide(b->tab_dev, V, s, false);
   hmj_launch_solve(b->tab_dev, V, 1, s, &b->spare_ctx, false);
@@ -1111,11 +1114,11 @@ static void enqueue_round_chain(hmj_batch_t* b) {
 static int launch_round(hmj_batch_t* b) {
   CK(cudaEventRecord(b->ev_main, b->stream));
   CK(cudaStreamWaitEvent(b->spare_stream, b->ev_main, 0));
-  b->launches += 15;
+  b->launches += 17;
   if (b->graph_mode == 0 || !b->warmed) {
     enqueue_round_chain(b);
     b->warmed = true;
-    b->host_launches += 15;
+    b->host_launches += 17;
   } else {
     if (!b->round_graph) {
       cudaGraph_t g = nullptr;
@@ -1315,8 +1318,9 @@ static void enqueue_rollout_chain(hmj_batch_t* b, const double* values_dev, int 
   hmj_launch_plan_init(b->buf, b->state_dev, b->stream);
   for (int t = 0; t < horizon - 1; t++) {
     hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, HMJ_PLAN_COST | HMJ_PLAN_POLICY, b->spline_times_dev, values_dev, nnode,
-                      interpolation, 1, b->stream);
-    if (record) hmj_launch_plan_record(b->buf, b->rec, t, b->stream);
+                      interpolation, 1, b->stream, &b->solve_ctx);
+    // the knot is recorded behind k_dyn (residual, cost) on the side stream; k_solve joins that stream before it moves the state
+    if (record) hmj_launch_plan_record(b->buf, b->rec, t, b->solve_ctx.side[0]);
     hmj_launch_factor(b->tab_dev, b->buf, b->stream, &b->solve_ctx);
     hmj_launch_collide(b->tab_dev, b->buf, b->stream, false);
     hmj_launch_solve(b->tab_dev, b->buf, 1, b->stream, &b->solve_ctx, false);
@@ -1332,11 +1336,11 @@ static void enqueue_rollout_chain(hmj_batch_t* b, const double* values_dev, int 
 // otherwise be ~1500 API calls per iteration.
 static int launch_rollouts(hmj_batch_t* b, const double* values_dev, int nnode, int interpolation, int horizon, int record,
                            double* returns_dev, int32_t* failure_dev) {
-  b->launches += 1 + (horizon - 1) * (8 + (record ? 1 : 0)) + 1 + (record ? 1 : 0) + 1;
+  b->launches += 1 + (horizon - 1) * (10 + (record ? 1 : 0)) + 2 + (record ? 1 : 0) + 1;
   if (b->graph_mode == 0 || !b->warmed) {   // first use of the launchers performs their one-time attribute queries
     enqueue_rollout_chain(b, values_dev, nnode, interpolation, horizon, record, returns_dev, failure_dev);
     b->warmed = true;
-    b->host_launches += 1 + (horizon - 1) * (8 + (record ? 1 : 0)) + 1 + (record ? 1 : 0) + 1;
+    b->host_launches += 1 + (horizon - 1) * (10 + (record ? 1 : 0)) + 2 + (record ? 1 : 0) + 1;
     CK(cudaGetLastError());
     return HMJ_OK;
   }

@@ -97,6 +97,8 @@ struct hmj_buffers_t {
   double* geom_xmat;  // [N][10][9]
   double* cdof;       // [N][18][6]
   double* com;        // [N][3]     subtree_com of the root body
+  double* xipos;      // [N][15][3] inertial frames, k_kin -> k_dyn
+  double* ximat;      // [N][15][9]
   double* qM;         // [N][117]
   double* qfrc_smooth;// [N][18]
   double* euler_factor; // [N][192]   Cholesky factor of M + h diag(damping): lower triangle, reciprocal diagonal
@@ -106,7 +108,7 @@ struct hmj_buffers_t {
   int32_t* wq_count;  // [64]       narrowphase tasks per group (zeroed every step)
   int2* wq_task;      // [group_base[NGROUP] * N]  (env, packed pair / slot ordinal / prism position)
   int32_t* solve_count; // [4]     envs per solver class (zeroed every step)
-  int32_t* solve_list;  // [3][N]  env ids of each solver class
+  int32_t* solve_list;  // [4][N]  env ids of each solver class
   // ---- outputs
   double* qacc;            // [N][18]
   double* qacc_smooth;     // [N][18]
@@ -191,6 +193,7 @@ __host__ __device__ __forceinline__ double hmj_rand_u01(uint64_t seed, uint32_t 
 #define SENS_TORSO_XPOS 0   /* xpos[2] (3) */
 #define SENS_ROOT_XQUAT 3   /* xquat[1] (4) */
 #define SENS_ROOT_Z 7       /* xpos[1][2] */
+#define SENS_SITE_XPOS 8    /* site_xpos[0..1] (6): the feet, for the planner residual */
 #define SENS_NUM 16
 
 // ------------------------------------------------------------------ small math (device)
@@ -312,11 +315,6 @@ __device__ __forceinline__ double warp_sum(double v) {
 
 __device__ __forceinline__ bool d_is_bad(double x) { return isnan(x) || x > HMJ_MAXVAL || x < -HMJ_MAXVAL; }
 
-// kernel launchers (defined in the .cu files, called from hmj_api.cu)
-void hmj_launch_smooth(const hmj_tables_t* tab, hmj_buffers_t buf, const hmj_task_t* task, int plan_mode,
-                       const double* spline_times, const double* spline_values, int nnode, int interpolation,
-                       int values_per_env, cudaStream_t stream);
-void hmj_launch_collide(const hmj_tables_t* tab, hmj_buffers_t buf, cudaStream_t stream, bool zero = true);
 // Side streams of hmj_launch_solve: the three solver classes are independent, so the (few, long) many-contact solves
 // and the (many, short) unconstrained ones run beside the main class instead of after it.  Null -> one stream.
 struct hmj_solve_ctx_t {
@@ -324,6 +322,11 @@ struct hmj_solve_ctx_t {
   cudaEvent_t fork, join[2];
   cudaEvent_t fac_fork, fac_done;   // k_factor on side[0], forked after k_smooth, joined by hmj_launch_solve
 };
+// kernel launchers (defined in the .cu files, called from hmj_api.cu)
+void hmj_launch_smooth(const hmj_tables_t* tab, hmj_buffers_t buf, const hmj_task_t* task, int plan_mode,
+                       const double* spline_times, const double* spline_values, int nnode, int interpolation,
+                       int values_per_env, cudaStream_t stream, const hmj_solve_ctx_t* ctx = nullptr);
+void hmj_launch_collide(const hmj_tables_t* tab, hmj_buffers_t buf, cudaStream_t stream, bool zero = true);
 // Contact-independent factorisations (qacc_smooth, Euler factor): call after hmj_launch_smooth, before hmj_launch_solve.
 void hmj_launch_factor(const hmj_tables_t* tab, hmj_buffers_t buf, cudaStream_t stream, const hmj_solve_ctx_t* ctx = nullptr);
 void hmj_launch_solve(const hmj_tables_t* tab, hmj_buffers_t buf, int integrate, cudaStream_t stream,

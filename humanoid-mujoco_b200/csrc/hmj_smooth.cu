@@ -1,8 +1,11 @@
-// hmj_smooth.cu — kernel 1 of the step: everything in mj_forward that does not depend on contacts.
+// hmj_smooth.cu — everything in mj_forward that does not depend on contacts, as TWO kernels:
 //
-//   mj_checkPos/Vel -> [planner: spline policy -> ctrl] -> mj_kinematics -> mj_comPos -> mj_crb
-//   -> mj_comVel -> mj_passive -> mj_rne -> mj_fwdActuation -> qfrc_smooth (+ xfrc_applied)
-//   -> [planner: sensors -> humanoid_cap Stand residual -> norms -> running cost]
+//   k_kin  (critical path, feeds the collision stage)
+//          mj_checkPos/Vel -> [planner: spline policy -> ctrl] -> mj_kinematics -> inertial / geom / site frames
+//          -> mj_comPos -> cdof
+//   k_dyn  (side stream, beside the collision kernels; feeds k_factor and k_solve)
+//          mj_crb -> qM, mj_comVel, mj_passive, mj_rne, mj_fwdActuation -> qfrc_smooth (+ xfrc_applied)
+//          -> [planner: sensors -> humanoid_cap Stand residual -> norms -> running cost]
 //
 // Restates (B200-first) the stages declared at simulation/mujoco/include/mujoco/mujoco.h:301-304,
 // 310-349,253 and mjpc/planners/sampling/policy.cc:52-59, mjpc/spline/spline.cc:103-156,
@@ -10,23 +13,30 @@
 //
 // Mapping: one warp per environment; lanes own bodies (15), dofs (18), geoms (10) or sparse-M
 // entries (117); the kinematic tree is walked level by level (bodies of equal depth in
-// parallel); per-env working set (~13 KB) lives in shared memory; subtree reductions use
-// warp shuffles.  Roofline: FP64 FMA pipe / issue-latency bound; HBM traffic is the state row
-// (qpos,qvel,ctrl,params: ~1.7 KB in) and the scratch row (geom frames, cdof, qM: ~3 KB out, L2).
+// parallel); subtree reductions use warp shuffles.  The split exists because only the geom frames gate the
+// collision stage: k_kin keeps 4 KB of shared memory per env (every env of a 4096-env batch is resident at once) and is
+// ~1/3 of the old single kernel's latency; the inertia / bias half runs concurrently with broad- and narrowphase.  The
+// two halves exchange xipos / ximat (180 doubles per env, L2) and the site positions (in the `sens` row).
+// Roofline: FP64 issue-latency bound; HBM traffic is the state row (qpos,qvel,ctrl,params: ~1.7 KB in) and the scratch
+// rows (geom frames, cdof, qM, xipos/ximat: ~4.5 KB out, L2 resident).
 #include "hmj_dev.cuh"
 
-struct SmoothSmem {
+struct KinSmem {
   double qpos[HMJ_NQ + 1];
-  double qvel[HMJ_NV];
-  double ctrl[HMJ_NU];
   double xpos[HMJ_NBODY][3];
   double xquat[HMJ_NBODY][4];
   double xmat[HMJ_NBODY][9];
   double xipos[HMJ_NBODY][3];
-  double ximat[HMJ_NBODY][9];
   double xanchor[HMJ_NJNT][3];
   double xaxis[HMJ_NJNT][3];
-  double site_xpos[HMJ_NSITE][3];
+  double com[4];
+};
+
+struct DynSmem {
+  double qpos[HMJ_NQ + 1];
+  double qvel[HMJ_NV];
+  double ctrl[HMJ_NU];
+  double xipos[HMJ_NBODY][3];
   double cinert[HMJ_NBODY][10];
   double crb[HMJ_NBODY][10];   // later reused for accumulated cfrc
   double cdof[HMJ_NV][6];
@@ -126,11 +136,11 @@ __device__ double norm_value(const double* x, const double* prm, int n, int type
   return y;
 }
 
+// ------------------------------------------------------------------ k_kin
 __global__ void __launch_bounds__(32 * HMJ_WARPS_PER_CTA)
-k_smooth(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* __restrict__ task, int plan_mode,
-         const double* __restrict__ spline_times, const double* __restrict__ spline_values, int nnode,
-         int interpolation, int values_per_env) {
-  extern __shared__ double smem_raw[];
+k_kin(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int plan_mode, const double* __restrict__ spline_times,
+      const double* __restrict__ spline_values, int nnode, int interpolation, int values_per_env) {
+  __shared__ KinSmem smem[HMJ_WARPS_PER_CTA];
   const int lane = threadIdx.x & 31;
   const int wib = threadIdx.x >> 5;
   const int env = blockIdx.x * HMJ_WARPS_PER_CTA + wib;
@@ -142,7 +152,7 @@ k_smooth(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* 
   if (env >= B.n) return;  // whole warp exits together
   if (B.active && !B.active[env]) return;
   if (lane < 4) B.slot_mask[(size_t)env * 4 + lane] = 0u;
-  SmoothSmem& S = reinterpret_cast<SmoothSmem*>(smem_raw)[wib];
+  KinSmem& S = smem[wib];
   const hmj_model_t& M = T->m;
   const hmj_params_t* P = B.params + env;
   const unsigned FULL = 0xffffffffu;
@@ -153,19 +163,11 @@ k_smooth(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* 
   double* g_ctrl = B.ctrl + (size_t)env * HMJ_NU;
   double qp = lane < HMJ_NQ ? g_qpos[lane] : 0.0;
   double qv = lane < HMJ_NV ? g_qvel[lane] : 0.0;
-  // Per-env parameters (domain randomisation) and step inputs this lane needs later, requested now: every one of them is
-  // an L2 round trip, and left at its point of use each would stall the warp on its own (they were 9 % of the samples).
-  const double pf_mass = (lane >= 1 && lane < HMJ_NBODY) ? P->body_mass[lane] : 0.0;
-  const double pf_arm = lane < HMJ_NV ? P->dof_armature[lane] : 0.0;
-  const double pf_stiff = lane < HMJ_NV ? P->jnt_stiffness[M.dof_jntid[lane]] : 0.0;
-  const double pf_gain = lane < HMJ_NU ? P->act_gainprm0[lane] : 0.0;
-  const double pf_fr0 = lane < HMJ_NU ? P->act_forcerange[lane][0] : 0.0;
-  const double pf_fr1 = lane < HMJ_NU ? P->act_forcerange[lane][1] : 0.0;
-  const int pf_xb = B.xfrc_body[env];
+  const double pf_mass = (lane >= 1 && lane < HMJ_NBODY) ? P->body_mass[lane] : 0.0;   // requested now: an L2 round trip
   int status = 0;
   bool badq = __any_sync(FULL, d_is_bad(qp));
   bool badv = __any_sync(FULL, d_is_bad(qv));
-  if (badq || badv) {  // mj_resetData semantics for this path
+  if (badq || badv) {  // mj_resetData semantics for this path (k_dyn starts after this kernel and sees the reset state)
     status |= badq ? HMJ_STATUS_BADQPOS : HMJ_STATUS_BADQVEL;
     qp = lane < HMJ_NQ ? M.qpos0[lane] : 0.0;
     qv = 0.0;
@@ -176,7 +178,6 @@ k_smooth(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* 
     if (lane == 0) B.time[env] = 0.0;
   }
   if (lane < HMJ_NQ) S.qpos[lane] = qp;
-  if (lane < HMJ_NV) S.qvel[lane] = qv;
 
   // ---------------- control: planner spline policy (SamplingPolicy::Action) or caller-provided ctrl
   double u = 0.0;
@@ -192,18 +193,12 @@ k_smooth(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* 
   }
   if (__any_sync(FULL, lane < HMJ_NU && d_is_bad(u))) {  // mjWARN_BADCTRL: controls zeroed
     status |= HMJ_STATUS_BADCTRL;
-    u = 0.0;
     if (lane < HMJ_NU) g_ctrl[lane] = 0.0;
   }
-  if (lane < HMJ_NU) S.ctrl[lane] = u;
   if (lane == 0) {
     S.xpos[0][0] = S.xpos[0][1] = S.xpos[0][2] = 0;
     S.xquat[0][0] = 1; S.xquat[0][1] = S.xquat[0][2] = S.xquat[0][3] = 0;
     for (int k = 0; k < 9; k++) S.xmat[0][k] = (k % 4 == 0) ? 1.0 : 0.0;
-    for (int k = 0; k < 6; k++) { S.cvel[0][k] = 0; S.cfrc[0][k] = 0; }
-    S.cacc[0][0] = S.cacc[0][1] = S.cacc[0][2] = 0;
-    S.cacc[0][3] = -M.gravity[0]; S.cacc[0][4] = -M.gravity[1]; S.cacc[0][5] = -M.gravity[2];
-    for (int k = 0; k < 10; k++) S.cinert[0][k] = 0;
     S.xipos[0][0] = S.xipos[0][1] = S.xipos[0][2] = 0;
   }
   __syncwarp();
@@ -254,18 +249,21 @@ k_smooth(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* 
     __syncwarp();
   }
 
-  // ---------------- inertial frames (lanes 1..14), geom frames (lanes 16..25), sites (lanes 26,27)
+  // ---------------- inertial frames (lanes 1..14) -> global for k_dyn, geom frames (lanes 16..25), sites (lanes 26,27)
   if (lane >= 1 && lane < HMJ_NBODY) {
     const int b = lane;
+    double* gi = B.xipos + ((size_t)env * HMJ_NBODY + b) * 3;
+    double* gm = B.ximat + ((size_t)env * HMJ_NBODY + b) * 9;
     if (M.body_sameframe[b]) {
-      for (int k = 0; k < 3; k++) S.xipos[b][k] = S.xpos[b][k];
-      for (int k = 0; k < 9; k++) S.ximat[b][k] = S.xmat[b][k];
+      for (int k = 0; k < 3; k++) { S.xipos[b][k] = S.xpos[b][k]; gi[k] = S.xpos[b][k]; }
+      for (int k = 0; k < 9; k++) gm[k] = S.xmat[b][k];
     } else {
-      double t[4], p[3];
+      double t[4], p[3], mat[9];
       d_rot_vec_mat(p, M.body_ipos[b], S.xmat[b]);
-      for (int k = 0; k < 3; k++) S.xipos[b][k] = p[k] + S.xpos[b][k];
+      for (int k = 0; k < 3; k++) { S.xipos[b][k] = p[k] + S.xpos[b][k]; gi[k] = S.xipos[b][k]; }
       d_mul_quat(t, S.xquat[b], M.body_iquat[b]);
-      d_quat2mat(S.ximat[b], t);
+      d_quat2mat(mat, t);
+      for (int k = 0; k < 9; k++) gm[k] = mat[k];
     }
   } else if (lane >= 16 && lane < 16 + HMJ_NGEOM) {
     const int g = lane - 16, b = M.geom_bodyid[g];
@@ -281,7 +279,7 @@ k_smooth(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* 
     const int s = lane - 26, b = M.site_bodyid[s];
     double p[3];
     d_rot_vec_mat(p, M.site_pos[s], S.xmat[b]);
-    for (int k = 0; k < 3; k++) S.site_xpos[s][k] = p[k] + S.xpos[b][k];
+    for (int k = 0; k < 3; k++) B.sens[(size_t)env * SENS_NUM + SENS_SITE_XPOS + 3 * s + k] = p[k] + S.xpos[b][k];
   }
   __syncwarp();
 
@@ -301,14 +299,10 @@ k_smooth(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* 
     }
   }
   __syncwarp();
-  if (lane >= 1 && lane < HMJ_NBODY) {
-    double off[3] = {S.xipos[lane][0] - S.com[0], S.xipos[lane][1] - S.com[1], S.xipos[lane][2] - S.com[2]};
-    inert_com(S.cinert[lane], M.body_inertia[lane], S.ximat[lane], off, mass);
-  }
   if (lane < HMJ_NV) {  // cdof, one dof per lane
     const int d = lane, j = M.dof_jntid[d], bi = M.jnt_bodyid[j];
     double off[3] = {S.com[0] - S.xanchor[j][0], S.com[1] - S.xanchor[j][1], S.com[2] - S.xanchor[j][2]};
-    double* c = S.cdof[d];
+    double c[6];
     if (M.jnt_type[j] == HMJ_JNT_FREE) {
       const int k = d - M.jnt_dofadr[j];
       if (k < 3) {
@@ -325,6 +319,56 @@ k_smooth(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* 
     }
     double* gc = B.cdof + ((size_t)env * HMJ_NV + d) * 6;
     for (int q = 0; q < 6; q++) gc[q] = c[q];
+  }
+  // ---------------- values the env epilogue reads after the step (one-step-stale by contract, SURVEY App. C.1)
+  if (lane < 3) B.sens[(size_t)env * SENS_NUM + SENS_TORSO_XPOS + lane] = S.xpos[2][lane];
+  if (lane < 4) B.sens[(size_t)env * SENS_NUM + SENS_ROOT_XQUAT + lane] = S.xquat[1][lane];
+  if (lane == 0) B.sens[(size_t)env * SENS_NUM + SENS_ROOT_Z] = S.xpos[1][2];
+  if (status && lane == 0) atomicOr(&B.status[env], status);
+}
+
+// ------------------------------------------------------------------ k_dyn
+__global__ void __launch_bounds__(32 * HMJ_WARPS_PER_CTA)
+k_dyn(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* __restrict__ task, int plan_mode) {
+  extern __shared__ double smem_raw[];
+  const int lane = threadIdx.x & 31;
+  const int wib = threadIdx.x >> 5;
+  const int env = blockIdx.x * HMJ_WARPS_PER_CTA + wib;
+  if (env >= B.n) return;  // whole warp exits together
+  if (B.active && !B.active[env]) return;
+  DynSmem& S = reinterpret_cast<DynSmem*>(smem_raw)[wib];
+  const hmj_model_t& M = T->m;
+  const hmj_params_t* P = B.params + env;
+  const unsigned FULL = 0xffffffffu;
+
+  // ---------------- state and the kinematic quantities k_kin left in L2; per-env parameters requested up front
+  if (lane < HMJ_NQ) S.qpos[lane] = B.qpos[(size_t)env * HMJ_NQ + lane];
+  if (lane < HMJ_NV) S.qvel[lane] = B.qvel[(size_t)env * HMJ_NV + lane];
+  if (lane < HMJ_NU) S.ctrl[lane] = B.ctrl[(size_t)env * HMJ_NU + lane];
+  const double pf_mass = (lane >= 1 && lane < HMJ_NBODY) ? P->body_mass[lane] : 0.0;
+  const double pf_arm = lane < HMJ_NV ? P->dof_armature[lane] : 0.0;
+  const double pf_stiff = lane < HMJ_NV ? P->jnt_stiffness[M.dof_jntid[lane]] : 0.0;
+  const double pf_gain = lane < HMJ_NU ? P->act_gainprm0[lane] : 0.0;
+  const double pf_fr0 = lane < HMJ_NU ? P->act_forcerange[lane][0] : 0.0;
+  const double pf_fr1 = lane < HMJ_NU ? P->act_forcerange[lane][1] : 0.0;
+  const int pf_xb = B.xfrc_body[env];
+  for (int t = lane; t < HMJ_NBODY * 3; t += 32) (&S.xipos[0][0])[t] = t < 3 ? 0.0 : B.xipos[(size_t)env * HMJ_NBODY * 3 + t];
+  for (int t = lane; t < HMJ_NV * 6; t += 32) (&S.cdof[0][0])[t] = B.cdof[(size_t)env * HMJ_NV * 6 + t];
+  if (lane < 3) S.com[lane] = B.com[(size_t)env * 3 + lane];
+  if (lane == 0) {
+    for (int k = 0; k < 6; k++) { S.cvel[0][k] = 0; S.cfrc[0][k] = 0; }
+    S.cacc[0][0] = S.cacc[0][1] = S.cacc[0][2] = 0;
+    S.cacc[0][3] = -M.gravity[0]; S.cacc[0][4] = -M.gravity[1]; S.cacc[0][5] = -M.gravity[2];
+    for (int k = 0; k < 10; k++) S.cinert[0][k] = 0;
+  }
+  __syncwarp();
+  const double mass = pf_mass;
+  if (lane >= 1 && lane < HMJ_NBODY) {
+    const double* gm = B.ximat + ((size_t)env * HMJ_NBODY + lane) * 9;
+    double ximat[9];
+    for (int k = 0; k < 9; k++) ximat[k] = gm[k];
+    double off[3] = {S.xipos[lane][0] - S.com[0], S.xipos[lane][1] - S.com[1], S.xipos[lane][2] - S.com[2]};
+    inert_com(S.cinert[lane], M.body_inertia[lane], ximat, off, mass);
   }
   __syncwarp();
 
@@ -456,14 +500,9 @@ k_smooth(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* 
     B.qfrc_smooth[(size_t)env * HMJ_NV + d] = f;
   }
 
-  // ---------------- values the env epilogue reads after the step (one-step-stale by contract, SURVEY App. C.1)
-  if (lane < 3) B.sens[(size_t)env * SENS_NUM + SENS_TORSO_XPOS + lane] = S.xpos[2][lane];
-  if (lane < 4) B.sens[(size_t)env * SENS_NUM + SENS_ROOT_XQUAT + lane] = S.xquat[1][lane];
-  if (lane == 0) B.sens[(size_t)env * SENS_NUM + SENS_ROOT_Z] = S.xpos[1][2];
-  if (status && lane == 0) atomicOr(&B.status[env], status);
-
   // ---------------- planner: sensors -> Stand residual -> cost accumulation
   if (plan_mode & 1) {
+    const double* sens = B.sens + (size_t)env * SENS_NUM;
     // mj_subtreeVel for the root: whole-robot CoM velocity (torso_subtreelinvel is attached to body 1)
     double lx = 0, ly = 0, lz = 0;
     if (lane >= 1 && lane < HMJ_NBODY) {
@@ -480,9 +519,9 @@ k_smooth(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* 
       double s2 = M.body_subtreemass[2] < HMJ_MINVAL ? 1.0 : P->body_mass[2] / fmax(HMJ_MINVAL, M.body_subtreemass[2]);
       double comx = S.xipos[2][0] * s2, comy = S.xipos[2][1] * s2;
       if (M.body_subtreemass[2] < HMJ_MINVAL) { comx = S.xipos[2][0]; comy = S.xipos[2][1]; }
-      const double* f1 = S.site_xpos[0];
-      const double* f2 = S.site_xpos[1];
-      S.residual[0] = (S.xpos[2][2] - 0.5 * (f1[2] + f2[2])) - task->height_goal;
+      const double* f1 = sens + SENS_SITE_XPOS;
+      const double* f2 = sens + SENS_SITE_XPOS + 3;
+      S.residual[0] = (sens[SENS_TORSO_XPOS + 2] - 0.5 * (f1[2] + f2[2])) - task->height_goal;
       double cpx = comx + lx * 0.2, cpy = comy + ly * 0.2;
       double fx = (f1[0] + f2[0]) * 0.5 - cpx, fy = (f1[1] + f2[1]) * 0.5 - cpy;
       S.residual[1] = sqrt(fx * fx + fy * fy);
@@ -492,7 +531,7 @@ k_smooth(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* 
     if (lane < 12) { S.residual[4 + lane] = S.qvel[6 + lane]; S.residual[16 + lane] = S.ctrl[lane]; }
     __syncwarp();
     if (lane < HMJ_NRESIDUAL) B.residual[(size_t)env * HMJ_NRESIDUAL + lane] = S.residual[lane];
-    if (lane < 3) B.trace[(size_t)env * 3 + lane] = S.xpos[2][lane];
+    if (lane < 3) B.trace[(size_t)env * 3 + lane] = sens[SENS_TORSO_XPOS + lane];
     // CostTerms: one lane per term, then sum in term order (task.cc:71-110)
     double term = 0.0;
     if (lane < task->nterm) {
@@ -507,17 +546,26 @@ k_smooth(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* 
   }
 }
 
+// k_kin on `stream`; k_dyn behind it on ctx->side[0] (where hmj_launch_factor queues k_factor next), or on `stream` itself
+// when there is no side stream.  hmj_launch_solve joins the side stream.
 void hmj_launch_smooth(const hmj_tables_t* tab, hmj_buffers_t buf, const hmj_task_t* task, int plan_mode,
                        const double* spline_times, const double* spline_values, int nnode, int interpolation,
-                       int values_per_env, cudaStream_t stream) {
+                       int values_per_env, cudaStream_t stream, const hmj_solve_ctx_t* ctx) {
   static bool configured[HMJ_MAX_DEVICES] = {false};   // function attributes are per device
-  const size_t smem = sizeof(SmoothSmem) * HMJ_WARPS_PER_CTA;
+  const size_t smem = sizeof(DynSmem) * HMJ_WARPS_PER_CTA;
   const int dev = hmj_current_device();
   if (!configured[dev]) {
-    cudaFuncSetAttribute(k_smooth, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(k_dyn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     configured[dev] = true;
   }
   const int grid = (buf.n + HMJ_WARPS_PER_CTA - 1) / HMJ_WARPS_PER_CTA;
-  k_smooth<<<grid, 32 * HMJ_WARPS_PER_CTA, smem, stream>>>(tab, buf, task, plan_mode, spline_times, spline_values,
-                                                           nnode, interpolation, values_per_env);
+  k_kin<<<grid, 32 * HMJ_WARPS_PER_CTA, 0, stream>>>(tab, buf, plan_mode, spline_times, spline_values, nnode, interpolation,
+                                                      values_per_env);
+  cudaStream_t s2 = stream;
+  if (ctx) {
+    cudaEventRecord(ctx->fac_fork, stream);
+    cudaStreamWaitEvent(ctx->side[0], ctx->fac_fork, 0);
+    s2 = ctx->side[0];
+  }
+  k_dyn<<<grid, 32 * HMJ_WARPS_PER_CTA, smem, s2>>>(tab, buf, task, plan_mode);
 }

@@ -31,6 +31,8 @@
 #define NLIMMAX 24
 #define NTRI (NV * (NV + 1) / 2)
 #define SOLVE_SMALL_CON 4       /* class 1 holds envs with at most this many contacts */
+#define SOLVE_MID_CON 8         /* class 2: up to this many; class 3: the rest (up to HMJ_MAXCON) */
+#define SOLVE_CLASS_OF(MAXC) ((MAXC) == 0 ? 0 : ((MAXC) <= SOLVE_SMALL_CON ? 1 : ((MAXC) <= SOLVE_MID_CON ? 2 : 3)))
 
 // staging rows of chol_factor_solve (below)
 struct CholScratch {
@@ -384,7 +386,7 @@ __global__ void __launch_bounds__(128) k_classify(const hmj_tables_t* __restrict
   }
   const bool anylim = __any_sync(FULL, lim);
   if (lane == 0) {
-    const int cls = (ncon == 0 && !anylim) ? 0 : (ncon <= SOLVE_SMALL_CON ? 1 : 2);
+    const int cls = (ncon == 0 && !anylim) ? 0 : (ncon <= SOLVE_SMALL_CON ? 1 : (ncon <= SOLVE_MID_CON ? 2 : 3));
     const int at = atomicAdd(&B.solve_count[cls], 1);
     B.solve_list[(size_t)cls * B.n + at] = env;
   }
@@ -395,13 +397,13 @@ template <int MAXC>
 #ifndef HMJ_SOLVE4_WARPS
 #define HMJ_SOLVE4_WARPS 14
 #endif
-__global__ void __launch_bounds__(32, MAXC == 0 ? 24 : (MAXC <= SOLVE_SMALL_CON ? HMJ_SOLVE4_WARPS : 6))
+__global__ void __launch_bounds__(32, MAXC == 0 ? 24 : (MAXC <= SOLVE_SMALL_CON ? HMJ_SOLVE4_WARPS : (MAXC <= SOLVE_MID_CON ? 10 : 6)))
 k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
   using Smem = SolveSmem<MAXC>;
   extern __shared__ double smem_raw[];
-  if ((int)blockIdx.x >= B.solve_count[MAXC == 0 ? 0 : (MAXC <= SOLVE_SMALL_CON ? 1 : 2)]) return;
+  if ((int)blockIdx.x >= B.solve_count[SOLVE_CLASS_OF(MAXC)]) return;
   const int lane = threadIdx.x & 31;
-  const int env = B.solve_list[(size_t)(MAXC == 0 ? 0 : (MAXC <= SOLVE_SMALL_CON ? 1 : 2)) * B.n + blockIdx.x];
+  const int env = B.solve_list[(size_t)SOLVE_CLASS_OF(MAXC) * B.n + blockIdx.x];
   Smem& S = *reinterpret_cast<Smem*>(smem_raw);
   const hmj_model_t& M = T->m;
   const hmj_params_t* P = B.params + env;
@@ -943,7 +945,7 @@ static void launch_class(const hmj_tables_t* tab, hmj_buffers_t buf, int integra
   k_solve<MAXC><<<buf.n, 32, smem, stream>>>(tab, buf, integrate);
 }
 
-// Four launches: classification, then one solver launch per class.  With side streams the many-contact class and the
+// Five launches: classification, then one solver launch per class.  With side streams the many-contact class and the
 // unconstrained class run concurrently with the main class; otherwise the heavy class goes first.
 void hmj_launch_solve(const hmj_tables_t* tab, hmj_buffers_t buf, int integrate, cudaStream_t stream,
                       const hmj_solve_ctx_t* ctx, bool zero) {
@@ -952,6 +954,7 @@ void hmj_launch_solve(const hmj_tables_t* tab, hmj_buffers_t buf, int integrate,
   k_classify<<<(buf.n + 3) / 4, 128, 0, stream>>>(tab, buf);
   if (!ctx) {
     launch_class<HMJ_MAXCON>(tab, buf, integrate, stream);
+    launch_class<SOLVE_MID_CON>(tab, buf, integrate, stream);
     launch_class<SOLVE_SMALL_CON>(tab, buf, integrate, stream);
     launch_class<0>(tab, buf, integrate, stream);
     return;
@@ -960,6 +963,7 @@ void hmj_launch_solve(const hmj_tables_t* tab, hmj_buffers_t buf, int integrate,
   cudaStreamWaitEvent(ctx->side[0], ctx->fork, 0);
   cudaStreamWaitEvent(ctx->side[1], ctx->fork, 0);
   launch_class<HMJ_MAXCON>(tab, buf, integrate, ctx->side[0]);
+  launch_class<SOLVE_MID_CON>(tab, buf, integrate, ctx->side[0]);
   launch_class<SOLVE_SMALL_CON>(tab, buf, integrate, stream);
   launch_class<0>(tab, buf, integrate, ctx->side[1]);
   cudaEventRecord(ctx->join[0], ctx->side[0]);
