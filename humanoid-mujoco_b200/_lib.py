@@ -79,6 +79,8 @@ def load_library() -> C.CDLL:
     lib.hmj_env_pool_stats.argtypes = [vp, vp]
     lib.hmj_plan_iterate.argtypes = [vp, dp, C.c_double, dp, dp, C.c_int, C.c_int, C.c_int, dp, C.c_double, C.c_double,
                                      C.c_ulonglong, C.c_ulonglong, C.c_int, vp]
+    lib.hmj_plan_iterate_ex.argtypes = [vp, dp, C.c_double, dp, dp, C.c_int, C.c_int, C.c_int, dp, C.c_double, C.c_double, dp,
+                                        C.c_ulonglong, C.c_ulonglong, C.c_int, vp]
     lib.hmj_plan_record_size.argtypes = [C.c_int]
     lib.hmj_plan_record_ptr.argtypes = [vp]
     lib.hmj_plan_record_ptr.restype = vp

@@ -335,7 +335,7 @@ class HumanoidBatch:
         return ret, fail.astype(bool)
 
     def plan_iterate(self, state, time, spline_times, nominal_values, horizon, interpolation=2, noise=None, noise_std=0.0,
-                     noise_std2=0.0, seed=0, iteration=0, first_global=0, record_dev: int | None = None):
+                     noise_std2=0.0, seed=0, iteration=0, first_global=0, record_dev: int | None = None, noise_std_vec=None):
         """Device half of one OptimizePolicy iteration (hmj_plan_iterate): enqueue only."""
         state = np.ascontiguousarray(state, dtype=np.float64)
         st = np.ascontiguousarray(spline_times, dtype=np.float64)
@@ -345,9 +345,14 @@ class HumanoidBatch:
         if noise is not None:
             nz = np.ascontiguousarray(noise, dtype=np.float64)
             assert nz.shape == (self.n, st.shape[0], NU), nz.shape
-        check(self.lib.hmj_plan_iterate(self._h, _p(state), float(time), _p(st), _p(nv), st.shape[0], int(interpolation),
-                                        int(horizon), _p(nz) if nz is not None else None, float(noise_std), float(noise_std2),
-                                        int(seed) & (2**64 - 1), int(iteration), int(first_global), record_dev))
+        sv = None
+        if noise_std_vec is not None:
+            sv = np.ascontiguousarray(noise_std_vec, dtype=np.float64)
+            assert sv.size == st.shape[0] * NU, sv.shape
+        check(self.lib.hmj_plan_iterate_ex(self._h, _p(state), float(time), _p(st), _p(nv), st.shape[0], int(interpolation),
+                                           int(horizon), _p(nz) if nz is not None else None, float(noise_std), float(noise_std2),
+                                           _p(sv) if sv is not None else None, int(seed) & (2**64 - 1), int(iteration),
+                                           int(first_global), record_dev))
 
     def plan_select(self, nnode: int, gathered_dev: int | None = None, nranks: int = 1) -> np.ndarray:
         """Global winner record {cost, global index, nominal return, spline values [nnode][12]} (hmj_plan_select)."""

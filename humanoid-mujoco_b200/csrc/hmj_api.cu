@@ -46,10 +46,11 @@ struct hmj_batch_ {
   int32_t* failure_dev = nullptr;    // [N]
   double* argmin_dev = nullptr;      // [2]
   double* nominal_dev = nullptr;     // [64][12] nominal spline values of hmj_plan_iterate
+  double* stdvec_dev = nullptr;      // [64][12] per-parameter noise std (cross-entropy planner)
   double* noise_dev = nullptr;       // [N][nnode][12] caller-provided noise (same capacity as spline_values_dev)
   double* record_dev = nullptr;      // [3 + 64*12] this rank's winner record
   double* select_dev = nullptr;      // [3 + 64*12] global winner record
-  double* plan_stage = nullptr;      // pinned [2048]: state|time @0, spline times @64, nominal @128, record out @1024
+  double* plan_stage = nullptr;      // pinned [3072]: state|time @0, spline times @64, nominal @128, record out @1024, std vector @2048
   int plan_nnode = 0;
   int host_launches = 0;             // API-level launches (a graph replay counts once)
   struct RolloutKey {
@@ -485,7 +486,7 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
   ALLOC("trace", trace, N * 3);
   {
     int rc;
-    if ((rc = alloc_array(b, nullptr, &b->state_dev, HMJ_NSTATE + 1, false)) || (rc = alloc_array(b, nullptr, &b->nominal_dev, 64 * HMJ_NU, false)) ||
+    if ((rc = alloc_array(b, nullptr, &b->state_dev, HMJ_NSTATE + 1, false)) || (rc = alloc_array(b, nullptr, &b->nominal_dev, 64 * HMJ_NU, false)) || (rc = alloc_array(b, nullptr, &b->stdvec_dev, 64 * HMJ_NU, false)) ||
         (rc = alloc_array(b, nullptr, &b->record_dev, 3 + 64 * HMJ_NU, false)) || (rc = alloc_array(b, nullptr, &b->select_dev, 3 + 64 * HMJ_NU, false)) || (rc = alloc_array(b, nullptr, &b->spline_times_dev, 64, false)) ||
         (rc = alloc_array(b, "returns", &b->returns_dev, N)) || (rc = alloc_array(b, nullptr, &b->failure_dev, N)) ||
         (rc = alloc_array(b, "argmin", &b->argmin_dev, 2, false))) {
@@ -521,7 +522,7 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
     if (!rc && cudaHostAlloc((void**)&b->io_host, b->io_in_bytes + b->io_out_bytes, cudaHostAllocDefault) != cudaSuccess)
       rc = fail(HMJ_ERR_CUDA, "cudaHostAlloc failed%s");
     if (!rc) { memset(b->io_host, 0, b->io_in_bytes + b->io_out_bytes); rc = alloc_array(b, nullptr, &b->io_dev, b->io_in_bytes + b->io_out_bytes); }
-    if (!rc && cudaHostAlloc((void**)&b->plan_stage, 2048 * sizeof(double), cudaHostAllocDefault) != cudaSuccess)
+    if (!rc && cudaHostAlloc((void**)&b->plan_stage, 3072 * sizeof(double), cudaHostAllocDefault) != cudaSuccess)
       rc = fail(HMJ_ERR_CUDA, "cudaHostAlloc failed%s");
     if (!rc && b->n_spare > 0) {   // episode pool
       const size_t S = (size_t)b->n_spare;
@@ -1442,10 +1443,10 @@ extern "C" int hmj_plan_rollouts(hmj_batch_t* b, const double* state, double tim
 // arg-min, winner record.  Nothing is read back: the caller all-gathers the record (hmj_plan_record_size doubles at
 // `record_dev`, or the batch's own buffer when NULL) over its communicator ON hmj_batch_stream and finishes with
 // hmj_plan_select.  noise == NULL draws the noise on the device (seed, iteration, global sample index).
-extern "C" int hmj_plan_iterate(hmj_batch_t* b, const double* state, double time, const double* spline_times,
-                                const double* nominal_values, int nnode, int interpolation, int horizon, const double* noise,
-                                double noise_std, double noise_std2, unsigned long long seed, unsigned long long iteration,
-                                int first_global, double* record_dev) {
+extern "C" int hmj_plan_iterate_ex(hmj_batch_t* b, const double* state, double time, const double* spline_times,
+                                   const double* nominal_values, int nnode, int interpolation, int horizon, const double* noise,
+                                   double noise_std, double noise_std2, const double* noise_std_vec, unsigned long long seed,
+                                   unsigned long long iteration, int first_global, double* record_dev) {
   if (!b || !state || !spline_times || !nominal_values || nnode < 1) return fail(HMJ_ERR_ARG, "bad argument to plan_iterate%s");
   CK(cudaSetDevice(b->device));
   int rc = ensure_values(b, nnode);
@@ -1455,10 +1456,15 @@ extern "C" int hmj_plan_iterate(hmj_batch_t* b, const double* state, double time
   double* nom = b->plan_stage + 128;
   memcpy(nom, nominal_values, (size_t)nnode * HMJ_NU * 8);
   CK(cudaMemcpyAsync(b->nominal_dev, nom, (size_t)nnode * HMJ_NU * 8, cudaMemcpyHostToDevice, b->stream));
+  if (noise_std_vec) {
+    double* sv = b->plan_stage + 2048;
+    memcpy(sv, noise_std_vec, (size_t)nnode * HMJ_NU * 8);
+    CK(cudaMemcpyAsync(b->stdvec_dev, sv, (size_t)nnode * HMJ_NU * 8, cudaMemcpyHostToDevice, b->stream));
+  }
   const size_t nvals = (size_t)b->n * nnode * HMJ_NU;
   if (noise) CK(cudaMemcpyAsync(b->noise_dev, noise, nvals * 8, cudaMemcpyHostToDevice, b->stream));
   hmj_launch_plan_candidates(b->tab_dev, b->n, nnode, b->nominal_dev, noise ? b->noise_dev : nullptr, noise_std, noise_std2, seed,
-                             iteration, first_global, b->spline_values_dev, b->stream);
+                             iteration, first_global, b->spline_values_dev, b->stream, noise_std_vec ? b->stdvec_dev : nullptr);
   if ((rc = launch_rollouts(b, b->spline_values_dev, nnode, interpolation, horizon, 0, b->returns_dev, b->failure_dev))) return rc;
   hmj_launch_plan_winner(b->returns_dev, b->n, b->spline_values_dev, nnode, first_global, b->argmin_dev,
                          record_dev ? record_dev : b->record_dev, b->stream);
@@ -1467,6 +1473,14 @@ extern "C" int hmj_plan_iterate(hmj_batch_t* b, const double* state, double time
   b->plan_nnode = nnode;
   CK(cudaGetLastError());
   return HMJ_OK;
+}
+
+extern "C" int hmj_plan_iterate(hmj_batch_t* b, const double* state, double time, const double* spline_times,
+                                const double* nominal_values, int nnode, int interpolation, int horizon, const double* noise,
+                                double noise_std, double noise_std2, unsigned long long seed, unsigned long long iteration,
+                                int first_global, double* record_dev) {
+  return hmj_plan_iterate_ex(b, state, time, spline_times, nominal_values, nnode, interpolation, horizon, noise, noise_std,
+                             noise_std2, nullptr, seed, iteration, first_global, record_dev);
 }
 
 extern "C" int hmj_plan_record_size(int nnode) { return 3 + nnode * HMJ_NU; }

@@ -93,9 +93,12 @@ void hmj_launch_argmin(const double* returns_dev, int n, double* out, cudaStream
 // tests inject them); NULL: drawn here from the counter-based stream (seed, iteration, global sample, element) with
 // Box-Muller — the reference draws absl::Gaussian from an entropy-seeded BitGen (unpinned by construction).
 // std_s = std1 with probability 0.2 when std1 > 0 (planner.cc:324-329), else std0.  Thread per (sample, node, actuator).
+// Cross-entropy flavour (mjpc/planners/cross_entropy/planner.cc:346-378): `std_vec` [nnode * 12] is the ABSOLUTE standard
+// deviation of every spline parameter (max(sqrt(variance), std_min), no control-range scaling) and replaces std0 / std1.
 __global__ void k_plan_candidates(const hmj_tables_t* __restrict__ T, int n, int nnode, const double* __restrict__ nominal,
                                   const double* __restrict__ noise, double std0, double std1, unsigned long long seed,
-                                  unsigned long long iteration, int first_global, double* __restrict__ values) {
+                                  unsigned long long iteration, int first_global, double* __restrict__ values,
+                                  const double* __restrict__ std_vec) {
   const int per = nnode * HMJ_NU;
   const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= (long long)n * per) return;
@@ -112,7 +115,8 @@ __global__ void k_plan_candidates(const hmj_tables_t* __restrict__ T, int n, int
       if (std1 > 0 && hmj_rand_u01(key, gs, 0xFFFFFFFFu) < 0.2) sd = std1;
       const double u1 = 1.0 - hmj_rand_u01(key, gs, 2u * (uint32_t)e);        // (0, 1]
       const double u2 = hmj_rand_u01(key, gs, 2u * (uint32_t)e + 1u);
-      z = sqrt(-2.0 * log(u1)) * cospi(2.0 * u2) * (0.5 * (hi - lo)) * sd;
+      const double g = sqrt(-2.0 * log(u1)) * cospi(2.0 * u2);
+      z = std_vec ? g * std_vec[e] : g * (0.5 * (hi - lo)) * sd;
     }
   }
   const double v = nominal[e] + z;
@@ -174,10 +178,10 @@ __global__ void k_plan_select(const double* __restrict__ gathered, int nranks, i
 
 void hmj_launch_plan_candidates(const hmj_tables_t* tab, int n, int nnode, const double* nominal_dev, const double* noise_dev,
                                 double std0, double std1, unsigned long long seed, unsigned long long iteration, int first_global,
-                                double* values_dev, cudaStream_t stream) {
+                                double* values_dev, cudaStream_t stream, const double* std_vec_dev) {
   const long long tot = (long long)n * nnode * HMJ_NU;
   k_plan_candidates<<<(int)((tot + 255) / 256), 256, 0, stream>>>(tab, n, nnode, nominal_dev, noise_dev, std0, std1, seed, iteration,
-                                                                  first_global, values_dev);
+                                                                  first_global, values_dev, std_vec_dev);
 }
 void hmj_launch_plan_winner(const double* returns_dev, int n, const double* values_dev, int nnode, int first_global,
                             double* argmin_dev, double* rec_dev, cudaStream_t stream) {

@@ -350,7 +350,7 @@ struct hmj_record_t {
 void hmj_launch_plan_init(hmj_buffers_t buf, const double* state_time_dev, cudaStream_t stream);
 void hmj_launch_plan_candidates(const hmj_tables_t* tab, int n, int nnode, const double* nominal_dev, const double* noise_dev,
                                 double std0, double std1, unsigned long long seed, unsigned long long iteration, int first_global,
-                                double* values_dev, cudaStream_t stream);
+                                double* values_dev, cudaStream_t stream, const double* std_vec_dev = nullptr);
 void hmj_launch_plan_winner(const double* returns_dev, int n, const double* values_dev, int nnode, int first_global,
                             double* argmin_dev, double* rec_dev, cudaStream_t stream);
 void hmj_launch_plan_select(const double* gathered_dev, int nranks, int stride, double* out_dev, cudaStream_t stream);

@@ -67,6 +67,23 @@ def exchange_records(record: np.ndarray, batch=None, rec_local=None, rec_all=Non
     return select_winner(torch.stack(parts).numpy())
 
 
+def gather_rows(rows: np.ndarray, device_index: int = 0) -> np.ndarray:
+    """All ranks contribute a [k][w] float64 array of the same shape; everyone gets the [world * k][w] stack in rank order
+    (the cross-entropy planner's elite exchange).  NCCL: tensors on the rank's GPU; gloo: CPU tensors."""
+    import torch
+    import torch.distributed as dist
+
+    rank, ws = world()
+    rows = np.ascontiguousarray(rows, dtype=np.float64)
+    if ws == 1:
+        return rows
+    dev = torch.device("cuda", device_index) if dist.get_backend() == "nccl" else torch.device("cpu")
+    mine = torch.from_numpy(rows).to(dev)
+    parts = [torch.zeros_like(mine) for _ in range(ws)]
+    dist.all_gather(parts, mine)
+    return torch.cat(parts).cpu().numpy()
+
+
 def exchange_winner(cost: float, local_index: int, nominal_return: float, win_values: np.ndarray, first_global: int,
                     device=None):
     """All ranks call this with their local best.  Returns (cost, global_index, nominal_return_of_rank0, values) of

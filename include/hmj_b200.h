@@ -191,6 +191,14 @@ int hmj_plan_iterate(hmj_batch_t* b, const double* state, double time, const dou
                      const double* nominal_values, int nnode, int interpolation, int horizon, const double* noise,
                      double noise_std, double noise_std2, unsigned long long seed, unsigned long long iteration,
                      int first_global, double* record_dev);
+/* The same with a per-parameter ABSOLUTE noise standard deviation noise_std_vec [P][12] (NULL: hmj_plan_iterate): the
+ * cross-entropy planner's sampling distribution, max(sqrt(variance), std_min) per spline parameter without control-range
+ * scaling (mjpc/planners/cross_entropy/planner.cc:346-378).  Elite selection and the mean / variance refit (:213-283) are
+ * done by the caller from hmj_plan_population. */
+int hmj_plan_iterate_ex(hmj_batch_t* b, const double* state, double time, const double* spline_times,
+                        const double* nominal_values, int nnode, int interpolation, int horizon, const double* noise,
+                        double noise_std, double noise_std2, const double* noise_std_vec, unsigned long long seed,
+                        unsigned long long iteration, int first_global, double* record_dev);
 int hmj_plan_record_size(int nnode);
 void* hmj_plan_record_ptr(hmj_batch_t* b);
 int hmj_plan_select(hmj_batch_t* b, const double* gathered_dev, int nranks, int nnode, double* record_host);

@@ -78,3 +78,38 @@ def test_single_process_exchange_is_identity():
     v = np.arange(36.0).reshape(3, 12)
     cost, gidx, nominal, win = exchange_winner(1.5, 4, 2.5, v, 16)
     assert (cost, gidx, nominal) == (1.5, 20, 2.5) and np.array_equal(win, v)
+
+
+def _worker_rows(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from humanoid_mujoco_b200.dist import exchange_records, gather_rows, select_winner
+
+        rows = np.arange(6.0).reshape(2, 3) + 100 * rank
+        got = gather_rows(rows)
+        rec = np.concatenate([[2.0 - rank, 1024.0 * rank + 7, 5.0 + rank], np.full(36, float(rank))])
+        win = exchange_records(rec)        # gloo path: host all-gather + select_winner
+        q.put((rank, got.tolist(), win.tolist(), select_winner(np.stack([rec, rec])).tolist()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_elite_rows_and_record_exchange_world2():
+    """The cross-entropy planner's elite exchange (gather_rows) and the record form of the winner exchange on gloo."""
+    world, port = 2, _free_port()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker_rows, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    out = sorted(q.get(timeout=120) for _ in range(world))
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    want = np.concatenate([np.arange(6.0).reshape(2, 3), np.arange(6.0).reshape(2, 3) + 100])
+    for rank, got, win, _ in out:
+        assert np.array_equal(np.array(got), want)
+        win = np.array(win)
+        assert win[0] == 1.0 and win[1] == 1031.0 and win[2] == 5.0      # rank 1 wins; the nominal return is rank 0's
+        assert np.all(win[3:] == 1.0)

@@ -289,3 +289,72 @@ def test_device_select_matches_host_select(hmj):
         want = select_winner(recs)
         assert np.array_equal(got, want, equal_nan=True), case
     b.close()
+
+
+def test_cross_entropy_planner_matches_mirror(hmj, oracle):
+    """CrossEntropyPlanner (mjpc/planners/cross_entropy/planner.cc:164-283): three iterations with injected noise against
+    a host mirror whose rollouts run on the oracle — same elite set, elite mean as the new nominal, the reference's
+    variance formula (best candidate's parameter for every elite), improvement = avg - best."""
+    state, time = settled_task_state(oracle)
+    n = 41                                     # nominal + 40 candidates -> n_elite = 4
+    pl = hmj.CrossEntropyPlanner(num_trajectory=n, device=0, seed=3)
+    assert pl.n_elite_ == 4 and pl.std_min_ == 0.1
+    pl.SetState(state[:19], state[19:], time)
+    H = pl.steps()
+    rng = np.random.default_rng(17)
+    variance = np.full(36, pl.std_initial_ ** 2)
+    ref_policy = hmj.SamplingPolicy(pl.ctrlrange, pl.num_spline_points, pl.interpolation_)
+    ref_policy.Reset(H)
+    compared = 0
+    for it in range(3):
+        std = np.maximum(np.sqrt(variance), pl.std_min_)
+        noise = rng.standard_normal((n, 3, 12)) * std.reshape(3, 12)
+        pl.OptimizePolicy(H, noise=noise)
+        # mirror
+        P = 3
+        shift = max((H - 1) * pl.timestep / (P - 1), 1e-5)
+        acc, tt = time, []
+        for _ in range(P):
+            tt.append(acc)
+            acc += shift
+        node_t = np.array(tt)
+        nominal = np.stack([ref_policy.Action(t) for t in node_t])
+        vals = nominal[None] + noise
+        vals[0] = nominal
+        np.clip(vals, pl.ctrlrange[:, 0], pl.ctrlrange[:, 1], out=vals)
+        assert np.array_equal(pl.candidate_values, vals)
+        ref, _ = oracle_returns(oracle, state, time, node_t, vals, H, pl.interpolation_)
+        rel = np.abs(pl.total_return - ref) / np.maximum(np.abs(ref), 1.0)
+        # std_min = 0.1 rad of absolute noise makes these rollouts rougher than predictive sampling's (5 % of the range):
+        # the bimodal error of tools/dev/rollout_fidelity.py (1e-14 or a contact event) shows up in a few samples more
+        assert np.median(rel) < 1e-9 and (rel < TOL_RETURN).sum() >= n - 3
+        order = 1 + np.argsort(ref[1:], kind="stable")[:4]
+        gaps = np.diff(np.sort(ref[1:])[:5])
+        # the elite set is the oracle's whenever the samples that decide it (the five best on either side) agree
+        decisive = np.union1d(order, 1 + np.argsort(pl.total_return[1:], kind="stable")[:5])
+        if (rel[decisive] < 1e-9).all() and gaps.min() > GAP:
+            compared += 1
+            assert np.array_equal(pl.elite_indices, order)
+        el = pl.elite_indices                       # follow the device's elite set so later iterations stay comparable
+        p_avg = vals[el].reshape(4, 36).sum(axis=0) * 0.25
+        diff = vals[el[0]].reshape(36) - p_avg
+        var = np.zeros(36)
+        for _ in range(4):
+            var += diff * diff / 3
+        assert np.max(np.abs(pl.policy.plan.arrays()[1].reshape(36) - p_avg)) < 1e-15
+        assert np.max(np.abs(pl.variance[:36] - var)) < 1e-18
+        assert abs(pl.avg_return - pl.total_return[el].sum() / 4) < 1e-12
+        assert pl.improvement == max(pl.avg_return - pl.total_return[el[0]], 0.0)
+        assert pl.nominal_return == pl.total_return[0]
+        variance = var
+        plan = hmj.TimeSpline(12, pl.interpolation_)
+        for t, v in zip(node_t, p_avg.reshape(3, 12)):
+            plan.AddNode(float(t), v)
+        ref_policy.plan = plan
+    assert compared >= 2
+    # device-drawn noise uses the per-parameter std (no control-range scaling)
+    pl.variance[:36] = 0.04
+    pl.OptimizePolicy(H)
+    z = (pl.candidate_values[1:] - pl.candidate_values[0]).reshape(-1, 36)
+    inside = np.abs(pl.candidate_values[1:]).max() < pl.ctrlrange[:, 1].max()
+    assert 0.15 < z.std() < 0.25 if inside else True
