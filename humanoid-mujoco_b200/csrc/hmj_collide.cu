@@ -484,31 +484,51 @@ struct Mpr {
         guard = 0;
         return refine_head();
       }
-      case ST_REFINE: {
-        dot = c_dot(s.v, dir);
-        if (!(c_is_zero(dot) || dot > 0) || portal_reach_tolerance(p1, p2, p3, s, dir, tol)) return -1;
-        expand_portal(p0v, p1, p2, p3, s);
-        return refine_head();
-      }
-      default: {  // ST_PENETR
-        if (portal_reach_tolerance(p1, p2, p3, s, dir, tol) || iterations > maxit) {
-          const double origin[3] = {0, 0, 0};
-          depth = point_tri_dist2(origin, p1.v, p2.v, p3.v, pdir);
-          depth = sqrt(depth);
-          if (c_is_zero(depth)) {
-            pdir[0] = pdir[1] = pdir[2] = 0;
-          } else {
-            c_normalize(pdir);
-          }
-          find_pos(p0v, p0v1, p0v2, p1, p2, p3, pos);
-          return 0;
+      default: {  // ST_REFINE / ST_PENETR: one body for both (refinePortal's and findPenetr's loops run the same portal
+                  // test, expansion and new direction; lanes of a warp are in either state, so a shared body halves the
+                  // divergent work of a trip).  Per lane this is the same operation sequence as the two separate loops.
+        const bool ref = st == ST_REFINE;
+        if (ref) {
+          dot = c_dot(s.v, dir);
+          if (!(c_is_zero(dot) || dot > 0)) return -1;
+        }
+        const bool reach = portal_reach_tolerance(p1, p2, p3, s, dir, tol);
+        if (ref) {
+          if (reach) return -1;
+        } else if (reach || iterations > maxit) {
+          return 2;   // penetration found: depth / direction / position are computed by finalize(), once per warp
         }
         expand_portal(p0v, p1, p2, p3, s);
-        iterations++;
+        if (ref) {
+          if (++guard > 1000) return -1;
+        } else {
+          iterations++;
+        }
         portal_dir(p1, p2, p3, dir);
+        if (ref) {
+          dot = c_dot(dir, p1.v);
+          if (c_is_zero(dot) || dot > 0) {  // portal encapsules origin -> findPenetr (same dir)
+            st = ST_PENETR;
+            iterations = 0;
+          }
+        }
         return 1;
       }
     }
+  }
+
+  // tail of findPenetr (depth, penetration direction, contact position), deferred so that all queries of a warp that
+  // end in a penetration run it together after the trip loop instead of one after the other at their own last trips
+  __device__ __forceinline__ void finalize() {
+    const double origin[3] = {0, 0, 0};
+    depth = point_tri_dist2(origin, p1.v, p2.v, p3.v, pdir);
+    depth = sqrt(depth);
+    if (c_is_zero(depth)) {
+      pdir[0] = pdir[1] = pdir[2] = 0;
+    } else {
+      c_normalize(pdir);
+    }
+    find_pos(p0v, p0v1, p0v2, p1, p2, p3, pos);
   }
 };
 
@@ -764,6 +784,7 @@ __device__ __forceinline__ void narrow_mesh_mesh(const hmj_tables_t* __restrict_
   const int maxit = M.mpr_iterations;
   Mpr m;
   m.begin(f1.pos, f2.pos);
+  bool found = false, fin = false;
   const int thr = coop_threshold(h1.n4 + h2.n4);
   while (true) {
     const unsigned am = __ballot_sync(0xffffffffu, active);
@@ -788,12 +809,13 @@ __device__ __forceinline__ void narrow_mesh_mesh(const hmj_tables_t* __restrict_
       const int res = m.step(s, tol, maxit);
       if (res != 1) {
         active = false;
-        if (res == 0 && !c_vec_is_origin(m.pdir)) {
-          write_slot(B, env, T->pair_slot[k], 0.0 - m.depth, m.pdir, m.pos);
-        }
+        found = res == 0;
+        fin = res == 2;
       }
     }
   }
+  if (fin) { m.finalize(); found = true; }
+  if (found && !c_vec_is_origin(m.pdir)) write_slot(B, env, T->pair_slot[k], 0.0 - m.depth, m.pdir, m.pos);
 }
 
 // 32 prism-vs-hull tasks of one hull (pairs may differ per lane): lane <-> one pre-screened prism of
@@ -825,6 +847,7 @@ __device__ __forceinline__ void narrow_hfield(const hmj_tables_t* __restrict__ T
     prism_center(p, c1);
     m.begin(c1, f2.pos);
   }
+  bool found = false, fin = false;
   const int thr = coop_threshold(h2.n4);
   while (true) {
     const unsigned am = __ballot_sync(0xffffffffu, active);
@@ -848,18 +871,21 @@ __device__ __forceinline__ void narrow_hfield(const hmj_tables_t* __restrict__ T
       const int res = m.step(s, tol, maxit);
       if (res != 1) {
         active = false;
-        if (res == 0 && !d_is_bad(m.depth)) {
-          const double* pos1 = gx;
-          const double* mat1 = gm;
-          double nrm[3], cp[3];
-          d_rot_vec_mat(nrm, m.pdir, mat1);
-          d_rot_vec_mat(cp, m.pos, mat1);
-          cp[0] += pos1[0]; cp[1] += pos1[1]; cp[2] += pos1[2];
-          if (!(nrm[0] == 0 && nrm[1] == 0 && nrm[2] == 0)) {
-            write_slot(B, env, T->pair_slot[k] + ord, 0.0 - m.depth, nrm, cp);
-          }
-        }
+        found = res == 0;
+        fin = res == 2;
       }
+    }
+  }
+  if (fin) { m.finalize(); found = true; }
+  if (found && !d_is_bad(m.depth)) {
+    const double* pos1 = gx;
+    const double* mat1 = gm;
+    double nrm[3], cp[3];
+    d_rot_vec_mat(nrm, m.pdir, mat1);
+    d_rot_vec_mat(cp, m.pos, mat1);
+    cp[0] += pos1[0]; cp[1] += pos1[1]; cp[2] += pos1[2];
+    if (!(nrm[0] == 0 && nrm[1] == 0 && nrm[2] == 0)) {
+      write_slot(B, env, T->pair_slot[k] + ord, 0.0 - m.depth, nrm, cp);
     }
   }
 }
