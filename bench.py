@@ -322,7 +322,7 @@ def plan_bench(local, rank, world, iters, cpu):
                      "kernel_nodes_per_iteration": (pl.batch.kernel_launches - l0) / nit,
                      "rollouts": "one CUDA-graph launch per iteration (candidates, rollouts, arg-min on the device)",
                      "winner": int(pl.winner), "winner_return": float(pl.winner_return),
-                     "exchange": "none" if n_glob == n_local else "all_gather(cost,idx) + broadcast(winner spline) over NCCL"}
+                     "exchange": "none" if n_glob == n_local else "one all-gather of the winner records {cost, global index, nominal return, spline} over NCCL on the batch stream + device selection (hmj_plan_select)"}
         if cpu and rank == 0:
             sys.path.insert(0, os.path.join(REPO, "oracle"))
             from oracle_py import OracleBatch   # cpu_baseline leg: the oracle is the timed CPU implementation
