@@ -291,6 +291,45 @@ def plan_start_state(device=0, timestep=0.02, nsteps=50):
     return q[0].copy(), v[0].copy(), float(t[0])
 
 
+def fd_bench(local, cpu):
+    """Finite-differenced transition matrices for the 18 knots of the C2 horizon (iLQG's ModelDerivatives::Compute,
+    mjpc/planners/model_derivatives.cc:51-96): ONE batched step of 18 x 97 envs (hmj_fd_transition, forward differences)
+    against the oracle's mjd_transitionFD restatement, one knot after the other on one host thread."""
+    import humanoid_mujoco_b200 as hmj
+    q, v, t = plan_start_state(local)
+    T = 18
+    b = hmj.HumanoidBatch(97 * T, device=local)
+    p = b.default_params()
+    p["timestep"] = 0.02
+    b.set_params(p)
+    rng = np.random.default_rng(0)
+    x = np.tile(np.concatenate([q, v]), (T, 1))
+    x[:, 7:19] += rng.normal(0, 0.02, (T, 12))
+    u = rng.normal(0, 0.05, (T, 12))
+    tt = t + 0.02 * np.arange(T)
+    for _ in range(3):
+        b.fd_transition(x, u, tt)
+    reps = 20
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        A, _B, _C, _D = b.fd_transition(x, u, tt)
+    dt = (time.perf_counter() - t0) / reps
+    out = {"knots": T, "ms_per_call": 1e3 * dt, "mj_steps_per_call": T * 49, "api": "hmj_fd_transition (host arrays in, A/B/C/D out)"}
+    if cpu:
+        sys.path.insert(0, os.path.join(REPO, "oracle"))
+        from oracle_py import Oracle   # cpu_baseline leg
+        o = Oracle()
+        o.params["timestep"][0] = 0.02
+        t0 = time.perf_counter()
+        for k in range(T):
+            Ar, _, _, _ = o.transition_fd(x[k], u[k], tt[k])
+        cdt = time.perf_counter() - t0
+        out["cpu_baseline"] = {"ms_per_call": 1e3 * cdt, "cores": 1, "kind": "port",
+                               "max_rel_diff_A_last_knot": float(np.max(np.abs(A[T - 1] - Ar) / np.maximum(np.abs(Ar), 1.0)))}
+    b.close()
+    return out
+
+
 def plan_bench(local, rank, world, iters, cpu):
     """MJPC predictive-sampling iterations/s: one iteration = SamplingPlanner.OptimizePolicy (resample nominal, noise,
     N rollouts of H-1 steps + 1 forward with fused policy/residual/cost, device argmin, winner exchange over the
@@ -649,6 +688,7 @@ def run_gpu(args):
         plan = plan_bench(local, rank, world, args.plan_iters, cpu=(world == 1 and not args.no_cpu))
         if rank == 0:
             line["plan"] = plan
+            line["fd"] = fd_bench(local, cpu=(world == 1 and not args.no_cpu))
     if world > 1:
         dist.destroy_process_group()
     sys.stdout.flush()

@@ -371,6 +371,21 @@ class HumanoidBatch:
     def host_launches(self) -> int:
         return int(self.lib.hmj_batch_host_launches(self._h))
 
+    def fd_transition(self, x, u, time, warmstart=None, eps: float = 1e-6, centered: bool = False):
+        """mjd_transitionFD for T knots in one batched step (hmj_fd_transition): returns A [T][36][36], B [T][36][12],
+        C [T][28][36], D [T][28][12].  Needs n_envs >= 97 T; overwrites the batch state."""
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        t = np.ascontiguousarray(time, dtype=np.float64)
+        T = x.shape[0]
+        assert x.shape == (T, DEFINES["HMJ_NSTATE"]) and u.shape == (T, NU) and t.shape == (T,)
+        ws = None if warmstart is None else np.ascontiguousarray(warmstart, dtype=np.float64)
+        nr, ndx = DEFINES["HMJ_NRESIDUAL"], 2 * NV
+        A, B, Cm, D = np.zeros((T, ndx, ndx)), np.zeros((T, ndx, NU)), np.zeros((T, nr, ndx)), np.zeros((T, nr, NU))
+        check(self.lib.hmj_fd_transition(self._h, T, _p(x), _p(u), _p(t), _p(ws) if ws is not None else None, float(eps),
+                                         int(bool(centered)), _p(A), _p(B), _p(Cm), _p(D)))
+        return A, B, Cm, D
+
     def plan_argmin(self):
         cost, idx = C.c_double(0), C.c_int32(0)
         check(self.lib.hmj_plan_argmin(self._h, C.byref(cost), C.byref(idx)))

@@ -86,6 +86,7 @@ struct hmj_batch_ {
   double pool_rf = 0, pool_max_sim_time = 0, pool_timestep = 0.002;
   unsigned long long pool_seed = 0;
   long long pool_rounds = 0, pool_drains = 0, pool_drain_iters = 0;
+  double* fd_dev = nullptr; size_t fd_cap = 0;   // scratch of hmj_fd_transition
   char* term_host = nullptr;         // pinned: terminal observations [N][30] f64 | env ids [N] i32 of a step with more than 64 endings
   size_t io_ext_offset = 0;          // byte offset of the pool's result block inside the IO out block
   hmj_solve_ctx_t solve_ctx{};       // side streams + events that overlap the solver classes
@@ -1558,6 +1559,64 @@ extern "C" int hmj_plan_fetch(hmj_batch_t* b, int sample, int horizon, double* s
   CK(cudaStreamSynchronize(b->stream));
   if (actions && horizon > 1)  // final action is a copy of the previous one (trajectory.cc:190-192)
     memcpy(actions + (size_t)(horizon - 1) * HMJ_NU, actions + (size_t)(horizon - 2) * HMJ_NU, HMJ_NU * 8);
+  return HMJ_OK;
+}
+
+// ------------------------------------------------------------------ batched finite-difference derivatives (hmj_fd.cu)
+/* mjd_transitionFD for T knots in one batched step (mjpc ModelDerivatives::Compute, model_derivatives.cc:51-96): the batch
+ * must hold at least 97 T environments; their state is overwritten (parameters are the caller's: set the planner timestep
+ * with hmj_batch_set_params).  x [T][37], u [T][12], time [T], warmstart [T][18] or NULL (zeros); eps as mjpc passes it
+ * (1e-6 forward in iLQG); outputs row-major per knot: A [T][36][36], B [T][36][12], C [T][28][36], D [T][28][12] (any NULL). */
+extern "C" int hmj_fd_transition(hmj_batch_t* b, int T, const double* x, const double* u, const double* time,
+                                 const double* warmstart, double eps, int centered, double* A, double* Bm, double* C, double* D) {
+  if (!b || T < 1 || !x || !u || !time || !(eps > 0)) return fail(HMJ_ERR_ARG, "bad argument to fd_transition%s");
+  const int slots = 97, ndx = 2 * HMJ_NV;
+  if ((long long)T * slots > b->n) return fail(HMJ_ERR_ARG, "fd_transition needs 97 environments per knot%s");
+  CK(cudaSetDevice(b->device));
+  const size_t nin = (size_t)T * (HMJ_NSTATE + HMJ_NU + 1 + HMJ_NV);
+  const size_t nout = (size_t)T * (ndx * ndx + ndx * HMJ_NU + HMJ_NRESIDUAL * ndx + HMJ_NRESIDUAL * HMJ_NU);
+  const size_t bytes = (nin + nout) * 8 + (size_t)T * slots * 4;
+  if (b->fd_cap < bytes) {
+    CK(cudaStreamSynchronize(b->stream));
+    if (b->fd_dev) {
+      for (size_t k = 0; k < b->allocs.size(); k++)
+        if (b->allocs[k] == (void*)b->fd_dev) { b->allocs.erase(b->allocs.begin() + k); break; }
+      cudaFree(b->fd_dev);
+      b->fd_dev = nullptr;
+    }
+    void* p = nullptr;
+    CK(cudaMalloc(&p, bytes));
+    b->allocs.push_back(p);
+    b->fd_dev = (double*)p;
+    b->fd_cap = bytes;
+  }
+  double* d_x = b->fd_dev;
+  double* d_u = d_x + (size_t)T * HMJ_NSTATE;
+  double* d_t = d_u + (size_t)T * HMJ_NU;
+  double* d_w = d_t + T;
+  double* d_A = d_w + (size_t)T * HMJ_NV;
+  double* d_B = d_A + (size_t)T * ndx * ndx;
+  double* d_C = d_B + (size_t)T * ndx * HMJ_NU;
+  double* d_D = d_C + (size_t)T * HMJ_NRESIDUAL * ndx;
+  int32_t* d_valid = (int32_t*)(d_D + (size_t)T * HMJ_NRESIDUAL * HMJ_NU);
+  int rc;
+  if ((rc = h2d(b, d_x, x, (size_t)T * HMJ_NSTATE * 8)) || (rc = h2d(b, d_u, u, (size_t)T * HMJ_NU * 8)) ||
+      (rc = h2d(b, d_t, time, (size_t)T * 8)) || (rc = h2d(b, d_w, warmstart, (size_t)T * HMJ_NV * 8)))
+    return rc;
+  hmj_buffers_t V = pipe_view(b->buf, 0, T * slots, 0, b->tab_host->group_base[HMJ_NGROUP]);
+  hmj_launch_fd_setup(b->tab_dev, V, T, d_x, d_u, d_t, warmstart ? d_w : nullptr, eps, centered, d_valid, b->stream);
+  hmj_launch_smooth(b->tab_dev, V, b->task_dev, HMJ_PLAN_COST, nullptr, nullptr, 0, 0, 0, b->stream, &b->solve_ctx);
+  hmj_launch_factor(b->tab_dev, V, b->stream, &b->solve_ctx);
+  hmj_launch_collide(b->tab_dev, V, b->stream, false);
+  hmj_launch_solve(b->tab_dev, V, 1, b->stream, &b->solve_ctx, false);
+  hmj_launch_fd_diff(b->tab_dev, V, T, d_valid, eps, d_A, d_B, d_C, d_D, b->stream);
+  b->warmed = true;
+  b->launches += 12; b->host_launches += 12;
+  if ((rc = d2h(b, A, d_A, (size_t)T * ndx * ndx * 8)) || (rc = d2h(b, Bm, d_B, (size_t)T * ndx * HMJ_NU * 8)) ||
+      (rc = d2h(b, C, d_C, (size_t)T * HMJ_NRESIDUAL * ndx * 8)) || (rc = d2h(b, D, d_D, (size_t)T * HMJ_NRESIDUAL * HMJ_NU * 8)))
+    return rc;
+  CK(cudaStreamSynchronize(b->stream));
+  CK(cudaGetLastError());
   return HMJ_OK;
 }
 

@@ -368,6 +368,11 @@ void hmj_launch_pool_validate(hmj_buffers_t spare, hmj_pool_t pool, cudaStream_t
 void hmj_launch_autoreset(hmj_buffers_t buf, hmj_envstate_t env, hmj_buffers_t spare, hmj_envstate_t spare_env, hmj_pool_t pool,
                           const int32_t* term, const int32_t* trunc, double* obs, double* time_out, double* quat_out, int flags /* 1 promote, 2 drain, 4 a round is launched right behind this step */,
                           cudaStream_t stream);
+void hmj_launch_fd_setup(const hmj_tables_t* tab, hmj_buffers_t view, int nknot, const double* x_dev, const double* u_dev,
+                         const double* time_dev, const double* ws_dev, double eps, int centered, int32_t* valid_dev,
+                         cudaStream_t stream);
+void hmj_launch_fd_diff(const hmj_tables_t* tab, hmj_buffers_t view, int nknot, const int32_t* valid_dev, double eps, double* A,
+                        double* B, double* C, double* D, cudaStream_t stream);
 void hmj_launch_pool_mark_pending(hmj_pool_t pool, const int32_t* ids_dev, int count, int n, cudaStream_t stream);
 void hmj_launch_env_post(hmj_buffers_t buf, hmj_envstate_t env, const int32_t* mask, double* obs, double* time_out, double* quat_out,
                          cudaStream_t stream);

@@ -202,6 +202,14 @@ int hmj_plan_iterate_ex(hmj_batch_t* b, const double* state, double time, const 
 int hmj_plan_record_size(int nnode);
 void* hmj_plan_record_ptr(hmj_batch_t* b);
 int hmj_plan_select(hmj_batch_t* b, const double* gathered_dev, int nranks, int nnode, double* record_host);
+/* ---- batched finite-difference transition matrices: mjd_transitionFD for T knots in ONE batched step, as mjpc's
+ * ModelDerivatives::Compute needs them for iLQG / gradient planners (mjpc/planners/model_derivatives.cc:51-96).  The batch
+ * must hold >= 97 T environments (1 + 2 x 48 nudged copies per knot); their state is overwritten, their parameters are
+ * the caller's.  x [T][37], u [T][12], time [T], warmstart [T][18] or NULL.  Row-major outputs per knot (NULL = skip):
+ * A [T][36][36] = dy/dx, B [T][36][12] = dy/du (y: next state in tangent coordinates), C [T][28][36], D [T][28][12]
+ * (s: the 28 task residuals of that step's forward pass). */
+int hmj_fd_transition(hmj_batch_t* b, int T, const double* x, const double* u, const double* time, const double* warmstart,
+                      double eps, int centered, double* A, double* B, double* C, double* D);
 /* ---- built-in winner exchange for hosts without a communicator of their own (a C++ SamplingPlanner): NCCL is
  * dlopen'ed at run time (libnccl.so.2; HMJ_NCCL_LIB overrides).  Rank 0 calls hmj_comm_unique_id (128 bytes) and hands
  * the id to the other processes by any means; every process calls hmj_comm_create with its rank and device.

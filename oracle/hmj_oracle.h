@@ -166,6 +166,9 @@ double orc_rollout_batch(const hmj_model_t* m, const hmj_params_t* p, const doub
                          const double* spline_times, const double* spline_values, int n, int nnode,
                          int interpolation, int horizon, double* total_return, int32_t* failure, int nthreads);
 
+/* mjd_transitionFD for one knot (hmj_oracle_fd.c): A [36][36], B [36][12], C [28][36], D [28][12] */
+int orc_transition_fd(const hmj_model_t* m, const hmj_params_t* p, const double* x, const double* u, double time,
+                      const double* warmstart, double eps, int centered, double* A, double* B, double* C, double* D);
 int orc_sizeof_data(void);
 int orc_sizeof_model(void);
 int orc_sizeof_params(void);

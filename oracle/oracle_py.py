@@ -140,6 +140,18 @@ class Oracle:
         out["failure"] = bool(fail)
         return out
 
+    def transition_fd(self, x, u, time, warmstart=None, eps=1e-6, centered=False):
+        """mjd_transitionFD for one knot (hmj_oracle_fd.c): A [36][36], B [36][12], C [28][36], D [28][12]."""
+        nv, nu, nr = DEFINES["HMJ_NV"], DEFINES["HMJ_NU"], DEFINES["HMJ_NRESIDUAL"]
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        ws = None if warmstart is None else np.ascontiguousarray(warmstart, dtype=np.float64)
+        A, B, Cm, D = np.zeros((2 * nv, 2 * nv)), np.zeros((2 * nv, nu)), np.zeros((nr, 2 * nv)), np.zeros((nr, nu))
+        self.lib.orc_transition_fd(_ptr(self.model), _ptr(self.params), _ptr(x), _ptr(u), C.c_double(time),
+                                   _ptr(ws) if ws is not None else None, C.c_double(eps), int(bool(centered)),
+                                   _ptr(A), _ptr(B), _ptr(Cm), _ptr(D))
+        return A, B, Cm, D
+
 
 class OracleBatch:
     """N oracle environments stepped by the pthread harness (hmj_oracle_batch.c): CPU-baseline timing and
