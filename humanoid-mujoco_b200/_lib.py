@@ -81,6 +81,7 @@ def load_library() -> C.CDLL:
                                      C.c_ulonglong, C.c_ulonglong, C.c_int, vp]
     lib.hmj_plan_iterate_ex.argtypes = [vp, dp, C.c_double, dp, dp, C.c_int, C.c_int, C.c_int, dp, C.c_double, C.c_double, dp,
                                         C.c_ulonglong, C.c_ulonglong, C.c_int, vp]
+    lib.hmj_batch_inverse.argtypes = [vp, dp, dp]
     lib.hmj_fd_transition.argtypes = [vp, C.c_int, dp, dp, dp, dp, C.c_double, C.c_int, dp, dp, dp, dp]
     lib.hmj_plan_record_size.argtypes = [C.c_int]
     lib.hmj_plan_record_ptr.argtypes = [vp]

@@ -371,6 +371,13 @@ class HumanoidBatch:
     def host_launches(self) -> int:
         return int(self.lib.hmj_batch_host_launches(self._h))
 
+    def inverse(self, qacc=None) -> np.ndarray:
+        """mj_inverse for every env at its current state / ctrl (hmj_batch_inverse): qfrc_inverse [N][18]."""
+        qa = None if qacc is None else self._f64(qacc, (NV,))
+        out = np.zeros((self.n, NV))
+        check(self.lib.hmj_batch_inverse(self._h, _p(qa) if qa is not None else None, _p(out)))
+        return out
+
     def fd_transition(self, x, u, time, warmstart=None, eps: float = 1e-6, centered: bool = False):
         """mjd_transitionFD for T knots in one batched step (hmj_fd_transition): returns A [T][36][36], B [T][36][12],
         C [T][28][36], D [T][28][12].  Needs n_envs >= 97 T; overwrites the batch state."""

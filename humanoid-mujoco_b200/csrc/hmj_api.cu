@@ -311,7 +311,7 @@ static hmj_buffers_t pipe_view(const hmj_buffers_t& B, int start, int count, int
   V.qM += s * HMJ_NM; V.qfrc_smooth += s * HMJ_NV; V.euler_factor += s * HMJ_FAC_DOUBLES; V.sens += s * SENS_NUM; V.slots += s * HMJ_NSLOT * HMJ_SLOT_DOUBLES; V.slot_mask += s * 4;
   V.wq_count += 64 * pipe; V.wq_task += s * group_total;
   V.solve_count += 4 * pipe; V.solve_list += 4 * s;
-  V.qacc += s * HMJ_NV; V.qacc_smooth += s * HMJ_NV; V.qfrc_constraint += s * HMJ_NV; V.contact += s * HMJ_MAXCON;
+  V.qacc += s * HMJ_NV; V.qacc_smooth += s * HMJ_NV; V.qfrc_constraint += s * HMJ_NV; V.qfrc_ext += s * HMJ_NV; V.qfrc_inverse += s * HMJ_NV; V.contact += s * HMJ_MAXCON;
   V.ncon += s; V.nefc += s; V.niter += s; V.status += s;
   V.residual += s * HMJ_NRESIDUAL; V.cost_sum += s; V.cost_last += s; V.trace += s * 3;
   return V;
@@ -476,6 +476,8 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
   ALLOC("qacc", qacc, N * HMJ_NV);
   ALLOC("qacc_smooth", qacc_smooth, N * HMJ_NV);
   ALLOC("qfrc_constraint", qfrc_constraint, N * HMJ_NV);
+  ALLOC("qfrc_ext", qfrc_ext, N * HMJ_NV);
+  ALLOC("qfrc_inverse", qfrc_inverse, N * HMJ_NV);
   ALLOC("contact", contact, N * HMJ_MAXCON);
   ALLOC("ncon", ncon, N);
   ALLOC("nefc", nefc, N);
@@ -1559,6 +1561,28 @@ extern "C" int hmj_plan_fetch(hmj_batch_t* b, int sample, int horizon, double* s
   CK(cudaStreamSynchronize(b->stream));
   if (actions && horizon > 1)  // final action is a copy of the previous one (trajectory.cc:190-192)
     memcpy(actions + (size_t)(horizon - 1) * HMJ_NU, actions + (size_t)(horizon - 2) * HMJ_NU, HMJ_NU * 8);
+  return HMJ_OK;
+}
+
+/* mj_inverse for every env (simulation/mujoco/include/mujoco/mujoco.h mj_inverse; the MPC workaround
+ * find_ideal_distance_to_ground runs it 200 times per control step, controllers/mpc_utils.py:36-55): position and velocity
+ * stages, collision, constraint rows, the constraint forces of the GIVEN acceleration (mj_invConstraint: no solver), and
+ * qfrc_inverse = M qacc + qfrc_bias - qfrc_passive - qfrc_constraint.  qacc [N][18] (NULL: zeros); qfrc_inverse [N][18] out. */
+extern "C" int hmj_batch_inverse(hmj_batch_t* b, const double* qacc, double* qfrc_inverse) {
+  if (!b || !qfrc_inverse) return fail(HMJ_ERR_ARG, "bad argument to batch_inverse%s");
+  CK(cudaSetDevice(b->device));
+  const size_t N = b->n;
+  if (qacc) CK(cudaMemcpyAsync(b->buf.qacc, qacc, N * HMJ_NV * 8, cudaMemcpyHostToDevice, b->stream));
+  else CK(cudaMemsetAsync(b->buf.qacc, 0, N * HMJ_NV * 8, b->stream));
+  hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, b->stream, &b->solve_ctx);
+  hmj_launch_factor(b->tab_dev, b->buf, b->stream, &b->solve_ctx);
+  hmj_launch_collide(b->tab_dev, b->buf, b->stream, false);
+  hmj_launch_solve(b->tab_dev, b->buf, 2, b->stream, &b->solve_ctx, false);
+  b->warmed = true;
+  b->launches += 10; b->host_launches += 10;
+  CK(cudaMemcpyAsync(qfrc_inverse, b->buf.qfrc_inverse, N * HMJ_NV * 8, cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  CK(cudaGetLastError());
   return HMJ_OK;
 }
 

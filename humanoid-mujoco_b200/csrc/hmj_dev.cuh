@@ -113,6 +113,8 @@ struct hmj_buffers_t {
   double* qacc;            // [N][18]
   double* qacc_smooth;     // [N][18]
   double* qfrc_constraint; // [N][18]
+  double* qfrc_ext;        // [N][18]  qfrc_actuator + J' xfrc_applied (k_dyn), for mj_inverse
+  double* qfrc_inverse;    // [N][18]  output of hmj_batch_inverse
   hmj_contact_t* contact;  // [N][MAXCON]
   int32_t* ncon;           // [N]
   int32_t* nefc;           // [N]

@@ -486,6 +486,7 @@ k_dyn(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* __r
     const int d = lane;
     double f = S.qfrc_passive[d] - S.qfrc_bias[d];
     f += S.qfrc_actuator[d];
+    double ext = S.qfrc_actuator[d];
     const int xb = pf_xb;
     if (xb > 0 && xb < HMJ_NBODY) {
       const double* w = B.xfrc + (size_t)env * 6;
@@ -493,11 +494,16 @@ k_dyn(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* __r
         double off[3] = {S.xipos[xb][0] - S.com[0], S.xipos[xb][1] - S.com[1], S.xipos[xb][2] - S.com[2]};
         double tmp[3];
         d_cross(tmp, S.cdof[d], off);
-        f += (S.cdof[d][3] + tmp[0]) * w[0] + (S.cdof[d][4] + tmp[1]) * w[1] + (S.cdof[d][5] + tmp[2]) * w[2];
-        f += S.cdof[d][0] * w[3] + S.cdof[d][1] * w[4] + S.cdof[d][2] * w[5];
+        const double fa = (S.cdof[d][3] + tmp[0]) * w[0] + (S.cdof[d][4] + tmp[1]) * w[1] + (S.cdof[d][5] + tmp[2]) * w[2];
+        const double fb = S.cdof[d][0] * w[3] + S.cdof[d][1] * w[4] + S.cdof[d][2] * w[5];
+        f += fa;
+        f += fb;
+        ext += fa;
+        ext += fb;
       }
     }
     B.qfrc_smooth[(size_t)env * HMJ_NV + d] = f;
+    B.qfrc_ext[(size_t)env * HMJ_NV + d] = ext;
   }
 
   // ---------------- planner: sensors -> Stand residual -> cost accumulation

@@ -364,7 +364,7 @@ void hmj_launch_factor(const hmj_tables_t* tab, hmj_buffers_t buf, cudaStream_t 
 // Warp per env: number of valid contact slots and whether any joint limit is active -> work class.
 // Class lists are filled with atomics (order is irrelevant: envs are independent); counters live in
 // B.solve_count[0..2] and are zeroed by hmj_launch_solve before this kernel.
-__global__ void __launch_bounds__(128) k_classify(const hmj_tables_t* __restrict__ T, hmj_buffers_t B) {
+__global__ void __launch_bounds__(128) k_classify(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int force_rows) {
   const int lane = threadIdx.x & 31;
   const int env = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (env >= B.n) return;
@@ -386,14 +386,15 @@ __global__ void __launch_bounds__(128) k_classify(const hmj_tables_t* __restrict
   }
   const bool anylim = __any_sync(FULL, lim);
   if (lane == 0) {
-    const int cls = (ncon == 0 && !anylim) ? 0 : (ncon <= SOLVE_SMALL_CON ? 1 : (ncon <= SOLVE_MID_CON ? 2 : 3));
+    // force_rows (mj_inverse): the unconstrained class does not carry the dense M the inverse needs
+    const int cls = (ncon == 0 && !anylim && !force_rows) ? 0 : (ncon <= SOLVE_SMALL_CON ? 1 : (ncon <= SOLVE_MID_CON ? 2 : 3));
     const int at = atomicAdd(&B.solve_count[cls], 1);
     B.solve_list[(size_t)cls * B.n + at] = env;
   }
 }
 
 // ---------------------------------------------------------------- the solver
-template <int MAXC>
+template <int MAXC, bool INV = false>
 #ifndef HMJ_SOLVE4_WARPS
 #define HMJ_SOLVE4_WARPS 14
 #endif
@@ -438,6 +439,7 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
   PH(1);
 
   double qacc = qas;  // lanes < NV
+  if constexpr (INV) qacc = lane < NV ? B.qacc[(size_t)env * NV + lane] : 0.0;   // mj_inverse: the acceleration is an input
   double qfc = 0.0;
   int niter = 0, ncon = 0, nefc = 0, status = 0;
 
@@ -600,6 +602,46 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
       };
 
       PH(3);
+      if constexpr (INV) {
+        // ---------------- mj_invConstraint: forces of the GIVEN acceleration, no solve.  Jaref = J qacc - aref, every
+        // active row (pyramidal cones: plain inequalities) pushes with -D Jaref, qfrc_constraint = J' f
+        __syncwarp();
+        if (lane < NV) S.vec[lane] = qacc;
+        __syncwarp();
+        jaref_of();
+        __syncwarp();
+#pragma unroll 1
+        for (int r = lane; r < nefc; r += 32) {
+          const double jar = S.rJaref[r];
+          S.rowbuf[r] = jar < 0 ? -S.rD[r] * jar : 0.0;
+        }
+        __syncwarp();
+#pragma unroll 1
+        for (int t = lane; t < ncon * 6; t += 32) {
+          const int c = t / 6, kk = t - c * 6;
+          const double* f = S.rowbuf + nlim + 10 * c;
+          double v;
+          if (kk == 0) {
+            v = 0.0;
+#pragma unroll
+            for (int e = 0; e < 10; e++) v += f[e];
+          } else {
+            v = S.cfric[c][kk - 1] * (f[2 * (kk - 1)] - f[2 * (kk - 1) + 1]);
+          }
+          S.jbv[c][kk] = v;
+        }
+        __syncwarp();
+        if (lane < NV) {
+#pragma unroll 1
+          for (int c = 0; c < ncon; c++) {
+#pragma unroll
+            for (int kk = 0; kk < 6; kk++) qfc += S.Jb[c][kk][lane] * S.jbv[c][kk];
+          }
+#pragma unroll 1
+          for (int r = 0; r < nlim; r++)
+            if (S.lim_dof[r] == lane) qfc += S.lim_sign[r] * S.rowbuf[r];
+        }
+      } else {
       // ---------------- warmstart: best of (qacc_warmstart, qacc_smooth)
       {
         __syncwarp();
@@ -863,10 +905,29 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
         for (int r = lane; r < nefc; r += 32) S.rJaref[r] += alpha * S.rJv[r];
         oldcost = cost;
       }
+      }   // !INV
     }
   }
 
   PH(9);
+  if constexpr (INV) {
+    // ---------------- mj_inverse: qfrc_inverse = M qacc + qfrc_bias - qfrc_passive - qfrc_constraint
+    //                                          = M qacc - qfrc_smooth + (qfrc_actuator + J' xfrc_applied) - qfrc_constraint
+    double Mq = 0.0;
+    if constexpr (MAXC > 0) {
+      __syncwarp();
+      if (lane < NV) S.vec[lane] = qacc;
+      __syncwarp();
+      Mq = mat_vec(S.M, S.vec, lane);
+    }
+    if (lane == 0) { B.ncon[env] = ncon; B.nefc[env] = nefc; B.niter[env] = 0; }
+    if (lane < NV) {
+      B.qfrc_constraint[(size_t)env * NV + lane] = qfc;
+      B.qfrc_inverse[(size_t)env * NV + lane] = Mq - qfs + B.qfrc_ext[(size_t)env * NV + lane] - qfc;
+    }
+    if (status && lane == 0) atomicOr(&B.status[env], status);
+    return;
+  }
   // ---------------- results of mj_fwdConstraint
   if (lane == 0) { B.ncon[env] = ncon; B.nefc[env] = nefc; B.niter[env] = niter; }
   if (lane < NV) {
@@ -939,10 +1000,12 @@ static void launch_class(const hmj_tables_t* tab, hmj_buffers_t buf, int integra
   const size_t smem = sizeof(SolveSmem<MAXC>);
   const int dev = hmj_current_device();
   if (!configured[dev]) {
-    cudaFuncSetAttribute(k_solve<MAXC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(k_solve<MAXC, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(k_solve<MAXC, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     configured[dev] = true;
   }
-  k_solve<MAXC><<<buf.n, 32, smem, stream>>>(tab, buf, integrate);
+  if (integrate == 2) k_solve<MAXC, true><<<buf.n, 32, smem, stream>>>(tab, buf, 0);   // mj_inverse
+  else k_solve<MAXC, false><<<buf.n, 32, smem, stream>>>(tab, buf, integrate);
 }
 
 // Five launches: classification, then one solver launch per class.  With side streams the many-contact class and the
@@ -951,7 +1014,7 @@ void hmj_launch_solve(const hmj_tables_t* tab, hmj_buffers_t buf, int integrate,
                       const hmj_solve_ctx_t* ctx, bool zero) {
   if (ctx) cudaStreamWaitEvent(stream, ctx->fac_done, 0);   // k_factor ran on side[0] beside the collision kernels
   if (zero) cudaMemsetAsync(buf.solve_count, 0, 4 * sizeof(int32_t), stream);   // else: zeroed by this step's k_smooth
-  k_classify<<<(buf.n + 3) / 4, 128, 0, stream>>>(tab, buf);
+  k_classify<<<(buf.n + 3) / 4, 128, 0, stream>>>(tab, buf, integrate == 2);
   if (!ctx) {
     launch_class<HMJ_MAXCON>(tab, buf, integrate, stream);
     launch_class<SOLVE_MID_CON>(tab, buf, integrate, stream);

@@ -202,6 +202,10 @@ int hmj_plan_iterate_ex(hmj_batch_t* b, const double* state, double time, const 
 int hmj_plan_record_size(int nnode);
 void* hmj_plan_record_ptr(hmj_batch_t* b);
 int hmj_plan_select(hmj_batch_t* b, const double* gathered_dev, int nranks, int nnode, double* record_host);
+/* ---- mj_inverse for every env: qfrc_inverse = M qacc + qfrc_bias - qfrc_passive - qfrc_constraint with the constraint
+ * forces of the GIVEN acceleration (no solver).  Replaces the 200 mj_inverse calls of find_ideal_distance_to_ground
+ * (controllers/mpc_utils.py:36-55) by one batched call.  qacc [N][18] (NULL: zeros), qfrc_inverse [N][18] out. */
+int hmj_batch_inverse(hmj_batch_t* b, const double* qacc, double* qfrc_inverse);
 /* ---- batched finite-difference transition matrices: mjd_transitionFD for T knots in ONE batched step, as mjpc's
  * ModelDerivatives::Compute needs them for iLQG / gradient planners (mjpc/planners/model_derivatives.cc:51-96).  The batch
  * must hold >= 97 T environments (1 + 2 x 48 nudged copies per knot); their state is overwritten, their parameters are

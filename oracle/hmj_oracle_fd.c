@@ -141,3 +141,31 @@ int orc_transition_fd(const hmj_model_t* m, const hmj_params_t* p, const double*
   }
   return 0;
 }
+
+/* ------------------------------------------------------------------ mj_inverse (mujoco.h: mj_inverse; used by
+ * controllers/mpc_utils.py:36-55): position / velocity stages, the constraint forces of the GIVEN acceleration
+ * (mj_invConstraint: Jaref = J qacc - aref, f = -D Jaref on the active rows, no solver), and
+ * qfrc_inverse = M qacc + qfrc_bias - qfrc_passive - qfrc_constraint.  Checker for hmj_batch_inverse. */
+void orc_inverse(const hmj_model_t* m, const hmj_params_t* p, orc_data_t* d, const double* qacc, double* qfrc_inverse) {
+  orc_kinematics(m, p, d);
+  orc_com_pos(m, p, d);
+  orc_crb(m, p, d);
+  orc_factor_m(m, p, d);
+  orc_collision(m, p, d);
+  orc_make_constraint(m, p, d);
+  orc_fwd_velocity(m, p, d);
+  double force[ORC_MAXEFC];
+  for (int r = 0; r < d->nefc; r++) {
+    double jar = -d->efc_aref[r];
+    for (int i = 0; i < HMJ_NV; i++) jar += d->efc_J[r][i] * qacc[i];
+    force[r] = jar < 0 ? -d->efc_D[r] * jar : 0.0;
+  }
+  double Ma[HMJ_NV];
+  orc_mul_m(m, d->qM, Ma, qacc);
+  for (int i = 0; i < HMJ_NV; i++) {
+    double fc = 0.0;
+    for (int r = 0; r < d->nefc; r++) fc += d->efc_J[r][i] * force[r];
+    d->qfrc_constraint[i] = fc;
+    qfrc_inverse[i] = Ma[i] + d->qfrc_bias[i] - d->qfrc_passive[i] - fc;
+  }
+}

@@ -140,6 +140,14 @@ class Oracle:
         out["failure"] = bool(fail)
         return out
 
+    def inverse(self, qacc=None):
+        """mj_inverse at the current state for the given acceleration (zeros by default): qfrc_inverse [18]."""
+        nv = DEFINES["HMJ_NV"]
+        qa = np.zeros(nv) if qacc is None else np.ascontiguousarray(qacc, dtype=np.float64)
+        out = np.zeros(nv)
+        self.lib.orc_inverse(_ptr(self.model), _ptr(self.params), _ptr(self.data), _ptr(qa), _ptr(out))
+        return out
+
     def transition_fd(self, x, u, time, warmstart=None, eps=1e-6, centered=False):
         """mjd_transitionFD for one knot (hmj_oracle_fd.c): A [36][36], B [36][12], C [28][36], D [28][12]."""
         nv, nu, nr = DEFINES["HMJ_NV"], DEFINES["HMJ_NU"], DEFINES["HMJ_NRESIDUAL"]
