@@ -17,9 +17,10 @@ from .batch import HumanoidBatch, default_params, load_model, pinned_empty  # no
 from .env import BatchedHumanoidEnv  # noqa: F401
 from .planner import SamplingPlanner, SamplingPolicy, TimeSpline  # noqa: F401
 from .planner_ce import CrossEntropyPlanner  # noqa: F401
+from .planner_robust import RobustPlanner  # noqa: F401
 from .vec_env import B200VecEnv  # noqa: F401
 
 __all__ = [
     "HmjError", "load_library", "lib_path", "HumanoidBatch", "default_params", "load_model",
-    "BatchedHumanoidEnv", "B200VecEnv", "SamplingPlanner", "SamplingPolicy", "TimeSpline", "CrossEntropyPlanner",
+    "BatchedHumanoidEnv", "B200VecEnv", "SamplingPlanner", "SamplingPolicy", "TimeSpline", "CrossEntropyPlanner", "RobustPlanner",
 ]

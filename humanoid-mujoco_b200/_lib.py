@@ -68,6 +68,8 @@ def load_library() -> C.CDLL:
     lib.hmj_fp64_peak.argtypes = [C.c_int, C.POINTER(C.c_double)]
     lib.hmj_plan_set_task.argtypes = [vp, C.c_int, vp, vp, dp, dp, C.c_double, C.c_double]
     lib.hmj_plan_rollouts.argtypes = [vp, dp, C.c_double, dp, dp, C.c_int, C.c_int, C.c_int, C.c_int, dp, vp]
+    lib.hmj_plan_rollouts_noisy.argtypes = [vp, dp, C.c_double, dp, dp, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, dp,
+                                            C.c_ulonglong, C.c_int, dp, vp]
     lib.hmj_plan_rollouts_dev.argtypes = [vp, dp, C.c_double, dp, dp, C.c_int, C.c_int, C.c_int, dp]
     lib.hmj_plan_argmin.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_int32)]
     lib.hmj_plan_fetch.argtypes = [vp, C.c_int, C.c_int, dp, dp, dp, dp, dp, dp]

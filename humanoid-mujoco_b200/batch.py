@@ -334,6 +334,24 @@ class HumanoidBatch:
                                          int(horizon), int(bool(record)), _p(ret), _p(fail)))
         return ret, fail.astype(bool)
 
+    def plan_rollouts_noisy(self, state, time, spline_times, spline_values, horizon, interpolation=2, xfrc_std=0.1, xfrc_rate=0.1,
+                            xfrc_noise=None, seed=0, first_global=0):
+        """Trajectory::NoisyRollout for every sample (hmj_plan_rollouts_noisy): OU wrench on every body."""
+        state = np.ascontiguousarray(state, dtype=np.float64)
+        st = np.ascontiguousarray(spline_times, dtype=np.float64)
+        sv = np.ascontiguousarray(spline_values, dtype=np.float64)
+        assert sv.shape == (self.n, st.shape[0], NU), sv.shape
+        nz = None
+        if xfrc_noise is not None:
+            nz = np.ascontiguousarray(xfrc_noise, dtype=np.float64)
+            assert nz.shape == (self.n, max(horizon - 1, 0), 90), nz.shape
+        ret = np.zeros(self.n)
+        fail = np.zeros(self.n, dtype=np.int32)
+        check(self.lib.hmj_plan_rollouts_noisy(self._h, _p(state), float(time), _p(st), _p(sv), st.shape[0], int(interpolation),
+                                               int(horizon), float(xfrc_std), float(xfrc_rate), _p(nz) if nz is not None else None,
+                                               int(seed) & (2**64 - 1), int(first_global), _p(ret), _p(fail)))
+        return ret, fail.astype(bool)
+
     def plan_iterate(self, state, time, spline_times, nominal_values, horizon, interpolation=2, noise=None, noise_std=0.0,
                      noise_std2=0.0, seed=0, iteration=0, first_global=0, record_dev: int | None = None, noise_std_vec=None):
         """Device half of one OptimizePolicy iteration (hmj_plan_iterate): enqueue only."""

@@ -2,6 +2,7 @@
 // Owns device buffers, derived lookup tables and one CUDA stream per batch; every entry point
 // returns an int status and never throws.  The product path: there is no CPU fallback — if CUDA
 // is unavailable every call fails with HMJ_ERR_CUDA.
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -47,6 +48,9 @@ struct hmj_batch_ {
   double* argmin_dev = nullptr;      // [2]
   double* nominal_dev = nullptr;     // [64][12] nominal spline values of hmj_plan_iterate
   double* stdvec_dev = nullptr;      // [64][12] per-parameter noise std (cross-entropy planner)
+  unsigned long long* seed_iter_dev = nullptr;   // [2] seed, call counter of the OU force noise
+  double* ou_noise_dev = nullptr; size_t ou_noise_cap = 0;   // injected unit normals [N][H-1][90]
+  unsigned long long ou_calls = 0;
   double* noise_dev = nullptr;       // [N][nnode][12] caller-provided noise (same capacity as spline_values_dev)
   double* record_dev = nullptr;      // [3 + 64*12] this rank's winner record
   double* select_dev = nullptr;      // [3 + 64*12] global winner record
@@ -305,7 +309,7 @@ static hmj_buffers_t pipe_view(const hmj_buffers_t& B, int start, int count, int
   const size_t s = (size_t)start;
   V.n = count;
   V.qpos += s * HMJ_NQ; V.qvel += s * HMJ_NV; V.time += s; V.warmstart += s * HMJ_NV; V.ctrl += s * HMJ_NU;
-  V.xfrc += s * 6; V.xfrc_body += s; V.params += s;
+  V.xfrc += s * 6; V.xfrc_body += s; V.xfrc_all += s * HMJ_NBODY * 6; V.params += s;
   V.geom_xpos += s * HMJ_NGEOM * 3; V.geom_xmat += s * HMJ_NGEOM * 9; V.cdof += s * HMJ_NV * 6; V.com += s * 3;
   V.xipos += s * HMJ_NBODY * 3; V.ximat += s * HMJ_NBODY * 9;
   V.qM += s * HMJ_NM; V.qfrc_smooth += s * HMJ_NV; V.euler_factor += s * HMJ_FAC_DOUBLES; V.sens += s * SENS_NUM; V.slots += s * HMJ_NSLOT * HMJ_SLOT_DOUBLES; V.slot_mask += s * 4;
@@ -456,6 +460,7 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
   ALLOC("ctrl", ctrl, N * HMJ_NU);
   ALLOC("xfrc", xfrc, N * 6);
   ALLOC("xfrc_body", xfrc_body, N);
+  ALLOC("xfrc_all", xfrc_all, N * HMJ_NBODY * 6);
   ALLOC("params", params, N);
   ALLOC("geom_xpos", geom_xpos, N * HMJ_NGEOM * 3);
   ALLOC("geom_xmat", geom_xmat, N * HMJ_NGEOM * 9);
@@ -489,7 +494,7 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
   ALLOC("trace", trace, N * 3);
   {
     int rc;
-    if ((rc = alloc_array(b, nullptr, &b->state_dev, HMJ_NSTATE + 1, false)) || (rc = alloc_array(b, nullptr, &b->nominal_dev, 64 * HMJ_NU, false)) || (rc = alloc_array(b, nullptr, &b->stdvec_dev, 64 * HMJ_NU, false)) ||
+    if ((rc = alloc_array(b, nullptr, &b->state_dev, HMJ_NSTATE + 1, false)) || (rc = alloc_array(b, nullptr, &b->nominal_dev, 64 * HMJ_NU, false)) || (rc = alloc_array(b, nullptr, &b->stdvec_dev, 64 * HMJ_NU, false)) || (rc = alloc_array(b, nullptr, &b->seed_iter_dev, 2, false)) ||
         (rc = alloc_array(b, nullptr, &b->record_dev, 3 + 64 * HMJ_NU, false)) || (rc = alloc_array(b, nullptr, &b->select_dev, 3 + 64 * HMJ_NU, false)) || (rc = alloc_array(b, nullptr, &b->spline_times_dev, 64, false)) ||
         (rc = alloc_array(b, "returns", &b->returns_dev, N)) || (rc = alloc_array(b, nullptr, &b->failure_dev, N)) ||
         (rc = alloc_array(b, "argmin", &b->argmin_dev, 2, false))) {
@@ -1317,11 +1322,15 @@ static int ensure_record(hmj_batch_t* b, int horizon) {
 // The launches of one batch of rollouts (Trajectory::NoisyRollout for every sample, trajectory.cc:100-210), no host data:
 // init from the state block, H-1 x [policy + smooth + residual/cost -> factor || collide -> solve + Euler], the final
 // mj_forward (sensors/residual only; ctrl keeps the last action, trajectory.cc:190-206), returns.
+struct RolloutNoise { double rate = 0, scale = 0; const double* noise_dev = nullptr; int first_global = 0; bool on = false; };
+
 static void enqueue_rollout_chain(hmj_batch_t* b, const double* values_dev, int nnode, int interpolation, int horizon, int record,
-                                  double* returns_dev, int32_t* failure_dev) {
+                                  double* returns_dev, int32_t* failure_dev, const RolloutNoise& ou = RolloutNoise()) {
   hmj_launch_plan_init(b->buf, b->state_dev, b->stream);
+  const int xf = ou.on ? HMJ_PLAN_XFRC : 0;
   for (int t = 0; t < horizon - 1; t++) {
-    hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, HMJ_PLAN_COST | HMJ_PLAN_POLICY, b->spline_times_dev, values_dev, nnode,
+    if (ou.on) hmj_launch_plan_ou(b->buf, t, horizon - 1, ou.rate, ou.scale, ou.noise_dev, b->seed_iter_dev, ou.first_global, b->stream);
+    hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, HMJ_PLAN_COST | HMJ_PLAN_POLICY | xf, b->spline_times_dev, values_dev, nnode,
                       interpolation, 1, b->stream, &b->solve_ctx);
     // the knot is recorded behind k_dyn (residual, cost) on the side stream; k_solve joins that stream before it moves the state
     if (record) hmj_launch_plan_record(b->buf, b->rec, t, b->solve_ctx.side[0]);
@@ -1329,7 +1338,7 @@ static void enqueue_rollout_chain(hmj_batch_t* b, const double* values_dev, int 
     hmj_launch_collide(b->tab_dev, b->buf, b->stream, false);
     hmj_launch_solve(b->tab_dev, b->buf, 1, b->stream, &b->solve_ctx, false);
   }
-  hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, HMJ_PLAN_COST, nullptr, nullptr, 0, 0, 0, b->stream);
+  hmj_launch_smooth(b->tab_dev, b->buf, b->task_dev, HMJ_PLAN_COST | xf, nullptr, nullptr, 0, 0, 0, b->stream);
   if (record) hmj_launch_plan_record(b->buf, b->rec, horizon - 1, b->stream);
   hmj_launch_plan_finish(b->buf, horizon, returns_dev, failure_dev, b->stream);
 }
@@ -1435,6 +1444,63 @@ extern "C" int hmj_plan_rollouts(hmj_batch_t* b, const double* state, double tim
   rc = enqueue_rollouts(b, state, time, spline_times, b->spline_values_dev, nnode, interpolation, horizon, record,
                         b->returns_dev, b->failure_dev);
   if (rc) return rc;
+  if ((rc = d2h(b, total_return, b->returns_dev, (size_t)b->n * 8)) || (rc = d2h(b, failure, b->failure_dev, (size_t)b->n * 4))) return rc;
+  CK(cudaStreamSynchronize(b->stream));
+  CK(cudaGetLastError());
+  return HMJ_OK;
+}
+
+/* Trajectory::NoisyRollout for every sample (mjpc/trajectory.cc:100-210 with xfrc_std > 0; RobustPlanner::OptimizePolicy,
+ * mjpc/planners/robust/robust_planner.cc:96-151): the rollouts of hmj_plan_rollouts with an Ornstein-Uhlenbeck wrench on
+ * every body, x <- rate x + N(0, scale), rate = exp(-dt / xfrc_rate), scale = xfrc_std sqrt(1 - rate^2), refreshed before every
+ * step.  xfrc_noise [N][H-1][90] = unit normals injected by the caller (NULL: drawn on the device from (seed, call counter,
+ * first_global + sample)).  dt is the timestep of env 0's parameters. */
+extern "C" int hmj_plan_rollouts_noisy(hmj_batch_t* b, const double* state, double time, const double* spline_times,
+                                       const double* spline_values, int nnode, int interpolation, int horizon, double xfrc_std,
+                                       double xfrc_rate, const double* xfrc_noise, unsigned long long seed, int first_global,
+                                       double* total_return, int32_t* failure) {
+  if (!b || !state || !spline_times || !spline_values || !total_return || !(xfrc_rate > 0) || xfrc_std < 0)
+    return fail(HMJ_ERR_ARG, "bad argument to plan_rollouts_noisy%s");
+  CK(cudaSetDevice(b->device));
+  int rc = ensure_values(b, nnode);
+  if (rc) return rc;
+  const size_t nvals = (size_t)b->n * nnode * HMJ_NU;
+  CK(cudaMemcpyAsync(b->spline_values_dev, spline_values, nvals * 8, cudaMemcpyHostToDevice, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  if ((rc = upload_plan_inputs(b, state, time, spline_times, nnode, horizon))) return rc;
+  hmj_params_t p0;
+  CK(cudaMemcpyAsync(&p0, b->buf.params, sizeof(p0), cudaMemcpyDeviceToHost, b->stream));
+  const unsigned long long si[2] = {seed, b->ou_calls++};
+  CK(cudaMemcpyAsync(b->seed_iter_dev, si, sizeof(si), cudaMemcpyHostToDevice, b->stream));
+  const size_t nn = (size_t)b->n * (horizon > 1 ? horizon - 1 : 0) * HMJ_NBODY * 6;
+  if (xfrc_noise && nn) {
+    if (b->ou_noise_cap < nn) {
+      CK(cudaStreamSynchronize(b->stream));
+      if (b->ou_noise_dev) {
+        for (size_t k = 0; k < b->allocs.size(); k++)
+          if (b->allocs[k] == (void*)b->ou_noise_dev) { b->allocs.erase(b->allocs.begin() + k); break; }
+        cudaFree(b->ou_noise_dev);
+        b->ou_noise_dev = nullptr;
+      }
+      void* p = nullptr;
+      CK(cudaMalloc(&p, nn * 8));
+      b->allocs.push_back(p);
+      b->ou_noise_dev = (double*)p;
+      b->ou_noise_cap = nn;
+    }
+    CK(cudaMemcpyAsync(b->ou_noise_dev, xfrc_noise, nn * 8, cudaMemcpyHostToDevice, b->stream));
+  }
+  CK(cudaStreamSynchronize(b->stream));
+  RolloutNoise ou;
+  ou.on = true;
+  ou.rate = exp(-p0.timestep / xfrc_rate);
+  ou.scale = xfrc_std * sqrt(1.0 - ou.rate * ou.rate);
+  ou.noise_dev = xfrc_noise ? b->ou_noise_dev : nullptr;
+  ou.first_global = first_global;
+  enqueue_rollout_chain(b, b->spline_values_dev, nnode, interpolation, horizon, 0, b->returns_dev, b->failure_dev, ou);
+  b->warmed = true;
+  const int nl = 1 + (horizon - 1) * 11 + 2 + 1;
+  b->launches += nl; b->host_launches += nl;
   if ((rc = d2h(b, total_return, b->returns_dev, (size_t)b->n * 8)) || (rc = d2h(b, failure, b->failure_dev, (size_t)b->n * 4))) return rc;
   CK(cudaStreamSynchronize(b->stream));
   CK(cudaGetLastError());

@@ -25,9 +25,41 @@ __global__ void k_plan_init(hmj_buffers_t B, const double* __restrict__ state) {
   // the reference leaves the worker's stale ctrl there, trajectory.cc:186-198)
   for (int k = 0; k < HMJ_NU; k++) B.ctrl[(size_t)env * HMJ_NU + k] = 0.0;
   B.xfrc_body[env] = 0;
+  // deterministic stand-in for the worker's stale xfrc_applied (NoisyRollout never clears it, trajectory.cc:100-155)
+  for (int k = 0; k < HMJ_NBODY * 6; k++) B.xfrc_all[(size_t)env * HMJ_NBODY * 6 + k] = 0.0;
   B.time[env] = time;
   B.cost_sum[env] = 0.0;
   B.status[env] = 0;
+}
+
+// Ornstein-Uhlenbeck force perturbation of Trajectory::NoisyRollout (mjpc/trajectory.cc:147-155), step t of the rollout:
+// xfrc_applied[i] = rate * xfrc_applied[i] + N(0, scale) for all 6 * nbody entries, applied after the policy and before the
+// step.  `noise` [N][nsteps][90] holds unit normals injected by the caller (parity tests); NULL draws them from the
+// counter-based stream (seed, call counter, global sample, t * 90 + k).  Thread per (sample, entry).
+__global__ void k_plan_ou(hmj_buffers_t B, int t, int nsteps, double rate, double scale, const double* __restrict__ noise,
+                          const unsigned long long* __restrict__ seed_iter, int first_global) {
+  const int id = blockIdx.x * blockDim.x + threadIdx.x;
+  const int per = HMJ_NBODY * 6;
+  if (id >= B.n * per) return;
+  const int env = id / per, k = id - env * per;
+  double z;
+  if (noise) {
+    z = noise[((size_t)env * nsteps + t) * per + k];
+  } else {
+    const uint64_t key = hmj_splitmix64(seed_iter[0] ^ hmj_splitmix64(seed_iter[1] + 0x0B0B0B0B0B0B0B0Bull));
+    const uint32_t c = 2u * (uint32_t)(t * per + k);
+    const double u1 = 1.0 - hmj_rand_u01(key, (uint32_t)(first_global + env), c);
+    const double u2 = hmj_rand_u01(key, (uint32_t)(first_global + env), c + 1u);
+    z = sqrt(-2.0 * log(u1)) * cospi(2.0 * u2);
+  }
+  double* x = B.xfrc_all + (size_t)env * per + k;
+  *x = rate * (*x) + z * scale;
+}
+
+void hmj_launch_plan_ou(hmj_buffers_t buf, int t, int nsteps, double rate, double scale, const double* noise_dev,
+                        const unsigned long long* seed_iter_dev, int first_global, cudaStream_t stream) {
+  const int tot = buf.n * HMJ_NBODY * 6;
+  k_plan_ou<<<(tot + 255) / 256, 256, 0, stream>>>(buf, t, nsteps, rate, scale, noise_dev, seed_iter_dev, first_global);
 }
 
 __global__ void k_plan_record(hmj_buffers_t B, hmj_record_t R, int t) {

@@ -91,6 +91,7 @@ struct hmj_buffers_t {
   double* ctrl;       // [N][12]
   double* xfrc;       // [N][6]   Cartesian wrench on one body (cpu_env.py:618-654)
   int32_t* xfrc_body; // [N]
+  double* xfrc_all;   // [N][15][6] wrench on EVERY body (planner robustness rollouts: OU noise, mjpc/trajectory.cc:147-155); used with HMJ_PLAN_XFRC
   hmj_params_t* params;  // [N]
   // ---- cross-kernel scratch (L2 resident)
   double* geom_xpos;  // [N][10][3]
@@ -337,6 +338,7 @@ void hmj_launch_solve(const hmj_tables_t* tab, hmj_buffers_t buf, int integrate,
 // plan_mode bits for hmj_launch_smooth
 #define HMJ_PLAN_COST 1    /* sensors -> residual -> cost accumulation */
 #define HMJ_PLAN_POLICY 2  /* ctrl from the spline policy at data time */
+#define HMJ_PLAN_XFRC 4    /* k_dyn also applies the per-body wrenches of xfrc_all */
 
 // trajectory recording buffers (optional), layout [H][N][dim]
 struct hmj_record_t {
@@ -350,6 +352,8 @@ struct hmj_record_t {
 };
 
 void hmj_launch_plan_init(hmj_buffers_t buf, const double* state_time_dev, cudaStream_t stream);
+void hmj_launch_plan_ou(hmj_buffers_t buf, int t, int nsteps, double rate, double scale, const double* noise_dev,
+                        const unsigned long long* seed_iter_dev, int first_global, cudaStream_t stream);
 void hmj_launch_plan_candidates(const hmj_tables_t* tab, int n, int nnode, const double* nominal_dev, const double* noise_dev,
                                 double std0, double std1, unsigned long long seed, unsigned long long iteration, int first_global,
                                 double* values_dev, cudaStream_t stream, const double* std_vec_dev = nullptr);

@@ -502,6 +502,20 @@ k_dyn(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* __r
         ext += fb;
       }
     }
+    if (plan_mode & HMJ_PLAN_XFRC) {   // xfrc_applied on every body (mj_xfrcAccumulate): force and torque at the body's CoM
+      const double* wa = B.xfrc_all + (size_t)env * HMJ_NBODY * 6;
+      for (int bb = 1; bb < HMJ_NBODY; bb++) {
+        if (!((T->body_dofmask[bb] >> d) & 1u)) continue;
+        const double* w = wa + bb * 6;
+        double off[3] = {S.xipos[bb][0] - S.com[0], S.xipos[bb][1] - S.com[1], S.xipos[bb][2] - S.com[2]};
+        double tmp[3];
+        d_cross(tmp, S.cdof[d], off);
+        const double fa = (S.cdof[d][3] + tmp[0]) * w[0] + (S.cdof[d][4] + tmp[1]) * w[1] + (S.cdof[d][5] + tmp[2]) * w[2];
+        const double fb = S.cdof[d][0] * w[3] + S.cdof[d][1] * w[4] + S.cdof[d][2] * w[5];
+        f += fa; f += fb;
+        ext += fa; ext += fb;
+      }
+    }
     B.qfrc_smooth[(size_t)env * HMJ_NV + d] = f;
     B.qfrc_ext[(size_t)env * HMJ_NV + d] = ext;
   }

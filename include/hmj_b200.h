@@ -165,6 +165,15 @@ int hmj_plan_set_task(hmj_batch_t* b, int nterm, const int32_t* dim, const int32
 int hmj_plan_rollouts(hmj_batch_t* b, const double* state, double time, const double* spline_times,
                       const double* spline_values, int nnode, int interpolation, int horizon, int record,
                       double* total_return, int32_t* failure);
+/* Trajectory::NoisyRollout (mjpc/trajectory.cc:100-210 with xfrc_std > 0) for every sample: the same rollouts with an
+ * Ornstein-Uhlenbeck wrench on EVERY body, refreshed before each step: x <- rate x + N(0, scale), rate = exp(-dt / xfrc_rate),
+ * scale = xfrc_std sqrt(1 - rate^2) (:147-155).  This is the robustness pass of RobustPlanner::OptimizePolicy
+ * (mjpc/planners/robust/robust_planner.cc:96-151).  xfrc_noise [N][H-1][90]: unit normals injected by the caller (NULL:
+ * drawn on the device from the counter-based stream (seed, call counter, first_global + sample)). */
+int hmj_plan_rollouts_noisy(hmj_batch_t* b, const double* state, double time, const double* spline_times,
+                            const double* spline_values, int nnode, int interpolation, int horizon, double xfrc_std,
+                            double xfrc_rate, const double* xfrc_noise, unsigned long long seed, int first_global,
+                            double* total_return, int32_t* failure);
 /* device-resident variant: spline_values_dev [N][P][12], returns_dev [N]; enqueue only */
 int hmj_plan_rollouts_dev(hmj_batch_t* b, const double* state, double time, const double* spline_times,
                           const double* spline_values_dev, int nnode, int interpolation, int horizon,

@@ -236,3 +236,41 @@ int orc_rollout(const hmj_model_t* m, const hmj_params_t* p, const double* state
   *total_return = tot / (horizon > 1 ? horizon : 1);
   return 0;
 }
+
+/* Trajectory::NoisyRollout with xfrc_std > 0 (mjpc/trajectory.cc:100-210, perturbation :147-155): orc_rollout with an
+ * Ornstein-Uhlenbeck wrench on every body; `noise` [horizon-1][6*nbody] are the unit normals (the reference draws them from an
+ * entropy-seeded absl::BitGen).  Returns the failure flag; total_return as UpdateReturn (:312-326). */
+int orc_rollout_noisy(const hmj_model_t* m, const hmj_params_t* p, const double* state, double time,
+                      const double* spline_times, const double* spline_values, int nnode, int interpolation,
+                      int horizon, double xfrc_std, double xfrc_rate, const double* noise, double* total_return) {
+  orc_data_t dd;
+  orc_data_t* d = &dd;
+  const int nu = HMJ_NU;
+  orc_reset_data(m, d);
+  memcpy(d->qpos, state, HMJ_NQ * sizeof(double));
+  memcpy(d->qvel, state + HMJ_NQ, HMJ_NV * sizeof(double));
+  d->time = time;
+  const double rate = exp(-p->timestep / xfrc_rate);
+  const double scale = xfrc_std * sqrt(1 - rate * rate);
+  double tot = 0;
+  for (int t = 0; t < horizon - 1; t++) {
+    double a[HMJ_NU];
+    orc_spline_sample(spline_times, spline_values, nnode, nu, interpolation, d->time, a);
+    for (int i = 0; i < nu; i++) {
+      if (a[i] < m->act_ctrlrange[i][0]) a[i] = m->act_ctrlrange[i][0];
+      else if (a[i] > m->act_ctrlrange[i][1]) a[i] = m->act_ctrlrange[i][1];
+    }
+    memcpy(d->ctrl, a, nu * sizeof(double));
+    if (xfrc_std > 0) {
+      double* x = &d->xfrc_applied[0][0];
+      for (int i = 0; i < 6 * HMJ_NBODY; i++) x[i] = rate * x[i] + noise[(size_t)t * 6 * HMJ_NBODY + i] * scale;
+    }
+    orc_step(m, p, d);
+    tot += orc_cost_value(m, d->residual);
+    if (d->status) { *total_return = 1.0e6; return 1; }
+  }
+  orc_forward(m, p, d);
+  tot += orc_cost_value(m, d->residual);
+  *total_return = tot / (horizon > 1 ? horizon : 1);
+  return 0;
+}

@@ -169,6 +169,9 @@ double orc_rollout_batch(const hmj_model_t* m, const hmj_params_t* p, const doub
 /* mjd_transitionFD for one knot (hmj_oracle_fd.c): A [36][36], B [36][12], C [28][36], D [28][12] */
 int orc_transition_fd(const hmj_model_t* m, const hmj_params_t* p, const double* x, const double* u, double time,
                       const double* warmstart, double eps, int centered, double* A, double* B, double* C, double* D);
+int orc_rollout_noisy(const hmj_model_t* m, const hmj_params_t* p, const double* state, double time,
+                      const double* spline_times, const double* spline_values, int nnode, int interpolation,
+                      int horizon, double xfrc_std, double xfrc_rate, const double* noise, double* total_return);
 /* mj_inverse for a given acceleration (hmj_oracle_fd.c) */
 void orc_inverse(const hmj_model_t* m, const hmj_params_t* p, orc_data_t* d, const double* qacc, double* qfrc_inverse);
 int orc_sizeof_data(void);

@@ -140,6 +140,18 @@ class Oracle:
         out["failure"] = bool(fail)
         return out
 
+    def rollout_noisy(self, state, time, spline_times, spline_values, horizon, interpolation, xfrc_std, xfrc_rate, noise):
+        """Trajectory::NoisyRollout with injected unit normals `noise` [horizon-1][90]: (total_return, failure)."""
+        state = np.ascontiguousarray(state, dtype=np.float64)
+        st = np.ascontiguousarray(spline_times, dtype=np.float64)
+        sv = np.ascontiguousarray(spline_values, dtype=np.float64)
+        nz = np.ascontiguousarray(noise, dtype=np.float64)
+        tot = C.c_double(0)
+        fail = self.lib.orc_rollout_noisy(_ptr(self.model), _ptr(self.params), _ptr(state), C.c_double(time), _ptr(st), _ptr(sv),
+                                          st.shape[0], int(interpolation), int(horizon), C.c_double(xfrc_std),
+                                          C.c_double(xfrc_rate), _ptr(nz), C.byref(tot))
+        return tot.value, bool(fail)
+
     def inverse(self, qacc=None):
         """mj_inverse at the current state for the given acceleration (zeros by default): qfrc_inverse [18]."""
         nv = DEFINES["HMJ_NV"]

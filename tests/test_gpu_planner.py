@@ -358,3 +358,42 @@ def test_cross_entropy_planner_matches_mirror(hmj, oracle):
     z = (pl.candidate_values[1:] - pl.candidate_values[0]).reshape(-1, 36)
     inside = np.abs(pl.candidate_values[1:]).max() < pl.ctrlrange[:, 1].max()
     assert 0.15 < z.std() < 0.25 if inside else True
+
+
+def test_noisy_rollouts_and_robust_planner(hmj, oracle):
+    """Trajectory::NoisyRollout (OU wrench on every body, trajectory.cc:147-155) against the oracle with injected normals,
+    then RobustPlanner.OptimizePolicy (robust_planner.cc:96-151): the candidate with the best mean noisy return wins."""
+    state, time = settled_task_state(oracle)
+    n, H = 24, 18
+    pl = hmj.SamplingPlanner(num_trajectory=n, device=0, seed=6)
+    pl.SetState(state[:19], state[19:], time)
+    rp = hmj.RobustPlanner(pl, ncandidates=4, nrepetitions=3, xfrc_std=0.5, xfrc_rate=0.1)
+    rng = np.random.default_rng(8)
+    scale = 0.5 * (pl.ctrlrange[:, 1] - pl.ctrlrange[:, 0])
+    noise = rng.standard_normal((n, 3, 12)) * scale * 0.05
+    xnoise = rng.standard_normal((12, H - 1, 90))
+    rp.OptimizePolicy(H, noise=noise, xfrc_noise=xnoise)
+    # the four candidates are the delegate's four best; each noisy rollout equals the oracle's
+    ret = pl.total_return
+    assert np.array_equal(rp.candidates, np.argsort(ret, kind="stable")[:4])
+    ref = np.zeros(12)
+    for k in range(12):
+        c = rp.candidates[k // 3]
+        ref[k], fail = oracle.rollout_noisy(state, time, pl.candidate_times, pl.candidate_values[c], H, pl.interpolation_,
+                                            0.5, 0.1, xnoise[k])
+        assert not fail
+    rel = np.abs(rp.noisy_return - ref) / np.maximum(np.abs(ref), 1.0)
+    assert np.median(rel) < 1e-9 and (rel < TOL_RETURN).sum() >= 11, rel
+    # the wrench matters (the same candidate under three different noise draws gives three different returns)
+    assert len(np.unique(rp.noisy_return[:3])) == 3 and abs(rp.noisy_return[0] - ret[rp.candidates[0]]) > 1e-9
+    want = int(np.argmin(ref.reshape(4, 3).mean(axis=1)))
+    gap = np.diff(np.sort(ref.reshape(4, 3).mean(axis=1)))[0]
+    if (rel < 1e-9).all() and gap > GAP:
+        assert rp.best_candidate == want
+    assert np.allclose(rp.scores, rp.noisy_return.reshape(4, 3).mean(axis=1), rtol=1e-12)
+    assert np.array_equal(pl.policy.plan.arrays()[1], pl.candidate_values[rp.candidates[rp.best_candidate]])
+    # device-drawn OU noise: runs, differs between calls, finite
+    a, fa = rp.batch.plan_rollouts_noisy(state, time, pl.candidate_times, np.repeat(pl.candidate_values[:4], 3, axis=0), H, 2, 0.5, 0.1, None, seed=1)
+    b2, _ = rp.batch.plan_rollouts_noisy(state, time, pl.candidate_times, np.repeat(pl.candidate_values[:4], 3, axis=0), H, 2, 0.5, 0.1, None, seed=1)
+    assert np.all(np.isfinite(a)) and not fa.any() and not np.array_equal(a, b2)
+    rp.close()
