@@ -5,6 +5,14 @@ import numpy as np
 import pytest
 
 
+@pytest.fixture(autouse=True)
+def _restore_oracle_params(oracle):
+    """The oracle fixture is shared by the whole session: put the default parameters back after each test here."""
+    yield
+    oracle.lib.orc_default_params(oracle.model.ctypes.data, oracle.params.ctypes.data)
+    oracle.reset()
+
+
 def plan_state(oracle, nsteps=50, timestep=0.02):
     oracle.reset()
     oracle.lib.orc_default_params(oracle.model.ctypes.data, oracle.params.ctypes.data)

@@ -6,6 +6,14 @@ import pytest
 from conftest import make_scenarios
 
 
+@pytest.fixture(autouse=True)
+def _restore_oracle_params(oracle):
+    """The oracle fixture is shared by the whole session: put the default parameters back after each test here."""
+    yield
+    oracle.lib.orc_default_params(oracle.model.ctypes.data, oracle.params.ctypes.data)
+    oracle.reset()
+
+
 def test_oracle_inverse_inverts_forward(oracle):
     """mj_inverse(mj_forward(x, u).qacc) returns the applied generalized forces: qfrc_actuator (+ J' xfrc), to the
     solver's tolerance."""
