@@ -258,6 +258,9 @@ static void build_tables(const hmj_model_t* m, hmj_tables_t* t) {
       t->vx[adr + i] = m->mesh_vert[va + src][0];
       t->vy[adr + i] = m->mesh_vert[va + src][1];
       t->vz[adr + i] = m->mesh_vert[va + src][2];
+      t->dvx[adr + i] = (double)t->vx[adr + i];
+      t->dvy[adr + i] = (double)t->vy[adr + i];
+      t->dvz[adr + i] = (double)t->vz[adr + i];
     }
     adr += npad;
   }

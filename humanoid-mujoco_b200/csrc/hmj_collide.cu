@@ -583,11 +583,16 @@ __device__ __forceinline__ int pack_task(int k, int ord, int r, int cmin, int s)
   return k | (ord << 6) | (r << 9) | (cmin << 12) | (s << 15);
 }
 
-__device__ __forceinline__ void stage_hulls(const hmj_tables_t* __restrict__ T, double* sx, double* sy, double* sz) {
-  const int nvert = T->mesh_adr[HMJ_NMESH];
-  for (int i = threadIdx.x; i < nvert; i += blockDim.x) {
-    sx[i] = (double)T->vx[i]; sy[i] = (double)T->vy[i]; sz[i] = (double)T->vz[i];
-  }
+// vertices [first, first + count) of the fp64 tables -> shared memory at the same offsets minus `first` (count and first are
+// multiples of 2: every mesh is padded to a multiple of 4), 16 bytes per thread and step
+__device__ __forceinline__ void stage_hulls(const hmj_tables_t* __restrict__ T, double* sx, double* sy, double* sz, int first, int count) {
+  const double2* gx = reinterpret_cast<const double2*>(T->dvx + first);
+  const double2* gy = reinterpret_cast<const double2*>(T->dvy + first);
+  const double2* gz = reinterpret_cast<const double2*>(T->dvz + first);
+  double2* tx = reinterpret_cast<double2*>(sx);
+  double2* ty = reinterpret_cast<double2*>(sy);
+  double2* tz = reinterpret_cast<double2*>(sz);
+  for (int i = threadIdx.x; i < (count >> 1); i += blockDim.x) { tx[i] = gx[i]; ty[i] = gy[i]; tz[i] = gz[i]; }
   __syncthreads();
 }
 
@@ -665,11 +670,12 @@ k_broad(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int npad) {
   }
   // ---- hfield pair.  NOTE: k_broad is launched with hfield pairs in their own CTAs (npad is a multiple of
   // BROAD_THREADS), so the barrier inside stage_hulls is reached by whole CTAs only.
-  stage_hulls(T, sx, sy, sz);
+  // this CTA works on ONE pair, i.e. one hull: only that hull is staged (at offset 0)
+  stage_hulls(T, sx, sy, sz, T->mesh_adr[M.geom_meshid[g2]], T->mesh_npad[M.geom_meshid[g2]]);
   const double* size1 = M.hfield_size;
   const int nrow = M.hfield_nrow, ncol = M.hfield_ncol;
   const float* data = B.params[env].hfield_data;
-  const Hull h2 = {T->mesh_adr[M.geom_meshid[g2]], T->mesh_npad[M.geom_meshid[g2]]};
+  const Hull h2 = {0, T->mesh_npad[M.geom_meshid[g2]]};
   Frame f2;
   hfield_rel_frame(f2, gx, gm, g2);
   bool active = in;
@@ -943,7 +949,7 @@ k_narrow(const hmj_tables_t* __restrict__ T, hmj_buffers_t B) {
 #ifdef HMJ_PHASE_PROF
   const long long w_t0 = clock64();
 #endif
-  stage_hulls(T, sx, sy, sz);
+  stage_hulls(T, sx, sy, sz, 0, T->mesh_adr[HMJ_NMESH]);
 #ifdef HMJ_PHASE_PROF
   const long long w_t1 = clock64();
 #endif

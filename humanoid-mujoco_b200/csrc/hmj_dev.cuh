@@ -61,6 +61,10 @@ struct hmj_tables_t {
   float vx[HMJ_MAXVERT + HMJ_NMESH * HMJ_MESH_PAD];
   float vy[HMJ_MAXVERT + HMJ_NMESH * HMJ_MESH_PAD];
   float vz[HMJ_MAXVERT + HMJ_NMESH * HMJ_MESH_PAD];
+  // the same vertices as fp64 (what the kernels stage in shared memory: a plain 16-byte copy, no conversion)
+  alignas(16) double dvx[HMJ_MAXVERT + HMJ_NMESH * HMJ_MESH_PAD];
+  alignas(16) double dvy[HMJ_MAXVERT + HMJ_NMESH * HMJ_MESH_PAD];
+  alignas(16) double dvz[HMJ_MAXVERT + HMJ_NMESH * HMJ_MESH_PAD];
   double mesh_lo[HMJ_NMESH + 1][3];  // local bounding box of each hull (exact min / max of its vertices)
   double mesh_hi[HMJ_NMESH + 1][3];
   // lower-triangle index maps for the 18x18 dense routines
