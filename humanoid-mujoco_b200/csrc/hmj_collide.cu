@@ -40,7 +40,11 @@
 #define NARROW_MIN_CTAS 2
 #endif
 
-struct Supp { double v[3], v1[3], v2[3]; };
+// A support point of the Minkowski difference.  Its two witnesses (the support points of the two shapes) are NOT carried
+// through the iteration: only the vertex indices are, and the points are recomputed — with the very expression that
+// produced them — in the one place that needs them (the contact position at the end of a query).  18 doubles of per-lane
+// state less for the three portal vertices, 6 more for the interior point's witnesses.
+struct Supp { double v[3]; int i1, i2; };
 
 // ------------------------------------------------------------------ libccd vec3 helpers
 __device__ __forceinline__ bool c_is_zero(double v) { return fabs(v) < CCD_EPS; }
@@ -87,7 +91,7 @@ __device__ __forceinline__ double c_dist2(const double* a, const double* b) {
 }
 
 __device__ __forceinline__ void cp3(double* d, const double* s) { d[0] = s[0]; d[1] = s[1]; d[2] = s[2]; }
-__device__ __forceinline__ void cps(Supp& d, const Supp& s) { cp3(d.v, s.v); cp3(d.v1, s.v1); cp3(d.v2, s.v2); }
+__device__ __forceinline__ void cps(Supp& d, const Supp& s) { cp3(d.v, s.v); d.i1 = s.i1; d.i2 = s.i2; }
 
 // ------------------------------------------------------------------ support functions
 // Hull vertices of all meshes live in shared memory as fp64 SoA (sx|sy|sz), each mesh starting at an even
@@ -99,7 +103,7 @@ struct Frame { double pos[3]; double mat[9]; };
 
 __device__ __forceinline__ void mesh_support(const double* __restrict__ sx, const double* __restrict__ sy,
                                              const double* __restrict__ sz, Hull h, const Frame& f, const double* dir,
-                                             double* out) {
+                                             double* out, int* idx = nullptr) {
   const double* mat = f.mat;
   const double ld0 = mat[0] * dir[0] + mat[3] * dir[1] + mat[6] * dir[2];
   const double ld1 = mat[1] * dir[0] + mat[4] * dir[1] + mat[7] * dir[2];
@@ -121,7 +125,18 @@ __device__ __forceinline__ void mesh_support(const double* __restrict__ sx, cons
     if (vb > b1) { b1 = vb; i1 = 2 * j + 1; }
   }
   if (b1 > b0 || (b1 == b0 && i1 < i0)) i0 = i1;
+  if (idx) *idx = i0;
   const double p0 = sx[h.base + i0], p1 = sy[h.base + i0], p2 = sz[h.base + i0];
+  out[0] = (mat[0] * p0 + mat[1] * p1 + mat[2] * p2) + f.pos[0];
+  out[1] = (mat[3] * p0 + mat[4] * p1 + mat[5] * p2) + f.pos[1];
+  out[2] = (mat[6] * p0 + mat[7] * p1 + mat[8] * p2) + f.pos[2];
+}
+
+// vertex i of hull h in the frame f: the tail of mesh_support, for recomputing a witness from its index (same bits)
+__device__ __forceinline__ void mesh_point(const double* __restrict__ sx, const double* __restrict__ sy,
+                                           const double* __restrict__ sz, Hull h, const Frame& f, int i, double* out) {
+  const double* mat = f.mat;
+  const double p0 = sx[h.base + i], p1 = sy[h.base + i], p2 = sz[h.base + i];
   out[0] = (mat[0] * p0 + mat[1] * p1 + mat[2] * p2) + f.pos[0];
   out[1] = (mat[3] * p0 + mat[4] * p1 + mat[5] * p2) + f.pos[1];
   out[2] = (mat[6] * p0 + mat[7] * p1 + mat[8] * p2) + f.pos[2];
@@ -134,7 +149,7 @@ __device__ __forceinline__ void mesh_support(const double* __restrict__ sx, cons
 #define COOP_G 4
 __device__ __forceinline__ void mesh_support_coop(const double* __restrict__ sx, const double* __restrict__ sy,
                                                   const double* __restrict__ sz, Hull h, const Frame& f, const double* dir,
-                                                  double* out, const int* src, int lane) {
+                                                  double* out, int* idx, const int* src, int lane) {
   const unsigned FULL = 0xffffffffu;
   const double* mat = f.mat;
   const double my0 = mat[0] * dir[0] + mat[3] * dir[1] + mat[6] * dir[2];
@@ -192,6 +207,7 @@ __device__ __forceinline__ void mesh_support_coop(const double* __restrict__ sx,
   }
   if (mine >= 0) {
     if (mine == 0x7fffffff) mine = 0;
+    *idx = mine;
     const double p0 = sx[h.base + mine], p1 = sy[h.base + mine], p2 = sz[h.base + mine];
     out[0] = (mat[0] * p0 + mat[1] * p1 + mat[2] * p2) + f.pos[0];
     out[1] = (mat[3] * p0 + mat[4] * p1 + mat[5] * p2) + f.pos[1];
@@ -241,16 +257,33 @@ __device__ __forceinline__ void mesh_aabb(const double* __restrict__ sx, const d
 // Height-field prism: three top vertices (strip order) over a flat bottom at z = zb with the same (x, y).
 struct Prism { double t[3][3]; double zb; };
 
-__device__ __forceinline__ void prism_support(const Prism& o, const double* dir, double* out) {
+// returns the vertex code: column i (0..2) + 3 when it is a top vertex
+__device__ __forceinline__ int prism_support(const Prism& o, const double* dir, double* out) {
   const bool top = !(dir[2] < 0);
   const double za = top ? o.t[0][2] : o.zb, zb = top ? o.t[1][2] : o.zb, zc = top ? o.t[2][2] : o.zb;
   double best = o.t[0][0] * dir[0] + o.t[0][1] * dir[1] + za * dir[2];
+  int code = 0;
   out[0] = o.t[0][0]; out[1] = o.t[0][1]; out[2] = za;
   double t = o.t[1][0] * dir[0] + o.t[1][1] * dir[1] + zb * dir[2];
-  if (t > best) { best = t; out[0] = o.t[1][0]; out[1] = o.t[1][1]; out[2] = zb; }
+  if (t > best) { best = t; code = 1; out[0] = o.t[1][0]; out[1] = o.t[1][1]; out[2] = zb; }
   t = o.t[2][0] * dir[0] + o.t[2][1] * dir[1] + zc * dir[2];
-  if (t > best) { best = t; out[0] = o.t[2][0]; out[1] = o.t[2][1]; out[2] = zc; }
+  if (t > best) { best = t; code = 2; out[0] = o.t[2][0]; out[1] = o.t[2][1]; out[2] = zc; }
+  return code + (top ? 3 : 0);
 }
+__device__ __forceinline__ void prism_point(const Prism& o, int code, double* out) {
+  const int i = code >= 3 ? code - 3 : code;
+  out[0] = o.t[i][0]; out[1] = o.t[i][1]; out[2] = code >= 3 ? o.t[i][2] : o.zb;
+}
+
+// Recomputation of witnesses from their indices: the two shapes of a query
+struct WitMesh {   // mesh vs mesh
+  const double *sx, *sy, *sz; const Frame *f1, *f2; Hull h1, h2;
+  __device__ __forceinline__ void get(int i1, int i2, double* v1, double* v2) const {
+    mesh_point(sx, sy, sz, h1, *f1, i1, v1);
+    mesh_point(sx, sy, sz, h2, *f2, i2, v2);
+  }
+  __device__ __forceinline__ void centers(double* c1, double* c2) const { cp3(c1, f1->pos); cp3(c2, f2->pos); }
+};
 
 __device__ __forceinline__ void prism_center(const Prism& o, double* c) {
   c[0] = c[1] = c[2] = 0;
@@ -260,6 +293,15 @@ __device__ __forceinline__ void prism_center(const Prism& o, double* c) {
   for (int i = 0; i < 3; i++) { c[0] += o.t[i][0]; c[1] += o.t[i][1]; c[2] += o.t[i][2]; }  // top vertices 3..5
   c[0] *= 1.0 / 6.0; c[1] *= 1.0 / 6.0; c[2] *= 1.0 / 6.0;
 }
+
+struct WitPrism {   // height-field prism vs mesh
+  const double *sx, *sy, *sz; const Prism* p; const Frame* f2; Hull h2;
+  __device__ __forceinline__ void get(int i1, int i2, double* v1, double* v2) const {
+    prism_point(*p, i1, v1);
+    mesh_point(sx, sy, sz, h2, *f2, i2, v2);
+  }
+  __device__ __forceinline__ void centers(double* c1, double* c2) const { prism_center(*p, c1); cp3(c2, f2->pos); }
+};
 
 // ------------------------------------------------------------------ MPR pieces (libccd mpr.c)
 __device__ __forceinline__ void portal_dir(const Supp& p1, const Supp& p2, const Supp& p3, double* dir) {
@@ -348,9 +390,11 @@ __device__ __forceinline__ double point_tri_dist2(const double* P, const double*
   return dist;
 }
 
-// p0v/p0v1/p0v2: the interior point of the Minkowski difference and its two witnesses
-__device__ __forceinline__ void find_pos(const double* p0v, const double* p0v1, const double* p0v2, const Supp& p1,
-                                         const Supp& p2, const Supp& p3, double* pos) {
+// p0v: the interior point of the Minkowski difference; its witnesses (the two centres) and those of the portal vertices
+// are recomputed from W
+template <typename W>
+__device__ __forceinline__ void find_pos(const double* p0v, const W& wit, const Supp& p1, const Supp& p2, const Supp& p3,
+                                         double* pos) {
   double dir[3], b0, b1, b2, b3, sum, inv, vec[3], q1[3] = {0, 0, 0}, q2[3] = {0, 0, 0};
   portal_dir(p1, p2, p3, dir);
   c_cross(vec, p1.v, p2.v); b0 = c_dot(vec, p3.v);
@@ -366,13 +410,19 @@ __device__ __forceinline__ void find_pos(const double* p0v, const double* p0v1, 
     sum = b1 + b2 + b3;
   }
   inv = 1.0 / sum;
+  double a1[3], a2[3];
+  wit.centers(a1, a2);
 #pragma unroll
-  for (int k = 0; k < 3; k++) {
-    q1[k] += p0v1[k] * b0; q2[k] += p0v2[k] * b0;
-    q1[k] += p1.v1[k] * b1; q2[k] += p1.v2[k] * b1;
-    q1[k] += p2.v1[k] * b2; q2[k] += p2.v2[k] * b2;
-    q1[k] += p3.v1[k] * b3; q2[k] += p3.v2[k] * b3;
-  }
+  for (int k = 0; k < 3; k++) { q1[k] += a1[k] * b0; q2[k] += a2[k] * b0; }
+  wit.get(p1.i1, p1.i2, a1, a2);
+#pragma unroll
+  for (int k = 0; k < 3; k++) { q1[k] += a1[k] * b1; q2[k] += a2[k] * b1; }
+  wit.get(p2.i1, p2.i2, a1, a2);
+#pragma unroll
+  for (int k = 0; k < 3; k++) { q1[k] += a1[k] * b2; q2[k] += a2[k] * b2; }
+  wit.get(p3.i1, p3.i2, a1, a2);
+#pragma unroll
+  for (int k = 0; k < 3; k++) { q1[k] += a1[k] * b3; q2[k] += a2[k] * b3; }
   c_scale(q1, inv);
   c_scale(q2, inv);
   pos[0] = q1[0] + q2[0]; pos[1] = q1[1] + q2[1]; pos[2] = q1[2] + q2[2];
@@ -386,16 +436,14 @@ enum { ST_D1 = 0, ST_D2, ST_D3, ST_REFINE, ST_PENETR };
 
 struct Mpr {
   Supp p1, p2, p3;
-  double p0v[3], p0v1[3], p0v2[3];
+  double p0v[3];
   double dir[3];
   int st, guard, iterations;
   double depth, pdir[3], pos[3];
 
   // discoverPortal, up to the first support call
   __device__ __forceinline__ void begin(const double* center1, const double* center2) {
-    cp3(p0v1, center1);
-    cp3(p0v2, center2);
-    c_sub2(p0v, p0v1, p0v2);
+    c_sub2(p0v, center1, center2);
     if (c_vec_is_origin(p0v)) p0v[0] += CCD_EPS * 10.0;
     cp3(dir, p0v);
     c_scale(dir, -1.0);
@@ -417,7 +465,8 @@ struct Mpr {
     return 1;
   }
 
-  __device__ __forceinline__ int step(const Supp& s, double tol, int maxit) {
+  template <typename W>
+  __device__ __forceinline__ int step(const Supp& s, double tol, int maxit, const W& wit) {
     double va[3], vb[3], dot;
     switch (st) {
       case ST_D1: {
@@ -426,12 +475,14 @@ struct Mpr {
         if (c_is_zero(dot) || dot < 0) return -1;
         c_cross(dir, p0v, p1.v);
         if (c_is_zero(c_dot(dir, dir))) {
+          double w1[3], w2[3];
+          wit.get(p1.i1, p1.i2, w1, w2);
           if (c_vec_is_origin(p1.v)) {  // touching contact on v1
             depth = 0;
             pdir[0] = pdir[1] = pdir[2] = 0;
-            for (int k = 0; k < 3; k++) pos[k] = (p1.v1[k] + p1.v2[k]) * 0.5;
+            for (int k = 0; k < 3; k++) pos[k] = (w1[k] + w2[k]) * 0.5;
           } else {  // origin on the v0-v1 segment
-            for (int k = 0; k < 3; k++) pos[k] = (p1.v1[k] + p1.v2[k]) * 0.5;
+            for (int k = 0; k < 3; k++) pos[k] = (w1[k] + w2[k]) * 0.5;
             cp3(pdir, p1.v);
             depth = sqrt(c_dot(pdir, pdir));
             c_normalize(pdir);
@@ -519,7 +570,8 @@ struct Mpr {
 
   // tail of findPenetr (depth, penetration direction, contact position), deferred so that all queries of a warp that
   // end in a penetration run it together after the trip loop instead of one after the other at their own last trips
-  __device__ __forceinline__ void finalize() {
+  template <typename W>
+  __device__ __forceinline__ void finalize(const W& wit) {
     const double origin[3] = {0, 0, 0};
     depth = point_tri_dist2(origin, p1.v, p2.v, p3.v, pdir);
     depth = sqrt(depth);
@@ -528,7 +580,7 @@ struct Mpr {
     } else {
       c_normalize(pdir);
     }
-    find_pos(p0v, p0v1, p0v2, p1, p2, p3, pos);
+    find_pos(p0v, wit, p1, p2, p3, pos);
   }
 };
 
@@ -790,6 +842,7 @@ __device__ __forceinline__ void narrow_mesh_mesh(const hmj_tables_t* __restrict_
   const int maxit = M.mpr_iterations;
   Mpr m;
   m.begin(f1.pos, f2.pos);
+  const WitMesh wit = {sx, sy, sz, &f1, &f2, h1, h2};
   bool found = false, fin = false;
   const int thr = coop_threshold(h1.n4 + h2.n4);
   while (true) {
@@ -799,20 +852,21 @@ __device__ __forceinline__ void narrow_mesh_mesh(const hmj_tables_t* __restrict_
     Supp s;
     double nd[3] = {m.dir[0], m.dir[1], m.dir[2]};
     c_scale(nd, -1.0);
+    double v1[3], v2[3];
     if (__popc(am) >= thr) {
-      mesh_support(sx, sy, sz, h1, f1, m.dir, s.v1);
-      mesh_support(sx, sy, sz, h2, f2, nd, s.v2);
+      mesh_support(sx, sy, sz, h1, f1, m.dir, v1, &s.i1);
+      mesh_support(sx, sy, sz, h2, f2, nd, v2, &s.i2);
     } else {
       for (unsigned mm = am; mm;) {
         int src[COOP_G];
         coop_take(mm, src);
-        mesh_support_coop(sx, sy, sz, h1, f1, m.dir, s.v1, src, lane);
-        mesh_support_coop(sx, sy, sz, h2, f2, nd, s.v2, src, lane);
+        mesh_support_coop(sx, sy, sz, h1, f1, m.dir, v1, &s.i1, src, lane);
+        mesh_support_coop(sx, sy, sz, h2, f2, nd, v2, &s.i2, src, lane);
       }
     }
-    c_sub2(s.v, s.v1, s.v2);
+    c_sub2(s.v, v1, v2);
     if (active) {
-      const int res = m.step(s, tol, maxit);
+      const int res = m.step(s, tol, maxit, wit);
       if (res != 1) {
         active = false;
         found = res == 0;
@@ -820,7 +874,7 @@ __device__ __forceinline__ void narrow_mesh_mesh(const hmj_tables_t* __restrict_
       }
     }
   }
-  if (fin) { m.finalize(); found = true; }
+  if (fin) { m.finalize(wit); found = true; }
   if (found && !c_vec_is_origin(m.pdir)) write_slot(B, env, T->pair_slot[k], 0.0 - m.depth, m.pdir, m.pos);
 }
 
@@ -853,6 +907,7 @@ __device__ __forceinline__ void narrow_hfield(const hmj_tables_t* __restrict__ T
     prism_center(p, c1);
     m.begin(c1, f2.pos);
   }
+  const WitPrism wit = {sx, sy, sz, &p, &f2, h2};
   bool found = false, fin = false;
   const int thr = coop_threshold(h2.n4);
   while (true) {
@@ -861,20 +916,21 @@ __device__ __forceinline__ void narrow_hfield(const hmj_tables_t* __restrict__ T
     NP_TRIP();
     Supp s;
     double nd[3] = {m.dir[0], m.dir[1], m.dir[2]};
-    prism_support(p, m.dir, s.v1);
+    double v1[3], v2[3];
+    s.i1 = prism_support(p, m.dir, v1);
     c_scale(nd, -1.0);
     if (__popc(am) >= thr) {
-      mesh_support(sx, sy, sz, h2, f2, nd, s.v2);
+      mesh_support(sx, sy, sz, h2, f2, nd, v2, &s.i2);
     } else {
       for (unsigned mm = am; mm;) {
         int src[COOP_G];
         coop_take(mm, src);
-        mesh_support_coop(sx, sy, sz, h2, f2, nd, s.v2, src, lane);
+        mesh_support_coop(sx, sy, sz, h2, f2, nd, v2, &s.i2, src, lane);
       }
     }
-    c_sub2(s.v, s.v1, s.v2);
+    c_sub2(s.v, v1, v2);
     if (active) {
-      const int res = m.step(s, tol, maxit);
+      const int res = m.step(s, tol, maxit, wit);
       if (res != 1) {
         active = false;
         found = res == 0;
@@ -882,7 +938,7 @@ __device__ __forceinline__ void narrow_hfield(const hmj_tables_t* __restrict__ T
       }
     }
   }
-  if (fin) { m.finalize(); found = true; }
+  if (fin) { m.finalize(wit); found = true; }
   if (found && !d_is_bad(m.depth)) {
     const double* pos1 = gx;
     const double* mat1 = gm;
