@@ -45,6 +45,7 @@
 // produced them — in the one place that needs them (the contact position at the end of a query).  18 doubles of per-lane
 // state less for the three portal vertices, 6 more for the interior point's witnesses.
 struct Supp { double v[3]; int i1, i2; };
+#define NARROW_SMEM_BYTES ((3 * HMJ_NVERT_SMEM + 24 * NARROW_THREADS) * sizeof(double))
 
 // ------------------------------------------------------------------ libccd vec3 helpers
 __device__ __forceinline__ bool c_is_zero(double v) { return fabs(v) < CCD_EPS; }
@@ -99,15 +100,28 @@ __device__ __forceinline__ void cps(Supp& d, const Supp& s) { cp3(d.v, s.v); d.i
 // lowest index).  `base`/`n4` are warp-uniform, so every LDS.128 is a broadcast.
 struct Hull { int base, n4; };
 
-struct Frame { double pos[3]; double mat[9]; };
+struct Frame {
+  double pos[3]; double mat[9];
+  __device__ __forceinline__ double P(int k) const { return pos[k]; }
+  __device__ __forceinline__ double M(int k) const { return mat[k]; }
+};
+// The same frame kept in shared memory, element k of this lane's frame at b[k * NARROW_THREADS] (conflict-free): k_narrow
+// holds its per-query frames there instead of in 24-48 registers per lane, which is what lets a third CTA fit on an SM.
+struct SFrame {
+  double* b;
+  __device__ __forceinline__ double P(int k) const { return b[k * NARROW_THREADS]; }
+  __device__ __forceinline__ double M(int k) const { return b[(3 + k) * NARROW_THREADS]; }
+  __device__ __forceinline__ void setP(int k, double v) { b[k * NARROW_THREADS] = v; }
+  __device__ __forceinline__ void setM(int k, double v) { b[(3 + k) * NARROW_THREADS] = v; }
+};
 
+template <typename F>
 __device__ __forceinline__ void mesh_support(const double* __restrict__ sx, const double* __restrict__ sy,
-                                             const double* __restrict__ sz, Hull h, const Frame& f, const double* dir,
+                                             const double* __restrict__ sz, Hull h, const F& f, const double* dir,
                                              double* out, int* idx = nullptr) {
-  const double* mat = f.mat;
-  const double ld0 = mat[0] * dir[0] + mat[3] * dir[1] + mat[6] * dir[2];
-  const double ld1 = mat[1] * dir[0] + mat[4] * dir[1] + mat[7] * dir[2];
-  const double ld2 = mat[2] * dir[0] + mat[5] * dir[1] + mat[8] * dir[2];
+  const double ld0 = f.M(0) * dir[0] + f.M(3) * dir[1] + f.M(6) * dir[2];
+  const double ld1 = f.M(1) * dir[0] + f.M(4) * dir[1] + f.M(7) * dir[2];
+  const double ld2 = f.M(2) * dir[0] + f.M(5) * dir[1] + f.M(8) * dir[2];
   // two interleaved "first maximum" chains (even / odd vertices), merged with lowest-index tie-break:
   // identical to the serial scan `if (vd > best) { best = vd; ibest = i; }`
   double b0 = -HMJ_MAXVAL, b1 = -HMJ_MAXVAL;
@@ -127,19 +141,19 @@ __device__ __forceinline__ void mesh_support(const double* __restrict__ sx, cons
   if (b1 > b0 || (b1 == b0 && i1 < i0)) i0 = i1;
   if (idx) *idx = i0;
   const double p0 = sx[h.base + i0], p1 = sy[h.base + i0], p2 = sz[h.base + i0];
-  out[0] = (mat[0] * p0 + mat[1] * p1 + mat[2] * p2) + f.pos[0];
-  out[1] = (mat[3] * p0 + mat[4] * p1 + mat[5] * p2) + f.pos[1];
-  out[2] = (mat[6] * p0 + mat[7] * p1 + mat[8] * p2) + f.pos[2];
+  out[0] = (f.M(0) * p0 + f.M(1) * p1 + f.M(2) * p2) + f.P(0);
+  out[1] = (f.M(3) * p0 + f.M(4) * p1 + f.M(5) * p2) + f.P(1);
+  out[2] = (f.M(6) * p0 + f.M(7) * p1 + f.M(8) * p2) + f.P(2);
 }
 
 // vertex i of hull h in the frame f: the tail of mesh_support, for recomputing a witness from its index (same bits)
+template <typename F>
 __device__ __forceinline__ void mesh_point(const double* __restrict__ sx, const double* __restrict__ sy,
-                                           const double* __restrict__ sz, Hull h, const Frame& f, int i, double* out) {
-  const double* mat = f.mat;
+                                           const double* __restrict__ sz, Hull h, const F& f, int i, double* out) {
   const double p0 = sx[h.base + i], p1 = sy[h.base + i], p2 = sz[h.base + i];
-  out[0] = (mat[0] * p0 + mat[1] * p1 + mat[2] * p2) + f.pos[0];
-  out[1] = (mat[3] * p0 + mat[4] * p1 + mat[5] * p2) + f.pos[1];
-  out[2] = (mat[6] * p0 + mat[7] * p1 + mat[8] * p2) + f.pos[2];
+  out[0] = (f.M(0) * p0 + f.M(1) * p1 + f.M(2) * p2) + f.P(0);
+  out[1] = (f.M(3) * p0 + f.M(4) * p1 + f.M(5) * p2) + f.P(1);
+  out[2] = (f.M(6) * p0 + f.M(7) * p1 + f.M(8) * p2) + f.P(2);
 }
 
 // Cooperative variant for sparsely populated warps: all 32 lanes scan the hull for the directions of up to
@@ -147,14 +161,14 @@ __device__ __forceinline__ void mesh_point(const double* __restrict__ sx, const 
 // the FP64 pipe and the shuffle unit busy; xor-butterfly with lowest-index tie-break == the serial "first
 // maximum").  Only the source lanes receive `out`.  Bit-identical to mesh_support.
 #define COOP_G 4
+template <typename F>
 __device__ __forceinline__ void mesh_support_coop(const double* __restrict__ sx, const double* __restrict__ sy,
-                                                  const double* __restrict__ sz, Hull h, const Frame& f, const double* dir,
+                                                  const double* __restrict__ sz, Hull h, const F& f, const double* dir,
                                                   double* out, int* idx, const int* src, int lane) {
   const unsigned FULL = 0xffffffffu;
-  const double* mat = f.mat;
-  const double my0 = mat[0] * dir[0] + mat[3] * dir[1] + mat[6] * dir[2];
-  const double my1 = mat[1] * dir[0] + mat[4] * dir[1] + mat[7] * dir[2];
-  const double my2 = mat[2] * dir[0] + mat[5] * dir[1] + mat[8] * dir[2];
+  const double my0 = f.M(0) * dir[0] + f.M(3) * dir[1] + f.M(6) * dir[2];
+  const double my1 = f.M(1) * dir[0] + f.M(4) * dir[1] + f.M(7) * dir[2];
+  const double my2 = f.M(2) * dir[0] + f.M(5) * dir[1] + f.M(8) * dir[2];
   double ld0[COOP_G], ld1[COOP_G], ld2[COOP_G], best[COOP_G];
   int ibest[COOP_G];
 #pragma unroll
@@ -209,9 +223,9 @@ __device__ __forceinline__ void mesh_support_coop(const double* __restrict__ sx,
     if (mine == 0x7fffffff) mine = 0;
     *idx = mine;
     const double p0 = sx[h.base + mine], p1 = sy[h.base + mine], p2 = sz[h.base + mine];
-    out[0] = (mat[0] * p0 + mat[1] * p1 + mat[2] * p2) + f.pos[0];
-    out[1] = (mat[3] * p0 + mat[4] * p1 + mat[5] * p2) + f.pos[1];
-    out[2] = (mat[6] * p0 + mat[7] * p1 + mat[8] * p2) + f.pos[2];
+    out[0] = (f.M(0) * p0 + f.M(1) * p1 + f.M(2) * p2) + f.P(0);
+    out[1] = (f.M(3) * p0 + f.M(4) * p1 + f.M(5) * p2) + f.P(1);
+    out[2] = (f.M(6) * p0 + f.M(7) * p1 + f.M(8) * p2) + f.P(2);
   }
 }
 
@@ -255,52 +269,72 @@ __device__ __forceinline__ void mesh_aabb(const double* __restrict__ sx, const d
 }
 
 // Height-field prism: three top vertices (strip order) over a flat bottom at z = zb with the same (x, y).
-struct Prism { double t[3][3]; double zb; };
+struct Prism {
+  double t[3][3]; double zb;
+  __device__ __forceinline__ double TT(int i, int k) const { return t[i][k]; }
+  __device__ __forceinline__ double ZB() const { return zb; }
+};
+// the same prism in shared memory (k_narrow), element e of this lane's prism at b[e * NARROW_THREADS]
+struct SPrism {
+  double* b;
+  __device__ __forceinline__ double TT(int i, int k) const { return b[(3 * i + k) * NARROW_THREADS]; }
+  __device__ __forceinline__ double ZB() const { return b[9 * NARROW_THREADS]; }
+};
 
 // returns the vertex code: column i (0..2) + 3 when it is a top vertex
-__device__ __forceinline__ int prism_support(const Prism& o, const double* dir, double* out) {
+template <typename PR>
+__device__ __forceinline__ int prism_support(const PR& o, const double* dir, double* out) {
   const bool top = !(dir[2] < 0);
-  const double za = top ? o.t[0][2] : o.zb, zb = top ? o.t[1][2] : o.zb, zc = top ? o.t[2][2] : o.zb;
-  double best = o.t[0][0] * dir[0] + o.t[0][1] * dir[1] + za * dir[2];
+  const double ozb = o.ZB();
+  const double za = top ? o.TT(0, 2) : ozb, zb = top ? o.TT(1, 2) : ozb, zc = top ? o.TT(2, 2) : ozb;
+  const double x0 = o.TT(0, 0), y0 = o.TT(0, 1), x1 = o.TT(1, 0), y1 = o.TT(1, 1), x2 = o.TT(2, 0), y2 = o.TT(2, 1);
+  double best = x0 * dir[0] + y0 * dir[1] + za * dir[2];
   int code = 0;
-  out[0] = o.t[0][0]; out[1] = o.t[0][1]; out[2] = za;
-  double t = o.t[1][0] * dir[0] + o.t[1][1] * dir[1] + zb * dir[2];
-  if (t > best) { best = t; code = 1; out[0] = o.t[1][0]; out[1] = o.t[1][1]; out[2] = zb; }
-  t = o.t[2][0] * dir[0] + o.t[2][1] * dir[1] + zc * dir[2];
-  if (t > best) { best = t; code = 2; out[0] = o.t[2][0]; out[1] = o.t[2][1]; out[2] = zc; }
+  out[0] = x0; out[1] = y0; out[2] = za;
+  double t = x1 * dir[0] + y1 * dir[1] + zb * dir[2];
+  if (t > best) { best = t; code = 1; out[0] = x1; out[1] = y1; out[2] = zb; }
+  t = x2 * dir[0] + y2 * dir[1] + zc * dir[2];
+  if (t > best) { best = t; code = 2; out[0] = x2; out[1] = y2; out[2] = zc; }
   return code + (top ? 3 : 0);
 }
-__device__ __forceinline__ void prism_point(const Prism& o, int code, double* out) {
+template <typename PR>
+__device__ __forceinline__ void prism_point(const PR& o, int code, double* out) {
   const int i = code >= 3 ? code - 3 : code;
-  out[0] = o.t[i][0]; out[1] = o.t[i][1]; out[2] = code >= 3 ? o.t[i][2] : o.zb;
+  out[0] = o.TT(i, 0); out[1] = o.TT(i, 1); out[2] = code >= 3 ? o.TT(i, 2) : o.ZB();
 }
 
 // Recomputation of witnesses from their indices: the two shapes of a query
 struct WitMesh {   // mesh vs mesh
-  const double *sx, *sy, *sz; const Frame *f1, *f2; Hull h1, h2;
+  const double *sx, *sy, *sz; const SFrame *f1, *f2; Hull h1, h2;
   __device__ __forceinline__ void get(int i1, int i2, double* v1, double* v2) const {
     mesh_point(sx, sy, sz, h1, *f1, i1, v1);
     mesh_point(sx, sy, sz, h2, *f2, i2, v2);
   }
-  __device__ __forceinline__ void centers(double* c1, double* c2) const { cp3(c1, f1->pos); cp3(c2, f2->pos); }
+  __device__ __forceinline__ void centers(double* c1, double* c2) const {
+    for (int k = 0; k < 3; k++) { c1[k] = f1->P(k); c2[k] = f2->P(k); }
+  }
 };
 
-__device__ __forceinline__ void prism_center(const Prism& o, double* c) {
+template <typename PR>
+__device__ __forceinline__ void prism_center(const PR& o, double* c) {
   c[0] = c[1] = c[2] = 0;
 #pragma unroll
-  for (int i = 0; i < 3; i++) { c[0] += o.t[i][0]; c[1] += o.t[i][1]; c[2] += o.zb; }  // bottom vertices 0..2
+  for (int i = 0; i < 3; i++) { c[0] += o.TT(i, 0); c[1] += o.TT(i, 1); c[2] += o.ZB(); }  // bottom vertices 0..2
 #pragma unroll
-  for (int i = 0; i < 3; i++) { c[0] += o.t[i][0]; c[1] += o.t[i][1]; c[2] += o.t[i][2]; }  // top vertices 3..5
+  for (int i = 0; i < 3; i++) { c[0] += o.TT(i, 0); c[1] += o.TT(i, 1); c[2] += o.TT(i, 2); }  // top vertices 3..5
   c[0] *= 1.0 / 6.0; c[1] *= 1.0 / 6.0; c[2] *= 1.0 / 6.0;
 }
 
 struct WitPrism {   // height-field prism vs mesh
-  const double *sx, *sy, *sz; const Prism* p; const Frame* f2; Hull h2;
+  const double *sx, *sy, *sz; const SPrism* p; const SFrame* f2; Hull h2;
   __device__ __forceinline__ void get(int i1, int i2, double* v1, double* v2) const {
     prism_point(*p, i1, v1);
     mesh_point(sx, sy, sz, h2, *f2, i2, v2);
   }
-  __device__ __forceinline__ void centers(double* c1, double* c2) const { prism_center(*p, c1); cp3(c2, f2->pos); }
+  __device__ __forceinline__ void centers(double* c1, double* c2) const {
+    prism_center(*p, c1);
+    for (int k = 0; k < 3; k++) c2[k] = f2->P(k);
+  }
 };
 
 // ------------------------------------------------------------------ MPR pieces (libccd mpr.c)
@@ -826,7 +860,7 @@ __device__ __forceinline__ void write_slot(const hmj_buffers_t& B, int env, int 
 
 // 32 mesh-mesh tasks of one pair (mjc_Convex, multiccd off): lane <-> environment.
 __device__ __forceinline__ void narrow_mesh_mesh(const hmj_tables_t* __restrict__ T, const hmj_buffers_t& B,
-                                                 const double* sx, const double* sy, const double* sz, int2 task,
+                                                 const double* sx, const double* sy, const double* sz, double* sfr, int2 task,
                                                  bool active, int lane, int& trips_) {
   const hmj_model_t& M = T->m;
   const int env = task.x, k = task.y & 63;
@@ -835,13 +869,16 @@ __device__ __forceinline__ void narrow_mesh_mesh(const hmj_tables_t* __restrict_
   const Hull h2 = {T->mesh_adr[M.geom_meshid[g2]], T->mesh_npad[M.geom_meshid[g2]]};
   const double* gx = B.geom_xpos + (size_t)env * HMJ_NGEOM * 3;
   const double* gm = B.geom_xmat + (size_t)env * HMJ_NGEOM * 9;
-  Frame f1, f2;
-  for (int q = 0; q < 3; q++) { f1.pos[q] = gx[g1 * 3 + q]; f2.pos[q] = gx[g2 * 3 + q]; }
-  for (int q = 0; q < 9; q++) { f1.mat[q] = gm[g1 * 9 + q]; f2.mat[q] = gm[g2 * 9 + q]; }
+  SFrame f1 = {sfr}, f2 = {sfr + 12 * NARROW_THREADS};   // this lane's two frames, in shared memory
+  for (int q = 0; q < 3; q++) { f1.setP(q, gx[g1 * 3 + q]); f2.setP(q, gx[g2 * 3 + q]); }
+  for (int q = 0; q < 9; q++) { f1.setM(q, gm[g1 * 9 + q]); f2.setM(q, gm[g2 * 9 + q]); }
   const double tol = M.mpr_tolerance;
   const int maxit = M.mpr_iterations;
   Mpr m;
-  m.begin(f1.pos, f2.pos);
+  {
+    const double c1[3] = {f1.P(0), f1.P(1), f1.P(2)}, c2[3] = {f2.P(0), f2.P(1), f2.P(2)};
+    m.begin(c1, c2);
+  }
   const WitMesh wit = {sx, sy, sz, &f1, &f2, h1, h2};
   bool found = false, fin = false;
   const int thr = coop_threshold(h1.n4 + h2.n4);
@@ -881,7 +918,8 @@ __device__ __forceinline__ void narrow_mesh_mesh(const hmj_tables_t* __restrict_
 // 32 prism-vs-hull tasks of one hull (pairs may differ per lane): lane <-> one pre-screened prism of
 // mjc_ConvexHField; the query restarts from the top (same arithmetic as the screen in k_broad).
 __device__ __forceinline__ void narrow_hfield(const hmj_tables_t* __restrict__ T, const hmj_buffers_t& B, const double* sx,
-                                              const double* sy, const double* sz, Hull h2, int2 task, bool active, int lane, int& trips_) {
+                                              const double* sy, const double* sz, double* sfr, Hull h2, int2 task, bool active, int lane,
+                                              int& trips_) {
   const hmj_model_t& M = T->m;
   const int env = task.x;
   const int k = task.y & 63, ord = (task.y >> 6) & 7, r = (task.y >> 9) & 7, cmin = (task.y >> 12) & 7, ps = (task.y >> 15) & 31;
@@ -893,19 +931,31 @@ __device__ __forceinline__ void narrow_hfield(const hmj_tables_t* __restrict__ T
   const float* data = B.params[env].hfield_data;
   const double tol = M.mpr_tolerance;
   const int maxit = M.mpr_iterations;
-  Frame f2;
-  hfield_rel_frame(f2, gx, gm, g2);
+  SFrame f2 = {sfr};   // this lane's frame of the mesh in the height field's frame, in shared memory
+  double c2[3];
+  {
+    Frame fr;
+    hfield_rel_frame(fr, gx, gm, g2);
+    for (int q = 0; q < 3; q++) { f2.setP(q, fr.pos[q]); c2[q] = fr.pos[q]; }
+    for (int q = 0; q < 9; q++) f2.setM(q, fr.mat[q]);
+  }
   const double dx = (2.0 * size1[0]) / (ncol - 1);
   const double dy = (2.0 * size1[1]) / (nrow - 1);
-  Prism p;
-  p.zb = -size1[3];
+  SPrism p = {sfr + 12 * NARROW_THREADS};   // this lane's prism, in shared memory behind its frame
+  {
+    Prism pr;
+    pr.zb = -size1[3];
 #pragma unroll
-  for (int a = 0; a < 3; a++) strip_vertex(p.t[a], r, cmin, max(ps - 2 + a, 0), data, size1, ncol, dx, dy);
+    for (int a = 0; a < 3; a++) strip_vertex(pr.t[a], r, cmin, max(ps - 2 + a, 0), data, size1, ncol, dx, dy);
+#pragma unroll
+    for (int e = 0; e < 9; e++) p.b[e * NARROW_THREADS] = pr.t[e / 3][e % 3];
+    p.b[9 * NARROW_THREADS] = pr.zb;
+  }
   Mpr m;
   {
     double c1[3];
     prism_center(p, c1);
-    m.begin(c1, f2.pos);
+    m.begin(c1, c2);
   }
   const WitPrism wit = {sx, sy, sz, &p, &f2, h2};
   bool found = false, fin = false;
@@ -956,9 +1006,12 @@ __device__ __forceinline__ void narrow_hfield(const hmj_tables_t* __restrict__ T
 // a work item is up to 32 consecutive tasks of one group, so the hull(s) a warp scans are uniform.
 __global__ void __launch_bounds__(NARROW_THREADS, NARROW_MIN_CTAS)
 k_narrow(const hmj_tables_t* __restrict__ T, hmj_buffers_t B) {
-  __shared__ __align__(16) double sx[HMJ_NVERT_SMEM];
-  __shared__ __align__(16) double sy[HMJ_NVERT_SMEM];
-  __shared__ __align__(16) double sz[HMJ_NVERT_SMEM];
+  // dynamic shared memory: hull vertices (fp64 SoA) | per-lane query frames (SFrame: [element][thread])
+  extern __shared__ __align__(16) double narrow_smem[];
+  double* sx = narrow_smem;
+  double* sy = sx + HMJ_NVERT_SMEM;
+  double* sz = sy + HMJ_NVERT_SMEM;
+  double* sfr = sz + HMJ_NVERT_SMEM;
   const int lane = threadIdx.x & 31;
   // work items: group g contributes ceil(count[g] / isz); groups are numbered across TWO registers per lane.
   // The item size isz (tasks per warp) is the smallest of 4 / 8 / 16 / 32 that still gives every item its own warp:
@@ -1033,9 +1086,9 @@ k_narrow(const hmj_tables_t* __restrict__ T, hmj_buffers_t B) {
     const int2 task = B.wq_task[(size_t)T->group_base[g] * B.n + (valid ? q : q0)];  // idle lanes shadow the item's first task
     if (g < HMJ_NMESH) {
       const Hull h2 = {T->mesh_adr[g], T->mesh_npad[g]};
-      narrow_hfield(T, B, sx, sy, sz, h2, task, valid, lane, trips_);
+      narrow_hfield(T, B, sx, sy, sz, sfr + threadIdx.x, h2, task, valid, lane, trips_);
     } else {
-      narrow_mesh_mesh(T, B, sx, sy, sz, task, valid, lane, trips_);
+      narrow_mesh_mesh(T, B, sx, sy, sz, sfr + threadIdx.x, task, valid, lane, trips_);
     }
 #ifdef HMJ_PHASE_PROF
     if (lane == 0) {
@@ -1061,7 +1114,8 @@ void hmj_launch_collide(const hmj_tables_t* tab, hmj_buffers_t buf, cudaStream_t
   if (!narrow_grids[dev]) {
     int sms = 148, per_sm = 2;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_narrow, NARROW_THREADS, 0);
+    cudaFuncSetAttribute(k_narrow, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NARROW_SMEM_BYTES);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_narrow, NARROW_THREADS, NARROW_SMEM_BYTES);
     narrow_grids[dev] = sms * (per_sm > 0 ? per_sm : 1);
   }
   const int narrow_grid = narrow_grids[dev];
@@ -1072,5 +1126,5 @@ void hmj_launch_collide(const hmj_tables_t* tab, hmj_buffers_t buf, cudaStream_t
   const int npad = (buf.n + BROAD_THREADS - 1) / BROAD_THREADS * BROAD_THREADS;  // CTAs are pair-uniform
   const long long nthread = (long long)npad * HMJ_NPAIR;
   k_broad<<<(int)(nthread / BROAD_THREADS), BROAD_THREADS, 0, stream>>>(tab, buf, npad);
-  k_narrow<<<narrow_grid, NARROW_THREADS, 0, stream>>>(tab, buf);
+  k_narrow<<<narrow_grid, NARROW_THREADS, NARROW_SMEM_BYTES, stream>>>(tab, buf);
 }
