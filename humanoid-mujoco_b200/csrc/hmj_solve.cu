@@ -38,7 +38,7 @@
 struct CholScratch {
   double col[2][32 + NV];   // staged column of the current pivot, double-buffered by pivot parity (tail: read padding)
   double xb[2][32];         // staged right-hand side
-  double invd[NV + 2];
+  double invd[NV];
 };
 
 template <int MAXC>
@@ -48,11 +48,10 @@ struct SolveSmem {
   static constexpr int MR = MAXC > 0 ? NLIMMAX + 10 * MAXC : 1;
   double M[NV * LD];
   double H[NV * LD];
-  double vec[NV + 2];           // vector being multiplied (search / qacc / qvel)
-  double qfs[NV + 2];           // qfrc_smooth
-  double com[4];
+  double vec[NV];               // vector being multiplied (search / qacc / qvel)
+  double qfs[NV];               // qfrc_smooth
+  double com[3];
   CholScratch chol;
-  unsigned char tri[NTRI][2];   // (i, j <= i) of the t-th lower-triangle entry, row-major
   // ---- constrained classes only
   double Jb[MC][6][LD];
   double jbv[MC][6];
@@ -65,7 +64,7 @@ struct SolveSmem {
   double cprm[MC][8];            // dist, solref[2], solimp[5]
   double lim_sign[NL], lim_pos[NL], lim_margin[NL];
   int32_t cslot[MC], cb1[MC], cb2[MC];
-  int32_t lim_dof[NL], lim_jnt[NL];
+  int32_t lim_dof[NL];   // the hinge joint of a limit row is dof - 5 (free joint first)
 };
 
 // ---------------------------------------------------------------- dense helpers (warp cooperative)
@@ -415,7 +414,6 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
 #endif
 
   // ---------------- load: dense M (constrained classes only), qfrc_smooth, state, qacc_smooth from k_factor
-  for (int t = lane; t < NTRI; t += 32) { S.tri[t][0] = (unsigned char)T->tri_i[t]; S.tri[t][1] = (unsigned char)T->tri_j[t]; }
   if constexpr (MAXC > 0) {
     for (int t = lane; t < NV * LD; t += 32) S.M[t] = 0.0;
     __syncwarp();
@@ -512,12 +510,12 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
       const int before = __popc(b0 & below) + __popc(b1 & below);
       if (act0) {
         S.lim_dof[before] = M.jnt_dofadr[j]; S.lim_sign[before] = 1.0; S.lim_pos[before] = dist0;
-        S.lim_margin[before] = margin; S.lim_jnt[before] = j;
+        S.lim_margin[before] = margin;
       }
       if (act1) {
         const int r = before + (act0 ? 1 : 0);
         S.lim_dof[r] = M.jnt_dofadr[j]; S.lim_sign[r] = -1.0; S.lim_pos[r] = dist1;
-        S.lim_margin[r] = margin; S.lim_jnt[r] = j;
+        S.lim_margin[r] = margin;
       }
       nlim = __popc(b0) + __popc(b1);
     }
@@ -562,7 +560,7 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
         double Rr, KI, Bc, pos, margin, diag, scaleR;
         const double *solref, *solimp;
         if (r < nlim) {
-          const int j = S.lim_jnt[r];
+          const int j = M.dof_jntid[S.lim_dof[r]];
           pos = S.lim_pos[r]; margin = S.lim_margin[r];
           solref = M.jnt_solref[j]; solimp = M.jnt_solimp[j];
           diag = M.dof_invweight0[S.lim_dof[r]];
@@ -766,7 +764,7 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
 #pragma unroll
           for (int q = 0; q < NQ; q++) {
             const int t = min(lane + 32 * q, NTRI - 1);
-            oi[q] = S.tri[t][0]; oj[q] = S.tri[t][1];
+            oi[q] = T->tri_i[t]; oj[q] = T->tri_j[t];   // L1-resident index tables (no per-env copy: 342 B of shared memory less)
             acc[q] = S.M[oi[q] * LD + oj[q]];
           }
           // diagonal of the active limit rows: lane d sums the rows of dof d (uniform loop, broadcast loads), added last
@@ -961,7 +959,7 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
 #pragma unroll
     for (int k = 0; k < (NTRI + 31) / 32; k++) {
       const int t = lane + 32 * k;
-      if (t < NTRI) S.H[S.tri[t][0] * LD + S.tri[t][1]] = fe[k];
+      if (t < NTRI) S.H[T->tri_i[t] * LD + T->tri_j[t]] = fe[k];
     }
     if (lane < NV) S.chol.invd[lane] = fi;
   }
