@@ -28,6 +28,7 @@
 // Roofline: FP64 add/mul issue bound (no FMA by contract); HBM/L2 traffic is 120 doubles of
 // geom frames in and <= 8 doubles per contact slot out.
 #include <float.h>
+#include <stdlib.h>
 
 #include "hmj_dev.cuh"
 
@@ -702,13 +703,13 @@ __device__ __forceinline__ void push_tasks(const hmj_tables_t* __restrict__ T, c
 //    survivors become MPR tasks, which restart the query from the top in k_narrow (same arithmetic).
 // The per-env slot bitmask is zeroed before this kernel; k_narrow sets the bits of the slots it fills.
 __global__ void __launch_bounds__(BROAD_THREADS)
-k_broad(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int npad) {
+k_broad(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int npad, int kpos0) {
   __shared__ __align__(16) double sx[HMJ_NVERT_SMEM];
   __shared__ __align__(16) double sy[HMJ_NVERT_SMEM];
   __shared__ __align__(16) double sz[HMJ_NVERT_SMEM];
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  const int kpos = t / npad;  // warp-uniform; whole CTAs can be past the last pair
-  const int e = t - kpos * npad;
+  const int kpos = kpos0 + t / npad;  // warp-uniform; whole CTAs can be past the last pair
+  const int e = t - (t / npad) * npad;
   const int lane = threadIdx.x & 31;
   const hmj_model_t& M = T->m;
   if (kpos >= HMJ_NPAIR) return;  // npad * NPAIR is a multiple of 32: whole warps leave together (before any barrier use)
@@ -825,6 +826,129 @@ k_broad(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int npad) {
     }
     push_tasks(T, B, g, survive, env, pack_task(k, ord, w.pr, w.cmin, w.ps), lane);
     if (has) ord++;
+  }
+}
+
+// ------------------------------------------------------------------ broadphase of the height-field pairs, small batches
+// The same work as the height-field branch of k_broad with ONE WARP per (pair, env) instead of one thread: the hull
+// scans — the bounding box in the height field's frame and the first support call of every prism — are split over the 32
+// lanes (k_broad's threads walk 200 vertices one after the other, 1 + #prisms times: 25 us of pure latency when the
+// batch is too small to hide it, which is the planner's case).  Lane p owns prism p of the strip walk; its slot ordinal
+// is its rank among the tested prisms, so tasks and slots are exactly k_broad's.  Bounding-box extrema are min / max
+// reductions (order-free), the support arg-max is mesh_support_coop (bit-identical to the serial scan): same contacts.
+// Vertices are read from the fp64 tables in global memory (25 KB, L1-resident); 4 warps per CTA.
+#define BROAD_COOP_MAX_N 512    /* launcher uses this kernel up to this batch size (measured: +11 % at 10-64 samples, +8 % at 256, -4 % at 1024) */
+__global__ void __launch_bounds__(128)
+k_broad_hf_coop(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int nhf) {
+  const unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const int wid = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (wid >= nhf * B.n) return;
+  const int kpos = wid / B.n, env = wid - kpos * B.n;
+  if (B.active && !B.active[env]) return;
+  const hmj_model_t& M = T->m;
+  const int k = T->broad_order[kpos];
+  const int g2 = M.pair_geom2[k];
+  const double* gx = B.geom_xpos + (size_t)env * HMJ_NGEOM * 3;
+  const double* gm = B.geom_xmat + (size_t)env * HMJ_NGEOM * 9;
+  const int nslot = T->pair_slot[k + 1] - T->pair_slot[k];
+  const double* sx = T->dvx;
+  const double* sy = T->dvy;
+  const double* sz = T->dvz;
+  const double* size1 = M.hfield_size;
+  const int nrow = M.hfield_nrow, ncol = M.hfield_ncol;
+  const float* data = B.params[env].hfield_data;
+  const Hull h2 = {T->mesh_adr[M.geom_meshid[g2]], T->mesh_npad[M.geom_meshid[g2]]};
+  Frame f2;
+  hfield_rel_frame(f2, gx, gm, g2);
+  {
+    const double r2 = M.geom_rbound[g2];
+    bool active = true;
+    for (int i = 0; i < 2; i++)
+      if ((size1[i] < f2.pos[i] - r2 - 0.0) || (-size1[i] > f2.pos[i] + r2 + 0.0)) active = false;
+    if (size1[2] < f2.pos[2] - r2 - 0.0) active = false;
+    if (-size1[3] > f2.pos[2] + r2 + 0.0) active = false;
+    if (!active) return;   // warp-uniform
+  }
+  // ---- bounding box of the hull in the height field's frame (mesh_aabb, vertices strided over the lanes)
+  double lo[3], hi[3];
+  {
+    const double* mat = f2.mat;
+    double mn0 = HMJ_MAXVAL, mn1 = HMJ_MAXVAL, mn2 = HMJ_MAXVAL, mx0 = -HMJ_MAXVAL, mx1 = -HMJ_MAXVAL, mx2 = -HMJ_MAXVAL;
+    for (int i = lane; i < h2.n4; i += 32) {
+      const double x = sx[h2.base + i], y = sy[h2.base + i], z = sz[h2.base + i];
+      double d;
+      d = mat[0] * x + mat[1] * y + mat[2] * z; mn0 = fmin(mn0, d); mx0 = fmax(mx0, d);
+      d = mat[3] * x + mat[4] * y + mat[5] * z; mn1 = fmin(mn1, d); mx1 = fmax(mx1, d);
+      d = mat[6] * x + mat[7] * y + mat[8] * z; mn2 = fmin(mn2, d); mx2 = fmax(mx2, d);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      mn0 = fmin(mn0, __shfl_xor_sync(FULL, mn0, o)); mx0 = fmax(mx0, __shfl_xor_sync(FULL, mx0, o));
+      mn1 = fmin(mn1, __shfl_xor_sync(FULL, mn1, o)); mx1 = fmax(mx1, __shfl_xor_sync(FULL, mx1, o));
+      mn2 = fmin(mn2, __shfl_xor_sync(FULL, mn2, o)); mx2 = fmax(mx2, __shfl_xor_sync(FULL, mx2, o));
+    }
+    lo[0] = mn0 + f2.pos[0]; lo[1] = mn1 + f2.pos[1]; lo[2] = mn2 + f2.pos[2];
+    hi[0] = mx0 + f2.pos[0]; hi[1] = mx1 + f2.pos[1]; hi[2] = mx2 + f2.pos[2];
+  }
+  if ((lo[0] > size1[0]) || (hi[0] < -size1[0]) || (lo[1] > size1[1]) || (hi[1] < -size1[1]) || (lo[2] > size1[2]) ||
+      (hi[2] < -size1[3]))
+    return;
+  int cmin = (int)floor((lo[0] + size1[0]) / (2 * size1[0]) * (ncol - 1));
+  int cmax = (int)ceil((hi[0] + size1[0]) / (2 * size1[0]) * (ncol - 1));
+  int rmin = (int)floor((lo[1] + size1[1]) / (2 * size1[1]) * (nrow - 1));
+  int rmax = (int)ceil((hi[1] + size1[1]) / (2 * size1[1]) * (nrow - 1));
+  cmin = max(0, cmin); cmax = min(ncol - 1, cmax);
+  rmin = max(0, rmin); rmax = min(nrow - 1, rmax);
+  if (cmin > cmax) return;
+  const int smax = 2 * (cmax - cmin + 1);       // strip vertices per row
+  const int per_row = smax - 2;                  // prisms per row (every three consecutive strip vertices)
+  const int nprism = (rmax > rmin ? rmax - rmin : 0) * per_row;
+  const double zmin = lo[2];
+  const double dx = (2.0 * size1[0]) / (ncol - 1);
+  const double dy = (2.0 * size1[1]) / (nrow - 1);
+  const int g = T->pair_group[k];
+  int ord_base = 0;
+  for (int p0 = 0; p0 < nprism; p0 += 32) {
+    const int pi = p0 + lane;
+    const bool exists = pi < nprism;
+    const int pr = rmin + (exists ? pi / per_row : 0);
+    const int ps = 2 + (exists ? pi % per_row : 0);        // strip index of the prism's newest vertex
+    Prism p;
+    p.zb = -size1[3];
+#pragma unroll
+    for (int a = 0; a < 3; a++) strip_vertex(p.t[a], pr, cmin, ps - 2 + a, data, size1, ncol, dx, dy);
+    const bool test = exists && !(p.t[0][2] < zmin && p.t[1][2] < zmin && p.t[2][2] < zmin);
+    const unsigned tm = __ballot_sync(FULL, test);
+    const int ord = ord_base + __popc(tm & ((1u << lane) - 1u));
+    // discoverPortal up to its first exit test (as in k_broad)
+    double c1[3], p0v[3], dir[3], v1[3], v2[3] = {0, 0, 0}, v[3], nd[3];
+    prism_center(p, c1);
+    c_sub2(p0v, c1, f2.pos);
+    if (c_vec_is_origin(p0v)) p0v[0] += CCD_EPS * 10.0;
+    cp3(dir, p0v);
+    c_scale(dir, -1.0);
+    c_normalize(dir);
+    prism_support(p, dir, v1);
+    cp3(nd, dir);
+    c_scale(nd, -1.0);
+    for (unsigned mm = tm; mm;) {
+      int src[COOP_G], idx = 0;
+      coop_take(mm, src);
+      mesh_support_coop(sx, sy, sz, h2, f2, nd, v2, &idx, src, lane);
+    }
+    c_sub2(v, v1, v2);
+    const double dot = c_dot(v, dir);
+    bool survive = test && !(c_is_zero(dot) || dot < 0);
+    const bool over = test && ord >= nslot;   // more tested prisms than slots: k_broad drops this one and stops the walk
+    const unsigned om = __ballot_sync(FULL, over);
+    if (om) {
+      if (lane == 0) atomicOr(&B.status[env], HMJ_STATUS_CONTACTFULL);
+      survive = survive && !over;
+    }
+    push_tasks(T, B, g, survive, env, pack_task(k, ord, pr, cmin, ps), lane);
+    if (om) return;
+    ord_base += __popc(tm);
   }
 }
 
@@ -1125,6 +1249,16 @@ void hmj_launch_collide(const hmj_tables_t* tab, hmj_buffers_t buf, cudaStream_t
   }
   const int npad = (buf.n + BROAD_THREADS - 1) / BROAD_THREADS * BROAD_THREADS;  // CTAs are pair-uniform
   const long long nthread = (long long)npad * HMJ_NPAIR;
-  k_broad<<<(int)(nthread / BROAD_THREADS), BROAD_THREADS, 0, stream>>>(tab, buf, npad);
+  const char* force = getenv("HMJ_BROAD_COOP");   // developer override: 0 / 1
+  const bool coop = force ? atoi(force) != 0 : buf.n <= BROAD_COOP_MAX_N;
+  if (coop) {
+    // small batch: the 9 height-field pairs (first in broad_order) go warp-per-(pair, env); the mesh-mesh pairs keep k_broad
+    const int nhf = HMJ_NPAIR - 28;
+    const long long nmm = (long long)npad * (HMJ_NPAIR - nhf);
+    k_broad<<<(int)(nmm / BROAD_THREADS), BROAD_THREADS, 0, stream>>>(tab, buf, npad, nhf);
+    k_broad_hf_coop<<<(nhf * buf.n + 3) / 4, 128, 0, stream>>>(tab, buf, nhf);
+  } else {
+    k_broad<<<(int)(nthread / BROAD_THREADS), BROAD_THREADS, 0, stream>>>(tab, buf, npad, 0);
+  }
   k_narrow<<<narrow_grid, NARROW_THREADS, NARROW_SMEM_BYTES, stream>>>(tab, buf);
 }
