@@ -694,6 +694,46 @@ __device__ __forceinline__ void push_tasks(const hmj_tables_t* __restrict__ T, c
   if (hit) B.wq_task[(size_t)T->group_base[g] * B.n + base + __popc(bal & ((1u << lane) - 1u))] = make_int2(env, word);
 }
 
+// Mesh-mesh candidate pair k of one env (lane <-> env, the pair is warp-uniform): bounding spheres, then a conservative
+// pre-screen of MPR's first exit; survivors become one narrowphase task.
+__device__ __forceinline__ void broad_mesh_mesh(const hmj_tables_t* __restrict__ T, const hmj_buffers_t& B, int k, int env,
+                                                bool in, int lane) {
+  const hmj_model_t& M = T->m;
+  const int g1 = M.pair_geom1[k], g2 = M.pair_geom2[k];
+  const double* gx = B.geom_xpos + (size_t)env * HMJ_NGEOM * 3;
+  const double dif0 = gx[g1 * 3] - gx[g2 * 3], dif1 = gx[g1 * 3 + 1] - gx[g2 * 3 + 1], dif2 = gx[g1 * 3 + 2] - gx[g2 * 3 + 2];
+  const double bound = M.geom_rbound[g1] + M.geom_rbound[g2];
+  bool hit = in && !(dif0 * dif0 + dif1 * dif1 + dif2 * dif2 > bound * bound);
+  if (hit) {
+    // Conservative pre-screen of ccdMPRPenetration's first exit (dot(support(dir), dir) <= 0 along the
+    // centre line): the hulls' local bounding boxes bound both supports, so a box gap larger than the
+    // rounding noise proves the exact test fails too.  Never rejects a query MPR would continue.
+    const double* gm = B.geom_xmat + (size_t)env * HMJ_NGEOM * 9;
+    const double n2 = dif0 * dif0 + dif1 * dif1 + dif2 * dif2;
+    if (n2 > 1e-12) {
+      const double inv = rsqrt(n2);
+      const double d[3] = {-dif0 * inv, -dif1 * inv, -dif2 * inv};  // from geom1's centre towards geom2's
+      const double* m1 = gm + g1 * 9;
+      const double* m2 = gm + g2 * 9;
+      const double* lo1 = T->mesh_lo[M.geom_meshid[g1]];
+      const double* hi1 = T->mesh_hi[M.geom_meshid[g1]];
+      const double* lo2 = T->mesh_lo[M.geom_meshid[g2]];
+      const double* hi2 = T->mesh_hi[M.geom_meshid[g2]];
+      double max1 = d[0] * gx[g1 * 3] + d[1] * gx[g1 * 3 + 1] + d[2] * gx[g1 * 3 + 2];
+      double min2 = d[0] * gx[g2 * 3] + d[1] * gx[g2 * 3 + 1] + d[2] * gx[g2 * 3 + 2];
+#pragma unroll
+      for (int q = 0; q < 3; q++) {
+        const double l1 = m1[q] * d[0] + m1[3 + q] * d[1] + m1[6 + q] * d[2];
+        const double l2 = m2[q] * d[0] + m2[3 + q] * d[1] + m2[6 + q] * d[2];
+        max1 += fmax(l1 * lo1[q], l1 * hi1[q]);
+        min2 += fmin(l2 * lo2[q], l2 * hi2[q]);
+      }
+      if (max1 - min2 < -1e-9) hit = false;
+    }
+  }
+  push_tasks(T, B, T->pair_group[k], hit, env, pack_task(k, 0, 0, 0, 0), lane);
+}
+
 // ------------------------------------------------------------------ broadphase + midphase
 // Thread t = k * npad + e (npad = N rounded up to 32, so the pair k is warp-uniform).
 //  * mesh-mesh pair: bounding spheres; survivors become one MPR task.
@@ -722,37 +762,7 @@ k_broad(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int npad, int kpos0
   const int nslot = T->pair_slot[k + 1] - T->pair_slot[k];
 
   if (g1 != 0) {
-    const double dif0 = gx[g1 * 3] - gx[g2 * 3], dif1 = gx[g1 * 3 + 1] - gx[g2 * 3 + 1], dif2 = gx[g1 * 3 + 2] - gx[g2 * 3 + 2];
-    const double bound = M.geom_rbound[g1] + M.geom_rbound[g2];
-    bool hit = in && !(dif0 * dif0 + dif1 * dif1 + dif2 * dif2 > bound * bound);
-    if (hit) {
-      // Conservative pre-screen of ccdMPRPenetration's first exit (dot(support(dir), dir) <= 0 along the
-      // centre line): the hulls' local bounding boxes bound both supports, so a box gap larger than the
-      // rounding noise proves the exact test fails too.  Never rejects a query MPR would continue.
-      const double* gm = B.geom_xmat + (size_t)env * HMJ_NGEOM * 9;
-      const double n2 = dif0 * dif0 + dif1 * dif1 + dif2 * dif2;
-      if (n2 > 1e-12) {
-        const double inv = rsqrt(n2);
-        const double d[3] = {-dif0 * inv, -dif1 * inv, -dif2 * inv};  // from geom1's centre towards geom2's
-        const double* m1 = gm + g1 * 9;
-        const double* m2 = gm + g2 * 9;
-        const double* lo1 = T->mesh_lo[M.geom_meshid[g1]];
-        const double* hi1 = T->mesh_hi[M.geom_meshid[g1]];
-        const double* lo2 = T->mesh_lo[M.geom_meshid[g2]];
-        const double* hi2 = T->mesh_hi[M.geom_meshid[g2]];
-        double max1 = d[0] * gx[g1 * 3] + d[1] * gx[g1 * 3 + 1] + d[2] * gx[g1 * 3 + 2];
-        double min2 = d[0] * gx[g2 * 3] + d[1] * gx[g2 * 3 + 1] + d[2] * gx[g2 * 3 + 2];
-#pragma unroll
-        for (int q = 0; q < 3; q++) {
-          const double l1 = m1[q] * d[0] + m1[3 + q] * d[1] + m1[6 + q] * d[2];
-          const double l2 = m2[q] * d[0] + m2[3 + q] * d[1] + m2[6 + q] * d[2];
-          max1 += fmax(l1 * lo1[q], l1 * hi1[q]);
-          min2 += fmin(l2 * lo2[q], l2 * hi2[q]);
-        }
-        if (max1 - min2 < -1e-9) hit = false;
-      }
-    }
-    push_tasks(T, B, T->pair_group[k], hit, env, pack_task(k, 0, 0, 0, 0), lane);
+    broad_mesh_mesh(T, B, k, env, in, lane);
     return;
   }
   // ---- hfield pair.  NOTE: k_broad is launched with hfield pairs in their own CTAs (npad is a multiple of
@@ -843,7 +853,15 @@ k_broad_hf_coop(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int nhf) {
   const unsigned FULL = 0xffffffffu;
   const int lane = threadIdx.x & 31;
   const int wid = blockIdx.x * 4 + (threadIdx.x >> 5);
-  if (wid >= nhf * B.n) return;
+  if (wid >= nhf * B.n) {   // trailing warps: the mesh-mesh pairs, lane <-> env as in k_broad (one launch for the whole stage)
+    const int w2 = wid - nhf * B.n, per = (B.n + 31) >> 5;
+    const int kp = nhf + w2 / per;
+    if (kp >= HMJ_NPAIR) return;
+    const int e = (w2 - (w2 / per) * per) * 32 + lane;
+    const bool in = e < B.n && (!B.active || B.active[e]);
+    broad_mesh_mesh(T, B, T->broad_order[kp], e < B.n ? e : B.n - 1, in, lane);
+    return;
+  }
   const int kpos = wid / B.n, env = wid - kpos * B.n;
   if (B.active && !B.active[env]) return;
   const hmj_model_t& M = T->m;
@@ -1252,11 +1270,11 @@ void hmj_launch_collide(const hmj_tables_t* tab, hmj_buffers_t buf, cudaStream_t
   const char* force = getenv("HMJ_BROAD_COOP");   // developer override: 0 / 1
   const bool coop = force ? atoi(force) != 0 : buf.n <= BROAD_COOP_MAX_N;
   if (coop) {
-    // small batch: the 9 height-field pairs (first in broad_order) go warp-per-(pair, env); the mesh-mesh pairs keep k_broad
+    // small batch: the 9 height-field pairs (first in broad_order) go warp-per-(pair, env), the mesh-mesh pairs ride in the
+    // trailing warps of the same launch
     const int nhf = HMJ_NPAIR - 28;
-    const long long nmm = (long long)npad * (HMJ_NPAIR - nhf);
-    k_broad<<<(int)(nmm / BROAD_THREADS), BROAD_THREADS, 0, stream>>>(tab, buf, npad, nhf);
-    k_broad_hf_coop<<<(nhf * buf.n + 3) / 4, 128, 0, stream>>>(tab, buf, nhf);
+    const int warps = nhf * buf.n + (HMJ_NPAIR - nhf) * ((buf.n + 31) / 32);
+    k_broad_hf_coop<<<(warps + 3) / 4, 128, 0, stream>>>(tab, buf, nhf);
   } else {
     k_broad<<<(int)(nthread / BROAD_THREADS), BROAD_THREADS, 0, stream>>>(tab, buf, npad, 0);
   }

@@ -32,6 +32,8 @@
 #define NTRI (NV * (NV + 1) / 2)
 #define SOLVE_SMALL_CON 4       /* class 1 holds envs with at most this many contacts */
 #define SOLVE_MID_CON 8         /* class 2: up to this many; class 3: the rest (up to HMJ_MAXCON) */
+#define HMJ_SOLVE_SELFCLASS 256  /* flag in k_solve's `integrate` argument */
+#define SOLVE_SELFCLASS_MAX_N 512
 #define SOLVE_CLASS_OF(MAXC) ((MAXC) == 0 ? 0 : ((MAXC) <= SOLVE_SMALL_CON ? 1 : ((MAXC) <= SOLVE_MID_CON ? 2 : 3)))
 
 // staging rows of chol_factor_solve (below)
@@ -401,9 +403,35 @@ __global__ void __launch_bounds__(32, MAXC == 0 ? 24 : (MAXC <= SOLVE_SMALL_CON 
 k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
   using Smem = SolveSmem<MAXC>;
   extern __shared__ double smem_raw[];
-  if ((int)blockIdx.x >= B.solve_count[SOLVE_CLASS_OF(MAXC)]) return;
   const int lane = threadIdx.x & 31;
-  const int env = B.solve_list[(size_t)SOLVE_CLASS_OF(MAXC) * B.n + blockIdx.x];
+  int env;
+  if (integrate & HMJ_SOLVE_SELFCLASS) {
+    // small batches: no k_classify launch; CTA b looks at env b and leaves unless the env belongs to this class
+    // (one kernel and one dependency edge less on the critical path of a step; the test is k_classify's)
+    env = blockIdx.x;
+    if (env >= B.n || (B.active && !B.active[env])) return;
+    const hmj_model_t& Mm = T->m;
+    const hmj_params_t* Pp = B.params + env;
+    const uint32_t mw = lane < 4 ? B.slot_mask[(size_t)env * 4 + lane] : 0u;
+    int nc = __popc(mw);
+#pragma unroll
+    for (int o = 2; o > 0; o >>= 1) nc += __shfl_xor_sync(0xffffffffu, nc, o);
+    nc = __shfl_sync(0xffffffffu, nc, 0);
+    bool lim = false;
+    const int j = lane + 1;
+    if (j < HMJ_NJNT && Mm.jnt_limited[j]) {
+      const double margin = Pp->jnt_margin[j];
+      const double value = B.qpos[(size_t)env * HMJ_NQ + Mm.jnt_qposadr[j]];
+      lim = (-(Pp->jnt_range[j][0] - value) < margin) || (Pp->jnt_range[j][1] - value < margin);
+    }
+    const bool anylim = __any_sync(0xffffffffu, lim);
+    const int cls = (nc == 0 && !anylim && !INV) ? 0 : (nc <= SOLVE_SMALL_CON ? 1 : (nc <= SOLVE_MID_CON ? 2 : 3));
+    if (cls != SOLVE_CLASS_OF(MAXC)) return;
+  } else {
+    if ((int)blockIdx.x >= B.solve_count[SOLVE_CLASS_OF(MAXC)]) return;
+    env = B.solve_list[(size_t)SOLVE_CLASS_OF(MAXC) * B.n + blockIdx.x];
+  }
+  integrate &= 1;
   Smem& S = *reinterpret_cast<Smem*>(smem_raw);
   const hmj_model_t& M = T->m;
   const hmj_params_t* P = B.params + env;
@@ -1002,8 +1030,9 @@ static void launch_class(const hmj_tables_t* tab, hmj_buffers_t buf, int integra
     cudaFuncSetAttribute(k_solve<MAXC, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     configured[dev] = true;
   }
-  if (integrate == 2) k_solve<MAXC, true><<<buf.n, 32, smem, stream>>>(tab, buf, 0);   // mj_inverse
-  else k_solve<MAXC, false><<<buf.n, 32, smem, stream>>>(tab, buf, integrate);
+  const int self = (integrate & HMJ_SOLVE_SELFCLASS);
+  if ((integrate & 3) == 2) k_solve<MAXC, true><<<buf.n, 32, smem, stream>>>(tab, buf, self);   // mj_inverse
+  else k_solve<MAXC, false><<<buf.n, 32, smem, stream>>>(tab, buf, (integrate & 1) | self);
 }
 
 // Five launches: classification, then one solver launch per class.  With side streams the many-contact class and the
@@ -1012,7 +1041,8 @@ void hmj_launch_solve(const hmj_tables_t* tab, hmj_buffers_t buf, int integrate,
                       const hmj_solve_ctx_t* ctx, bool zero) {
   if (ctx) cudaStreamWaitEvent(stream, ctx->fac_done, 0);   // k_factor ran on side[0] beside the collision kernels
   if (zero) cudaMemsetAsync(buf.solve_count, 0, 4 * sizeof(int32_t), stream);   // else: zeroed by this step's k_smooth
-  k_classify<<<(buf.n + 3) / 4, 128, 0, stream>>>(tab, buf, integrate == 2);
+  if (buf.n <= SOLVE_SELFCLASS_MAX_N) integrate |= HMJ_SOLVE_SELFCLASS;   // the solver CTAs classify their own env
+  else k_classify<<<(buf.n + 3) / 4, 128, 0, stream>>>(tab, buf, integrate == 2);
   if (!ctx) {
     launch_class<HMJ_MAXCON>(tab, buf, integrate, stream);
     launch_class<SOLVE_MID_CON>(tab, buf, integrate, stream);
