@@ -137,7 +137,7 @@ __device__ double norm_value(const double* x, const double* prm, int n, int type
 }
 
 // ------------------------------------------------------------------ k_kin
-__global__ void __launch_bounds__(32 * HMJ_WARPS_PER_CTA)
+__global__ void __launch_bounds__(32 * HMJ_WARPS_PER_CTA, 7)   // 7 CTAs x 4 warps x 148 SMs >= 4096 envs: one wave
 k_kin(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int plan_mode, const double* __restrict__ spline_times,
       const double* __restrict__ spline_values, int nnode, int interpolation, int values_per_env) {
   __shared__ KinSmem smem[HMJ_WARPS_PER_CTA];
@@ -164,6 +164,25 @@ k_kin(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int plan_mode, const 
   double qp = lane < HMJ_NQ ? g_qpos[lane] : 0.0;
   double qv = lane < HMJ_NV ? g_qvel[lane] : 0.0;
   const double pf_mass = (lane >= 1 && lane < HMJ_NBODY) ? P->body_mass[lane] : 0.0;   // requested now: an L2 round trip
+  // model constants of the body this lane owns in the tree walk (independent loads, in flight together with the state)
+  const int kc_nlevel = T->nlevel;
+  int kc_depth = -1, kc_pid = 0, kc_jadr = 0, kc_jnum = 0, kc_jtype = 0, kc_qadr = 0;
+  double kc_bpos[3] = {0, 0, 0}, kc_bquat[4] = {1, 0, 0, 0}, kc_jaxis[3] = {0, 0, 0}, kc_jpos[3] = {0, 0, 0}, kc_q0 = 0.0;
+  if (lane >= 1 && lane < HMJ_NBODY) {
+    const int b = lane;
+    kc_depth = M.body_depth[b];
+    kc_pid = M.body_parentid[b];
+    kc_jadr = M.body_jntadr[b];
+    kc_jnum = M.body_jntnum[b];
+    for (int k = 0; k < 3; k++) kc_bpos[k] = M.body_pos[b][k];
+    for (int k = 0; k < 4; k++) kc_bquat[k] = M.body_quat[b][k];
+    if (kc_jnum == 1) {
+      kc_jtype = M.jnt_type[kc_jadr];
+      kc_qadr = M.jnt_qposadr[kc_jadr];
+      for (int k = 0; k < 3; k++) { kc_jaxis[k] = M.jnt_axis[kc_jadr][k]; kc_jpos[k] = M.jnt_pos[kc_jadr][k]; }
+      kc_q0 = M.qpos0[kc_qadr];
+    }
+  }
   int status = 0;
   bool badq = __any_sync(FULL, d_is_bad(qp));
   bool badv = __any_sync(FULL, d_is_bad(qv));
@@ -203,37 +222,39 @@ k_kin(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int plan_mode, const 
   }
   __syncwarp();
 
-  // ---------------- mj_kinematics, level by level
-  for (int L = 1; L < T->nlevel; L++) {
-    if (lane < T->level_n[L]) {
-      const int b = T->level_body[L][lane];
-      const int pid = M.body_parentid[b];
-      const int jadr = M.body_jntadr[b];
+  // ---------------- mj_kinematics, level by level.  Lane b owns body b and holds that body's model constants in
+  // registers (requested with the state at kernel entry, see kc_*): the loop itself touches no table, where it used to
+  // pay three dependent L1-cold lookups per level (depth -> body -> joint -> axis / offsets), 7 levels deep.
+  for (int L = 1; L < kc_nlevel; L++) {
+    if (kc_depth == L) {
+      const int b = lane;
+      const int pid = kc_pid;
+      const int jadr = kc_jadr;
       double xpos[3], xquat[4];
-      if (M.body_jntnum[b] == 1 && M.jnt_type[jadr] == HMJ_JNT_FREE) {
-        const int qadr = M.jnt_qposadr[jadr];
+      if (kc_jnum == 1 && kc_jtype == HMJ_JNT_FREE) {
+        const int qadr = kc_qadr;
         xpos[0] = S.qpos[qadr]; xpos[1] = S.qpos[qadr + 1]; xpos[2] = S.qpos[qadr + 2];
         xquat[0] = S.qpos[qadr + 3]; xquat[1] = S.qpos[qadr + 4]; xquat[2] = S.qpos[qadr + 5]; xquat[3] = S.qpos[qadr + 6];
         d_normalize4(xquat);
-        for (int k = 0; k < 3; k++) { S.xanchor[jadr][k] = xpos[k]; S.xaxis[jadr][k] = M.jnt_axis[jadr][k]; }
+        for (int k = 0; k < 3; k++) { S.xanchor[jadr][k] = xpos[k]; S.xaxis[jadr][k] = kc_jaxis[k]; }
       } else {
         if (pid) {
-          d_rot_vec_mat(xpos, M.body_pos[b], S.xmat[pid]);
+          d_rot_vec_mat(xpos, kc_bpos, S.xmat[pid]);
           xpos[0] += S.xpos[pid][0]; xpos[1] += S.xpos[pid][1]; xpos[2] += S.xpos[pid][2];
-          d_mul_quat(xquat, S.xquat[pid], M.body_quat[b]);
+          d_mul_quat(xquat, S.xquat[pid], kc_bquat);
         } else {
-          for (int k = 0; k < 3; k++) xpos[k] = M.body_pos[b][k];
-          for (int k = 0; k < 4; k++) xquat[k] = M.body_quat[b][k];
+          for (int k = 0; k < 3; k++) xpos[k] = kc_bpos[k];
+          for (int k = 0; k < 4; k++) xquat[k] = kc_bquat[k];
         }
-        if (M.body_jntnum[b] == 1) {  // one hinge
-          const int qadr = M.jnt_qposadr[jadr];
+        if (kc_jnum == 1) {  // one hinge
+          const int qadr = kc_qadr;
           double axis[3], anchor[3], qloc[4], vec[3];
-          d_rot_vec_quat(axis, M.jnt_axis[jadr], xquat);
-          d_rot_vec_quat(anchor, M.jnt_pos[jadr], xquat);
+          d_rot_vec_quat(axis, kc_jaxis, xquat);
+          d_rot_vec_quat(anchor, kc_jpos, xquat);
           anchor[0] += xpos[0]; anchor[1] += xpos[1]; anchor[2] += xpos[2];
-          d_axis_angle2quat(qloc, M.jnt_axis[jadr], S.qpos[qadr] - M.qpos0[qadr]);
+          d_axis_angle2quat(qloc, kc_jaxis, S.qpos[qadr] - kc_q0);
           d_mul_quat(xquat, xquat, qloc);
-          d_rot_vec_quat(vec, M.jnt_pos[jadr], xquat);
+          d_rot_vec_quat(vec, kc_jpos, xquat);
           for (int k = 0; k < 3; k++) {
             xpos[k] = anchor[k] - vec[k];
             S.xanchor[jadr][k] = anchor[k];
