@@ -98,6 +98,7 @@ struct hmj_batch_ {
   // its own stream, forked from / joined to the main stream inside the call.  Every stage is a single wave whose length is
   // its slowest env, so stages of different pipes fill each other's tails (envs are independent: no data-path exchange).
   struct Pipe {
+    int start = 0;                   // first env of the pipe
     hmj_buffers_t view{};
     cudaStream_t stream = nullptr;
     cudaEvent_t done = nullptr;
@@ -107,6 +108,18 @@ struct hmj_batch_ {
   cudaEvent_t pipe_fork = nullptr;
   // step graphs: [0] forward only, [1] with integration
   cudaGraphExec_t step_graph[2] = {nullptr, nullptr};
+  // control-step graph of hmj_env_step_fused_from (prologue, physics, epilogue and result copies inside the pipes)
+  struct CtrlKey {
+    int has_action = -1, split = 0;
+    double rf = 0, mst = 0;
+    unsigned long long seed = 0;
+    bool operator==(const CtrlKey& o) const {
+      return has_action == o.has_action && split == o.split && rf == o.rf && mst == o.mst && seed == o.seed;
+    }
+  };
+  cudaGraphExec_t ctrl_graph = nullptr;
+  CtrlKey ctrl_key{};
+  int ctrl_mode = 1;                 // 0: prologue / epilogue as whole-batch kernels around the step graph (HMJ_E2E=0)
   int graph_mode = 1;
   bool warmed = false;
   // per-kernel CUDA-event profiling (hmj_batch_profile): events bracket every launch of a step
@@ -346,6 +359,7 @@ static int make_pipes(hmj_batch_* b) {
     hmj_batch_::Pipe& pp = b->pipes[p];
     const int count = base + (p < rem ? 1 : 0);
     pp.view = pipe_view(b->buf, start, count, p, group_total);
+    pp.start = start;
     start += count;
     CK(cudaStreamCreateWithFlags(&pp.stream, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&pp.done, cudaEventDisableTiming));
@@ -374,6 +388,7 @@ extern "C" void hmj_batch_destroy(hmj_batch_t* b) {
   if (b->task_dev) cudaFree(b->task_dev);
   for (int k = 0; k < 2; k++)
     if (b->step_graph[k]) cudaGraphExecDestroy(b->step_graph[k]);
+  if (b->ctrl_graph) cudaGraphExecDestroy(b->ctrl_graph);
   for (auto& pp : b->pipes) {
     for (int k = 0; k < 2; k++) {
       if (pp.ctx.side[k]) cudaStreamDestroy(pp.ctx.side[k]);
@@ -588,6 +603,7 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
     CKB(cudaStreamSynchronize(b->stream));
   }
   if (const char* e = getenv("HMJ_GRAPH")) b->graph_mode = atoi(e);   // developer override: 0 = direct launches
+  if (const char* e = getenv("HMJ_E2E")) b->ctrl_mode = atoi(e);      // developer override: 0 = whole-batch prologue / epilogue
   {
     int rc = make_pipes(b);
     if (rc) { hmj_batch_destroy(b); return rc; }
@@ -734,6 +750,72 @@ static void enqueue_one_step(hmj_batch_t* b, int integrate) {
     cudaEventRecord(pp.done, pp.stream);
     cudaStreamWaitEvent(b->stream, pp.done, 0);
   }
+}
+
+// ONE control step of the whole batch as a chain on the main stream (captured into b->ctrl_graph): every pipe runs its
+// own prologue (k_env_pre on its rows), physics step and epilogue (observation, reward, flags, delay FIFOs in one kernel)
+// and, with `to_host`, copies its observation rows to the pinned result block as soon as they exist — prologue, epilogue
+// and copy of one pipe overlap the physics of the other; the small result arrays follow in one copy after the join.
+// Without `to_host` the caller copies the block itself (the episode pool patches it first).
+static void enqueue_control_chain(hmj_batch_t* b, int has_action, double rf, double mst, unsigned long long seed, bool to_host) {
+  const size_t N = b->n;
+  const double* d_action = has_action ? (const double*)b->io_dev : nullptr;
+  double* d_out = (double*)(b->io_dev + b->io_in_bytes);
+  char* h_out = b->io_host + b->io_in_bytes;
+  hmj_results_t R{};
+  R.obs = d_out; R.reward = d_out + N * 30; R.time = d_out + N * 31; R.quat = d_out + N * 32;
+  R.terminated = (int32_t*)(d_out + N * 36); R.truncated = R.terminated + N; R.self_collision = R.terminated + 2 * N;
+  struct Part { hmj_buffers_t view; int start; cudaStream_t stream; const hmj_solve_ctx_t* ctx; };
+  std::vector<Part> parts;
+  if (b->pipes.empty()) parts.push_back(Part{b->buf, 0, b->stream, &b->solve_ctx});
+  else {
+    cudaEventRecord(b->pipe_fork, b->stream);
+    for (auto& pp : b->pipes) {
+      cudaStreamWaitEvent(pp.stream, b->pipe_fork, 0);
+      parts.push_back(Part{pp.view, pp.start, pp.stream, &pp.ctx});
+    }
+  }
+  for (auto& q : parts) hmj_launch_env_pre_rows(b->buf, b->env, d_action, rf, seed, q.start, q.view.n, q.stream);
+  for (auto& q : parts) hmj_launch_smooth(b->tab_dev, q.view, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, q.stream, q.ctx);
+  for (auto& q : parts) hmj_launch_factor(b->tab_dev, q.view, q.stream, q.ctx);
+  for (auto& q : parts) hmj_launch_collide(b->tab_dev, q.view, q.stream, false);
+  for (auto& q : parts) hmj_launch_solve(b->tab_dev, q.view, 1, q.stream, q.ctx, false);
+  for (auto& q : parts) {
+    hmj_launch_env_epilogue(b->tab_dev, b->buf, b->env, mst, R, q.start, q.view.n, q.stream);
+    if (to_host)
+      cudaMemcpyAsync(h_out + (size_t)q.start * 30 * 8, R.obs + (size_t)q.start * 30, (size_t)q.view.n * 30 * 8,
+                      cudaMemcpyDeviceToHost, q.stream);
+  }
+  for (auto& pp : b->pipes) {
+    cudaEventRecord(pp.done, pp.stream);
+    cudaStreamWaitEvent(b->stream, pp.done, 0);
+  }
+  if (to_host) cudaMemcpyAsync(h_out + N * 30 * 8, R.reward, b->io_ext_offset - N * 30 * 8, cudaMemcpyDeviceToHost, b->stream);
+}
+
+// Replays (capturing it first when the scalars baked into it changed) the control-step graph.  false: not available.
+static bool launch_control_graph(hmj_batch_t* b, int has_action, double rf, double mst, unsigned long long seed, bool split) {
+  hmj_batch_::CtrlKey key;
+  key.has_action = has_action; key.split = split ? 1 : 0; key.rf = rf; key.mst = mst; key.seed = seed;
+  if (!b->ctrl_graph || !(key == b->ctrl_key)) {
+    if (b->ctrl_graph) { cudaGraphExecDestroy(b->ctrl_graph); b->ctrl_graph = nullptr; }
+    cudaGraph_t g = nullptr;
+    if (cudaStreamBeginCapture(b->stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) { cudaGetLastError(); return false; }
+    enqueue_control_chain(b, has_action, rf, mst, seed, split);
+    if (cudaStreamEndCapture(b->stream, &g) != cudaSuccess || !g || cudaGraphInstantiate(&b->ctrl_graph, g, 0) != cudaSuccess) {
+      if (g) cudaGraphDestroy(g);
+      b->ctrl_graph = nullptr;
+      cudaGetLastError();
+      return false;
+    }
+    cudaGraphDestroy(g);
+    b->ctrl_key = key;
+  }
+  if (cudaGraphLaunch(b->ctrl_graph, b->stream) != cudaSuccess) { cudaGetLastError(); return false; }
+  const int P = b->pipes.empty() ? 1 : (int)b->pipes.size();
+  b->launches += 12 * P;   // prologue + 10 step kernels + epilogue per pipe
+  b->host_launches += 1;
+  return true;
 }
 
 // nsteps physics steps of the whole batch.  The step chain (8 kernels per pipe, forks and joins; the per-step counters are zeroed inside k_smooth) is
@@ -1046,18 +1128,29 @@ extern "C" int hmj_env_step_fused_from(hmj_batch_t* b, const double* action_host
     if (has_mask) CK(cudaMemcpyAsync(d_mask, b->io_host + N * HMJ_NU * 8, N * 4, cudaMemcpyHostToDevice, b->stream));
   }
   const int32_t* mask = has_mask ? d_mask : nullptr;
-  if (nsteps >= 0) hmj_launch_env_pre(b->buf, b->env, has_action ? d_action : nullptr, mask, rf, seed, b->stream);
-  enqueue_steps(b, 1, nsteps);
-  hmj_launch_env_obs_reward(b->tab_dev, b->buf, b->env.prev_action, b->env.latest_action, b->env.obs_noise, max_sim_time, d_obs,
-                            d_rew, d_flags, d_flags + N, d_flags + 2 * N, b->stream);
-  hmj_launch_env_post(b->buf, b->env, mask, d_obs, d_time, d_quat, b->stream);
-  b->launches += 3; b->host_launches += 3;
   const bool pool = b->pool_on && nsteps >= 0 && !has_mask;
+  // the common call (one physics step, every env) replays the control-step graph; its result copies are inside unless the
+  // episode pool still has to look at (and patch) the results
+  bool copied = false, done = false;
+  if (b->ctrl_mode && !has_mask && nsteps == 1 && !b->profile && b->warmed && b->graph_mode != 0) {
+    done = launch_control_graph(b, has_action, rf, max_sim_time, seed, !pool);
+    if (done) copied = !pool;
+    else b->ctrl_mode = 0;   // capture unavailable: whole-batch kernels around the step graph from now on
+  }
+  if (!done) {
+    if (nsteps >= 0) hmj_launch_env_pre(b->buf, b->env, has_action ? d_action : nullptr, mask, rf, seed, b->stream);
+    enqueue_steps(b, 1, nsteps);
+    hmj_launch_env_obs_reward(b->tab_dev, b->buf, b->env.prev_action, b->env.latest_action, b->env.obs_noise, max_sim_time, d_obs,
+                              d_rew, d_flags, d_flags + N, d_flags + 2 * N, b->stream);
+    hmj_launch_env_post(b->buf, b->env, mask, d_obs, d_time, d_quat, b->stream);
+    b->launches += 3; b->host_launches += 3;
+  }
   if (pool) {
     int rc = pool_step(b, d_flags, d_flags + N, false);
     if (rc) return rc;
   }
-  CK(cudaMemcpyAsync(b->io_host + b->io_in_bytes, d_out, pool ? b->io_out_bytes : b->io_ext_offset, cudaMemcpyDeviceToHost, b->stream));
+  if (!copied)
+    CK(cudaMemcpyAsync(b->io_host + b->io_in_bytes, d_out, pool ? b->io_out_bytes : b->io_ext_offset, cudaMemcpyDeviceToHost, b->stream));
   CK(cudaStreamSynchronize(b->stream));
   CK(cudaGetLastError());
   if (pool) {

@@ -7,6 +7,7 @@
 //    (simulation/reward_functions.py:247-374), one thread per environment.
 // These are HBM/L2-bound streaming kernels (a few hundred bytes per env), thread-per-env.
 #include "hmj_dev.cuh"
+#include "hmj_envstep.cuh"
 
 // ------------------------------------------------------------------ planner
 // `state` = qpos | qvel | time (HMJ_NSTATE + 1 doubles on the device: no by-value argument changes between planning
@@ -223,120 +224,36 @@ void hmj_launch_plan_select(const double* gathered_dev, int nranks, int stride, 
   k_plan_select<<<1, 32, 0, stream>>>(gathered_dev, nranks, stride, out_dev);
 }
 
-// ------------------------------------------------------------------ CPUEnv epilogue
-__device__ __forceinline__ double scaled_exp(double x) { return exp(-x / 0.5); }
-
-// inverseRotateVectors(q, (0,0,-1)) with scipy/JAX Rotation semantics (normalises q): -(third row of R(q))
-__device__ __forceinline__ void local_gravity(const double* quat_in, double* g) {
-  double q[4] = {quat_in[0], quat_in[1], quat_in[2], quat_in[3]};
-  const double n = sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
-  const double s = 1.0 / n;
-  q[0] *= s; q[1] *= s; q[2] *= s; q[3] *= s;
-  double R[9];
-  d_quat2mat(R, q);
-  g[0] = -R[6]; g[1] = -R[7]; g[2] = -R[8];
-}
-
-// One warp per environment: lanes 0..11 own one actuator each (its two observation entries and its three exp() reward
-// terms), lanes 0..5 then the six symmetry terms, lane 12 the noisy-quaternion gravity of the observation, lane 0 the
-// remaining scalar terms and the final sum.  Every sum is formed by lane 0 in the reference's order (a = 0..11), so the
-// result is the same bits as the one-thread-per-env form; the 45 exp() calls are what made that form ~20 us of latency.
+// ------------------------------------------------------------------ CPUEnv epilogue (per-warp bodies: hmj_envstep.cuh)
+// One warp per environment of rows [first, last).  `post`: also the delay FIFOs / torso_quat of k_env_post (no mask).
 #define OBS_WARPS 4
 __global__ void __launch_bounds__(32 * OBS_WARPS)
 k_env_obs_reward(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const double* __restrict__ prev_action,
                  const double* __restrict__ latest_action, const double* __restrict__ noise, double max_sim_time,
-                 double* __restrict__ obs, double* __restrict__ reward, int32_t* __restrict__ terminated,
-                 int32_t* __restrict__ truncated, int32_t* __restrict__ self_collision) {
-  __shared__ double st[OBS_WARPS][5][HMJ_NU];   // tq, dc, reg, u per actuator; sym terms
+                 hmj_results_t R, int first, int last, hmj_envstate_t E, int post) {
+  __shared__ double st[OBS_WARPS][5 * HMJ_NU];   // tq, dc, reg, u per actuator; sym terms
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  const int env = blockIdx.x * OBS_WARPS + w;
-  if (env >= B.n) return;
+  const int env = first + blockIdx.x * OBS_WARPS + w;
+  if (env >= last) return;
   if (B.active && !B.active[env]) return;
-  const hmj_model_t& M = T->m;
-  const double* qpos = B.qpos + (size_t)env * HMJ_NQ;
-  const double* qvel = B.qvel + (size_t)env * HMJ_NV;
-  const double* sens = B.sens + (size_t)env * SENS_NUM;
-  const double* nz = noise ? noise + (size_t)env * 31 : nullptr;
-  const double* tq = sens + SENS_ROOT_XQUAT;  // data.xquat[torso_idx]: one step stale
-  double* o = obs + (size_t)env * 30;
-  // ---- observation (cpu_env.py:465-571), undelayed; JOINT_NAMES follow the actuator order
-  if (lane < HMJ_NU) {
-    const int a = lane;
-    o[a] = qpos[M.act_qposadr[a]] + (nz ? nz[a] : 0.0);
-    o[12 + a] = qvel[M.act_dofadr[a]] + (nz ? nz[12 + a] : 0.0);
-    // ---- per-actuator terms of standupReward (reward_functions.py:247-374)
-    const int d = M.act_dofadr[a];
-    const double tau = B.qfrc_constraint[(size_t)env * HMJ_NV + d] + B.qfrc_smooth[(size_t)env * HMJ_NV + d];
-    const double ex = fmax(fabs(tau) - 1.0, 0.0);
-    const double lat = latest_action[(size_t)env * HMJ_NU + a] / (HMJ_PI / 2);
-    const double prv = prev_action[(size_t)env * HMJ_NU + a] / (HMJ_PI / 2);
-    const double dc = (lat - prv) * 500.0;
-    st[w][0][a] = scaled_exp(ex * ex);
-    st[w][1][a] = scaled_exp(dc * dc);
-    st[w][2][a] = scaled_exp(lat * lat);
-    st[w][3][a] = lat;
-  } else if (lane < HMJ_NU + 3) {
-    const int k = lane - HMJ_NU;
-    o[24 + k] = qvel[3 + k] + (nz ? nz[24 + k] : 0.0);
-  } else if (lane == HMJ_NU + 3) {
-    double nq[4] = {tq[0] + (nz ? nz[27] : 0.0), tq[1] + (nz ? nz[28] : 0.0), tq[2] + (nz ? nz[29] : 0.0), tq[3] + (nz ? nz[30] : 0.0)};
-    double g[3];
-    local_gravity(nq, g);
-    o[27] = g[0]; o[28] = g[1]; o[29] = g[2];
-  }
-  __syncwarp();
-  if (lane < 6) {
-    const double* u = st[w][3];
-    // elbows equal; hip roll / hip pitch / knee / shoulder pitch / shoulder roll opposite
-    const int i1[6] = {5, 6, 7, 8, 3, 4}, i2[6] = {2, 9, 10, 11, 0, 1};
-    const double v = (lane == 0) ? (u[i1[0]] - u[i2[0]]) : (u[i1[lane]] + u[i2[lane]]);
-    st[w][4][lane] = scaled_exp(v * v);
-  }
-  __syncwarp();
-  if (lane != 0) return;
-  double gl[3];
-  local_gravity(tq, gl);
-  const double z = sens[SENS_ROOT_Z];
-  double r = 0.0;
-  r += 5.0 * scaled_exp(qvel[0] * qvel[0] + qvel[1] * qvel[1]);                 // horizontal velocity (target 0)
-  {
-    const double dx = gl[0], dy = gl[1], dz = gl[2] + 1.0;
-    r += 10.0 * scaled_exp(dx * dx + dy * dy + dz * dz);                        // upright (yaw weight 0)
-  }
-  {
-    const double z0 = -0.6, z1 = -0.375;                                         // np.interp(z, [MIN_Z, TARGET_Z], [0, 15])
-    r += (z <= z0) ? 0.0 : (z >= z1 ? 15.0 : (z - z0) / (z1 - z0) * 15.0);
-  }
-  double tq_sum = 0.0, dc_sum = 0.0, reg_sum = 0.0;
-  for (int a = 0; a < HMJ_NU; a++) { tq_sum += st[w][0][a]; dc_sum += st[w][1][a]; reg_sum += st[w][2][a]; }
-  r += 2.5 * tq_sum / 12.0;
-  r += 2.0 * dc_sum / 12.0;
-  r += 0.5 * reg_sum / 12.0;
-  {
-    double sym = 0.0;
-    for (int k = 0; k < 6; k++) sym += st[w][4][k];
-    r += 1.0 * sym / 6.0;
-  }
-  int selfc = 0;
-  const int nc = B.ncon[env];
-  for (int c = 0; c < nc; c++)
-    if (B.contact[(size_t)env * HMJ_MAXCON + c].g1 != 0) selfc = 1;
-  if (selfc) r += -20.0;
-  const int term = B.time[env] >= max_sim_time;
-  if (term) r = -100.0;
-  const int upright = fmax(fabs(gl[0]), fabs(gl[1])) < 0.7;
-  reward[env] = r;
-  terminated[env] = term;
-  truncated[env] = (z >= -0.375) && upright;
-  if (self_collision) self_collision[env] = selfc;
+  env_obs_reward_warp(T, B, env, env, lane, st[w], prev_action, latest_action, noise, max_sim_time, R, post, E);
 }
 
 void hmj_launch_env_obs_reward(const hmj_tables_t* tab, hmj_buffers_t buf, const double* prev_action, const double* latest_action,
                                const double* noise, double max_sim_time, double* obs, double* reward, int32_t* terminated,
                                int32_t* truncated, int32_t* self_collision, cudaStream_t stream) {
-  k_env_obs_reward<<<(buf.n + OBS_WARPS - 1) / OBS_WARPS, 32 * OBS_WARPS, 0, stream>>>(tab, buf, prev_action, latest_action, noise,
-                                                                                       max_sim_time, obs, reward, terminated,
-                                                                                       truncated, self_collision);
+  hmj_results_t R{};
+  R.obs = obs; R.reward = reward; R.terminated = terminated; R.truncated = truncated; R.self_collision = self_collision;
+  k_env_obs_reward<<<(buf.n + OBS_WARPS - 1) / OBS_WARPS, 32 * OBS_WARPS, 0, stream>>>(
+      tab, buf, prev_action, latest_action, noise, max_sim_time, R, 0, buf.n, hmj_envstate_t{}, 0);
+}
+
+// Epilogue of the control step for envs [first, first + count) of the batch as a kernel of its own: observation + reward
+// + the delay FIFOs and torso_quat of k_env_post (no mask).
+void hmj_launch_env_epilogue(const hmj_tables_t* tab, hmj_buffers_t buf, hmj_envstate_t env, double max_sim_time, hmj_results_t R,
+                             int first, int count, cudaStream_t stream) {
+  k_env_obs_reward<<<(count + OBS_WARPS - 1) / OBS_WARPS, 32 * OBS_WARPS, 0, stream>>>(
+      tab, buf, env.prev_action, env.latest_action, env.obs_noise, max_sim_time, R, first, first + count, env, 1);
 }
 
 // ------------------------------------------------------------------ CPUEnv prologue / delay FIFOs on the device
@@ -345,10 +262,10 @@ void hmj_launch_env_obs_reward(const hmj_tables_t* tab, hmj_buffers_t buf, const
 #define ENV_WARPS 4
 __global__ void __launch_bounds__(32 * ENV_WARPS)
 k_env_pre(hmj_buffers_t B, hmj_envstate_t E, const double* __restrict__ action, const int32_t* __restrict__ mask,
-          double rf, unsigned long long seed, int sid0) {
+          double rf, unsigned long long seed, int sid0, int first, int last) {
   const int lane = threadIdx.x & 31;
-  const int env = blockIdx.x * ENV_WARPS + (threadIdx.x >> 5);
-  if (env >= B.n || (mask && !mask[env])) return;
+  const int env = first + blockIdx.x * ENV_WARPS + (threadIdx.x >> 5);
+  if (env >= last || (mask && !mask[env])) return;
   // ---- action: + constant noise, delay FIFO, NO clipping (cpu_env.py:670-671); action == NULL re-sends data.ctrl
   const int cnt = E.act_count[env];
   const int d = E.act_delay[env];
@@ -402,36 +319,21 @@ k_env_post(hmj_buffers_t B, hmj_envstate_t E, const int32_t* __restrict__ mask, 
   const int lane = threadIdx.x & 31;
   const int env = blockIdx.x * ENV_WARPS + (threadIdx.x >> 5);
   if (env >= B.n) return;
-  if (lane == 0 && time_out) time_out[env] = B.time[env];
-  if (mask && !mask[env]) {
-    if (quat_out && lane < 4) quat_out[(size_t)env * 4 + lane] = E.torso_quat[(size_t)env * 4 + lane];
-    return;
-  }
-  if (lane < 4) {
-    const double v = B.sens[(size_t)env * SENS_NUM + SENS_ROOT_XQUAT + lane] + E.obs_noise[(size_t)env * 31 + 27 + lane];
-    E.torso_quat[(size_t)env * 4 + lane] = v;
-    if (quat_out) quat_out[(size_t)env * 4 + lane] = v;
-  }
-  const int cnt = E.obs_count[env];
-  if (lane < 30) {
-    const int k = lane;
-    double* hist = E.obs_hist + (size_t)env * HMJ_ENV_HIST * 30;
-    double* o = obs + (size_t)env * 30;
-    const int slot = cnt % HMJ_ENV_HIST;
-    const double v = o[k];
-    hist[slot * 30 + k] = v;
-    const int g = k < 24 ? 0 : (k < 27 ? 1 : 2);   // joint pos+vel / angular velocity / gravity groups
-    const int d = E.obs_delay[(size_t)env * 3 + g];
-    const int src = ((cnt - d) % HMJ_ENV_HIST + HMJ_ENV_HIST) % HMJ_ENV_HIST;
-    o[k] = (cnt >= d) ? (src == slot ? v : hist[src * 30 + k]) : ((k == 29) ? -1.0 : 0.0);
-  }
-  __syncwarp();
-  if (lane == 0) E.obs_count[env] = cnt + 1;
+  hmj_results_t R{};
+  R.obs = obs; R.time = time_out; R.quat = quat_out;
+  env_post_warp(B, E, mask, R, env, env, lane);
 }
 
 void hmj_launch_env_pre(hmj_buffers_t buf, hmj_envstate_t env, const double* action, const int32_t* mask, double rf,
                         unsigned long long seed, cudaStream_t stream, int stream_id_offset) {
-  k_env_pre<<<(buf.n + ENV_WARPS - 1) / ENV_WARPS, 32 * ENV_WARPS, 0, stream>>>(buf, env, action, mask, rf, seed, stream_id_offset);
+  k_env_pre<<<(buf.n + ENV_WARPS - 1) / ENV_WARPS, 32 * ENV_WARPS, 0, stream>>>(buf, env, action, mask, rf, seed, stream_id_offset, 0,
+                                                                                buf.n);
+}
+// the same for envs [first, first + count) of the batch (`buf` is the whole batch)
+void hmj_launch_env_pre_rows(hmj_buffers_t buf, hmj_envstate_t env, const double* action, double rf, unsigned long long seed,
+                             int first, int count, cudaStream_t stream) {
+  k_env_pre<<<(count + ENV_WARPS - 1) / ENV_WARPS, 32 * ENV_WARPS, 0, stream>>>(buf, env, action, nullptr, rf, seed, 0, first,
+                                                                                first + count);
 }
 void hmj_launch_env_post(hmj_buffers_t buf, hmj_envstate_t env, const int32_t* mask, double* obs, double* time_out, double* quat_out,
                          cudaStream_t stream) {

@@ -152,6 +152,16 @@ struct hmj_envstate_t {
   double* torso_quat;    // [N][4]   noisy root quaternion (CPUEnv.torso_quat, read by controllers/mpc_in_env.py:25)
 };
 
+// Result block of a control step (CPUEnv.step's return values), rows indexed by the env id of the whole batch.
+struct hmj_results_t {
+  double* obs;           // [N][30]
+  double* reward;        // [N]
+  double* time;          // [N]
+  double* quat;          // [N][4]  CPUEnv.torso_quat
+  int32_t* terminated;   // [N]
+  int32_t* truncated;    // [N]
+  int32_t* self_collision; // [N]
+};
 // Episode pool (hmj_reset.cu): S spare rows behind the N envs of a batch hold pre-validated fresh episodes.
 #define HMJ_POOL_EMPTY 0     /* row free: the next generation round draws a new episode into it */
 #define HMJ_POOL_PROBING 1   /* being generated: the round's kernels run on it (active mask) */
@@ -384,5 +394,9 @@ void hmj_launch_fd_setup(const hmj_tables_t* tab, hmj_buffers_t view, int nknot,
 void hmj_launch_fd_diff(const hmj_tables_t* tab, hmj_buffers_t view, int nknot, const int32_t* valid_dev, double eps, double* A,
                         double* B, double* C, double* D, cudaStream_t stream);
 void hmj_launch_pool_mark_pending(hmj_pool_t pool, const int32_t* ids_dev, int count, int n, cudaStream_t stream);
+void hmj_launch_env_epilogue(const hmj_tables_t* tab, hmj_buffers_t buf, hmj_envstate_t env, double max_sim_time, hmj_results_t R,
+                             int first, int count, cudaStream_t stream);
+void hmj_launch_env_pre_rows(hmj_buffers_t buf, hmj_envstate_t env, const double* action, double rf, unsigned long long seed,
+                             int first, int count, cudaStream_t stream);
 void hmj_launch_env_post(hmj_buffers_t buf, hmj_envstate_t env, const int32_t* mask, double* obs, double* time_out, double* quat_out,
                          cudaStream_t stream);

@@ -1,8 +1,20 @@
 #!/bin/bash
-# A/B of two builds of the library on the bench workload: lib/ (A) vs lib_prof/ (B)
-for v in A B; do
-  if [ $v = B ]; then export HMJ_B200_LIB=humanoid-mujoco_b200/lib_prof/libhmj_b200.so; fi
-  python bench.py --steps 200 --warmup 10 --no-plan 2>/dev/null > gpurun_out/ab_$v.json
-  python -c "
-import json; d=json.load(open('gpurun_out/ab_$v.json')); print('$v', '%.4g' % d['value'], '%.4g' % d['e2e']['value'], {k: round(x, 4) for k, x in d['roofline']['kernel_ms'].items()})"
+# Developer A/B: quick bench (both regimes, value + e2e) under a list of environment settings.
+# usage: tools/dev/ab.sh <tag> "VAR=1 VAR2=2" "..." ...     (an empty string = defaults)
+TAG=$1; shift
+mkdir -p gpurun_out
+i=0
+for cfg in "$@"; do
+  out=gpurun_out/${TAG}_ab${i}.json
+  env $cfg timeout 600 python bench.py --steps 200 --warmup 10 --no-plan --no-c5 --no-cpu > $out 2> gpurun_out/${TAG}_ab${i}.err
+  python - "$cfg" $out <<'P'
+import json, sys
+try:
+    d = json.load(open(sys.argv[2]))
+    w = d["workloads"]
+    print("[%s]" % sys.argv[1], " ".join("%s value %.4g e2e %.4g" % (k, v["value"], v["e2e"]["value"]) for k, v in w.items()))
+except Exception as e:
+    print("[%s] failed: %s" % (sys.argv[1], e))
+P
+  i=$((i+1))
 done
