@@ -255,6 +255,8 @@ class HumanoidBatch:
                 cnt = int(np.prod(shape))
                 ct = C.c_double if dt is np.float64 else C.c_int32
                 io[name] = np.ctypeslib.as_array((ct * cnt).from_address(p.value)).reshape(shape)
+            # terminated | truncated | self_collision are adjacent in the block (hmj_env_io): one byte view over all three
+            io["flag_bytes"] = np.ctypeslib.as_array((C.c_bool * (12 * n)).from_address(ptrs[6].value))
             self._io = io
         return self._io
 

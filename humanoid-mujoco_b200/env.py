@@ -524,6 +524,9 @@ class BatchedHumanoidEnv:
         self.batch.env_step_fused(act, only is not None, self.randomization_factor, self.max_simulation_time, self.seed, 1)
         self.time = io["time"]
         self.torso_quat = io["torso_quat"]
+        if not io["flag_bytes"].any():    # almost every step: no flag of any kind raised (one scan instead of three)
+            af = self._all_false
+            return self._finish(io["obs"], io["reward"], af, af, af, only)
         return self._finish(io["obs"], io["reward"], self._flags(io["terminated"]), self._flags(io["truncated"]),
                             self._flags(io["self_collision"]), only)
 

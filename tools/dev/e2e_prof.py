@@ -1,52 +1,49 @@
-"""Where the end-to-end control step spends its time (4096 envs): python staging, the fused C call, result handling."""
-import sys, time, os
+"""Developer tool: where the end-to-end control step spends its time beyond the device step (bench workload C3).
+usage: e2e_prof.py [scale] [steps]"""
+import os, sys, time
 import numpy as np
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+sys.path[:0] = [os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))]
 import bench
 import humanoid_mujoco_b200 as hmj
 
-n = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
-env = hmj.BatchedHumanoidEnv(n, randomization_factor=1.0, device=0, seed=1)
+scale = float(sys.argv[1]) if len(sys.argv) > 1 else 1.0
+K = int(sys.argv[2]) if len(sys.argv) > 2 else 300
+n = 4096
+env = hmj.BatchedHumanoidEnv(n, randomization_factor=0.0, seed=1)
 b = env.batch
-params, qpos = bench.make_workload(b.default_params(), b.model["qpos0"][0], n, 1)
-env.params[:] = params
-b.set_params(params)
-b.set_state(qpos, np.zeros((n, 18)), np.zeros(n), np.zeros((n, 18)))
+z18 = np.zeros((n, 18))
+def probe(params, qpos):
+    b.set_params(params); b.set_state(qpos, z18, np.zeros(n), z18); b.step(np.zeros((n, 12)), 1); return b.get("ncon") > 0
+params, qpos, attempts = bench.make_workload(b.default_params(), b.model["qpos0"][0], n, 1, probe)
+b.set("status", np.zeros(n, dtype=np.int32))
+env.reset_to(params, qpos)
 b.step(np.zeros((n, 12)), bench.SETTLE_STEPS)
 acts = hmj.pinned_empty((64, n, 12))
-acts[...] = np.random.default_rng(5).uniform(-1, 1, acts.shape)
-for s in range(20):
-    env.step(acts[s])
-K = 300
-T0 = time.perf_counter()
-for s in range(K):
+acts[...] = np.random.default_rng(5).uniform(-scale, scale, acts.shape)
+for s in range(150):
     env.step(acts[s % 64])
-T1 = time.perf_counter()
-print("env.step per step us:", round(1e6 * (T1 - T0) / K, 1))
-T0 = time.perf_counter()
-for s in range(K):
-    b.env_step_fused(acts[s % 64], False, env.randomization_factor, env.max_simulation_time, env.seed, 1)
-T1 = time.perf_counter()
-print("fused C call (pinned action) per step us:", round(1e6 * (T1 - T0) / K, 1))
-import torch
-st = torch.cuda.ExternalStream(b.stream)
-ring = torch.as_tensor(acts[:64]).cuda()
-e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-e0.record(st)
-for s in range(K):
-    b.step_dev(ring[s % 64].data_ptr(), 1)
-e1.record(st)
-b.sync()
-print("device-only physics step (random ctrl ring) us:", round(1e3 * e0.elapsed_time(e1) / K, 1))
+lib, h = b.lib, b._h
+calls = []
+orig = lib.hmj_env_step_fused_from
+def timed(*a):
+    t = time.perf_counter(); r = orig(*a); calls.append(time.perf_counter() - t); return r
+b.lib.hmj_env_step_fused_from = timed
 t0 = time.perf_counter()
 for s in range(K):
-    b.step_dev(ring[s % 64].data_ptr(), 1)
-    b.sync()
-print("physics step + sync each step us:", round(1e6 * (time.perf_counter() - t0) / K, 1))
-import cProfile, pstats
-pr = cProfile.Profile()
-pr.enable()
-for s in range(K):
     env.step(acts[s % 64])
-pr.disable()
-pstats.Stats(pr).sort_stats("tottime").print_stats(14)
+tot = (time.perf_counter() - t0) / K
+b.lib.hmj_env_step_fused_from = orig
+c = float(np.mean(calls))
+# device-only steps (same controls already on the device)
+b.sync()
+t0 = time.perf_counter()
+for s in range(K):
+    b.step_dev(None, 1)
+b.sync()
+dev = (time.perf_counter() - t0) / K
+# replayed controls (no H2D)
+t0 = time.perf_counter()
+for s in range(K):
+    env.step(None)
+rep = (time.perf_counter() - t0) / K
+print(f"env.step {tot*1e6:.1f} us | C call {c*1e6:.1f} us | python around it {(tot-c)*1e6:.1f} us | device-only step loop {dev*1e6:.1f} us | env.step(None) {rep*1e6:.1f} us")
