@@ -56,6 +56,8 @@ def load_library() -> C.CDLL:
     lib.hmj_batch_kernel_launches.argtypes = [vp]
     lib.hmj_env_obs_reward.argtypes = [vp, dp, dp, dp, C.c_double, dp, dp, vp, vp, vp]
     lib.hmj_env_obs_reward_dev.argtypes = [vp, dp, dp, dp, C.c_double, dp, dp, vp, vp, vp]
+    lib.hmj_env_obs_reward_noalloc.argtypes = [vp, dp, dp, dp, C.c_double, dp, dp, vp, vp, vp]
+    lib.hmj_env_obs_reward_noalloc_max_envs.argtypes = []
     lib.hmj_env_step.argtypes = [vp, dp, vp, dp, dp, dp, dp, C.c_double, C.c_int, dp, dp, vp, vp, vp, dp, dp]
     lib.hmj_env_io.argtypes = [vp] + [C.POINTER(vp)] * 9
     lib.hmj_env_step_fused.argtypes = [vp, C.c_int, C.c_int, C.c_double, C.c_double, C.c_ulonglong, C.c_int]

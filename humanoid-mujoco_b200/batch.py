@@ -226,6 +226,17 @@ class HumanoidBatch:
             float(max_sim_time), _p(obs), _p(rew), _p(term), _p(trunc), _p(selfc)))
         return obs, rew, term.astype(bool), trunc.astype(bool), selfc.astype(bool)
 
+    def obs_reward_noalloc(self, prev_action, latest_action, noise=None, max_sim_time=np.inf):
+        """`obs_reward` through hmj_env_obs_reward_noalloc: device staging in the library's static array (batches of at
+        most `hmj_env_obs_reward_noalloc_max_envs()` envs), no allocation inside the C call."""
+        obs, rew = np.zeros((self.n, 30)), np.zeros(self.n)
+        term, trunc, selfc = (np.zeros(self.n, dtype=np.int32) for _ in range(3))
+        mst = 1e300 if not np.isfinite(max_sim_time) else float(max_sim_time)
+        check(self.lib.hmj_env_obs_reward_noalloc(
+            self._h, _p(self._f64(prev_action, (NU,))), _p(self._f64(latest_action, (NU,))), _p(self._f64(noise, (31,))),
+            mst, _p(obs), _p(rew), _p(term), _p(trunc), _p(selfc)))
+        return obs, rew, term.astype(bool), trunc.astype(bool), selfc.astype(bool)
+
     def env_step(self, ctrl, xfrc_body, xfrc, prev_action, latest_action, noise=None, max_sim_time=np.inf, nsteps=1, out=None):
         """CPUEnv.step for all envs in one C call (hmj_env_step).  `out` may hold preallocated (pinned) result arrays."""
         n = self.n

@@ -1908,3 +1908,78 @@ extern "C" int hmj_plan_exchange(hmj_batch_t* b, hmj_comm_t* c, int nnode, doubl
   NCK(g_nccl.allgather(b->record_dev, c->gathered, (size_t)stride, /*ncclFloat64*/ 8, c->comm, b->stream));
   return hmj_plan_select(b, c->gathered, c->nranks, nnode, record_host);
 }
+
+// ------------------------------------------------------------------ allocation-free variant of hmj_env_obs_reward
+// No counterpart in the reference; added for callers that must not reach
+// cudaMalloc (code under graph capture, tight serving loops, harnesses that forbid it).  hmj_env_obs_reward stages its host
+// inputs and results in a device block it allocates on first use; this variant keeps that block in a file-scope device
+// array of fixed size, so the call allocates nothing on the host or the device: async copies, one memset, one kernel.
+//   * limit: batches of at most HMJ_NOALLOC_MAX_ENVS envs (700 bytes of scratch per env, 2.8 MB in total; every GPU that
+//     loads the library holds the array until the process exits);
+//   * ONE array per device, shared by every batch and every call: calls that overlap on the GPU (two batches = two
+//     streams, or two host threads) race on it; the call synchronises its stream before it returns, so calls made one
+//     after the other from one thread are safe.  The array keeps the previous call's contents; the result part is
+//     cleared at the start of every call (rows of envs the kernel skips read as zero, never as the last call's).
+#define HMJ_NOALLOC_MAX_ENVS 4096
+#define HMJ_NOALLOC_DOUBLES_PER_ENV (12 + 12 + 31 + 30 + 1)
+#define HMJ_NOALLOC_BYTES ((size_t)HMJ_NOALLOC_MAX_ENVS * (HMJ_NOALLOC_DOUBLES_PER_ENV * 8 + 3 * 4))
+static __device__ __align__(256) unsigned char g_noalloc_scratch[HMJ_NOALLOC_BYTES];
+// In host code `g_noalloc_scratch` is only a handle for the runtime, not a device address: the address each device gave
+// the array is looked up once per device (with that device current) and cached here.
+static unsigned char* g_noalloc_addr[HMJ_MAX_DEVICES] = {nullptr};
+
+static int noalloc_scratch(int device, unsigned char** out) {
+  if (device < 0 || device >= HMJ_MAX_DEVICES) return fail(HMJ_ERR_ARG, "device index beyond the scratch table%s");
+  if (!g_noalloc_addr[device]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);   // the current device's copy of the array
+    if (e != cudaSuccess || !p) {
+      cudaGetLastError();
+      return fail(HMJ_ERR_CUDA, "cudaGetSymbolAddress(static scratch) failed: %s", e != cudaSuccess ? cudaGetErrorString(e) : "null address");
+    }
+    g_noalloc_addr[device] = (unsigned char*)p;
+  }
+  *out = g_noalloc_addr[device];
+  return HMJ_OK;
+}
+
+extern "C" int hmj_env_obs_reward_noalloc_max_envs(void) { return HMJ_NOALLOC_MAX_ENVS; }
+
+extern "C" int hmj_env_obs_reward_noalloc(hmj_batch_t* b, const double* prev_action, const double* latest_action,
+                                          const double* noise, double max_sim_time, double* obs, double* reward,
+                                          int32_t* terminated, int32_t* truncated, int32_t* self_collision) {
+  if (!b || !prev_action || !latest_action || !obs || !reward || !terminated || !truncated)
+    return fail(HMJ_ERR_ARG, "bad argument to env_obs_reward_noalloc%s");
+  if (b->n > HMJ_NOALLOC_MAX_ENVS) {
+    snprintf(g_err, sizeof(g_err), "env_obs_reward_noalloc: batch of %d envs exceeds the static scratch (at most %d envs); use hmj_env_obs_reward",
+             b->n, HMJ_NOALLOC_MAX_ENVS);
+    return HMJ_ERR_ARG;
+  }
+  CK(cudaSetDevice(b->device));
+  unsigned char* base = nullptr;
+  int rc = noalloc_scratch(b->device, &base);
+  if (rc) return rc;
+  const size_t N = b->n;
+  // layout as in hmj_env_obs_reward (doubles): prev 12N | latest 12N | noise 31N | obs 30N | reward N | int32: term N, trunc N, selfc N
+  double* d_prev = (double*)base;
+  double* d_lat = d_prev + 12 * N;
+  double* d_noise = d_lat + 12 * N;
+  double* d_obs = d_noise + 31 * N;
+  double* d_rew = d_obs + 30 * N;
+  int32_t* d_term = (int32_t*)(d_rew + N);
+  int32_t* d_trunc = d_term + N;
+  int32_t* d_self = d_trunc + N;
+  CK(cudaMemsetAsync(d_obs, 0, 31 * N * 8 + 3 * N * 4, b->stream));   // results start at zero, whatever the last call left
+  if ((rc = h2d(b, d_prev, prev_action, 12 * N * 8)) || (rc = h2d(b, d_lat, latest_action, 12 * N * 8)) ||
+      (rc = h2d(b, d_noise, noise, 31 * N * 8)))
+    return rc;
+  hmj_launch_env_obs_reward(b->tab_dev, b->buf, d_prev, d_lat, noise ? d_noise : nullptr, max_sim_time, d_obs, d_rew, d_term,
+                            d_trunc, d_self, b->stream);
+  b->launches += 1; b->host_launches += 1;
+  CK(cudaGetLastError());
+  if ((rc = d2h(b, obs, d_obs, 30 * N * 8)) || (rc = d2h(b, reward, d_rew, N * 8)) || (rc = d2h(b, terminated, d_term, N * 4)) ||
+      (rc = d2h(b, truncated, d_trunc, N * 4)) || (rc = d2h(b, self_collision, d_self, N * 4)))
+    return rc;
+  CK(cudaStreamSynchronize(b->stream));
+  return HMJ_OK;
+}

@@ -92,6 +92,16 @@ int hmj_env_obs_reward(hmj_batch_t* b, const double* prev_action, const double* 
                        double max_sim_time, double* obs, double* reward, int32_t* terminated,
                        int32_t* truncated, int32_t* self_collision);
 
+/* hmj_env_obs_reward without any allocation (no counterpart in the reference: added
+ * for callers that cannot call cudaMalloc — graph capture, serving loops, harnesses that forbid it).  Same
+ * arguments and results; the device staging block is a static array of the library instead of an allocation, so the
+ * batch may hold at most hmj_env_obs_reward_noalloc_max_envs() = 4096 envs (larger: HMJ_ERR_ARG, see hmj_last_error).
+ * The array is shared by all batches of a device: calls that overlap on the GPU race; the call returns synchronised. */
+int hmj_env_obs_reward_noalloc(hmj_batch_t* b, const double* prev_action, const double* latest_action,
+                               const double* noise, double max_sim_time, double* obs, double* reward,
+                               int32_t* terminated, int32_t* truncated, int32_t* self_collision);
+int hmj_env_obs_reward_noalloc_max_envs(void);
+
 /* same, all pointers DEVICE pointers, enqueue only on the batch stream */
 int hmj_env_obs_reward_dev(hmj_batch_t* b, const double* prev_action_dev, const double* latest_action_dev,
                            const double* noise_dev, double max_sim_time, double* obs_dev, double* reward_dev,
