@@ -7,6 +7,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <mutex>
 #include <string>
 #include <tuple>
 #include <vector>
@@ -156,6 +157,79 @@ extern "C" int hmj_default_params(const hmj_model_t* m, hmj_params_t* p) {
   return HMJ_OK;
 }
 
+// Support candidates per direction cell.  A direction d with major axis `ax` (largest |component|, lowest axis on ties) and
+// sign sgn lies on cube face 2 * ax + (sgn < 0) at (u, v) = (d[a], d[b]) / |d[ax]|, a = (ax + 1) % 3, b = (ax + 2) % 3;
+// cell (iu, iv) of the face covers u in [-1 + 2 iu / G, -1 + 2 (iu + 1) / G], likewise v, widened by HMJ_SUP_DELTA on every
+// side (the kernels find the cell in fp32).  Vertex w is dropped from a cell when ONE other vertex u beats it by more than
+// `margin` at the four corner directions of the widened cell: (p_u - p_w) . d is affine in (u, v), so u then beats w by more
+// than margin * |d[ax]| for every direction of the cell — ten million times the rounding error of the kernels' fp64 dot
+// products (coordinates < 1 m) — and w can be neither the exact nor the computed arg-max there.  Everything else stays.
+static void build_support_cells(const hmj_model_t* m, hmj_tables_t* t) {
+  const int G = HMJ_SUP_G;
+  const double margin = 1e-9;
+  t->sup_ok = 0;
+  static std::mutex mu;
+  static std::vector<unsigned char> cache_key;
+  static std::vector<uint16_t> cache_start, cache_vert;
+  std::lock_guard<std::mutex> lock(mu);
+  std::vector<unsigned char> key(sizeof(m->mesh_vert) + sizeof(m->mesh_vertadr) + sizeof(m->mesh_vertnum));
+  memcpy(key.data(), m->mesh_vert, sizeof(m->mesh_vert));
+  memcpy(key.data() + sizeof(m->mesh_vert), m->mesh_vertadr, sizeof(m->mesh_vertadr));
+  memcpy(key.data() + sizeof(m->mesh_vert) + sizeof(m->mesh_vertadr), m->mesh_vertnum, sizeof(m->mesh_vertnum));
+  if (key != cache_key) {   // built once per process and model (a few ms)
+    std::vector<uint16_t> start, vert;
+    std::vector<double> D;
+    std::vector<int> keep;
+    for (int k = 0; k < HMJ_NMESH; k++) {
+      const int nv = m->mesh_vertnum[k], va = m->mesh_vertadr[k];
+      D.assign((size_t)nv * 4, 0.0);
+      for (int face = 0; face < 6; face++) {
+        const int ax = face >> 1, a = (ax + 1) % 3, b = (ax + 2) % 3;
+        const double sgn = (face & 1) ? -1.0 : 1.0;
+        for (int iu = 0; iu < G; iu++)
+          for (int iv = 0; iv < G; iv++) {
+            start.push_back((uint16_t)vert.size());
+            const double ub[2] = {-1.0 + 2.0 * iu / G - HMJ_SUP_DELTA, -1.0 + 2.0 * (iu + 1) / G + HMJ_SUP_DELTA};
+            const double vb[2] = {-1.0 + 2.0 * iv / G - HMJ_SUP_DELTA, -1.0 + 2.0 * (iv + 1) / G + HMJ_SUP_DELTA};
+            int lead = 0;
+            double lead_sum = -1e300;
+            for (int i = 0; i < nv; i++) {
+              const double p[3] = {(double)m->mesh_vert[va + i][0], (double)m->mesh_vert[va + i][1], (double)m->mesh_vert[va + i][2]};
+              double sum = 0;
+              for (int c = 0; c < 4; c++) {
+                const double d = sgn * p[ax] + ub[c >> 1] * p[a] + vb[c & 1] * p[b];
+                D[(size_t)i * 4 + c] = d;
+                sum += d;
+              }
+              if (sum > lead_sum) { lead_sum = sum; lead = i; }
+            }
+            auto beats = [&](int u, int w) {
+              for (int c = 0; c < 4; c++)
+                if (!(D[(size_t)u * 4 + c] - D[(size_t)w * 4 + c] > margin)) return false;
+              return true;
+            };
+            keep.clear();
+            for (int w = 0; w < nv; w++) {
+              bool out = w != lead && beats(lead, w);   // the vertex best at the cell's centre removes almost everyone
+              for (int u = 0; u < nv && !out; u++)
+                if (u != w && beats(u, w)) out = true;
+              if (!out) keep.push_back(w);
+            }
+            for (int w : keep) vert.push_back((uint16_t)w);
+          }
+      }
+      start.push_back((uint16_t)vert.size());   // entry HMJ_SUP_CELLS of this mesh
+      start.push_back((uint16_t)vert.size());   // padding entry
+      if (vert.size() > HMJ_SUP_CAP) return;    // does not fit: sup_ok stays 0, the kernels scan whole hulls
+    }
+    cache_key = key; cache_start = start; cache_vert = vert;
+  }
+  memcpy(t->sup_start, cache_start.data(), sizeof(t->sup_start));
+  memset(t->sup_vert, 0, sizeof(t->sup_vert));
+  memcpy(t->sup_vert, cache_vert.data(), cache_vert.size() * sizeof(uint16_t));
+  t->sup_ok = getenv("HMJ_SUP_CELLS_OFF") ? 0 : 1;   // developer switch: whole-hull scans
+}
+
 static void build_tables(const hmj_model_t* m, hmj_tables_t* t) {
   memset(t, 0, sizeof(*t));
   t->m = *m;
@@ -278,6 +352,7 @@ static void build_tables(const hmj_model_t* m, hmj_tables_t* t) {
     adr += npad;
   }
   t->mesh_adr[HMJ_NMESH] = adr;
+  build_support_cells(m, t);
   int e = 0;
   for (int i = 0; i < HMJ_NV; i++)
     for (int j = 0; j <= i; j++) { t->tri_i[e] = i; t->tri_j[e] = j; e++; }

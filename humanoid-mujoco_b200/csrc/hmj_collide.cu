@@ -116,35 +116,102 @@ struct SFrame {
   __device__ __forceinline__ void setM(int k, double v) { b[(3 + k) * NARROW_THREADS] = v; }
 };
 
+// ---- support through the direction-cell candidate lists (hmj_tables_t::sup_start / sup_vert, built in hmj_api.cu)
+struct SupTab { const uint16_t* start; const uint16_t* vert; };   // start == nullptr: no tables, scan the hull
+__device__ __forceinline__ SupTab sup_tab(const hmj_tables_t* __restrict__ T, int mesh) {
+  SupTab t;
+  t.start = T->sup_ok ? T->sup_start[mesh] : nullptr;
+  t.vert = T->sup_vert;
+  return t;
+}
+
+// Cell of the direction (d0, d1, d2) (any length), -1 when the direction is degenerate (zero, huge, not finite: the
+// caller scans the whole hull).  The face comes from exact fp64 comparisons; the position on the face is found in fp32,
+// which the overlap of the cells (HMJ_SUP_DELTA = 1e-3, fp32 error < 1e-6) makes safe.
+__device__ __forceinline__ int sup_cell(double d0, double d1, double d2) {
+  const double a0 = fabs(d0), a1 = fabs(d1), a2 = fabs(d2);
+  int ax = 0;
+  double am = a0;
+  if (a1 > am) { ax = 1; am = a1; }
+  if (a2 > am) { ax = 2; am = a2; }
+  if (!(am > 1e-30 && am < 1e8)) return -1;   // |dot| stays far below HMJ_MAXVAL, the scans' start value
+  const double dm = ax == 0 ? d0 : (ax == 1 ? d1 : d2);
+  const double da = ax == 0 ? d1 : (ax == 1 ? d2 : d0);
+  const double db = ax == 0 ? d2 : (ax == 1 ? d0 : d1);
+  const float inv = 1.0f / (float)am;
+  const float u = (float)da * inv, v = (float)db * inv;
+  const int iu = min(max((int)((u + 1.0f) * (0.5f * HMJ_SUP_G)), 0), HMJ_SUP_G - 1);
+  const int iv = min(max((int)((v + 1.0f) * (0.5f * HMJ_SUP_G)), 0), HMJ_SUP_G - 1);
+  return ((ax << 1) | (dm < 0.0 ? 1 : 0)) * (HMJ_SUP_G * HMJ_SUP_G) + iu * HMJ_SUP_G + iv;
+}
+
+// arg-max of ld . v over the whole hull, first maximum (the definition the candidate lists are a shortcut for)
+__device__ __noinline__ int hull_argmax(const double* __restrict__ sx, const double* __restrict__ sy,
+                                        const double* __restrict__ sz, int base, int n4, double ld0, double ld1, double ld2) {
+  double best = -HMJ_MAXVAL;
+  int ib = 0;
+  for (int i = 0; i < n4; i++) {
+    const double va = ld0 * sx[base + i] + ld1 * sy[base + i] + ld2 * sz[base + i];
+    if (va > best) { best = va; ib = i; }
+  }
+  return ib;
+}
+
+// obj_support of a mesh geom: arg-max over the candidates of the direction's cell (ascending vertex order, strict >:
+// the first maximum, as the scan over the whole hull finds it — same expression per vertex, same bits).
 template <typename F>
 __device__ __forceinline__ void mesh_support(const double* __restrict__ sx, const double* __restrict__ sy,
-                                             const double* __restrict__ sz, Hull h, const F& f, const double* dir,
+                                             const double* __restrict__ sz, Hull h, SupTab tab, const F& f, const double* dir,
                                              double* out, int* idx = nullptr) {
   const double ld0 = f.M(0) * dir[0] + f.M(3) * dir[1] + f.M(6) * dir[2];
   const double ld1 = f.M(1) * dir[0] + f.M(4) * dir[1] + f.M(7) * dir[2];
   const double ld2 = f.M(2) * dir[0] + f.M(5) * dir[1] + f.M(8) * dir[2];
-  // two interleaved "first maximum" chains (even / odd vertices), merged with lowest-index tie-break:
-  // identical to the serial scan `if (vd > best) { best = vd; ibest = i; }`
-  double b0 = -HMJ_MAXVAL, b1 = -HMJ_MAXVAL;
-  int i0 = 0, i1 = 0x7fffffff;
-  const double2* px = reinterpret_cast<const double2*>(sx + h.base);
-  const double2* py = reinterpret_cast<const double2*>(sy + h.base);
-  const double2* pz = reinterpret_cast<const double2*>(sz + h.base);
-  const int n2 = h.n4 >> 1;
+  const int c = tab.start ? sup_cell(ld0, ld1, ld2) : -1;
+  int i0 = 0;
+  if (c >= 0) {
+    int k = tab.start[c];
+    const int k1 = tab.start[c + 1];
+    double best = -HMJ_MAXVAL;
 #pragma unroll 2
-  for (int j = 0; j < n2; j++) {
-    const double2 x = px[j], y = py[j], z = pz[j];
-    const double va = ld0 * x.x + ld1 * y.x + ld2 * z.x;
-    const double vb = ld0 * x.y + ld1 * y.y + ld2 * z.y;
-    if (va > b0) { b0 = va; i0 = 2 * j; }
-    if (vb > b1) { b1 = vb; i1 = 2 * j + 1; }
+    for (; k < k1; k++) {
+      const int i = tab.vert[k];
+      const double va = ld0 * sx[h.base + i] + ld1 * sy[h.base + i] + ld2 * sz[h.base + i];
+      if (va > best) { best = va; i0 = i; }
+    }
+  } else {
+    i0 = hull_argmax(sx, sy, sz, h.base, h.n4, ld0, ld1, ld2);
   }
-  if (b1 > b0 || (b1 == b0 && i1 < i0)) i0 = i1;
   if (idx) *idx = i0;
   const double p0 = sx[h.base + i0], p1 = sy[h.base + i0], p2 = sz[h.base + i0];
   out[0] = (f.M(0) * p0 + f.M(1) * p1 + f.M(2) * p2) + f.P(0);
   out[1] = (f.M(3) * p0 + f.M(4) * p1 + f.M(5) * p2) + f.P(1);
   out[2] = (f.M(6) * p0 + f.M(7) * p1 + f.M(8) * p2) + f.P(2);
+}
+
+// extreme values of row . v over the hull: min through the cell of -row, max through the cell of +row (the extreme
+// vertex is in the list and every value is computed by the same expression as in a scan of the whole hull)
+__device__ __forceinline__ void hull_extent(const double* __restrict__ sx, const double* __restrict__ sy,
+                                            const double* __restrict__ sz, Hull h, SupTab tab, double r0, double r1, double r2,
+                                            double* mn_out, double* mx_out) {
+  double mn = HMJ_MAXVAL, mx = -HMJ_MAXVAL;
+  const int cp = tab.start ? sup_cell(r0, r1, r2) : -1;
+  if (cp >= 0) {
+    const int cm = sup_cell(-r0, -r1, -r2);
+    for (int k = tab.start[cp]; k < tab.start[cp + 1]; k++) {
+      const int i = tab.vert[k];
+      mx = fmax(mx, r0 * sx[h.base + i] + r1 * sy[h.base + i] + r2 * sz[h.base + i]);
+    }
+    for (int k = tab.start[cm]; k < tab.start[cm + 1]; k++) {
+      const int i = tab.vert[k];
+      mn = fmin(mn, r0 * sx[h.base + i] + r1 * sy[h.base + i] + r2 * sz[h.base + i]);
+    }
+  } else {
+    for (int i = 0; i < h.n4; i++) {
+      const double d = r0 * sx[h.base + i] + r1 * sy[h.base + i] + r2 * sz[h.base + i];
+      mn = fmin(mn, d); mx = fmax(mx, d);
+    }
+  }
+  *mn_out = mn; *mx_out = mx;
 }
 
 // vertex i of hull h in the frame f: the tail of mesh_support, for recomputing a witness from its index (same bits)
@@ -157,116 +224,17 @@ __device__ __forceinline__ void mesh_point(const double* __restrict__ sx, const 
   out[2] = (f.M(6) * p0 + f.M(7) * p1 + f.M(8) * p2) + f.P(2);
 }
 
-// Cooperative variant for sparsely populated warps: all 32 lanes scan the hull for the directions of up to
-// four still-active lanes at once (lane l takes vertices l, l + 32, ...; four independent arg-max chains keep
-// the FP64 pipe and the shuffle unit busy; xor-butterfly with lowest-index tie-break == the serial "first
-// maximum").  Only the source lanes receive `out`.  Bit-identical to mesh_support.
-#define COOP_G 4
-template <typename F>
-__device__ __forceinline__ void mesh_support_coop(const double* __restrict__ sx, const double* __restrict__ sy,
-                                                  const double* __restrict__ sz, Hull h, const F& f, const double* dir,
-                                                  double* out, int* idx, const int* src, int lane) {
-  const unsigned FULL = 0xffffffffu;
-  const double my0 = f.M(0) * dir[0] + f.M(3) * dir[1] + f.M(6) * dir[2];
-  const double my1 = f.M(1) * dir[0] + f.M(4) * dir[1] + f.M(7) * dir[2];
-  const double my2 = f.M(2) * dir[0] + f.M(5) * dir[1] + f.M(8) * dir[2];
-  double ld0[COOP_G], ld1[COOP_G], ld2[COOP_G], best[COOP_G];
-  int ibest[COOP_G];
-#pragma unroll
-  for (int g = 0; g < COOP_G; g++) {
-    ld0[g] = __shfl_sync(FULL, my0, src[g]);
-    ld1[g] = __shfl_sync(FULL, my1, src[g]);
-    ld2[g] = __shfl_sync(FULL, my2, src[g]);
-    best[g] = -HMJ_MAXVAL;
-    ibest[g] = 0x7fffffff;
-  }
-  for (int i = lane; i < h.n4; i += 32) {
-    const double x = sx[h.base + i], y = sy[h.base + i], z = sz[h.base + i];
-#pragma unroll
-    for (int g = 0; g < COOP_G; g++) {
-      const double vd = ld0[g] * x + ld1[g] * y + ld2[g] * z;
-      if (vd > best[g]) { best[g] = vd; ibest[g] = i; }
-    }
-  }
-  // Transposing butterfly: the four arg-max problems are merged across the warp with 6 exchanges instead of 20.
-  // Round xor-16 leaves each half-warp with two of the groups, round xor-8 leaves each quarter with one, three plain
-  // rounds finish it; group g's result then sits in the lanes with (bit4, bit3) == (g >> 1, g & 1).  The merge (larger
-  // value, lowest index on ties) is associative and commutative: same bits as four full butterflies.
-  static_assert(COOP_G == 4, "the transposing merge is written for four groups");
-  auto merge = [](double& b, int& i, double ob, int oi) { if (ob > b || (ob == b && oi < i)) { b = ob; i = oi; } };
-  const bool hi16 = lane & 16, hi8 = lane & 8;
-  double k0 = hi16 ? best[2] : best[0], k1 = hi16 ? best[3] : best[1];
-  int j0 = hi16 ? ibest[2] : ibest[0], j1 = hi16 ? ibest[3] : ibest[1];
-  {
-    const double s0 = hi16 ? best[0] : best[2], s1 = hi16 ? best[1] : best[3];
-    const int t0 = hi16 ? ibest[0] : ibest[2], t1 = hi16 ? ibest[1] : ibest[3];
-    const double r0 = __shfl_xor_sync(FULL, s0, 16), r1 = __shfl_xor_sync(FULL, s1, 16);
-    const int u0 = __shfl_xor_sync(FULL, t0, 16), u1 = __shfl_xor_sync(FULL, t1, 16);
-    merge(k0, j0, r0, u0);
-    merge(k1, j1, r1, u1);
-  }
-  double kb = hi8 ? k1 : k0;
-  int jb = hi8 ? j1 : j0;
-  {
-    const double sb = hi8 ? k0 : k1;
-    const int tb = hi8 ? j0 : j1;
-    merge(kb, jb, __shfl_xor_sync(FULL, sb, 8), __shfl_xor_sync(FULL, tb, 8));
-  }
-#pragma unroll
-  for (int o = 4; o > 0; o >>= 1) merge(kb, jb, __shfl_xor_sync(FULL, kb, o), __shfl_xor_sync(FULL, jb, o));
-  int mine = -1;
-#pragma unroll
-  for (int g = 0; g < COOP_G; g++) {
-    const int ig = __shfl_sync(FULL, jb, (g >> 1) * 16 + (g & 1) * 8);
-    if (lane == src[g]) mine = ig;
-  }
-  if (mine >= 0) {
-    if (mine == 0x7fffffff) mine = 0;
-    *idx = mine;
-    const double p0 = sx[h.base + mine], p1 = sy[h.base + mine], p2 = sz[h.base + mine];
-    out[0] = (f.M(0) * p0 + f.M(1) * p1 + f.M(2) * p2) + f.P(0);
-    out[1] = (f.M(3) * p0 + f.M(4) * p1 + f.M(5) * p2) + f.P(1);
-    out[2] = (f.M(6) * p0 + f.M(7) * p1 + f.M(8) * p2) + f.P(2);
-  }
-}
-
-// the next (up to) COOP_G active lanes of `mm`, removed from it; short groups repeat their last lane
-__device__ __forceinline__ void coop_take(unsigned& mm, int* src) {
-#pragma unroll
-  for (int g = 0; g < COOP_G; g++) {
-    if (mm) { src[g] = __ffs(mm) - 1; mm &= mm - 1; }
-    else src[g] = src[g - (g > 0)];
-  }
-}
-
-// Lane count below which the cooperative scan is cheaper than the lane-serial one for hull(s) of n vertices.
-// Both are latency bound at the occupancy this kernel runs at: a serial trip costs ~25 n cycles for the whole
-// warp, a cooperative pass ~(n + 700) cycles per group of COOP_G lanes (measured, profiles/).
-__device__ __forceinline__ int coop_threshold(int n) { return (COOP_G * 25 * n) / (n + 700) + 1; }
-
 // Axis-aligned bounding box of a hull in the frame `f` == the six obj_support(+-e_r) calls of
 // mjc_ConvexHField (see the header comment for why min/max of three dot products is bit-identical).
 __device__ __forceinline__ void mesh_aabb(const double* __restrict__ sx, const double* __restrict__ sy,
-                                          const double* __restrict__ sz, Hull h, const Frame& f, double* lo, double* hi) {
-  const double* mat = f.mat;
-  double mn0 = HMJ_MAXVAL, mn1 = HMJ_MAXVAL, mn2 = HMJ_MAXVAL, mx0 = -HMJ_MAXVAL, mx1 = -HMJ_MAXVAL, mx2 = -HMJ_MAXVAL;
-  const double2* px = reinterpret_cast<const double2*>(sx + h.base);
-  const double2* py = reinterpret_cast<const double2*>(sy + h.base);
-  const double2* pz = reinterpret_cast<const double2*>(sz + h.base);
-  const int n2 = h.n4 >> 1;
-#pragma unroll 2
-  for (int j = 0; j < n2; j++) {
-    const double2 x = px[j], y = py[j], z = pz[j];
-    double d;
-    d = mat[0] * x.x + mat[1] * y.x + mat[2] * z.x; mn0 = fmin(mn0, d); mx0 = fmax(mx0, d);
-    d = mat[3] * x.x + mat[4] * y.x + mat[5] * z.x; mn1 = fmin(mn1, d); mx1 = fmax(mx1, d);
-    d = mat[6] * x.x + mat[7] * y.x + mat[8] * z.x; mn2 = fmin(mn2, d); mx2 = fmax(mx2, d);
-    d = mat[0] * x.y + mat[1] * y.y + mat[2] * z.y; mn0 = fmin(mn0, d); mx0 = fmax(mx0, d);
-    d = mat[3] * x.y + mat[4] * y.y + mat[5] * z.y; mn1 = fmin(mn1, d); mx1 = fmax(mx1, d);
-    d = mat[6] * x.y + mat[7] * y.y + mat[8] * z.y; mn2 = fmin(mn2, d); mx2 = fmax(mx2, d);
+                                          const double* __restrict__ sz, Hull h, SupTab tab, const Frame& f, double* lo, double* hi) {
+#pragma unroll
+  for (int r = 0; r < 3; r++) {
+    double mn, mx;
+    hull_extent(sx, sy, sz, h, tab, f.mat[3 * r], f.mat[3 * r + 1], f.mat[3 * r + 2], &mn, &mx);
+    lo[r] = mn + f.pos[r];
+    hi[r] = mx + f.pos[r];
   }
-  lo[0] = mn0 + f.pos[0]; lo[1] = mn1 + f.pos[1]; lo[2] = mn2 + f.pos[2];
-  hi[0] = mx0 + f.pos[0]; hi[1] = mx1 + f.pos[1]; hi[2] = mx2 + f.pos[2];
 }
 
 // Height-field prism: three top vertices (strip order) over a flat bottom at z = zb with the same (x, y).
@@ -773,6 +741,7 @@ k_broad(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int npad, int kpos0
   const int nrow = M.hfield_nrow, ncol = M.hfield_ncol;
   const float* data = B.params[env].hfield_data;
   const Hull h2 = {0, T->mesh_npad[M.geom_meshid[g2]]};
+  const SupTab tab2 = sup_tab(T, M.geom_meshid[g2]);
   Frame f2;
   hfield_rel_frame(f2, gx, gm, g2);
   bool active = in;
@@ -785,7 +754,7 @@ k_broad(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int npad, int kpos0
   }
   if (!__any_sync(0xffffffffu, active)) return;
   double lo[3], hi[3];
-  mesh_aabb(sx, sy, sz, h2, f2, lo, hi);
+  mesh_aabb(sx, sy, sz, h2, tab2, f2, lo, hi);
   if ((lo[0] > size1[0]) || (hi[0] < -size1[0]) || (lo[1] > size1[1]) || (hi[1] < -size1[1]) || (lo[2] > size1[2]) ||
       (hi[2] < -size1[3]))
     active = false;
@@ -825,7 +794,7 @@ k_broad(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int npad, int kpos0
     prism_support(p, dir, v1);
     cp3(nd, dir);
     c_scale(nd, -1.0);
-    mesh_support(sx, sy, sz, h2, f2, nd, v2);
+    mesh_support(sx, sy, sz, h2, tab2, f2, nd, v2);
     c_sub2(v, v1, v2);
     const double dot = c_dot(v, dir);
     bool survive = has && !(c_is_zero(dot) || dot < 0);
@@ -888,27 +857,10 @@ k_broad_hf_coop(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int nhf) {
     if (-size1[3] > f2.pos[2] + r2 + 0.0) active = false;
     if (!active) return;   // warp-uniform
   }
-  // ---- bounding box of the hull in the height field's frame (mesh_aabb, vertices strided over the lanes)
+  // ---- bounding box of the hull in the height field's frame (every lane the same few candidates: broadcast loads)
+  const SupTab tab2 = sup_tab(T, M.geom_meshid[g2]);
   double lo[3], hi[3];
-  {
-    const double* mat = f2.mat;
-    double mn0 = HMJ_MAXVAL, mn1 = HMJ_MAXVAL, mn2 = HMJ_MAXVAL, mx0 = -HMJ_MAXVAL, mx1 = -HMJ_MAXVAL, mx2 = -HMJ_MAXVAL;
-    for (int i = lane; i < h2.n4; i += 32) {
-      const double x = sx[h2.base + i], y = sy[h2.base + i], z = sz[h2.base + i];
-      double d;
-      d = mat[0] * x + mat[1] * y + mat[2] * z; mn0 = fmin(mn0, d); mx0 = fmax(mx0, d);
-      d = mat[3] * x + mat[4] * y + mat[5] * z; mn1 = fmin(mn1, d); mx1 = fmax(mx1, d);
-      d = mat[6] * x + mat[7] * y + mat[8] * z; mn2 = fmin(mn2, d); mx2 = fmax(mx2, d);
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      mn0 = fmin(mn0, __shfl_xor_sync(FULL, mn0, o)); mx0 = fmax(mx0, __shfl_xor_sync(FULL, mx0, o));
-      mn1 = fmin(mn1, __shfl_xor_sync(FULL, mn1, o)); mx1 = fmax(mx1, __shfl_xor_sync(FULL, mx1, o));
-      mn2 = fmin(mn2, __shfl_xor_sync(FULL, mn2, o)); mx2 = fmax(mx2, __shfl_xor_sync(FULL, mx2, o));
-    }
-    lo[0] = mn0 + f2.pos[0]; lo[1] = mn1 + f2.pos[1]; lo[2] = mn2 + f2.pos[2];
-    hi[0] = mx0 + f2.pos[0]; hi[1] = mx1 + f2.pos[1]; hi[2] = mx2 + f2.pos[2];
-  }
+  mesh_aabb(sx, sy, sz, h2, tab2, f2, lo, hi);
   if ((lo[0] > size1[0]) || (hi[0] < -size1[0]) || (lo[1] > size1[1]) || (hi[1] < -size1[1]) || (lo[2] > size1[2]) ||
       (hi[2] < -size1[3]))
     return;
@@ -950,11 +902,7 @@ k_broad_hf_coop(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int nhf) {
     prism_support(p, dir, v1);
     cp3(nd, dir);
     c_scale(nd, -1.0);
-    for (unsigned mm = tm; mm;) {
-      int src[COOP_G], idx = 0;
-      coop_take(mm, src);
-      mesh_support_coop(sx, sy, sz, h2, f2, nd, v2, &idx, src, lane);
-    }
+    if (test) mesh_support(sx, sy, sz, h2, tab2, f2, nd, v2);
     c_sub2(v, v1, v2);
     const double dot = c_dot(v, dir);
     bool survive = test && !(c_is_zero(dot) || dot < 0);
@@ -1023,7 +971,7 @@ __device__ __forceinline__ void narrow_mesh_mesh(const hmj_tables_t* __restrict_
   }
   const WitMesh wit = {sx, sy, sz, &f1, &f2, h1, h2};
   bool found = false, fin = false;
-  const int thr = coop_threshold(h1.n4 + h2.n4);
+  const SupTab tab1 = sup_tab(T, M.geom_meshid[g1]), tab2 = sup_tab(T, M.geom_meshid[g2]);
   while (true) {
     const unsigned am = __ballot_sync(0xffffffffu, active);
     if (!am) break;
@@ -1032,19 +980,10 @@ __device__ __forceinline__ void narrow_mesh_mesh(const hmj_tables_t* __restrict_
     double nd[3] = {m.dir[0], m.dir[1], m.dir[2]};
     c_scale(nd, -1.0);
     double v1[3], v2[3];
-    if (__popc(am) >= thr) {
-      mesh_support(sx, sy, sz, h1, f1, m.dir, v1, &s.i1);
-      mesh_support(sx, sy, sz, h2, f2, nd, v2, &s.i2);
-    } else {
-      for (unsigned mm = am; mm;) {
-        int src[COOP_G];
-        coop_take(mm, src);
-        mesh_support_coop(sx, sy, sz, h1, f1, m.dir, v1, &s.i1, src, lane);
-        mesh_support_coop(sx, sy, sz, h2, f2, nd, v2, &s.i2, src, lane);
-      }
-    }
-    c_sub2(s.v, v1, v2);
     if (active) {
+      mesh_support(sx, sy, sz, h1, tab1, f1, m.dir, v1, &s.i1);
+      mesh_support(sx, sy, sz, h2, tab2, f2, nd, v2, &s.i2);
+      c_sub2(s.v, v1, v2);
       const int res = m.step(s, tol, maxit, wit);
       if (res != 1) {
         active = false;
@@ -1101,7 +1040,7 @@ __device__ __forceinline__ void narrow_hfield(const hmj_tables_t* __restrict__ T
   }
   const WitPrism wit = {sx, sy, sz, &p, &f2, h2};
   bool found = false, fin = false;
-  const int thr = coop_threshold(h2.n4);
+  const SupTab tab2 = sup_tab(T, M.geom_meshid[g2]);
   while (true) {
     const unsigned am = __ballot_sync(0xffffffffu, active);
     if (!am) break;
@@ -1111,17 +1050,9 @@ __device__ __forceinline__ void narrow_hfield(const hmj_tables_t* __restrict__ T
     double v1[3], v2[3];
     s.i1 = prism_support(p, m.dir, v1);
     c_scale(nd, -1.0);
-    if (__popc(am) >= thr) {
-      mesh_support(sx, sy, sz, h2, f2, nd, v2, &s.i2);
-    } else {
-      for (unsigned mm = am; mm;) {
-        int src[COOP_G];
-        coop_take(mm, src);
-        mesh_support_coop(sx, sy, sz, h2, f2, nd, v2, &s.i2, src, lane);
-      }
-    }
-    c_sub2(s.v, v1, v2);
     if (active) {
+      mesh_support(sx, sy, sz, h2, tab2, f2, nd, v2, &s.i2);
+      c_sub2(s.v, v1, v2);
       const int res = m.step(s, tol, maxit, wit);
       if (res != 1) {
         active = false;

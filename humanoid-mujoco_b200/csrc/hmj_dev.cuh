@@ -33,6 +33,10 @@ static inline int hmj_current_device() {
 #define HMJ_PI 3.14159265358979323846
 
 // Host-derived lookup tables (built once in hmj_batch_create, read through L1/L2).
+#define HMJ_SUP_G 8                                  /* cells per cube-face edge */
+#define HMJ_SUP_CELLS (6 * HMJ_SUP_G * HMJ_SUP_G)
+#define HMJ_SUP_CAP 16384                            /* candidate entries over all meshes (this model: ~7100) */
+#define HMJ_SUP_DELTA 1e-3                           /* cells overlap by this much in cube-map coordinates: covers the fp32 cell look-up */
 struct hmj_tables_t {
   hmj_model_t m;
   // kinematic levels (bodies of equal depth are independent)
@@ -67,6 +71,13 @@ struct hmj_tables_t {
   alignas(16) double dvz[HMJ_MAXVERT + HMJ_NMESH * HMJ_MESH_PAD];
   double mesh_lo[HMJ_NMESH + 1][3];  // local bounding box of each hull (exact min / max of its vertices)
   double mesh_hi[HMJ_NMESH + 1][3];
+  // support candidates by direction cell (hmj_api.cu: build_support_cells): the directions of space are cut into
+  // 6 x G x G cells (cube map); sup_vert[sup_start[mesh][c] .. sup_start[mesh][c + 1]) lists, in ascending order, every
+  // vertex of the hull that can be the support point for SOME direction of cell c (a strict superset, built with a margin
+  // far above rounding), so the arg-max over the list is the arg-max over the hull, bit for bit.
+  int32_t sup_ok;                                        // 0: tables not built (capacity): kernels scan the whole hull
+  uint16_t sup_start[HMJ_NMESH][HMJ_SUP_CELLS + 2];      // offsets into sup_vert
+  uint16_t sup_vert[HMJ_SUP_CAP];                        // vertex indices within the mesh
   // lower-triangle index maps for the 18x18 dense routines
   int32_t tri_i[HMJ_NV * (HMJ_NV + 1) / 2];
   int32_t tri_j[HMJ_NV * (HMJ_NV + 1) / 2];
