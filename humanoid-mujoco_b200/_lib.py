@@ -54,6 +54,7 @@ def load_library() -> C.CDLL:
     lib.hmj_batch_stream.argtypes = [vp]
     lib.hmj_batch_stream.restype = vp
     lib.hmj_batch_kernel_launches.argtypes = [vp]
+    lib.hmj_support_cells.argtypes = [vp, vp, C.c_int, vp, C.c_int, vp, vp]
     lib.hmj_env_obs_reward.argtypes = [vp, dp, dp, dp, C.c_double, dp, dp, vp, vp, vp]
     lib.hmj_env_obs_reward_dev.argtypes = [vp, dp, dp, dp, C.c_double, dp, dp, vp, vp, vp]
     lib.hmj_env_obs_reward_noalloc.argtypes = [vp, dp, dp, dp, C.c_double, dp, dp, vp, vp, vp]

@@ -230,6 +230,24 @@ static void build_support_cells(const hmj_model_t* m, hmj_tables_t* t) {
   t->sup_ok = getenv("HMJ_SUP_CELLS_OFF") ? 0 : 1;   // developer switch: whole-hull scans
 }
 
+// The candidate tables of a model, for inspection (tests/test_host_logic.py checks them against whole-hull arg-max on the
+// CPU; no GPU needed).  start: [HMJ_NMESH][cells + 2] offsets into vert; returns the cells-per-face-edge count G in *grid.
+extern "C" int hmj_support_cells(const hmj_model_t* model, uint16_t* start, int start_cap, uint16_t* vert, int vert_cap, int* grid,
+                                 int* entries) {
+  if (!model || !start || !vert || start_cap < HMJ_NMESH * (HMJ_SUP_CELLS + 2) || vert_cap < HMJ_SUP_CAP)
+    return fail(HMJ_ERR_ARG, "bad argument to support_cells%s");
+  hmj_tables_t* t = new hmj_tables_t;
+  memset(t, 0, sizeof(*t));
+  build_support_cells(model, t);
+  const int ok = t->sup_ok || getenv("HMJ_SUP_CELLS_OFF");
+  memcpy(start, t->sup_start, sizeof(t->sup_start));
+  memcpy(vert, t->sup_vert, sizeof(t->sup_vert));
+  if (grid) *grid = HMJ_SUP_G;
+  if (entries) *entries = t->sup_start[HMJ_NMESH - 1][HMJ_SUP_CELLS];
+  delete t;
+  return ok ? HMJ_OK : fail(HMJ_ERR_ARG, "candidate tables exceed their capacity%s");
+}
+
 static void build_tables(const hmj_model_t* m, hmj_tables_t* t) {
   memset(t, 0, sizeof(*t));
   t->m = *m;

@@ -83,6 +83,14 @@ void* hmj_batch_device_ptr(hmj_batch_t* b, const char* name);
 void* hmj_batch_stream(hmj_batch_t* b);
 int hmj_batch_kernel_launches(const hmj_batch_t* b); /* kernels launched since create */
 
+/* Support-function candidate tables of the model's convex hulls (the engine's counterpart of MuJoCo's mesh_graph
+ * hill-climb, simulation/mujoco/include/mujoco/mjmodel.h:867,876): directions are binned into 6 x G x G cube-map cells and
+ * every cell lists the hull vertices that can be the support point for a direction in it, so a support call scans a
+ * handful of vertices instead of the hull and still returns the exhaustive scan's vertex.  Host-only (no GPU needed);
+ * start is [7][6*G*G + 2] offsets into vert, capacities are checked. */
+int hmj_support_cells(const hmj_model_t* model, uint16_t* start, int start_cap, uint16_t* vert, int vert_cap, int* grid,
+                      int* entries);
+
 /* ---- CPUEnv.step epilogue on device (cpu_env.py:465-616 + reward_functions.py:247-374):
  * obs [N][30], reward [N], terminated/truncated/self_collision [N] (int32).  Reads the one-step-stale
  * xquat/xpos/qfrc/contacts exactly like the reference.

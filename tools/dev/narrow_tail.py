@@ -1,26 +1,33 @@
-"""Developer tool: per-group item statistics of k_narrow over a few 4096-env steps (prof build, see phase_tail.py)."""
+"""Developer tool: per-group item statistics of k_narrow over a few 4096-env steps at the steady state of a bench regime
+(prof build: tools/dev/build_variant.sh prof -DHMJ_PHASE_PROF, run with HMJ_B200_LIB=.../lib_prof/libhmj_b200.so HMJ_PIPES=1).
+usage: narrow_tail.py [control scale] [lead-in steps]"""
 import ctypes as C, os, sys
 import numpy as np
 sys.path[:0] = [os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))]
 import bench
 import humanoid_mujoco_b200 as hmj
 
+scale = float(sys.argv[1]) if len(sys.argv) > 1 else 1.0
+lead = int(sys.argv[2]) if len(sys.argv) > 2 else 150
 n = 4096
 b = hmj.HumanoidBatch(n)
-params, qpos = bench.make_workload(b.default_params(), b.model["qpos0"][0], n, 1)
-b.set_params(params)
-b.set_state(qpos, np.zeros((n, 18)), np.zeros(n), np.zeros((n, 18)))
-b.step(np.zeros((n, 12)), 300)
+z18 = np.zeros((n, 18))
+def probe(params, qpos):
+    b.set_params(params); b.set_state(qpos, z18, np.zeros(n), z18); b.step(np.zeros((n, 12)), 1); return b.get("ncon") > 0
+params, qpos, attempts = bench.make_workload(b.default_params(), b.model["qpos0"][0], n, 1, probe)
+b.set("status", np.zeros(n, dtype=np.int32))
+b.set_state(qpos, z18, np.zeros(n), z18)
+b.step(np.zeros((n, 12)), bench.SETTLE_STEPS)
 rng = np.random.default_rng(2)
-for _ in range(20):
-    b.step(rng.uniform(-1, 1, (n, 12)), 1)
+for _ in range(lead):
+    b.step(scale * rng.uniform(-1, 1, (n, 12)), 1)
 out = np.zeros((64, 5), dtype=np.uint64)
 warp = np.zeros(12, dtype=np.uint64)
 b.lib.hmj_debug_narrow_prof.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
 b.lib.hmj_debug_narrow_prof(out.ctypes.data, warp.ctypes.data, 1)
 K = 10
 for _ in range(K):
-    b.step(rng.uniform(-1, 1, (n, 12)), 1)
+    b.step(scale * rng.uniform(-1, 1, (n, 12)), 1)
 b.lib.hmj_debug_narrow_prof(out.ctypes.data, warp.ctypes.data, 0)
 print(f"per launch: busy warps {warp[2] / K:.0f}, max warp busy {warp[0]} cycles (max over {K} launches), mean {warp[1] / max(warp[2], 1):.0f}, staging max {warp[3]}")
 print("launches by item size 4/8/16/32:", warp[6:10].tolist(), " items/launch", warp[10] / K, " queries/launch", warp[11] / K)
