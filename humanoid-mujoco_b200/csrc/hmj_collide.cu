@@ -443,6 +443,12 @@ struct Mpr {
   double dir[3];
   int st, guard, iterations;
   double depth, pdir[3], pos[3];
+#ifdef HMJ_PHASE_PROF
+  double sepgap;   // developer build: -dot(s.v, dir) at a no-contact exit that proves separation along dir (else 0)
+#define MPR_SEP(d) (sepgap = -(d))
+#else
+#define MPR_SEP(d) ((void)0)
+#endif
 
   // discoverPortal, up to the first support call
   __device__ __forceinline__ void begin(const double* center1, const double* center2) {
@@ -475,7 +481,7 @@ struct Mpr {
       case ST_D1: {
         cps(p1, s);
         dot = c_dot(p1.v, dir);
-        if (c_is_zero(dot) || dot < 0) return -1;
+        if (c_is_zero(dot) || dot < 0) { MPR_SEP(dot); return -1; }
         c_cross(dir, p0v, p1.v);
         if (c_is_zero(c_dot(dir, dir))) {
           double w1[3], w2[3];
@@ -499,7 +505,7 @@ struct Mpr {
       case ST_D2: {
         cps(p2, s);
         dot = c_dot(p2.v, dir);
-        if (c_is_zero(dot) || dot < 0) return -1;
+        if (c_is_zero(dot) || dot < 0) { MPR_SEP(dot); return -1; }
         c_sub2(va, p1.v, p0v);
         c_sub2(vb, p2.v, p0v);
         c_cross(dir, va, vb);
@@ -517,7 +523,7 @@ struct Mpr {
       case ST_D3: {
         cps(p3, s);
         dot = c_dot(p3.v, dir);
-        if (c_is_zero(dot) || dot < 0) return -1;
+        if (c_is_zero(dot) || dot < 0) { MPR_SEP(dot); return -1; }
         bool cont = false;
         c_cross(va, p1.v, p3.v);
         dot = c_dot(va, p0v);
@@ -544,7 +550,7 @@ struct Mpr {
         const bool ref = st == ST_REFINE;
         if (ref) {
           dot = c_dot(s.v, dir);
-          if (!(c_is_zero(dot) || dot > 0)) return -1;
+          if (!(c_is_zero(dot) || dot > 0)) { MPR_SEP(dot); return -1; }
         }
         const bool reach = portal_reach_tolerance(p1, p2, p3, s, dir, tol);
         if (ref) {
@@ -923,6 +929,7 @@ k_broad_hf_coop(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int nhf) {
 // per-warp busy time {max cycles, sum cycles, warps, staging cycles}
 __device__ unsigned long long hmj_narrow_prof[64][5];
 __device__ unsigned long long hmj_narrow_warp[12];   // [4 + shift]: launches that ran with item size 1 << shift; [10]: sum of total items, [11]: sum of queries
+__device__ unsigned long long hmj_narrow_q[12];   // queries: [0..2] contact {n, trips, max trips}, [3..5] no contact, [6..9] no-contact exits with a separation gap > 1e-9 / 1e-6 / 1e-4 / 1e-3
 __device__ int hmj_narrow_trips;   // scratch written by the narrow_* routines (lane 0 of the running warp reads its own)
 extern "C" int hmj_debug_narrow_prof(unsigned long long* out, unsigned long long* warp, int reset) {
   cudaDeviceSynchronize();
@@ -935,9 +942,22 @@ extern "C" int hmj_debug_narrow_prof(unsigned long long* out, unsigned long long
   }
   return 0;
 }
+extern "C" int hmj_debug_narrow_q(unsigned long long* out, int reset) {
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out, hmj_narrow_q, sizeof(unsigned long long) * 12);
+  if (reset) { void* p = nullptr; cudaGetSymbolAddress(&p, hmj_narrow_q); cudaMemset(p, 0, sizeof(unsigned long long) * 12); }
+  return 0;
+}
+#define NP_QUERY(valid, mt, found, gap) do { if (valid) { const int o_ = (found) ? 0 : 3; atomicAdd(&hmj_narrow_q[o_], 1ull); \
+  atomicAdd(&hmj_narrow_q[o_ + 1], (unsigned long long)(mt)); atomicMax(&hmj_narrow_q[o_ + 2], (unsigned long long)(mt)); \
+  if (!(found)) { if ((gap) > 1e-9) atomicAdd(&hmj_narrow_q[6], 1ull); if ((gap) > 1e-6) atomicAdd(&hmj_narrow_q[7], 1ull); \
+  if ((gap) > 1e-4) atomicAdd(&hmj_narrow_q[8], 1ull); if ((gap) > 1e-3) atomicAdd(&hmj_narrow_q[9], 1ull); } } } while (0)
 #define NP_TRIP() do { trips_++; } while (0)
+#define NP_MINE() do { if (active) my_trips_++; } while (0)
 #else
 #define NP_TRIP() do { } while (0)
+#define NP_MINE() do { } while (0)
+#define NP_QUERY(valid, mt, found, gap) do { } while (0)
 #endif
 // ------------------------------------------------------------------ narrowphase
 __device__ __forceinline__ void write_slot(const hmj_buffers_t& B, int env, int s, double dist, const double* nrm, const double* pos) {
@@ -972,10 +992,13 @@ __device__ __forceinline__ void narrow_mesh_mesh(const hmj_tables_t* __restrict_
   const WitMesh wit = {sx, sy, sz, &f1, &f2, h1, h2};
   bool found = false, fin = false;
   const SupTab tab1 = sup_tab(T, M.geom_meshid[g1]), tab2 = sup_tab(T, M.geom_meshid[g2]);
+#ifdef HMJ_PHASE_PROF
+  const bool valid_ = active; int my_trips_ = 0; m.sepgap = 0;
+#endif
   while (true) {
     const unsigned am = __ballot_sync(0xffffffffu, active);
     if (!am) break;
-    NP_TRIP();
+    NP_TRIP(); NP_MINE();
     Supp s;
     double nd[3] = {m.dir[0], m.dir[1], m.dir[2]};
     c_scale(nd, -1.0);
@@ -993,6 +1016,7 @@ __device__ __forceinline__ void narrow_mesh_mesh(const hmj_tables_t* __restrict_
     }
   }
   if (fin) { m.finalize(wit); found = true; }
+  NP_QUERY(valid_, my_trips_, found, m.sepgap);
   if (found && !c_vec_is_origin(m.pdir)) write_slot(B, env, T->pair_slot[k], 0.0 - m.depth, m.pdir, m.pos);
 }
 
@@ -1041,10 +1065,13 @@ __device__ __forceinline__ void narrow_hfield(const hmj_tables_t* __restrict__ T
   const WitPrism wit = {sx, sy, sz, &p, &f2, h2};
   bool found = false, fin = false;
   const SupTab tab2 = sup_tab(T, M.geom_meshid[g2]);
+#ifdef HMJ_PHASE_PROF
+  const bool valid_ = active; int my_trips_ = 0; m.sepgap = 0;
+#endif
   while (true) {
     const unsigned am = __ballot_sync(0xffffffffu, active);
     if (!am) break;
-    NP_TRIP();
+    NP_TRIP(); NP_MINE();
     Supp s;
     double nd[3] = {m.dir[0], m.dir[1], m.dir[2]};
     double v1[3], v2[3];
@@ -1062,6 +1089,7 @@ __device__ __forceinline__ void narrow_hfield(const hmj_tables_t* __restrict__ T
     }
   }
   if (fin) { m.finalize(wit); found = true; }
+  NP_QUERY(valid_, my_trips_, found, m.sepgap);
   if (found && !d_is_bad(m.depth)) {
     const double* pos1 = gx;
     const double* mat1 = gm;

@@ -35,3 +35,11 @@ print("group  items/launch  mean cycles  max cycles  mean trips  max trips")
 for g in range(64):
     if out[g, 0]:
         print(f"{g:5d} {out[g, 0] / K:12.1f} {out[g, 1] / out[g, 0]:12.0f} {out[g, 2]:11d} {out[g, 3] / out[g, 0]:11.1f} {out[g, 4]:10d}")
+q = np.zeros(12, dtype=np.uint64)
+if hasattr(b.lib, "hmj_debug_narrow_q"):
+    b.lib.hmj_debug_narrow_q.argtypes = [C.c_void_p, C.c_int]
+    b.lib.hmj_debug_narrow_q(q.ctypes.data, 0)
+    q = q.astype(np.float64)
+    # counters run since process start: report fractions
+    print(f"queries with contact: {q[0]:.0f} (mean trips {q[1]/max(q[0],1):.1f}, max {q[2]:.0f}); without: {q[3]:.0f} (mean trips {q[4]/max(q[3],1):.1f}, max {q[5]:.0f})")
+    print("no-contact exits proving a separation gap > 1e-9 / 1e-6 / 1e-4 / 1e-3:", (q[6:10] / max(q[3], 1)).round(3).tolist())
