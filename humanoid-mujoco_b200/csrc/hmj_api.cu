@@ -373,6 +373,12 @@ static void build_tables(const hmj_model_t* m, hmj_tables_t* t) {
   }
   t->mesh_adr[HMJ_NMESH] = adr;
   build_support_cells(m, t);
+  {   // the structure the tree Cholesky is written for: root dofs 0-5 in a line, four serial 3-dof chains off dof 5
+    static const int expect[HMJ_NV] = {-1, 0, 1, 2, 3, 4, 5, 6, 7, 5, 9, 10, 5, 12, 13, 5, 15, 16};
+    bool ok = true;
+    for (int d = 0; d < HMJ_NV; d++) ok = ok && m->dof_parentid[d] == expect[d];
+    t->tree_chol = (ok && !getenv("HMJ_TREE_CHOL_OFF")) ? 1 : 0;   // developer switch: dense factorisations everywhere
+  }
   int e = 0;
   for (int i = 0; i < HMJ_NV; i++)
     for (int j = 0; j <= i; j++) { t->tri_i[e] = i; t->tri_j[e] = j; e++; }

@@ -75,6 +75,7 @@ struct hmj_tables_t {
   // 6 x G x G cells (cube map); sup_vert[sup_start[mesh][c] .. sup_start[mesh][c + 1]) lists, in ascending order, every
   // vertex of the hull that can be the support point for SOME direction of cell c (a strict superset, built with a margin
   // far above rounding), so the arg-max over the list is the arg-max over the hull, bit for bit.
+  int32_t tree_chol;                                     // 1: dofs are a free root + four 3-hinge chains (hmj_solve.cu: tree_factor_solve)
   int32_t sup_ok;                                        // 0: tables not built (capacity): kernels scan the whole hull
   uint16_t sup_start[HMJ_NMESH][HMJ_SUP_CELLS + 2];      // offsets into sup_vert
   uint16_t sup_vert[HMJ_SUP_CAP];                        // vertex indices within the mesh

@@ -132,6 +132,170 @@ __device__ __forceinline__ double chol_factor_solve(double* H, CholScratch* C, d
   return lane < NV ? res : 0.0;
 }
 
+// ---------------------------------------------------------------- Cholesky along the kinematic tree
+// The robot is a free root (dofs 0-5) carrying four serial chains of three hinges (dofs 6-8, 9-11, 12-14, 15-17;
+// checked against dof_parentid when the tables are built: hmj_tables_t::tree_chol).  M couples a chain only with itself
+// and the root: the 18 x 18 matrix is  [ R  B' ; B  C ]  with C block-diagonal.  Eliminating leaf-first (MuJoCo's own
+// order for M, mj_factorM) creates no fill, and the four chains are independent of one another, so the 18 dependent
+// pivots of the dense routine become 3 steps (one dof of every chain at a time) + 6 root pivots.  Used for the two
+// factorisations of k_factor (M and M + h diag(damping)) and mj_Euler's solve; the Newton Hessian keeps the dense routine
+// (a contact between two chains fills C, and carrying both routines in k_solve cost more than the tree one saved).
+// Lane i holds row i of the lower triangle: r[j] = H(i, j) for the root columns j (root lanes: j <= i), c[t] = H(i, first
+// dof of its chain + t) for t <= its position.  Pivot k scales its own row (u = row / sqrt(d)), publishes it through a
+// shared staging row, and every ancestor lane i subtracts u_i u_j from its entries: H = sum_k u_k u_k' = L' L with row k
+// of L = u_k.  L' y = b rides along (b_j -= u_j y_k), L x = y walks root first, then down the chains.
+struct TreeRow { double r[6]; double c[3]; double inv; };
+#define TREE_STAGE 40   /* doubles per staging buffer: 4 chains x (6 root + 3 chain entries + y) */
+
+__device__ __forceinline__ void tree_load(TreeRow& R, const double* __restrict__ H, int lane, double diag_add) {
+  const int i = lane < NV ? lane : 0;   // idle lanes shadow row 0 and never publish
+  const bool chain = lane >= 6 && lane < NV;
+  const int pos = chain ? (lane - 6) % 3 : 0, first = i - pos;
+#pragma unroll
+  for (int j = 0; j < 6; j++) {
+    R.r[j] = (chain || j <= i) ? H[i * LD + j] : 0.0;
+    if (!chain && j == i) R.r[j] += diag_add;
+  }
+#pragma unroll
+  for (int t = 0; t < 3; t++) {
+    R.c[t] = (chain && t <= pos) ? H[i * LD + first + t] : 0.0;
+    if (chain && t == pos) R.c[t] += diag_add;
+  }
+  R.inv = 0.0;
+}
+
+// factor (R becomes row `lane` of L and 1 / L(lane, lane)) and solve: returns x = H^-1 b for lanes < NV
+__device__ __forceinline__ double tree_factor_solve(TreeRow& R, double* stage, double b, int lane) {
+  const unsigned FULL = 0xffffffffu;
+  const bool chain = lane >= 6 && lane < NV;
+  const int ci = chain ? (lane - 6) / 3 : 0, pos = chain ? (lane - 6) - 3 * ci : -1;
+  double y = 0.0;
+  __syncwarp();
+#pragma unroll
+  for (int s = 0; s < 3; s++) {   // position q of every chain, deepest first
+    const int q = 2 - s;
+    double* st = stage + (s & 1) * TREE_STAGE;
+    if (pos == q) {
+      double d = R.c[q];
+      if (d < HMJ_MINVAL) d = HMJ_MINVAL;
+      const double inv = rsqrt(d);
+      R.inv = inv;
+#pragma unroll
+      for (int j = 0; j < 6; j++) { R.r[j] *= inv; st[ci * 10 + j] = R.r[j]; }
+#pragma unroll
+      for (int t = 0; t < q; t++) { R.c[t] *= inv; st[ci * 10 + 6 + t] = R.c[t]; }
+      R.c[q] = d * inv;
+      y = b * inv;
+      st[ci * 10 + 9] = y;
+    }
+    __syncwarp();
+    if (chain && pos < q) {
+      const double* u = st + ci * 10;
+      const double ui = u[6 + pos];
+#pragma unroll
+      for (int j = 0; j < 6; j++) R.r[j] -= ui * u[j];
+#pragma unroll
+      for (int t = 0; t < q; t++) R.c[t] -= ui * u[6 + t];   // entries past this lane's position are never read
+      b -= ui * u[9];
+    } else if (lane < 6) {
+#pragma unroll
+      for (int cc = 0; cc < 4; cc++) {
+        const double* u = st + cc * 10;
+        const double ui = u[lane];
+#pragma unroll
+        for (int j = 0; j < 6; j++) R.r[j] -= ui * u[j];      // columns past the diagonal are never read
+        b -= ui * u[9];
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 5; k >= 0; k--) {   // the root block
+    double* st = stage + (k & 1) * TREE_STAGE;
+    if (lane == k) {
+      double d = R.r[k];
+      if (d < HMJ_MINVAL) d = HMJ_MINVAL;
+      const double inv = rsqrt(d);
+      R.inv = inv;
+#pragma unroll
+      for (int j = 0; j < k; j++) { R.r[j] *= inv; st[j] = R.r[j]; }
+      R.r[k] = d * inv;
+      y = b * inv;
+      st[6] = y;
+    }
+    __syncwarp();
+    if (lane < k) {
+      const double ui = st[lane];
+#pragma unroll
+      for (int j = 0; j < k; j++) R.r[j] -= ui * st[j];
+      b -= ui * st[6];
+    }
+  }
+  // L x = y: root rows in order, then down the chains
+  double acc = y, x = 0.0;
+#pragma unroll
+  for (int k = 0; k < 6; k++) {
+    const double xk = __shfl_sync(FULL, acc * R.inv, k);
+    if (lane == k) x = xk;
+    else if (lane > k && lane < NV) acc -= R.r[k] * xk;
+  }
+#pragma unroll
+  for (int q = 0; q < 3; q++) {
+    const double xq = __shfl_sync(FULL, acc * R.inv, chain ? 6 + 3 * ci + q : lane);
+    if (pos == q) x = xq;
+    else if (pos > q) acc -= R.c[q] * xq;
+  }
+  return lane < NV ? x : 0.0;
+}
+
+// x = (L' L)^-1 b with the factor rows already in R (k_factor -> mj_Euler)
+__device__ __forceinline__ double tree_solve(const TreeRow& R, double* stage, double b, int lane) {
+  const unsigned FULL = 0xffffffffu;
+  const bool chain = lane >= 6 && lane < NV;
+  const int ci = chain ? (lane - 6) / 3 : 0, pos = chain ? (lane - 6) - 3 * ci : -1;
+  double y = 0.0;
+  __syncwarp();
+#pragma unroll
+  for (int s = 0; s < 3; s++) {
+    const int q = 2 - s;
+    double* st = stage + (s & 1) * TREE_STAGE;
+    if (pos == q) {
+      y = b * R.inv;
+#pragma unroll
+      for (int j = 0; j < 6; j++) st[ci * 10 + j] = R.r[j] * y;
+#pragma unroll
+      for (int t = 0; t < q; t++) st[ci * 10 + 6 + t] = R.c[t] * y;
+    }
+    __syncwarp();
+    if (chain && pos < q) b -= st[ci * 10 + 6 + pos];
+    else if (lane < 6) b -= ((st[lane] + st[10 + lane]) + (st[20 + lane] + st[30 + lane]));
+  }
+#pragma unroll
+  for (int k = 5; k >= 0; k--) {
+    double* st = stage + (k & 1) * TREE_STAGE;
+    if (lane == k) {
+      y = b * R.inv;
+#pragma unroll
+      for (int j = 0; j < k; j++) st[j] = R.r[j] * y;
+    }
+    __syncwarp();
+    if (lane < k) b -= st[lane];
+  }
+  double acc = y, x = 0.0;
+#pragma unroll
+  for (int k = 0; k < 6; k++) {
+    const double xk = __shfl_sync(FULL, acc * R.inv, k);
+    if (lane == k) x = xk;
+    else if (lane > k && lane < NV) acc -= R.r[k] * xk;
+  }
+#pragma unroll
+  for (int q = 0; q < 3; q++) {
+    const double xq = __shfl_sync(FULL, acc * R.inv, chain ? 6 + 3 * ci + q : lane);
+    if (pos == q) x = xq;
+    else if (pos > q) acc -= R.c[q] * xq;
+  }
+  return lane < NV ? x : 0.0;
+}
+
 __device__ __noinline__ double mat_vec(const double* A, const double* v, int lane) {
   double s = 0.0;
   if (lane < NV) {
@@ -336,6 +500,23 @@ __global__ void __launch_bounds__(32) k_factor(const hmj_tables_t* __restrict__ 
   }
   const double qfs = lane < NV ? B.qfrc_smooth[(size_t)env * NV + lane] : 0.0;
   __syncwarp();
+  if (T->tree_chol) {   // M and M + h diag(damping) have the tree's sparsity: 9 pivot steps each instead of 18
+    TreeRow R;
+    tree_load(R, S.M, lane, 0.0);
+    const double qa = tree_factor_solve(R, &S.chol.col[0][0], qfs, lane);
+    if (lane < NV) B.qacc_smooth[(size_t)env * NV + lane] = qa;
+    tree_load(R, S.M, lane, lane < NV ? h * M.dof_damping[lane] : 0.0);
+    tree_factor_solve(R, &S.chol.col[0][0], 0.0, lane);
+    double* F = B.euler_factor + (size_t)env * FAC_DOUBLES;   // [10][NV]: r[0..5], c[0..2], 1 / diagonal of every row
+    if (lane < NV) {
+#pragma unroll
+      for (int j = 0; j < 6; j++) F[j * NV + lane] = R.r[j];
+#pragma unroll
+      for (int t = 0; t < 3; t++) F[(6 + t) * NV + lane] = R.c[t];
+      F[9 * NV + lane] = R.inv;
+    }
+    return;
+  }
   for (int t = lane; t < NV * LD; t += 32) S.H[t] = S.M[t];
   const double qas = chol_factor_solve(S.H, &S.chol, qfs, lane);
   if (lane < NV) B.qacc_smooth[(size_t)env * NV + lane] = qas;
@@ -978,7 +1159,18 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
   // ---------------- mj_Euler with implicit joint damping: (M + h diag(b)) a = qfrc_smooth + qfrc_constraint,
   // with the factor k_factor left in B.euler_factor
   __syncwarp();
-  {
+  double qacc_e;
+  if (T->tree_chol) {
+    const double* F = B.euler_factor + (size_t)env * FAC_DOUBLES;
+    TreeRow R;
+    const int li = lane < NV ? lane : 0;
+#pragma unroll
+    for (int j = 0; j < 6; j++) R.r[j] = F[j * NV + li];
+#pragma unroll
+    for (int t = 0; t < 3; t++) R.c[t] = F[(6 + t) * NV + li];
+    R.inv = F[9 * NV + li];
+    qacc_e = tree_solve(R, &S.chol.col[0][0], qfs + qfc, lane);
+  } else {
     const double* F = B.euler_factor + (size_t)env * FAC_DOUBLES;
     double fe[(NTRI + 31) / 32];
     const double fi = F[NTRI + (lane < NV ? lane : 0)];
@@ -990,9 +1182,9 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
       if (t < NTRI) S.H[T->tri_i[t] * LD + T->tri_j[t]] = fe[k];
     }
     if (lane < NV) S.chol.invd[lane] = fi;
+    __syncwarp();
+    qacc_e = chol_solve_only(S.H, S.chol.invd, qfs + qfc, lane);
   }
-  __syncwarp();
-  const double qacc_e = chol_solve_only(S.H, S.chol.invd, qfs + qfc, lane);
   PH(11);
   if (lane < NV) {
     qvel += h * qacc_e;

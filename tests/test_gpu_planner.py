@@ -383,7 +383,23 @@ def test_noisy_rollouts_and_robust_planner(hmj, oracle):
                                             0.5, 0.1, xnoise[k])
         assert not fail
     rel = np.abs(rp.noisy_return - ref) / np.maximum(np.abs(ref), 1.0)
-    assert np.median(rel) < 1e-9 and (rel < TOL_RETURN).sum() >= 11, rel
+    # 17 steps of a pushed robot in contact amplify rounding: a rollout may cross one of the reference algorithm's own
+    # discontinuities (profiles/r2_step_discontinuity_probe.txt).  Bar: the bulk agrees to 1e-9, and
+    # every rollout that does not agree to TOL_RETURN must be one where the ORACLE ITSELF answers differently when its
+    # start state moves by one unit in the last place.
+    off = np.nonzero(rel >= TOL_RETURN)[0]
+    assert np.median(rel) < 1e-9 and len(off) <= 3, rel
+    for k in off:
+        c = rp.candidates[k // 3]
+        moved = 0.0
+        for dof in (2, 7, 10, 13):
+            for side in (-np.inf, np.inf):
+                st = state.copy()
+                st[dof] = np.nextafter(st[dof], side)
+                r2, _ = oracle.rollout_noisy(st, time, pl.candidate_times, pl.candidate_values[c], H, pl.interpolation_,
+                                             0.5, 0.1, xnoise[k])
+                moved = max(moved, abs(r2 - ref[k]) / max(abs(ref[k]), 1.0))
+        assert moved >= TOL_RETURN, (k, rel[k], moved)
     # the wrench matters (the same candidate under three different noise draws gives three different returns)
     assert len(np.unique(rp.noisy_return[:3])) == 3 and abs(rp.noisy_return[0] - ret[rp.candidates[0]]) > 1e-9
     want = int(np.argmin(ref.reshape(4, 3).mean(axis=1)))
