@@ -296,6 +296,19 @@ __device__ __forceinline__ double tree_solve(const TreeRow& R, double* stage, do
   return lane < NV ? x : 0.0;
 }
 
+// the same with the rows read from k_factor's record ([10][NV]: r[0..5], c[0..2], 1 / diagonal).  Out of line: once per
+// env-step, and its ten row registers stay out of the solver's allocation.
+__device__ __noinline__ double tree_solve_stored(const double* __restrict__ F, double* stage, double b, int lane) {
+  TreeRow R;
+  const int li = lane < NV ? lane : 0;
+#pragma unroll
+  for (int j = 0; j < 6; j++) R.r[j] = F[j * NV + li];
+#pragma unroll
+  for (int t = 0; t < 3; t++) R.c[t] = F[(6 + t) * NV + li];
+  R.inv = F[9 * NV + li];
+  return tree_solve(R, stage, b, lane);
+}
+
 __device__ __noinline__ double mat_vec(const double* A, const double* v, int lane) {
   double s = 0.0;
   if (lane < NV) {
@@ -1161,15 +1174,7 @@ k_solve(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int integrate) {
   __syncwarp();
   double qacc_e;
   if (T->tree_chol) {
-    const double* F = B.euler_factor + (size_t)env * FAC_DOUBLES;
-    TreeRow R;
-    const int li = lane < NV ? lane : 0;
-#pragma unroll
-    for (int j = 0; j < 6; j++) R.r[j] = F[j * NV + li];
-#pragma unroll
-    for (int t = 0; t < 3; t++) R.c[t] = F[(6 + t) * NV + li];
-    R.inv = F[9 * NV + li];
-    qacc_e = tree_solve(R, &S.chol.col[0][0], qfs + qfc, lane);
+    qacc_e = tree_solve_stored(B.euler_factor + (size_t)env * FAC_DOUBLES, &S.chol.col[0][0], qfs + qfc, lane);
   } else {
     const double* F = B.euler_factor + (size_t)env * FAC_DOUBLES;
     double fe[(NTRI + 31) / 32];
