@@ -116,6 +116,14 @@ struct SFrame {
   __device__ __forceinline__ void setM(int k, double v) { b[(3 + k) * NARROW_THREADS] = v; }
 };
 
+#ifdef HMJ_PHASE_PROF
+__device__ unsigned long long hmj_sup_stat[10];   // support calls, candidates scanned, histogram of list lengths by 8
+extern "C" int hmj_debug_sup_stat(unsigned long long* out) {
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out, hmj_sup_stat, sizeof(unsigned long long) * 10);
+  return 0;
+}
+#endif
 // ---- support through the direction-cell candidate lists (hmj_tables_t::sup_start / sup_vert, built in hmj_api.cu)
 struct SupTab { const uint16_t* start; const uint16_t* vert; };   // start == nullptr: no tables, scan the hull
 __device__ __forceinline__ SupTab sup_tab(const hmj_tables_t* __restrict__ T, int mesh) {
@@ -171,12 +179,25 @@ __device__ __forceinline__ void mesh_support(const double* __restrict__ sx, cons
   if (c >= 0) {
     int k = tab.start[c];
     const int k1 = tab.start[c + 1];
+#ifdef HMJ_PHASE_PROF
+    atomicAdd(&hmj_sup_stat[0], 1ull); atomicAdd(&hmj_sup_stat[1], (unsigned long long)(k1 - k));
+    atomicAdd(&hmj_sup_stat[2 + min((k1 - k) >> 3, 7)], 1ull);
+#endif
     double best = -HMJ_MAXVAL;
-#pragma unroll 2
-    for (; k < k1; k++) {
-      const int i = tab.vert[k];
-      const double va = ld0 * sx[h.base + i] + ld1 * sy[h.base + i] + ld2 * sz[h.base + i];
-      if (va > best) { best = va; i0 = i; }
+    // four candidates per round, their loads and products independent of one another (the lanes of a warp wait for the
+    // longest list among them); a short round repeats its last candidate, which cannot win (strict >, same value)
+#pragma unroll 1
+    for (; k < k1; k += 4) {
+      const int e = k1 - 1;
+      const int ia = tab.vert[k], ib = tab.vert[min(k + 1, e)], ic = tab.vert[min(k + 2, e)], id = tab.vert[min(k + 3, e)];
+      const double va = ld0 * sx[h.base + ia] + ld1 * sy[h.base + ia] + ld2 * sz[h.base + ia];
+      const double vb = ld0 * sx[h.base + ib] + ld1 * sy[h.base + ib] + ld2 * sz[h.base + ib];
+      const double vc = ld0 * sx[h.base + ic] + ld1 * sy[h.base + ic] + ld2 * sz[h.base + ic];
+      const double vd = ld0 * sx[h.base + id] + ld1 * sy[h.base + id] + ld2 * sz[h.base + id];
+      if (va > best) { best = va; i0 = ia; }
+      if (vb > best) { best = vb; i0 = ib; }
+      if (vc > best) { best = vc; i0 = ic; }
+      if (vd > best) { best = vd; i0 = id; }
     }
   } else {
     i0 = hull_argmax(sx, sy, sz, h.base, h.n4, ld0, ld1, ld2);

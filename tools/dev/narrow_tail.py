@@ -43,3 +43,9 @@ if hasattr(b.lib, "hmj_debug_narrow_q"):
     # counters run since process start: report fractions
     print(f"queries with contact: {q[0]:.0f} (mean trips {q[1]/max(q[0],1):.1f}, max {q[2]:.0f}); without: {q[3]:.0f} (mean trips {q[4]/max(q[3],1):.1f}, max {q[5]:.0f})")
     print("no-contact exits proving a separation gap > 1e-9 / 1e-6 / 1e-4 / 1e-3:", (q[6:10] / max(q[3], 1)).round(3).tolist())
+if hasattr(b.lib, "hmj_debug_sup_stat"):
+    st = np.zeros(10, dtype=np.uint64)
+    b.lib.hmj_debug_sup_stat.argtypes = [C.c_void_p]
+    b.lib.hmj_debug_sup_stat(st.ctypes.data)
+    st = st.astype(np.float64)
+    print(f"support calls {st[0]:.0f}, mean candidates {st[1]/max(st[0],1):.1f}; list length histogram by 8: {(st[2:]/max(st[0],1)).round(3).tolist()}")
