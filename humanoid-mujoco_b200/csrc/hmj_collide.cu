@@ -665,17 +665,44 @@ __device__ __forceinline__ int pack_task(int k, int ord, int r, int cmin, int s)
   return k | (ord << 6) | (r << 9) | (cmin << 12) | (s << 15);
 }
 
-// vertices [first, first + count) of the fp64 tables -> shared memory at the same offsets minus `first` (count and first are
-// multiples of 2: every mesh is padded to a multiple of 4), 16 bytes per thread and step
-__device__ __forceinline__ void stage_hulls(const hmj_tables_t* __restrict__ T, double* sx, double* sy, double* sz, int first, int count) {
-  const double2* gx = reinterpret_cast<const double2*>(T->dvx + first);
-  const double2* gy = reinterpret_cast<const double2*>(T->dvy + first);
-  const double2* gz = reinterpret_cast<const double2*>(T->dvz + first);
-  double2* tx = reinterpret_cast<double2*>(sx);
-  double2* ty = reinterpret_cast<double2*>(sy);
-  double2* tz = reinterpret_cast<double2*>(sz);
-  for (int i = threadIdx.x; i < (count >> 1); i += blockDim.x) { tx[i] = gx[i]; ty[i] = gy[i]; tz[i] = gz[i]; }
-  __syncthreads();
+// ---- hull vertices into shared memory with the bulk-copy engine (TMA, 1-D): one thread programs the copies against an
+// mbarrier and the CTA goes on with work that does not need the vertices (frames, bounding tests, fetching its first work
+// item); every thread waits on the barrier right before its first support call.  Sources and sizes are multiples of 16
+// bytes: every mesh starts at a multiple of 4 vertices and is padded to a multiple of 4 (hmj_api.cu: build_tables).
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(bar)));
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_load(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_addr(dst)),
+               "l"(src), "r"(bytes), "r"(smem_addr(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t phase) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "HMJ_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra HMJ_DONE;\n"
+      "bra HMJ_WAIT;\n"
+      "HMJ_DONE:\n"
+      "}\n" ::"r"(smem_addr(bar)),
+      "r"(phase)
+      : "memory");
+}
+// vertices [first, first + count) of the fp64 tables -> sx / sy / sz at offset 0; call from ONE thread after mbar_init
+__device__ __forceinline__ void stage_hulls_async(const hmj_tables_t* __restrict__ T, double* sx, double* sy, double* sz, int first,
+                                                  int count, uint64_t* bar) {
+  const uint32_t bytes = (uint32_t)count * 8u;
+  mbar_expect(bar, 3u * bytes);
+  bulk_load(sx, T->dvx + first, bytes, bar);
+  bulk_load(sy, T->dvy + first, bytes, bar);
+  bulk_load(sz, T->dvz + first, bytes, bar);
 }
 
 // warp-aggregated append of (env, word) to task group g for the lanes with `hit`
@@ -761,9 +788,12 @@ k_broad(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int npad, int kpos0
     return;
   }
   // ---- hfield pair.  NOTE: k_broad is launched with hfield pairs in their own CTAs (npad is a multiple of
-  // BROAD_THREADS), so the barrier inside stage_hulls is reached by whole CTAs only.
+  // BROAD_THREADS), so the barrier below is reached by whole CTAs only.
   // this CTA works on ONE pair, i.e. one hull: only that hull is staged (at offset 0)
-  stage_hulls(T, sx, sy, sz, T->mesh_adr[M.geom_meshid[g2]], T->mesh_npad[M.geom_meshid[g2]]);
+  __shared__ uint64_t bar;
+  if (threadIdx.x == 0) mbar_init(&bar);
+  __syncthreads();
+  if (threadIdx.x == 0) stage_hulls_async(T, sx, sy, sz, T->mesh_adr[M.geom_meshid[g2]], T->mesh_npad[M.geom_meshid[g2]], &bar);
   const double* size1 = M.hfield_size;
   const int nrow = M.hfield_nrow, ncol = M.hfield_ncol;
   const float* data = B.params[env].hfield_data;
@@ -779,6 +809,7 @@ k_broad(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int npad, int kpos0
     if (size1[2] < f2.pos[2] - r2 - 0.0) active = false;
     if (-size1[3] > f2.pos[2] + r2 + 0.0) active = false;
   }
+  mbar_wait(&bar, 0);   // the hull is in shared memory (also before leaving: no CTA exits with a copy in flight)
   if (!__any_sync(0xffffffffu, active)) return;
   double lo[3], hi[3];
   mesh_aabb(sx, sy, sz, h2, tab2, f2, lo, hi);
@@ -1180,7 +1211,11 @@ k_narrow(const hmj_tables_t* __restrict__ T, hmj_buffers_t B) {
 #ifdef HMJ_PHASE_PROF
   const long long w_t0 = clock64();
 #endif
-  stage_hulls(T, sx, sy, sz, 0, T->mesh_adr[HMJ_NMESH]);
+  __shared__ uint64_t bar;
+  if (threadIdx.x == 0) mbar_init(&bar);
+  __syncthreads();
+  if (threadIdx.x == 0) stage_hulls_async(T, sx, sy, sz, 0, HMJ_NVERT_SMEM, &bar);   // dvx | dvy | dvz whole: 3 x 8.4 KB
+  bool staged = false;
 #ifdef HMJ_PHASE_PROF
   const long long w_t1 = clock64();
 #endif
@@ -1191,6 +1226,7 @@ k_narrow(const hmj_tables_t* __restrict__ T, hmj_buffers_t B) {
     if (lane == 0) item = atomicAdd(&B.wq_count[63], 1);
     item = __shfl_sync(0xffffffffu, item, 0);
     if (item >= total) break;
+    if (!staged) { mbar_wait(&bar, 0); staged = true; }   // the copy ran beside the schedule look-up and the hand-out
 #ifdef HMJ_PHASE_PROF
     const long long i_t0 = clock64();
     trips_ = 0;
@@ -1220,6 +1256,7 @@ k_narrow(const hmj_tables_t* __restrict__ T, hmj_buffers_t B) {
     }
 #endif
   }
+  if (!staged) mbar_wait(&bar, 0);   // no warp leaves with the copy into its CTA's shared memory in flight
 #ifdef HMJ_PHASE_PROF
   if (lane == 0) {
     const unsigned long long dt = (unsigned long long)(clock64() - w_t0);
