@@ -218,13 +218,21 @@ __device__ __forceinline__ void hull_extent(const double* __restrict__ sx, const
   const int cp = tab.start ? sup_cell(r0, r1, r2) : -1;
   if (cp >= 0) {
     const int cm = sup_cell(-r0, -r1, -r2);
-    for (int k = tab.start[cp]; k < tab.start[cp + 1]; k++) {
-      const int i = tab.vert[k];
-      mx = fmax(mx, r0 * sx[h.base + i] + r1 * sy[h.base + i] + r2 * sz[h.base + i]);
-    }
-    for (int k = tab.start[cm]; k < tab.start[cm + 1]; k++) {
-      const int i = tab.vert[k];
-      mn = fmin(mn, r0 * sx[h.base + i] + r1 * sy[h.base + i] + r2 * sz[h.base + i]);
+    // both lists two candidates per round, loads and products independent (a short round repeats its last candidate:
+    // min / max do not care)
+    int kp = tab.start[cp], km = tab.start[cm];
+    const int ep = tab.start[cp + 1] - 1, em = tab.start[cm + 1] - 1;
+#pragma unroll 1
+    while (kp <= ep || km <= em) {
+      const int ia = tab.vert[min(kp, ep)], ib = tab.vert[min(kp + 1, ep)];
+      const int ic = tab.vert[min(km, em)], id = tab.vert[min(km + 1, em)];
+      const double va = r0 * sx[h.base + ia] + r1 * sy[h.base + ia] + r2 * sz[h.base + ia];
+      const double vb = r0 * sx[h.base + ib] + r1 * sy[h.base + ib] + r2 * sz[h.base + ib];
+      const double vc = r0 * sx[h.base + ic] + r1 * sy[h.base + ic] + r2 * sz[h.base + ic];
+      const double vd = r0 * sx[h.base + id] + r1 * sy[h.base + id] + r2 * sz[h.base + id];
+      mx = fmax(mx, fmax(va, vb));
+      mn = fmin(mn, fmin(vc, vd));
+      kp += 2; km += 2;
     }
   } else {
     for (int i = 0; i < h.n4; i++) {
