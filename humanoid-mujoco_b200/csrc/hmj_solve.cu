@@ -318,6 +318,12 @@ __device__ __noinline__ double mat_vec(const double* A, const double* v, int lan
   return s;
 }
 
+// pow for the impedance curve: the exponents that occur are solimp[4] = 2 (default) and solimp[4] - 1 = 1, where pow is
+// exactly x * x and x; anything else goes through an out-of-line call (the inlined pow was 5 KB of code in the set-up
+// stream of every solver warp, four times over)
+__device__ __noinline__ double pow_general(double x, double p) { return pow(x, p); }
+__device__ __forceinline__ double pow_imp(double x, double p) { return p == 2.0 ? x * x : (p == 1.0 ? x : pow_general(x, p)); }
+
 __device__ __forceinline__ void get_impedance(const double* solimp, double pos, double margin, double* imp) {
   if (solimp[0] == solimp[1] || solimp[2] <= HMJ_MINVAL) { *imp = 0.5 * (solimp[0] + solimp[1]); return; }
   double x = (pos - margin) / solimp[2];
@@ -327,11 +333,11 @@ __device__ __forceinline__ void get_impedance(const double* solimp, double pos, 
   if (solimp[4] == 1) {
     y = x;
   } else if (x <= solimp[3]) {
-    double a = 1 / pow(solimp[3], solimp[4] - 1);
-    y = a * pow(x, solimp[4]);
+    double a = 1 / pow_imp(solimp[3], solimp[4] - 1);
+    y = a * pow_imp(x, solimp[4]);
   } else {
-    double b = 1 / pow(1 - solimp[3], solimp[4] - 1);
-    y = 1 - b * pow(1 - x, solimp[4]);
+    double b = 1 / pow_imp(1 - solimp[3], solimp[4] - 1);
+    y = 1 - b * pow_imp(1 - x, solimp[4]);
   }
   *imp = solimp[0] + y * (solimp[1] - solimp[0]);
 }
