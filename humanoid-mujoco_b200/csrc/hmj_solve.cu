@@ -81,6 +81,39 @@ struct SolveSmem {
 //   * the forward substitution rides along (column j of L is final when pivot j is done); L is published to shared
 //     memory for the backward substitution, which walks columns.
 // On return H holds L (lower triangle; entries above the diagonal are garbage), S.invd the reciprocal diagonal.
+// one pivot of chol_factor_solve; MC = how many of the rotated row entries are still alive (NV - 1 - j at pivot j, rounded
+// up to the phase's bound): the rank-1 update touches only those
+template <int MC>
+__device__ __forceinline__ void chol_pivot(double (&a)[NV], double& dj, double& x, double& yv, double* H, CholScratch* C, int j,
+                                           int lane) {
+  const unsigned FULL = 0xffffffffu;
+  if (dj < HMJ_MINVAL) dj = HMJ_MINVAL;
+  const double inv = rsqrt(dj);
+  const double lij = (lane == j) ? dj * inv : a[0] * inv;   // a[0] is this row's entry of column j
+  // next pivot's diagonal, formed by its owner lane (j + 1) ahead of the column broadcast: this shuffle -> rsqrt ->
+  // scale -> FMA is the only loop-carried chain; the staged broadcast below runs beside the next rsqrt
+  const double dnext = a[1] - lij * lij;
+  dj = __shfl_sync(FULL, dnext, (j + 1) & 31);
+  double* col = C->col[j & 1];
+  double* xb = C->xb[j & 1];
+  col[lane] = lij;
+  xb[lane] = x;
+  if (lane >= j && lane < NV) H[lane * LD + j] = lij;
+  if (lane == 0) C->invd[j] = inv;
+  __syncwarp();
+  const double* cj = col + j;                                // cj[m] = l(j + m, j)
+  double cm[MC];                                             // all broadcast loads in flight before the first FMA
+#pragma unroll
+  for (int m = 1; m <= MC; m++) cm[m - 1] = cj[m];
+#pragma unroll
+  for (int m = 1; m <= MC; m++) a[m - 1] = a[m] - lij * cm[m - 1];
+  // forward substitution step j: y_j = x_j / l_jj, then x_i -= l_ij y_j for i > j
+  const double xj = xb[j] * inv;
+  yv = (lane == j) ? xj : yv;
+  const double lm = (lane > j) ? lij : 0.0;
+  x = x - lm * xj;
+}
+
 __device__ __forceinline__ double chol_factor_solve(double* H, CholScratch* C, double x, int lane) {
   const unsigned FULL = 0xffffffffu;
   const int row = lane < NV ? lane : NV - 1;
@@ -90,34 +123,15 @@ __device__ __forceinline__ double chol_factor_solve(double* H, CholScratch* C, d
   for (int k = 0; k < NV; k++) a[k] = H[row * LD + k];
   double yv = 0.0;
   double dj = __shfl_sync(FULL, a[0], 0);
+  // three phases of six pivots: the remaining matrix shrinks, and so does the update (17, 11, 5 entries per row instead
+  // of 17 throughout: a third of the loop's broadcast loads and FMAs gone; same operations on the live entries)
+  static_assert(NV == 18, "phases are written for 18 dofs");
 #pragma unroll 1
-  for (int j = 0; j < NV; j++) {
-    if (dj < HMJ_MINVAL) dj = HMJ_MINVAL;
-    const double inv = rsqrt(dj);
-    const double lij = (lane == j) ? dj * inv : a[0] * inv;   // a[0] is this row's entry of column j
-    // next pivot's diagonal, formed by its owner lane (j + 1) ahead of the column broadcast: this shuffle -> rsqrt ->
-    // scale -> FMA is the only loop-carried chain; the staged broadcast below runs beside the next rsqrt
-    const double dnext = a[1] - lij * lij;
-    dj = __shfl_sync(FULL, dnext, (j + 1) & 31);
-    double* col = C->col[j & 1];
-    double* xb = C->xb[j & 1];
-    col[lane] = lij;
-    xb[lane] = x;
-    if (lane >= j && lane < NV) H[lane * LD + j] = lij;
-    if (lane == 0) C->invd[j] = inv;
-    __syncwarp();
-    const double* cj = col + j;                                // cj[m] = l(j + m, j)
-    double cm[NV - 1];                                         // all 17 broadcast loads in flight before the first FMA
-#pragma unroll
-    for (int m = 1; m < NV; m++) cm[m - 1] = cj[m];
-#pragma unroll
-    for (int m = 1; m < NV; m++) a[m - 1] = a[m] - lij * cm[m - 1];
-    // forward substitution step j: y_j = x_j / l_jj, then x_i -= l_ij y_j for i > j
-    const double xj = xb[j] * inv;
-    yv = (lane == j) ? xj : yv;
-    const double lm = (lane > j) ? lij : 0.0;
-    x = x - lm * xj;
-  }
+  for (int j = 0; j < 6; j++) chol_pivot<17>(a, dj, x, yv, H, C, j, lane);
+#pragma unroll 1
+  for (int j = 6; j < 12; j++) chol_pivot<11>(a, dj, x, yv, H, C, j, lane);
+#pragma unroll 1
+  for (int j = 12; j < 18; j++) chol_pivot<5>(a, dj, x, yv, H, C, j, lane);
   __syncwarp();
   // backward substitution: lane k publishes x_k = y_k / l_kk, lanes below it eliminate column k
   x = yv;
