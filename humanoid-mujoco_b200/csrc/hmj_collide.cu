@@ -9,15 +9,15 @@
 //             hull AABB, strip walk over the prisms under the AABB, and the FIRST support call of every prism's
 //             MPR query (where 64 % of them end).  Survivors are appended to task lists grouped by hull
 //             (warp-aggregated atomics); the per-env slot bitmask (zeroed before the launch) marks the slots k_narrow fills.
-//   k_narrow  persistent warps; a work item is 32 tasks OF THE SAME GROUP, ONE MPR QUERY PER LANE.  The
-//             hull(s) are therefore warp-uniform: the exhaustive support scan reads each vertex once per
-//             warp (shared memory broadcast, fp64 SoA) while every lane evaluates it against its own
-//             direction.  MPR is written as a state machine with exactly one support call per trip, so
-//             lanes in different phases (discover / refine / penetration) stay converged on the scan,
-//             which is >90 % of the arithmetic; the portal logic runs per lane, not redundantly.  When few
-//             lanes of a warp are still iterating, the scan switches to a 32-lane cooperative arg-max per
-//             remaining query.  A contact's slot is fixed by (pair, prism ordinal), so the contact order
-//             k_solve compacts is MuJoCo's regardless of which warp produced it.
+//   k_narrow  persistent warps; a work item is up to 32 tasks OF THE SAME GROUP, ONE MPR QUERY PER LANE.  MPR is
+//             written as a state machine with exactly one support call per trip, so lanes in different phases
+//             (discover / refine / penetration) meet at the support call; the portal logic runs per lane.
+//             A contact's slot is fixed by (pair, prism ordinal), so the contact order k_solve compacts is MuJoCo's
+//             regardless of which warp produced it.
+// Support calls do not scan the hull: every hull carries, per cell of a 6 x 8 x 8 cube map of directions, the list of
+// vertices that can be the support point for some direction of the cell (hmj_api.cu: build_support_cells), and the
+// arg-max runs over that list (2-4 vertices on average) with the scan's own expression and tie rule: same vertex, same
+// bits.  Hull vertices sit in shared memory (fp64 SoA), brought in by the bulk-copy engine while the CTA sets up.
 //
 // THIS TRANSLATION UNIT IS COMPILED WITH -fmad=false: contact count and geom pairs must be
 // bit-identical to the reference path, so every expression is the same sequence of IEEE-754
@@ -875,14 +875,13 @@ k_broad(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int npad, int kpos0
 }
 
 // ------------------------------------------------------------------ broadphase of the height-field pairs, small batches
-// The same work as the height-field branch of k_broad with ONE WARP per (pair, env) instead of one thread: the hull
-// scans — the bounding box in the height field's frame and the first support call of every prism — are split over the 32
-// lanes (k_broad's threads walk 200 vertices one after the other, 1 + #prisms times: 25 us of pure latency when the
-// batch is too small to hide it, which is the planner's case).  Lane p owns prism p of the strip walk; its slot ordinal
-// is its rank among the tested prisms, so tasks and slots are exactly k_broad's.  Bounding-box extrema are min / max
-// reductions (order-free), the support arg-max is mesh_support_coop (bit-identical to the serial scan): same contacts.
-// Vertices are read from the fp64 tables in global memory (25 KB, L1-resident); 4 warps per CTA.
-#define BROAD_COOP_MAX_N 512    /* launcher uses this kernel up to this batch size (measured: +11 % at 10-64 samples, +8 % at 256, -4 % at 1024) */
+// The same work as the height-field branch of k_broad with ONE WARP per (pair, env) instead of one thread: lane p owns
+// prism p of the strip walk (k_broad's thread walks them one after the other: pure latency when the batch is too small
+// to hide it, which is the planner's case); its slot ordinal is its rank among the tested prisms, so tasks and slots are
+// exactly k_broad's.  The bounding box is computed by every lane alike (a handful of candidates, broadcast loads), the
+// first support call of a prism by its lane.  Vertices are read from the fp64 tables in global memory (25 KB,
+// L1-resident); 4 warps per CTA.
+#define BROAD_COOP_MAX_N 512    /* launcher uses this kernel up to this batch size (measured with the candidate lists: +4 % at 10-64 samples, even at 256) */
 __global__ void __launch_bounds__(128)
 k_broad_hf_coop(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int nhf) {
   const unsigned FULL = 0xffffffffu;
@@ -1176,9 +1175,9 @@ k_narrow(const hmj_tables_t* __restrict__ T, hmj_buffers_t B) {
   const int lane = threadIdx.x & 31;
   // work items: group g contributes ceil(count[g] / isz); groups are numbered across TWO registers per lane.
   // The item size isz (tasks per warp) is the smallest of 4 / 8 / 16 / 32 that still gives every item its own warp:
-  // a step has a few thousand queries against 1184 resident warps, and an MPR trip costs the whole warp ~25 n cycles
-  // lane-serial but only ~(n + 700) per 4 queries with the cooperative scan, so short items cut the query-chain
-  // latency that bounds this kernel.  Every query is independent: the item size never changes a result bit.
+  // a step has a few thousand to tens of thousands of queries against 1184 resident warps, and a trip costs a warp the
+  // more the more of its lanes are in different MPR phases (3-6 k cycles at 16 lanes), so short items cut the
+  // query-chain latency that bounds this kernel.  Every query is independent: the item size never changes a result bit.
   // Lane l holds schedule positions l and l + 32; position p is group T->group_order[p] (most expensive first).
   const int ga = T->group_order[lane];
   const int gb = (lane + 32 < HMJ_NGROUP) ? T->group_order[lane + 32] : 0;
