@@ -21,6 +21,7 @@ dt = 0.002, one mj_step + observation/reward epilogue per env-step.
 from __future__ import annotations
 
 import argparse
+import gc
 import json
 import os
 import subprocess
@@ -597,6 +598,10 @@ def run_gpu(args):
         host_actions[...] = np.random.default_rng(5 + rank).uniform(-scale, scale, host_actions.shape)
         for s in range(W):
             env.step(host_actions[s % host_actions.shape[0]])
+        # the interpreter's cyclic collector can fire inside a 6 ms timed region and cost a millisecond on this heap
+        # (torch + numpy loaded): collect now and park the survivors, as a serving loop would at start-up
+        gc.collect()
+        gc.freeze()
         barrier()
         torch.cuda.synchronize()
         t0 = time.perf_counter()
