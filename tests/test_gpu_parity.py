@@ -244,3 +244,21 @@ def test_bench_workload_slices_against_oracle(hmj, oracle, regime):
         assert ncon1.mean() > 2.5
     oracle.lib.orc_default_params(oracle.model.ctypes.data, oracle.params.ctypes.data)
     b.close()
+
+
+def test_whole_hull_and_dense_fallbacks_match_too():
+    """The collision kernels fall back to scanning the whole hull when a support direction is degenerate or the candidate
+    tables are switched off, and k_factor / mj_Euler fall back to the dense Cholesky for a model without the tree
+    structure.  The fall-backs define what the shortcuts must reproduce: the bit-exact contact test and the one-step /
+    ten-step tests are run again in a fresh process with both developer switches set."""
+    import os
+    import subprocess
+    import sys
+
+    env = dict(os.environ, HMJ_SUP_CELLS_OFF="1", HMJ_TREE_CHOL_OFF="1")
+    here = os.path.dirname(os.path.abspath(__file__))
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(here, "test_gpu_parity.py"), "-m", "gpu", "-x", "-q", "-k",
+                        "narrowphase_bit_exact or forward_contacts or one_step_and_ten"], env=env, capture_output=True, text=True,
+                       timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "passed" in r.stdout
