@@ -362,6 +362,9 @@ void hmj_launch_solve(const hmj_tables_t* tab, hmj_buffers_t buf, int integrate,
                       const hmj_solve_ctx_t* ctx = nullptr, bool zero = true);
 
 // plan_mode bits for hmj_launch_smooth
+// internal, transient status bit: k_kin found a bad state this step (mj_resetData) and k_dyn still has to zero the controls
+// and the applied wrench of the env (k_kin leaves both alone so that their writers may run beside it); k_dyn clears it
+#define HMJ_STATUS_RESET_PENDING (1 << 30)
 #define HMJ_PLAN_COST 1    /* sensors -> residual -> cost accumulation */
 #define HMJ_PLAN_POLICY 2  /* ctrl from the spline policy at data time */
 #define HMJ_PLAN_XFRC 4    /* k_dyn also applies the per-body wrenches of xfrc_all */

@@ -187,13 +187,11 @@ k_kin(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int plan_mode, const 
   bool badq = __any_sync(FULL, d_is_bad(qp));
   bool badv = __any_sync(FULL, d_is_bad(qv));
   if (badq || badv) {  // mj_resetData semantics for this path (k_dyn starts after this kernel and sees the reset state)
-    status |= badq ? HMJ_STATUS_BADQPOS : HMJ_STATUS_BADQVEL;
+    status |= (badq ? HMJ_STATUS_BADQPOS : HMJ_STATUS_BADQVEL) | HMJ_STATUS_RESET_PENDING;   // ctrl and xfrc: zeroed by k_dyn
     qp = lane < HMJ_NQ ? M.qpos0[lane] : 0.0;
     qv = 0.0;
     if (lane < HMJ_NQ) g_qpos[lane] = qp;
     if (lane < HMJ_NV) { g_qvel[lane] = 0.0; B.warmstart[(size_t)env * HMJ_NV + lane] = 0.0; }
-    if (lane < HMJ_NU) g_ctrl[lane] = 0.0;
-    if (lane < 6) B.xfrc[(size_t)env * 6 + lane] = 0.0;
     if (lane == 0) B.time[env] = 0.0;
   }
   if (lane < HMJ_NQ) S.qpos[lane] = qp;
@@ -206,11 +204,12 @@ k_kin(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, int plan_mode, const 
       u = spline_sample1(spline_times, vals, HMJ_NU, nnode, interpolation, B.time[env]);
       u = fmin(fmax(u, M.act_ctrlrange[lane][0]), M.act_ctrlrange[lane][1]);  // Clamp (utilities.cc:94-98)
       g_ctrl[lane] = u;
-    } else {
-      u = g_ctrl[lane];
     }
   }
-  if (__any_sync(FULL, lane < HMJ_NU && d_is_bad(u))) {  // mjWARN_BADCTRL: controls zeroed
+  // mjWARN_BADCTRL (controls zeroed): checked here for the controls this kernel makes itself (the spline policy);
+  // caller-provided controls are checked by their consumer, k_dyn — this kernel does not read them, so whatever writes
+  // them (k_env_pre behind the action upload) can run beside it
+  if ((plan_mode & 2) && __any_sync(FULL, lane < HMJ_NU && d_is_bad(u))) {
     status |= HMJ_STATUS_BADCTRL;
     if (lane < HMJ_NU) g_ctrl[lane] = 0.0;
   }
@@ -365,7 +364,23 @@ k_dyn(const hmj_tables_t* __restrict__ T, hmj_buffers_t B, const hmj_task_t* __r
   // ---------------- state and the kinematic quantities k_kin left in L2; per-env parameters requested up front
   if (lane < HMJ_NQ) S.qpos[lane] = B.qpos[(size_t)env * HMJ_NQ + lane];
   if (lane < HMJ_NV) S.qvel[lane] = B.qvel[(size_t)env * HMJ_NV + lane];
-  if (lane < HMJ_NU) S.ctrl[lane] = B.ctrl[(size_t)env * HMJ_NU + lane];
+  {
+    // the tail of k_kin's mj_resetData: a bad state this step zeroes the controls and the applied wrench
+    const bool reset = (B.status[env] & HMJ_STATUS_RESET_PENDING) != 0;
+    if (reset) {
+      if (lane < HMJ_NU) B.ctrl[(size_t)env * HMJ_NU + lane] = 0.0;
+      if (lane < 6) B.xfrc[(size_t)env * 6 + lane] = 0.0;
+      __syncwarp();
+      if (lane == 0) atomicAnd(&B.status[env], ~HMJ_STATUS_RESET_PENDING);
+    }
+    const double u = (lane < HMJ_NU && !reset) ? B.ctrl[(size_t)env * HMJ_NU + lane] : 0.0;
+    const bool badu = !(plan_mode & 2) && __any_sync(FULL, lane < HMJ_NU && d_is_bad(u));   // mjWARN_BADCTRL: controls zeroed
+    if (lane < HMJ_NU) {
+      S.ctrl[lane] = badu ? 0.0 : u;
+      if (badu) B.ctrl[(size_t)env * HMJ_NU + lane] = 0.0;
+    }
+    if (badu && lane == 0) atomicOr(&B.status[env], HMJ_STATUS_BADCTRL);
+  }
   const double pf_mass = (lane >= 1 && lane < HMJ_NBODY) ? P->body_mass[lane] : 0.0;
   const double pf_arm = lane < HMJ_NV ? P->dof_armature[lane] : 0.0;
   const double pf_stiff = lane < HMJ_NV ? P->jnt_stiffness[M.dof_jntid[lane]] : 0.0;
