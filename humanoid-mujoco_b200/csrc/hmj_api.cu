@@ -120,7 +120,13 @@ struct hmj_batch_ {
   };
   cudaGraphExec_t ctrl_graph = nullptr;
   CtrlKey ctrl_key{};
-  int ctrl_mode = 1;                 // 0: prologue / epilogue as whole-batch kernels around the step graph (HMJ_E2E=0)
+  // the action upload of a control step runs on a stream of its own; the graph's prologue kernels wait for this event
+  // (an event-wait node), everything that does not need the actions (k_kin, the collision kernels) starts at once
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t h2d_event = nullptr;
+  bool ctrl_graph_waits_h2d = false;
+  int ctrl_mode = 2;                 // 2: control-step graph, action upload on the copy stream beside k_kin; 1: upload in front of the graph;
+                                     // 0: prologue / epilogue as whole-batch kernels around the step graph (HMJ_E2E)
   int graph_mode = 1;
   bool warmed = false;
   // per-kernel CUDA-event profiling (hmj_batch_profile): events bracket every launch of a step
@@ -490,6 +496,8 @@ extern "C" void hmj_batch_destroy(hmj_batch_t* b) {
   for (int k = 0; k < 2; k++)
     if (b->step_graph[k]) cudaGraphExecDestroy(b->step_graph[k]);
   if (b->ctrl_graph) cudaGraphExecDestroy(b->ctrl_graph);
+  if (b->copy_stream) { cudaStreamSynchronize(b->copy_stream); cudaStreamDestroy(b->copy_stream); }
+  if (b->h2d_event) cudaEventDestroy(b->h2d_event);
   for (auto& pp : b->pipes) {
     for (int k = 0; k < 2; k++) {
       if (pp.ctx.side[k]) cudaStreamDestroy(pp.ctx.side[k]);
@@ -540,6 +548,8 @@ extern "C" int hmj_batch_create(const hmj_model_t* model, int n_envs, int device
   b->device = device;
   b->buf.n = n_envs;
   CKB(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
+  CKB(cudaStreamCreateWithFlags(&b->copy_stream, cudaStreamNonBlocking));
+  CKB(cudaEventCreateWithFlags(&b->h2d_event, cudaEventDisableTiming));
   for (int k = 0; k < 2; k++) {
     CKB(cudaStreamCreateWithFlags(&b->solve_ctx.side[k], cudaStreamNonBlocking));
     CKB(cudaEventCreateWithFlags(&b->solve_ctx.join[k], cudaEventDisableTiming));
@@ -876,7 +886,13 @@ static void enqueue_control_chain(hmj_batch_t* b, int has_action, double rf, dou
       parts.push_back(Part{pp.view, pp.start, pp.stream, &pp.ctx});
     }
   }
-  for (auto& q : parts) hmj_launch_env_pre_rows(b->buf, b->env, d_action, rf, seed, q.start, q.view.n, q.stream);
+  // the prologue (action noise + FIFO -> ctrl, push scheduler -> xfrc) feeds k_dyn, not k_kin: it goes to the part's side
+  // stream, where k_dyn follows it, and runs beside k_kin (with the action upload in front of it: launch_control_graph)
+  for (auto& q : parts) {
+    cudaEventRecord(q.ctx->fork, q.stream);
+    cudaStreamWaitEvent(q.ctx->side[0], q.ctx->fork, 0);
+    hmj_launch_env_pre_rows(b->buf, b->env, d_action, rf, seed, q.start, q.view.n, q.ctx->side[0]);
+  }
   for (auto& q : parts) hmj_launch_smooth(b->tab_dev, q.view, b->task_dev, 0, nullptr, nullptr, 0, 0, 0, q.stream, q.ctx);
   for (auto& q : parts) hmj_launch_factor(b->tab_dev, q.view, q.stream, q.ctx);
   for (auto& q : parts) hmj_launch_collide(b->tab_dev, q.view, q.stream, false);
@@ -895,15 +911,41 @@ static void enqueue_control_chain(hmj_batch_t* b, int has_action, double rf, dou
 }
 
 // Replays (capturing it first when the scalars baked into it changed) the control-step graph.  false: not available.
-static bool launch_control_graph(hmj_batch_t* b, int has_action, double rf, double mst, unsigned long long seed, bool split) {
+static bool launch_control_graph(hmj_batch_t* b, int has_action, double rf, double mst, unsigned long long seed, bool split,
+                                 bool side_copy) {
   hmj_batch_::CtrlKey key;
-  key.has_action = has_action; key.split = split ? 1 : 0; key.rf = rf; key.mst = mst; key.seed = seed;
+  key.has_action = has_action; key.split = (split ? 1 : 0) + (side_copy ? 2 : 0); key.rf = rf; key.mst = mst; key.seed = seed;
   if (!b->ctrl_graph || !(key == b->ctrl_key)) {
     if (b->ctrl_graph) { cudaGraphExecDestroy(b->ctrl_graph); b->ctrl_graph = nullptr; }
     cudaGraph_t g = nullptr;
     if (cudaStreamBeginCapture(b->stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) { cudaGetLastError(); return false; }
     enqueue_control_chain(b, has_action, rf, mst, seed, split);
-    if (cudaStreamEndCapture(b->stream, &g) != cudaSuccess || !g || cudaGraphInstantiate(&b->ctrl_graph, g, 0) != cudaSuccess) {
+    bool ok = cudaStreamEndCapture(b->stream, &g) == cudaSuccess && g;
+    b->ctrl_graph_waits_h2d = false;
+    if (ok && side_copy) {
+      // an event-wait node in front of every prologue kernel: the action upload is recorded into h2d_event before each launch
+      size_t nn = 0;
+      std::vector<cudaGraphNode_t> nodes;
+      if (cudaGraphGetNodes(g, nullptr, &nn) == cudaSuccess && nn) {
+        nodes.resize(nn);
+        cudaGraphGetNodes(g, nodes.data(), &nn);
+      }
+      cudaGraphNode_t wait_node = nullptr;
+      int wired = 0;
+      if (cudaGraphAddEventWaitNode(&wait_node, g, nullptr, 0, b->h2d_event) == cudaSuccess) {
+        for (cudaGraphNode_t nd : nodes) {
+          cudaGraphNodeType ty;
+          cudaKernelNodeParams kp;
+          if (cudaGraphNodeGetType(nd, &ty) != cudaSuccess || ty != cudaGraphNodeTypeKernel) continue;
+          if (cudaGraphKernelNodeGetParams(nd, &kp) != cudaSuccess || kp.func != hmj_env_pre_kernel()) continue;
+          if (cudaGraphAddDependencies(g, &wait_node, &nd, 1) == cudaSuccess) wired++;
+        }
+      }
+      const int want = b->pipes.empty() ? 1 : (int)b->pipes.size();
+      if (wired == want) b->ctrl_graph_waits_h2d = true;
+      else { ok = false; cudaGetLastError(); }   // do not run a half-wired graph
+    }
+    if (!ok || cudaGraphInstantiate(&b->ctrl_graph, g, 0) != cudaSuccess) {
       if (g) cudaGraphDestroy(g);
       b->ctrl_graph = nullptr;
       cudaGetLastError();
@@ -1222,7 +1264,14 @@ extern "C" int hmj_env_step_fused_from(hmj_batch_t* b, const double* action_host
   double* d_time = d_out + N * 31;
   double* d_quat = d_out + N * 32;
   int32_t* d_flags = (int32_t*)(d_out + N * 36);
-  if (has_action && has_mask && (const char*)action_host == b->io_host) {
+  // the common call (one physics step, every env) replays the control-step graph; there the action upload goes to the copy
+  // stream and only the graph's prologue kernels wait for it (ctrl_mode 2)
+  const bool graph_path = b->ctrl_mode && !has_mask && nsteps == 1 && !b->profile && b->warmed && b->graph_mode != 0;
+  const bool side_copy = graph_path && has_action && b->ctrl_mode == 2;
+  if (side_copy) {
+    CK(cudaMemcpyAsync(d_action, action_host, N * HMJ_NU * 8, cudaMemcpyHostToDevice, b->copy_stream));
+    CK(cudaEventRecord(b->h2d_event, b->copy_stream));
+  } else if (has_action && has_mask && (const char*)action_host == b->io_host) {
     CK(cudaMemcpyAsync(b->io_dev, b->io_host, N * HMJ_NU * 8 + N * 4, cudaMemcpyHostToDevice, b->stream));  // action + mask in one copy
   } else {
     if (has_action) CK(cudaMemcpyAsync(d_action, action_host, N * HMJ_NU * 8, cudaMemcpyHostToDevice, b->stream));
@@ -1230,13 +1279,15 @@ extern "C" int hmj_env_step_fused_from(hmj_batch_t* b, const double* action_host
   }
   const int32_t* mask = has_mask ? d_mask : nullptr;
   const bool pool = b->pool_on && nsteps >= 0 && !has_mask;
-  // the common call (one physics step, every env) replays the control-step graph; its result copies are inside unless the
-  // episode pool still has to look at (and patch) the results
+  // the graph's result copies are inside unless the episode pool still has to look at (and patch) the results
   bool copied = false, done = false;
-  if (b->ctrl_mode && !has_mask && nsteps == 1 && !b->profile && b->warmed && b->graph_mode != 0) {
-    done = launch_control_graph(b, has_action, rf, max_sim_time, seed, !pool);
+  if (graph_path) {
+    done = launch_control_graph(b, has_action, rf, max_sim_time, seed, !pool, side_copy);
     if (done) copied = !pool;
-    else b->ctrl_mode = 0;   // capture unavailable: whole-batch kernels around the step graph from now on
+    else {
+      b->ctrl_mode = 0;   // capture unavailable: whole-batch kernels around the step graph from now on
+      if (side_copy) CK(cudaStreamWaitEvent(b->stream, b->h2d_event, 0));   // the kernels below need the upload
+    }
   }
   if (!done) {
     if (nsteps >= 0) hmj_launch_env_pre(b->buf, b->env, has_action ? d_action : nullptr, mask, rf, seed, b->stream);

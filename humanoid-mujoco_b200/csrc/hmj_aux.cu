@@ -329,6 +329,8 @@ void hmj_launch_env_pre(hmj_buffers_t buf, hmj_envstate_t env, const double* act
   k_env_pre<<<(buf.n + ENV_WARPS - 1) / ENV_WARPS, 32 * ENV_WARPS, 0, stream>>>(buf, env, action, mask, rf, seed, stream_id_offset, 0,
                                                                                 buf.n);
 }
+// address of the prologue kernel (hmj_api.cu looks its nodes up in the captured control-step graph)
+const void* hmj_env_pre_kernel() { return (const void*)k_env_pre; }
 // the same for envs [first, first + count) of the batch (`buf` is the whole batch)
 void hmj_launch_env_pre_rows(hmj_buffers_t buf, hmj_envstate_t env, const double* action, double rf, unsigned long long seed,
                              int first, int count, cudaStream_t stream) {

@@ -411,6 +411,7 @@ void hmj_launch_fd_diff(const hmj_tables_t* tab, hmj_buffers_t view, int nknot, 
 void hmj_launch_pool_mark_pending(hmj_pool_t pool, const int32_t* ids_dev, int count, int n, cudaStream_t stream);
 void hmj_launch_env_epilogue(const hmj_tables_t* tab, hmj_buffers_t buf, hmj_envstate_t env, double max_sim_time, hmj_results_t R,
                              int first, int count, cudaStream_t stream);
+const void* hmj_env_pre_kernel();
 void hmj_launch_env_pre_rows(hmj_buffers_t buf, hmj_envstate_t env, const double* action, double rf, unsigned long long seed,
                              int first, int count, cudaStream_t stream);
 void hmj_launch_env_post(hmj_buffers_t buf, hmj_envstate_t env, const int32_t* mask, double* obs, double* time_out, double* quat_out,
